@@ -1,0 +1,173 @@
+/* pmx.h -- C ABI of libpmx.so, the B200-native Prometheus aggregate engine.
+ *
+ * Drop-in boundary for the data path of k8s-rocm-metrics-dashboard.  The reference has no FFI
+ * of its own (it is one Python file); every entry point below names the reference lines
+ * (/root/reference/app.py) or the SURVEY.md section-8 row whose work it takes over.
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes, no exceptions across the boundary.
+ *   - every function returns 0 (PMX_OK) or a negative pmx_status; pmx_last_error() returns the
+ *     message of the calling thread's last failure.
+ *   - pointers named d_* are DEVICE pointers owned by the caller (e.g. torch tensors); the
+ *     library never frees or retains them.  Pointers named h_* are host pointers.
+ *   - every device entry point is asynchronous on `stream` (a cudaStream_t passed as void*);
+ *     ctx scratch is stream-ordered, so one ctx must be driven from one stream at a time.
+ *   - ts is int64 milliseconds; values are IEEE binary64; ragged series are CSR:
+ *     d_off[s]..d_off[s+1] index the flat d_ts/d_val arrays (int64, n_series+1 entries).
+ *   - [S,T] outputs are row-major, one row per series.  Output pointers may be NULL to skip
+ *     that output unless stated otherwise.
+ */
+#ifndef PMX_H
+#define PMX_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PMX_VERSION 100                      /* 0.1.0 */
+#define PMX_STALE_NAN_BITS 0x7FF0000000000002ULL   /* Prometheus staleness marker            */
+#define PMX_QUANTILE_DIGIT_BITS 11           /* radix-select digit: 2048-bin histograms      */
+#define PMX_QUANTILE_BINS 2048
+#define PMX_QUANTILE_PASSES 6                /* 11+11+11+11+11+9 = 64 key bits               */
+
+typedef enum pmx_status {
+  PMX_OK = 0,
+  PMX_E_INVALID = -1,      /* bad argument (NULL, negative size, misaligned pointer)          */
+  PMX_E_CUDA = -2,         /* a CUDA runtime call failed; message holds cudaGetErrorString    */
+  PMX_E_VALUE = -3,        /* malformed number  -> adapter raises ValueError (app.py:188)     */
+  PMX_E_KEY = -4,          /* missing label     -> adapter raises KeyError  (app.py:186-187)  */
+  PMX_E_CAPACITY = -5,     /* caller-provided output capacity too small                       */
+  PMX_E_JSON = -6,         /* body is not a Prometheus success response (json.loads failure)  */
+  PMX_E_LIMIT = -7         /* size beyond a documented limit of an entry point                */
+} pmx_status;
+
+typedef struct pmx_ctx pmx_ctx;             /* per (process, GPU): scratch + constant tables   */
+typedef void* pmx_stream;                   /* cudaStream_t                                   */
+
+int pmx_version(void);
+const char* pmx_last_error(void);
+/* Binds to CUDA device `device`; allocates nothing until an entry point needs scratch. */
+int pmx_ctx_create(int device, pmx_ctx** out);
+void pmx_ctx_destroy(pmx_ctx* ctx);
+/* Bytes of device scratch the ctx currently holds (grow-only, reused across calls). */
+size_t pmx_ctx_scratch_bytes(const pmx_ctx* ctx);
+
+/* ---- X1  Prometheus JSON ingestion (HOST).  Replaces json.loads at app.py:163,178 for the
+ * "result" array: finds every sample's timestamp / value token without building objects.
+ * Works for resultType "matrix" ("values":[[t,"v"],...]) and "vector" ("value":[t,"v"]).
+ *   h_ts_off[i], h_val_off[i] : byte offset of sample i's timestamp token (ends at ',') and of
+ *                               its value token (first byte after the opening quote; ends at '"')
+ *                               in the FLAT buffer = body followed by h_extra.
+ *   h_series_off[s]           : CSR sample offsets (n_series+1 entries).
+ *   h_metric_off/len[s]       : byte span of series s' "metric" object ({...}) in body.
+ *   h_extra                   : value tokens that contained JSON escapes, decoded; the caller
+ *                               appends h_extra[0..extra_len) to body to form the flat buffer.
+ * Capacities: cap_samples >= len/8+1 and cap_series >= len/24+1 and cap_extra >= len always
+ * suffice.  Returns PMX_E_JSON unless "status" is "success" and the shape is as above. */
+typedef struct pmx_tokenize_result {
+  int64_t n_samples, n_series, extra_len;
+  int32_t result_type;                      /* 0 = matrix, 1 = vector                          */
+} pmx_tokenize_result;
+int pmx_tokenize(const char* h_body, size_t len,
+                 uint32_t* h_ts_off, uint32_t* h_val_off, int64_t cap_samples,
+                 int64_t* h_series_off, uint32_t* h_metric_off, uint32_t* h_metric_len,
+                 int64_t cap_series, char* h_extra, size_t cap_extra,
+                 pmx_tokenize_result* res);
+
+/* ---- X2 / H2  value decode (K1).  Replaces float(metric["value"][1]) at app.py:188: decimal
+ * text -> binary64, correctly rounded, bit-exact with CPython float() for ASCII input (sign,
+ * digits with single underscores, '.', exponent, inf/infinity/nan in any case, surrounding
+ * ASCII whitespace).  d_first_bad (device int64, required) receives the smallest index of a
+ * malformed token or INT64_MAX; the adapter turns it into ValueError. */
+int pmx_parse_f64(pmx_ctx* ctx, const uint8_t* d_text, uint64_t text_len,
+                  const uint32_t* d_val_off, int64_t n, double* d_out,
+                  int64_t* d_first_bad, pmx_stream stream);
+/* Timestamp tokens (JSON numbers, seconds, at most 3 decimals) -> exact int64 ms. */
+int pmx_parse_ts_ms(pmx_ctx* ctx, const uint8_t* d_text, uint64_t text_len,
+                    const uint32_t* d_ts_off, int64_t n, int64_t* d_out,
+                    int64_t* d_first_bad, pmx_stream stream);
+
+/* ---- X3  step-aligned resample (K2).  grid g_j = start + j*step.  For each series and j:
+ * idx = (last sample with ts <= g_j); valid iff it exists, g_j - ts[idx] < lookback and the
+ * sample is not the stale marker; invalid -> NaN / -1.  d_out_idx is relative to the series. */
+int pmx_align(pmx_ctx* ctx, const int64_t* d_ts, const double* d_val, const int64_t* d_off,
+              int64_t n_series, int64_t start_ms, int64_t step_ms, int64_t n_steps,
+              int64_t lookback_ms, double* d_out_val, int32_t* d_out_idx, pmx_stream stream);
+
+/* ---- X4  rolling min/max/mean/count (K3) over the trailing `window_steps` points of a dense
+ * [S,T] matrix (pandas rolling('<W>') on a regular index: window (t-W, t], NaN skipped,
+ * +-inf excluded from min/max/mean but counted, stat = NaN below min_periods finite points). */
+int pmx_rolling(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
+                int64_t window_steps, int64_t min_periods,
+                double* d_min, double* d_max, double* d_mean, int32_t* d_count,
+                pmx_stream stream);
+/* Ragged form: window (t_i - window_ms, t_i] evaluated at each sample of each series. */
+int pmx_rolling_ragged(pmx_ctx* ctx, const int64_t* d_ts, const double* d_val,
+                       const int64_t* d_off, int64_t n_series, int64_t n_samples,
+                       int64_t window_ms, int64_t min_periods,
+                       double* d_min, double* d_max, double* d_mean, int32_t* d_count,
+                       pmx_stream stream);
+
+/* ---- X5  counter increase / rate with reset handling (K4).  Window as in pmx_rolling; NaN
+ * skipped; >=2 samples needed.  increase = (x_last - x_first) + sum of the values that
+ * preceded each drop inside the window; rate = increase / elapsed seconds first..last. */
+int pmx_rate(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
+             int64_t window_steps, int64_t step_ms,
+             double* d_increase, double* d_rate, int32_t* d_n_resets, pmx_stream stream);
+int pmx_rate_ragged(pmx_ctx* ctx, const int64_t* d_ts, const double* d_val,
+                    const int64_t* d_off, int64_t n_series, int64_t n_samples,
+                    int64_t window_ms,
+                    double* d_increase, double* d_rate, int32_t* d_n_resets, pmx_stream stream);
+
+/* ---- X3+X4+X5 fused (the roofline kernel): reads (ts,val) once, writes the aligned value,
+ * rolling min/max/mean and rate of every grid point: 16 B in, 40 B out per sample. */
+int pmx_fused_align_rolling_rate(pmx_ctx* ctx, const int64_t* d_ts, const double* d_val,
+                                 const int64_t* d_off, int64_t n_series,
+                                 int64_t start_ms, int64_t step_ms, int64_t n_steps,
+                                 int64_t lookback_ms, int64_t window_steps, int64_t min_periods,
+                                 double* d_aligned, double* d_min, double* d_max,
+                                 double* d_mean, double* d_rate, pmx_stream stream);
+
+/* ---- X6 / H7-H9  group-by reductions (K5).  Groups are given as a CSR over series:
+ * d_perm[d_goff[g] .. d_goff[g+1]) are the series of group g in ascending series order
+ * (pmx_group_index builds both on the host from a group id per series; id < 0 = no group).
+ * per_step = 0: reduce over all steps -> [G];  per_step = 1: reduce over series only -> [G,T].
+ * NaN skipped; count is int64; empty group -> sum 0, count 0, min/max/mean NaN.  Sums visit
+ * series in group order (per_step: strictly sequential, the order pandas uses at app.py:218). */
+int pmx_group_index(const int32_t* h_group_id, int64_t n_series, int64_t n_groups,
+                    int32_t* h_perm, int64_t* h_goff);
+int pmx_group_reduce(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
+                     const int32_t* d_perm, const int64_t* d_goff, int64_t n_groups,
+                     int per_step, double* d_sum, int64_t* d_count, double* d_min,
+                     double* d_max, double* d_mean, pmx_stream stream);
+
+/* ---- X7  exact quantiles (K6) by radix select over order-preserving 64-bit keys.
+ * Values of series s belong to segment d_seg[s] (or none if < 0).  State per segment:
+ *   d_state: opaque uint64 [n_seg * (2 + 4*n_q)] owned by the caller, zeroed by pass 0.
+ * One pass p = 0..PMX_QUANTILE_PASSES-1 is: pmx_quantile_hist (local histograms of the p-th
+ * digit of the keys that match each target's prefix) -> [all-reduce d_hist across ranks, sum,
+ * uint64] -> pmx_quantile_pick (device-side prefix scan: choose the bin holding each target
+ * rank, extend the prefix).  After the last pass pmx_quantile_finish converts the keys back
+ * and interpolates like numpy's _lerp (Series.quantile / np.percentile 'linear').
+ * d_hist is uint64 [n_seg * 2*n_q * PMX_QUANTILE_BINS] (pass 0 uses the first n_seg*BINS). */
+int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
+                      const int32_t* d_seg, int64_t n_seg, int64_t n_q, int pass,
+                      const uint64_t* d_state, uint64_t* d_hist, pmx_stream stream);
+int pmx_quantile_pick(pmx_ctx* ctx, const uint64_t* d_hist, int64_t n_seg, const double* d_q,
+                      int64_t n_q, int pass, uint64_t* d_state, pmx_stream stream);
+int pmx_quantile_finish(pmx_ctx* ctx, const uint64_t* d_state, int64_t n_seg, const double* d_q,
+                        int64_t n_q, int64_t* d_n, int64_t* d_lo, int64_t* d_hi,
+                        double* d_x_lo, double* d_x_hi, double* d_value, pmx_stream stream);
+/* Single-GPU convenience: all passes back to back (no collective); hist/state in ctx scratch. */
+int pmx_quantile_select(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
+                        const int32_t* d_seg, int64_t n_seg, const double* d_q, int64_t n_q,
+                        int64_t* d_n, int64_t* d_lo, int64_t* d_hi,
+                        double* d_x_lo, double* d_x_hi, double* d_value, pmx_stream stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PMX_H */

@@ -1,0 +1,18 @@
+// Host build of csrc/strtod_core.h for the CPU-side fuzz test of the parser state machine
+// (tests/test_strtod_host.py).  Test infrastructure: the product only runs this code on the GPU.
+#include <stdint.h>
+#include <stddef.h>
+#define PMX_POW5_QUALIFIER static const
+#include "../../k8s_rocm_metrics_dashboard_b200/csrc/pow5_table.h"
+#include "../../k8s_rocm_metrics_dashboard_b200/csrc/strtod_core.h"
+
+extern "C" int host_parse_f64(const uint8_t* p, int64_t len, uint64_t* bits) {
+  return pmx::parse_f64(p, len, pmx_pow5_128, bits);
+}
+extern "C" int host_parse_ts_ms(const uint8_t* p, int64_t len, int64_t* out) {
+  return pmx::parse_ts_ms(p, len, out);
+}
+// many tokens at once: offsets[n+1] into buf
+extern "C" void host_parse_many(const uint8_t* buf, const int64_t* off, int64_t n, uint64_t* bits, int32_t* status) {
+  for (int64_t i = 0; i < n; ++i) status[i] = pmx::parse_f64(buf + off[i], off[i + 1] - off[i], pmx_pow5_128, bits + i);
+}
