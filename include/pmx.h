@@ -144,6 +144,22 @@ int pmx_group_reduce(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t 
                      int per_step, double* d_sum, int64_t* d_count, double* d_min,
                      double* d_max, double* d_mean, pmx_stream stream);
 
+/* ---- H5 / H6 / H9  the per-card steps of the instant path.
+ * pmx_pivot_gather: long -> wide (df.pivot at app.py:207): out[cell] = val[src[cell]] or NaN when
+ *   src[cell] < 0 (missing cell).  Duplicate (gpu_id, metric) keys are detected by the adapter
+ *   from the label table and raised as ValueError before this call.
+ * pmx_ratio_pct: out = num/den*100 with the two roundings of Python's (used/total)*100
+ *   (app.py:210-212); *d_zero_flag becomes 1 if any denominator is 0 so the adapter can raise
+ *   ZeroDivisionError.  Strides are in elements.
+ * pmx_where_gt: out = x > threshold ? x : NaN  (app.py:343 power_values[power_values > 0]). */
+int pmx_pivot_gather(pmx_ctx* ctx, const double* d_val, const int32_t* d_cell_src, int64_t n_cells,
+                     double* d_out, pmx_stream stream);
+int pmx_ratio_pct(pmx_ctx* ctx, const double* d_num, int64_t num_stride, const double* d_den,
+                  int64_t den_stride, int64_t n, double* d_out, int64_t out_stride,
+                  int32_t* d_zero_flag, pmx_stream stream);
+int pmx_where_gt(pmx_ctx* ctx, const double* d_x, int64_t n, double threshold, double* d_out,
+                 pmx_stream stream);
+
 /* ---- X7  exact quantiles (K6) by radix select over order-preserving 64-bit keys.
  * Values of series s belong to segment d_seg[s] (or none if < 0).  State per segment:
  *   d_state: opaque uint64 [n_seg * (2 + 4*n_q)] owned by the caller, zeroed by pass 0.

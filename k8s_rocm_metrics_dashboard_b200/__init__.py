@@ -1,0 +1,16 @@
+"""B200-native engine for the Prometheus aggregate path of k8s-rocm-metrics-dashboard.
+
+Public surface (mirrors the reference's data path, /root/reference/app.py:153-227, :335-345):
+
+    from k8s_rocm_metrics_dashboard_b200 import fetch_gpu_metrics, aggregate_instant, aggregate_range
+
+Numeric work runs in ``libpmx.so`` (hand-written sm_100a CUDA behind the C ABI in
+``include/pmx.h``).  There is no CPU fallback: without the library or without a GPU the
+calls raise.
+"""
+from .engine import DEFAULT_LOOKBACK_MS, Engine, Tokens, group_index, tokenize  # noqa: F401
+from .adapter import (aggregate_instant, aggregate_range, fetch_gpu_metrics,  # noqa: F401
+                      selected_averages)
+
+__all__ = ["Engine", "Tokens", "tokenize", "group_index", "fetch_gpu_metrics", "aggregate_instant",
+           "aggregate_range", "selected_averages", "DEFAULT_LOOKBACK_MS"]

@@ -1,0 +1,95 @@
+"""ctypes binding of libpmx.so (include/pmx.h).  No fallback: a missing library is an error.
+
+``lib()`` loads the in-tree shared object (building it first if the sources are newer and nvcc
+is present).  Every device entry point takes raw device pointers and a ``cudaStream_t``; the
+``Engine`` class passes ``tensor.data_ptr()`` and ``torch.cuda.current_stream().cuda_stream``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libpmx.so")
+
+OK, E_INVALID, E_CUDA, E_VALUE, E_KEY, E_CAPACITY, E_JSON, E_LIMIT = 0, -1, -2, -3, -4, -5, -6, -7
+QUANTILE_BINS = 2048
+QUANTILE_PASSES = 6
+INT64_MAX = (1 << 63) - 1
+
+
+class PmxError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__(f"libpmx error {code}: {message}")
+        self.code = code
+        self.message = message
+
+
+class TokenizeResult(C.Structure):
+    _fields_ = [("n_samples", C.c_int64), ("n_series", C.c_int64), ("extra_len", C.c_int64),
+                ("result_type", C.c_int32)]
+
+
+_p = C.c_void_p
+_i64 = C.c_int64
+_u64 = C.c_uint64
+_int = C.c_int
+
+# name -> (restype, argtypes); mirrors include/pmx.h one to one
+SIGNATURES = {
+    "pmx_version": (_int, []),
+    "pmx_last_error": (C.c_char_p, []),
+    "pmx_ctx_create": (_int, [_int, C.POINTER(_p)]),
+    "pmx_ctx_destroy": (None, [_p]),
+    "pmx_ctx_scratch_bytes": (C.c_size_t, [_p]),
+    "pmx_tokenize": (_int, [_p, C.c_size_t, _p, _p, _i64, _p, _p, _p, _i64, _p, C.c_size_t,
+                            C.POINTER(TokenizeResult)]),
+    "pmx_parse_f64": (_int, [_p, _p, _u64, _p, _i64, _p, _p, _p]),
+    "pmx_parse_ts_ms": (_int, [_p, _p, _u64, _p, _i64, _p, _p, _p]),
+    "pmx_align": (_int, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _p, _p, _p]),
+    "pmx_rolling": (_int, [_p, _p, _i64, _i64, _i64, _i64, _p, _p, _p, _p, _p]),
+    "pmx_rolling_ragged": (_int, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _p, _p, _p, _p, _p]),
+    "pmx_rate": (_int, [_p, _p, _i64, _i64, _i64, _i64, _p, _p, _p, _p]),
+    "pmx_rate_ragged": (_int, [_p, _p, _p, _p, _i64, _i64, _i64, _p, _p, _p, _p]),
+    "pmx_fused_align_rolling_rate": (_int, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i64, _i64,
+                                            _p, _p, _p, _p, _p, _p]),
+    "pmx_group_index": (_int, [_p, _i64, _i64, _p, _p]),
+    "pmx_group_reduce": (_int, [_p, _p, _i64, _i64, _p, _p, _i64, _int, _p, _p, _p, _p, _p, _p]),
+    "pmx_pivot_gather": (_int, [_p, _p, _p, _i64, _p, _p]),
+    "pmx_ratio_pct": (_int, [_p, _p, _i64, _p, _i64, _i64, _p, _i64, _p, _p]),
+    "pmx_where_gt": (_int, [_p, _p, _i64, C.c_double, _p, _p]),
+    "pmx_quantile_hist": (_int, [_p, _p, _i64, _i64, _p, _i64, _i64, _int, _p, _p, _p]),
+    "pmx_quantile_pick": (_int, [_p, _p, _i64, _p, _i64, _int, _p, _p]),
+    "pmx_quantile_finish": (_int, [_p, _p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _p]),
+    "pmx_quantile_select": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _p]),
+}
+
+_lib = None
+
+
+def lib():
+    """The loaded library; raises if it cannot be found or built (there is no CPU path)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        from . import build as _build
+        try:
+            _build.build()
+        except Exception as e:  # noqa: BLE001
+            raise ImportError(
+                f"libpmx.so is missing at {LIB_PATH} and could not be built ({e}); run "
+                "`python -m k8s_rocm_metrics_dashboard_b200.build` where nvcc is available. "
+                "This engine has no CPU fallback.") from e
+    l = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(l, name)          # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    _lib = l
+    return l
+
+
+def check(rc):
+    if rc != OK:
+        raise PmxError(rc, lib().pmx_last_error().decode("utf-8", "replace"))

@@ -1,0 +1,180 @@
+"""The reference-facing call surface: same names, arguments and error behaviour as app.py.
+
+* ``fetch_gpu_metrics()``            -- drop-in for ``/root/reference/app.py:153-227``: two HTTP GETs,
+  then the engine instead of ``json.loads`` + the per-series Python loop + pandas reductions.
+  Returns ``(df_pivot, stats)`` or ``(None, None)`` after reporting the error, like the reference.
+* ``aggregate_instant(body)``        -- the inner seam (``app.py:178-221``) on a response body.
+* ``selected_averages(df, selected)``-- ``app.py:335-345``.
+* ``aggregate_range(body, ...)``     -- the range-query counterpart north_star asks for: matrix body in,
+  tidy DataFrame (or dict of arrays) out.
+
+All numeric work happens in libpmx.so on the GPU; pandas is only used to assemble the frames
+the Streamlit charts consume (object dtype, lexicographic ``gpu_id`` index, as the reference).
+"""
+from __future__ import annotations
+
+import os
+
+import numpy as np
+import pandas as pd
+
+from .engine import DEFAULT_LOOKBACK_MS, Engine, tokenize
+
+PROMETHEUS_METRICS_ENDPOINT = os.environ.get("PROMETHEUS_METRICS_ENDPOINT", "http://localhost:9090/api/v1/query")
+PROMETHEUS_METRICS_PODNAME = os.environ.get("PROMETHEUS_METRICS_PODNAME", "prometheus")
+
+_engine = None
+last_error = None          # message of the last failure (what the reference passes to st.error)
+
+
+def engine() -> Engine:
+    global _engine
+    if _engine is None:
+        _engine = Engine()
+    return _engine
+
+
+def _report(msg):
+    global last_error
+    last_error = msg
+    try:
+        import streamlit as st
+        st.error(msg)
+    except Exception:  # noqa: BLE001  (streamlit absent or not in a script run)
+        pass
+
+
+def aggregate_instant(body, eng: Engine | None = None):
+    """app.py:178-221 on the GPU.  Raises what the reference's code would raise
+    (KeyError for a missing label, ValueError for a malformed number or duplicate key,
+    ZeroDivisionError for total_vram == 0); ``fetch_gpu_metrics`` catches them."""
+    eng = eng or engine()
+    t = eng.torch
+    tok = tokenize(body)                                              # app.py:178
+    labels = tok.labels()
+    if tok.result_type != "vector":
+        raise ValueError("instant path expects resultType vector")
+    # app.py:183-194: label access order is gpu_id, __name__, float(value), card_model
+    _, val = eng.parse(tok, want_ts=False) if tok.n_samples else (None, eng._empty((0,), t.float64))
+    models, keys = {}, []
+    for i, lab in enumerate(labels):
+        gid, name = lab["gpu_id"], lab["__name__"]
+        keys.append((gid, name))
+        if gid not in models:
+            models[gid] = lab["card_model"]
+    if not keys:
+        raise KeyError("gpu_id")                                      # pivot on an empty frame (app.py:207)
+    if len(set(keys)) != len(keys):
+        raise ValueError("Index contains duplicate entries, cannot reshape")
+    gids = sorted(models)                                             # pivot sorts the index
+    names = sorted({n for _, n in keys})
+    for need in ("amd_gpu_used_vram", "amd_gpu_total_vram"):
+        if need not in names:
+            raise KeyError(need)                                      # app.py:210-212
+    cols = names + ["vram_usage_ratio"]
+    G, Cn = len(gids), len(cols)
+    row = {g: i for i, g in enumerate(gids)}
+    col = {n: i for i, n in enumerate(cols)}
+    src = np.full(G * Cn, -1, dtype=np.int32)
+    for i, (g, n) in enumerate(keys):
+        src[row[g] * Cn + col[n]] = i
+    mat = eng.pivot_gather(val, src).view(G, Cn)                      # app.py:207
+    if eng.ratio_pct(mat, col["amd_gpu_used_vram"], col["amd_gpu_total_vram"], col["vram_usage_ratio"]):
+        raise ZeroDivisionError("float division by zero")             # app.py:210-212 on Python floats
+    # app.py:216-221: column-wise mean/max/min over cards, NaN skipped, cards in index order
+    sm, cnt, mn, mx, mean = eng.group_reduce(mat, np.zeros(G, dtype=np.int32), 1, per_step=True)
+    host = mat.cpu().numpy()
+    h_mean, h_max, h_min = mean.cpu().numpy()[0], mx.cpu().numpy()[0], mn.cpu().numpy()[0]
+    # assemble the frame the charts consume (object dtype like the reference's pivot)
+    data = {n: [float(host[r, col[n]]) for r in range(G)] for n in names}
+    data["card_model"] = [models[g] for g in gids]
+    ordered = sorted(names + ["card_model"])
+    df = pd.DataFrame({n: pd.Series(data[n], index=gids, dtype=object) for n in ordered},
+                      index=pd.Index(gids, name="gpu_id"))
+    df.columns.name = "metric_name"
+    df["vram_usage_ratio"] = pd.Series([float(host[r, col["vram_usage_ratio"]]) for r in range(G)],
+                                       index=df.index, dtype=object)
+    numeric = [c for c in df.columns if c != "card_model"]
+    idx = pd.Index(numeric, name="metric_name")
+    stats = {
+        "mean": pd.Series([float(h_mean[col[c]]) for c in numeric], index=idx, dtype=object),
+        "max": pd.Series([float(h_max[col[c]]) for c in numeric], index=idx, dtype=object),
+        "min": pd.Series([float(h_min[col[c]]) for c in numeric], index=idx, dtype=object),
+    }
+    return df, stats
+
+
+def selected_averages(df_pivot, selected, eng: Engine | None = None):
+    """app.py:335-345: column means over the selected cards (selection order), with the power
+    mean taken over strictly positive readings when there is any."""
+    eng = eng or engine()
+    t = eng.torch
+    f = df_pivot.loc[selected]                                        # KeyError like the reference
+    numeric = [c for c in f.columns if c != "card_model"]
+    mat = t.as_tensor(f[numeric].to_numpy(dtype=np.float64), dtype=t.float64, device=eng.device)
+    k = len(selected)
+    _, _, _, _, mean = eng.group_reduce(mat, np.zeros(k, dtype=np.int32), 1, per_step=True)
+    avg = pd.Series([float(v) for v in mean.cpu().numpy()[0]], index=pd.Index(numeric, name=f.columns.name),
+                    dtype=object)
+    pc = numeric.index("amd_gpu_average_package_power")
+    pos = eng.where_gt(mat[:, pc].contiguous(), 0.0).view(k, 1)
+    _, cnt, _, _, pmean = eng.group_reduce(pos, np.zeros(k, dtype=np.int32), 1, per_step=True)
+    if int(cnt.item()) > 0:
+        avg["amd_gpu_average_package_power"] = float(pmean.item())
+    return avg
+
+
+def fetch_gpu_metrics():
+    """Drop-in for app.py:153-227 (same two queries, same return contract)."""
+    try:
+        import requests
+        q1 = f"kube_pod_info{{pod=~\".*{PROMETHEUS_METRICS_PODNAME}.*\"}}"
+        r1 = requests.get(url=PROMETHEUS_METRICS_ENDPOINT, params={"query": q1})
+        r1.raise_for_status()
+        import json
+        host_ip = json.loads(r1.text)["data"]["result"][0]["metric"]["host_ip"]
+        q2 = ("{__name__=~\"amd_gpu_edge_temperature|amd_gpu_gfx_activity|amd_gpu_average_package_power|"
+              "amd_gpu_used_vram|amd_gpu_total_vram\", instance=~\"" + host_ip + ":.+\"}")
+        r2 = requests.get(url=PROMETHEUS_METRICS_ENDPOINT, params={"query": q2})
+        r2.raise_for_status()
+        return aggregate_instant(r2.text)
+    except Exception as e:  # noqa: BLE001  -- the reference swallows everything (app.py:225-227)
+        _report(f"Error fetching GPU metrics: {str(e)}")
+        return None, None
+
+
+def aggregate_range(body, start_ms, step_ms, n_steps, window_ms, lookback_ms=DEFAULT_LOOKBACK_MS,
+                    quantiles=(0.5, 0.95, 0.99), as_frame=True, eng: Engine | None = None):
+    """Range path: ``query_range`` matrix body -> per (series, step) tidy frame + per-metric summary.
+
+    Returns (tidy, summary).  tidy columns: instance, gpu_id, metric_name, ts, value, roll_min,
+    roll_max, roll_mean, rate.  summary: one row per metric name with sum/count/min/max/mean of the
+    aligned values and the requested quantiles.  With ``as_frame=False`` both are dicts of arrays.
+    """
+    eng = eng or engine()
+    tok = tokenize(body)
+    labels = tok.labels()
+    ts, val = eng.parse(tok)
+    w = int(window_ms // step_ms)
+    out = eng.fused(ts, val, tok.series_off, start_ms, step_ms, n_steps, w, lookback_ms)
+    names = sorted({l.get("__name__", "") for l in labels})
+    gid = np.array([names.index(l.get("__name__", "")) for l in labels], dtype=np.int32)
+    sm, cnt, mn, mx, mean = eng.group_reduce(out["aligned"], gid, len(names))
+    qd = eng.quantiles(out["aligned"], gid, len(names), list(quantiles))
+    host = {k: v.cpu().numpy() for k, v in out.items()}
+    summary = {"metric_name": names, "sum": sm.cpu().numpy(), "count": cnt.cpu().numpy(),
+               "min": mn.cpu().numpy(), "max": mx.cpu().numpy(), "mean": mean.cpu().numpy()}
+    qv = qd["value"].cpu().numpy()
+    for i, q in enumerate(quantiles):
+        summary[f"p{int(round(q * 100))}"] = qv[:, i]
+    S = len(labels)
+    grid = start_ms + step_ms * np.arange(n_steps, dtype=np.int64)
+    tidy = {"instance": np.repeat([l.get("instance", "") for l in labels], n_steps),
+            "gpu_id": np.repeat([l.get("gpu_id", "") for l in labels], n_steps),
+            "metric_name": np.repeat([l.get("__name__", "") for l in labels], n_steps),
+            "ts": np.tile(grid, S), "value": host["aligned"].ravel(), "roll_min": host["roll_min"].ravel(),
+            "roll_max": host["roll_max"].ravel(), "roll_mean": host["roll_mean"].ravel(),
+            "rate": host["rate"].ravel()}
+    if not as_frame:
+        return tidy, summary
+    return pd.DataFrame(tidy), pd.DataFrame(summary)

@@ -1,0 +1,74 @@
+// ctx.cu -- context, error reporting, scratch.
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include <new>
+#include "pmx_common.cuh"
+
+static thread_local char g_err[512] = "";
+
+int pmx_fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+int pmx_cuda_fail(cudaError_t e, const char* what) {
+  snprintf(g_err, sizeof(g_err), "CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
+  return PMX_E_CUDA;
+}
+
+void* pmx_scratch(pmx_ctx* ctx, size_t bytes) {
+  if (bytes <= ctx->scratch_bytes) return ctx->scratch;
+  // cudaFree synchronises the device, so work still using the old block has finished.
+  if (ctx->scratch) cudaFree(ctx->scratch);
+  ctx->scratch = nullptr;
+  ctx->scratch_bytes = 0;
+  size_t want = (bytes + (size_t(1) << 20) - 1) & ~((size_t(1) << 20) - 1);
+  cudaError_t e = cudaMalloc(&ctx->scratch, want);
+  if (e != cudaSuccess) { pmx_cuda_fail(e, "cudaMalloc(scratch)"); return nullptr; }
+  ctx->scratch_bytes = want;
+  return ctx->scratch;
+}
+
+extern "C" {
+
+int pmx_version(void) { return PMX_VERSION; }
+
+const char* pmx_last_error(void) { return g_err; }
+
+int pmx_ctx_create(int device, pmx_ctx** out) {
+  if (!out) return pmx_fail(PMX_E_INVALID, "pmx_ctx_create: out is NULL");
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0)
+    return pmx_fail(PMX_E_CUDA, "pmx_ctx_create: no CUDA device available (%s); this engine has no CPU path",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+  if (device < 0 || device >= n) return pmx_fail(PMX_E_INVALID, "pmx_ctx_create: device %d out of range [0,%d)", device, n);
+  PMX_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  PMX_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10)
+    return pmx_fail(PMX_E_CUDA, "pmx_ctx_create: device %d is sm_%d%d; libpmx is built for sm_100a only", device, prop.major, prop.minor);
+  pmx_ctx* c = new (std::nothrow) pmx_ctx();
+  if (!c) return pmx_fail(PMX_E_INVALID, "pmx_ctx_create: out of host memory");
+  c->device = device;
+  c->sm_count = prop.multiProcessorCount;
+  c->scratch = nullptr;
+  c->scratch_bytes = 0;
+  *out = c;
+  return PMX_OK;
+}
+
+void pmx_ctx_destroy(pmx_ctx* ctx) {
+  if (!ctx) return;
+  if (ctx->scratch) cudaFree(ctx->scratch);
+  delete ctx;
+}
+
+size_t pmx_ctx_scratch_bytes(const pmx_ctx* ctx) { return ctx ? ctx->scratch_bytes : 0; }
+
+}  // extern "C"

@@ -1,0 +1,44 @@
+// pmx_common.cuh -- shared by every translation unit of libpmx.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/pmx.h"
+
+struct pmx_ctx {
+  int device;
+  int sm_count;
+  void* scratch;          // grow-only device scratch (group partials, quantile state, ...)
+  size_t scratch_bytes;
+};
+
+// error plumbing (ctx.cu)
+int pmx_fail(int code, const char* fmt, ...);
+int pmx_cuda_fail(cudaError_t e, const char* what);
+// returns NULL (and sets the error) on failure
+void* pmx_scratch(pmx_ctx* ctx, size_t bytes);
+
+#define PMX_CUDA(call)                                                   \
+  do {                                                                   \
+    cudaError_t e_ = (call);                                             \
+    if (e_ != cudaSuccess) return pmx_cuda_fail(e_, #call);              \
+  } while (0)
+
+#define PMX_REQUIRE(cond, msg)                                           \
+  do {                                                                   \
+    if (!(cond)) return pmx_fail(PMX_E_INVALID, "%s: %s", __func__, msg); \
+  } while (0)
+
+#define PMX_LAUNCH_CHECK() PMX_CUDA(cudaGetLastError())
+
+static inline cudaStream_t pmx_st(pmx_stream s) { return (cudaStream_t)s; }
+
+#define PMX_CANON_NAN_BITS 0x7FF8000000000000ULL
+
+#if defined(__CUDACC__)
+__device__ __forceinline__ double pmx_nan() { return __longlong_as_double(0x7FF8000000000000LL); }
+__device__ __forceinline__ bool pmx_isnan(double v) { return v != v; }
+__device__ __forceinline__ bool pmx_isfinite(double v) {
+  return (__double_as_longlong(v) & 0x7FF0000000000000LL) != 0x7FF0000000000000LL;
+}
+#endif

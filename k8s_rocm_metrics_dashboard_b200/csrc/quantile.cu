@@ -1,0 +1,261 @@
+// quantile.cu -- K6: exact quantiles by radix select on order-preserving keys.
+//
+// float64 -> uint64 key that sorts like the number (NaN excluded), then PMX_QUANTILE_PASSES
+// passes of 11-bit digits, most significant first.  A pass is
+//   hist : per-CTA shared-memory histograms (one per target still being refined) of the digit of
+//          every key that matches the target's prefix, flushed with integer atomics -- so the
+//          global histogram is deterministic and can be all-reduced across ranks as is;
+//   pick : prefix-scan the (reduced) histogram on the device, choose the bin that holds the
+//          target rank, append it to the prefix, subtract the ranks below it.
+// After the last pass every target's prefix IS the key of the wanted order statistic.  Targets
+// per segment: for each q the ranks lo = floor((n-1)q) and hi = min(lo+1, n-1), then numpy's
+// _lerp.  No sample ever moves between GPUs; a pass exchanges 16 KiB per target.
+//
+// State per segment (uint64 words): [0] n, [1] reserved, then per target t: [2+2t] prefix,
+// [3+2t] remaining rank inside the prefix bucket.
+#include "pmx_common.cuh"
+
+namespace {
+
+constexpr int BINS = PMX_QUANTILE_BINS;
+constexpr int MAX_TARGETS = 16;
+
+__device__ __forceinline__ uint64_t f64_key(double v) {
+  const uint64_t b = (uint64_t)__double_as_longlong(v);
+  return (b >> 63) ? ~b : (b | 0x8000000000000000ULL);
+}
+__device__ __forceinline__ double key_f64(uint64_t k) {
+  const uint64_t b = (k >> 63) ? (k & 0x7fffffffffffffffULL) : ~k;
+  return __longlong_as_double((long long)b);
+}
+__host__ __device__ __forceinline__ int digit_shift(int pass) { return pass < 5 ? 53 - 11 * pass : 0; }
+__host__ __device__ __forceinline__ int digit_bits(int pass) { return pass < 5 ? 11 : 9; }
+__host__ __device__ __forceinline__ int state_words(int64_t n_q) { return 2 + 4 * (int)n_q; }
+
+__global__ void __launch_bounds__(256)
+hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __restrict__ seg,
+            int n_t, int pass, const uint64_t* __restrict__ state, int sw,
+            unsigned long long* __restrict__ hist, int rows_per_cta, int64_t n_series) {
+  extern __shared__ unsigned int sh[];                     // [n_h][BINS]
+  const int n_h = pass == 0 ? 1 : n_t;
+  const int64_t s0 = (int64_t)blockIdx.x * rows_per_cta;
+  const int shift = digit_shift(pass);
+  const unsigned mask = (1u << digit_bits(pass)) - 1u;
+  const int pshift = 64 - 11 * pass;                       // key >> pshift == prefix  (pass >= 1)
+  int cur_seg = -1;
+  uint64_t prefix[MAX_TARGETS];
+  for (int r = 0; r < rows_per_cta; ++r) {
+    const int64_t s = s0 + r;
+    if (s >= n_series) break;
+    const int sg = seg[s];
+    if (sg < 0) continue;
+    if (sg != cur_seg) {                                   // flush, switch segment
+      if (cur_seg >= 0) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < n_h * BINS; i += blockDim.x) {
+          const unsigned c = sh[i];
+          if (c) atomicAdd(&hist[((size_t)cur_seg * n_h) * BINS + i], (unsigned long long)c);
+        }
+      }
+      __syncthreads();
+      for (int i = threadIdx.x; i < n_h * BINS; i += blockDim.x) sh[i] = 0;
+      cur_seg = sg;
+      if (pass > 0)
+        for (int k = 0; k < n_t; ++k) prefix[k] = state[(size_t)sg * sw + 2 + 2 * k];
+      __syncthreads();
+    }
+    const double* xr = x + s * n_steps;
+    for (int64_t j = threadIdx.x; j < n_steps; j += blockDim.x) {
+      const double v = xr[j];
+      if (v != v) continue;
+      const uint64_t key = f64_key(v);
+      const unsigned d = (unsigned)(key >> shift) & mask;
+      if (pass == 0) atomicAdd(&sh[d], 1u);
+      else {
+        const uint64_t top = key >> pshift;
+        for (int k = 0; k < n_t; ++k)
+          if (top == prefix[k]) atomicAdd(&sh[k * BINS + d], 1u);
+      }
+    }
+  }
+  if (cur_seg >= 0) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < n_h * BINS; i += blockDim.x) {
+      const unsigned c = sh[i];
+      if (c) atomicAdd(&hist[((size_t)cur_seg * n_h) * BINS + i], (unsigned long long)c);
+    }
+  }
+}
+
+// grid (n_t, n_seg); one CTA scans one histogram
+__global__ void __launch_bounds__(256)
+pick_kernel(const unsigned long long* __restrict__ hist, const double* __restrict__ q, int n_q,
+            int pass, uint64_t* __restrict__ state, int sw) {
+  const int tg = blockIdx.x, sg = blockIdx.y;
+  const int n_t = 2 * n_q;
+  const int n_h = pass == 0 ? 1 : n_t;
+  const unsigned long long* h = hist + ((size_t)sg * n_h + (pass == 0 ? 0 : tg)) * BINS;
+  uint64_t* st = state + (size_t)sg * sw;
+  __shared__ unsigned long long part[256];
+  __shared__ unsigned long long s_total;
+  constexpr int PER = BINS / 256;                          // 8 bins per thread
+  unsigned long long loc[PER]; unsigned long long sum = 0;
+#pragma unroll
+  for (int i = 0; i < PER; ++i) { loc[i] = h[threadIdx.x * PER + i]; sum += loc[i]; }
+  part[threadIdx.x] = sum;
+  __syncthreads();
+  if (threadIdx.x == 0) {                                  // 256-element exclusive scan, serial
+    unsigned long long acc = 0;
+    for (int i = 0; i < 256; ++i) { unsigned long long v = part[i]; part[i] = acc; acc += v; }
+    s_total = acc;
+  }
+  __syncthreads();
+  unsigned long long k;
+  if (pass == 0) {
+    const unsigned long long n = s_total;
+    if (threadIdx.x == 0 && tg == 0) { st[0] = n; st[1] = 0; }
+    if (n == 0) { if (threadIdx.x == 0) { st[2 + 2 * tg] = 0; st[3 + 2 * tg] = 0; } return; }
+    const double pos = (double)(n - 1) * q[tg >> 1];
+    unsigned long long lo = (unsigned long long)floor(pos);
+    if (lo > n - 1) lo = n - 1;
+    const unsigned long long hi = lo + 1 < n ? lo + 1 : n - 1;
+    k = (tg & 1) ? hi : lo;
+  } else {
+    if (st[0] == 0) return;
+    k = st[3 + 2 * tg];
+  }
+  // the bin b with cum[b] <= k < cum[b+1]
+  unsigned long long acc = part[threadIdx.x];
+#pragma unroll
+  for (int i = 0; i < PER; ++i) {
+    if (k >= acc && k < acc + loc[i]) {
+      const uint64_t old = pass == 0 ? 0 : st[2 + 2 * tg];
+      st[2 + 2 * tg] = (old << digit_bits(pass)) | (uint64_t)(threadIdx.x * PER + i);
+      st[3 + 2 * tg] = k - acc;
+    }
+    acc += loc[i];
+  }
+}
+
+__global__ void finish_kernel(const uint64_t* __restrict__ state, int sw, int64_t n_seg,
+                              const double* __restrict__ q, int n_q, int64_t* o_n, int64_t* o_lo,
+                              int64_t* o_hi, double* o_xlo, double* o_xhi, double* o_val) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_seg * n_q) return;
+  const int64_t sg = i / n_q; const int qi = (int)(i % n_q);
+  const uint64_t* st = state + (size_t)sg * sw;
+  const unsigned long long n = st[0];
+  if (qi == 0 && o_n) o_n[sg] = (int64_t)n;
+  if (n == 0) {
+    if (o_lo) o_lo[i] = -1;
+    if (o_hi) o_hi[i] = -1;
+    if (o_xlo) o_xlo[i] = pmx_nan();
+    if (o_xhi) o_xhi[i] = pmx_nan();
+    if (o_val) o_val[i] = pmx_nan();
+    return;
+  }
+  const double pos = (double)(n - 1) * q[qi];
+  unsigned long long lo = (unsigned long long)floor(pos);
+  if (lo > n - 1) lo = n - 1;
+  const unsigned long long hi = lo + 1 < n ? lo + 1 : n - 1;
+  const double t = pos - (double)lo;
+  const double a = key_f64(st[2 + 2 * (2 * qi)]);
+  const double b = key_f64(st[2 + 2 * (2 * qi + 1)]);
+  // numpy _lerp: a + (b-a)*t, and b - (b-a)*(1-t) when t >= 0.5 (no FMA contraction)
+  const double d = __dsub_rn(b, a);
+  double v = __dadd_rn(a, __dmul_rn(d, t));
+  if (t >= 0.5) v = __dsub_rn(b, __dmul_rn(d, __dsub_rn(1.0, t)));
+  if (o_lo) o_lo[i] = (int64_t)lo;
+  if (o_hi) o_hi[i] = (int64_t)hi;
+  if (o_xlo) o_xlo[i] = a;
+  if (o_xhi) o_xhi[i] = b;
+  if (o_val) o_val[i] = v;
+}
+
+}  // namespace
+
+extern "C" {
+
+int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
+                      const int32_t* d_seg, int64_t n_seg, int64_t n_q, int pass,
+                      const uint64_t* d_state, uint64_t* d_hist, pmx_stream stream) {
+  PMX_REQUIRE(ctx, "ctx is NULL");
+  PMX_REQUIRE(n_series >= 0 && n_steps >= 0 && n_seg >= 0, "bad sizes");
+  PMX_REQUIRE(n_q >= 1 && 2 * n_q <= MAX_TARGETS, "n_q must be in [1, 8]");
+  PMX_REQUIRE(pass >= 0 && pass < PMX_QUANTILE_PASSES, "pass out of range");
+  if (n_seg == 0) return PMX_OK;
+  PMX_REQUIRE(d_hist && d_state, "NULL buffer");
+  const int n_t = 2 * (int)n_q;
+  const int n_h = pass == 0 ? 1 : n_t;
+  cudaStream_t st = pmx_st(stream);
+  PMX_CUDA(cudaMemsetAsync(d_hist, 0, (size_t)n_seg * n_h * BINS * sizeof(uint64_t), st));
+  if (n_series == 0 || n_steps == 0) return PMX_OK;
+  PMX_REQUIRE(d_x && d_seg, "NULL buffer");
+  const size_t smem = (size_t)n_h * BINS * sizeof(unsigned int);
+  PMX_CUDA(cudaFuncSetAttribute(hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(MAX_TARGETS * BINS * sizeof(unsigned int))));
+  // a CTA sweeps consecutive rows so that a segment's private histogram is flushed rarely
+  int64_t want_ctas = (int64_t)ctx->sm_count * 8;
+  int64_t rows = (n_series + want_ctas - 1) / want_ctas;
+  if (rows < 1) rows = 1;
+  const int64_t grid = (n_series + rows - 1) / rows;
+  hist_kernel<<<(unsigned)grid, 256, smem, st>>>(d_x, n_steps, d_seg, n_t, pass, d_state, state_words(n_q),
+                                                (unsigned long long*)d_hist, (int)rows, n_series);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
+int pmx_quantile_pick(pmx_ctx* ctx, const uint64_t* d_hist, int64_t n_seg, const double* d_q,
+                      int64_t n_q, int pass, uint64_t* d_state, pmx_stream stream) {
+  PMX_REQUIRE(ctx, "ctx is NULL");
+  PMX_REQUIRE(n_seg >= 0 && n_seg <= 65535, "n_seg must be in [0, 65535]");
+  PMX_REQUIRE(n_q >= 1 && 2 * n_q <= MAX_TARGETS, "n_q must be in [1, 8]");
+  PMX_REQUIRE(pass >= 0 && pass < PMX_QUANTILE_PASSES, "pass out of range");
+  if (n_seg == 0) return PMX_OK;
+  PMX_REQUIRE(d_hist && d_q && d_state, "NULL buffer");
+  dim3 grid((unsigned)(2 * n_q), (unsigned)n_seg);
+  pick_kernel<<<grid, 256, 0, pmx_st(stream)>>>((const unsigned long long*)d_hist, d_q, (int)n_q, pass, d_state,
+                                               state_words(n_q));
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
+int pmx_quantile_finish(pmx_ctx* ctx, const uint64_t* d_state, int64_t n_seg, const double* d_q,
+                        int64_t n_q, int64_t* d_n, int64_t* d_lo, int64_t* d_hi, double* d_x_lo,
+                        double* d_x_hi, double* d_value, pmx_stream stream) {
+  PMX_REQUIRE(ctx, "ctx is NULL");
+  PMX_REQUIRE(n_seg >= 0, "bad sizes");
+  PMX_REQUIRE(n_q >= 1 && 2 * n_q <= MAX_TARGETS, "n_q must be in [1, 8]");
+  if (n_seg == 0) return PMX_OK;
+  PMX_REQUIRE(d_state && d_q, "NULL buffer");
+  const int64_t n = n_seg * n_q;
+  finish_kernel<<<(unsigned)((n + 127) / 128), 128, 0, pmx_st(stream)>>>(d_state, state_words(n_q), n_seg, d_q, (int)n_q,
+                                                                        d_n, d_lo, d_hi, d_x_lo, d_x_hi, d_value);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
+int pmx_quantile_select(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
+                        const int32_t* d_seg, int64_t n_seg, const double* d_q, int64_t n_q,
+                        int64_t* d_n, int64_t* d_lo, int64_t* d_hi, double* d_x_lo, double* d_x_hi,
+                        double* d_value, pmx_stream stream) {
+  PMX_REQUIRE(ctx, "ctx is NULL");
+  PMX_REQUIRE(n_q >= 1 && 2 * n_q <= MAX_TARGETS, "n_q must be in [1, 8]");
+  PMX_REQUIRE(n_seg >= 0 && n_seg <= 65535, "n_seg must be in [0, 65535]");
+  if (n_seg == 0) return PMX_OK;
+  const size_t state_bytes = ((size_t)n_seg * state_words(n_q) * 8 + 255) & ~size_t(255);
+  const size_t hist_bytes = (size_t)n_seg * 2 * n_q * BINS * 8;
+  unsigned char* scr = (unsigned char*)pmx_scratch(ctx, state_bytes + hist_bytes);
+  if (!scr) return PMX_E_CUDA;
+  uint64_t* state = (uint64_t*)scr;
+  uint64_t* hist = (uint64_t*)(scr + state_bytes);
+  PMX_CUDA(cudaMemsetAsync(state, 0, state_bytes, pmx_st(stream)));
+  for (int pass = 0; pass < PMX_QUANTILE_PASSES; ++pass) {
+    int rc = pmx_quantile_hist(ctx, d_x, n_series, n_steps, d_seg, n_seg, n_q, pass, state, hist, stream);
+    if (rc) return rc;
+    rc = pmx_quantile_pick(ctx, hist, n_seg, d_q, n_q, pass, state, stream);
+    if (rc) return rc;
+  }
+  return pmx_quantile_finish(ctx, state, n_seg, d_q, n_q, d_n, d_lo, d_hi, d_x_lo, d_x_hi, d_value, stream);
+}
+
+}  // extern "C"

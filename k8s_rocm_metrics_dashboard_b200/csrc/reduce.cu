@@ -1,0 +1,145 @@
+// reduce.cu -- K5: NaN-skipping group-by reductions (app.py:216-221, :335-345).
+//
+// Groups arrive as a CSR over series (perm/goff) so that every sum visits its inputs in a
+// fixed order: results are deterministic and, for the per-step form, strictly sequential in
+// series order -- the order pandas' object-dtype column reductions use at app.py:218-220.
+#include <math.h>
+#include "pmx_common.cuh"
+
+namespace {
+
+struct Part { double sum; double mn; double mx; long long cnt; };
+
+__device__ __forceinline__ void part_add(Part& p, double v) {
+  if (v == v) { p.sum += v; p.mn = fmin(p.mn, v); p.mx = fmax(p.mx, v); p.cnt++; }
+}
+__device__ __forceinline__ void part_merge(Part& a, const Part& b) {
+  a.sum += b.sum; a.mn = fmin(a.mn, b.mn); a.mx = fmax(a.mx, b.mx); a.cnt += b.cnt;
+}
+__device__ __forceinline__ Part part_identity() {
+  const double INF = __longlong_as_double(0x7FF0000000000000LL);
+  return Part{0.0, INF, -INF, 0};
+}
+__device__ __forceinline__ Part part_shfl_down(const Part& p, int d) {
+  Part q;
+  q.sum = __shfl_down_sync(0xffffffffu, p.sum, d);
+  q.mn = __shfl_down_sync(0xffffffffu, p.mn, d);
+  q.mx = __shfl_down_sync(0xffffffffu, p.mx, d);
+  q.cnt = __shfl_down_sync(0xffffffffu, p.cnt, d);
+  return q;
+}
+
+// one CTA per series: partial (sum, min, max, count) over all steps -> part[s]
+__global__ void __launch_bounds__(256)
+series_partial_kernel(const double* __restrict__ x, int64_t n_steps, Part* __restrict__ part) {
+  const int64_t s = blockIdx.x;
+  const double* xr = x + s * n_steps;
+  Part p = part_identity();
+  for (int64_t j = threadIdx.x; j < n_steps; j += blockDim.x) part_add(p, xr[j]);
+#pragma unroll
+  for (int d = 16; d >= 1; d >>= 1) { Part q = part_shfl_down(p, d); part_merge(p, q); }
+  __shared__ Part sh[8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) sh[warp] = p;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    Part r = sh[0];
+    for (int w = 1; w < (int)(blockDim.x >> 5); ++w) part_merge(r, sh[w]);
+    part[s] = r;
+  }
+}
+
+// one thread per group: fold the series partials in group order
+__global__ void group_fold_kernel(const Part* __restrict__ part, const int32_t* __restrict__ perm,
+                                  const int64_t* __restrict__ goff, int64_t n_groups,
+                                  double* o_sum, int64_t* o_cnt, double* o_min, double* o_max, double* o_mean) {
+  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= n_groups) return;
+  Part r = part_identity();
+  for (int64_t k = goff[g]; k < goff[g + 1]; ++k) part_merge(r, part[perm[k]]);
+  const bool any = r.cnt > 0;
+  if (o_sum) o_sum[g] = r.sum;
+  if (o_cnt) o_cnt[g] = r.cnt;
+  if (o_min) o_min[g] = any ? r.mn : pmx_nan();
+  if (o_max) o_max[g] = any ? r.mx : pmx_nan();
+  if (o_mean) o_mean[g] = any ? r.sum / (double)r.cnt : pmx_nan();
+}
+
+// per-step form: thread per (group, step), series visited sequentially in group order
+__global__ void __launch_bounds__(256)
+group_step_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __restrict__ perm,
+                  const int64_t* __restrict__ goff, double* o_sum, int64_t* o_cnt, double* o_min,
+                  double* o_max, double* o_mean) {
+  const int64_t g = blockIdx.y;
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n_steps) return;
+  Part r = part_identity();
+  for (int64_t k = goff[g]; k < goff[g + 1]; ++k) part_add(r, x[(int64_t)perm[k] * n_steps + j]);
+  const bool any = r.cnt > 0;
+  const int64_t o = g * n_steps + j;
+  if (o_sum) o_sum[o] = r.sum;
+  if (o_cnt) o_cnt[o] = r.cnt;
+  if (o_min) o_min[o] = any ? r.mn : pmx_nan();
+  if (o_max) o_max[o] = any ? r.mx : pmx_nan();
+  if (o_mean) o_mean[o] = any ? r.sum / (double)r.cnt : pmx_nan();
+}
+
+}  // namespace
+
+extern "C" {
+
+int pmx_group_index(const int32_t* h_group_id, int64_t n_series, int64_t n_groups, int32_t* h_perm,
+                    int64_t* h_goff) {
+  if (!h_goff || n_series < 0 || n_groups < 0 || (n_series > 0 && (!h_group_id || !h_perm)))
+    return pmx_fail(PMX_E_INVALID, "pmx_group_index: bad argument");
+  if (n_series > 0x7fffffffLL) return pmx_fail(PMX_E_LIMIT, "pmx_group_index: more than 2^31-1 series");
+  for (int64_t g = 0; g <= n_groups; ++g) h_goff[g] = 0;
+  for (int64_t s = 0; s < n_series; ++s) {
+    const int32_t g = h_group_id[s];
+    if (g >= n_groups) return pmx_fail(PMX_E_INVALID, "pmx_group_index: group id %d >= n_groups", g);
+    if (g >= 0) h_goff[g + 1]++;
+  }
+  for (int64_t g = 0; g < n_groups; ++g) h_goff[g + 1] += h_goff[g];
+  // counting sort, stable: series stay in ascending order inside each group
+  int64_t* cursor = new int64_t[n_groups > 0 ? n_groups : 1];
+  for (int64_t g = 0; g < n_groups; ++g) cursor[g] = h_goff[g];
+  for (int64_t s = 0; s < n_series; ++s) {
+    const int32_t g = h_group_id[s];
+    if (g >= 0) h_perm[cursor[g]++] = (int32_t)s;
+  }
+  delete[] cursor;
+  return PMX_OK;
+}
+
+int pmx_group_reduce(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
+                     const int32_t* d_perm, const int64_t* d_goff, int64_t n_groups, int per_step,
+                     double* d_sum, int64_t* d_count, double* d_min, double* d_max, double* d_mean,
+                     pmx_stream stream) {
+  PMX_REQUIRE(ctx, "ctx is NULL");
+  PMX_REQUIRE(n_series >= 0 && n_steps >= 0 && n_groups >= 0, "bad sizes");
+  if (n_groups == 0) return PMX_OK;
+  PMX_REQUIRE(d_goff, "d_goff is NULL");
+  PMX_REQUIRE(n_series == 0 || (d_x && d_perm), "NULL buffer");
+  cudaStream_t st = pmx_st(stream);
+  if (per_step) {
+    if (n_steps == 0) return PMX_OK;
+    PMX_REQUIRE(n_groups <= 65535, "per_step form supports at most 65535 groups");
+    dim3 grid((unsigned)((n_steps + 255) / 256), (unsigned)n_groups);
+    group_step_kernel<<<grid, 256, 0, st>>>(d_x, n_steps, d_perm, d_goff, d_sum, d_count, d_min, d_max, d_mean);
+    PMX_LAUNCH_CHECK();
+    return PMX_OK;
+  }
+  Part* part = nullptr;
+  if (n_series > 0) {
+    part = (Part*)pmx_scratch(ctx, (size_t)n_series * sizeof(Part));
+    if (!part) return PMX_E_CUDA;
+    series_partial_kernel<<<(unsigned)n_series, 256, 0, st>>>(d_x, n_steps, part);
+    PMX_LAUNCH_CHECK();
+  }
+  group_fold_kernel<<<(unsigned)((n_groups + 127) / 128), 128, 0, st>>>(part, d_perm, d_goff, n_groups, d_sum, d_count,
+                                                                      d_min, d_max, d_mean);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
+}  // extern "C"

@@ -17,8 +17,10 @@
 
 #if defined(__CUDACC__)
 #define PMX_HD __host__ __device__
+#define PMX_COLD __noinline__
 #else
 #define PMX_HD
+#define PMX_COLD __attribute__((noinline))
 #endif
 
 namespace pmx {
@@ -261,7 +263,7 @@ PMX_HD inline int scan_number(const Byte& s, int64_t i, int64_t end, Scan& r) {
 }
 
 // Exact decision for the hard cases.  `bits` is a candidate (finite, non-negative).
-PMX_HD inline uint64_t exact_round(const Byte& s, const Scan& sc, uint64_t bits) {
+PMX_HD PMX_COLD inline uint64_t exact_round(const Byte& s, const Scan& sc, uint64_t bits) {
   // rebuild up to 769 significant digits, then a sticky 1 if anything non-zero was dropped
   Big D; D.set(0);
   int64_t taken = 0; bool sticky = false;

@@ -1,0 +1,326 @@
+"""Engine: one pmx_ctx on one GPU; torch is used for device memory and streams only.
+
+Every method hands raw device pointers to libpmx.so through the C ABI (include/pmx.h).  There
+is no CPU path: constructing an Engine without a CUDA device raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import _abi
+
+DEFAULT_LOOKBACK_MS = 300_000
+
+
+@dataclass
+class Tokens:
+    """Host-side result of pmx_tokenize: the flat byte buffer and per-sample offsets."""
+    flat: np.ndarray            # uint8: body + decoded escaped tokens
+    ts_off: np.ndarray          # uint32[N]
+    val_off: np.ndarray         # uint32[N]
+    series_off: np.ndarray      # int64[S+1]
+    metric_spans: list          # [(off, len)] of each series' "metric" object in the body
+    result_type: str            # "matrix" | "vector"
+
+    @property
+    def n_samples(self):
+        return len(self.ts_off)
+
+    @property
+    def n_series(self):
+        return len(self.series_off) - 1
+
+    def labels(self):
+        import json
+        body = self.flat
+        return [json.loads(bytes(body[o:o + n])) if n else {} for o, n in self.metric_spans]
+
+
+def tokenize(body: bytes) -> Tokens:
+    """X1 on the host (C++, no Python objects per sample).  Raises ValueError on a malformed body."""
+    if isinstance(body, str):
+        body = body.encode("utf-8")
+    lib = _abi.lib()
+    n = len(body)
+    cap_s, cap_r = n // 8 + 1, n // 24 + 1
+    ts_off = np.empty(cap_s, dtype=np.uint32)
+    val_off = np.empty(cap_s, dtype=np.uint32)
+    series_off = np.empty(cap_r + 1, dtype=np.int64)
+    m_off = np.empty(cap_r, dtype=np.uint32)
+    m_len = np.empty(cap_r, dtype=np.uint32)
+    extra = np.empty(n + 16, dtype=np.uint8)
+    res = _abi.TokenizeResult()
+    rc = lib.pmx_tokenize(body, n, ts_off.ctypes.data, val_off.ctypes.data, cap_s,
+                          series_off.ctypes.data, m_off.ctypes.data, m_len.ctypes.data, cap_r,
+                          extra.ctypes.data, extra.size, C.byref(res))
+    if rc == _abi.E_KEY:
+        raise KeyError("result")
+    if rc != _abi.OK:
+        raise ValueError(lib.pmx_last_error().decode("utf-8", "replace"))
+    ns, nr, ne = res.n_samples, res.n_series, res.extra_len
+    flat = np.frombuffer(body, dtype=np.uint8)
+    if ne:
+        flat = np.concatenate([flat, extra[:ne]])
+    return Tokens(flat, ts_off[:ns].copy(), val_off[:ns].copy(), series_off[:nr + 1].copy(),
+                  list(zip(m_off[:nr].tolist(), m_len[:nr].tolist())),
+                  "matrix" if res.result_type == 0 else "vector")
+
+
+def group_index(group_id, n_groups):
+    """Host helper (pmx_group_index): group id per series -> (perm int32[S'], goff int64[G+1])."""
+    gid = np.ascontiguousarray(group_id, dtype=np.int32)
+    perm = np.empty(max(1, len(gid)), dtype=np.int32)
+    goff = np.empty(n_groups + 1, dtype=np.int64)
+    _abi.check(_abi.lib().pmx_group_index(gid.ctypes.data, len(gid), n_groups, perm.ctypes.data, goff.ctypes.data))
+    return perm[:int(goff[-1])], goff
+
+
+class Engine:
+    def __init__(self, device=None):
+        import torch
+        if not torch.cuda.is_available():
+            raise RuntimeError("k8s_rocm_metrics_dashboard_b200.Engine needs a CUDA device (B200, sm_100a); "
+                               "there is no CPU fallback")
+        self.torch = torch
+        self.device = torch.device("cuda", torch.cuda.current_device() if device is None else device)
+        self.lib = _abi.lib()
+        ctx = C.c_void_p()
+        with torch.cuda.device(self.device):
+            _abi.check(self.lib.pmx_ctx_create(self.device.index, C.byref(ctx)))
+        self.ctx = ctx
+        self.launches = 0           # kernels of ours launched (bench's gpu_launches claim)
+
+    def close(self):
+        if getattr(self, "ctx", None):
+            self.lib.pmx_ctx_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+    # ------------------------------------------------------------------ helpers
+    def _stream(self):
+        return C.c_void_p(self.torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _empty(self, shape, dtype):
+        return self.torch.empty(shape, dtype=dtype, device=self.device)
+
+    def _dev(self, a, dtype):
+        t = self.torch
+        if isinstance(a, t.Tensor):
+            return a.to(device=self.device, dtype=dtype).contiguous()
+        return t.as_tensor(np.ascontiguousarray(a), dtype=dtype).to(self.device)
+
+    @staticmethod
+    def _ptr(t):
+        return C.c_void_p(t.data_ptr()) if t is not None else None
+
+    def scratch_bytes(self):
+        return int(self.lib.pmx_ctx_scratch_bytes(self.ctx))
+
+    # ------------------------------------------------------------------ K1
+    def parse(self, tok: Tokens, want_ts=True):
+        """Device decode of all value (and timestamp) tokens.  Returns (ts int64[N] | None, val float64[N]).
+        Raises ValueError naming the first malformed token, like float() at app.py:188."""
+        t = self.torch
+        text = t.from_numpy(tok.flat).to(self.device)
+        n = tok.n_samples
+        val = self._empty((n,), t.float64)
+        bad = self._empty((2,), t.int64)
+        voff = t.from_numpy(tok.val_off.view(np.int32)).to(self.device)
+        _abi.check(self.lib.pmx_parse_f64(self.ctx, self._ptr(text), text.numel(), self._ptr(voff), n,
+                                          self._ptr(val), self._ptr(bad[0:]), self._stream()))
+        self.launches += 2
+        ts = None
+        if want_ts:
+            ts = self._empty((n,), t.int64)
+            toff = t.from_numpy(tok.ts_off.view(np.int32)).to(self.device)
+            _abi.check(self.lib.pmx_parse_ts_ms(self.ctx, self._ptr(text), text.numel(), self._ptr(toff), n,
+                                                self._ptr(ts), self._ptr(bad[1:]), self._stream()))
+            self.launches += 2
+        b = bad.cpu().tolist()
+        if b[0] != _abi.INT64_MAX:
+            o = int(tok.val_off[b[0]])
+            end = o
+            while end < len(tok.flat) and tok.flat[end] != 0x22:
+                end += 1
+            raise ValueError(f"could not convert string to float: {bytes(tok.flat[o:end]).decode('utf-8', 'replace')!r}")
+        if want_ts and b[1] != _abi.INT64_MAX:
+            raise ValueError(f"malformed timestamp in sample {b[1]}")
+        return ts, val
+
+    # ------------------------------------------------------------------ K2
+    def align(self, ts, val, off, start_ms, step_ms, n_steps, lookback_ms=DEFAULT_LOOKBACK_MS, want_idx=True):
+        t = self.torch
+        ts, val, off = self._dev(ts, t.int64), self._dev(val, t.float64), self._dev(off, t.int64)
+        S = off.numel() - 1
+        out = self._empty((S, n_steps), t.float64)
+        idx = self._empty((S, n_steps), t.int32) if want_idx else None
+        _abi.check(self.lib.pmx_align(self.ctx, self._ptr(ts), self._ptr(val), self._ptr(off), S, start_ms, step_ms,
+                                      n_steps, lookback_ms, self._ptr(out), self._ptr(idx), self._stream()))
+        self.launches += 1
+        return out, idx
+
+    # ------------------------------------------------------------------ K3
+    def rolling(self, x, window_steps, min_periods=1, want_count=True):
+        t = self.torch
+        x = self._dev(x, t.float64)
+        S, T = x.shape
+        mn, mx, mean = (self._empty((S, T), t.float64) for _ in range(3))
+        cnt = self._empty((S, T), t.int32) if want_count else None
+        _abi.check(self.lib.pmx_rolling(self.ctx, self._ptr(x), S, T, window_steps, min_periods, self._ptr(mn),
+                                        self._ptr(mx), self._ptr(mean), self._ptr(cnt), self._stream()))
+        self.launches += 1
+        return mn, mx, mean, cnt
+
+    def rolling_ragged(self, ts, val, off, window_ms, min_periods=1):
+        t = self.torch
+        ts, val, off = self._dev(ts, t.int64), self._dev(val, t.float64), self._dev(off, t.int64)
+        N, S = ts.numel(), off.numel() - 1
+        mn, mx, mean = (self._empty((N,), t.float64) for _ in range(3))
+        cnt = self._empty((N,), t.int32)
+        _abi.check(self.lib.pmx_rolling_ragged(self.ctx, self._ptr(ts), self._ptr(val), self._ptr(off), S, N,
+                                               window_ms, min_periods, self._ptr(mn), self._ptr(mx),
+                                               self._ptr(mean), self._ptr(cnt), self._stream()))
+        self.launches += 1
+        return mn, mx, mean, cnt
+
+    # ------------------------------------------------------------------ K4
+    def rate(self, x, window_steps, step_ms):
+        t = self.torch
+        x = self._dev(x, t.float64)
+        S, T = x.shape
+        inc, rt = self._empty((S, T), t.float64), self._empty((S, T), t.float64)
+        nres = self._empty((S, T), t.int32)
+        _abi.check(self.lib.pmx_rate(self.ctx, self._ptr(x), S, T, window_steps, step_ms, self._ptr(inc),
+                                     self._ptr(rt), self._ptr(nres), self._stream()))
+        self.launches += 1
+        return inc, rt, nres
+
+    def rate_ragged(self, ts, val, off, window_ms):
+        t = self.torch
+        ts, val, off = self._dev(ts, t.int64), self._dev(val, t.float64), self._dev(off, t.int64)
+        N, S = ts.numel(), off.numel() - 1
+        inc, rt = self._empty((N,), t.float64), self._empty((N,), t.float64)
+        nres = self._empty((N,), t.int32)
+        _abi.check(self.lib.pmx_rate_ragged(self.ctx, self._ptr(ts), self._ptr(val), self._ptr(off), S, N, window_ms,
+                                            self._ptr(inc), self._ptr(rt), self._ptr(nres), self._stream()))
+        self.launches += 1
+        return inc, rt, nres
+
+    # ------------------------------------------------------------------ fused
+    def fused(self, ts, val, off, start_ms, step_ms, n_steps, window_steps, lookback_ms=DEFAULT_LOOKBACK_MS,
+              min_periods=1, out=None):
+        """X3+X4+X5 in one kernel.  ``out`` may hold preallocated [S, n_steps] float64 tensors
+        (keys aligned, roll_min, roll_max, roll_mean, rate) to avoid allocation in a timed loop."""
+        t = self.torch
+        ts, val, off = self._dev(ts, t.int64), self._dev(val, t.float64), self._dev(off, t.int64)
+        S = off.numel() - 1
+        if out is None:
+            out = {k: self._empty((S, n_steps), t.float64)
+                   for k in ("aligned", "roll_min", "roll_max", "roll_mean", "rate")}
+        _abi.check(self.lib.pmx_fused_align_rolling_rate(
+            self.ctx, self._ptr(ts), self._ptr(val), self._ptr(off), S, start_ms, step_ms, n_steps, lookback_ms,
+            window_steps, min_periods, self._ptr(out["aligned"]), self._ptr(out["roll_min"]),
+            self._ptr(out["roll_max"]), self._ptr(out["roll_mean"]), self._ptr(out["rate"]), self._stream()))
+        self.launches += 1
+        return out
+
+    # ------------------------------------------------------------------ K5
+    def group_reduce(self, x, group_id, n_groups, per_step=False, perm_goff=None):
+        """NaN-skipping sum/count/min/max/mean per group.  group_id: int per series (host)."""
+        t = self.torch
+        x = self._dev(x, t.float64)
+        S, T = x.shape
+        perm, goff = perm_goff if perm_goff is not None else group_index(group_id, n_groups)
+        d_perm, d_goff = self._dev(perm, t.int32), self._dev(goff, t.int64)
+        shape = (n_groups, T) if per_step else (n_groups,)
+        sm, mn, mx, mean = (self._empty(shape, t.float64) for _ in range(4))
+        cnt = self._empty(shape, t.int64)
+        _abi.check(self.lib.pmx_group_reduce(self.ctx, self._ptr(x), S, T, self._ptr(d_perm), self._ptr(d_goff),
+                                             n_groups, 1 if per_step else 0, self._ptr(sm), self._ptr(cnt),
+                                             self._ptr(mn), self._ptr(mx), self._ptr(mean), self._stream()))
+        self.launches += 1 if per_step else 2
+        return sm, cnt, mn, mx, mean
+
+    # ------------------------------------------------------------------ instant-path steps
+    def pivot_gather(self, val, cell_src):
+        t = self.torch
+        val = self._dev(val, t.float64)
+        src = self._dev(cell_src, t.int32)
+        out = self._empty((src.numel(),), t.float64)
+        _abi.check(self.lib.pmx_pivot_gather(self.ctx, self._ptr(val), self._ptr(src), src.numel(), self._ptr(out),
+                                             self._stream()))
+        self.launches += 1
+        return out
+
+    def ratio_pct(self, mat, num_col, den_col, out_col):
+        """mat[:, out_col] = mat[:, num_col] / mat[:, den_col] * 100 on a row-major [G, C] matrix.
+        Returns True if any denominator was zero."""
+        t = self.torch
+        G, Cc = mat.shape
+        flag = self._empty((1,), t.int32)
+        base = mat.data_ptr()
+        _abi.check(self.lib.pmx_ratio_pct(self.ctx, C.c_void_p(base + 8 * num_col), Cc, C.c_void_p(base + 8 * den_col),
+                                          Cc, G, C.c_void_p(base + 8 * out_col), Cc, self._ptr(flag), self._stream()))
+        self.launches += 1
+        return bool(flag.item())
+
+    def where_gt(self, x, threshold):
+        t = self.torch
+        x = self._dev(x, t.float64)
+        out = self.torch.empty_like(x)
+        _abi.check(self.lib.pmx_where_gt(self.ctx, self._ptr(x), x.numel(), float(threshold), self._ptr(out),
+                                         self._stream()))
+        self.launches += 1
+        return out
+
+    # ------------------------------------------------------------------ K6
+    def quantile_buffers(self, n_seg, n_q):
+        t = self.torch
+        state = self.torch.zeros((n_seg, 2 + 4 * n_q), dtype=t.int64, device=self.device)
+        hist = self._empty((n_seg * 2 * n_q, _abi.QUANTILE_BINS), t.int64)
+        return state, hist
+
+    def quantiles(self, x, seg, n_seg, qs, group=None, buffers=None):
+        """Exact quantiles per segment.  x: [S,T] device; seg: int per series (host or device).
+        With ``group`` (a torch.distributed process group over NCCL) the histograms of every pass
+        are all-reduced, so the result is the quantile of the union of all ranks' values."""
+        t = self.torch
+        x = self._dev(x, t.float64)
+        S, T = x.shape
+        d_seg = self._dev(seg, t.int32)
+        n_q = len(qs)
+        d_q = self._dev(np.asarray(qs, dtype=np.float64), t.float64)
+        outs = {"n": self._empty((n_seg,), t.int64), "lo": self._empty((n_seg, n_q), t.int64),
+                "hi": self._empty((n_seg, n_q), t.int64), "x_lo": self._empty((n_seg, n_q), t.float64),
+                "x_hi": self._empty((n_seg, n_q), t.float64), "value": self._empty((n_seg, n_q), t.float64)}
+        if group is None:
+            _abi.check(self.lib.pmx_quantile_select(
+                self.ctx, self._ptr(x), S, T, self._ptr(d_seg), n_seg, self._ptr(d_q), n_q, self._ptr(outs["n"]),
+                self._ptr(outs["lo"]), self._ptr(outs["hi"]), self._ptr(outs["x_lo"]), self._ptr(outs["x_hi"]),
+                self._ptr(outs["value"]), self._stream()))
+            self.launches += 2 * _abi.QUANTILE_PASSES + 1
+            return outs
+        import torch.distributed as dist
+        state, hist = buffers if buffers is not None else self.quantile_buffers(n_seg, n_q)
+        state.zero_()
+        for p in range(_abi.QUANTILE_PASSES):
+            _abi.check(self.lib.pmx_quantile_hist(self.ctx, self._ptr(x), S, T, self._ptr(d_seg), n_seg, n_q, p,
+                                                  self._ptr(state), self._ptr(hist), self._stream()))
+            n_h = n_seg * (1 if p == 0 else 2 * n_q)
+            dist.all_reduce(hist[:n_h], op=dist.ReduceOp.SUM, group=group)
+            _abi.check(self.lib.pmx_quantile_pick(self.ctx, self._ptr(hist), n_seg, self._ptr(d_q), n_q, p,
+                                                  self._ptr(state), self._stream()))
+        _abi.check(self.lib.pmx_quantile_finish(self.ctx, self._ptr(state), n_seg, self._ptr(d_q), n_q,
+                                                self._ptr(outs["n"]), self._ptr(outs["lo"]), self._ptr(outs["hi"]),
+                                                self._ptr(outs["x_lo"]), self._ptr(outs["x_hi"]),
+                                                self._ptr(outs["value"]), self._stream()))
+        self.launches += 2 * _abi.QUANTILE_PASSES + 1
+        return outs

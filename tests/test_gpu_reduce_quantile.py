@@ -1,0 +1,85 @@
+"""GPU: K5 group reductions and K6 radix-select quantiles against the oracle."""
+import numpy as np
+import pytest
+
+from k8s_rocm_metrics_dashboard_b200 import synth
+from oracle import prom_oracle as O
+from tests.util import assert_bits_equal, assert_close, assert_exact_or_nan
+
+pytestmark = pytest.mark.gpu
+
+
+def _np(t):
+    return t.cpu().numpy()
+
+
+@pytest.mark.parametrize("S,T,G", [(12, 40, 3), (96, 1000, 7), (5, 1, 5), (300, 257, 1)])
+def test_group_reduce_scalar_and_per_step(eng, S, T, G):
+    rng = np.random.default_rng(S * T)
+    x = rng.uniform(-5, 10, (S, T)); x[rng.random(x.shape) < 0.1] = np.nan
+    gid = rng.integers(-1, G, S).astype(np.int32)
+    gid[0] = G - 1
+    for per_step in (False, True):
+        sm, cnt, mn, mx, mean = eng.group_reduce(x, gid, G, per_step=per_step)
+        osm, ocnt, omn, omx, omean = O.group_reduce(x, gid, G, per_step=per_step)
+        assert np.array_equal(_np(cnt), ocnt)
+        assert_exact_or_nan(_np(mn), omn, "min"); assert_exact_or_nan(_np(mx), omx, "max")
+        scale = 10.0 * np.maximum(ocnt, 1)
+        assert_close(_np(sm), osm, scale=scale, rtol=1e-12, what="sum")
+        assert_close(_np(mean), omean, scale=np.full(omean.shape, 10.0), rtol=1e-12, what="mean")
+
+
+def test_group_reduce_empty_group_and_all_nan(eng):
+    x = np.full((4, 10), np.nan); x[0, 3] = 2.0
+    sm, cnt, mn, mx, mean = eng.group_reduce(x, np.array([0, 0, 1, 1], dtype=np.int32), 3)
+    assert _np(cnt).tolist() == [1, 0, 0] and _np(sm).tolist() == [2.0, 0.0, 0.0]
+    assert _np(mn)[0] == 2.0 and np.isnan(_np(mn)[1:]).all() and np.isnan(_np(mean)[2])
+
+
+def test_group_reduce_per_step_is_sequential_like_pandas(eng):
+    """Per-step sums visit the series in order: bit-identical to a left-to-right Python sum."""
+    rng = np.random.default_rng(1)
+    x = rng.uniform(0, 1e6, (50, 33))
+    sm, cnt, *_ = eng.group_reduce(x, np.zeros(50, dtype=np.int32), 1, per_step=True)
+    exp = np.zeros(33)
+    for s in range(50):
+        exp = exp + x[s]
+    assert_bits_equal(_np(sm)[0], exp)
+
+
+def _check_quantiles(eng, x, seg, n_seg, qs):
+    out = eng.quantiles(x, seg, n_seg, qs)
+    for g in range(n_seg):
+        o = O.quantiles(x[np.asarray(seg) == g], qs)
+        assert int(_np(out["n"])[g]) == o["n"]
+        assert _np(out["lo"])[g].tolist() == o["lo"] and _np(out["hi"])[g].tolist() == o["hi"]
+        assert_bits_equal(_np(out["x_lo"])[g], np.array(o["x_lo"]), "x_lo")
+        assert_bits_equal(_np(out["x_hi"])[g], np.array(o["x_hi"]), "x_hi")
+        assert_bits_equal(_np(out["value"])[g], np.array(o["value"]), "value")
+
+
+def test_quantiles_exact_order_statistics(eng):
+    rng = np.random.default_rng(4)
+    x = rng.normal(size=(24, 700)) * np.exp(rng.normal(size=(24, 1)) * 5)
+    x[rng.random(x.shape) < 0.05] = np.nan
+    x[0, 0] = np.inf; x[1, 1] = -np.inf; x[2, 2] = -0.0; x[3, 3] = 0.0; x[4, 4] = 5e-324; x[5, 5] = -5e-324
+    seg = (np.arange(24) % 3).astype(np.int32)
+    _check_quantiles(eng, x, seg, 3, [0.5, 0.95, 0.99])
+    _check_quantiles(eng, x, seg, 3, [0.0, 1.0, 0.25, 0.123456789])
+
+
+def test_quantiles_heavy_ties_and_tiny_segments(eng):
+    rng = np.random.default_rng(5)
+    x = rng.integers(0, 101, (16, 500)).astype(np.float64)       # gfx_activity: 101 distinct values
+    seg = np.array([0] * 8 + [1] * 7 + [-1], dtype=np.int32)
+    _check_quantiles(eng, x, seg, 2, [0.5, 0.95, 0.99])
+    y = np.full((3, 4), np.nan); y[0, 1] = 7.0; y[1, 0] = 1.0; y[1, 3] = 2.0
+    _check_quantiles(eng, y, np.array([0, 1, 2], dtype=np.int32), 3, [0.5, 0.99])   # n = 1, 2, 0
+
+
+def test_quantiles_config4_shape_scaled(eng):
+    d = synth.config("config4", seed=2, scale=1 / 16)
+    al, _ = O.align(d["ts"], d["val"], d["off"], d["start_ms"], d["step_ms"], d["n_steps"])
+    names = sorted({l["__name__"] for l in d["labels"]})
+    seg = np.array([names.index(l["__name__"]) for l in d["labels"]], dtype=np.int32)
+    _check_quantiles(eng, al, seg, len(names), [0.5, 0.95, 0.99])

@@ -1,0 +1,173 @@
+"""GPU: K2 align, K3 rolling, K4 rate and the fused kernel against the oracle (C ABI path)."""
+import numpy as np
+import pytest
+
+from k8s_rocm_metrics_dashboard_b200 import synth
+from oracle import prom_oracle as O
+from tests.util import assert_bits_equal, assert_close, assert_exact_or_nan
+
+pytestmark = pytest.mark.gpu
+
+
+def _np(t):
+    return t.cpu().numpy()
+
+
+def _check_roll(eng, x, w, min_periods=1):
+    mn, mx, mean, cnt = eng.rolling(x, w, min_periods)
+    omn, omx, omean, ocnt = O.rolling(x, w, min_periods)
+    assert_exact_or_nan(_np(mn), omn, f"min w={w}")
+    assert_exact_or_nan(_np(mx), omx, f"max w={w}")
+    assert np.array_equal(_np(cnt), ocnt), f"count w={w}"
+    assert_close(_np(mean), omean, scale=O.rolling_scale(x, w), rtol=1e-12, what=f"mean w={w}")
+
+
+@pytest.mark.parametrize("w", [1, 2, 7, 8, 9, 16, 17, 60, 61, 64, 240, 1000, 1025, 3000])
+def test_rolling_windows(eng, w):
+    rng = np.random.default_rng(w)
+    T = 5000 if w <= 1025 else 3500
+    x = np.round(rng.uniform(-50, 100, (5, T)), 3)
+    x[rng.random(x.shape) < 0.03] = np.nan
+    x[0, 100] = np.inf; x[1, 200] = -np.inf; x[2, :2100] = np.nan; x[3, 7] = -0.0
+    _check_roll(eng, x, w)
+
+
+@pytest.mark.parametrize("shape", [(1, 1), (3, 5), (1, 2047), (2, 2048), (2, 2049), (7, 1989), (1, 1990), (300, 17)])
+def test_rolling_shapes(eng, shape):
+    rng = np.random.default_rng(shape[1])
+    x = rng.normal(size=shape)
+    x[rng.random(shape) < 0.1] = np.nan
+    for w in (1, 5, 60):
+        _check_roll(eng, x, w)
+
+
+def test_rolling_min_periods_and_all_nan(eng):
+    rng = np.random.default_rng(0)
+    x = rng.normal(size=(3, 700)); x[1, 300] = np.nan; x[2] = np.nan
+    _check_roll(eng, x, 60, min_periods=60)
+    _check_roll(eng, x, 60, min_periods=3)
+
+
+def test_rolling_mean_is_fresh_per_window(eng):
+    """A huge value leaving the window must not poison later means (no prefix differences)."""
+    x = np.ones((1, 4000)); x[0, 10] = 1e300; x[0, 2500] = -1e250
+    _check_roll(eng, x, 60)
+    mn, mx, mean, cnt = eng.rolling(x, 60)
+    assert _np(mean)[0, 100] == 1.0 and _np(mean)[0, 3000] == 1.0
+
+
+def _check_rate(eng, x, w, step_ms=15000):
+    inc, rt, nr = eng.rate(x, w, step_ms)
+    oinc, ort, onr = O.rate(x, w, step_ms)
+    assert np.array_equal(_np(nr), onr), f"n_resets w={w}"
+    sc = O.rate_scale(x, w)
+    assert_close(_np(inc), oinc, scale=sc, rtol=1e-12, what=f"increase w={w}")
+    with np.errstate(divide="ignore", invalid="ignore"):
+        assert_close(_np(rt), ort, scale=sc / (step_ms / 1000.0), rtol=1e-12, what=f"rate w={w}")
+
+
+@pytest.mark.parametrize("w", [1, 2, 3, 8, 9, 60, 100, 1030])
+def test_rate_with_resets(eng, w):
+    d = synth.dense(1, 2, 3, 2600, seed=w, all_counters=True, reset_prob=0.02, nan_frac=0.02)
+    x = d["val"].reshape(6, 2600)
+    x[5, :2200] = np.nan
+    _check_rate(eng, x, w)
+
+
+def test_rate_small_cases(eng):
+    x = np.array([[10., 20., 5., 7., np.nan, 9., 2., 2.], [np.nan] * 8, [1., np.nan, np.nan, np.nan, np.nan, np.nan, np.nan, 2.]])
+    _check_rate(eng, x, 4, 1000)
+    _check_rate(eng, x, 8, 1000)
+
+
+def _check_align(eng, d, n_steps, start=None, step=None, lookback=300_000):
+    start = d.get("start_ms", synth.START_MS) if start is None else start
+    step = d.get("step_ms", synth.STEP_MS) if step is None else step
+    al, idx = eng.align(d["ts"], d["val"], d["off"], start, step, n_steps, lookback)
+    oal, oidx = O.align(d["ts"], d["val"], d["off"], start, step, n_steps, lookback)
+    assert np.array_equal(_np(idx), oidx), "alignment indices"
+    assert_bits_equal(_np(al), oal, "aligned values")
+
+
+def test_align_regular_and_empty(eng):
+    d = synth.dense(2, 2, 3, 3000, seed=1, nan_frac=0.01)
+    _check_align(eng, d, 3000)
+    _check_align(eng, d, 7000, start=d["start_ms"] - 500 * 15000)       # grid wider than the data
+    _check_align(eng, d, 100, step=60_000)                               # coarser grid (down-sampling)
+    _check_align(eng, d, 4500, step=1000)                                # finer grid than the scrape
+    d["off"] = np.concatenate([d["off"][:3], d["off"][2:]])              # an empty series in the middle
+    d["off"][3] = d["off"][2]
+    _check_align(eng, d, 3000)
+
+
+def test_align_ragged_staleness_and_markers(eng):
+    d = synth.ragged(300, seed=3, mean_len=300, nan_frac=0.02, stale_frac=0.02, gap_frac=0.03)
+    t0 = int(d["ts"].min())
+    _check_align(eng, d, 2500, start=t0, step=15000)
+    _check_align(eng, d, 2500, start=t0, step=15000, lookback=20_000)
+    _check_align(eng, d, 300, start=t0 + 7, step=200_000)                # many samples per grid step
+
+
+def test_fused_matches_oracle_config1(eng):
+    d = synth.config("config1", seed=0)
+    w = 60
+    out = eng.fused(d["ts"], d["val"], d["off"], d["start_ms"], d["step_ms"], d["n_steps"], w)
+    ref = O.aggregate_range(d["ts"], d["val"], d["off"], d["start_ms"], d["step_ms"], d["n_steps"], w * d["step_ms"])
+    assert_bits_equal(_np(out["aligned"]), ref["aligned"], "aligned")
+    assert_exact_or_nan(_np(out["roll_min"]), ref["roll_min"], "roll_min")
+    assert_exact_or_nan(_np(out["roll_max"]), ref["roll_max"], "roll_max")
+    assert_close(_np(out["roll_mean"]), ref["roll_mean"], scale=O.rolling_scale(ref["aligned"], w), what="roll_mean")
+    assert_close(_np(out["rate"]), ref["rate"], scale=O.rate_scale(ref["aligned"], w) / 15.0, what="rate")
+
+
+@pytest.mark.parametrize("name,scale", [("config2", 1 / 32), ("config4", 1 / 32)])
+def test_fused_matches_oracle_scaled_configs(eng, name, scale):
+    d = synth.config(name, seed=1, scale=scale)
+    w = 60
+    out = eng.fused(d["ts"], d["val"], d["off"], d["start_ms"], d["step_ms"], d["n_steps"], w)
+    ref = O.aggregate_range(d["ts"], d["val"], d["off"], d["start_ms"], d["step_ms"], d["n_steps"], w * d["step_ms"])
+    assert_bits_equal(_np(out["aligned"]), ref["aligned"], "aligned")
+    assert_exact_or_nan(_np(out["roll_min"]), ref["roll_min"], "roll_min")
+    assert_exact_or_nan(_np(out["roll_max"]), ref["roll_max"], "roll_max")
+    assert_close(_np(out["roll_mean"]), ref["roll_mean"], scale=O.rolling_scale(ref["aligned"], w), what="roll_mean")
+    assert_close(_np(out["rate"]), ref["rate"], scale=O.rate_scale(ref["aligned"], w) / 15.0, what="rate")
+
+
+def test_fused_equals_unfused_at_full_config2(eng):
+    """Size-independent property at BASELINE.json's full size: the fused kernel and the three
+    separate kernels (align -> rolling, rate) agree bit for bit on 35.4 M samples."""
+    t = eng.torch
+    ts, val, off = synth.dense_device(6144, 5760, 12, seed=0, device=eng.device)
+    out = eng.fused(ts, val, off, synth.START_MS, synth.STEP_MS, 5760, 60)
+    al, _ = eng.align(ts, val, off, synth.START_MS, synth.STEP_MS, 5760, want_idx=False)
+    assert t.equal(out["aligned"].view(t.int64), al.view(t.int64))
+    mn, mx, mean, _ = eng.rolling(al, 60, want_count=False)
+    for a, b in ((out["roll_min"], mn), (out["roll_max"], mx), (out["roll_mean"], mean)):
+        assert t.equal(a.view(t.int64), b.view(t.int64))
+    _, rt, _ = eng.rate(al, 60, synth.STEP_MS)
+    assert t.equal(out["rate"].view(t.int64), rt.view(t.int64))
+    # rolling min <= mean <= max wherever defined; first grid point of every series has no sample
+    ok = ~t.isnan(mean)
+    assert bool(((mn <= mean + 1e-9 * mean.abs()) & (mean <= mx + 1e-9 * mx.abs()))[ok].all())
+    assert bool(t.isnan(al[:, 0]).float().mean() > 0.99)
+
+
+def test_fused_window_limit_is_reported(eng):
+    d = synth.dense(1, 1, 1, 100, seed=0)
+    from k8s_rocm_metrics_dashboard_b200._abi import PmxError
+    with pytest.raises(PmxError, match="exceeds the fused limit"):
+        eng.fused(d["ts"], d["val"], d["off"], d["start_ms"], d["step_ms"], 100, 5000)
+
+
+def test_ragged_rolling_and_rate(eng):
+    d = synth.ragged(400, seed=5, mean_len=150, nan_frac=0.02, stale_frac=0.01, gap_frac=0.02)
+    mn, mx, mean, cnt = eng.rolling_ragged(d["ts"], d["val"], d["off"], 900_000)
+    omn, omx, omean, ocnt = O.rolling_ragged(d["ts"], d["val"], d["off"], 900_000)
+    assert_exact_or_nan(_np(mn), omn); assert_exact_or_nan(_np(mx), omx)
+    assert np.array_equal(_np(cnt), ocnt)
+    assert_close(_np(mean), omean, rtol=1e-12)
+    inc, rt, nr = eng.rate_ragged(d["ts"], d["val"], d["off"], 900_000)
+    oinc, ort, onr = O.rate_ragged(d["ts"], d["val"], d["off"], 900_000)
+    assert np.array_equal(_np(nr), onr)
+    assert_close(_np(inc), oinc, scale=np.full(len(oinc), 1000.0), rtol=1e-12)
+    assert_close(_np(rt), ort, scale=np.full(len(ort), 1000.0 / 13.0), rtol=1e-12)

@@ -1,0 +1,183 @@
+"""CPU: the C-ABI library loads and exports what include/pmx.h declares; host-side logic
+(tokenizer, group index) and the host build of the parser state machine."""
+import ctypes as C
+import json
+import os
+import re
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+
+from k8s_rocm_metrics_dashboard_b200 import _abi, synth, tokenize, group_index
+from oracle import prom_oracle as O
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "pmx.h")).read()
+    declared = set(re.findall(r"\b(pmx_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 20
+    lib = _abi.lib()
+    for name in sorted(declared):
+        assert hasattr(lib, name), f"{name} declared in pmx.h but not exported by libpmx.so"
+    assert declared == set(_abi.SIGNATURES), declared ^ set(_abi.SIGNATURES)
+    assert lib.pmx_version() == 100
+
+
+def test_no_gpu_fails_loudly():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from k8s_rocm_metrics_dashboard_b200 import Engine
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        Engine()
+    p = C.c_void_p()
+    assert _abi.lib().pmx_ctx_create(0, C.byref(p)) == _abi.E_CUDA
+    assert b"no CPU path" in _abi.lib().pmx_last_error()
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "k8s_rocm_metrics_dashboard_b200")
+    for dp, _, fs in os.walk(pkg):
+        for f in fs:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dp, f)).read()
+                assert "from oracle" not in src and "import oracle" not in src and "prom_oracle" not in src, f
+
+
+def _tok_text(tok, offs, term):
+    out = []
+    for o in offs:
+        e = int(o)
+        while tok.flat[e] != term:
+            e += 1
+        out.append(bytes(tok.flat[int(o):e]).decode())
+    return out
+
+
+def test_tokenizer_matches_json_loads_matrix():
+    d = synth.dense(2, 2, 3, 20, seed=4, nan_frac=0.1)
+    d["val"][3] = np.inf; d["val"][7] = -np.inf
+    body = synth.to_matrix_json(d["labels"], d["ts"], d["val"], d["off"])
+    tok = tokenize(body)
+    ts_tok, val_tok, off = O.raw_tokens(body)
+    assert tok.result_type == "matrix"
+    assert tok.series_off.tolist() == off
+    assert _tok_text(tok, tok.val_off, 0x22) == val_tok
+    assert [t.strip() for t in _tok_text(tok, tok.ts_off, 0x2C)] == ts_tok
+    assert tok.labels() == d["labels"]
+
+
+def test_tokenizer_vector_whitespace_escapes_and_extra_keys():
+    body = ('{ "status" : "success", "warnings":["x",{"a":[1,2,{"b":"]}"}]}], "data" : {"result" : [\n'
+            ' {"metric":{"__name__":"m","gpu_id":"0","q":"a\\"b}"}, "value" : [ 1700000000.5 , "1.5" ] , "extra": null},\n'
+            ' {"value":[1700000001,"\\u0031\\t2"],"metric":{}},'
+            ' {"metric":{"k":"v"},"values":[]}, {"metric":{"k":"w"},"histograms":[[1,{"count":"3"}]]}\n'
+            '], "resultType":"vector" } }').encode()
+    tok = tokenize(body)
+    assert tok.result_type == "vector" and tok.n_series == 4 and tok.n_samples == 2
+    assert tok.series_off.tolist() == [0, 1, 2, 2, 2]
+    assert _tok_text(tok, tok.val_off, 0x22) == ["1.5", "1\t2"]
+    assert tok.val_off[1] >= len(body)                      # decoded copy lives in the extra region
+    assert [t.strip() for t in _tok_text(tok, tok.ts_off, 0x2C)] == ["1700000000.5", "1700000001"]
+    assert tok.labels()[0] == {"__name__": "m", "gpu_id": "0", "q": 'a"b}'}
+
+
+@pytest.mark.parametrize("body, exc", [
+    (b'{"status":"error","errorType":"bad_data","error":"x"}', ValueError),
+    (b'{"status":"success","data":{"resultType":"matrix"}}', KeyError),
+    (b'{"status":"success","data":{"resultType":"matrix","result":[{"metric":{},"values":[[1,"2"]}]}}', ValueError),
+    (b'{"status":"success","data":{"resultType":"scalar","result":[]}}', ValueError),
+    (b'[1,2]', ValueError), (b'', ValueError),
+    (b'{"status":"success","data":{"resultType":"matrix","result":[]}} trailing', ValueError),
+])
+def test_tokenizer_rejects(body, exc):
+    with pytest.raises(exc):
+        tokenize(body)
+
+
+def test_tokenizer_empty_result():
+    tok = tokenize(b'{"status":"success","data":{"resultType":"vector","result":[]}}')
+    assert tok.n_series == 0 and tok.n_samples == 0 and tok.series_off.tolist() == [0]
+
+
+def test_group_index_stable_csr():
+    gid = np.array([2, 0, -1, 2, 1, 0, 2], dtype=np.int32)
+    perm, goff = group_index(gid, 4)
+    assert goff.tolist() == [0, 2, 3, 6, 6]
+    assert perm.tolist() == [1, 5, 4, 0, 3, 6]
+
+
+@pytest.fixture(scope="module")
+def host_lib():
+    so = os.path.join(ROOT, "tests", "_build", "strtod_host.so")
+    src = os.path.join(ROOT, "tests", "host", "strtod_host.cpp")
+    os.makedirs(os.path.dirname(so), exist_ok=True)
+    subprocess.check_call(["g++", "-O2", "-shared", "-fPIC", "-o", so, src])
+    return C.CDLL(so)
+
+
+def _host_parse(lib, toks):
+    enc = [t.encode("utf-8") for t in toks]
+    off = np.zeros(len(enc) + 1, dtype=np.int64)
+    off[1:] = np.cumsum([len(e) for e in enc])
+    buf = b"".join(enc) + b"\0"
+    bits = np.zeros(len(enc), dtype=np.uint64); st = np.zeros(len(enc), dtype=np.int32)
+    lib.host_parse_many(buf, C.c_void_p(off.ctypes.data), C.c_int64(len(enc)), C.c_void_p(bits.ctypes.data),
+                        C.c_void_p(st.ctypes.data))
+    return bits, st
+
+
+def test_parser_state_machine_on_host_matches_float_golden(host_lib, golden_dir):
+    """Same strtod_core.h the K1 kernel compiles, built for the host: every golden token
+    (ASCII ones; CPython also accepts non-ASCII digits, which Prometheus never emits)."""
+    g = [(t, e) for t, e in json.load(open(os.path.join(golden_dir, "float_golden.json")))
+         if all(ord(c) < 128 for c in t)]
+    bits, st = _host_parse(host_lib, [t for t, _ in g])
+    for (tok, exp), b, s in zip(g, bits, st):
+        got = "ValueError" if s else "%016x" % b
+        assert got == exp, repr(tok[:80])
+
+
+def test_parser_state_machine_fuzz_vs_python_float(host_lib):
+    import random
+    rnd = random.Random(7)
+    toks = []
+    for _ in range(60000):
+        k = rnd.random()
+        if k < 0.35:
+            x = struct.unpack("<d", struct.pack("<Q", rnd.getrandbits(64)))[0]
+            toks.append(repr(x) if x == x else "nan")
+        elif k < 0.7:
+            nd = rnd.randint(1, 45)
+            s = "".join(rnd.choice("0123456789") for _ in range(nd))
+            p = rnd.randint(0, nd)
+            s = s[:p] + "." + s[p:] if rnd.random() < 0.7 else s
+            if rnd.random() < 0.7:
+                s += "e%d" % rnd.randint(-350, 320)
+            toks.append(rnd.choice(["", "-", "+"]) + s)
+        else:
+            x = struct.unpack("<d", struct.pack("<Q", rnd.getrandbits(63)))[0]
+            if x == x and x != float("inf"):
+                toks.append("%.*e" % (rnd.randint(15, 40), x))
+    bits, st = _host_parse(host_lib, toks)
+    exp = np.array([struct.unpack("<Q", struct.pack("<d", float(t)))[0] for t in toks], dtype=np.uint64)
+    assert not st.any()
+    bad = np.flatnonzero(bits != exp)
+    assert len(bad) == 0, [toks[i] for i in bad[:5]]
+
+
+def test_timestamp_parser_host(host_lib):
+    for tok, exp in [("1700000000", 1700000000000), ("1700000000.5", 1700000000500), ("1700000000.123", 1700000000123),
+                     ("0", 0), ("-1.5", -1500), (" 12.250 ", 12250), ("1.0000", 1000)]:
+        out = C.c_int64()
+        b = tok.encode()
+        assert host_lib.host_parse_ts_ms(b, C.c_int64(len(b)), C.byref(out)) == 0 and out.value == exp, tok
+        assert out.value == O.parse_ts_ms(tok.strip())
+    for tok in ["", ".", "1.", "1.2345", "1e9", "abc", "1.5x", "99999999999999999999"]:
+        out = C.c_int64()
+        b = tok.encode()
+        assert host_lib.host_parse_ts_ms(b, C.c_int64(len(b)), C.byref(out)) != 0, tok
