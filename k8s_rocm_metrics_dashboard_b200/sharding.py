@@ -1,0 +1,116 @@
+"""Multi-GPU layer: one process per GPU, series sharded by label set.
+
+Series are independent for decode / align / rolling / rate, so ranks never exchange samples.
+The only exchange steps are
+  * per-group partials (sum, count, min, max) -- one all-reduce each (SUM, SUM, MIN, MAX) over
+    ``n_groups`` numbers, for groups that span ranks (cluster-wide per-metric groups);
+  * exact quantiles -- per pass, the 2048-bin histograms of every (segment, target) are summed
+    with one all-reduce (16 KiB per histogram), then every rank picks the same bin on its
+    own device (pmx_quantile_pick): no sample movement, no host round trip inside the passes.
+``torch.distributed`` (NCCL over NVLink/NVSwitch on GPUs, gloo in the CPU tests) is the plumbing.
+The combine logic is written against tensors and a process group so that the world_size-2
+gloo tests exercise exactly this code with CPU tensors.
+"""
+from __future__ import annotations
+
+import json
+import zlib
+
+import numpy as np
+
+
+def label_hash(labels: dict) -> int:
+    """Stable hash of a sorted label set (independent of process, rank and PYTHONHASHSEED)."""
+    canon = json.dumps(sorted(labels.items()), separators=(",", ":"), ensure_ascii=True)
+    return zlib.crc32(canon.encode("ascii"))
+
+
+def partition(label_sets, world_size: int):
+    """rank of every series: hash(sorted label set) mod world_size."""
+    return np.fromiter((label_hash(l) % world_size for l in label_sets), dtype=np.int32, count=len(label_sets))
+
+
+def shard_csr(ts, val, off, owner, rank):
+    """The CSR arrays of the series owned by ``rank`` (host arrays), plus their global indices."""
+    mine = np.flatnonzero(owner == rank)
+    lens = (off[1:] - off[:-1])[mine]
+    new_off = np.zeros(len(mine) + 1, dtype=np.int64)
+    np.cumsum(lens, out=new_off[1:])
+    if len(mine):
+        idx = np.concatenate([np.arange(off[s], off[s + 1]) for s in mine]) if new_off[-1] else np.zeros(0, dtype=np.int64)
+    else:
+        idx = np.zeros(0, dtype=np.int64)
+    return ts[idx], val[idx], new_off, mine
+
+
+def combine_group_partials(sm, cnt, mn, mx, group=None):
+    """All-reduce per-group partials in place and return (sum, count, min, max, mean).
+
+    Inputs are torch tensors of shape [G] (or [G,T]) as produced by ``Engine.group_reduce`` on the
+    local shard: empty groups carry sum 0, count 0, min/max NaN."""
+    import torch
+    import torch.distributed as dist
+    inf = float("inf")
+    mn = torch.where(cnt > 0, mn, torch.full_like(mn, inf))
+    mx = torch.where(cnt > 0, mx, torch.full_like(mx, -inf))
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM, group=group)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM, group=group)
+        dist.all_reduce(mn, op=dist.ReduceOp.MIN, group=group)
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX, group=group)
+    nan = torch.full_like(mn, float("nan"))
+    any_ = cnt > 0
+    mean = torch.where(any_, sm / cnt.to(sm.dtype).clamp(min=1), nan)
+    return sm, cnt, torch.where(any_, mn, nan), torch.where(any_, mx, nan), mean
+
+
+def distributed_quantiles(hist_fn, pick_fn, finish_fn, n_seg, n_q, group=None, passes=6):
+    """The radix-select protocol, independent of where hist/pick run.
+
+    hist_fn(pass) -> int64 tensor [n_hist, 2048] of LOCAL counts (n_hist = n_seg for pass 0,
+    n_seg*2*n_q afterwards); pick_fn(pass, reduced_hist) advances the per-target state;
+    finish_fn() returns the result.  The GPU engine plugs its kernels in (Engine.quantiles does
+    the same inline); the gloo tests plug in a numpy restatement."""
+    import torch.distributed as dist
+    for p in range(passes):
+        h = hist_fn(p)
+        if dist.is_initialized() and dist.get_world_size(group) > 1:
+            dist.all_reduce(h, op=dist.ReduceOp.SUM, group=group)
+        pick_fn(p, h)
+    return finish_fn()
+
+
+class ShardedEngine:
+    """Engine + process group: the aggregate step on this rank's shard with cluster-wide summaries."""
+
+    def __init__(self, engine, group=None):
+        import torch.distributed as dist
+        self.eng = engine
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self._qbuf = {}
+
+    def aggregate_step(self, ts, val, off, start_ms, step_ms, n_steps, window_steps, seg, n_seg, perm_goff,
+                       qs=(0.5, 0.95, 0.99), out=None, lookback_ms=300_000):
+        """fused align+rolling+rate on the shard, then per-metric sum/count/min/max/mean and exact
+        quantiles of the aligned values over ALL ranks.  ``seg``: metric id per local series."""
+        eng = self.eng
+        out = eng.fused(ts, val, off, start_ms, step_ms, n_steps, window_steps, lookback_ms, out=out)
+        sm, cnt, mn, mx, _ = eng.group_reduce(out["aligned"], None, n_seg, perm_goff=perm_goff)
+        if self.world > 1:
+            summary = combine_group_partials(sm, cnt, mn, mx, self.group)
+            key = (n_seg, len(qs))
+            if key not in self._qbuf:
+                self._qbuf[key] = eng.quantile_buffers(n_seg, len(qs))
+            q = eng.quantiles(out["aligned"], seg, n_seg, list(qs), group=self.group or _world_group(),
+                              buffers=self._qbuf[key])
+        else:
+            summary = combine_group_partials(sm, cnt, mn, mx, None)
+            q = eng.quantiles(out["aligned"], seg, n_seg, list(qs))
+        return out, summary, q
+
+
+def _world_group():
+    import torch.distributed as dist
+    return dist.group.WORLD

@@ -419,3 +419,19 @@ def aggregate_range_pandas(ts, val, off, start_ms, step_ms, n_steps, window_ms,
     rate_ = ((tot - d_first) / (t_last - t_first)).where(n >= 2)
     return {"aligned": al, "roll_min": mn.values.T, "roll_max": mx.values.T,
             "roll_mean": mean.values.T, "rate": rate_.values.T}
+
+
+def aggregate_step_pandas(ts, val, off, start_ms, step_ms, n_steps, window_ms, group_id, n_groups,
+                          qs=(0.5, 0.95, 0.99), lookback_ms=DEFAULT_LOOKBACK_MS):
+    """One whole aggregate step the way the reference would write it with pandas: the range
+    pipeline, then per-group sum/count/min/max/mean and quantiles of the aligned values.
+    This is what bench.py's cpu_baseline / --impl reference legs time."""
+    r = aggregate_range_pandas(ts, val, off, start_ms, step_ms, n_steps, window_ms, lookback_ms)
+    al = r["aligned"]
+    S = al.shape[0]
+    long = pd.DataFrame({"g": np.repeat(np.asarray(group_id), n_steps), "v": al.ravel()})
+    gb = long[long["g"] >= 0].groupby("g")["v"]
+    r["summary"] = gb.agg(["sum", "count", "min", "max", "mean"]).reindex(range(n_groups))
+    r["quantiles"] = gb.quantile(list(qs)).unstack().reindex(range(n_groups))
+    del S
+    return r
