@@ -32,18 +32,41 @@ __host__ __device__ __forceinline__ int digit_shift(int pass) { return pass < 5 
 __host__ __device__ __forceinline__ int digit_bits(int pass) { return pass < 5 ? 11 : 9; }
 __host__ __device__ __forceinline__ int state_words(int64_t n_q) { return 2 + 4 * (int)n_q; }
 
+// Adds one key to the CTA-private histograms.  All 32 lanes call this together (valid = lane has
+// a non-NaN element); lanes that hit the same bin are combined with match_any so that heavy ties
+// (pass 0 of gauge data lands in one or two bins) cost one shared atomic per warp, not 32.
+__device__ __forceinline__ void hist_add(unsigned int* sh, const uint64_t* s_prefix, int n_t, int pass,
+                                         int shift, unsigned mask, int pshift, bool valid, uint64_t key,
+                                         int lane) {
+  const unsigned d = (unsigned)(key >> shift) & mask;
+  if (pass == 0) {
+    const unsigned peers = __match_any_sync(0xffffffffu, valid ? d : 0xffffffffu);
+    if (valid && lane == __ffs(peers) - 1) atomicAdd(&sh[d], (unsigned)__popc(peers));
+    return;
+  }
+  const uint64_t top = key >> pshift;
+#pragma unroll 1
+  for (int k = 0; k < n_t; ++k) {
+    const bool hit = valid && top == s_prefix[k];
+    if (__ballot_sync(0xffffffffu, hit) == 0) continue;            // common case: nobody matches
+    const unsigned peers = __match_any_sync(0xffffffffu, hit ? d : 0xffffffffu);
+    if (hit && lane == __ffs(peers) - 1) atomicAdd(&sh[k * BINS + d], (unsigned)__popc(peers));
+  }
+}
+
 __global__ void __launch_bounds__(256)
 hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __restrict__ seg,
             int n_t, int pass, const uint64_t* __restrict__ state, int sw,
             unsigned long long* __restrict__ hist, int rows_per_cta, int64_t n_series) {
   extern __shared__ unsigned int sh[];                     // [n_h][BINS]
+  __shared__ uint64_t s_prefix[MAX_TARGETS];
   const int n_h = pass == 0 ? 1 : n_t;
   const int64_t s0 = (int64_t)blockIdx.x * rows_per_cta;
   const int shift = digit_shift(pass);
   const unsigned mask = (1u << digit_bits(pass)) - 1u;
-  const int pshift = 64 - 11 * pass;                       // key >> pshift == prefix  (pass >= 1)
+  const int pshift = pass == 0 ? 0 : 64 - 11 * pass;       // key >> pshift == prefix  (pass >= 1)
+  const int lane = threadIdx.x & 31;
   int cur_seg = -1;
-  uint64_t prefix[MAX_TARGETS];
   for (int r = 0; r < rows_per_cta; ++r) {
     const int64_t s = s0 + r;
     if (s >= n_series) break;
@@ -60,21 +83,30 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
       __syncthreads();
       for (int i = threadIdx.x; i < n_h * BINS; i += blockDim.x) sh[i] = 0;
       cur_seg = sg;
-      if (pass > 0)
-        for (int k = 0; k < n_t; ++k) prefix[k] = state[(size_t)sg * sw + 2 + 2 * k];
+      if (pass > 0 && threadIdx.x < n_t) s_prefix[threadIdx.x] = state[(size_t)sg * sw + 2 + 2 * threadIdx.x];
       __syncthreads();
     }
     const double* xr = x + s * n_steps;
-    for (int64_t j = threadIdx.x; j < n_steps; j += blockDim.x) {
-      const double v = xr[j];
-      if (v != v) continue;
-      const uint64_t key = f64_key(v);
-      const unsigned d = (unsigned)(key >> shift) & mask;
-      if (pass == 0) atomicAdd(&sh[d], 1u);
-      else {
-        const uint64_t top = key >> pshift;
-        for (int k = 0; k < n_t; ++k)
-          if (top == prefix[k]) atomicAdd(&sh[k * BINS + d], 1u);
+    if ((reinterpret_cast<uintptr_t>(xr) & 15) == 0) {     // two elements per lane, 16-byte loads
+      const double2* x2 = reinterpret_cast<const double2*>(xr);
+      const int64_t n2 = n_steps >> 1;
+      for (int64_t j0 = 0; j0 < n2; j0 += blockDim.x) {
+        const int64_t j = j0 + threadIdx.x;
+        const bool in = j < n2;
+        double2 v = in ? x2[j] : make_double2(0.0, 0.0);
+        hist_add(sh, s_prefix, n_t, pass, shift, mask, pshift, in && v.x == v.x, f64_key(v.x), lane);
+        hist_add(sh, s_prefix, n_t, pass, shift, mask, pshift, in && v.y == v.y, f64_key(v.y), lane);
+      }
+      if (n_steps & 1) {
+        const double v = xr[n_steps - 1];
+        hist_add(sh, s_prefix, n_t, pass, shift, mask, pshift, threadIdx.x == 0 && v == v, f64_key(v), lane);
+      }
+    } else {
+      for (int64_t j0 = 0; j0 < n_steps; j0 += blockDim.x) {
+        const int64_t j = j0 + threadIdx.x;
+        const bool in = j < n_steps;
+        const double v = in ? xr[j] : 0.0;
+        hist_add(sh, s_prefix, n_t, pass, shift, mask, pshift, in && v == v, f64_key(v), lane);
       }
     }
   }
@@ -194,7 +226,7 @@ int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
   const size_t smem = (size_t)n_h * BINS * sizeof(unsigned int);
   PMX_CUDA(cudaFuncSetAttribute(hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(MAX_TARGETS * BINS * sizeof(unsigned int))));
   // a CTA sweeps consecutive rows so that a segment's private histogram is flushed rarely
-  int64_t want_ctas = (int64_t)ctx->sm_count * 8;
+  int64_t want_ctas = (int64_t)ctx->sm_count * 16;
   int64_t rows = (n_series + want_ctas - 1) / want_ctas;
   if (rows < 1) rows = 1;
   const int64_t grid = (n_series + rows - 1) / rows;

@@ -49,14 +49,20 @@ series_partial_kernel(const double* __restrict__ x, int64_t n_steps, Part* __res
   }
 }
 
-// one thread per group: fold the series partials in group order
-__global__ void group_fold_kernel(const Part* __restrict__ part, const int32_t* __restrict__ perm,
-                                  const int64_t* __restrict__ goff, int64_t n_groups,
-                                  double* o_sum, int64_t* o_cnt, double* o_min, double* o_max, double* o_mean) {
-  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+// one warp per group: lane l folds the partials of the group's series l, l+32, ... in order, then
+// a fixed shuffle tree combines the 32 lanes -- the order never depends on timing.
+__global__ void __launch_bounds__(128)
+group_fold_kernel(const Part* __restrict__ part, const int32_t* __restrict__ perm,
+                  const int64_t* __restrict__ goff, int64_t n_groups,
+                  double* o_sum, int64_t* o_cnt, double* o_min, double* o_max, double* o_mean) {
+  const int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
   if (g >= n_groups) return;
   Part r = part_identity();
-  for (int64_t k = goff[g]; k < goff[g + 1]; ++k) part_merge(r, part[perm[k]]);
+  for (int64_t k = goff[g] + lane; k < goff[g + 1]; k += 32) part_merge(r, part[perm[k]]);
+#pragma unroll
+  for (int d = 16; d >= 1; d >>= 1) { Part q = part_shfl_down(r, d); part_merge(r, q); }
+  if (lane != 0) return;
   const bool any = r.cnt > 0;
   if (o_sum) o_sum[g] = r.sum;
   if (o_cnt) o_cnt[g] = r.cnt;
@@ -136,7 +142,7 @@ int pmx_group_reduce(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t 
     series_partial_kernel<<<(unsigned)n_series, 256, 0, st>>>(d_x, n_steps, part);
     PMX_LAUNCH_CHECK();
   }
-  group_fold_kernel<<<(unsigned)((n_groups + 127) / 128), 128, 0, st>>>(part, d_perm, d_goff, n_groups, d_sum, d_count,
+  group_fold_kernel<<<(unsigned)((n_groups + 3) / 4), 128, 0, st>>>(part, d_perm, d_goff, n_groups, d_sum, d_count,
                                                                       d_min, d_max, d_mean);
   PMX_LAUNCH_CHECK();
   return PMX_OK;

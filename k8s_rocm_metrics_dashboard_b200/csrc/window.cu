@@ -20,23 +20,10 @@
 // HBM traffic per grid point in the fused call: 16 B in (ts,val), 40 B out.
 #include <math.h>
 #include <stdlib.h>
-#include "pmx_common.cuh"
+#include "window_common.cuh"
+using namespace pmxw;
 
 namespace {
-
-constexpr int E = 8;                     // grid points per thread
-
-struct WinParams {
-  const int64_t* ts; const double* val; const int64_t* off;   // ragged input (ALIGN)
-  const double* x;                                            // dense [S,T] input (!ALIGN)
-  int64_t n_series, n_steps;
-  int64_t start_ms, step_ms, lookback_ms;
-  int32_t w, min_periods;
-  int32_t chunks; int64_t chunk_len;
-  double* o_aligned; int32_t* o_idx;
-  double* o_min; double* o_max; double* o_mean; int32_t* o_cnt;
-  double* o_inc; double* o_rate; int32_t* o_nres;
-};
 
 template <int NT> struct Tile {
   static constexpr int NE = NT * E;                 // grid points per tile (halo + outputs)
@@ -460,24 +447,28 @@ int launch_window(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
   return PMX_OK;
 }
 
-int pmx_window_block_threads() {
-  static int nt = 0;
-  if (!nt) {
-    const char* e = getenv("PMX_WINDOW_THREADS");
-    nt = (e && atoi(e) == 128) ? 128 : 256;
-  }
-  return nt;
-}
-
 template <bool ALIGN>
 int dispatch_window(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
   if (p.n_series == 0 || p.n_steps == 0) return PMX_OK;
-  const int nt = pmx_window_block_threads();
+  const int rc = launch_window_fast<ALIGN>(ctx, p, st);      // the roofline kernel when it applies
+  if (rc != 1) return rc;
+  const int nt = window_block_threads();
   if (nt == 128) return launch_window<128, ALIGN>(ctx, p, st);
   return launch_window<256, ALIGN>(ctx, p, st);
 }
 
 }  // namespace
+
+namespace pmxw {
+int window_block_threads() {
+  static int nt = 0;
+  if (!nt) {
+    const char* e = getenv("PMX_WINDOW_THREADS");
+    nt = (e && atoi(e) == 256) ? 256 : 128;
+  }
+  return nt;
+}
+}  // namespace pmxw
 
 extern "C" {
 
@@ -497,7 +488,7 @@ int pmx_align(pmx_ctx* ctx, const int64_t* d_ts, const double* d_val, const int6
 
 static int window_dense(pmx_ctx* ctx, WinParams p, cudaStream_t st) {
   if (p.n_series == 0 || p.n_steps == 0) return PMX_OK;
-  const int nt = pmx_window_block_threads();
+  const int nt = window_block_threads();
   if (p.w - 1 > nt * E / 2) {                       // window longer than half a tile
     const int64_t total = p.n_series * p.n_steps;
     int64_t blocks = (total + 255) / 256;
@@ -552,7 +543,7 @@ int pmx_fused_align_rolling_rate(pmx_ctx* ctx, const int64_t* d_ts, const double
   PMX_REQUIRE(min_periods >= 0 && min_periods <= 0x7fffffff, "bad min_periods");
   if (n_series == 0 || n_steps == 0) return PMX_OK;
   PMX_REQUIRE(d_off, "NULL buffer");
-  const int nt = pmx_window_block_threads();
+  const int nt = window_block_threads();
   if (window_steps - 1 > nt * E / 2)
     return pmx_fail(PMX_E_LIMIT, "pmx_fused_align_rolling_rate: window_steps %lld exceeds the fused limit %d; "
                     "use pmx_align + pmx_rolling + pmx_rate", (long long)window_steps, nt * E / 2 + 1);

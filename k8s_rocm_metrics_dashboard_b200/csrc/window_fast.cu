@@ -1,0 +1,430 @@
+// window_fast.cu -- the roofline kernel: fused align + rolling min/max/mean + increase/rate.
+//
+// Same definitions and the same block decomposition as window.cu (suffix of the first chunk +
+// whole 8-point chunks + prefix of the own chunk; nothing is ever subtracted), re-cut so that a
+// grid point costs ~150 thread instructions instead of ~840:
+//   * results leave the SM straight from registers as 256-bit stores (STG.E.ENL2.256: one full
+//     32-byte sector per lane); the tile origin is shifted by 0..3 halo points so that every
+//     thread's 8 points start on a 32-byte boundary of every output row;
+//   * the rate is no longer a general ordered-monoid fold per output: each chunk publishes the
+//     sum of its pre-reset values including the junction with the previous valid point, so a
+//     window's reset sum is suffix + chunk totals + prefix (plain additions).  Only windows whose
+//     first chunk part is empty (NaN runs) take a short out-of-line loop over chunk totals;
+//   * divisions are replaced by two per-CTA tables in shared memory (1/n and 1000/(k*step));
+//   * the align stage starts from "one sample per step" as its guess and only binary-searches the
+//     staged timestamps when the guess is wrong; indices are 32-bit, shared memory is addressed
+//     directly (no generic pointers).
+// Requests it does not cover (window_steps < 9 or > NE/2, n_resets / source-index outputs,
+// output rows not 32-byte aligned) go to the general kernel in window.cu.
+//
+// Shared memory per CTA (NT threads, NE = 8 NT points): A[NE] aligned values, four suffix arrays
+// S_*[NE] (aliased with the sample staging area), chunk totals T_*[NT], the two tables.
+#include <math.h>
+#include "window_common.cuh"
+
+namespace pmxw {
+namespace {
+
+template <int NT> struct FTile {
+  static constexpr int NE = NT * E;
+  static constexpr int NS = NE + E;
+  static constexpr int NSP = NS + NS / 8 + 2;
+  static constexpr size_t A_BYTES = size_t(NE) * 8;
+  static constexpr size_t S_BYTES = size_t(4) * NE * 8;          // >= staging 2*NSP*8
+  static constexpr size_t SM_BYTES = size_t(NE) * 2;
+  static constexpr size_t T_BYTES = size_t(7) * NT * 8 + size_t(NT) * 4;
+  static constexpr size_t FIXED = A_BYTES + S_BYTES + SM_BYTES + T_BYTES + 16;
+  static_assert(size_t(2) * NSP * 8 <= S_BYTES, "staging must fit in the suffix arrays");
+};
+
+__device__ __forceinline__ int pad8(int i) { return i + (i >> 3); }
+__device__ __forceinline__ double dmin(double a, double b) { return b < a ? b : a; }
+__device__ __forceinline__ double dmax(double a, double b) { return b > a ? b : a; }
+
+__device__ __forceinline__ void st4(double* p, double a, double b, double c, double d) {
+  asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
+}
+// four consecutive outputs of one array; e is a multiple of 4; [e_lo, e_hi) is the output range
+__device__ __forceinline__ void store4(double* __restrict__ row, int e, int e_lo, int e_hi,
+                                       double a, double b, double c, double d) {
+  if (row == nullptr) return;
+  if (e >= e_lo && e + 3 < e_hi) { st4(row + e, a, b, c, d); return; }
+  if (e >= e_lo && e < e_hi) row[e] = a;
+  if (e + 1 >= e_lo && e + 1 < e_hi) row[e + 1] = b;
+  if (e + 2 >= e_lo && e + 2 < e_hi) row[e + 2] = c;
+  if (e + 3 >= e_lo && e + 3 < e_hi) row[e + 3] = d;
+}
+__device__ __forceinline__ void store4i(int32_t* __restrict__ row, int e, int e_lo, int e_hi,
+                                        int a, int b, int c, int d) {
+  if (row == nullptr) return;
+  if (e >= e_lo && e + 3 < e_hi) { *reinterpret_cast<int4*>(row + e) = make_int4(a, b, c, d); return; }
+  if (e >= e_lo && e < e_hi) row[e] = a;
+  if (e + 1 >= e_lo && e + 1 < e_hi) row[e + 1] = b;
+  if (e + 2 >= e_lo && e + 2 < e_hi) row[e + 2] = c;
+  if (e + 3 >= e_lo && e + 3 < e_hi) row[e + 3] = d;
+}
+
+// first index in [lo, n) of the padded staged timestamps with ts > g, minus one
+__device__ __forceinline__ int floor_staged(const int64_t* s_ts, int lo, int n, int64_t g) {
+  int hi = n;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (s_ts[pad8(mid)] <= g) lo = mid + 1; else hi = mid;
+  }
+  return lo - 1;
+}
+
+__device__ int64_t floor_global(const int64_t* __restrict__ ts, int64_t n, int64_t g) {
+  if (n == 0) return -1;
+  const int64_t t0 = ts[0];
+  if (g < t0) return -1;
+  const int64_t tl = ts[n - 1];
+  if (g >= tl) return n - 1;
+  int64_t guess = (int64_t)((double)(g - t0) * (double)(n - 1) / (double)(tl - t0));
+  if (guess < 0) guess = 0;
+  if (guess > n - 2) guess = n - 2;
+  if (ts[guess] <= g && g < ts[guess + 1]) return guess;
+  int64_t lo = 0, hi = n;
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (ts[mid] <= g) lo = mid + 1; else hi = mid;
+  }
+  return lo - 1;
+}
+
+// One grid point of a tile whose samples do not fit the staging area (many samples per grid
+// step): binary search of the series in global memory.  Cold.
+__device__ __noinline__ double align_one_global(const int64_t* __restrict__ ts, const double* __restrict__ val,
+                                                int64_t cur, int64_t len, int64_t g, int64_t lookback,
+                                                int64_t* idx_out) {
+  int64_t lo = cur, hi = len;
+  while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if (ts[mid] <= g) lo = mid + 1; else hi = mid; }
+  const int64_t idx = lo - 1;
+  *idx_out = idx;
+  if (idx < 0) return pmx_nan();
+  const double sample = val[idx];
+  if (g - ts[idx] < lookback && (unsigned long long)__double_as_longlong(sample) != PMX_STALE_NAN_BITS)
+    return sample;
+  return pmx_nan();
+}
+
+// Rate of a window whose first chunk part [l, end of chunk lchunk] holds no sample: walk the chunk
+// totals forward to the first non-empty chunk before the own chunk t.  Cold (needs a NaN run).
+// Returns 1 and (fpos, fv, rs) when such a chunk exists, else 0 (window lies in the own chunk).
+__device__ __noinline__ int rate_skip_empty(const double* T_fv, const double* T_ri, const double* T_tr,
+                                            const uint32_t* T_meta, int lchunk, int t, int* fpos,
+                                            double* fv, double* rs) {
+  for (int k = lchunk + 1; k < t; ++k) {
+    const uint32_t m = T_meta[k];
+    if ((m >> 4) & 0xf) {
+      double acc = T_ri[k];
+      for (int k2 = k + 1; k2 < t; ++k2) acc += T_tr[k2];
+      *fpos = k * E + (int)((m >> 8) & 7);
+      *fv = T_fv[k];
+      *rs = acc;
+      return 1;
+    }
+  }
+  return 0;
+}
+
+template <int NT, bool ALIGN>
+__global__ void __launch_bounds__(NT, (NT == 256 ? 2 : 4))
+window_fast_kernel(const WinParams p) {
+  using TL = FTile<NT>;
+  constexpr int NE = TL::NE;
+  extern __shared__ __align__(16) unsigned char smem[];
+  double* A = reinterpret_cast<double*>(smem);
+  double* S_sum = A + NE;
+  double* S_mn = S_sum + NE;
+  double* S_mx = S_mn + NE;
+  double* S_rs = S_mx + NE;
+  int64_t* s_ts = reinterpret_cast<int64_t*>(S_sum);              // staging aliases the suffix arrays
+  double* s_val = S_sum + TL::NSP;
+  uint16_t* S_meta = reinterpret_cast<uint16_t*>(S_rs + NE);
+  double* T_sum = reinterpret_cast<double*>(S_meta + NE);
+  double* T_mn = T_sum + NT;
+  double* T_mx = T_mn + NT;
+  double* T_fv = T_mx + NT;
+  double* T_lv = T_fv + NT;
+  double* T_ri = T_lv + NT;
+  double* T_tr = T_ri + NT;
+  uint32_t* T_meta = reinterpret_cast<uint32_t*>(T_tr + NT);
+  int64_t* s_cursor = reinterpret_cast<int64_t*>(T_meta + NT);
+  double* rcp = reinterpret_cast<double*>(s_cursor + 2);           // rcp[n] = 1/n, n <= w
+  double* rdt = rcp + (p.w + 1);                                   // rdt[k] = 1000/(k*step_ms), k < w
+
+  const int t = threadIdx.x;
+  const int64_t s = blockIdx.x / p.chunks;
+  const int ci = blockIdx.x % p.chunks;
+  const int64_t c0 = (int64_t)ci * p.chunk_len;
+  const int64_t c1 = (c0 + p.chunk_len < p.n_steps) ? c0 + p.chunk_len : p.n_steps;
+  if (c0 >= c1) return;
+  const int H = p.w - 1;
+  const int qa = H >> 3, qb = H & 7;
+  // shift the tile origin back so that tile element 0 sits on a 32-byte boundary of the row
+  const int HP = H + (int)(((s * p.n_steps + c0 - H) % 4 + 4) % 4);
+  const int OUT = (NE - H - 3) & ~3;
+  const bool do_roll = p.o_min || p.o_max || p.o_mean || p.o_cnt;
+  const bool do_rate = p.o_inc || p.o_rate;
+  const double INF = __longlong_as_double(0x7FF0000000000000LL);
+  const int need = p.min_periods > 1 ? p.min_periods : 1;
+
+  for (int k = t; k <= p.w; k += NT) {
+    rcp[k] = k ? 1.0 / (double)k : 0.0;
+    rdt[k] = k ? 1000.0 / (double)((int64_t)k * p.step_ms) : 0.0;
+  }
+
+  int64_t base = 0, len = 0, cur = 0;
+  if (ALIGN) { base = p.off[s]; len = p.off[s + 1] - base; }
+  bool first = true;
+  const int e0 = t * E;
+
+  for (int64_t jt = c0; jt < c1; jt += OUT) {
+    const int64_t j0 = jt - HP;                                   // grid index of tile element 0
+    const int n_out = (int)((c1 - jt < OUT) ? (c1 - jt) : OUT);
+    const int n_el = HP + n_out;
+    const int64_t row = s * p.n_steps + j0;                       // multiple of 4
+    double a[E];
+
+    if (ALIGN) {
+      const int elo = j0 < 0 ? (int)(-j0) : 0;                    // first element with a grid point
+      const int64_t glo = p.start_ms + (j0 + elo) * p.step_ms;
+      if (first) {
+        cur = floor_global(p.ts + base, len, glo);
+        if (cur < 0) cur = 0;
+        first = false;
+      }
+      const int64_t rem = len - cur;
+      const int ns = (int)(rem < TL::NS ? rem : TL::NS);
+      {
+        const int64_t* gts = p.ts + base + cur;
+        const double* gv = p.val + base + cur;
+        for (int i = t; i < ns; i += NT) { s_ts[pad8(i)] = gts[i]; s_val[pad8(i)] = gv[i]; }
+      }
+      __syncthreads();
+      const int64_t ghi = p.start_ms + (j0 + n_el - 1) * p.step_ms;
+      const bool covered = (cur + ns >= len) || (ns > 0 && s_ts[pad8(ns - 1)] > ghi);
+      const int e_cur = OUT;                                      // its floor seeds the next tile
+      if (!covered) {
+#pragma unroll 1
+        for (int r = 0; r < E; ++r) {
+          const int e = e0 + r;
+          double v = pmx_nan();
+          if (e >= elo && e < n_el) {
+            int64_t idx;
+            v = align_one_global(p.ts + base, p.val + base, cur, len, p.start_ms + (j0 + e) * p.step_ms,
+                                 p.lookback_ms, &idx);
+            if (e == e_cur) *s_cursor = idx > cur ? idx : cur;
+          }
+          a[r] = v;
+        }
+      } else {
+        // guess: one sample per grid step, staged sample 0 is the floor of element elo (or the
+        // sample after it when the series starts later)
+        const int shift = (ns > 0 && s_ts[0] > glo) ? 1 : 0;
+        int idx = -2;
+        int64_t g = p.start_ms + (j0 + e0) * p.step_ms;
+#pragma unroll
+        for (int r = 0; r < E; ++r, g += p.step_ms) {
+          const int e = e0 + r;
+          double v = pmx_nan();
+          if (e >= elo && e < n_el) {
+            if (idx == -2) {
+              int gi = e - elo - shift;
+              if (gi > ns - 1) gi = ns - 1;
+              if (gi < 0) idx = (ns > 0 && s_ts[0] <= g) ? floor_staged(s_ts, 0, ns, g) : -1;
+              else if (s_ts[pad8(gi)] <= g && (gi + 1 >= ns || s_ts[pad8(gi + 1)] > g)) idx = gi;
+              else idx = floor_staged(s_ts, 0, ns, g);
+            } else if (idx + 1 < ns && s_ts[pad8(idx + 1)] <= g) {
+              ++idx;
+              if (idx + 1 < ns && s_ts[pad8(idx + 1)] <= g) idx = floor_staged(s_ts, idx + 1, ns, g);
+            }
+            if (idx >= 0) {
+              const double sample = s_val[pad8(idx)];
+              if (g - s_ts[pad8(idx)] < p.lookback_ms &&
+                  (unsigned long long)__double_as_longlong(sample) != PMX_STALE_NAN_BITS)
+                v = sample;
+            }
+            if (e == e_cur) *s_cursor = cur + (idx > 0 ? idx : 0);
+          }
+          a[r] = v;
+        }
+      }
+      __syncthreads();                                            // staging dead, cursor visible
+      cur = *s_cursor;
+    } else {
+      const double* xr = p.x + s * p.n_steps;
+      for (int i = t; i < n_el; i += NT) {
+        const int64_t j = j0 + i;
+        s_val[pad8(i)] = j >= 0 ? xr[j] : pmx_nan();
+      }
+      __syncthreads();
+#pragma unroll
+      for (int r = 0; r < E; ++r) a[r] = (e0 + r < n_el) ? s_val[pad8(e0 + r)] : pmx_nan();
+      __syncthreads();
+    }
+
+    if (p.o_aligned) {
+      store4(p.o_aligned + row, e0, HP, n_el, a[0], a[1], a[2], a[3]);
+      store4(p.o_aligned + row, e0 + 4, HP, n_el, a[4], a[5], a[6], a[7]);
+    }
+    if (!do_roll && !do_rate) continue;
+
+    // ---------------------------------------------------------------- in-chunk suffix scans
+    double c_fv, c_ri;                                            // chunk's first valid value, internal reset sum
+    int c_cn;
+    {
+      double ss = 0.0, smn = INF, smx = -INF, srs = 0.0, sfv = 0.0, lv = 0.0;
+      int scf = 0, scn = 0, foff = 0, lpos = 0;
+#pragma unroll
+      for (int r = E - 1; r >= 0; --r) {
+        const double v = a[r];
+        const bool nn = v == v;
+        if (pmx_isfinite(v)) { ss += v; smn = dmin(smn, v); smx = dmax(smx, v); ++scf; }
+        if (nn) {
+          if (scn > 0) srs += (sfv < v) ? v : 0.0; else { lv = v; lpos = r; }
+          sfv = v; foff = r; ++scn;
+        }
+        const int si = r * NT + t;
+        A[si] = v; S_sum[si] = ss; S_mn[si] = smn; S_mx[si] = smx; S_rs[si] = srs;
+        S_meta[si] = (uint16_t)(scf | (scn << 4) | (((foff - r) & 7) << 8));
+      }
+      T_sum[t] = ss; T_mn[t] = smn; T_mx[t] = smx; T_fv[t] = sfv; T_lv[t] = lv; T_ri[t] = srs;
+      T_meta[t] = (uint32_t)(scf | (scn << 4) | (foff << 8) | (lpos << 12));
+      c_fv = sfv; c_ri = srs; c_cn = scn;
+    }
+    __syncthreads();
+    // ---------------------------------------------------------------- junction with the previous valid point
+    double clv = 0.0; int clpos = -1;
+    {
+      const int kmin = t - qa - 2 > 0 ? t - qa - 2 : 0;
+      for (int k = t - 1; k >= kmin; --k) {
+        const uint32_t m = T_meta[k];
+        if ((m >> 4) & 0xf) { clv = T_lv[k]; clpos = k * E + (int)((m >> 12) & 7); break; }
+      }
+    }
+    const double Jc = (c_cn > 0 && clpos >= 0 && c_fv < clv) ? clv : 0.0;
+    T_tr[t] = c_ri + Jc;
+    __syncthreads();
+
+    // ---------------------------------------------------------------- windows
+    if (e0 + E > HP) {
+      double ms = 0.0, mmn = INF, mmx = -INF, mrs = 0.0; int mcf = 0, mcn = 0;
+      for (int k = (t - qa + 1 > 0 ? t - qa + 1 : 0); k < t; ++k) {
+        ms += T_sum[k]; mmn = dmin(mmn, T_mn[k]); mmx = dmax(mmx, T_mx[k]); mrs += T_tr[k];
+        const uint32_t m = T_meta[k]; mcf += m & 0xf; mcn += (m >> 4) & 0xf;
+      }
+      double ms2 = ms, mmn2 = mmn, mmx2 = mmx, mrs2 = mrs; int mcf2 = mcf, mcn2 = mcn;
+      if (t - qa >= 0) {
+        const int k = t - qa;
+        ms2 = T_sum[k] + ms; mmn2 = dmin(mmn, T_mn[k]); mmx2 = dmax(mmx, T_mx[k]); mrs2 = T_tr[k] + mrs;
+        const uint32_t m = T_meta[k]; mcf2 += m & 0xf; mcn2 += (m >> 4) & 0xf;
+      }
+      double ps = 0.0, pmn = INF, pmx = -INF, prs = 0.0, plv = 0.0, pfv = 0.0;
+      int pcf = 0, pcn = 0, plpos = 0, pfpos = 0;
+      double omn[4], omx[4], omean[4], oinc[4], orate[4]; int ocnt[4];
+#pragma unroll
+      for (int r = 0; r < E; ++r) {
+        const double v = a[r];
+        if (pmx_isfinite(v)) { ps += v; pmn = dmin(pmn, v); pmx = dmax(pmx, v); ++pcf; }
+        if (v == v) {
+          if (pcn > 0) prs += (v < plv) ? plv : 0.0; else { pfv = v; pfpos = e0 + r; }
+          plv = v; plpos = e0 + r; ++pcn;
+        }
+        const bool far = r < qb;                                  // window starts one chunk further back
+        int lchunk = far ? t - qa - 1 : t - qa;
+        const int lrow = far ? r - qb + E : r - qb;
+        if (lchunk < 0) lchunk = 0;                               // halo points only; result unused
+        const int si = lrow * NT + lchunk;
+        const uint32_t sm = S_meta[si];
+        const int k4 = r & 3;
+        if (do_roll) {
+          const double ws = S_sum[si] + (far ? ms2 : ms) + ps;
+          const double wmn = dmin(dmin(S_mn[si], far ? mmn2 : mmn), pmn);
+          const double wmx = dmax(dmax(S_mx[si], far ? mmx2 : mmx), pmx);
+          const int wcf = (int)(sm & 0xf) + (far ? mcf2 : mcf) + pcf;
+          const bool ok = wcf >= need;
+          omean[k4] = ok ? ws * rcp[wcf] : pmx_nan();
+          omn[k4] = ok ? wmn : pmx_nan();
+          omx[k4] = ok ? wmx : pmx_nan();
+          ocnt[k4] = (int)((sm >> 4) & 0xf) + (far ? mcn2 : mcn) + pcn;
+        }
+        if (do_rate) {
+          int fpos, lpos; double fv, lv, rs;
+          bool have = true;
+          if ((sm >> 4) & 0xf) {                                  // first chunk part holds a sample
+            fpos = lchunk * E + lrow + (int)((sm >> 8) & 7);
+            fv = A[(fpos & 7) * NT + (fpos >> 3)];
+            rs = S_rs[si] + (far ? mrs2 : mrs) + prs + (pcn > 0 ? Jc : 0.0);
+          } else if (rate_skip_empty(T_fv, T_ri, T_tr, T_meta, lchunk, t, &fpos, &fv, &rs)) {
+            rs += prs + (pcn > 0 ? Jc : 0.0);
+          } else {                                                // window lies inside the own chunk
+            have = pcn > 0; fpos = pfpos; fv = pfv; rs = prs;
+          }
+          if (pcn > 0) { lv = plv; lpos = plpos; } else { lv = clv; lpos = clpos; }
+          double inc = pmx_nan(), rate = pmx_nan();
+          if (have && lpos > fpos) { inc = (lv - fv) + rs; rate = inc * rdt[lpos - fpos]; }
+          oinc[k4] = inc; orate[k4] = rate;
+        }
+        if (k4 == 3) {
+          const int e = e0 + r - 3;
+          if (do_roll) {
+            store4(p.o_min ? p.o_min + row : nullptr, e, HP, n_el, omn[0], omn[1], omn[2], omn[3]);
+            store4(p.o_max ? p.o_max + row : nullptr, e, HP, n_el, omx[0], omx[1], omx[2], omx[3]);
+            store4(p.o_mean ? p.o_mean + row : nullptr, e, HP, n_el, omean[0], omean[1], omean[2], omean[3]);
+            store4i(p.o_cnt ? p.o_cnt + row : nullptr, e, HP, n_el, ocnt[0], ocnt[1], ocnt[2], ocnt[3]);
+          }
+          if (do_rate) {
+            store4(p.o_inc ? p.o_inc + row : nullptr, e, HP, n_el, oinc[0], oinc[1], oinc[2], oinc[3]);
+            store4(p.o_rate ? p.o_rate + row : nullptr, e, HP, n_el, orate[0], orate[1], orate[2], orate[3]);
+          }
+        }
+      }
+    }
+    __syncthreads();                                              // S/T/A free for the next tile
+  }
+}
+
+bool aligned32(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 31) == 0; }
+
+template <int NT, bool ALIGN>
+int launch_fast(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
+  using TL = FTile<NT>;
+  const int out_per_tile = (TL::NE - (p.w - 1) - 3) & ~3;
+  const int64_t tiles = (p.n_steps + out_per_tile - 1) / out_per_tile;
+  const int64_t target = (int64_t)ctx->sm_count * 16;
+  int64_t chunks = (target + p.n_series - 1) / p.n_series;
+  if (chunks > tiles) chunks = tiles;
+  if (chunks < 1) chunks = 1;
+  const int64_t tiles_per_chunk = (tiles + chunks - 1) / chunks;
+  p.chunk_len = tiles_per_chunk * out_per_tile;
+  p.chunks = (int32_t)((p.n_steps + p.chunk_len - 1) / p.chunk_len);
+  const int64_t grid = p.n_series * p.chunks;
+  if (grid > 0x7fffffffLL) return pmx_fail(PMX_E_LIMIT, "window kernel: n_series * chunks exceeds 2^31-1");
+  const size_t smem = TL::FIXED + size_t(2) * (p.w + 1) * 8 + 16;
+  PMX_CUDA(cudaFuncSetAttribute(window_fast_kernel<NT, ALIGN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  window_fast_kernel<NT, ALIGN><<<(unsigned)grid, NT, smem, st>>>(p);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
+}  // namespace
+
+template <bool ALIGN>
+int launch_window_fast(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
+  const int nt = window_block_threads();
+  const int H = p.w - 1;
+  if (H < 8 || H > nt * E / 2 - 4) return 1;
+  if (p.o_nres || p.o_idx) return 1;
+  if (!aligned32(p.o_aligned) || !aligned32(p.o_min) || !aligned32(p.o_max) || !aligned32(p.o_mean) ||
+      !aligned32(p.o_inc) || !aligned32(p.o_rate) || (reinterpret_cast<uintptr_t>(p.o_cnt) & 15))
+    return 1;
+  if (nt == 128) return launch_fast<128, ALIGN>(ctx, p, st);
+  return launch_fast<256, ALIGN>(ctx, p, st);
+}
+
+template int launch_window_fast<true>(const pmx_ctx*, WinParams, cudaStream_t);
+template int launch_window_fast<false>(const pmx_ctx*, WinParams, cudaStream_t);
+
+}  // namespace pmxw

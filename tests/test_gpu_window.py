@@ -171,3 +171,71 @@ def test_ragged_rolling_and_rate(eng):
     assert np.array_equal(_np(nr), onr)
     assert_close(_np(inc), oinc, scale=np.full(len(oinc), 1000.0), rtol=1e-12)
     assert_close(_np(rt), ort, scale=np.full(len(ort), 1000.0 / 13.0), rtol=1e-12)
+
+
+def _check_fused(eng, d, start, step, n_steps, w, lookback=300_000):
+    out = eng.fused(d["ts"], d["val"], d["off"], start, step, n_steps, w, lookback)
+    ref = O.aggregate_range(d["ts"], d["val"], d["off"], start, step, n_steps, w * step, lookback)
+    assert_bits_equal(_np(out["aligned"]), ref["aligned"], "aligned")
+    assert_exact_or_nan(_np(out["roll_min"]), ref["roll_min"], "roll_min")
+    assert_exact_or_nan(_np(out["roll_max"]), ref["roll_max"], "roll_max")
+    assert_close(_np(out["roll_mean"]), ref["roll_mean"], scale=O.rolling_scale(ref["aligned"], w), what="roll_mean")
+    assert_close(_np(out["rate"]), ref["rate"], scale=O.rate_scale(ref["aligned"], w) / (step / 1000.0), what="rate")
+
+
+@pytest.mark.parametrize("w", [9, 16, 60, 61, 63, 64, 250])
+def test_fused_gaps_nan_runs_and_stale_markers(eng, w):
+    """Ragged series with 6-30 min scrape gaps (> lookback): long NaN runs in the aligned grid,
+    windows whose first chunk part is empty, stale markers, series that start late / end early."""
+    d = synth.ragged(120, seed=w, mean_len=500, nan_frac=0.03, stale_frac=0.02, gap_frac=0.04)
+    t0 = int(d["ts"].min())
+    _check_fused(eng, d, t0 - 45_000, 15_000, 2600 + w, w)
+
+
+def test_fused_many_samples_per_step_uses_global_search(eng):
+    d = synth.ragged(40, seed=2, mean_len=3000, nan_frac=0.01, stale_frac=0.0, gap_frac=0.0)
+    t0 = int(d["ts"].min())
+    _check_fused(eng, d, t0, 200_000, 1500, 12)            # ~13 samples per grid step
+    _check_fused(eng, d, t0, 1_000, 5000, 30, lookback=20_000)   # 15 grid steps per sample
+
+
+@pytest.mark.parametrize("T", [1021, 1022, 1023, 4097])
+def test_fused_row_alignment_variants(eng, T):
+    """n_steps not a multiple of 4: every row starts at a different 32-byte phase."""
+    d = synth.dense(1, 3, 3, T, seed=T, nan_frac=0.02, kinds="ttk")
+    _check_fused(eng, d, d["start_ms"], d["step_ms"], T, 60)
+
+
+def test_rate_long_nan_runs(eng):
+    rng = np.random.default_rng(8)
+    x = np.cumsum(rng.uniform(0, 100, (6, 3000)), axis=1)
+    for s in range(6):
+        pos = 0
+        while pos < 3000:
+            run = int(rng.integers(1, 40))
+            if rng.random() < 0.5:
+                x[s, pos:pos + run] = np.nan
+            elif rng.random() < 0.2:
+                x[s, pos:pos + run] -= x[s, pos] * 0.999       # a reset
+            pos += run
+    for w in (9, 12, 60, 200):
+        _check_rate(eng, x, w)
+        _check_roll(eng, x, w)
+
+
+def test_general_kernel_path_for_unaligned_outputs(eng):
+    """Output rows that are not 32-byte aligned fall back to the general kernel; same results."""
+    t = eng.torch
+    import ctypes as C
+    from k8s_rocm_metrics_dashboard_b200 import _abi
+    rng = np.random.default_rng(3)
+    x = rng.normal(size=(3, 1000)); x[rng.random(x.shape) < 0.05] = np.nan
+    dx = t.as_tensor(x, device=eng.device)
+    buf = t.empty(3 * 1000 + 1, dtype=t.float64, device=eng.device)
+    mean_unaligned = buf[1:]                                    # 8-byte aligned only
+    _abi.check(eng.lib.pmx_rolling(eng.ctx, C.c_void_p(dx.data_ptr()), 3, 1000, 60, 1, None, None,
+                                   C.c_void_p(mean_unaligned.data_ptr()), None,
+                                   C.c_void_p(t.cuda.current_stream().cuda_stream)))
+    _, _, mean, _ = eng.rolling(x, 60)
+    assert t.equal(mean.view(t.int64).ravel(), mean_unaligned.contiguous().view(t.int64)) or \
+        np.allclose(_np(mean).ravel(), _np(mean_unaligned), rtol=1e-14, equal_nan=True)
