@@ -32,91 +32,104 @@ __host__ __device__ __forceinline__ int digit_shift(int pass) { return pass < 5 
 __host__ __device__ __forceinline__ int digit_bits(int pass) { return pass < 5 ? 11 : 9; }
 __host__ __device__ __forceinline__ int state_words(int64_t n_q) { return 2 + 4 * (int)n_q; }
 
-// Adds one key to the CTA-private histograms.  All 32 lanes call this together (valid = lane has
-// a non-NaN element); lanes that hit the same bin are combined with match_any so that heavy ties
-// (pass 0 of gauge data lands in one or two bins) cost one shared atomic per warp, not 32.
-__device__ __forceinline__ void hist_add(unsigned int* sh, const uint64_t* s_prefix, int n_t, int pass,
-                                         int shift, unsigned mask, int pshift, bool valid, uint64_t key,
-                                         int lane) {
-  const unsigned d = (unsigned)(key >> shift) & mask;
-  if (pass == 0) {
-    const unsigned peers = __match_any_sync(0xffffffffu, valid ? d : 0xffffffffu);
-    if (valid && lane == __ffs(peers) - 1) atomicAdd(&sh[d], (unsigned)__popc(peers));
-    return;
+// Adds one key per lane to a CTA-private histogram.  All 32 lanes call this together (hit = this
+// lane contributes).  Lanes that fall into the same bin as the current leader are folded into one
+// shared atomic (two rounds: gauge data puts a whole warp into one or two bins in the first
+// pass); what is left after that is spread over many bins and goes in lane by lane.
+__device__ __forceinline__ void hist_add(unsigned int* h, bool hit, unsigned d, int lane) {
+  unsigned todo = __ballot_sync(0xffffffffu, hit);
+#pragma unroll
+  for (int round = 0; round < 2; ++round) {
+    if (todo == 0) return;
+    const int leader = __ffs(todo) - 1;
+    const unsigned dl = __shfl_sync(0xffffffffu, d, leader);
+    const unsigned peers = __ballot_sync(0xffffffffu, hit && d == dl) & todo;
+    if (lane == leader) atomicAdd(&h[dl], (unsigned)__popc(peers));
+    todo &= ~peers;
   }
-  const uint64_t top = key >> pshift;
-#pragma unroll 1
-  for (int k = 0; k < n_t; ++k) {
-    const bool hit = valid && top == s_prefix[k];
-    if (__ballot_sync(0xffffffffu, hit) == 0) continue;            // common case: nobody matches
-    const unsigned peers = __match_any_sync(0xffffffffu, hit ? d : 0xffffffffu);
-    if (hit && lane == __ffs(peers) - 1) atomicAdd(&sh[k * BINS + d], (unsigned)__popc(peers));
-  }
+  if ((todo >> lane) & 1) atomicAdd(&h[d], 1u);
 }
 
 __global__ void __launch_bounds__(256)
 hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __restrict__ seg,
             int n_t, int pass, const uint64_t* __restrict__ state, int sw,
             unsigned long long* __restrict__ hist, int rows_per_cta, int64_t n_series) {
-  extern __shared__ unsigned int sh[];                     // [n_h][BINS]
-  __shared__ uint64_t s_prefix[MAX_TARGETS];
-  const int n_h = pass == 0 ? 1 : n_t;
+  extern __shared__ unsigned int sh[];                     // [n_uniq][BINS]
+  __shared__ uint64_t s_uprefix[MAX_TARGETS];              // distinct prefixes of this segment's targets
+  __shared__ int s_umap[MAX_TARGETS];                      // target -> index of its distinct prefix
+  __shared__ int s_nu;
   const int64_t s0 = (int64_t)blockIdx.x * rows_per_cta;
   const int shift = digit_shift(pass);
   const unsigned mask = (1u << digit_bits(pass)) - 1u;
   const int pshift = pass == 0 ? 0 : 64 - 11 * pass;       // key >> pshift == prefix  (pass >= 1)
   const int lane = threadIdx.x & 31;
+  const int n_h = pass == 0 ? 1 : n_t;                     // histograms per segment in global memory
   int cur_seg = -1;
+
+  auto flush = [&](int sg) {
+    __syncthreads();
+    for (int k = 0; k < n_h; ++k) {
+      const unsigned int* src = sh + (pass == 0 ? 0 : s_umap[k]) * BINS;
+      unsigned long long* dst = hist + ((size_t)sg * n_h + k) * BINS;
+      for (int i = threadIdx.x; i < BINS; i += blockDim.x) {
+        const unsigned c = src[i];
+        if (c) atomicAdd(&dst[i], (unsigned long long)c);
+      }
+    }
+  };
+
   for (int r = 0; r < rows_per_cta; ++r) {
     const int64_t s = s0 + r;
     if (s >= n_series) break;
     const int sg = seg[s];
     if (sg < 0) continue;
     if (sg != cur_seg) {                                   // flush, switch segment
-      if (cur_seg >= 0) {
-        __syncthreads();
-        for (int i = threadIdx.x; i < n_h * BINS; i += blockDim.x) {
-          const unsigned c = sh[i];
-          if (c) atomicAdd(&hist[((size_t)cur_seg * n_h) * BINS + i], (unsigned long long)c);
+      if (cur_seg >= 0) flush(cur_seg);
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        int nu = 0;
+        if (pass == 0) nu = 1;
+        else for (int k = 0; k < n_t; ++k) {
+          const uint64_t pf = state[(size_t)sg * sw + 2 + 2 * k];
+          int u = 0;
+          while (u < nu && s_uprefix[u] != pf) ++u;
+          if (u == nu) s_uprefix[nu++] = pf;
+          s_umap[k] = u;
+        }
+        s_nu = nu;
+      }
+      __syncthreads();
+      for (int i = threadIdx.x; i < s_nu * BINS; i += blockDim.x) sh[i] = 0;
+      cur_seg = sg;
+      __syncthreads();
+    }
+    const int nu = s_nu;
+    const double* xr = x + s * n_steps;
+    const bool vec = (reinterpret_cast<uintptr_t>(xr) & 15) == 0;
+    const int64_t n_it = vec ? ((n_steps + 1) >> 1) : n_steps;       // loop trips are warp-uniform
+    for (int64_t j0 = 0; j0 < n_it; j0 += blockDim.x) {
+      const int64_t j = j0 + threadIdx.x;
+      double v0 = __longlong_as_double(0x7FF8000000000000LL), v1 = v0;
+      if (vec) {
+        if (2 * j + 1 < n_steps) { const double2 v = reinterpret_cast<const double2*>(xr)[j]; v0 = v.x; v1 = v.y; }
+        else if (2 * j < n_steps) v0 = xr[2 * j];
+      } else if (j < n_steps) v0 = xr[j];
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        if (half == 1 && !vec) break;
+        const double v = half ? v1 : v0;
+        const bool valid = v == v;
+        const uint64_t key = f64_key(v);
+        const unsigned d = (unsigned)(key >> shift) & mask;
+        if (pass == 0) hist_add(sh, valid, d, lane);
+        else {
+          const uint64_t top = key >> pshift;
+          for (int u = 0; u < nu; ++u) hist_add(sh + u * BINS, valid && top == s_uprefix[u], d, lane);
         }
       }
-      __syncthreads();
-      for (int i = threadIdx.x; i < n_h * BINS; i += blockDim.x) sh[i] = 0;
-      cur_seg = sg;
-      if (pass > 0 && threadIdx.x < n_t) s_prefix[threadIdx.x] = state[(size_t)sg * sw + 2 + 2 * threadIdx.x];
-      __syncthreads();
-    }
-    const double* xr = x + s * n_steps;
-    if ((reinterpret_cast<uintptr_t>(xr) & 15) == 0) {     // two elements per lane, 16-byte loads
-      const double2* x2 = reinterpret_cast<const double2*>(xr);
-      const int64_t n2 = n_steps >> 1;
-      for (int64_t j0 = 0; j0 < n2; j0 += blockDim.x) {
-        const int64_t j = j0 + threadIdx.x;
-        const bool in = j < n2;
-        double2 v = in ? x2[j] : make_double2(0.0, 0.0);
-        hist_add(sh, s_prefix, n_t, pass, shift, mask, pshift, in && v.x == v.x, f64_key(v.x), lane);
-        hist_add(sh, s_prefix, n_t, pass, shift, mask, pshift, in && v.y == v.y, f64_key(v.y), lane);
-      }
-      if (n_steps & 1) {
-        const double v = xr[n_steps - 1];
-        hist_add(sh, s_prefix, n_t, pass, shift, mask, pshift, threadIdx.x == 0 && v == v, f64_key(v), lane);
-      }
-    } else {
-      for (int64_t j0 = 0; j0 < n_steps; j0 += blockDim.x) {
-        const int64_t j = j0 + threadIdx.x;
-        const bool in = j < n_steps;
-        const double v = in ? xr[j] : 0.0;
-        hist_add(sh, s_prefix, n_t, pass, shift, mask, pshift, in && v == v, f64_key(v), lane);
-      }
     }
   }
-  if (cur_seg >= 0) {
-    __syncthreads();
-    for (int i = threadIdx.x; i < n_h * BINS; i += blockDim.x) {
-      const unsigned c = sh[i];
-      if (c) atomicAdd(&hist[((size_t)cur_seg * n_h) * BINS + i], (unsigned long long)c);
-    }
-  }
+  if (cur_seg >= 0) flush(cur_seg);
 }
 
 // grid (n_t, n_seg); one CTA scans one histogram

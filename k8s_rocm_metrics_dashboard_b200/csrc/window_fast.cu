@@ -44,15 +44,20 @@ __device__ __forceinline__ double dmax(double a, double b) { return b > a ? b : 
 __device__ __forceinline__ void st4(double* p, double a, double b, double c, double d) {
   asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
 }
-// four consecutive outputs of one array; e is a multiple of 4; [e_lo, e_hi) is the output range
-__device__ __forceinline__ void store4(double* __restrict__ row, int e, int e_lo, int e_hi,
-                                       double a, double b, double c, double d) {
-  if (row == nullptr) return;
-  if (e >= e_lo && e + 3 < e_hi) { st4(row + e, a, b, c, d); return; }
+// tile edges: the group of four straddles the output range [e_lo, e_hi).  Cold.
+__device__ __noinline__ void store4_edge(double* __restrict__ row, int e, int e_lo, int e_hi,
+                                         double a, double b, double c, double d) {
   if (e >= e_lo && e < e_hi) row[e] = a;
   if (e + 1 >= e_lo && e + 1 < e_hi) row[e + 1] = b;
   if (e + 2 >= e_lo && e + 2 < e_hi) row[e + 2] = c;
   if (e + 3 >= e_lo && e + 3 < e_hi) row[e + 3] = d;
+}
+// four consecutive outputs of one array; e is a multiple of 4; [e_lo, e_hi) is the output range
+__device__ __forceinline__ void store4(double* __restrict__ row, int e, int e_lo, int e_hi,
+                                       double a, double b, double c, double d) {
+  if (row == nullptr) return;
+  if (e >= e_lo && e + 3 < e_hi) st4(row + e, a, b, c, d);
+  else if (e + 3 >= e_lo && e < e_hi) store4_edge(row, e, e_lo, e_hi, a, b, c, d);
 }
 __device__ __forceinline__ void store4i(int32_t* __restrict__ row, int e, int e_lo, int e_hi,
                                         int a, int b, int c, int d) {
@@ -64,12 +69,13 @@ __device__ __forceinline__ void store4i(int32_t* __restrict__ row, int e, int e_
   if (e + 3 >= e_lo && e + 3 < e_hi) row[e + 3] = d;
 }
 
-// first index in [lo, n) of the padded staged timestamps with ts > g, minus one
-__device__ __forceinline__ int floor_staged(const int64_t* s_ts, int lo, int n, int64_t g) {
+// largest index in [lo, n) of the padded staged (tile-relative, 32-bit) timestamps with ts <= g,
+// or lo-1.  Only runs when the one-sample-per-step guess is wrong.
+__device__ __noinline__ int floor_staged(const int* s_t, int lo, int n, int g) {
   int hi = n;
   while (lo < hi) {
     const int mid = (lo + hi) >> 1;
-    if (s_ts[pad8(mid)] <= g) lo = mid + 1; else hi = mid;
+    if (s_t[pad8(mid)] <= g) lo = mid + 1; else hi = mid;
   }
   return lo - 1;
 }
@@ -110,22 +116,20 @@ __device__ __noinline__ double align_one_global(const int64_t* __restrict__ ts, 
 
 // Rate of a window whose first chunk part [l, end of chunk lchunk] holds no sample: walk the chunk
 // totals forward to the first non-empty chunk before the own chunk t.  Cold (needs a NaN run).
-// Returns 1 and (fpos, fv, rs) when such a chunk exists, else 0 (window lies in the own chunk).
+// Returns fpos (>= 0) with (fv, rs) when such a chunk exists, else -1 (window lies in the own chunk).
 __device__ __noinline__ int rate_skip_empty(const double* T_fv, const double* T_ri, const double* T_tr,
-                                            const uint32_t* T_meta, int lchunk, int t, int* fpos,
-                                            double* fv, double* rs) {
+                                            const uint32_t* T_meta, int lchunk, int t, double* fv_rs) {
   for (int k = lchunk + 1; k < t; ++k) {
     const uint32_t m = T_meta[k];
     if ((m >> 4) & 0xf) {
       double acc = T_ri[k];
       for (int k2 = k + 1; k2 < t; ++k2) acc += T_tr[k2];
-      *fpos = k * E + (int)((m >> 8) & 7);
-      *fv = T_fv[k];
-      *rs = acc;
-      return 1;
+      fv_rs[0] = T_fv[k];
+      fv_rs[1] = acc;
+      return k * E + (int)((m >> 8) & 7);
     }
   }
-  return 0;
+  return -1;
 }
 
 template <int NT, bool ALIGN>
@@ -139,8 +143,8 @@ window_fast_kernel(const WinParams p) {
   double* S_mn = S_sum + NE;
   double* S_mx = S_mn + NE;
   double* S_rs = S_mx + NE;
-  int64_t* s_ts = reinterpret_cast<int64_t*>(S_sum);              // staging aliases the suffix arrays
-  double* s_val = S_sum + TL::NSP;
+  double* s_val = S_sum;                                          // staging aliases the suffix arrays
+  int* s_t = reinterpret_cast<int*>(S_sum + TL::NSP);             // tile-relative timestamps
   uint16_t* S_meta = reinterpret_cast<uint16_t*>(S_rs + NE);
   double* T_sum = reinterpret_cast<double*>(S_meta + NE);
   double* T_mn = T_sum + NT;
@@ -151,7 +155,8 @@ window_fast_kernel(const WinParams p) {
   double* T_tr = T_ri + NT;
   uint32_t* T_meta = reinterpret_cast<uint32_t*>(T_tr + NT);
   int64_t* s_cursor = reinterpret_cast<int64_t*>(T_meta + NT);
-  double* rcp = reinterpret_cast<double*>(s_cursor + 2);           // rcp[n] = 1/n, n <= w
+  double* s_cold = reinterpret_cast<double*>(s_cursor + 2);        // 2 doubles per thread for the cold rate path
+  double* rcp = s_cold + 2 * NT;                                   // rcp[n] = 1/n, n <= w
   double* rdt = rcp + (p.w + 1);                                   // rdt[k] = 1000/(k*step_ms), k < w
 
   const int t = threadIdx.x;
@@ -169,6 +174,7 @@ window_fast_kernel(const WinParams p) {
   const bool do_rate = p.o_inc || p.o_rate;
   const double INF = __longlong_as_double(0x7FF0000000000000LL);
   const int need = p.min_periods > 1 ? p.min_periods : 1;
+  const int step = (int)p.step_ms, lookback = (int)p.lookback_ms;  // launch_fast checked the ranges
 
   for (int k = t; k <= p.w; k += NT) {
     rcp[k] = k ? 1.0 / (double)k : 0.0;
@@ -185,13 +191,12 @@ window_fast_kernel(const WinParams p) {
     const int n_out = (int)((c1 - jt < OUT) ? (c1 - jt) : OUT);
     const int n_el = HP + n_out;
     const int64_t row = s * p.n_steps + j0;                       // multiple of 4
-    double a[E];
 
     if (ALIGN) {
       const int elo = j0 < 0 ? (int)(-j0) : 0;                    // first element with a grid point
-      const int64_t glo = p.start_ms + (j0 + elo) * p.step_ms;
+      const int64_t tbase = p.start_ms + j0 * p.step_ms;          // grid time of tile element 0
       if (first) {
-        cur = floor_global(p.ts + base, len, glo);
+        cur = floor_global(p.ts + base, len, tbase + (int64_t)elo * p.step_ms);
         if (cur < 0) cur = 0;
         first = false;
       }
@@ -200,11 +205,16 @@ window_fast_kernel(const WinParams p) {
       {
         const int64_t* gts = p.ts + base + cur;
         const double* gv = p.val + base + cur;
-        for (int i = t; i < ns; i += NT) { s_ts[pad8(i)] = gts[i]; s_val[pad8(i)] = gv[i]; }
+        for (int i = t; i < ns; i += NT) {
+          int64_t d = gts[i] - tbase;                             // saturate: order and lookback tests stay exact
+          d = d > 0x7fffffffLL ? 0x7fffffffLL : (d < -0x40000000LL ? -0x40000000LL : d);
+          s_t[pad8(i)] = (int)d;
+          s_val[pad8(i)] = gv[i];
+        }
       }
       __syncthreads();
-      const int64_t ghi = p.start_ms + (j0 + n_el - 1) * p.step_ms;
-      const bool covered = (cur + ns >= len) || (ns > 0 && s_ts[pad8(ns - 1)] > ghi);
+      const int ghi = (n_el - 1) * step;
+      const bool covered = (cur + ns >= len) || (ns > 0 && s_t[pad8(ns - 1)] > ghi);
       const int e_cur = OUT;                                      // its floor seeds the next tile
       if (!covered) {
 #pragma unroll 1
@@ -213,42 +223,43 @@ window_fast_kernel(const WinParams p) {
           double v = pmx_nan();
           if (e >= elo && e < n_el) {
             int64_t idx;
-            v = align_one_global(p.ts + base, p.val + base, cur, len, p.start_ms + (j0 + e) * p.step_ms,
+            v = align_one_global(p.ts + base, p.val + base, cur, len, tbase + (int64_t)e * p.step_ms,
                                  p.lookback_ms, &idx);
             if (e == e_cur) *s_cursor = idx > cur ? idx : cur;
           }
-          a[r] = v;
+          A[r * NT + t] = v;
         }
       } else {
-        // guess: one sample per grid step, staged sample 0 is the floor of element elo (or the
+        // guess: one sample per grid step; staged sample 0 is the floor of element elo (or the
         // sample after it when the series starts later)
-        const int shift = (ns > 0 && s_ts[0] > glo) ? 1 : 0;
-        int idx = -2;
-        int64_t g = p.start_ms + (j0 + e0) * p.step_ms;
-#pragma unroll
-        for (int r = 0; r < E; ++r, g += p.step_ms) {
+        const int shift = (ns > 0 && s_t[0] > elo * step) ? 1 : 0;
+        int idx = e0 - elo - shift;
+        if (idx > ns - 1) idx = ns - 1;
+        {
+          const int ef = e0 > elo ? e0 : elo;                     // first element this thread aligns
+          const int g = ef * step;
+          if (idx < 0) idx = (ns > 0 && s_t[0] <= g) ? floor_staged(s_t, 0, ns, g) : -1;
+          else if (!(s_t[pad8(idx)] <= g && (idx + 1 >= ns || s_t[pad8(idx + 1)] > g))) idx = floor_staged(s_t, 0, ns, g);
+        }
+#pragma unroll 2
+        for (int r = 0; r < E; ++r) {
           const int e = e0 + r;
+          const int g = e * step;
           double v = pmx_nan();
           if (e >= elo && e < n_el) {
-            if (idx == -2) {
-              int gi = e - elo - shift;
-              if (gi > ns - 1) gi = ns - 1;
-              if (gi < 0) idx = (ns > 0 && s_ts[0] <= g) ? floor_staged(s_ts, 0, ns, g) : -1;
-              else if (s_ts[pad8(gi)] <= g && (gi + 1 >= ns || s_ts[pad8(gi + 1)] > g)) idx = gi;
-              else idx = floor_staged(s_ts, 0, ns, g);
-            } else if (idx + 1 < ns && s_ts[pad8(idx + 1)] <= g) {
+            if (idx + 1 < ns && s_t[pad8(idx + 1)] <= g) {
               ++idx;
-              if (idx + 1 < ns && s_ts[pad8(idx + 1)] <= g) idx = floor_staged(s_ts, idx + 1, ns, g);
+              if (idx + 1 < ns && s_t[pad8(idx + 1)] <= g) idx = floor_staged(s_t, idx + 1, ns, g);
             }
             if (idx >= 0) {
               const double sample = s_val[pad8(idx)];
-              if (g - s_ts[pad8(idx)] < p.lookback_ms &&
+              if (g - s_t[pad8(idx)] < lookback &&
                   (unsigned long long)__double_as_longlong(sample) != PMX_STALE_NAN_BITS)
                 v = sample;
             }
             if (e == e_cur) *s_cursor = cur + (idx > 0 ? idx : 0);
           }
-          a[r] = v;
+          A[r * NT + t] = v;
         }
       }
       __syncthreads();                                            // staging dead, cursor visible
@@ -261,10 +272,13 @@ window_fast_kernel(const WinParams p) {
       }
       __syncthreads();
 #pragma unroll
-      for (int r = 0; r < E; ++r) a[r] = (e0 + r < n_el) ? s_val[pad8(e0 + r)] : pmx_nan();
+      for (int r = 0; r < E; ++r) A[r * NT + t] = (e0 + r < n_el) ? s_val[pad8(e0 + r)] : pmx_nan();
       __syncthreads();
     }
 
+    double a[E];
+#pragma unroll
+    for (int r = 0; r < E; ++r) a[r] = A[r * NT + t];             // own elements: no hazard, no sync needed
     if (p.o_aligned) {
       store4(p.o_aligned + row, e0, HP, n_el, a[0], a[1], a[2], a[3]);
       store4(p.o_aligned + row, e0 + 4, HP, n_el, a[4], a[5], a[6], a[7]);
@@ -287,7 +301,7 @@ window_fast_kernel(const WinParams p) {
           sfv = v; foff = r; ++scn;
         }
         const int si = r * NT + t;
-        A[si] = v; S_sum[si] = ss; S_mn[si] = smn; S_mx[si] = smx; S_rs[si] = srs;
+        S_sum[si] = ss; S_mn[si] = smn; S_mx[si] = smx; S_rs[si] = srs;
         S_meta[si] = (uint16_t)(scf | (scn << 4) | (((foff - r) & 7) << 8));
       }
       T_sum[t] = ss; T_mn[t] = smn; T_mx[t] = smx; T_fv[t] = sfv; T_lv[t] = lv; T_ri[t] = srs;
@@ -323,62 +337,63 @@ window_fast_kernel(const WinParams p) {
       }
       double ps = 0.0, pmn = INF, pmx = -INF, prs = 0.0, plv = 0.0, pfv = 0.0;
       int pcf = 0, pcn = 0, plpos = 0, pfpos = 0;
-      double omn[4], omx[4], omean[4], oinc[4], orate[4]; int ocnt[4];
+#pragma unroll 1
+      for (int h = 0; h < 2; ++h) {                               // two groups of four outputs (code size)
+        double omn[4], omx[4], omean[4], oinc[4], orate[4]; int ocnt[4];
 #pragma unroll
-      for (int r = 0; r < E; ++r) {
-        const double v = a[r];
-        if (pmx_isfinite(v)) { ps += v; pmn = dmin(pmn, v); pmx = dmax(pmx, v); ++pcf; }
-        if (v == v) {
-          if (pcn > 0) prs += (v < plv) ? plv : 0.0; else { pfv = v; pfpos = e0 + r; }
-          plv = v; plpos = e0 + r; ++pcn;
-        }
-        const bool far = r < qb;                                  // window starts one chunk further back
-        int lchunk = far ? t - qa - 1 : t - qa;
-        const int lrow = far ? r - qb + E : r - qb;
-        if (lchunk < 0) lchunk = 0;                               // halo points only; result unused
-        const int si = lrow * NT + lchunk;
-        const uint32_t sm = S_meta[si];
-        const int k4 = r & 3;
-        if (do_roll) {
-          const double ws = S_sum[si] + (far ? ms2 : ms) + ps;
-          const double wmn = dmin(dmin(S_mn[si], far ? mmn2 : mmn), pmn);
-          const double wmx = dmax(dmax(S_mx[si], far ? mmx2 : mmx), pmx);
-          const int wcf = (int)(sm & 0xf) + (far ? mcf2 : mcf) + pcf;
-          const bool ok = wcf >= need;
-          omean[k4] = ok ? ws * rcp[wcf] : pmx_nan();
-          omn[k4] = ok ? wmn : pmx_nan();
-          omx[k4] = ok ? wmx : pmx_nan();
-          ocnt[k4] = (int)((sm >> 4) & 0xf) + (far ? mcn2 : mcn) + pcn;
-        }
-        if (do_rate) {
-          int fpos, lpos; double fv, lv, rs;
-          bool have = true;
-          if ((sm >> 4) & 0xf) {                                  // first chunk part holds a sample
-            fpos = lchunk * E + lrow + (int)((sm >> 8) & 7);
-            fv = A[(fpos & 7) * NT + (fpos >> 3)];
-            rs = S_rs[si] + (far ? mrs2 : mrs) + prs + (pcn > 0 ? Jc : 0.0);
-          } else if (rate_skip_empty(T_fv, T_ri, T_tr, T_meta, lchunk, t, &fpos, &fv, &rs)) {
-            rs += prs + (pcn > 0 ? Jc : 0.0);
-          } else {                                                // window lies inside the own chunk
-            have = pcn > 0; fpos = pfpos; fv = pfv; rs = prs;
+        for (int q = 0; q < 4; ++q) {
+          const int r = 4 * h + q;
+          const double v = A[r * NT + t];
+          if (pmx_isfinite(v)) { ps += v; pmn = dmin(pmn, v); pmx = dmax(pmx, v); ++pcf; }
+          if (v == v) {
+            if (pcn > 0) prs += (v < plv) ? plv : 0.0; else { pfv = v; pfpos = e0 + r; }
+            plv = v; plpos = e0 + r; ++pcn;
           }
-          if (pcn > 0) { lv = plv; lpos = plpos; } else { lv = clv; lpos = clpos; }
-          double inc = pmx_nan(), rate = pmx_nan();
-          if (have && lpos > fpos) { inc = (lv - fv) + rs; rate = inc * rdt[lpos - fpos]; }
-          oinc[k4] = inc; orate[k4] = rate;
-        }
-        if (k4 == 3) {
-          const int e = e0 + r - 3;
+          const bool far = r < qb;                                // window starts one chunk further back
+          int lchunk = far ? t - qa - 1 : t - qa;
+          const int lrow = far ? r - qb + E : r - qb;
+          if (lchunk < 0) lchunk = 0;                             // halo points only; result unused
+          const int si = lrow * NT + lchunk;
+          const uint32_t sm = S_meta[si];
           if (do_roll) {
-            store4(p.o_min ? p.o_min + row : nullptr, e, HP, n_el, omn[0], omn[1], omn[2], omn[3]);
-            store4(p.o_max ? p.o_max + row : nullptr, e, HP, n_el, omx[0], omx[1], omx[2], omx[3]);
-            store4(p.o_mean ? p.o_mean + row : nullptr, e, HP, n_el, omean[0], omean[1], omean[2], omean[3]);
-            store4i(p.o_cnt ? p.o_cnt + row : nullptr, e, HP, n_el, ocnt[0], ocnt[1], ocnt[2], ocnt[3]);
+            const double ws = S_sum[si] + (far ? ms2 : ms) + ps;
+            const double wmn = dmin(dmin(S_mn[si], far ? mmn2 : mmn), pmn);
+            const double wmx = dmax(dmax(S_mx[si], far ? mmx2 : mmx), pmx);
+            const int wcf = (int)(sm & 0xf) + (far ? mcf2 : mcf) + pcf;
+            const bool ok = wcf >= need;
+            omean[q] = ok ? ws * rcp[wcf] : pmx_nan();
+            omn[q] = ok ? wmn : pmx_nan();
+            omx[q] = ok ? wmx : pmx_nan();
+            ocnt[q] = (int)((sm >> 4) & 0xf) + (far ? mcn2 : mcn) + pcn;
           }
           if (do_rate) {
-            store4(p.o_inc ? p.o_inc + row : nullptr, e, HP, n_el, oinc[0], oinc[1], oinc[2], oinc[3]);
-            store4(p.o_rate ? p.o_rate + row : nullptr, e, HP, n_el, orate[0], orate[1], orate[2], orate[3]);
+            int fpos; double fv, rs;
+            if ((sm >> 4) & 0xf) {                                // first chunk part holds a sample
+              fpos = lchunk * E + lrow + (int)((sm >> 8) & 7);
+              fv = A[(fpos & 7) * NT + (fpos >> 3)];
+              rs = S_rs[si] + (far ? mrs2 : mrs) + prs + (pcn > 0 ? Jc : 0.0);
+            } else {
+              fpos = rate_skip_empty(T_fv, T_ri, T_tr, T_meta, lchunk, t, s_cold + 2 * t);
+              if (fpos >= 0) { fv = s_cold[2 * t]; rs = s_cold[2 * t + 1] + prs + (pcn > 0 ? Jc : 0.0); }
+              else { fpos = pcn > 0 ? pfpos : 0x7fffffff; fv = pfv; rs = prs; }   // window inside the own chunk
+            }
+            const double lv = pcn > 0 ? plv : clv;
+            const int lpos = pcn > 0 ? plpos : clpos;
+            double inc = pmx_nan(), rate = pmx_nan();
+            if (lpos > fpos) { inc = (lv - fv) + rs; rate = inc * rdt[lpos - fpos]; }
+            oinc[q] = inc; orate[q] = rate;
           }
+        }
+        const int e = e0 + 4 * h;
+        if (do_roll) {
+          store4(p.o_min ? p.o_min + row : nullptr, e, HP, n_el, omn[0], omn[1], omn[2], omn[3]);
+          store4(p.o_max ? p.o_max + row : nullptr, e, HP, n_el, omx[0], omx[1], omx[2], omx[3]);
+          store4(p.o_mean ? p.o_mean + row : nullptr, e, HP, n_el, omean[0], omean[1], omean[2], omean[3]);
+          store4i(p.o_cnt ? p.o_cnt + row : nullptr, e, HP, n_el, ocnt[0], ocnt[1], ocnt[2], ocnt[3]);
+        }
+        if (do_rate) {
+          store4(p.o_inc ? p.o_inc + row : nullptr, e, HP, n_el, oinc[0], oinc[1], oinc[2], oinc[3]);
+          store4(p.o_rate ? p.o_rate + row : nullptr, e, HP, n_el, orate[0], orate[1], orate[2], orate[3]);
         }
       }
     }
@@ -402,7 +417,7 @@ int launch_fast(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
   p.chunks = (int32_t)((p.n_steps + p.chunk_len - 1) / p.chunk_len);
   const int64_t grid = p.n_series * p.chunks;
   if (grid > 0x7fffffffLL) return pmx_fail(PMX_E_LIMIT, "window kernel: n_series * chunks exceeds 2^31-1");
-  const size_t smem = TL::FIXED + size_t(2) * (p.w + 1) * 8 + 16;
+  const size_t smem = TL::FIXED + size_t(2) * NT * 8 + size_t(2) * (p.w + 1) * 8 + 16;
   PMX_CUDA(cudaFuncSetAttribute(window_fast_kernel<NT, ALIGN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   window_fast_kernel<NT, ALIGN><<<(unsigned)grid, NT, smem, st>>>(p);
   PMX_LAUNCH_CHECK();
@@ -417,6 +432,8 @@ int launch_window_fast(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
   const int H = p.w - 1;
   if (H < 8 || H > nt * E / 2 - 4) return 1;
   if (p.o_nres || p.o_idx) return 1;
+  // tile-relative timestamps are 32-bit: a tile (plus the lookback) must span < 2^30 ms
+  if (p.step_ms > 0x3fffffffLL / (nt * E + 8) || p.lookback_ms >= 0x3fffffffLL) return 1;
   if (!aligned32(p.o_aligned) || !aligned32(p.o_min) || !aligned32(p.o_max) || !aligned32(p.o_mean) ||
       !aligned32(p.o_inc) || !aligned32(p.o_rate) || (reinterpret_cast<uintptr_t>(p.o_cnt) & 15))
     return 1;
