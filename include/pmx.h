@@ -168,7 +168,9 @@ int pmx_where_gt(pmx_ctx* ctx, const double* d_x, int64_t n, double threshold, d
  * uint64] -> pmx_quantile_pick (device-side prefix scan: choose the bin holding each target
  * rank, extend the prefix).  After the last pass pmx_quantile_finish converts the keys back
  * and interpolates like numpy's _lerp (Series.quantile / np.percentile 'linear').
- * d_hist is uint64 [n_seg * 2*n_q * PMX_QUANTILE_BINS] (pass 0 uses the first n_seg*BINS). */
+ * d_hist is uint64 [n_seg * 2*n_q * PMX_QUANTILE_BINS] (pass 0 uses the first n_seg*BINS).
+ * Pass 2 keeps the keys that still match a target in ctx scratch (<= 2^20 per segment) and passes
+ * 3-5 read only those; one selection at a time per ctx, passes in order 0..5. */
 int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
                       const int32_t* d_seg, int64_t n_seg, int64_t n_q, int pass,
                       const uint64_t* d_state, uint64_t* d_hist, pmx_stream stream);

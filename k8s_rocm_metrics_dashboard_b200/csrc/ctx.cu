@@ -20,17 +20,17 @@ int pmx_cuda_fail(cudaError_t e, const char* what) {
   return PMX_E_CUDA;
 }
 
-void* pmx_scratch(pmx_ctx* ctx, size_t bytes) {
-  if (bytes <= ctx->scratch_bytes) return ctx->scratch;
+void* pmx_scratch(pmx_ctx* ctx, int slot, size_t bytes) {
+  if (bytes <= ctx->scratch_bytes[slot]) return ctx->scratch[slot];
   // cudaFree synchronises the device, so work still using the old block has finished.
-  if (ctx->scratch) cudaFree(ctx->scratch);
-  ctx->scratch = nullptr;
-  ctx->scratch_bytes = 0;
+  if (ctx->scratch[slot]) cudaFree(ctx->scratch[slot]);
+  ctx->scratch[slot] = nullptr;
+  ctx->scratch_bytes[slot] = 0;
   size_t want = (bytes + (size_t(1) << 20) - 1) & ~((size_t(1) << 20) - 1);
-  cudaError_t e = cudaMalloc(&ctx->scratch, want);
+  cudaError_t e = cudaMalloc(&ctx->scratch[slot], want);
   if (e != cudaSuccess) { pmx_cuda_fail(e, "cudaMalloc(scratch)"); return nullptr; }
-  ctx->scratch_bytes = want;
-  return ctx->scratch;
+  ctx->scratch_bytes[slot] = want;
+  return ctx->scratch[slot];
 }
 
 extern "C" {
@@ -57,18 +57,19 @@ int pmx_ctx_create(int device, pmx_ctx** out) {
   if (!c) return pmx_fail(PMX_E_INVALID, "pmx_ctx_create: out of host memory");
   c->device = device;
   c->sm_count = prop.multiProcessorCount;
-  c->scratch = nullptr;
-  c->scratch_bytes = 0;
+  for (int i = 0; i < 3; ++i) { c->scratch[i] = nullptr; c->scratch_bytes[i] = 0; }
   *out = c;
   return PMX_OK;
 }
 
 void pmx_ctx_destroy(pmx_ctx* ctx) {
   if (!ctx) return;
-  if (ctx->scratch) cudaFree(ctx->scratch);
+  for (int i = 0; i < 3; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
   delete ctx;
 }
 
-size_t pmx_ctx_scratch_bytes(const pmx_ctx* ctx) { return ctx ? ctx->scratch_bytes : 0; }
+size_t pmx_ctx_scratch_bytes(const pmx_ctx* ctx) {
+  return ctx ? ctx->scratch_bytes[0] + ctx->scratch_bytes[1] + ctx->scratch_bytes[2] : 0;
+}
 
 }  // extern "C"

@@ -8,15 +8,19 @@
 struct pmx_ctx {
   int device;
   int sm_count;
-  void* scratch;          // grow-only device scratch (group partials, quantile state, ...)
-  size_t scratch_bytes;
+  // grow-only device scratch, one block per purpose so that they can live side by side:
+  // 0 = per-series partials of pmx_group_reduce, 1 = state + histograms of pmx_quantile_select,
+  // 2 = candidate keys kept between the passes of a quantile selection
+  void* scratch[3];
+  size_t scratch_bytes[3];
 };
+enum { PMX_SCR_PARTIALS = 0, PMX_SCR_QSELECT = 1, PMX_SCR_QCAND = 2 };
 
 // error plumbing (ctx.cu)
 int pmx_fail(int code, const char* fmt, ...);
 int pmx_cuda_fail(cudaError_t e, const char* what);
 // returns NULL (and sets the error) on failure
-void* pmx_scratch(pmx_ctx* ctx, size_t bytes);
+void* pmx_scratch(pmx_ctx* ctx, int slot, size_t bytes);
 
 #define PMX_CUDA(call)                                                   \
   do {                                                                   \

@@ -10,6 +10,9 @@
 // After the last pass every target's prefix IS the key of the wanted order statistic.  Targets
 // per segment: for each q the ranks lo = floor((n-1)q) and hi = min(lo+1, n-1), then numpy's
 // _lerp.  No sample ever moves between GPUs; a pass exchanges 16 KiB per target.
+// Passes 0-2 read every value.  Pass 2 also copies the keys that still match a target prefix
+// (22 bits known by then) into a per-segment candidate list; passes 3-5 read only that list.
+// A segment whose list overflows (heavy ties) keeps reading the full data.
 //
 // State per segment (uint64 words): [0] n, [1] reserved, then per target t: [2+2t] prefix,
 // [3+2t] remaining rank inside the prefix bucket.
@@ -50,13 +53,32 @@ __device__ __forceinline__ void hist_add(unsigned int* h, bool hit, unsigned d, 
   if ((todo >> lane) & 1) atomicAdd(&h[d], 1u);
 }
 
+// distinct prefixes of a segment's targets (lo/hi ranks and nearby quantiles usually share one)
+__device__ __forceinline__ void load_prefixes(const uint64_t* __restrict__ state, int sw, int sg, int n_t,
+                                              int pass, uint64_t* s_uprefix, int* s_umap, int* s_nu) {
+  int nu = 0;
+  if (pass == 0) nu = 1;
+  else for (int k = 0; k < n_t; ++k) {
+    const uint64_t pf = state[(size_t)sg * sw + 2 + 2 * k];
+    int u = 0;
+    while (u < nu && s_uprefix[u] != pf) ++u;
+    if (u == nu) s_uprefix[nu++] = pf;
+    s_umap[k] = u;
+  }
+  *s_nu = nu;
+}
+
+// mode 0: histogram only; mode 1 (pass 2): also append matching keys to the segment's candidate
+// list; mode 2 (pass >= 3): skip segments whose candidate list is complete (cand_hist_kernel
+// serves them).
 __global__ void __launch_bounds__(256)
 hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __restrict__ seg,
             int n_t, int pass, const uint64_t* __restrict__ state, int sw,
-            unsigned long long* __restrict__ hist, int rows_per_cta, int64_t n_series) {
+            unsigned long long* __restrict__ hist, int rows_per_cta, int64_t n_series,
+            int mode, unsigned long long* __restrict__ cand, unsigned int* __restrict__ cand_cnt, unsigned cap) {
   extern __shared__ unsigned int sh[];                     // [n_uniq][BINS]
-  __shared__ uint64_t s_uprefix[MAX_TARGETS];              // distinct prefixes of this segment's targets
-  __shared__ int s_umap[MAX_TARGETS];                      // target -> index of its distinct prefix
+  __shared__ uint64_t s_uprefix[MAX_TARGETS];
+  __shared__ int s_umap[MAX_TARGETS];
   __shared__ int s_nu;
   const int64_t s0 = (int64_t)blockIdx.x * rows_per_cta;
   const int shift = digit_shift(pass);
@@ -83,21 +105,11 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
     if (s >= n_series) break;
     const int sg = seg[s];
     if (sg < 0) continue;
+    if (mode == 2 && cand_cnt[sg] <= cap) continue;        // complete candidate list: not our job
     if (sg != cur_seg) {                                   // flush, switch segment
       if (cur_seg >= 0) flush(cur_seg);
       __syncthreads();
-      if (threadIdx.x == 0) {
-        int nu = 0;
-        if (pass == 0) nu = 1;
-        else for (int k = 0; k < n_t; ++k) {
-          const uint64_t pf = state[(size_t)sg * sw + 2 + 2 * k];
-          int u = 0;
-          while (u < nu && s_uprefix[u] != pf) ++u;
-          if (u == nu) s_uprefix[nu++] = pf;
-          s_umap[k] = u;
-        }
-        s_nu = nu;
-      }
+      if (threadIdx.x == 0) load_prefixes(state, sw, sg, n_t, pass, s_uprefix, s_umap, &s_nu);
       __syncthreads();
       for (int i = threadIdx.x; i < s_nu * BINS; i += blockDim.x) sh[i] = 0;
       cur_seg = sg;
@@ -121,15 +133,71 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
         const bool valid = v == v;
         const uint64_t key = f64_key(v);
         const unsigned d = (unsigned)(key >> shift) & mask;
-        if (pass == 0) hist_add(sh, valid, d, lane);
-        else {
-          const uint64_t top = key >> pshift;
-          for (int u = 0; u < nu; ++u) hist_add(sh + u * BINS, valid && top == s_uprefix[u], d, lane);
+        if (pass == 0) { hist_add(sh, valid, d, lane); continue; }
+        const uint64_t top = key >> pshift;
+        unsigned hits = 0;                                 // bit u: this lane's key carries distinct prefix u
+        for (int u = 0; u < nu; ++u) hits |= (valid && top == s_uprefix[u]) ? (1u << u) : 0u;
+        const unsigned any = __ballot_sync(0xffffffffu, hits != 0);
+        if (any == 0) continue;                            // common case from pass 2 on
+        for (int u = 0; u < nu; ++u) hist_add(sh + u * BINS, (hits >> u) & 1, d, lane);
+        if (mode == 1) {                                   // append to the candidate list, one atomic per warp
+          const int leader = __ffs(any) - 1;
+          unsigned base = 0;
+          if (lane == leader) base = atomicAdd(&cand_cnt[sg], (unsigned)__popc(any));
+          base = __shfl_sync(0xffffffffu, base, leader);
+          if (hits) {
+            const unsigned pos = base + (unsigned)__popc(any & ((1u << lane) - 1u));
+            if (pos < cap) cand[(size_t)sg * cap + pos] = key;
+          }
         }
       }
     }
   }
   if (cur_seg >= 0) flush(cur_seg);
+}
+
+// passes >= 3 over the candidate lists: grid (blocks, n_seg)
+__global__ void __launch_bounds__(256)
+cand_hist_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __restrict__ cand_cnt,
+                 unsigned cap, int n_t, int pass, const uint64_t* __restrict__ state, int sw,
+                 unsigned long long* __restrict__ hist) {
+  extern __shared__ unsigned int sh[];
+  __shared__ uint64_t s_uprefix[MAX_TARGETS];
+  __shared__ int s_umap[MAX_TARGETS];
+  __shared__ int s_nu;
+  const int sg = blockIdx.y;
+  const unsigned n = cand_cnt[sg];
+  if (n > cap || n == 0) return;
+  const unsigned per = (n + gridDim.x - 1) / gridDim.x;
+  const unsigned a = blockIdx.x * per, b = a + per < n ? a + per : n;
+  if (a >= b) return;
+  const int shift = digit_shift(pass);
+  const unsigned mask = (1u << digit_bits(pass)) - 1u;
+  const int pshift = 64 - 11 * pass;
+  const int lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) load_prefixes(state, sw, sg, n_t, pass, s_uprefix, s_umap, &s_nu);
+  __syncthreads();
+  const int nu = s_nu;
+  for (int i = threadIdx.x; i < nu * BINS; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  const unsigned long long* keys = cand + (size_t)sg * cap;
+  for (unsigned i0 = a; i0 < b; i0 += blockDim.x) {
+    const unsigned i = i0 + threadIdx.x;
+    const bool in = i < b;
+    const uint64_t key = in ? keys[i] : 0;
+    const unsigned d = (unsigned)(key >> shift) & mask;
+    const uint64_t top = key >> pshift;
+    for (int u = 0; u < nu; ++u) hist_add(sh + u * BINS, in && top == s_uprefix[u], d, lane);
+  }
+  __syncthreads();
+  for (int k = 0; k < n_t; ++k) {
+    const unsigned int* src = sh + s_umap[k] * BINS;
+    unsigned long long* dst = hist + ((size_t)sg * n_t + k) * BINS;
+    for (int i = threadIdx.x; i < BINS; i += blockDim.x) {
+      const unsigned c = src[i];
+      if (c) atomicAdd(&dst[i], (unsigned long long)c);
+    }
+  }
 }
 
 // grid (n_t, n_seg); one CTA scans one histogram
@@ -236,15 +304,39 @@ int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
   PMX_CUDA(cudaMemsetAsync(d_hist, 0, (size_t)n_seg * n_h * BINS * sizeof(uint64_t), st));
   if (n_series == 0 || n_steps == 0) return PMX_OK;
   PMX_REQUIRE(d_x && d_seg, "NULL buffer");
+  // candidate lists (ctx scratch; they live from pass 2 to pass 5 of one selection)
+  unsigned cap = 0; unsigned int* cand_cnt = nullptr; unsigned long long* cand = nullptr;
+  int mode = 0;
+  if (pass >= 2) {
+    int64_t c = ((int64_t)256 << 20) / 8 / n_seg;
+    if (c > (1 << 20)) c = 1 << 20;
+    if (c < 4096) c = 4096;
+    cap = (unsigned)c;
+    const size_t hdr = ((size_t)n_seg * sizeof(unsigned int) + 255) & ~size_t(255);
+    unsigned char* scr = (unsigned char*)pmx_scratch(ctx, PMX_SCR_QCAND, hdr + (size_t)n_seg * cap * 8);
+    if (!scr) return PMX_E_CUDA;
+    cand_cnt = (unsigned int*)scr;
+    cand = (unsigned long long*)(scr + hdr);
+    mode = pass == 2 ? 1 : 2;
+    if (pass == 2) PMX_CUDA(cudaMemsetAsync(cand_cnt, 0, hdr, st));
+  }
   const size_t smem = (size_t)n_h * BINS * sizeof(unsigned int);
   PMX_CUDA(cudaFuncSetAttribute(hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(MAX_TARGETS * BINS * sizeof(unsigned int))));
+  if (mode == 2) {
+    PMX_CUDA(cudaFuncSetAttribute(cand_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(MAX_TARGETS * BINS * sizeof(unsigned int))));
+    dim3 grid(8, (unsigned)n_seg);
+    cand_hist_kernel<<<grid, 256, smem, st>>>(cand, cand_cnt, cap, n_t, pass, d_state, state_words(n_q),
+                                            (unsigned long long*)d_hist);
+    PMX_LAUNCH_CHECK();
+  }
   // a CTA sweeps consecutive rows so that a segment's private histogram is flushed rarely
   int64_t want_ctas = (int64_t)ctx->sm_count * 16;
   int64_t rows = (n_series + want_ctas - 1) / want_ctas;
   if (rows < 1) rows = 1;
   const int64_t grid = (n_series + rows - 1) / rows;
   hist_kernel<<<(unsigned)grid, 256, smem, st>>>(d_x, n_steps, d_seg, n_t, pass, d_state, state_words(n_q),
-                                                (unsigned long long*)d_hist, (int)rows, n_series);
+                                                (unsigned long long*)d_hist, (int)rows, n_series, mode, cand,
+                                                cand_cnt, cap);
   PMX_LAUNCH_CHECK();
   return PMX_OK;
 }
@@ -289,7 +381,7 @@ int pmx_quantile_select(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64
   if (n_seg == 0) return PMX_OK;
   const size_t state_bytes = ((size_t)n_seg * state_words(n_q) * 8 + 255) & ~size_t(255);
   const size_t hist_bytes = (size_t)n_seg * 2 * n_q * BINS * 8;
-  unsigned char* scr = (unsigned char*)pmx_scratch(ctx, state_bytes + hist_bytes);
+  unsigned char* scr = (unsigned char*)pmx_scratch(ctx, PMX_SCR_QSELECT, state_bytes + hist_bytes);
   if (!scr) return PMX_E_CUDA;
   uint64_t* state = (uint64_t*)scr;
   uint64_t* hist = (uint64_t*)(scr + state_bytes);

@@ -137,7 +137,7 @@ int pmx_group_reduce(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t 
   }
   Part* part = nullptr;
   if (n_series > 0) {
-    part = (Part*)pmx_scratch(ctx, (size_t)n_series * sizeof(Part));
+    part = (Part*)pmx_scratch(ctx, PMX_SCR_PARTIALS, (size_t)n_series * sizeof(Part));
     if (!part) return PMX_E_CUDA;
     series_partial_kernel<<<(unsigned)n_series, 256, 0, st>>>(d_x, n_steps, part);
     PMX_LAUNCH_CHECK();

@@ -83,3 +83,16 @@ def test_quantiles_config4_shape_scaled(eng):
     names = sorted({l["__name__"] for l in d["labels"]})
     seg = np.array([names.index(l["__name__"]) for l in d["labels"]], dtype=np.int32)
     _check_quantiles(eng, al, seg, len(names), [0.5, 0.95, 0.99])
+
+
+def test_quantiles_candidate_list_overflow_falls_back_to_full_passes(eng):
+    """More than 2^20 equal values in one segment overflow its candidate list (kept from pass 2
+    on); that segment must keep reading the full data, the other one uses its list."""
+    rng = np.random.default_rng(9)
+    x = np.full((320, 4096), 5.0)                       # 1.3 M ties
+    x[:, ::97] = rng.normal(size=x[:, ::97].shape)
+    y = rng.normal(size=(8, 4096))
+    z = np.concatenate([x, y])
+    seg = np.array([0] * 320 + [1] * 8, dtype=np.int32)
+    _check_quantiles(eng, z, seg, 2, [0.5, 0.95, 0.99])
+    _check_quantiles(eng, z, seg, 2, [0.001, 0.999])
