@@ -144,6 +144,19 @@ int pmx_group_reduce(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t 
                      int per_step, double* d_sum, int64_t* d_count, double* d_min,
                      double* d_max, double* d_mean, pmx_stream stream);
 
+/* ---- pmx_group_reduce(per_step = 0) without any device allocation.  No counterpart in the
+ * reference: it exists for callers that cannot allocate when they call -- the GPU's memory is
+ * already handed out in full to another allocator (a late cudaMalloc may fail), or the implicit
+ * device-wide synchronisation of cudaMalloc/cudaFree does not fit a refresh loop.  The per-series
+ * partials live in a fixed 2 MiB array inside the library (held by every GPU that loads it):
+ * at most 65536 series (PMX_E_LIMIT beyond); no ctx; the first call on a device looks the array's
+ * address up once and should be made outside stream capture; all calls share the array, so calls
+ * that overlap on the GPU race.  Results equal pmx_group_reduce's. */
+int pmx_group_reduce_noalloc(const double* d_x, int64_t n_series, int64_t n_steps,
+                             const int32_t* d_perm, const int64_t* d_goff, int64_t n_groups,
+                             double* d_sum, int64_t* d_count, double* d_min, double* d_max,
+                             double* d_mean, pmx_stream stream);
+
 /* ---- H5 / H6 / H9  the per-card steps of the instant path.
  * pmx_pivot_gather: long -> wide (df.pivot at app.py:207): out[cell] = val[src[cell]] or NaN when
  *   src[cell] < 0 (missing cell).  Duplicate (gpu_id, metric) keys are detected by the adapter

@@ -55,6 +55,7 @@ SIGNATURES = {
                                             _p, _p, _p, _p, _p, _p]),
     "pmx_group_index": (_int, [_p, _i64, _i64, _p, _p]),
     "pmx_group_reduce": (_int, [_p, _p, _i64, _i64, _p, _p, _i64, _int, _p, _p, _p, _p, _p, _p]),
+    "pmx_group_reduce_noalloc": (_int, [_p, _i64, _i64, _p, _p, _i64, _p, _p, _p, _p, _p, _p]),
     "pmx_pivot_gather": (_int, [_p, _p, _p, _i64, _p, _p]),
     "pmx_ratio_pct": (_int, [_p, _p, _i64, _p, _i64, _i64, _p, _i64, _p, _p]),
     "pmx_where_gt": (_int, [_p, _p, _i64, C.c_double, _p, _p]),

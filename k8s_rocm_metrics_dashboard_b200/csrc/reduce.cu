@@ -29,6 +29,13 @@ __device__ __forceinline__ Part part_shfl_down(const Part& p, int d) {
   return q;
 }
 
+// Scratch of pmx_group_reduce_noalloc: lives in the library image, so no allocation is ever made
+// for it.  Every GPU that loads libpmx.so holds these 2 MiB until the process exits.
+constexpr int64_t NOALLOC_MAX_SERIES = 65536;
+static __device__ __align__(256) unsigned char g_noalloc_partials[NOALLOC_MAX_SERIES * sizeof(Part)];
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static Part* g_noalloc_addr[NOALLOC_MAX_DEVICES];      // device address of the array, per CUDA device
+
 // one CTA per series: partial (sum, min, max, count) over all steps -> part[s]
 __global__ void __launch_bounds__(256)
 series_partial_kernel(const double* __restrict__ x, int64_t n_steps, Part* __restrict__ part) {
@@ -144,6 +151,50 @@ int pmx_group_reduce(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t 
   }
   group_fold_kernel<<<(unsigned)((n_groups + 3) / 4), 128, 0, st>>>(part, d_perm, d_goff, n_groups, d_sum, d_count,
                                                                       d_min, d_max, d_mean);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
+// Same result as pmx_group_reduce(per_step = 0), for callers that cannot allocate device memory
+// when the call is made: programs whose memory budget is already handed out in full (another
+// allocator owns the rest of the GPU, so a late cudaMalloc can fail), and latency-bound refresh
+// loops where the implicit device synchronisation of cudaMalloc/cudaFree is not acceptable.
+// The per-series partials go to a fixed array inside the library instead of ctx scratch:
+//   * at most 65536 series; more is refused with PMX_E_LIMIT;
+//   * the first call on a device resolves the array's device address (cudaGetSymbolAddress, with
+//     that device current) and keeps it; make that first call outside of any stream capture;
+//   * no cudaMalloc / cudaFree / allocating library call happens here, and no ctx is needed;
+//   * every call uses the same array.  Each call overwrites the slots it reads, so nothing has to
+//     be cleared, but two calls that overlap on the GPU (different streams) race on it.
+int pmx_group_reduce_noalloc(const double* d_x, int64_t n_series, int64_t n_steps, const int32_t* d_perm,
+                             const int64_t* d_goff, int64_t n_groups, double* d_sum, int64_t* d_count,
+                             double* d_min, double* d_max, double* d_mean, pmx_stream stream) {
+  if (n_series < 0 || n_steps < 0 || n_groups < 0)
+    return pmx_fail(PMX_E_INVALID, "pmx_group_reduce_noalloc: negative size");
+  if (n_series > NOALLOC_MAX_SERIES)
+    return pmx_fail(PMX_E_LIMIT, "pmx_group_reduce_noalloc: %lld series exceed the fixed scratch of %lld; "
+                    "use pmx_group_reduce", (long long)n_series, (long long)NOALLOC_MAX_SERIES);
+  if (n_groups == 0) return PMX_OK;
+  if (!d_goff || (n_series > 0 && (!d_x || !d_perm)))
+    return pmx_fail(PMX_E_INVALID, "pmx_group_reduce_noalloc: NULL buffer");
+  int dev = -1;
+  PMX_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= NOALLOC_MAX_DEVICES)
+    return pmx_fail(PMX_E_LIMIT, "pmx_group_reduce_noalloc: device ordinal %d not supported", dev);
+  if (!g_noalloc_addr[dev]) {
+    // in host code the array's name is only a handle; kernels need its address on THIS device
+    void* p = nullptr;
+    PMX_CUDA(cudaGetSymbolAddress(&p, g_noalloc_partials));
+    g_noalloc_addr[dev] = static_cast<Part*>(p);
+  }
+  Part* part = g_noalloc_addr[dev];
+  cudaStream_t st = pmx_st(stream);
+  if (n_series > 0) {
+    series_partial_kernel<<<(unsigned)n_series, 256, 0, st>>>(d_x, n_steps, part);
+    PMX_LAUNCH_CHECK();
+  }
+  group_fold_kernel<<<(unsigned)((n_groups + 3) / 4), 128, 0, st>>>(part, d_perm, d_goff, n_groups, d_sum, d_count,
+                                                                  d_min, d_max, d_mean);
   PMX_LAUNCH_CHECK();
   return PMX_OK;
 }
