@@ -6,10 +6,12 @@
 //   * results leave the SM straight from registers as 256-bit stores (STG.E.ENL2.256: one full
 //     32-byte sector per lane); the tile origin is shifted by 0..3 halo points so that every
 //     thread's 8 points start on a 32-byte boundary of every output row;
-//   * the rate is no longer a general ordered-monoid fold per output: each chunk publishes the
-//     sum of its pre-reset values including the junction with the previous valid point, so a
-//     window's reset sum is suffix + chunk totals + prefix (plain additions).  Only windows whose
-//     first chunk part is empty (NaN runs) take a short out-of-line loop over chunk totals;
+//   * the increase is accumulated as a sum of per-sample deltas (x - prev, or x itself after a
+//     drop; the telescoped form of (last - first) + pre-reset values, equal within a few ulp of
+//     the increments), so a window's increase is suffix + chunk totals + prefix like the sum, and
+//     no first/last value has to be fetched.  Junction deltas between chunks are formed on the
+//     fly while the chunk totals are folded.  Only windows whose first chunk part is empty (NaN
+//     runs) take a short out-of-line loop over chunk totals;
 //   * divisions are replaced by two per-CTA tables in shared memory (1/n and 1000/(k*step));
 //   * the align stage starts from "one sample per step" as its guess and only binary-searches the
 //     staged timestamps when the guess is wrong; indices are 32-bit, shared memory is addressed
@@ -17,10 +19,15 @@
 // Requests it does not cover (window_steps < 9 or > NE/2, n_resets / source-index outputs,
 // output rows not 32-byte aligned) go to the general kernel in window.cu.
 //
-// Shared memory per CTA (NT threads, NE = 8 NT points): A[NE] aligned values, four suffix arrays
-// S_*[NE] (aliased with the sample staging area), chunk totals T_*[NT], the two tables.
+// Shared memory per CTA (NT threads, NE = 8 NT points): four suffix arrays S_*[NE] (aliased with
+// the sample staging area and the aligned-value hand-off), chunk totals T_*[NT], the two tables.
 #include <math.h>
+#include <stdlib.h>
 #include "window_common.cuh"
+
+#ifndef PMX_FAST_CTAS_128
+#define PMX_FAST_CTAS_128 4
+#endif
 
 namespace pmxw {
 namespace {
@@ -29,12 +36,12 @@ template <int NT> struct FTile {
   static constexpr int NE = NT * E;
   static constexpr int NS = NE + E;
   static constexpr int NSP = NS + NS / 8 + 2;
-  static constexpr size_t A_BYTES = size_t(NE) * 8;
-  static constexpr size_t S_BYTES = size_t(4) * NE * 8;          // >= staging 2*NSP*8
+  static constexpr size_t S_BYTES = size_t(4) * NE * 8;          // sum, min, max, delta-sum
   static constexpr size_t SM_BYTES = size_t(NE) * 2;
-  static constexpr size_t T_BYTES = size_t(7) * NT * 8 + size_t(NT) * 4;
-  static constexpr size_t FIXED = A_BYTES + S_BYTES + SM_BYTES + T_BYTES + 16;
-  static_assert(size_t(2) * NSP * 8 <= S_BYTES, "staging must fit in the suffix arrays");
+  static constexpr size_t T_BYTES = size_t(6) * NT * 8 + size_t(NT) * 4;
+  static constexpr size_t FIXED = S_BYTES + SM_BYTES + T_BYTES + 16;
+  // staging (values + 32-bit times) sits in S_sum/S_mn, the aligned values in S_d meanwhile
+  static_assert(size_t(NSP) * 12 <= size_t(2) * NE * 8, "staging must fit in two suffix arrays");
 };
 
 __device__ __forceinline__ int pad8(int i) { return i + (i >> 3); }
@@ -114,46 +121,50 @@ __device__ __noinline__ double align_one_global(const int64_t* __restrict__ ts, 
   return pmx_nan();
 }
 
-// Rate of a window whose first chunk part [l, end of chunk lchunk] holds no sample: walk the chunk
-// totals forward to the first non-empty chunk before the own chunk t.  Cold (needs a NaN run).
-// Returns fpos (>= 0) with (fv, rs) when such a chunk exists, else -1 (window lies in the own chunk).
-__device__ __noinline__ int rate_skip_empty(const double* T_fv, const double* T_ri, const double* T_tr,
-                                            const uint32_t* T_meta, int lchunk, int t, double* fv_rs) {
+__device__ __forceinline__ double delta_of(double cur, double prev) { return cur < prev ? cur : cur - prev; }
+
+// Increase of a window whose first chunk part [l, end of chunk lchunk] holds no sample: walk the
+// chunk totals forward from the first non-empty chunk before the own chunk t, forming junction
+// deltas on the way.  Cold (needs a NaN run).  Returns fpos (>= 0) and, in out[0..1], the delta sum
+// up to the own chunk and the last valid value before it; -1 when the window lies in the own chunk.
+__device__ __noinline__ int rate_skip_empty(const double* T_fv, const double* T_lv, const double* T_di,
+                                            const uint32_t* T_meta, int lchunk, int t, double* out) {
   for (int k = lchunk + 1; k < t; ++k) {
     const uint32_t m = T_meta[k];
     if ((m >> 4) & 0xf) {
-      double acc = T_ri[k];
-      for (int k2 = k + 1; k2 < t; ++k2) acc += T_tr[k2];
-      fv_rs[0] = T_fv[k];
-      fv_rs[1] = acc;
+      double acc = T_di[k], lv = T_lv[k];
+      for (int k2 = k + 1; k2 < t; ++k2) {
+        if ((T_meta[k2] >> 4) & 0xf) { acc += T_di[k2] + delta_of(T_fv[k2], lv); lv = T_lv[k2]; }
+      }
+      out[0] = acc;
+      out[1] = lv;
       return k * E + (int)((m >> 8) & 7);
     }
   }
   return -1;
 }
 
-template <int NT, bool ALIGN>
-__global__ void __launch_bounds__(NT, (NT == 256 ? 2 : 4))
+template <int NT, bool ALIGN, int MINB>
+__global__ void __launch_bounds__(NT, MINB)
 window_fast_kernel(const WinParams p) {
   using TL = FTile<NT>;
   constexpr int NE = TL::NE;
   extern __shared__ __align__(16) unsigned char smem[];
-  double* A = reinterpret_cast<double*>(smem);
-  double* S_sum = A + NE;
+  double* S_sum = reinterpret_cast<double*>(smem);
   double* S_mn = S_sum + NE;
   double* S_mx = S_mn + NE;
-  double* S_rs = S_mx + NE;
-  double* s_val = S_sum;                                          // staging aliases the suffix arrays
+  double* S_d = S_mx + NE;
+  double* s_val = S_sum;                                          // staging aliases S_sum/S_mn
   int* s_t = reinterpret_cast<int*>(S_sum + TL::NSP);             // tile-relative timestamps
-  uint16_t* S_meta = reinterpret_cast<uint16_t*>(S_rs + NE);
+  double* A = S_d;                                                // aligned values, align -> registers
+  uint16_t* S_meta = reinterpret_cast<uint16_t*>(S_d + NE);
   double* T_sum = reinterpret_cast<double*>(S_meta + NE);
   double* T_mn = T_sum + NT;
   double* T_mx = T_mn + NT;
   double* T_fv = T_mx + NT;
   double* T_lv = T_fv + NT;
-  double* T_ri = T_lv + NT;
-  double* T_tr = T_ri + NT;
-  uint32_t* T_meta = reinterpret_cast<uint32_t*>(T_tr + NT);
+  double* T_di = T_lv + NT;
+  uint32_t* T_meta = reinterpret_cast<uint32_t*>(T_di + NT);
   int64_t* s_cursor = reinterpret_cast<int64_t*>(T_meta + NT);
   double* s_cold = reinterpret_cast<double*>(s_cursor + 2);        // 2 doubles per thread for the cold rate path
   double* rcp = s_cold + 2 * NT;                                   // rcp[n] = 1/n, n <= w
@@ -264,6 +275,14 @@ window_fast_kernel(const WinParams p) {
       }
       __syncthreads();                                            // staging dead, cursor visible
       cur = *s_cursor;
+      if (jt + OUT < c1) {                                        // pull the next tile's samples towards L2
+        const int64_t nrem = len - cur;
+        const int lines = (int)(((nrem < TL::NS ? nrem : TL::NS) * 8 + 127) >> 7);
+        if (t < lines) {
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(p.ts + base + cur + t * 16));
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(p.val + base + cur + t * 16));
+        }
+      }
     } else {
       const double* xr = p.x + s * p.n_steps;
       for (int i = t; i < n_el; i += NT) {
@@ -278,7 +297,7 @@ window_fast_kernel(const WinParams p) {
 
     double a[E];
 #pragma unroll
-    for (int r = 0; r < E; ++r) a[r] = A[r * NT + t];             // own elements: no hazard, no sync needed
+    for (int r = 0; r < E; ++r) a[r] = A[r * NT + t];             // own elements: written by this thread
     if (p.o_aligned) {
       store4(p.o_aligned + row, e0, HP, n_el, a[0], a[1], a[2], a[3]);
       store4(p.o_aligned + row, e0 + 4, HP, n_el, a[4], a[5], a[6], a[7]);
@@ -286,56 +305,62 @@ window_fast_kernel(const WinParams p) {
     if (!do_roll && !do_rate) continue;
 
     // ---------------------------------------------------------------- in-chunk suffix scans
-    double c_fv, c_ri;                                            // chunk's first valid value, internal reset sum
+    double c_fv;                                                  // chunk's first valid value
     int c_cn;
     {
-      double ss = 0.0, smn = INF, smx = -INF, srs = 0.0, sfv = 0.0, lv = 0.0;
+      double ss = 0.0, smn = INF, smx = -INF, sd = 0.0, sfv = 0.0, lv = 0.0;
       int scf = 0, scn = 0, foff = 0, lpos = 0;
 #pragma unroll
       for (int r = E - 1; r >= 0; --r) {
         const double v = a[r];
-        const bool nn = v == v;
         if (pmx_isfinite(v)) { ss += v; smn = dmin(smn, v); smx = dmax(smx, v); ++scf; }
-        if (nn) {
-          if (scn > 0) srs += (sfv < v) ? v : 0.0; else { lv = v; lpos = r; }
+        if (v == v) {
+          if (scn > 0) sd += delta_of(sfv, v); else { lv = v; lpos = r; }
           sfv = v; foff = r; ++scn;
         }
         const int si = r * NT + t;
-        S_sum[si] = ss; S_mn[si] = smn; S_mx[si] = smx; S_rs[si] = srs;
+        S_sum[si] = ss; S_mn[si] = smn; S_mx[si] = smx; S_d[si] = sd;
         S_meta[si] = (uint16_t)(scf | (scn << 4) | (((foff - r) & 7) << 8));
       }
-      T_sum[t] = ss; T_mn[t] = smn; T_mx[t] = smx; T_fv[t] = sfv; T_lv[t] = lv; T_ri[t] = srs;
+      T_sum[t] = ss; T_mn[t] = smn; T_mx[t] = smx; T_fv[t] = sfv; T_lv[t] = lv; T_di[t] = sd;
       T_meta[t] = (uint32_t)(scf | (scn << 4) | (foff << 8) | (lpos << 12));
-      c_fv = sfv; c_ri = srs; c_cn = scn;
+      c_fv = sfv; c_cn = scn;
     }
-    __syncthreads();
-    // ---------------------------------------------------------------- junction with the previous valid point
-    double clv = 0.0; int clpos = -1;
-    {
-      const int kmin = t - qa - 2 > 0 ? t - qa - 2 : 0;
-      for (int k = t - 1; k >= kmin; --k) {
-        const uint32_t m = T_meta[k];
-        if ((m >> 4) & 0xf) { clv = T_lv[k]; clpos = k * E + (int)((m >> 12) & 7); break; }
-      }
-    }
-    const double Jc = (c_cn > 0 && clpos >= 0 && c_fv < clv) ? clv : 0.0;
-    T_tr[t] = c_ri + Jc;
     __syncthreads();
 
     // ---------------------------------------------------------------- windows
     if (e0 + E > HP) {
-      double ms = 0.0, mmn = INF, mmx = -INF, mrs = 0.0; int mcf = 0, mcn = 0;
-      for (int k = (t - qa + 1 > 0 ? t - qa + 1 : 0); k < t; ++k) {
-        ms += T_sum[k]; mmn = dmin(mmn, T_mn[k]); mmx = dmax(mmx, T_mx[k]); mrs += T_tr[k];
-        const uint32_t m = T_meta[k]; mcf += m & 0xf; mcn += (m >> 4) & 0xf;
+      // fold the chunk totals between the window start and the own chunk, forming the junction
+      // delta of every non-empty chunk with the last valid value before it
+      double ms = 0.0, mmn = INF, mmx = -INF, md = 0.0; int mcf = 0, mcn = 0;       // chunks t-qa+1 .. t-1
+      double ms2 = 0.0, mmn2 = INF, mmx2 = -INF, md2 = 0.0; int mcf2 = 0, mcn2 = 0;  // chunk t-qa
+      double clv = 0.0; int clpos = -1;                            // last valid value / position before the own chunk
+      if (t - qa - 1 >= 0) {
+        const uint32_t m = T_meta[t - qa - 1];
+        if ((m >> 4) & 0xf) { clv = T_lv[t - qa - 1]; clpos = (t - qa - 1) * E + (int)((m >> 12) & 7); }
       }
-      double ms2 = ms, mmn2 = mmn, mmx2 = mmx, mrs2 = mrs; int mcf2 = mcf, mcn2 = mcn;
       if (t - qa >= 0) {
         const int k = t - qa;
-        ms2 = T_sum[k] + ms; mmn2 = dmin(mmn, T_mn[k]); mmx2 = dmax(mmx, T_mx[k]); mrs2 = T_tr[k] + mrs;
-        const uint32_t m = T_meta[k]; mcf2 += m & 0xf; mcn2 += (m >> 4) & 0xf;
+        const uint32_t m = T_meta[k];
+        ms2 = T_sum[k]; mmn2 = T_mn[k]; mmx2 = T_mx[k]; mcf2 = m & 0xf; mcn2 = (m >> 4) & 0xf;
+        if (mcn2) {
+          md2 = T_di[k] + (clpos >= 0 ? delta_of(T_fv[k], clv) : 0.0);
+          clv = T_lv[k]; clpos = k * E + (int)((m >> 12) & 7);
+        }
       }
-      double ps = 0.0, pmn = INF, pmx = -INF, prs = 0.0, plv = 0.0, pfv = 0.0;
+      for (int k = (t - qa + 1 > 0 ? t - qa + 1 : 0); k < t; ++k) {
+        const uint32_t m = T_meta[k];
+        ms += T_sum[k]; mmn = dmin(mmn, T_mn[k]); mmx = dmax(mmx, T_mx[k]);
+        mcf += m & 0xf; mcn += (m >> 4) & 0xf;
+        if ((m >> 4) & 0xf) {
+          md += T_di[k] + (clpos >= 0 ? delta_of(T_fv[k], clv) : 0.0);
+          clv = T_lv[k]; clpos = k * E + (int)((m >> 12) & 7);
+        }
+      }
+      ms2 += ms; mmn2 = dmin(mmn2, mmn); mmx2 = dmax(mmx2, mmx); md2 += md; mcf2 += mcf; mcn2 += mcn;
+      const double Jc = (c_cn > 0 && clpos >= 0) ? delta_of(c_fv, clv) : 0.0;     // own chunk's junction delta
+
+      double ps = 0.0, pmn = INF, pmx = -INF, pd = 0.0, plv = 0.0;
       int pcf = 0, pcn = 0, plpos = 0, pfpos = 0;
 #pragma unroll 1
       for (int h = 0; h < 2; ++h) {                               // two groups of four outputs (code size)
@@ -343,10 +368,10 @@ window_fast_kernel(const WinParams p) {
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const int r = 4 * h + q;
-          const double v = A[r * NT + t];
+          const double v = h ? a[4 + q] : a[q];
           if (pmx_isfinite(v)) { ps += v; pmn = dmin(pmn, v); pmx = dmax(pmx, v); ++pcf; }
           if (v == v) {
-            if (pcn > 0) prs += (v < plv) ? plv : 0.0; else { pfv = v; pfpos = e0 + r; }
+            if (pcn > 0) pd += delta_of(v, plv); else pfpos = e0 + r;
             plv = v; plpos = e0 + r; ++pcn;
           }
           const bool far = r < qb;                                // window starts one chunk further back
@@ -367,21 +392,21 @@ window_fast_kernel(const WinParams p) {
             ocnt[q] = (int)((sm >> 4) & 0xf) + (far ? mcn2 : mcn) + pcn;
           }
           if (do_rate) {
-            int fpos; double fv, rs;
+            int fpos; double inc;
+            const double pj = pd + (pcn > 0 ? Jc : 0.0);          // own prefix incl. its junction
             if ((sm >> 4) & 0xf) {                                // first chunk part holds a sample
               fpos = lchunk * E + lrow + (int)((sm >> 8) & 7);
-              fv = A[(fpos & 7) * NT + (fpos >> 3)];
-              rs = S_rs[si] + (far ? mrs2 : mrs) + prs + (pcn > 0 ? Jc : 0.0);
+              inc = S_d[si] + (far ? md2 : md) + pj;
             } else {
-              fpos = rate_skip_empty(T_fv, T_ri, T_tr, T_meta, lchunk, t, s_cold + 2 * t);
-              if (fpos >= 0) { fv = s_cold[2 * t]; rs = s_cold[2 * t + 1] + prs + (pcn > 0 ? Jc : 0.0); }
-              else { fpos = pcn > 0 ? pfpos : 0x7fffffff; fv = pfv; rs = prs; }   // window inside the own chunk
+              fpos = rate_skip_empty(T_fv, T_lv, T_di, T_meta, lchunk, t, s_cold + 2 * t);
+              if (fpos >= 0)
+                inc = s_cold[2 * t] + pd + (pcn > 0 ? delta_of(c_fv, s_cold[2 * t + 1]) : 0.0);
+              else { fpos = pcn > 0 ? pfpos : 0x7fffffff; inc = pd; }   // window inside the own chunk
             }
-            const double lv = pcn > 0 ? plv : clv;
             const int lpos = pcn > 0 ? plpos : clpos;
-            double inc = pmx_nan(), rate = pmx_nan();
-            if (lpos > fpos) { inc = (lv - fv) + rs; rate = inc * rdt[lpos - fpos]; }
-            oinc[q] = inc; orate[q] = rate;
+            const bool have = lpos > fpos;
+            oinc[q] = have ? inc : pmx_nan();
+            orate[q] = have ? inc * rdt[have ? lpos - fpos : 0] : pmx_nan();
           }
         }
         const int e = e0 + 4 * h;
@@ -397,13 +422,13 @@ window_fast_kernel(const WinParams p) {
         }
       }
     }
-    __syncthreads();                                              // S/T/A free for the next tile
+    __syncthreads();                                              // S/T free for the next tile
   }
 }
 
 bool aligned32(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 31) == 0; }
 
-template <int NT, bool ALIGN>
+template <int NT, bool ALIGN, int MINB>
 int launch_fast(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
   using TL = FTile<NT>;
   const int out_per_tile = (TL::NE - (p.w - 1) - 3) & ~3;
@@ -418,8 +443,8 @@ int launch_fast(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
   const int64_t grid = p.n_series * p.chunks;
   if (grid > 0x7fffffffLL) return pmx_fail(PMX_E_LIMIT, "window kernel: n_series * chunks exceeds 2^31-1");
   const size_t smem = TL::FIXED + size_t(2) * NT * 8 + size_t(2) * (p.w + 1) * 8 + 16;
-  PMX_CUDA(cudaFuncSetAttribute(window_fast_kernel<NT, ALIGN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  window_fast_kernel<NT, ALIGN><<<(unsigned)grid, NT, smem, st>>>(p);
+  PMX_CUDA(cudaFuncSetAttribute(window_fast_kernel<NT, ALIGN, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  window_fast_kernel<NT, ALIGN, MINB><<<(unsigned)grid, NT, smem, st>>>(p);
   PMX_LAUNCH_CHECK();
   return PMX_OK;
 }
@@ -437,8 +462,14 @@ int launch_window_fast(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
   if (!aligned32(p.o_aligned) || !aligned32(p.o_min) || !aligned32(p.o_max) || !aligned32(p.o_mean) ||
       !aligned32(p.o_inc) || !aligned32(p.o_rate) || (reinterpret_cast<uintptr_t>(p.o_cnt) & 15))
     return 1;
-  if (nt == 128) return launch_fast<128, ALIGN>(ctx, p, st);
-  return launch_fast<256, ALIGN>(ctx, p, st);
+  static int minb = 0;
+  if (!minb) { const char* e = getenv("PMX_FAST_MINB"); minb = e ? atoi(e) : 4; }
+  if (nt == 128) {
+    if (minb == 5) return launch_fast<128, ALIGN, 5>(ctx, p, st);
+    if (minb == 6) return launch_fast<128, ALIGN, 6>(ctx, p, st);
+    return launch_fast<128, ALIGN, 4>(ctx, p, st);
+  }
+  return launch_fast<256, ALIGN, 2>(ctx, p, st);
 }
 
 template int launch_window_fast<true>(const pmx_ctx*, WinParams, cudaStream_t);

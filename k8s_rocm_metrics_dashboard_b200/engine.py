@@ -306,7 +306,7 @@ class Engine:
                 self.ctx, self._ptr(x), S, T, self._ptr(d_seg), n_seg, self._ptr(d_q), n_q, self._ptr(outs["n"]),
                 self._ptr(outs["lo"]), self._ptr(outs["hi"]), self._ptr(outs["x_lo"]), self._ptr(outs["x_hi"]),
                 self._ptr(outs["value"]), self._stream()))
-            self.launches += 2 * _abi.QUANTILE_PASSES + 1
+            self.launches += 3 * _abi.QUANTILE_PASSES - 3 + 1    # hist (two kernels from pass 3 on) + pick + finish
             return outs
         import torch.distributed as dist
         state, hist = buffers if buffers is not None else self.quantile_buffers(n_seg, n_q)
@@ -322,5 +322,5 @@ class Engine:
                                                 self._ptr(outs["n"]), self._ptr(outs["lo"]), self._ptr(outs["hi"]),
                                                 self._ptr(outs["x_lo"]), self._ptr(outs["x_hi"]),
                                                 self._ptr(outs["value"]), self._stream()))
-        self.launches += 2 * _abi.QUANTILE_PASSES + 1
+        self.launches += 3 * _abi.QUANTILE_PASSES - 3 + 1
         return outs
