@@ -29,8 +29,9 @@ extern "C" {
 
 #define PMX_VERSION 100                      /* 0.1.0 */
 #define PMX_STALE_NAN_BITS 0x7FF0000000000002ULL   /* Prometheus staleness marker            */
-#define PMX_QUANTILE_BINS 2048               /* radix-select histograms hold up to 2^11 bins */
-#define PMX_QUANTILE_PASSES 7                /* digits of 11+6+6+11+11+11+8 = 64 key bits    */
+#define PMX_QUANTILE_DIGIT_BITS 11           /* radix-select digit: 2048-bin histograms      */
+#define PMX_QUANTILE_BINS 2048
+#define PMX_QUANTILE_PASSES 6                /* 11+11+11+11+11+9 = 64 key bits               */
 
 typedef enum pmx_status {
   PMX_OK = 0,
@@ -181,8 +182,8 @@ int pmx_where_gt(pmx_ctx* ctx, const double* d_x, int64_t n, double threshold, d
  * rank, extend the prefix).  After the last pass pmx_quantile_finish converts the keys back
  * and interpolates like numpy's _lerp (Series.quantile / np.percentile 'linear').
  * d_hist is uint64 [n_seg * 2*n_q * PMX_QUANTILE_BINS] (pass 0 uses the first n_seg*BINS).
- * Pass 2 keeps the keys that still match a target (17 bits known) in ctx scratch (<= 2^20 per segment) and passes
- * 3-6 read only those; one selection at a time per ctx, passes in order 0..6. */
+ * Pass 2 keeps the keys that still match a target in ctx scratch (<= 2^20 per segment) and passes
+ * 3-5 read only those; one selection at a time per ctx, passes in order 0..5. */
 int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
                       const int32_t* d_seg, int64_t n_seg, int64_t n_q, int pass,
                       const uint64_t* d_state, uint64_t* d_hist, pmx_stream stream);

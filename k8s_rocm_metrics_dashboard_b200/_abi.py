@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(HERE, "libpmx.so")
 
 OK, E_INVALID, E_CUDA, E_VALUE, E_KEY, E_CAPACITY, E_JSON, E_LIMIT = 0, -1, -2, -3, -4, -5, -6, -7
 QUANTILE_BINS = 2048
-QUANTILE_PASSES = 7
+QUANTILE_PASSES = 6
 INT64_MAX = (1 << 63) - 1
 
 

@@ -1,7 +1,7 @@
 // quantile.cu -- K6: exact quantiles by radix select on order-preserving keys.
 //
 // float64 -> uint64 key that sorts like the number (NaN excluded), then PMX_QUANTILE_PASSES
-// passes over digits of 11, 6, 6, 11, 11, 11 and 8 bits, most significant first.  A pass is
+// passes of 11-bit digits, most significant first.  A pass is
 //   hist : per-CTA shared-memory histograms (one per target still being refined) of the digit of
 //          every key that matches the target's prefix, flushed with integer atomics -- so the
 //          global histogram is deterministic and can be all-reduced across ranks as is;
@@ -10,14 +10,9 @@
 // After the last pass every target's prefix IS the key of the wanted order statistic.  Targets
 // per segment: for each q the ranks lo = floor((n-1)q) and hi = min(lo+1, n-1), then numpy's
 // _lerp.  No sample ever moves between GPUs; a pass exchanges 16 KiB per target.
-// Passes 0-2 read every value.  Pass 0 (sign + 10 exponent bits) puts gauge data into one or two
-// bins, which the leader-fold turns into one shared atomic per warp.  Passes 1 and 2 see nearly all
-// values again, now spread over their bins; shared atomics would serialise (2 cycles per lane), so
-// their 6-bit digits are counted with warp ballots instead: six ballots give every lane the set of
-// lanes in "its" two bins, a popcount adds them to warp-private counters, no atomics at all.
-// Pass 2 also copies the keys that still match a target prefix (17 bits known by then) into a
-// per-segment candidate list; passes 3-6 read only that list.  A segment whose list overflows
-// (heavy ties) keeps reading the full data.
+// Passes 0-2 read every value.  Pass 2 also copies the keys that still match a target prefix
+// (22 bits known by then) into a per-segment candidate list; passes 3-5 read only that list.
+// A segment whose list overflows (heavy ties) keeps reading the full data.
 //
 // State per segment (uint64 words): [0] n, [1] reserved, then per target t: [2+2t] prefix,
 // [3+2t] remaining rank inside the prefix bucket.
@@ -36,12 +31,8 @@ __device__ __forceinline__ double key_f64(uint64_t k) {
   const uint64_t b = (k >> 63) ? (k & 0x7fffffffffffffffULL) : ~k;
   return __longlong_as_double((long long)b);
 }
-// digit widths 11,6,6,11,11,11,8; prefix_bits = bits known before the pass
-__host__ __device__ __forceinline__ int digit_bits(int pass) { return pass == 0 ? 11 : pass <= 2 ? 6 : pass <= 5 ? 11 : 8; }
-__host__ __device__ __forceinline__ int prefix_bits(int pass) {
-  return pass == 0 ? 0 : pass == 1 ? 11 : pass == 2 ? 17 : 23 + 11 * (pass - 3);
-}
-__host__ __device__ __forceinline__ int digit_shift(int pass) { return 64 - prefix_bits(pass) - digit_bits(pass); }
+__host__ __device__ __forceinline__ int digit_shift(int pass) { return pass < 5 ? 53 - 11 * pass : 0; }
+__host__ __device__ __forceinline__ int digit_bits(int pass) { return pass < 5 ? 11 : 9; }
 __host__ __device__ __forceinline__ int state_words(int64_t n_q) { return 2 + 4 * (int)n_q; }
 
 // Adds one key per lane to a CTA-private histogram.  All 32 lanes call this together (hit = this
@@ -92,26 +83,13 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
   const int64_t s0 = (int64_t)blockIdx.x * rows_per_cta;
   const int shift = digit_shift(pass);
   const unsigned mask = (1u << digit_bits(pass)) - 1u;
-  const int pshift = pass == 0 ? 0 : 64 - prefix_bits(pass);   // key >> pshift == prefix  (pass >= 1)
+  const int pshift = pass == 0 ? 0 : 64 - 11 * pass;       // key >> pshift == prefix  (pass >= 1)
   const int lane = threadIdx.x & 31;
   const int n_h = pass == 0 ? 1 : n_t;                     // histograms per segment in global memory
   int cur_seg = -1;
 
-  const bool ballot_mode = digit_bits(pass) == 6;          // warp-private counters [warp][u][64]
-  unsigned xmask[5];
-#pragma unroll
-  for (int b = 0; b < 5; ++b) xmask[b] = ((lane >> b) & 1) ? 0u : 0xffffffffu;
   auto flush = [&](int sg) {
     __syncthreads();
-    if (ballot_mode) {
-      for (int i = threadIdx.x; i < n_h * 64; i += blockDim.x) {
-        const int k = i >> 6, bin = i & 63;
-        unsigned c = 0;
-        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) c += sh[w * (MAX_TARGETS * 64) + s_umap[k] * 64 + bin];
-        if (c) atomicAdd(&hist[((size_t)sg * n_h + k) * BINS + bin], (unsigned long long)c);
-      }
-      return;
-    }
     for (int k = 0; k < n_h; ++k) {
       const unsigned int* src = sh + (pass == 0 ? 0 : s_umap[k]) * BINS;
       unsigned long long* dst = hist + ((size_t)sg * n_h + k) * BINS;
@@ -133,7 +111,7 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
       __syncthreads();
       if (threadIdx.x == 0) load_prefixes(state, sw, sg, n_t, pass, s_uprefix, s_umap, &s_nu);
       __syncthreads();
-      for (int i = threadIdx.x; i < (ballot_mode ? (int)(blockDim.x >> 5) * MAX_TARGETS * 64 : s_nu * BINS); i += blockDim.x) sh[i] = 0;
+      for (int i = threadIdx.x; i < s_nu * BINS; i += blockDim.x) sh[i] = 0;
       cur_seg = sg;
       __syncthreads();
     }
@@ -161,21 +139,7 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
         for (int u = 0; u < nu; ++u) hits |= (valid && top == s_uprefix[u]) ? (1u << u) : 0u;
         const unsigned any = __ballot_sync(0xffffffffu, hits != 0);
         if (any == 0) continue;                            // common case from pass 2 on
-        if (ballot_mode) {
-          // lanes whose digit is `lane` (bit 5 clear) / `lane + 32` (bit 5 set): AND of six ballots
-          unsigned mine = any;
-#pragma unroll
-          for (int b = 0; b < 5; ++b) mine &= __ballot_sync(0xffffffffu, (d >> b) & 1) ^ xmask[b];
-          const unsigned b5 = __ballot_sync(0xffffffffu, (d >> 5) & 1);
-          unsigned int* wh = sh + (threadIdx.x >> 5) * (MAX_TARGETS * 64);
-          for (int u = 0; u < nu; ++u) {
-            const unsigned hm = nu == 1 ? any : __ballot_sync(0xffffffffu, (hits >> u) & 1);
-            const unsigned m = mine & hm;
-            if (m) { wh[u * 64 + lane] += __popc(m & ~b5); wh[u * 64 + 32 + lane] += __popc(m & b5); }
-          }
-        } else {
-          for (int u = 0; u < nu; ++u) hist_add(sh + u * BINS, (hits >> u) & 1, d, lane);
-        }
+        for (int u = 0; u < nu; ++u) hist_add(sh + u * BINS, (hits >> u) & 1, d, lane);
         if (mode == 1) {                                   // append to the candidate list, one atomic per warp
           const int leader = __ffs(any) - 1;
           unsigned base = 0;
@@ -209,7 +173,7 @@ cand_hist_kernel(const unsigned long long* __restrict__ cand, const unsigned int
   if (a >= b) return;
   const int shift = digit_shift(pass);
   const unsigned mask = (1u << digit_bits(pass)) - 1u;
-  const int pshift = 64 - prefix_bits(pass);
+  const int pshift = 64 - 11 * pass;
   const int lane = threadIdx.x & 31;
   if (threadIdx.x == 0) load_prefixes(state, sw, sg, n_t, pass, s_uprefix, s_umap, &s_nu);
   __syncthreads();
@@ -356,12 +320,11 @@ int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
     mode = pass == 2 ? 1 : 2;
     if (pass == 2) PMX_CUDA(cudaMemsetAsync(cand_cnt, 0, hdr, st));
   }
-  size_t smem = (size_t)n_h * BINS * sizeof(unsigned int);
-  if (digit_bits(pass) == 6) smem = (size_t)8 * MAX_TARGETS * 64 * sizeof(unsigned int);
+  const size_t smem = (size_t)n_h * BINS * sizeof(unsigned int);
   PMX_CUDA(cudaFuncSetAttribute(hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(MAX_TARGETS * BINS * sizeof(unsigned int))));
   if (mode == 2) {
     PMX_CUDA(cudaFuncSetAttribute(cand_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(MAX_TARGETS * BINS * sizeof(unsigned int))));
-    dim3 grid(8, (unsigned)n_seg);
+    dim3 grid(32, (unsigned)n_seg);
     cand_hist_kernel<<<grid, 256, smem, st>>>(cand, cand_cnt, cap, n_t, pass, d_state, state_words(n_q),
                                             (unsigned long long*)d_hist);
     PMX_LAUNCH_CHECK();

@@ -64,7 +64,7 @@ def combine_group_partials(sm, cnt, mn, mx, group=None):
     return sm, cnt, torch.where(any_, mn, nan), torch.where(any_, mx, nan), mean
 
 
-def distributed_quantiles(hist_fn, pick_fn, finish_fn, n_seg, n_q, group=None, passes=7):
+def distributed_quantiles(hist_fn, pick_fn, finish_fn, n_seg, n_q, group=None, passes=6):
     """The radix-select protocol, independent of where hist/pick run.
 
     hist_fn(pass) -> int64 tensor [n_hist, 2048] of LOCAL counts (n_hist = n_seg for pass 0,

@@ -14,9 +14,8 @@ from k8s_rocm_metrics_dashboard_b200 import sharding, synth
 from oracle import prom_oracle as O
 
 BINS = 2048
-BITS = [11, 6, 6, 11, 11, 11, 8]
-PREFIX = [0, 11, 17, 23, 34, 45, 56]
-SHIFT = [64 - p - b for p, b in zip(PREFIX, BITS)]
+SHIFT = [53, 42, 31, 20, 9, 0]
+BITS = [11, 11, 11, 11, 11, 9]
 
 
 def _free_port():
@@ -41,7 +40,7 @@ class NumpySelect:
             keys = self.keys[g]
             d = ((keys >> np.uint64(SHIFT[p])) & np.uint64((1 << BITS[p]) - 1)).astype(np.int64)
             for t in range(n_h):
-                m = np.ones(len(keys), dtype=bool) if p == 0 else (keys >> np.uint64(64 - PREFIX[p])) == self.prefix[g, t]
+                m = np.ones(len(keys), dtype=bool) if p == 0 else (keys >> np.uint64(64 - 11 * p)) == self.prefix[g, t]
                 h[g * n_h + t] = np.bincount(d[m], minlength=BINS)
         return torch.from_numpy(h)
 
