@@ -26,7 +26,7 @@
 #include "window_common.cuh"
 
 #ifndef PMX_FAST_CTAS_128
-#define PMX_FAST_CTAS_128 4
+#define PMX_FAST_CTAS_128 5
 #endif
 
 namespace pmxw {
@@ -144,8 +144,8 @@ __device__ __noinline__ int rate_skip_empty(const double* T_fv, const double* T_
   return -1;
 }
 
-template <int NT, bool ALIGN, int MINB>
-__global__ void __launch_bounds__(NT, MINB)
+template <int NT, bool ALIGN>
+__global__ void __launch_bounds__(NT, (NT == 256 ? 2 : PMX_FAST_CTAS_128))
 window_fast_kernel(const WinParams p) {
   using TL = FTile<NT>;
   constexpr int NE = TL::NE;
@@ -217,9 +217,9 @@ window_fast_kernel(const WinParams p) {
         const int64_t* gts = p.ts + base + cur;
         const double* gv = p.val + base + cur;
         for (int i = t; i < ns; i += NT) {
-          int64_t d = gts[i] - tbase;                             // saturate: order and lookback tests stay exact
-          d = d > 0x7fffffffLL ? 0x7fffffffLL : (d < -0x40000000LL ? -0x40000000LL : d);
-          s_t[pad8(i)] = (int)d;
+          int d32;                                                // saturate: order and lookback tests stay exact
+          asm("cvt.sat.s32.s64 %0, %1;" : "=r"(d32) : "l"(gts[i] - tbase));
+          s_t[pad8(i)] = d32 < -0x40000000 ? -0x40000000 : d32;
           s_val[pad8(i)] = gv[i];
         }
       }
@@ -329,11 +329,68 @@ window_fast_kernel(const WinParams p) {
     __syncthreads();
 
     // ---------------------------------------------------------------- windows
-    if (e0 + E > HP) {
-      // fold the chunk totals between the window start and the own chunk, forming the junction
-      // delta of every non-empty chunk with the last valid value before it
-      double ms = 0.0, mmn = INF, mmx = -INF, md = 0.0; int mcf = 0, mcn = 0;       // chunks t-qa+1 .. t-1
-      double ms2 = 0.0, mmn2 = INF, mmx2 = -INF, md2 = 0.0; int mcf2 = 0, mcn2 = 0;  // chunk t-qa
+    // Two passes over the thread's 8 outputs, rolling statistics first, increase/rate second:
+    // each pass keeps half of the state in registers (5 CTAs per SM instead of 4).
+    const int kfirst = t - qa + 1 > 0 ? t - qa + 1 : 0;
+    if (do_roll && e0 + E > HP) {
+      double ms = 0.0, mmn = INF, mmx = -INF; int mcf = 0, mcn = 0;                 // chunks t-qa+1 .. t-1
+      for (int k = kfirst; k < t; ++k) {
+        const uint32_t m = T_meta[k];
+        ms += T_sum[k]; mmn = dmin(mmn, T_mn[k]); mmx = dmax(mmx, T_mx[k]);
+        mcf += m & 0xf; mcn += (m >> 4) & 0xf;
+      }
+      double ms2 = ms, mmn2 = mmn, mmx2 = mmx; int mcf2 = mcf, mcn2 = mcn;         // ... plus chunk t-qa
+      if (t - qa >= 0) {
+        const int k = t - qa;
+        const uint32_t m = T_meta[k];
+        ms2 = T_sum[k] + ms; mmn2 = dmin(T_mn[k], mmn); mmx2 = dmax(T_mx[k], mmx);
+        mcf2 += m & 0xf; mcn2 += (m >> 4) & 0xf;
+      }
+      double ps = 0.0, pmn = INF, pmx = -INF; int pcf = 0, pcn = 0;
+#pragma unroll 1
+      for (int h = 0; h < 2; ++h) {                               // two groups of four outputs (code size)
+        double omn[4], omx[4], omean[4]; int ocnt[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int r = 4 * h + q;
+          const double v = h ? a[4 + q] : a[q];
+          if (pmx_isfinite(v)) { ps += v; pmn = dmin(pmn, v); pmx = dmax(pmx, v); ++pcf; }
+          pcn += (v == v) ? 1 : 0;
+          const bool far = r < qb;                                // window starts one chunk further back
+          int lchunk = far ? t - qa - 1 : t - qa;
+          const int lrow = far ? r - qb + E : r - qb;
+          if (lchunk < 0) lchunk = 0;                             // halo points only; result unused
+          const int si = lrow * NT + lchunk;
+          const uint32_t sm = S_meta[si];
+          const double ws = S_sum[si] + (far ? ms2 : ms) + ps;
+          const double wmn = dmin(dmin(S_mn[si], far ? mmn2 : mmn), pmn);
+          const double wmx = dmax(dmax(S_mx[si], far ? mmx2 : mmx), pmx);
+          const int wcf = (int)(sm & 0xf) + (far ? mcf2 : mcf) + pcf;
+          const bool ok = wcf >= need;
+          omean[q] = ok ? ws * rcp[wcf] : pmx_nan();
+          omn[q] = ok ? wmn : pmx_nan();
+          omx[q] = ok ? wmx : pmx_nan();
+          ocnt[q] = (int)((sm >> 4) & 0xf) + (far ? mcn2 : mcn) + pcn;
+        }
+        const int e = e0 + 4 * h;
+        if (e >= HP && e + 3 < n_el) {                            // whole group inside the output range
+          const int64_t o = row + e;
+          if (p.o_min) st4(p.o_min + o, omn[0], omn[1], omn[2], omn[3]);
+          if (p.o_max) st4(p.o_max + o, omx[0], omx[1], omx[2], omx[3]);
+          if (p.o_mean) st4(p.o_mean + o, omean[0], omean[1], omean[2], omean[3]);
+          if (p.o_cnt) *reinterpret_cast<int4*>(p.o_cnt + o) = make_int4(ocnt[0], ocnt[1], ocnt[2], ocnt[3]);
+        } else if (e + 3 >= HP && e < n_el) {                     // tile edge
+          if (p.o_min) store4_edge(p.o_min + row, e, HP, n_el, omn[0], omn[1], omn[2], omn[3]);
+          if (p.o_max) store4_edge(p.o_max + row, e, HP, n_el, omx[0], omx[1], omx[2], omx[3]);
+          if (p.o_mean) store4_edge(p.o_mean + row, e, HP, n_el, omean[0], omean[1], omean[2], omean[3]);
+          store4i(p.o_cnt ? p.o_cnt + row : nullptr, e, HP, n_el, ocnt[0], ocnt[1], ocnt[2], ocnt[3]);
+        }
+      }
+    }
+    if (do_rate && e0 + E > HP) {
+      // fold the delta sums of the chunks between the window start and the own chunk, forming the
+      // junction delta of every non-empty chunk with the last valid value before it
+      double md = 0.0, md2 = 0.0;
       double clv = 0.0; int clpos = -1;                            // last valid value / position before the own chunk
       if (t - qa - 1 >= 0) {
         const uint32_t m = T_meta[t - qa - 1];
@@ -342,83 +399,63 @@ window_fast_kernel(const WinParams p) {
       if (t - qa >= 0) {
         const int k = t - qa;
         const uint32_t m = T_meta[k];
-        ms2 = T_sum[k]; mmn2 = T_mn[k]; mmx2 = T_mx[k]; mcf2 = m & 0xf; mcn2 = (m >> 4) & 0xf;
-        if (mcn2) {
+        if ((m >> 4) & 0xf) {
           md2 = T_di[k] + (clpos >= 0 ? delta_of(T_fv[k], clv) : 0.0);
           clv = T_lv[k]; clpos = k * E + (int)((m >> 12) & 7);
         }
       }
-      for (int k = (t - qa + 1 > 0 ? t - qa + 1 : 0); k < t; ++k) {
+      for (int k = kfirst; k < t; ++k) {
         const uint32_t m = T_meta[k];
-        ms += T_sum[k]; mmn = dmin(mmn, T_mn[k]); mmx = dmax(mmx, T_mx[k]);
-        mcf += m & 0xf; mcn += (m >> 4) & 0xf;
         if ((m >> 4) & 0xf) {
           md += T_di[k] + (clpos >= 0 ? delta_of(T_fv[k], clv) : 0.0);
           clv = T_lv[k]; clpos = k * E + (int)((m >> 12) & 7);
         }
       }
-      ms2 += ms; mmn2 = dmin(mmn2, mmn); mmx2 = dmax(mmx2, mmx); md2 += md; mcf2 += mcf; mcn2 += mcn;
+      md2 += md;
       const double Jc = (c_cn > 0 && clpos >= 0) ? delta_of(c_fv, clv) : 0.0;     // own chunk's junction delta
-
-      double ps = 0.0, pmn = INF, pmx = -INF, pd = 0.0, plv = 0.0;
-      int pcf = 0, pcn = 0, plpos = 0, pfpos = 0;
+      double pd = 0.0, plv = 0.0;
+      int pcn = 0, plpos = 0, pfpos = 0;
 #pragma unroll 1
-      for (int h = 0; h < 2; ++h) {                               // two groups of four outputs (code size)
-        double omn[4], omx[4], omean[4], oinc[4], orate[4]; int ocnt[4];
+      for (int h = 0; h < 2; ++h) {
+        double oinc[4], orate[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const int r = 4 * h + q;
           const double v = h ? a[4 + q] : a[q];
-          if (pmx_isfinite(v)) { ps += v; pmn = dmin(pmn, v); pmx = dmax(pmx, v); ++pcf; }
           if (v == v) {
             if (pcn > 0) pd += delta_of(v, plv); else pfpos = e0 + r;
             plv = v; plpos = e0 + r; ++pcn;
           }
-          const bool far = r < qb;                                // window starts one chunk further back
+          const bool far = r < qb;
           int lchunk = far ? t - qa - 1 : t - qa;
           const int lrow = far ? r - qb + E : r - qb;
-          if (lchunk < 0) lchunk = 0;                             // halo points only; result unused
+          if (lchunk < 0) lchunk = 0;
           const int si = lrow * NT + lchunk;
           const uint32_t sm = S_meta[si];
-          if (do_roll) {
-            const double ws = S_sum[si] + (far ? ms2 : ms) + ps;
-            const double wmn = dmin(dmin(S_mn[si], far ? mmn2 : mmn), pmn);
-            const double wmx = dmax(dmax(S_mx[si], far ? mmx2 : mmx), pmx);
-            const int wcf = (int)(sm & 0xf) + (far ? mcf2 : mcf) + pcf;
-            const bool ok = wcf >= need;
-            omean[q] = ok ? ws * rcp[wcf] : pmx_nan();
-            omn[q] = ok ? wmn : pmx_nan();
-            omx[q] = ok ? wmx : pmx_nan();
-            ocnt[q] = (int)((sm >> 4) & 0xf) + (far ? mcn2 : mcn) + pcn;
+          int fpos; double inc;
+          const double pj = pd + (pcn > 0 ? Jc : 0.0);            // own prefix incl. its junction
+          if ((sm >> 4) & 0xf) {                                  // first chunk part holds a sample
+            fpos = lchunk * E + lrow + (int)((sm >> 8) & 7);
+            inc = S_d[si] + (far ? md2 : md) + pj;
+          } else {
+            fpos = rate_skip_empty(T_fv, T_lv, T_di, T_meta, lchunk, t, s_cold + 2 * t);
+            if (fpos >= 0)
+              inc = s_cold[2 * t] + pd + (pcn > 0 ? delta_of(c_fv, s_cold[2 * t + 1]) : 0.0);
+            else { fpos = pcn > 0 ? pfpos : 0x7fffffff; inc = pd; }     // window inside the own chunk
           }
-          if (do_rate) {
-            int fpos; double inc;
-            const double pj = pd + (pcn > 0 ? Jc : 0.0);          // own prefix incl. its junction
-            if ((sm >> 4) & 0xf) {                                // first chunk part holds a sample
-              fpos = lchunk * E + lrow + (int)((sm >> 8) & 7);
-              inc = S_d[si] + (far ? md2 : md) + pj;
-            } else {
-              fpos = rate_skip_empty(T_fv, T_lv, T_di, T_meta, lchunk, t, s_cold + 2 * t);
-              if (fpos >= 0)
-                inc = s_cold[2 * t] + pd + (pcn > 0 ? delta_of(c_fv, s_cold[2 * t + 1]) : 0.0);
-              else { fpos = pcn > 0 ? pfpos : 0x7fffffff; inc = pd; }   // window inside the own chunk
-            }
-            const int lpos = pcn > 0 ? plpos : clpos;
-            const bool have = lpos > fpos;
-            oinc[q] = have ? inc : pmx_nan();
-            orate[q] = have ? inc * rdt[have ? lpos - fpos : 0] : pmx_nan();
-          }
+          const int lpos = pcn > 0 ? plpos : clpos;
+          const bool have = lpos > fpos;
+          oinc[q] = have ? inc : pmx_nan();
+          orate[q] = have ? inc * rdt[have ? lpos - fpos : 0] : pmx_nan();
         }
         const int e = e0 + 4 * h;
-        if (do_roll) {
-          store4(p.o_min ? p.o_min + row : nullptr, e, HP, n_el, omn[0], omn[1], omn[2], omn[3]);
-          store4(p.o_max ? p.o_max + row : nullptr, e, HP, n_el, omx[0], omx[1], omx[2], omx[3]);
-          store4(p.o_mean ? p.o_mean + row : nullptr, e, HP, n_el, omean[0], omean[1], omean[2], omean[3]);
-          store4i(p.o_cnt ? p.o_cnt + row : nullptr, e, HP, n_el, ocnt[0], ocnt[1], ocnt[2], ocnt[3]);
-        }
-        if (do_rate) {
-          store4(p.o_inc ? p.o_inc + row : nullptr, e, HP, n_el, oinc[0], oinc[1], oinc[2], oinc[3]);
-          store4(p.o_rate ? p.o_rate + row : nullptr, e, HP, n_el, orate[0], orate[1], orate[2], orate[3]);
+        if (e >= HP && e + 3 < n_el) {
+          const int64_t o = row + e;
+          if (p.o_inc) st4(p.o_inc + o, oinc[0], oinc[1], oinc[2], oinc[3]);
+          if (p.o_rate) st4(p.o_rate + o, orate[0], orate[1], orate[2], orate[3]);
+        } else if (e + 3 >= HP && e < n_el) {
+          if (p.o_inc) store4_edge(p.o_inc + row, e, HP, n_el, oinc[0], oinc[1], oinc[2], oinc[3]);
+          if (p.o_rate) store4_edge(p.o_rate + row, e, HP, n_el, orate[0], orate[1], orate[2], orate[3]);
         }
       }
     }
@@ -428,12 +465,14 @@ window_fast_kernel(const WinParams p) {
 
 bool aligned32(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 31) == 0; }
 
-template <int NT, bool ALIGN, int MINB>
+template <int NT, bool ALIGN>
 int launch_fast(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
   using TL = FTile<NT>;
   const int out_per_tile = (TL::NE - (p.w - 1) - 3) & ~3;
   const int64_t tiles = (p.n_steps + out_per_tile - 1) / out_per_tile;
-  const int64_t target = (int64_t)ctx->sm_count * 16;
+  static int tmul = 0;
+  if (!tmul) { const char* e = getenv("PMX_FAST_TARGET_MUL"); tmul = e ? atoi(e) : 16; }
+  const int64_t target = (int64_t)ctx->sm_count * tmul;
   int64_t chunks = (target + p.n_series - 1) / p.n_series;
   if (chunks > tiles) chunks = tiles;
   if (chunks < 1) chunks = 1;
@@ -443,8 +482,8 @@ int launch_fast(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
   const int64_t grid = p.n_series * p.chunks;
   if (grid > 0x7fffffffLL) return pmx_fail(PMX_E_LIMIT, "window kernel: n_series * chunks exceeds 2^31-1");
   const size_t smem = TL::FIXED + size_t(2) * NT * 8 + size_t(2) * (p.w + 1) * 8 + 16;
-  PMX_CUDA(cudaFuncSetAttribute(window_fast_kernel<NT, ALIGN, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  window_fast_kernel<NT, ALIGN, MINB><<<(unsigned)grid, NT, smem, st>>>(p);
+  PMX_CUDA(cudaFuncSetAttribute(window_fast_kernel<NT, ALIGN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  window_fast_kernel<NT, ALIGN><<<(unsigned)grid, NT, smem, st>>>(p);
   PMX_LAUNCH_CHECK();
   return PMX_OK;
 }
@@ -462,14 +501,8 @@ int launch_window_fast(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
   if (!aligned32(p.o_aligned) || !aligned32(p.o_min) || !aligned32(p.o_max) || !aligned32(p.o_mean) ||
       !aligned32(p.o_inc) || !aligned32(p.o_rate) || (reinterpret_cast<uintptr_t>(p.o_cnt) & 15))
     return 1;
-  static int minb = 0;
-  if (!minb) { const char* e = getenv("PMX_FAST_MINB"); minb = e ? atoi(e) : 4; }
-  if (nt == 128) {
-    if (minb == 5) return launch_fast<128, ALIGN, 5>(ctx, p, st);
-    if (minb == 6) return launch_fast<128, ALIGN, 6>(ctx, p, st);
-    return launch_fast<128, ALIGN, 4>(ctx, p, st);
-  }
-  return launch_fast<256, ALIGN, 2>(ctx, p, st);
+  if (nt == 128) return launch_fast<128, ALIGN>(ctx, p, st);
+  return launch_fast<256, ALIGN>(ctx, p, st);
 }
 
 template int launch_window_fast<true>(const pmx_ctx*, WinParams, cudaStream_t);
