@@ -192,7 +192,7 @@ window_fast_kernel(const WinParams p) {
     rdt[k] = k ? 1000.0 / (double)((int64_t)k * p.step_ms) : 0.0;
   }
 
-  int64_t base = 0, len = 0, cur = 0;
+  int64_t base = 0, len = 0, cursor = -1;
   if (ALIGN) { base = p.off[s]; len = p.off[s + 1] - base; }
   bool first = true;
   const int e0 = t * E;
@@ -203,101 +203,141 @@ window_fast_kernel(const WinParams p) {
     const int n_el = HP + n_out;
     const int64_t row = s * p.n_steps + j0;                       // multiple of 4
 
+    double a[E];
     if (ALIGN) {
       const int elo = j0 < 0 ? (int)(-j0) : 0;                    // first element with a grid point
       const int64_t tbase = p.start_ms + j0 * p.step_ms;          // grid time of tile element 0
       if (first) {
-        cur = floor_global(p.ts + base, len, tbase + (int64_t)elo * p.step_ms);
-        if (cur < 0) cur = 0;
+        cursor = floor_global(p.ts + base, len, tbase + (int64_t)elo * p.step_ms);
         first = false;
       }
-      const int64_t rem = len - cur;
-      const int ns = (int)(rem < TL::NS ? rem : TL::NS);
+      // cursor = index of the last sample at or before the tile's first grid point, or -1
+      const int64_t cur = cursor > 0 ? cursor : 0;
+      const int shift = cursor < 0 ? 1 : 0;
+      // ---- regular tile: exactly one sample per grid step.  Every thread fetches "its" nine
+      // timestamps and eight values straight from global memory (full sectors, no staging) and
+      // checks ts[k] <= g < ts[k+1] for each of its points; one barrier votes.
+      bool ok = true;
       {
-        const int64_t* gts = p.ts + base + cur;
-        const double* gv = p.val + base + cur;
-        for (int i = t; i < ns; i += NT) {
-          int d32;                                                // saturate: order and lookback tests stay exact
-          asm("cvt.sat.s32.s64 %0, %1;" : "=r"(d32) : "l"(gts[i] - tbase));
-          s_t[pad8(i)] = d32 < -0x40000000 ? -0x40000000 : d32;
-          s_val[pad8(i)] = gv[i];
+        const int64_t k0 = cur + (e0 - elo - shift);
+        const int64_t* gts = p.ts + base;
+        const double* gv = p.val + base;
+        int64_t tk[E + 1]; double vk[E];
+#pragma unroll
+        for (int r = 0; r <= E; ++r) {
+          const int64_t k = k0 + r;
+          tk[r] = (k >= 0 && k < len) ? gts[k] : (k < 0 ? (int64_t)0x8000000000000000LL : 0x7fffffffffffffffLL);
         }
-      }
-      __syncthreads();
-      const int ghi = (n_el - 1) * step;
-      const bool covered = (cur + ns >= len) || (ns > 0 && s_t[pad8(ns - 1)] > ghi);
-      const int e_cur = OUT;                                      // its floor seeds the next tile
-      if (!covered) {
-#pragma unroll 1
+#pragma unroll
         for (int r = 0; r < E; ++r) {
+          const int64_t k = k0 + r;
+          vk[r] = (k >= 0 && k < len) ? gv[k] : pmx_nan();
+        }
+        int64_t g = tbase + (int64_t)e0 * p.step_ms;
+#pragma unroll
+        for (int r = 0; r < E; ++r, g += p.step_ms) {
           const int e = e0 + r;
           double v = pmx_nan();
           if (e >= elo && e < n_el) {
-            int64_t idx;
-            v = align_one_global(p.ts + base, p.val + base, cur, len, tbase + (int64_t)e * p.step_ms,
-                                 p.lookback_ms, &idx);
-            if (e == e_cur) *s_cursor = idx > cur ? idx : cur;
+            ok = ok && tk[r] <= g && tk[r + 1] > g;
+            if (k0 + r >= 0 && g - tk[r] < p.lookback_ms &&
+                (unsigned long long)__double_as_longlong(vk[r]) != PMX_STALE_NAN_BITS)
+              v = vk[r];
           }
-          A[r * NT + t] = v;
+          a[r] = v;
         }
+      }
+      if (__syncthreads_and(ok)) {
+        cursor = cur + (OUT - elo - shift);
       } else {
-        // guess: one sample per grid step; staged sample 0 is the floor of element elo (or the
-        // sample after it when the series starts later)
-        const int shift = (ns > 0 && s_t[0] > elo * step) ? 1 : 0;
-        int idx = e0 - elo - shift;
-        if (idx > ns - 1) idx = ns - 1;
+        // ---- general tile: stage the samples that can serve it, search/walk per point
+        const int64_t rem = len - cur;
+        const int ns = (int)(rem < TL::NS ? rem : TL::NS);
         {
-          const int ef = e0 > elo ? e0 : elo;                     // first element this thread aligns
-          const int g = ef * step;
-          if (idx < 0) idx = (ns > 0 && s_t[0] <= g) ? floor_staged(s_t, 0, ns, g) : -1;
-          else if (!(s_t[pad8(idx)] <= g && (idx + 1 >= ns || s_t[pad8(idx + 1)] > g))) idx = floor_staged(s_t, 0, ns, g);
-        }
-#pragma unroll 2
-        for (int r = 0; r < E; ++r) {
-          const int e = e0 + r;
-          const int g = e * step;
-          double v = pmx_nan();
-          if (e >= elo && e < n_el) {
-            if (idx + 1 < ns && s_t[pad8(idx + 1)] <= g) {
-              ++idx;
-              if (idx + 1 < ns && s_t[pad8(idx + 1)] <= g) idx = floor_staged(s_t, idx + 1, ns, g);
-            }
-            if (idx >= 0) {
-              const double sample = s_val[pad8(idx)];
-              if (g - s_t[pad8(idx)] < lookback &&
-                  (unsigned long long)__double_as_longlong(sample) != PMX_STALE_NAN_BITS)
-                v = sample;
-            }
-            if (e == e_cur) *s_cursor = cur + (idx > 0 ? idx : 0);
+          const int64_t* gts = p.ts + base + cur;
+          const double* gv = p.val + base + cur;
+          for (int i = t; i < ns; i += NT) {
+            int d32;                                              // saturate: order and lookback tests stay exact
+            asm("cvt.sat.s32.s64 %0, %1;" : "=r"(d32) : "l"(gts[i] - tbase));
+            s_t[pad8(i)] = d32 < -0x40000000 ? -0x40000000 : d32;
+            s_val[pad8(i)] = gv[i];
           }
-          A[r * NT + t] = v;
         }
+        __syncthreads();
+        const int ghi = (n_el - 1) * step;
+        const bool covered = (cur + ns >= len) || (ns > 0 && s_t[pad8(ns - 1)] > ghi);
+        const int e_cur = OUT;                                    // its floor seeds the next tile
+        if (!covered) {
+#pragma unroll 1
+          for (int r = 0; r < E; ++r) {
+            const int e = e0 + r;
+            double v = pmx_nan();
+            if (e >= elo && e < n_el) {
+              int64_t idx;
+              v = align_one_global(p.ts + base, p.val + base, cur, len, tbase + (int64_t)e * p.step_ms,
+                                   p.lookback_ms, &idx);
+              if (e == e_cur) *s_cursor = idx;
+            }
+            A[r * NT + t] = v;
+          }
+        } else {
+          // guess: one sample per grid step; staged sample 0 is the floor of element elo (or the
+          // sample after it when the series starts later)
+          int idx = e0 - elo - shift;
+          if (idx > ns - 1) idx = ns - 1;
+          {
+            const int ef = e0 > elo ? e0 : elo;                   // first element this thread aligns
+            const int g = ef * step;
+            if (idx < 0) idx = (ns > 0 && s_t[0] <= g) ? floor_staged(s_t, 0, ns, g) : -1;
+            else if (!(s_t[pad8(idx)] <= g && (idx + 1 >= ns || s_t[pad8(idx + 1)] > g))) idx = floor_staged(s_t, 0, ns, g);
+          }
+#pragma unroll 1
+          for (int r = 0; r < E; ++r) {
+            const int e = e0 + r;
+            const int g = e * step;
+            double v = pmx_nan();
+            if (e >= elo && e < n_el) {
+              if (idx + 1 < ns && s_t[pad8(idx + 1)] <= g) {
+                ++idx;
+                if (idx + 1 < ns && s_t[pad8(idx + 1)] <= g) idx = floor_staged(s_t, idx + 1, ns, g);
+              }
+              if (idx >= 0) {
+                const double sample = s_val[pad8(idx)];
+                if (g - s_t[pad8(idx)] < lookback &&
+                    (unsigned long long)__double_as_longlong(sample) != PMX_STALE_NAN_BITS)
+                  v = sample;
+              }
+              if (e == e_cur) *s_cursor = idx >= 0 ? cur + idx : -1;
+            }
+            A[r * NT + t] = v;
+          }
+        }
+        __syncthreads();                                          // staging dead, cursor visible
+        cursor = *s_cursor;
+#pragma unroll
+        for (int r = 0; r < E; ++r) a[r] = A[r * NT + t];         // own elements: written by this thread
       }
-      __syncthreads();                                            // staging dead, cursor visible
-      cur = *s_cursor;
       if (jt + OUT < c1) {                                        // pull the next tile's samples towards L2
-        const int64_t nrem = len - cur;
+        const int64_t ncur = cursor > 0 ? cursor : 0;
+        const int64_t nrem = len - ncur;
         const int lines = (int)(((nrem < TL::NS ? nrem : TL::NS) * 8 + 127) >> 7);
         if (t < lines) {
-          asm volatile("prefetch.global.L2 [%0];" ::"l"(p.ts + base + cur + t * 16));
-          asm volatile("prefetch.global.L2 [%0];" ::"l"(p.val + base + cur + t * 16));
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(p.ts + base + ncur + t * 16));
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(p.val + base + ncur + t * 16));
         }
       }
     } else {
-      const double* xr = p.x + s * p.n_steps;
-      for (int i = t; i < n_el; i += NT) {
-        const int64_t j = j0 + i;
-        s_val[pad8(i)] = j >= 0 ? xr[j] : pmx_nan();
-      }
-      __syncthreads();
+      // dense input: every thread reads its own eight points (256-bit loads when the row allows)
+      const double* xr = p.x + row;
+      if (e0 + E <= n_el && j0 + e0 >= 0 && (reinterpret_cast<uintptr_t>(xr) & 31) == 0) {
+        asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a[0]), "=d"(a[1]), "=d"(a[2]), "=d"(a[3]) : "l"(xr + e0));
+        asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a[4]), "=d"(a[5]), "=d"(a[6]), "=d"(a[7]) : "l"(xr + e0 + 4));
+      } else {
 #pragma unroll
-      for (int r = 0; r < E; ++r) A[r * NT + t] = (e0 + r < n_el) ? s_val[pad8(e0 + r)] : pmx_nan();
-      __syncthreads();
+        for (int r = 0; r < E; ++r) a[r] = (e0 + r < n_el && j0 + e0 + r >= 0) ? xr[e0 + r] : pmx_nan();
+      }
     }
 
-    double a[E];
-#pragma unroll
-    for (int r = 0; r < E; ++r) a[r] = A[r * NT + t];             // own elements: written by this thread
     if (p.o_aligned) {
       store4(p.o_aligned + row, e0, HP, n_el, a[0], a[1], a[2], a[3]);
       store4(p.o_aligned + row, e0 + 4, HP, n_el, a[4], a[5], a[6], a[7]);
