@@ -76,7 +76,7 @@ def main():
     rec("K5 group reduce per metric", N, 8, timeit(lambda: eng.group_reduce(al, None, 12, perm_goff=pg)))
     rec("K5 group reduce per step [12,T]", N, 8, timeit(lambda: eng.group_reduce(al, None, 12, per_step=True, perm_goff=pg)))
     seg = torch.as_tensor(gid, device=dev)
-    rec("K6 quantiles p50/p95/p99 x12", N, 24, timeit(lambda: eng.quantiles(al, seg, 12, [0.5, 0.95, 0.99])),
+    rec("K6 quantiles p50/p95/p99 x12", N, 24, timeit(lambda: eng.quantiles(al, seg, 12, [0.5, 0.95, 0.99], row_order=pg[0])),
         "3 full passes + candidate lists")
     # config 4: all counters with resets
     ts4, val4, off4 = synth.dense_device(S, T, 12, seed=2, all_counters=True, reset_prob=1e-3, nan_frac=0.0, device=dev)

@@ -182,10 +182,14 @@ int pmx_where_gt(pmx_ctx* ctx, const double* d_x, int64_t n, double threshold, d
  * rank, extend the prefix).  After the last pass pmx_quantile_finish converts the keys back
  * and interpolates like numpy's _lerp (Series.quantile / np.percentile 'linear').
  * d_hist is uint64 [n_seg * 2*n_q * PMX_QUANTILE_BINS] (pass 0 uses the first n_seg*BINS).
+ * d_row_order (optional, n_rows entries): the rows to visit, grouped by segment -- the d_perm of
+ * pmx_group_index serves; a CTA then switches its private histograms rarely.  NULL = all rows in
+ * storage order.
  * Pass 2 keeps the keys that still match a target in ctx scratch (<= 2^20 per segment) and passes
  * 3-5 read only those; one selection at a time per ctx, passes in order 0..5. */
 int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
-                      const int32_t* d_seg, int64_t n_seg, int64_t n_q, int pass,
+                      const int32_t* d_seg, int64_t n_seg,
+                      const int32_t* d_row_order, int64_t n_rows, int64_t n_q, int pass,
                       const uint64_t* d_state, uint64_t* d_hist, pmx_stream stream);
 int pmx_quantile_pick(pmx_ctx* ctx, const uint64_t* d_hist, int64_t n_seg, const double* d_q,
                       int64_t n_q, int pass, uint64_t* d_state, pmx_stream stream);
@@ -194,7 +198,8 @@ int pmx_quantile_finish(pmx_ctx* ctx, const uint64_t* d_state, int64_t n_seg, co
                         double* d_x_lo, double* d_x_hi, double* d_value, pmx_stream stream);
 /* Single-GPU convenience: all passes back to back (no collective); hist/state in ctx scratch. */
 int pmx_quantile_select(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
-                        const int32_t* d_seg, int64_t n_seg, const double* d_q, int64_t n_q,
+                        const int32_t* d_seg, int64_t n_seg,
+                        const int32_t* d_row_order, int64_t n_rows, const double* d_q, int64_t n_q,
                         int64_t* d_n, int64_t* d_lo, int64_t* d_hi,
                         double* d_x_lo, double* d_x_hi, double* d_value, pmx_stream stream);
 

@@ -159,8 +159,10 @@ def aggregate_range(body, start_ms, step_ms, n_steps, window_ms, lookback_ms=DEF
     out = eng.fused(ts, val, tok.series_off, start_ms, step_ms, n_steps, w, lookback_ms)
     names = sorted({l.get("__name__", "") for l in labels})
     gid = np.array([names.index(l.get("__name__", "")) for l in labels], dtype=np.int32)
-    sm, cnt, mn, mx, mean = eng.group_reduce(out["aligned"], gid, len(names))
-    qd = eng.quantiles(out["aligned"], gid, len(names), list(quantiles))
+    from .engine import group_index
+    perm_goff = group_index(gid, len(names))
+    sm, cnt, mn, mx, mean = eng.group_reduce(out["aligned"], None, len(names), perm_goff=perm_goff)
+    qd = eng.quantiles(out["aligned"], gid, len(names), list(quantiles), row_order=perm_goff[0])
     host = {k: v.cpu().numpy() for k, v in out.items()}
     summary = {"metric_name": names, "sum": sm.cpu().numpy(), "count": cnt.cpu().numpy(),
                "min": mn.cpu().numpy(), "max": mx.cpu().numpy(), "mean": mean.cpu().numpy()}

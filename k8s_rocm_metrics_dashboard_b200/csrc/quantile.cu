@@ -74,7 +74,8 @@ __device__ __forceinline__ void load_prefixes(const uint64_t* __restrict__ state
 __global__ void __launch_bounds__(256)
 hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __restrict__ seg,
             int n_t, int pass, const uint64_t* __restrict__ state, int sw,
-            unsigned long long* __restrict__ hist, int rows_per_cta, int64_t n_series,
+            unsigned long long* __restrict__ hist, int rows_per_cta, int64_t n_rows,
+            const int32_t* __restrict__ order,
             int mode, unsigned long long* __restrict__ cand, unsigned int* __restrict__ cand_cnt, unsigned cap) {
   extern __shared__ unsigned int sh[];                     // [n_uniq][BINS]
   __shared__ uint64_t s_uprefix[MAX_TARGETS];
@@ -101,8 +102,8 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
   };
 
   for (int r = 0; r < rows_per_cta; ++r) {
-    const int64_t s = s0 + r;
-    if (s >= n_series) break;
+    if (s0 + r >= n_rows) break;
+    const int64_t s = order ? (int64_t)order[s0 + r] : s0 + r;   // rows grouped by segment when given
     const int sg = seg[s];
     if (sg < 0) continue;
     if (mode == 2 && cand_cnt[sg] <= cap) continue;        // complete candidate list: not our job
@@ -118,20 +119,24 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
     const int nu = s_nu;
     const double* xr = x + s * n_steps;
     const bool vec = (reinterpret_cast<uintptr_t>(xr) & 15) == 0;
-    const int64_t n_it = vec ? ((n_steps + 1) >> 1) : n_steps;       // loop trips are warp-uniform
-    for (int64_t j0 = 0; j0 < n_it; j0 += blockDim.x) {
-      const int64_t j = j0 + threadIdx.x;
-      double v0 = __longlong_as_double(0x7FF8000000000000LL), v1 = v0;
-      if (vec) {
-        if (2 * j + 1 < n_steps) { const double2 v = reinterpret_cast<const double2*>(xr)[j]; v0 = v.x; v1 = v.y; }
-        else if (2 * j < n_steps) v0 = xr[2 * j];
-      } else if (j < n_steps) v0 = xr[j];
+    // loop trips are warp-uniform; every lane has four elements in flight per trip
+    const int64_t per_trip = (int64_t)blockDim.x * 4;
+    for (int64_t j0 = 0; j0 < n_steps; j0 += per_trip) {
+      double v[4];
+      const int64_t ja = j0 + 2 * threadIdx.x, jb = ja + 2 * blockDim.x;
+      const double qnan = __longlong_as_double(0x7FF8000000000000LL);
+      if (vec && jb + 1 < n_steps) {
+        const double2 a = *reinterpret_cast<const double2*>(xr + ja);
+        const double2 b = *reinterpret_cast<const double2*>(xr + jb);
+        v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+      } else {
+        v[0] = ja < n_steps ? xr[ja] : qnan; v[1] = ja + 1 < n_steps ? xr[ja + 1] : qnan;
+        v[2] = jb < n_steps ? xr[jb] : qnan; v[3] = jb + 1 < n_steps ? xr[jb + 1] : qnan;
+      }
 #pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        if (half == 1 && !vec) break;
-        const double v = half ? v1 : v0;
-        const bool valid = v == v;
-        const uint64_t key = f64_key(v);
+      for (int i = 0; i < 4; ++i) {
+        const bool valid = v[i] == v[i];
+        const uint64_t key = f64_key(v[i]);
         const unsigned d = (unsigned)(key >> shift) & mask;
         if (pass == 0) { hist_add(sh, valid, d, lane); continue; }
         const uint64_t top = key >> pshift;
@@ -290,8 +295,8 @@ __global__ void finish_kernel(const uint64_t* __restrict__ state, int sw, int64_
 extern "C" {
 
 int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
-                      const int32_t* d_seg, int64_t n_seg, int64_t n_q, int pass,
-                      const uint64_t* d_state, uint64_t* d_hist, pmx_stream stream) {
+                      const int32_t* d_seg, int64_t n_seg, const int32_t* d_row_order, int64_t n_rows,
+                      int64_t n_q, int pass, const uint64_t* d_state, uint64_t* d_hist, pmx_stream stream) {
   PMX_REQUIRE(ctx, "ctx is NULL");
   PMX_REQUIRE(n_series >= 0 && n_steps >= 0 && n_seg >= 0, "bad sizes");
   PMX_REQUIRE(n_q >= 1 && 2 * n_q <= MAX_TARGETS, "n_q must be in [1, 8]");
@@ -330,13 +335,16 @@ int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
     PMX_LAUNCH_CHECK();
   }
   // a CTA sweeps consecutive rows so that a segment's private histogram is flushed rarely
+  if (!d_row_order) n_rows = n_series;
+  PMX_REQUIRE(n_rows >= 0 && n_rows <= n_series, "n_rows out of range");
+  if (n_rows == 0) return PMX_OK;
   int64_t want_ctas = (int64_t)ctx->sm_count * 16;
-  int64_t rows = (n_series + want_ctas - 1) / want_ctas;
+  int64_t rows = (n_rows + want_ctas - 1) / want_ctas;
   if (rows < 1) rows = 1;
-  const int64_t grid = (n_series + rows - 1) / rows;
+  const int64_t grid = (n_rows + rows - 1) / rows;
   hist_kernel<<<(unsigned)grid, 256, smem, st>>>(d_x, n_steps, d_seg, n_t, pass, d_state, state_words(n_q),
-                                                (unsigned long long*)d_hist, (int)rows, n_series, mode, cand,
-                                                cand_cnt, cap);
+                                                (unsigned long long*)d_hist, (int)rows, n_rows, d_row_order, mode,
+                                                cand, cand_cnt, cap);
   PMX_LAUNCH_CHECK();
   return PMX_OK;
 }
@@ -372,7 +380,8 @@ int pmx_quantile_finish(pmx_ctx* ctx, const uint64_t* d_state, int64_t n_seg, co
 }
 
 int pmx_quantile_select(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
-                        const int32_t* d_seg, int64_t n_seg, const double* d_q, int64_t n_q,
+                        const int32_t* d_seg, int64_t n_seg, const int32_t* d_row_order, int64_t n_rows,
+                        const double* d_q, int64_t n_q,
                         int64_t* d_n, int64_t* d_lo, int64_t* d_hi, double* d_x_lo, double* d_x_hi,
                         double* d_value, pmx_stream stream) {
   PMX_REQUIRE(ctx, "ctx is NULL");
@@ -387,7 +396,8 @@ int pmx_quantile_select(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64
   uint64_t* hist = (uint64_t*)(scr + state_bytes);
   PMX_CUDA(cudaMemsetAsync(state, 0, state_bytes, pmx_st(stream)));
   for (int pass = 0; pass < PMX_QUANTILE_PASSES; ++pass) {
-    int rc = pmx_quantile_hist(ctx, d_x, n_series, n_steps, d_seg, n_seg, n_q, pass, state, hist, stream);
+    int rc = pmx_quantile_hist(ctx, d_x, n_series, n_steps, d_seg, n_seg, d_row_order, n_rows, n_q, pass, state, hist,
+                               stream);
     if (rc) return rc;
     rc = pmx_quantile_pick(ctx, hist, n_seg, d_q, n_q, pass, state, stream);
     if (rc) return rc;

@@ -288,14 +288,18 @@ class Engine:
         hist = self._empty((n_seg * 2 * n_q, _abi.QUANTILE_BINS), t.int64)
         return state, hist
 
-    def quantiles(self, x, seg, n_seg, qs, group=None, buffers=None):
+    def quantiles(self, x, seg, n_seg, qs, group=None, buffers=None, row_order=None):
         """Exact quantiles per segment.  x: [S,T] device; seg: int per series (host or device).
         With ``group`` (a torch.distributed process group over NCCL) the histograms of every pass
-        are all-reduced, so the result is the quantile of the union of all ranks' values."""
+        are all-reduced, so the result is the quantile of the union of all ranks' values.
+        ``row_order``: optional int32 device tensor of row indices grouped by segment (the perm of
+        ``group_index``); lets a CTA keep one set of histograms for long runs of rows."""
         t = self.torch
         x = self._dev(x, t.float64)
         S, T = x.shape
         d_seg = self._dev(seg, t.int32)
+        d_ord = self._dev(row_order, t.int32) if row_order is not None else None
+        n_rows = d_ord.numel() if d_ord is not None else 0
         n_q = len(qs)
         d_q = self._dev(np.asarray(qs, dtype=np.float64), t.float64)
         outs = {"n": self._empty((n_seg,), t.int64), "lo": self._empty((n_seg, n_q), t.int64),
@@ -303,7 +307,8 @@ class Engine:
                 "x_hi": self._empty((n_seg, n_q), t.float64), "value": self._empty((n_seg, n_q), t.float64)}
         if group is None:
             _abi.check(self.lib.pmx_quantile_select(
-                self.ctx, self._ptr(x), S, T, self._ptr(d_seg), n_seg, self._ptr(d_q), n_q, self._ptr(outs["n"]),
+                self.ctx, self._ptr(x), S, T, self._ptr(d_seg), n_seg, self._ptr(d_ord), n_rows, self._ptr(d_q), n_q,
+                self._ptr(outs["n"]),
                 self._ptr(outs["lo"]), self._ptr(outs["hi"]), self._ptr(outs["x_lo"]), self._ptr(outs["x_hi"]),
                 self._ptr(outs["value"]), self._stream()))
             self.launches += 3 * _abi.QUANTILE_PASSES - 3 + 1    # hist (two kernels from pass 3 on) + pick + finish
@@ -312,7 +317,8 @@ class Engine:
         state, hist = buffers if buffers is not None else self.quantile_buffers(n_seg, n_q)
         state.zero_()
         for p in range(_abi.QUANTILE_PASSES):
-            _abi.check(self.lib.pmx_quantile_hist(self.ctx, self._ptr(x), S, T, self._ptr(d_seg), n_seg, n_q, p,
+            _abi.check(self.lib.pmx_quantile_hist(self.ctx, self._ptr(x), S, T, self._ptr(d_seg), n_seg,
+                                                  self._ptr(d_ord), n_rows, n_q, p,
                                                   self._ptr(state), self._ptr(hist), self._stream()))
             n_h = n_seg * (1 if p == 0 else 2 * n_q)
             dist.all_reduce(hist[:n_h], op=dist.ReduceOp.SUM, group=group)

@@ -104,10 +104,10 @@ class ShardedEngine:
             if key not in self._qbuf:
                 self._qbuf[key] = eng.quantile_buffers(n_seg, len(qs))
             q = eng.quantiles(out["aligned"], seg, n_seg, list(qs), group=self.group or _world_group(),
-                              buffers=self._qbuf[key])
+                              buffers=self._qbuf[key], row_order=perm_goff[0])
         else:
             summary = combine_group_partials(sm, cnt, mn, mx, None)
-            q = eng.quantiles(out["aligned"], seg, n_seg, list(qs))
+            q = eng.quantiles(out["aligned"], seg, n_seg, list(qs), row_order=perm_goff[0])
         return out, summary, q
 
 

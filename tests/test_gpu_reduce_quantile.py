@@ -48,7 +48,13 @@ def test_group_reduce_per_step_is_sequential_like_pandas(eng):
 
 
 def _check_quantiles(eng, x, seg, n_seg, qs):
-    out = eng.quantiles(x, seg, n_seg, qs)
+    from k8s_rocm_metrics_dashboard_b200 import group_index
+    _check_quantiles_1(eng, x, seg, n_seg, qs, None)                                   # rows in storage order
+    _check_quantiles_1(eng, x, seg, n_seg, qs, group_index(np.asarray(seg), n_seg)[0])  # rows grouped by segment
+
+
+def _check_quantiles_1(eng, x, seg, n_seg, qs, order):
+    out = eng.quantiles(x, seg, n_seg, qs, row_order=order)
     for g in range(n_seg):
         o = O.quantiles(x[np.asarray(seg) == g], qs)
         assert int(_np(out["n"])[g]) == o["n"]
@@ -96,3 +102,11 @@ def test_quantiles_candidate_list_overflow_falls_back_to_full_passes(eng):
     seg = np.array([0] * 320 + [1] * 8, dtype=np.int32)
     _check_quantiles(eng, z, seg, 2, [0.5, 0.95, 0.99])
     _check_quantiles(eng, z, seg, 2, [0.001, 0.999])
+
+
+def test_quantiles_many_segments_use_row_major_schedule(eng):
+    """> 256 segments: CTAs sweep consecutive rows and switch histograms (one series per segment)."""
+    rng = np.random.default_rng(12)
+    x = rng.normal(size=(300, 257)); x[rng.random(x.shape) < 0.1] = np.nan
+    seg = np.arange(300, dtype=np.int32)
+    _check_quantiles(eng, x, seg, 300, [0.5, 0.9])
