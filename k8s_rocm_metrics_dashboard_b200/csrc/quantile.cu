@@ -22,6 +22,11 @@ namespace {
 
 constexpr int BINS = PMX_QUANTILE_BINS;
 constexpr int MAX_TARGETS = 16;
+#ifndef PMX_HIST_SMEM_LANES
+#define PMX_HIST_SMEM_LANES 8       // of every 8 lanes, how many keep their increment in shared memory.
+                                    // 8 = all: sending 5 of 8 to the L2 atomic units measured 374 us vs 225 us
+                                    // for the all-match pass of config 2 (2048 hot addresses per segment)
+#endif
 
 __device__ __forceinline__ uint64_t f64_key(double v) {
   const uint64_t b = (uint64_t)__double_as_longlong(v);
@@ -39,7 +44,8 @@ __host__ __device__ __forceinline__ int state_words(int64_t n_q) { return 2 + 4 
 // lane contributes).  Lanes that fall into the same bin as the current leader are folded into one
 // shared atomic (two rounds: gauge data puts a whole warp into one or two bins in the first
 // pass); what is left after that is spread over many bins and goes in lane by lane.
-__device__ __forceinline__ void hist_add(unsigned int* h, bool hit, unsigned d, int lane) {
+__device__ __forceinline__ void hist_add(unsigned int* h, bool hit, unsigned d, int lane,
+                                         unsigned long long* g = nullptr) {
   unsigned todo = __ballot_sync(0xffffffffu, hit);
 #pragma unroll
   for (int round = 0; round < 2; ++round) {
@@ -50,19 +56,27 @@ __device__ __forceinline__ void hist_add(unsigned int* h, bool hit, unsigned d, 
     if (lane == leader) atomicAdd(&h[dl], (unsigned)__popc(peers));
     todo &= ~peers;
   }
-  if ((todo >> lane) & 1) atomicAdd(&h[d], 1u);
+  // spread regime: shared atomics retire about one lane every two cycles per SM.  Optionally part
+  // of the lanes can send their increment to the L2 atomic units instead (PMX_HIST_SMEM_LANES < 8)
+  if ((todo >> lane) & 1) {
+    if (g != nullptr && (lane & 7) >= PMX_HIST_SMEM_LANES) atomicAdd(&g[d], 1ULL);
+    else atomicAdd(&h[d], 1u);
+  }
 }
 
 // distinct prefixes of a segment's targets (lo/hi ranks and nearby quantiles usually share one)
+// s_urep[u] = first target that carries distinct prefix u: the kernels accumulate into that
+// target's global histogram only; hist_broadcast_kernel copies it to the other targets of u.
 __device__ __forceinline__ void load_prefixes(const uint64_t* __restrict__ state, int sw, int sg, int n_t,
-                                              int pass, uint64_t* s_uprefix, int* s_umap, int* s_nu) {
+                                              int pass, uint64_t* s_uprefix, int* s_umap, int* s_urep,
+                                              int* s_nu) {
   int nu = 0;
-  if (pass == 0) nu = 1;
+  if (pass == 0) { nu = 1; s_urep[0] = 0; }
   else for (int k = 0; k < n_t; ++k) {
     const uint64_t pf = state[(size_t)sg * sw + 2 + 2 * k];
     int u = 0;
     while (u < nu && s_uprefix[u] != pf) ++u;
-    if (u == nu) s_uprefix[nu++] = pf;
+    if (u == nu) { s_uprefix[nu] = pf; s_urep[nu] = k; ++nu; }
     s_umap[k] = u;
   }
   *s_nu = nu;
@@ -80,7 +94,9 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
   extern __shared__ unsigned int sh[];                     // [n_uniq][BINS]
   __shared__ uint64_t s_uprefix[MAX_TARGETS];
   __shared__ int s_umap[MAX_TARGETS];
+  __shared__ int s_urep[MAX_TARGETS];
   __shared__ int s_nu;
+  __shared__ unsigned int s_bitmap[BINS / 32];             // previous digits carried by some target prefix
   const int64_t s0 = (int64_t)blockIdx.x * rows_per_cta;
   const int shift = digit_shift(pass);
   const unsigned mask = (1u << digit_bits(pass)) - 1u;
@@ -91,9 +107,9 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
 
   auto flush = [&](int sg) {
     __syncthreads();
-    for (int k = 0; k < n_h; ++k) {
-      const unsigned int* src = sh + (pass == 0 ? 0 : s_umap[k]) * BINS;
-      unsigned long long* dst = hist + ((size_t)sg * n_h + k) * BINS;
+    for (int u = 0; u < s_nu; ++u) {
+      const unsigned int* src = sh + u * BINS;
+      unsigned long long* dst = hist + ((size_t)sg * n_h + s_urep[u]) * BINS;
       for (int i = threadIdx.x; i < BINS; i += blockDim.x) {
         const unsigned c = src[i];
         if (c) atomicAdd(&dst[i], (unsigned long long)c);
@@ -110,8 +126,13 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
     if (sg != cur_seg) {                                   // flush, switch segment
       if (cur_seg >= 0) flush(cur_seg);
       __syncthreads();
-      if (threadIdx.x == 0) load_prefixes(state, sw, sg, n_t, pass, s_uprefix, s_umap, &s_nu);
+      if (threadIdx.x < BINS / 32) s_bitmap[threadIdx.x] = 0;
+      if (threadIdx.x == 0) load_prefixes(state, sw, sg, n_t, pass, s_uprefix, s_umap, s_urep, &s_nu);
       __syncthreads();
+      if (pass > 0 && threadIdx.x < s_nu) {
+        const unsigned pd = (unsigned)s_uprefix[threadIdx.x] & (BINS - 1);
+        atomicOr(&s_bitmap[pd >> 5], 1u << (pd & 31));
+      }
       for (int i = threadIdx.x; i < s_nu * BINS; i += blockDim.x) sh[i] = 0;
       cur_seg = sg;
       __syncthreads();
@@ -138,13 +159,18 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
         const bool valid = v[i] == v[i];
         const uint64_t key = f64_key(v[i]);
         const unsigned d = (unsigned)(key >> shift) & mask;
-        if (pass == 0) { hist_add(sh, valid, d, lane); continue; }
+        if (pass == 0) { hist_add(sh, valid, d, lane, hist + (size_t)sg * BINS); continue; }
         const uint64_t top = key >> pshift;
+        // cheap filter first: does any target prefix end in this key's previous digit?
+        const unsigned pdig = (unsigned)top & (BINS - 1);
+        const bool maybe = valid && (pass < 2 || ((s_bitmap[pdig >> 5] >> (pdig & 31)) & 1));
+        if (__ballot_sync(0xffffffffu, maybe) == 0) continue;   // common case from pass 2 on
         unsigned hits = 0;                                 // bit u: this lane's key carries distinct prefix u
-        for (int u = 0; u < nu; ++u) hits |= (valid && top == s_uprefix[u]) ? (1u << u) : 0u;
+        for (int u = 0; u < nu; ++u) hits |= (maybe && top == s_uprefix[u]) ? (1u << u) : 0u;
         const unsigned any = __ballot_sync(0xffffffffu, hits != 0);
-        if (any == 0) continue;                            // common case from pass 2 on
-        for (int u = 0; u < nu; ++u) hist_add(sh + u * BINS, (hits >> u) & 1, d, lane);
+        if (any == 0) continue;
+        for (int u = 0; u < nu; ++u)
+          hist_add(sh + u * BINS, (hits >> u) & 1, d, lane, hist + ((size_t)sg * n_h + s_urep[u]) * BINS);
         if (mode == 1) {                                   // append to the candidate list, one atomic per warp
           const int leader = __ffs(any) - 1;
           unsigned base = 0;
@@ -169,6 +195,7 @@ cand_hist_kernel(const unsigned long long* __restrict__ cand, const unsigned int
   extern __shared__ unsigned int sh[];
   __shared__ uint64_t s_uprefix[MAX_TARGETS];
   __shared__ int s_umap[MAX_TARGETS];
+  __shared__ int s_urep[MAX_TARGETS];
   __shared__ int s_nu;
   const int sg = blockIdx.y;
   const unsigned n = cand_cnt[sg];
@@ -180,7 +207,7 @@ cand_hist_kernel(const unsigned long long* __restrict__ cand, const unsigned int
   const unsigned mask = (1u << digit_bits(pass)) - 1u;
   const int pshift = 64 - 11 * pass;
   const int lane = threadIdx.x & 31;
-  if (threadIdx.x == 0) load_prefixes(state, sw, sg, n_t, pass, s_uprefix, s_umap, &s_nu);
+  if (threadIdx.x == 0) load_prefixes(state, sw, sg, n_t, pass, s_uprefix, s_umap, s_urep, &s_nu);
   __syncthreads();
   const int nu = s_nu;
   for (int i = threadIdx.x; i < nu * BINS; i += blockDim.x) sh[i] = 0;
@@ -195,14 +222,29 @@ cand_hist_kernel(const unsigned long long* __restrict__ cand, const unsigned int
     for (int u = 0; u < nu; ++u) hist_add(sh + u * BINS, in && top == s_uprefix[u], d, lane);
   }
   __syncthreads();
-  for (int k = 0; k < n_t; ++k) {
-    const unsigned int* src = sh + s_umap[k] * BINS;
-    unsigned long long* dst = hist + ((size_t)sg * n_t + k) * BINS;
+  for (int u = 0; u < nu; ++u) {
+    const unsigned int* src = sh + u * BINS;
+    unsigned long long* dst = hist + ((size_t)sg * n_t + s_urep[u]) * BINS;
     for (int i = threadIdx.x; i < BINS; i += blockDim.x) {
       const unsigned c = src[i];
       if (c) atomicAdd(&dst[i], (unsigned long long)c);
     }
   }
+}
+
+// After the histogram kernels: targets that share a prefix share a histogram; copy the
+// representative's to the others.  grid (n_t, n_seg).
+__global__ void __launch_bounds__(256)
+hist_broadcast_kernel(unsigned long long* __restrict__ hist, const uint64_t* __restrict__ state, int sw, int n_t) {
+  const int k = blockIdx.x, sg = blockIdx.y;
+  const uint64_t* st = state + (size_t)sg * sw;
+  const uint64_t pf = st[2 + 2 * k];
+  int rep = k;
+  for (int j = 0; j < k; ++j) if (st[2 + 2 * j] == pf) { rep = j; break; }
+  if (rep == k) return;
+  const unsigned long long* src = hist + ((size_t)sg * n_t + rep) * BINS;
+  unsigned long long* dst = hist + ((size_t)sg * n_t + k) * BINS;
+  for (int i = threadIdx.x; i < BINS; i += blockDim.x) dst[i] = src[i];
 }
 
 // grid (n_t, n_seg); one CTA scans one histogram
@@ -298,7 +340,7 @@ int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
                       const int32_t* d_seg, int64_t n_seg, const int32_t* d_row_order, int64_t n_rows,
                       int64_t n_q, int pass, const uint64_t* d_state, uint64_t* d_hist, pmx_stream stream) {
   PMX_REQUIRE(ctx, "ctx is NULL");
-  PMX_REQUIRE(n_series >= 0 && n_steps >= 0 && n_seg >= 0, "bad sizes");
+  PMX_REQUIRE(n_series >= 0 && n_steps >= 0 && n_seg >= 0 && n_seg <= 65535, "bad sizes (n_seg <= 65535)");
   PMX_REQUIRE(n_q >= 1 && 2 * n_q <= MAX_TARGETS, "n_q must be in [1, 8]");
   PMX_REQUIRE(pass >= 0 && pass < PMX_QUANTILE_PASSES, "pass out of range");
   if (n_seg == 0) return PMX_OK;
@@ -346,6 +388,11 @@ int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
                                                 (unsigned long long*)d_hist, (int)rows, n_rows, d_row_order, mode,
                                                 cand, cand_cnt, cap);
   PMX_LAUNCH_CHECK();
+  if (pass > 0) {
+    dim3 bgrid((unsigned)n_t, (unsigned)n_seg);
+    hist_broadcast_kernel<<<bgrid, 256, 0, st>>>((unsigned long long*)d_hist, d_state, state_words(n_q), n_t);
+    PMX_LAUNCH_CHECK();
+  }
   return PMX_OK;
 }
 
