@@ -144,6 +144,82 @@ __device__ __noinline__ int rate_skip_empty(const double* T_fv, const double* T_
   return -1;
 }
 
+// General tile (gaps, several samples per grid step, series ends): stage the samples that can
+// serve the tile in shared memory as 32-bit tile-relative timestamps + values, then guess / verify /
+// binary-search per thread and walk forward.  Out of line: regular tiles never come here, and the
+// hot loop stays small.  All threads of the CTA call it together (it synchronises).  Writes the
+// aligned values to A and returns the cursor for the next tile.
+template <int NT>
+__device__ __noinline__ int64_t align_general_tile(const int64_t* __restrict__ gts0, const double* __restrict__ gv0,
+                                                   int64_t len, int64_t cur, int shift, int elo, int64_t tbase,
+                                                   int64_t step_ms, int64_t lookback_ms, int n_el, int OUT, int e0,
+                                                   int t, double* s_val, int* s_t, double* A, int64_t* s_cursor) {
+  using TL = FTile<NT>;
+  const int step = (int)step_ms, lookback = (int)lookback_ms;
+  const int64_t rem = len - cur;
+  const int ns = (int)(rem < TL::NS ? rem : TL::NS);
+  {
+    const int64_t* gts = gts0 + cur;
+    const double* gv = gv0 + cur;
+    for (int i = t; i < ns; i += NT) {
+      int d32;                                                    // saturate: order and lookback tests stay exact
+      asm("cvt.sat.s32.s64 %0, %1;" : "=r"(d32) : "l"(gts[i] - tbase));
+      s_t[pad8(i)] = d32 < -0x40000000 ? -0x40000000 : d32;
+      s_val[pad8(i)] = gv[i];
+    }
+  }
+  __syncthreads();
+  const int ghi = (n_el - 1) * step;
+  const bool covered = (cur + ns >= len) || (ns > 0 && s_t[pad8(ns - 1)] > ghi);
+  const int e_cur = OUT;                                          // its floor seeds the next tile
+  if (!covered) {
+#pragma unroll 1
+    for (int r = 0; r < E; ++r) {
+      const int e = e0 + r;
+      double v = pmx_nan();
+      if (e >= elo && e < n_el) {
+        int64_t idx;
+        v = align_one_global(gts0, gv0, cur, len, tbase + (int64_t)e * step_ms, lookback_ms, &idx);
+        if (e == e_cur) *s_cursor = idx;
+      }
+      A[r * NT + t] = v;
+    }
+  } else {
+    // guess: one sample per grid step; staged sample 0 is the floor of element elo (or the sample
+    // after it when the series starts later)
+    int idx = e0 - elo - shift;
+    if (idx > ns - 1) idx = ns - 1;
+    {
+      const int ef = e0 > elo ? e0 : elo;                         // first element this thread aligns
+      const int g = ef * step;
+      if (idx < 0) idx = (ns > 0 && s_t[0] <= g) ? floor_staged(s_t, 0, ns, g) : -1;
+      else if (!(s_t[pad8(idx)] <= g && (idx + 1 >= ns || s_t[pad8(idx + 1)] > g))) idx = floor_staged(s_t, 0, ns, g);
+    }
+#pragma unroll 1
+    for (int r = 0; r < E; ++r) {
+      const int e = e0 + r;
+      const int g = e * step;
+      double v = pmx_nan();
+      if (e >= elo && e < n_el) {
+        if (idx + 1 < ns && s_t[pad8(idx + 1)] <= g) {
+          ++idx;
+          if (idx + 1 < ns && s_t[pad8(idx + 1)] <= g) idx = floor_staged(s_t, idx + 1, ns, g);
+        }
+        if (idx >= 0) {
+          const double sample = s_val[pad8(idx)];
+          if (g - s_t[pad8(idx)] < lookback &&
+              (unsigned long long)__double_as_longlong(sample) != PMX_STALE_NAN_BITS)
+            v = sample;
+        }
+        if (e == e_cur) *s_cursor = idx >= 0 ? cur + idx : -1;
+      }
+      A[r * NT + t] = v;
+    }
+  }
+  __syncthreads();                                                // staging dead, cursor visible
+  return *s_cursor;
+}
+
 template <int NT, bool ALIGN>
 __global__ void __launch_bounds__(NT, (NT == 256 ? 2 : PMX_FAST_CTAS_128))
 window_fast_kernel(const WinParams p) {
@@ -185,7 +261,6 @@ window_fast_kernel(const WinParams p) {
   const bool do_rate = p.o_inc || p.o_rate;
   const double INF = __longlong_as_double(0x7FF0000000000000LL);
   const int need = p.min_periods > 1 ? p.min_periods : 1;
-  const int step = (int)p.step_ms, lookback = (int)p.lookback_ms;  // launch_fast checked the ranges
 
   for (int k = t; k <= p.w; k += NT) {
     rcp[k] = k ? 1.0 / (double)k : 0.0;
@@ -250,70 +325,8 @@ window_fast_kernel(const WinParams p) {
       if (__syncthreads_and(ok)) {
         cursor = cur + (OUT - elo - shift);
       } else {
-        // ---- general tile: stage the samples that can serve it, search/walk per point
-        const int64_t rem = len - cur;
-        const int ns = (int)(rem < TL::NS ? rem : TL::NS);
-        {
-          const int64_t* gts = p.ts + base + cur;
-          const double* gv = p.val + base + cur;
-          for (int i = t; i < ns; i += NT) {
-            int d32;                                              // saturate: order and lookback tests stay exact
-            asm("cvt.sat.s32.s64 %0, %1;" : "=r"(d32) : "l"(gts[i] - tbase));
-            s_t[pad8(i)] = d32 < -0x40000000 ? -0x40000000 : d32;
-            s_val[pad8(i)] = gv[i];
-          }
-        }
-        __syncthreads();
-        const int ghi = (n_el - 1) * step;
-        const bool covered = (cur + ns >= len) || (ns > 0 && s_t[pad8(ns - 1)] > ghi);
-        const int e_cur = OUT;                                    // its floor seeds the next tile
-        if (!covered) {
-#pragma unroll 1
-          for (int r = 0; r < E; ++r) {
-            const int e = e0 + r;
-            double v = pmx_nan();
-            if (e >= elo && e < n_el) {
-              int64_t idx;
-              v = align_one_global(p.ts + base, p.val + base, cur, len, tbase + (int64_t)e * p.step_ms,
-                                   p.lookback_ms, &idx);
-              if (e == e_cur) *s_cursor = idx;
-            }
-            A[r * NT + t] = v;
-          }
-        } else {
-          // guess: one sample per grid step; staged sample 0 is the floor of element elo (or the
-          // sample after it when the series starts later)
-          int idx = e0 - elo - shift;
-          if (idx > ns - 1) idx = ns - 1;
-          {
-            const int ef = e0 > elo ? e0 : elo;                   // first element this thread aligns
-            const int g = ef * step;
-            if (idx < 0) idx = (ns > 0 && s_t[0] <= g) ? floor_staged(s_t, 0, ns, g) : -1;
-            else if (!(s_t[pad8(idx)] <= g && (idx + 1 >= ns || s_t[pad8(idx + 1)] > g))) idx = floor_staged(s_t, 0, ns, g);
-          }
-#pragma unroll 1
-          for (int r = 0; r < E; ++r) {
-            const int e = e0 + r;
-            const int g = e * step;
-            double v = pmx_nan();
-            if (e >= elo && e < n_el) {
-              if (idx + 1 < ns && s_t[pad8(idx + 1)] <= g) {
-                ++idx;
-                if (idx + 1 < ns && s_t[pad8(idx + 1)] <= g) idx = floor_staged(s_t, idx + 1, ns, g);
-              }
-              if (idx >= 0) {
-                const double sample = s_val[pad8(idx)];
-                if (g - s_t[pad8(idx)] < lookback &&
-                    (unsigned long long)__double_as_longlong(sample) != PMX_STALE_NAN_BITS)
-                  v = sample;
-              }
-              if (e == e_cur) *s_cursor = idx >= 0 ? cur + idx : -1;
-            }
-            A[r * NT + t] = v;
-          }
-        }
-        __syncthreads();                                          // staging dead, cursor visible
-        cursor = *s_cursor;
+        cursor = align_general_tile<NT>(p.ts + base, p.val + base, len, cur, shift, elo, tbase, p.step_ms,
+                                        p.lookback_ms, n_el, OUT, e0, t, s_val, s_t, A, s_cursor);
 #pragma unroll
         for (int r = 0; r < E; ++r) a[r] = A[r * NT + t];         // own elements: written by this thread
       }
