@@ -247,12 +247,13 @@ def run_engine(args):
     h_sum = torch.empty((5 + 3, N_METRICS), dtype=torch.float64).pin_memory()
     d_ts, d_val, d_off = torch.empty_like(ts), torch.empty_like(val), torch.empty_like(off)
 
+    host = {"dev": {"ts": d_ts, "val": d_val, "off": d_off, **out}, "out": h_out}
+
     def e2e_step():
-        d_ts.copy_(h_ts, non_blocking=True); d_val.copy_(h_val, non_blocking=True); d_off.copy_(h_off, non_blocking=True)
-        o, summ, q = sh.aggregate_step(d_ts, d_val, d_off, START_MS, STEP_MS, T, WINDOW_STEPS, seg, N_METRICS,
-                                       perm_goff, QS, out=out, lookback_ms=LOOKBACK_MS)
-        for k in h_out:
-            h_out[k].copy_(o[k], non_blocking=True)
+        # public API with HOST buffers: pipelined H2D -> fused kernel -> D2H over series slices,
+        # then the cluster-wide summary, whose result is read back too
+        o, summ, q = sh.aggregate_step(h_ts, h_val, h_off, START_MS, STEP_MS, T, WINDOW_STEPS, seg, N_METRICS,
+                                       perm_goff, QS, lookback_ms=LOOKBACK_MS, host=host)
         packed = torch.stack([summ[0], summ[1].to(torch.float64), summ[2], summ[3], summ[4],
                               q["value"][:, 0], q["value"][:, 1], q["value"][:, 2]])
         h_sum.copy_(packed, non_blocking=True)

@@ -232,6 +232,57 @@ class Engine:
         self.launches += 1
         return out
 
+    def fused_from_host(self, h_ts, h_val, h_off, start_ms, step_ms, n_steps, window_steps, dev, h_out,
+                        lookback_ms=DEFAULT_LOOKBACK_MS, min_periods=1, n_chunks=8):
+        """The fused kernel fed from PINNED host arrays, results returned to pinned host arrays.
+
+        Series are cut into ``n_chunks`` slices; the H2D copy of slice k+1, the kernel on slice k and
+        the D2H copy of slice k-1 run on three streams, so the step costs about max(H2D, D2H) of
+        the PCIe link instead of their sum.  ``dev``: dict of preallocated device tensors
+        (ts, val, off, aligned, roll_min, roll_max, roll_mean, rate); ``h_out``: dict of pinned host
+        tensors for the five outputs.  Returns the device outputs (valid after the current stream
+        has been synchronised; the call makes the current stream wait for all three)."""
+        t = self.torch
+        if not hasattr(self, "_streams"):
+            self._streams = [t.cuda.Stream(device=self.device) for _ in range(3)]
+        s_in, s_run, s_out = self._streams
+        cur = t.cuda.current_stream(self.device)
+        for s in self._streams:
+            s.wait_stream(cur)
+        S = h_off.numel() - 1
+        keys = ("aligned", "roll_min", "roll_max", "roll_mean", "rate")
+        with t.cuda.stream(s_in):
+            dev["off"].copy_(h_off, non_blocking=True)
+        off_list = h_off.tolist() if S <= 65536 else None
+        bounds = [S * k // n_chunks for k in range(n_chunks + 1)]
+        for k in range(n_chunks):
+            a, b = bounds[k], bounds[k + 1]
+            if a == b:
+                continue
+            lo = off_list[a] if off_list is not None else int(h_off[a])
+            hi = off_list[b] if off_list is not None else int(h_off[b])
+            with t.cuda.stream(s_in):
+                dev["ts"][lo:hi].copy_(h_ts[lo:hi], non_blocking=True)
+                dev["val"][lo:hi].copy_(h_val[lo:hi], non_blocking=True)
+                ev_in = t.cuda.Event(); ev_in.record(s_in)
+            with t.cuda.stream(s_run):
+                s_run.wait_event(ev_in)
+                # offsets stay absolute: the slice is addressed through off + a over the full ts/val buffers
+                _abi.check(self.lib.pmx_fused_align_rolling_rate(
+                    self.ctx, self._ptr(dev["ts"]), self._ptr(dev["val"]), C.c_void_p(dev["off"].data_ptr() + 8 * a),
+                    b - a, start_ms, step_ms, n_steps, lookback_ms, window_steps, min_periods,
+                    *(C.c_void_p(dev[key].data_ptr() + 8 * a * n_steps) for key in keys),
+                    C.c_void_p(s_run.cuda_stream)))
+                self.launches += 1
+                ev_run = t.cuda.Event(); ev_run.record(s_run)
+            with t.cuda.stream(s_out):
+                s_out.wait_event(ev_run)
+                for key in keys:
+                    h_out[key][a:b].copy_(dev[key][a:b], non_blocking=True)
+        for s in self._streams:
+            cur.wait_stream(s)
+        return {key: dev[key] for key in keys}
+
     # ------------------------------------------------------------------ K5
     def group_reduce(self, x, group_id, n_groups, per_step=False, perm_goff=None):
         """NaN-skipping sum/count/min/max/mean per group.  group_id: int per series (host)."""

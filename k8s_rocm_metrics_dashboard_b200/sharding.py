@@ -92,11 +92,17 @@ class ShardedEngine:
         self._qbuf = {}
 
     def aggregate_step(self, ts, val, off, start_ms, step_ms, n_steps, window_steps, seg, n_seg, perm_goff,
-                       qs=(0.5, 0.95, 0.99), out=None, lookback_ms=300_000):
+                       qs=(0.5, 0.95, 0.99), out=None, lookback_ms=300_000, host=None):
         """fused align+rolling+rate on the shard, then per-metric sum/count/min/max/mean and exact
-        quantiles of the aligned values over ALL ranks.  ``seg``: metric id per local series."""
+        quantiles of the aligned values over ALL ranks.  ``seg``: metric id per local series.
+        With ``host`` = {"dev": device buffers, "out": pinned host outputs} the inputs are pinned host
+        tensors and the copies are pipelined with the kernel (Engine.fused_from_host)."""
         eng = self.eng
-        out = eng.fused(ts, val, off, start_ms, step_ms, n_steps, window_steps, lookback_ms, out=out)
+        if host is not None:        # ts/val/off are pinned host tensors; results also go to host["out"]
+            out = eng.fused_from_host(ts, val, off, start_ms, step_ms, n_steps, window_steps, host["dev"],
+                                      host["out"], lookback_ms)
+        else:
+            out = eng.fused(ts, val, off, start_ms, step_ms, n_steps, window_steps, lookback_ms, out=out)
         sm, cnt, mn, mx, _ = eng.group_reduce(out["aligned"], None, n_seg, perm_goff=perm_goff)
         if self.world > 1:
             summary = combine_group_partials(sm, cnt, mn, mx, self.group)

@@ -242,3 +242,24 @@ def test_general_kernel_path_for_unaligned_outputs(eng):
     _, _, mean, _ = eng.rolling(x, 60)
     assert t.equal(mean.view(t.int64).ravel(), mean_unaligned.contiguous().view(t.int64)) or \
         np.allclose(_np(mean).ravel(), _np(mean_unaligned), rtol=1e-14, equal_nan=True)
+
+
+def test_fused_from_host_pipeline_equals_fused(eng):
+    """Host-buffer entry (three streams, series slices) returns the same bits as the one-shot call."""
+    t = eng.torch
+    d = synth.dense(3, 8, 6, 700, seed=31, nan_frac=0.01, kinds="ttk")
+    S, T = len(d["off"]) - 1, 700
+    ref = eng.fused(d["ts"], d["val"], d["off"], d["start_ms"], d["step_ms"], T, 60)
+    h_ts, h_val, h_off = (t.as_tensor(d[k]).pin_memory() for k in ("ts", "val", "off"))
+    keys = ("aligned", "roll_min", "roll_max", "roll_mean", "rate")
+    dev = {"ts": t.empty(len(d["ts"]), dtype=t.int64, device=eng.device),
+           "val": t.empty(len(d["val"]), dtype=t.float64, device=eng.device),
+           "off": t.empty(S + 1, dtype=t.int64, device=eng.device),
+           **{k: t.full((S, T), -1.0, dtype=t.float64, device=eng.device) for k in keys}}
+    h_out = {k: t.empty((S, T), dtype=t.float64).pin_memory() for k in keys}
+    for n_chunks in (1, 5, 8):
+        out = eng.fused_from_host(h_ts, h_val, h_off, d["start_ms"], d["step_ms"], T, 60, dev, h_out, n_chunks=n_chunks)
+        t.cuda.synchronize()
+        for k in keys:
+            assert t.equal(out[k].view(t.int64), ref[k].view(t.int64)), k
+            assert t.equal(h_out[k].view(t.int64), ref[k].cpu().view(t.int64)), k
