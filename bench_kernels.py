@@ -119,7 +119,7 @@ def main():
     r_ts, r_val, r_off = (torch.as_tensor(d5[k], device=dev) for k in ("ts", "val", "off"))
     n5 = int(d5["off"][-1])
     rec("ragged rolling (cfg5, 200k series)", n5, 44, timeit(lambda: eng.rolling_ragged(r_ts, r_val, r_off, 900_000), iters=3, warm=1))
-    rec("ragged rate (cfg5, 200k series)", n5, 36, timeit(lambda: eng.rate_ragged(r_ts, r_val, r_off, 900_000), iters=3, warm=1))
+    rec("ragged rate (cfg5, 200k series)", n5, 36, timeit(lambda: eng.rate_ragged(r_ts, r_val, r_off, 900_000, want_resets=False), iters=3, warm=1))
     t0i = int(d5["ts"].min())
     outr = None
     rec("fused on ragged cfg5 -> 15 s grid", 200_000 * 640, 56,

@@ -4,16 +4,11 @@
 // on the series' own timestamps and folds the window directly (fresh sums, exact min/max).
 // Window (t_i - W, t_i]; NaN (and therefore stale-marker) samples are skipped.
 #include <math.h>
-#include "pmx_common.cuh"
+#include <stdlib.h>
+#include "ragged_common.cuh"
+using pmxr::RParams;
 
 namespace {
-
-struct RParams {
-  const int64_t* ts; const double* val; const int64_t* off;
-  int64_t n_series; int64_t window_ms; int32_t min_periods;
-  double* o_min; double* o_max; double* o_mean; int32_t* o_cnt;
-  double* o_inc; double* o_rate; int32_t* o_nres;
-};
 
 __global__ void __launch_bounds__(256)
 ragged_window_kernel(const RParams p) {
@@ -69,6 +64,12 @@ ragged_window_kernel(const RParams p) {
 
 int launch(pmx_ctx* ctx, const RParams& p, cudaStream_t st) {
   if (p.n_series == 0) return PMX_OK;
+  static int direct_only = -1;                            // PMX_RAGGED_DIRECT=1 keeps the first-version kernel
+  if (direct_only < 0) { const char* e = getenv("PMX_RAGGED_DIRECT"); direct_only = (e && atoi(e)) ? 1 : 0; }
+  if (!direct_only) {
+    const int rc = pmxr::launch_ragged_fast(ctx, p, st);
+    if (rc != 1) return rc;
+  }
   int64_t blocks = (p.n_series + 7) / 8;                 // 8 warps per CTA
   const int64_t cap = (int64_t)ctx->sm_count * 32;
   if (blocks > cap) blocks = cap;
@@ -89,7 +90,7 @@ int pmx_rolling_ragged(pmx_ctx* ctx, const int64_t* d_ts, const double* d_val, c
   PMX_REQUIRE(min_periods >= 0 && min_periods <= 0x7fffffff, "bad min_periods");
   if (n_series == 0 || n_samples == 0) return PMX_OK;
   PMX_REQUIRE(d_ts && d_val && d_off && (d_min || d_max || d_mean || d_count), "NULL buffer");
-  RParams p{d_ts, d_val, d_off, n_series, window_ms, (int32_t)min_periods, d_min, d_max, d_mean, d_count,
+  RParams p{d_ts, d_val, d_off, n_series, n_samples, window_ms, (int32_t)min_periods, d_min, d_max, d_mean, d_count,
             nullptr, nullptr, nullptr};
   return launch(ctx, p, pmx_st(stream));
 }
@@ -101,7 +102,7 @@ int pmx_rate_ragged(pmx_ctx* ctx, const int64_t* d_ts, const double* d_val, cons
   PMX_REQUIRE(n_series >= 0 && n_samples >= 0 && window_ms > 0, "bad sizes");
   if (n_series == 0 || n_samples == 0) return PMX_OK;
   PMX_REQUIRE(d_ts && d_val && d_off && (d_increase || d_rate || d_n_resets), "NULL buffer");
-  RParams p{d_ts, d_val, d_off, n_series, window_ms, 1, nullptr, nullptr, nullptr, nullptr,
+  RParams p{d_ts, d_val, d_off, n_series, n_samples, window_ms, 1, nullptr, nullptr, nullptr, nullptr,
             d_increase, d_rate, d_n_resets};
   return launch(ctx, p, pmx_st(stream));
 }

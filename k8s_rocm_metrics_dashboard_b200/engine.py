@@ -203,12 +203,14 @@ class Engine:
         self.launches += 1
         return inc, rt, nres
 
-    def rate_ragged(self, ts, val, off, window_ms):
+    def rate_ragged(self, ts, val, off, window_ms, want_resets=True):
+        """Increase / rate at every sample.  ``want_resets=False`` skips n_resets (and lets the
+        tiled kernel serve the call; the reset counts come from the direct kernel)."""
         t = self.torch
         ts, val, off = self._dev(ts, t.int64), self._dev(val, t.float64), self._dev(off, t.int64)
         N, S = ts.numel(), off.numel() - 1
         inc, rt = self._empty((N,), t.float64), self._empty((N,), t.float64)
-        nres = self._empty((N,), t.int32)
+        nres = self._empty((N,), t.int32) if want_resets else None
         _abi.check(self.lib.pmx_rate_ragged(self.ctx, self._ptr(ts), self._ptr(val), self._ptr(off), S, N, window_ms,
                                             self._ptr(inc), self._ptr(rt), self._ptr(nres), self._stream()))
         self.launches += 1

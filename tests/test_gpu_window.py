@@ -263,3 +263,56 @@ def test_fused_from_host_pipeline_equals_fused(eng):
         for k in keys:
             assert t.equal(out[k].view(t.int64), ref[k].view(t.int64)), k
             assert t.equal(h_out[k].view(t.int64), ref[k].cpu().view(t.int64)), k
+
+
+def _check_ragged(eng, d, window_ms):
+    mn, mx, mean, cnt = eng.rolling_ragged(d["ts"], d["val"], d["off"], window_ms)
+    omn, omx, omean, ocnt = O.rolling_ragged(d["ts"], d["val"], d["off"], window_ms)
+    assert_exact_or_nan(_np(mn), omn, "ragged min"); assert_exact_or_nan(_np(mx), omx, "ragged max")
+    assert np.array_equal(_np(cnt), ocnt), "ragged count"
+    assert_close(_np(mean), omean, rtol=1e-12, what="ragged mean")
+    inc, rt, _ = eng.rate_ragged(d["ts"], d["val"], d["off"], window_ms, want_resets=False)
+    oinc, ort, _ = O.rate_ragged(d["ts"], d["val"], d["off"], window_ms)
+    scale = np.full(len(oinc), float(np.nanmax(np.abs(np.where(np.isfinite(d["val"]), d["val"], 0.0))) + 1.0))
+    assert_close(_np(inc), oinc, scale=scale, rtol=1e-12, what="ragged increase")
+    assert_close(_np(rt), ort, scale=scale / 13.0, rtol=1e-12, what="ragged rate")
+
+
+@pytest.mark.parametrize("window_ms", [20_000, 120_000, 900_000, 3_600_000])
+def test_ragged_tiled_kernel_windows(eng, window_ms):
+    """Config-5 shaped data through the tiled kernel: windows of 1-2 samples (inside one chunk),
+    ~8, ~60 and ~240 samples (the last one longer than the halo: direct folds)."""
+    d = synth.ragged(300, seed=window_ms % 97, mean_len=250, nan_frac=0.03, stale_frac=0.01, gap_frac=0.03)
+    _check_ragged(eng, d, window_ms)
+
+
+def test_ragged_tiled_kernel_tiny_and_empty_series(eng):
+    """Hundreds of series starts per tile, single-sample and empty series, long NaN runs."""
+    rng = np.random.default_rng(4)
+    lens = rng.integers(0, 5, 3000)
+    lens[::50] = rng.integers(200, 1500, len(lens[::50]))
+    off = np.zeros(len(lens) + 1, dtype=np.int64); np.cumsum(lens, out=off[1:])
+    N = int(off[-1])
+    gaps = 15_000 + rng.integers(-2000, 2001, N)
+    ts = np.cumsum(gaps).astype(np.int64)
+    val = np.round(rng.uniform(0, 1000, N), 3)
+    pos = 0
+    while pos < N:                                              # NaN runs of up to 30 samples
+        run = int(rng.integers(1, 60))
+        if rng.random() < 0.3:
+            val[pos:pos + min(run, 30)] = np.nan
+        pos += run
+    d = {"ts": ts, "val": val, "off": off}
+    _check_ragged(eng, d, 900_000)
+    _check_ragged(eng, d, 60_000)
+
+
+def test_ragged_tiled_kernel_more_series_starts_than_fit(eng):
+    """> 1152 (empty) series starting inside one tile: that tile's outputs are folded directly."""
+    rng = np.random.default_rng(6)
+    lens = np.concatenate([[700], np.zeros(2000, dtype=np.int64), [900], np.zeros(10, dtype=np.int64), [1500]])
+    off = np.zeros(len(lens) + 1, dtype=np.int64); np.cumsum(lens, out=off[1:])
+    N = int(off[-1])
+    ts = np.cumsum(15_000 + rng.integers(-2000, 2001, N)).astype(np.int64)
+    val = np.round(rng.uniform(0, 100, N), 3); val[rng.random(N) < 0.02] = np.nan
+    _check_ragged(eng, {"ts": ts, "val": val, "off": off}, 900_000)
