@@ -183,7 +183,14 @@ ragged_fast_kernel(const RParams p, int64_t n_tiles, int tiles_per_cta) {
         const int lob = srel > 0 ? srel : 0;
         if (l < lob) l = lob;
         const int64_t edge = tk[r] - p.window_ms;
-        while (l < e && sm.ts[pad8(l)] <= edge) ++l;
+        if (l < e && sm.ts[pad8(l)] <= edge) {               // usually one step; after a scrape gap or a
+          ++l;                                               // series start it jumps: binary search then
+          if (l < e && sm.ts[pad8(l)] <= edge) {
+            int lo = l + 1, hi = e;
+            while (lo < hi) { const int m = (lo + hi) >> 1; if (sm.ts[pad8(m)] <= edge) lo = m + 1; else hi = m; }
+            l = lo;
+          }
+        }
         sr[r] = srel;
         // the series continues before the tile and the window still covers element 0: the halo
         // is too short for this output
