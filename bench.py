@@ -157,6 +157,38 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def instant_path_times(eng):
+    """The reference's OWN path (app.py:153-227, one node, 8 cards x 5 series = 40 samples per call):
+    unmodified fetch_gpu_metrics under import stubs (baseline/_ref/app.py, copied there by build())
+    against this engine's aggregate_instant on the same body.  A 40-sample call is latency-bound on
+    a GPU; reported for completeness, not as the optimisation target."""
+    try:
+        from k8s_rocm_metrics_dashboard_b200 import adapter, synth
+        from oracle import ref_app
+        _, _, body = synth.instant_snapshot(0, 8, seed=0)
+        out = {"samples_per_call": 40}
+        for _ in range(3):
+            adapter.aggregate_instant(body, eng)
+        t0 = time.perf_counter()
+        for _ in range(20):
+            adapter.aggregate_instant(body, eng)
+        out["engine_ms_per_call"] = (time.perf_counter() - t0) / 20 * 1e3
+        if ref_app.reference_path():
+            mod, _ = ref_app.load_reference()
+            text = body.decode()
+            for _ in range(3):
+                ref_app.run_fetch(mod, text)
+            t0 = time.perf_counter()
+            for _ in range(20):
+                ref_app.run_fetch(mod, text)
+            out["reference_ms_per_call"] = (time.perf_counter() - t0) / 20 * 1e3
+        else:
+            out["reference_ms_per_call"] = None
+        return out
+    except Exception as e:  # noqa: BLE001
+        return {"error": str(e)[:200]}
+
+
 def _pandas_version():
     import pandas
     return pandas.__version__
@@ -300,6 +332,9 @@ def run_engine(args):
             cpu = {"value": ns * T / sec, "unit": "samples/s", "cores": 1, "kind": "port",
                    "sample": f"first {ns} of {S} series x {T} steps of the same device data ({ns * T} samples), "
                              f"pandas {_pandas_version()} single process, host has {os.cpu_count()} cores"}
+        instant = None
+        if world == 1 and not args.no_cpu_baseline:
+            instant = instant_path_times(eng)
         line = {"metric": METRIC, "value": world * n_samples * args.steps / (ms * 1e-3), "unit": "samples/s",
                 "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -313,7 +348,7 @@ def run_engine(args):
                 "cpu_baseline": cpu,
                 "e2e": {"value": world * n_samples * e2e_steps / e2e_s, "unit": "samples/s",
                         "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps},
-                "gpu_launches": launches, "clocks": clocks}
+                "gpu_launches": launches, "clocks": clocks, "instant_path": instant}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -129,7 +129,10 @@ class Engine:
         """Device decode of all value (and timestamp) tokens.  Returns (ts int64[N] | None, val float64[N]).
         Raises ValueError naming the first malformed token, like float() at app.py:188."""
         t = self.torch
-        text = t.from_numpy(tok.flat).to(self.device)
+        import warnings
+        with warnings.catch_warnings():                    # the body is a read-only bytes view; it is only read
+            warnings.simplefilter("ignore", UserWarning)
+            text = t.from_numpy(tok.flat).to(self.device)
         n = tok.n_samples
         val = self._empty((n,), t.float64)
         bad = self._empty((2,), t.int64)
