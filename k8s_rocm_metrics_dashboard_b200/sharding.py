@@ -54,10 +54,13 @@ def combine_group_partials(sm, cnt, mn, mx, group=None):
     mn = torch.where(cnt > 0, mn, torch.full_like(mn, inf))
     mx = torch.where(cnt > 0, mx, torch.full_like(mx, -inf))
     if dist.is_initialized() and dist.get_world_size(group) > 1:
-        dist.all_reduce(sm, op=dist.ReduceOp.SUM, group=group)
-        dist.all_reduce(cnt, op=dist.ReduceOp.SUM, group=group)
-        dist.all_reduce(mn, op=dist.ReduceOp.MIN, group=group)
-        dist.all_reduce(mx, op=dist.ReduceOp.MAX, group=group)
+        # two collectives instead of four: the exchanges are latency-bound (a few KB each)
+        add = torch.stack([sm, cnt.to(sm.dtype)])            # counts stay exact in float64 below 2^53
+        ext = torch.stack([-mn, mx])                         # min(x) = -max(-x)
+        dist.all_reduce(add, op=dist.ReduceOp.SUM, group=group)
+        dist.all_reduce(ext, op=dist.ReduceOp.MAX, group=group)
+        sm, cnt = add[0], add[1].round().to(cnt.dtype)
+        mn, mx = -ext[0], ext[1]
     nan = torch.full_like(mn, float("nan"))
     any_ = cnt > 0
     mean = torch.where(any_, sm / cnt.to(sm.dtype).clamp(min=1), nan)
