@@ -113,13 +113,16 @@ int pmx_rolling_ragged(pmx_ctx* ctx, const int64_t* d_ts, const double* d_val,
 
 /* ---- X5  counter increase / rate with reset handling (K4).  Window as in pmx_rolling; NaN
  * skipped; >=2 samples needed.  increase = (x_last - x_first) + sum of the values that
- * preceded each drop inside the window; rate = increase / elapsed seconds first..last. */
+ * preceded each drop inside the window.  mode 0: rate = increase / elapsed seconds first..last.
+ * mode 1: Prometheus' extrapolatedRate -- the increase is stretched to the window edges when they
+ * are closer than 1.1 mean sample spacings (else by half a spacing), not beyond the counter's zero
+ * crossing, and rate = extrapolated increase / window seconds (d_increase is the extrapolated one). */
 int pmx_rate(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
-             int64_t window_steps, int64_t step_ms,
+             int64_t window_steps, int64_t step_ms, int mode,
              double* d_increase, double* d_rate, int32_t* d_n_resets, pmx_stream stream);
 int pmx_rate_ragged(pmx_ctx* ctx, const int64_t* d_ts, const double* d_val,
                     const int64_t* d_off, int64_t n_series, int64_t n_samples,
-                    int64_t window_ms,
+                    int64_t window_ms, int mode,
                     double* d_increase, double* d_rate, int32_t* d_n_resets, pmx_stream stream);
 
 /* ---- X3+X4+X5 fused (the roofline kernel): reads (ts,val) once, writes the aligned value,

@@ -49,8 +49,8 @@ SIGNATURES = {
     "pmx_align": (_int, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _p, _p, _p]),
     "pmx_rolling": (_int, [_p, _p, _i64, _i64, _i64, _i64, _p, _p, _p, _p, _p]),
     "pmx_rolling_ragged": (_int, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _p, _p, _p, _p, _p]),
-    "pmx_rate": (_int, [_p, _p, _i64, _i64, _i64, _i64, _p, _p, _p, _p]),
-    "pmx_rate_ragged": (_int, [_p, _p, _p, _p, _i64, _i64, _i64, _p, _p, _p, _p]),
+    "pmx_rate": (_int, [_p, _p, _i64, _i64, _i64, _i64, _int, _p, _p, _p, _p]),
+    "pmx_rate_ragged": (_int, [_p, _p, _p, _p, _i64, _i64, _i64, _int, _p, _p, _p, _p]),
     "pmx_fused_align_rolling_rate": (_int, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i64, _i64,
                                             _p, _p, _p, _p, _p, _p]),
     "pmx_group_index": (_int, [_p, _i64, _i64, _p, _p]),

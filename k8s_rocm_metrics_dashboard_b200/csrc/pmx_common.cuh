@@ -45,4 +45,27 @@ __device__ __forceinline__ bool pmx_isnan(double v) { return v != v; }
 __device__ __forceinline__ bool pmx_isfinite(double v) {
   return (__double_as_longlong(v) & 0x7FF0000000000000LL) != 0x7FF0000000000000LL;
 }
+// Rate mode 1: Prometheus' extrapolatedRate for counters (promql/functions.go).  `inc` is the
+// reset-corrected increase first..last, `fv` the first sample, `cnt` >= 2 samples, `sampled` the
+// seconds first..last, `dstart`/`dend` the seconds from the window start to the first sample and
+// from the last sample to the window end, `range_s` the window length.  The increase is stretched
+// to the window edges when they are closer than 1.1 mean sample spacings (else by half a
+// spacing), never further back than the counter's zero crossing; rate = that / range.
+__device__ __forceinline__ void pmx_extrapolate(double inc, double fv, int cnt, double sampled, double dstart,
+                                                double dend, double range_s, double* inc_out, double* rate_out) {
+  const double avg = sampled / (double)(cnt - 1);
+  if (inc > 0.0 && fv >= 0.0) {
+    const double dzero = sampled * (fv / inc);
+    if (dzero < dstart) dstart = dzero;
+  }
+  const double thr = avg * 1.1;
+  double ext = sampled;
+  if (dstart >= thr) dstart = avg / 2.0;
+  ext += dstart;
+  if (dend >= thr) dend = avg / 2.0;
+  ext += dend;
+  const double factor = ext / sampled;
+  *inc_out = inc * factor;
+  *rate_out = (inc * factor) / range_s;
+}
 #endif

@@ -53,6 +53,9 @@ ragged_window_kernel(const RParams p) {
           inc = (lv - fv) + rs;
           const double dt = (double)(lt - ft) / 1000.0;
           rate = dt != 0.0 ? inc / dt : pmx_nan();
+          if (p.rate_mode == 1 && dt != 0.0)                 // window (ti - W, ti]
+            pmx_extrapolate(inc, fv, cnt, dt, (double)(ft - edge) / 1000.0, (double)(ti - lt) / 1000.0,
+                            (double)p.window_ms / 1000.0, &inc, &rate);
         }
         if (p.o_inc) p.o_inc[o] = inc;
         if (p.o_rate) p.o_rate[o] = rate;
@@ -90,19 +93,20 @@ int pmx_rolling_ragged(pmx_ctx* ctx, const int64_t* d_ts, const double* d_val, c
   PMX_REQUIRE(min_periods >= 0 && min_periods <= 0x7fffffff, "bad min_periods");
   if (n_series == 0 || n_samples == 0) return PMX_OK;
   PMX_REQUIRE(d_ts && d_val && d_off && (d_min || d_max || d_mean || d_count), "NULL buffer");
-  RParams p{d_ts, d_val, d_off, n_series, n_samples, window_ms, (int32_t)min_periods, d_min, d_max, d_mean, d_count,
+  RParams p{d_ts, d_val, d_off, n_series, n_samples, window_ms, (int32_t)min_periods, 0, d_min, d_max, d_mean, d_count,
             nullptr, nullptr, nullptr};
   return launch(ctx, p, pmx_st(stream));
 }
 
 int pmx_rate_ragged(pmx_ctx* ctx, const int64_t* d_ts, const double* d_val, const int64_t* d_off,
-                    int64_t n_series, int64_t n_samples, int64_t window_ms, double* d_increase,
+                    int64_t n_series, int64_t n_samples, int64_t window_ms, int mode, double* d_increase,
                     double* d_rate, int32_t* d_n_resets, pmx_stream stream) {
   PMX_REQUIRE(ctx, "ctx is NULL");
+  PMX_REQUIRE(mode == 0 || mode == 1, "mode must be 0 (first..last) or 1 (extrapolated)");
   PMX_REQUIRE(n_series >= 0 && n_samples >= 0 && window_ms > 0, "bad sizes");
   if (n_series == 0 || n_samples == 0) return PMX_OK;
   PMX_REQUIRE(d_ts && d_val && d_off && (d_increase || d_rate || d_n_resets), "NULL buffer");
-  RParams p{d_ts, d_val, d_off, n_series, n_samples, window_ms, 1, nullptr, nullptr, nullptr, nullptr,
+  RParams p{d_ts, d_val, d_off, n_series, n_samples, window_ms, 1, mode, nullptr, nullptr, nullptr, nullptr,
             d_increase, d_rate, d_n_resets};
   return launch(ctx, p, pmx_st(stream));
 }

@@ -6,7 +6,7 @@ namespace pmxr {
 
 struct RParams {
   const int64_t* ts; const double* val; const int64_t* off;
-  int64_t n_series; int64_t n_samples; int64_t window_ms; int32_t min_periods;
+  int64_t n_series; int64_t n_samples; int64_t window_ms; int32_t min_periods; int32_t rate_mode;
   double* o_min; double* o_max; double* o_mean; int32_t* o_cnt;
   double* o_inc; double* o_rate; int32_t* o_nres;
 };

@@ -390,7 +390,7 @@ bool aligned32(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 31) == 
 }  // namespace
 
 int launch_ragged_fast(const pmx_ctx* ctx, const RParams& p, cudaStream_t st) {
-  if (p.o_nres) return 1;
+  if (p.o_nres || p.rate_mode != 0) return 1;
   if (!aligned32(p.o_min) || !aligned32(p.o_max) || !aligned32(p.o_mean) || !aligned32(p.o_inc) ||
       !aligned32(p.o_rate) || (reinterpret_cast<uintptr_t>(p.o_cnt) & 15))
     return 1;

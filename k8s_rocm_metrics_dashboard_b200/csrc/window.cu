@@ -375,6 +375,12 @@ window_kernel(const WinParams p) {
             inc = (W.lv - W.fv) + W.rs;
             const double dt = (double)((int64_t)(W.lpos - W.fpos) * p.step_ms) / 1000.0;
             rate = inc / dt;
+            if (p.rate_mode == 1) {
+              const int e = e0 + r;                          // window (e - w, e] in tile element indices
+              pmx_extrapolate(inc, W.fv, W.cnt, dt, (double)((int64_t)(W.fpos - (e - p.w)) * p.step_ms) / 1000.0,
+                              (double)((int64_t)(e - W.lpos) * p.step_ms) / 1000.0,
+                              (double)((int64_t)p.w * p.step_ms) / 1000.0, &inc, &rate);
+            }
           }
           oinc[r] = inc; orate[r] = rate; onres[r] = W.cnt >= 2 ? W.nres : 0;
         }
@@ -418,7 +424,14 @@ window_naive_kernel(const WinParams p) {
     double inc = pmx_nan(), rate = pmx_nan();
     if (W.cnt >= 2) {
       inc = (W.lv - W.fv) + W.rs;
-      rate = inc / ((double)((int64_t)(W.lpos - W.fpos) * p.step_ms) / 1000.0);
+      const double dt = (double)((int64_t)(W.lpos - W.fpos) * p.step_ms) / 1000.0;
+      rate = inc / dt;
+      if (p.rate_mode == 1) {                              // positions are relative to lo; window (j - w, j]
+        const int64_t wstart = j - p.w - lo;
+        pmx_extrapolate(inc, W.fv, W.cnt, dt, (double)((W.fpos - wstart) * p.step_ms) / 1000.0,
+                        (double)((j - lo - W.lpos) * p.step_ms) / 1000.0,
+                        (double)((int64_t)p.w * p.step_ms) / 1000.0, &inc, &rate);
+      }
     }
     if (p.o_inc) p.o_inc[o] = inc;
     if (p.o_rate) p.o_rate[o] = rate;
@@ -517,16 +530,17 @@ int pmx_rolling(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_ste
 }
 
 int pmx_rate(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
-             int64_t window_steps, int64_t step_ms, double* d_increase, double* d_rate,
+             int64_t window_steps, int64_t step_ms, int mode, double* d_increase, double* d_rate,
              int32_t* d_n_resets, pmx_stream stream) {
   PMX_REQUIRE(ctx, "ctx is NULL");
+  PMX_REQUIRE(mode == 0 || mode == 1, "mode must be 0 (first..last) or 1 (extrapolated)");
   PMX_REQUIRE(n_series >= 0 && n_steps >= 0 && step_ms > 0, "bad sizes");
   PMX_REQUIRE(window_steps >= 1 && window_steps <= 0x7fffffff, "window_steps must be >= 1");
   if (n_series == 0 || n_steps == 0) return PMX_OK;
   PMX_REQUIRE(d_x && (d_increase || d_rate || d_n_resets), "NULL buffer");
   WinParams p{};
   p.x = d_x; p.n_series = n_series; p.n_steps = n_steps; p.step_ms = step_ms;
-  p.w = (int32_t)window_steps; p.min_periods = 1;
+  p.w = (int32_t)window_steps; p.min_periods = 1; p.rate_mode = mode;
   p.o_inc = d_increase; p.o_rate = d_rate; p.o_nres = d_n_resets;
   return window_dense(ctx, p, pmx_st(stream));
 }

@@ -12,6 +12,7 @@ struct WinParams {
   int64_t n_series, n_steps;
   int64_t start_ms, step_ms, lookback_ms;
   int32_t w, min_periods;
+  int32_t rate_mode;                                          // 0 = first..last, 1 = extrapolated (general kernel)
   int32_t chunks; int64_t chunk_len;
   double* o_aligned; int32_t* o_idx;
   double* o_min; double* o_max; double* o_mean; int32_t* o_cnt;

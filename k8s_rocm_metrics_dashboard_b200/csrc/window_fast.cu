@@ -548,7 +548,7 @@ int launch_window_fast(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
   const int nt = window_block_threads();
   const int H = p.w - 1;
   if (H < 8 || H > nt * E / 2 - 4) return 1;
-  if (p.o_nres || p.o_idx) return 1;
+  if (p.o_nres || p.o_idx || p.rate_mode != 0) return 1;
   // tile-relative timestamps are 32-bit: a tile (plus the lookback) must span < 2^30 ms
   if (p.step_ms > 0x3fffffffLL / (nt * E + 8) || p.lookback_ms >= 0x3fffffffLL) return 1;
   if (!aligned32(p.o_aligned) || !aligned32(p.o_min) || !aligned32(p.o_max) || !aligned32(p.o_mean) ||

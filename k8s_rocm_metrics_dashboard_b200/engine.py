@@ -195,18 +195,18 @@ class Engine:
         return mn, mx, mean, cnt
 
     # ------------------------------------------------------------------ K4
-    def rate(self, x, window_steps, step_ms):
+    def rate(self, x, window_steps, step_ms, mode=0):
         t = self.torch
         x = self._dev(x, t.float64)
         S, T = x.shape
         inc, rt = self._empty((S, T), t.float64), self._empty((S, T), t.float64)
         nres = self._empty((S, T), t.int32)
-        _abi.check(self.lib.pmx_rate(self.ctx, self._ptr(x), S, T, window_steps, step_ms, self._ptr(inc),
+        _abi.check(self.lib.pmx_rate(self.ctx, self._ptr(x), S, T, window_steps, step_ms, mode, self._ptr(inc),
                                      self._ptr(rt), self._ptr(nres), self._stream()))
         self.launches += 1
         return inc, rt, nres
 
-    def rate_ragged(self, ts, val, off, window_ms, want_resets=True):
+    def rate_ragged(self, ts, val, off, window_ms, want_resets=True, mode=0):
         """Increase / rate at every sample.  ``want_resets=False`` skips n_resets (and lets the
         tiled kernel serve the call; the reset counts come from the direct kernel)."""
         t = self.torch
@@ -214,7 +214,7 @@ class Engine:
         N, S = ts.numel(), off.numel() - 1
         inc, rt = self._empty((N,), t.float64), self._empty((N,), t.float64)
         nres = self._empty((N,), t.int32) if want_resets else None
-        _abi.check(self.lib.pmx_rate_ragged(self.ctx, self._ptr(ts), self._ptr(val), self._ptr(off), S, N, window_ms,
+        _abi.check(self.lib.pmx_rate_ragged(self.ctx, self._ptr(ts), self._ptr(val), self._ptr(off), S, N, window_ms, mode,
                                             self._ptr(inc), self._ptr(rt), self._ptr(nres), self._stream()))
         self.launches += 1
         return inc, rt, nres

@@ -188,12 +188,33 @@ def rolling_ragged(ts, val, off, window_ms, min_periods=1):
 
 
 # --------------------------------------------------------------------------- X5
-def _rate_series(k, x, t_of, lo_of, T_out, extrapolate=None):
+def extrapolate(inc, first_val, n, sampled_s, to_start_s, to_end_s, range_s):
+    """Prometheus extrapolatedRate for counters (promql/functions.go), SURVEY X5 mode 1.
+    Returns (extrapolated increase, rate)."""
+    avg = sampled_s / (n - 1)
+    if inc > 0 and first_val >= 0:
+        to_zero = sampled_s * (first_val / inc)
+        if to_zero < to_start_s:
+            to_start_s = to_zero
+    thr = avg * 1.1
+    ext = sampled_s
+    if to_start_s >= thr:
+        to_start_s = avg / 2.0
+    ext += to_start_s
+    if to_end_s >= thr:
+        to_end_s = avg / 2.0
+    ext += to_end_s
+    factor = ext / sampled_s
+    return inc * factor, (inc * factor) / range_s
+
+
+def _rate_series(k, x, t_of, lo_of, T_out, mode=0, win_end_ms=None, range_ms=None):
     """Shared body: k = positions of non-NaN samples, x their values.
 
     For output j the window holds the non-NaN samples with position in [lo_of(j), j].
     increase = (x_last - x_first) + sum_{resets m>first} x_{m-1}   
-    rate     = increase / ((t_last - t_first)/1000)
+    mode 0: rate = increase / ((t_last - t_first)/1000)
+    mode 1: Prometheus extrapolation over the window (win_end_ms(j) - range_ms, win_end_ms(j)]
     """
     inc = np.full(T_out, np.nan); rate = np.full(T_out, np.nan)
     nres = np.zeros(T_out, dtype=np.int32)
@@ -210,31 +231,35 @@ def _rate_series(k, x, t_of, lo_of, T_out, extrapolate=None):
             continue
         r = math.fsum(rterm[p + 1:q + 1])
         nres[j] = int(reset[p + 1:q + 1].sum())
-        with np.errstate(invalid="ignore", over="ignore"):
+        with np.errstate(invalid="ignore", over="ignore", divide="ignore"):
             inc[j] = (x[q] - x[p]) + r
             dt = (t_of(k[q]) - t_of(k[p])) / 1000.0
             rate[j] = inc[j] / dt if dt != 0 else np.nan
+            if mode == 1 and dt != 0:
+                end = win_end_ms(j)
+                inc[j], rate[j] = extrapolate(inc[j], x[p], q - p + 1, dt, (t_of(k[p]) - (end - range_ms)) / 1000.0,
+                                              (end - t_of(k[q])) / 1000.0, range_ms / 1000.0)
     return inc, rate, nres
 
 
-def rate(x, w, step_ms):
+def rate(x, w, step_ms, mode=0):
     """Counter increase / rate with reset handling over trailing ``w`` grid points.
 
     ``x`` is the aligned [S, T] matrix (NaN = absent).  NaN samples are skipped; +-inf are
-    ordinary values here.  Fewer than 2 samples in the window -> NaN.
-    Returns (increase, rate float64[S,T], n_resets int32[S,T]).
+    ordinary values here.  Fewer than 2 samples in the window -> NaN.  mode 1 = Prometheus
+    extrapolation (``extrapolate``).  Returns (increase, rate float64[S,T], n_resets int32[S,T]).
     """
     x = np.asarray(x, dtype=np.float64)
     S, T = x.shape
     inc = np.empty((S, T)); rt = np.empty((S, T)); nr = np.empty((S, T), dtype=np.int32)
     for s in range(S):
         k = np.flatnonzero(~np.isnan(x[s]))
-        inc[s], rt[s], nr[s] = _rate_series(k, x[s][k], lambda p: p * step_ms,
-                                            lambda j: j - w + 1, T)
+        inc[s], rt[s], nr[s] = _rate_series(k, x[s][k], lambda p: p * step_ms, lambda j: j - w + 1, T,
+                                            mode, lambda j: j * step_ms, w * step_ms)
     return inc, rt, nr
 
 
-def rate_ragged(ts, val, off, window_ms):
+def rate_ragged(ts, val, off, window_ms, mode=0):
     """``rate`` evaluated at each sample of a ragged series with window (t_i - W, t_i]."""
     N = len(ts)
     inc = np.full(N, np.nan); rt = np.full(N, np.nan); nr = np.zeros(N, dtype=np.int32)
@@ -243,7 +268,8 @@ def rate_ragged(ts, val, off, window_ms):
         t = ts[a:b]; v = val[a:b]
         lo = np.searchsorted(t, t - window_ms, side="right")
         k = np.flatnonzero(~np.isnan(v))
-        i_, r_, n_ = _rate_series(k, v[k], lambda p: int(t[p]), lambda j: int(lo[j]), b - a)
+        i_, r_, n_ = _rate_series(k, v[k], lambda p: int(t[p]), lambda j: int(lo[j]), b - a,
+                                  mode, lambda j: int(t[j]), window_ms)
         inc[a:b], rt[a:b], nr[a:b] = i_, r_, n_
     return inc, rt, nr
 

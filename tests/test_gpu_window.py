@@ -316,3 +316,25 @@ def test_ragged_tiled_kernel_more_series_starts_than_fit(eng):
     ts = np.cumsum(15_000 + rng.integers(-2000, 2001, N)).astype(np.int64)
     val = np.round(rng.uniform(0, 100, N), 3); val[rng.random(N) < 0.02] = np.nan
     _check_ragged(eng, {"ts": ts, "val": val, "off": off}, 900_000)
+
+
+@pytest.mark.parametrize("w", [9, 60, 1030])
+def test_extrapolated_rate_mode(eng, w):
+    d = synth.dense(1, 2, 3, 2600, seed=w, all_counters=True, reset_prob=0.02, nan_frac=0.05)
+    x = d["val"].reshape(6, 2600); x[5, :2200] = np.nan; x[4, 100:400] = np.nan
+    inc, rt, nr = eng.rate(x, w, 15000, mode=1)
+    oinc, ort, onr = O.rate(x, w, 15000, mode=1)
+    assert np.array_equal(_np(nr), onr)
+    sc = O.rate_scale(x, w) * 2.0
+    assert_close(_np(inc), oinc, scale=sc, rtol=1e-12, what="extrapolated increase")
+    assert_close(_np(rt), ort, scale=sc / 15.0, rtol=1e-12, what="extrapolated rate")
+
+
+def test_extrapolated_rate_mode_ragged(eng):
+    d = synth.ragged(150, seed=11, mean_len=200, nan_frac=0.03, stale_frac=0.01, gap_frac=0.03)
+    d["val"] = np.abs(np.cumsum(np.where(np.isnan(d["val"]), 0.0, d["val"])) % 5000.0)   # counter-like with resets
+    inc, rt, nr = eng.rate_ragged(d["ts"], d["val"], d["off"], 900_000, mode=1)
+    oinc, ort, onr = O.rate_ragged(d["ts"], d["val"], d["off"], 900_000, mode=1)
+    assert np.array_equal(_np(nr), onr)
+    assert_close(_np(inc), oinc, scale=np.full(len(oinc), 1e4), rtol=1e-12, what="ragged extrapolated increase")
+    assert_close(_np(rt), ort, scale=np.full(len(ort), 1e3), rtol=1e-12, what="ragged extrapolated rate")

@@ -178,3 +178,23 @@ def test_ragged_rolling_matches_pandas_time_window():
         assert_exact_or_nan(mn[a:b], r.min().values); assert_exact_or_nan(mx[a:b], r.max().values)
         assert np.array_equal(cnt[a:b], r.count().values.astype(np.int32))
         assert_close(mean[a:b], r.mean().values, rtol=1e-12)
+
+
+def test_extrapolated_rate_matches_prometheus_examples():
+    """Hand-checked extrapolatedRate cases (promql/functions.go): dense counter, counter that starts
+    mid-window (zero-crossing cap), and a window edge further than 1.1 spacings away."""
+    # dense: 60 points 15 s apart over a 900 s window: first is 15 s after the window start -> full stretch
+    x = np.arange(100, dtype=np.float64)[None, :] * 30.0 + 1000.0
+    inc, rt, _ = O.rate(x, 60, 15000, mode=1)
+    j = 80
+    raw = 59 * 30.0
+    assert np.isclose(inc[0, j], raw * 900.0 / 885.0, rtol=1e-15) and np.isclose(rt[0, j], inc[0, j] / 900.0, rtol=1e-15)
+    # counter born inside the window at a small value: start extrapolation capped at the zero crossing
+    y = np.full((1, 100), np.nan); y[0, 50:] = 3.0 + 30.0 * np.arange(50)
+    inc, rt, _ = O.rate(y, 60, 15000, mode=1)
+    j = 60                                              # samples at 50..60, first value 3, raw = 300 over 150 s
+    to_zero = 150.0 * (3.0 / 300.0)
+    assert np.isclose(inc[0, j], 300.0 * (150.0 + to_zero) / 150.0, rtol=1e-15)
+    # mode 0 unchanged
+    inc0, rt0, _ = O.rate(y, 60, 15000)
+    assert inc0[0, j] == 300.0 and rt0[0, j] == 2.0
