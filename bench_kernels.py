@@ -88,10 +88,19 @@ def main():
     t0 = time.perf_counter()
     body = synth.to_matrix_json(d1["labels"], d1["ts"], d1["val"], d1["off"])
     t_fmt = time.perf_counter() - t0
+    tokenize(body, threads=1)                                  # touch the pages once
     t0 = time.perf_counter()
-    tok = tokenize(body)
+    tok = tokenize(body, threads=1)
     t_tok = time.perf_counter() - t0
     n1 = tok.n_samples
+    ncpu = os.cpu_count() or 1
+    tokenize(body, threads=ncpu)
+    t0 = time.perf_counter()
+    tokenize(body, threads=ncpu)
+    t_mt = time.perf_counter() - t0
+    print(f"tokenizer (host, {ncpu} threads): {n1 / t_mt / 1e6:.1f} M samples/s, {len(body) / t_mt / 1e9:.2f} GB/s")
+    rows.append({"kernel": f"X1 tokenizer (host C++, {ncpu} threads)", "samples": n1, "ms": t_mt * 1e3,
+                 "samples_per_s": n1 / t_mt, "bytes_per_sample": len(body) / n1, "GBps": len(body) / t_mt / 1e9})
     print(f"tokenizer (host, 1 core): {len(body) / 1e6:.1f} MB, {n1 / 1e6:.2f} M samples in {t_tok * 1e3:.1f} ms = "
           f"{n1 / t_tok / 1e6:.1f} M samples/s, {len(body) / t_tok / 1e9:.2f} GB/s (text formatting took {t_fmt:.1f} s)")
     rows.append({"kernel": "X1 tokenizer (host C++, 1 core)", "samples": n1, "ms": t_tok * 1e3, "samples_per_s": n1 / t_tok,

@@ -76,6 +76,14 @@ int pmx_tokenize(const char* h_body, size_t len,
                  int64_t* h_series_off, uint32_t* h_metric_off, uint32_t* h_metric_len,
                  int64_t cap_series, char* h_extra, size_t cap_extra,
                  pmx_tokenize_result* res);
+/* Same result with the result array cut at series boundaries and walked by n_threads host threads
+ * (bodies >= 1 MiB in Prometheus' canonical envelope; everything else is passed to pmx_tokenize).
+ * Decoded escaped tokens keep their raw length in h_extra, so extra_len may be larger. */
+int pmx_tokenize_mt(const char* h_body, size_t len,
+                    uint32_t* h_ts_off, uint32_t* h_val_off, int64_t cap_samples,
+                    int64_t* h_series_off, uint32_t* h_metric_off, uint32_t* h_metric_len,
+                    int64_t cap_series, char* h_extra, size_t cap_extra, int n_threads,
+                    pmx_tokenize_result* res);
 
 /* ---- X2 / H2  value decode (K1).  Replaces float(metric["value"][1]) at app.py:188: decimal
  * text -> binary64, correctly rounded, bit-exact with CPython float() for ASCII input (sign,

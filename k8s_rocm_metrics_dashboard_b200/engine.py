@@ -39,12 +39,17 @@ class Tokens:
         return [json.loads(bytes(body[o:o + n])) if n else {} for o, n in self.metric_spans]
 
 
-def tokenize(body: bytes) -> Tokens:
-    """X1 on the host (C++, no Python objects per sample).  Raises ValueError on a malformed body."""
+def tokenize(body: bytes, threads=None) -> Tokens:
+    """X1 on the host (C++, no Python objects per sample).  Raises ValueError on a malformed body.
+    Bodies of 1 MiB and more are cut at series boundaries and walked by ``threads`` host threads
+    (default: the host's cores, at most 32); ``threads=1`` forces the single walk."""
     if isinstance(body, str):
         body = body.encode("utf-8")
     lib = _abi.lib()
     n = len(body)
+    if threads is None:
+        import os
+        threads = min(32, os.cpu_count() or 1)
     cap_s, cap_r = n // 8 + 1, n // 24 + 1
     ts_off = np.empty(cap_s, dtype=np.uint32)
     val_off = np.empty(cap_s, dtype=np.uint32)
@@ -53,9 +58,14 @@ def tokenize(body: bytes) -> Tokens:
     m_len = np.empty(cap_r, dtype=np.uint32)
     extra = np.empty(n + 16, dtype=np.uint8)
     res = _abi.TokenizeResult()
-    rc = lib.pmx_tokenize(body, n, ts_off.ctypes.data, val_off.ctypes.data, cap_s,
-                          series_off.ctypes.data, m_off.ctypes.data, m_len.ctypes.data, cap_r,
-                          extra.ctypes.data, extra.size, C.byref(res))
+    if threads > 1 and n >= (1 << 20):
+        rc = lib.pmx_tokenize_mt(body, n, ts_off.ctypes.data, val_off.ctypes.data, cap_s,
+                                 series_off.ctypes.data, m_off.ctypes.data, m_len.ctypes.data, cap_r,
+                                 extra.ctypes.data, extra.size, threads, C.byref(res))
+    else:
+        rc = lib.pmx_tokenize(body, n, ts_off.ctypes.data, val_off.ctypes.data, cap_s,
+                              series_off.ctypes.data, m_off.ctypes.data, m_len.ctypes.data, cap_r,
+                              extra.ctypes.data, extra.size, C.byref(res))
     if rc == _abi.E_KEY:
         raise KeyError("result")
     if rc != _abi.OK:

@@ -181,3 +181,34 @@ def test_timestamp_parser_host(host_lib):
         out = C.c_int64()
         b = tok.encode()
         assert host_lib.host_parse_ts_ms(b, C.c_int64(len(b)), C.byref(out)) != 0, tok
+
+
+def test_tokenizer_multithreaded_equals_single_walk():
+    """pmx_tokenize_mt (series-boundary chunks, count + fill passes) against the single walk on a
+    body above its 1 MiB threshold, with escaped value tokens and a warnings tail."""
+    d = synth.dense(4, 8, 6, 400, seed=8, nan_frac=0.01)
+    body = synth.to_matrix_json(d["labels"], d["ts"], d["val"], d["off"])
+    assert len(body) > (1 << 20)
+    # a few escaped value tokens (decoded copies go to the extra region) and a tail after "data"
+    body = body.replace(b'"NaN"', b'"N\\u0061N"', 7)
+    body = body[:-1] + b',"warnings":["x]}","y"],"infos":[]}'
+    one = tokenize(body, threads=1)
+    for th in (2, 5, 16):
+        mt = tokenize(body, threads=th)
+        assert mt.result_type == one.result_type and mt.n_series == one.n_series and mt.n_samples == one.n_samples
+        assert np.array_equal(mt.series_off, one.series_off)
+        assert np.array_equal(mt.ts_off, one.ts_off)
+        assert mt.metric_spans == one.metric_spans
+        assert _tok_text(mt, mt.val_off, 0x22) == _tok_text(one, one.val_off, 0x22)
+    assert sum(1 for o in one.val_off if o >= len(body)) == 7
+
+
+def test_tokenizer_multithreaded_reports_errors_like_single_walk():
+    d = synth.dense(4, 8, 6, 400, seed=9)
+    body = synth.to_matrix_json(d["labels"], d["ts"], d["val"], d["off"])
+    broken = body[:700_000] + b"]" + body[700_000:]            # stray bracket deep inside one chunk
+    for th in (1, 8):
+        with pytest.raises(ValueError):
+            tokenize(broken, threads=th)
+    not_canonical = b' ' + body                                  # leading space: plain walk serves it
+    assert tokenize(not_canonical, threads=8).n_samples == 192 * 400
