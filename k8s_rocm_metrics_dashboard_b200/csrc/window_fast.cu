@@ -269,6 +269,8 @@ window_fast_kernel(const WinParams p) {
 
   int64_t base = 0, len = 0, cursor = -1;
   if (ALIGN) { base = p.off[s]; len = p.off[s + 1] - base; }
+  // ts and val must share the 16-byte phase for the paired loads
+  const bool vec_in = ALIGN && ((reinterpret_cast<uintptr_t>(p.ts) | reinterpret_cast<uintptr_t>(p.val)) & 15) == 0;
   bool first = true;
   const int e0 = t * E;
 
@@ -298,15 +300,44 @@ window_fast_kernel(const WinParams p) {
         const int64_t* gts = p.ts + base;
         const double* gv = p.val + base;
         int64_t tk[E + 1]; double vk[E];
+        // 128-bit loads when all nine samples exist; the pairing follows the parity of the first
+        // sample's address (the same for every thread of the CTA: e0 is a multiple of 8).
+        // (256-bit loads of three aligned groups + selection by phase were slower: 48 more live
+        // registers, spills; 0.703 ms against 0.659 ms.)
+        const bool inside = k0 >= 0 && k0 + E < len;
+        const bool odd = ((reinterpret_cast<uintptr_t>(gts + k0) >> 3) & 1) != 0;
+        if (inside && vec_in && !odd) {
 #pragma unroll
-        for (int r = 0; r <= E; ++r) {
-          const int64_t k = k0 + r;
-          tk[r] = (k >= 0 && k < len) ? gts[k] : (k < 0 ? (int64_t)0x8000000000000000LL : 0x7fffffffffffffffLL);
-        }
+          for (int r = 0; r < E; r += 2) {
+            const longlong2 a2 = *reinterpret_cast<const longlong2*>(gts + k0 + r);
+            const double2 v2 = *reinterpret_cast<const double2*>(gv + k0 + r);
+            tk[r] = a2.x; tk[r + 1] = a2.y; vk[r] = v2.x; vk[r + 1] = v2.y;
+          }
+          tk[E] = gts[k0 + E];
+        } else if (inside && vec_in) {
+          tk[0] = gts[k0]; vk[0] = gv[k0];
 #pragma unroll
-        for (int r = 0; r < E; ++r) {
-          const int64_t k = k0 + r;
-          vk[r] = (k >= 0 && k < len) ? gv[k] : pmx_nan();
+          for (int r = 1; r < E; r += 2) {
+            const longlong2 a2 = *reinterpret_cast<const longlong2*>(gts + k0 + r);
+            tk[r] = a2.x; tk[r + 1] = a2.y;
+          }
+#pragma unroll
+          for (int r = 1; r + 1 < E; r += 2) {
+            const double2 v2 = *reinterpret_cast<const double2*>(gv + k0 + r);
+            vk[r] = v2.x; vk[r + 1] = v2.y;
+          }
+          vk[E - 1] = gv[k0 + E - 1];
+        } else {
+#pragma unroll
+          for (int r = 0; r <= E; ++r) {
+            const int64_t k = k0 + r;
+            tk[r] = (k >= 0 && k < len) ? gts[k] : (k < 0 ? (int64_t)0x8000000000000000LL : 0x7fffffffffffffffLL);
+          }
+#pragma unroll
+          for (int r = 0; r < E; ++r) {
+            const int64_t k = k0 + r;
+            vk[r] = (k >= 0 && k < len) ? gv[k] : pmx_nan();
+          }
         }
         int64_t g = tbase + (int64_t)e0 * p.step_ms;
 #pragma unroll
