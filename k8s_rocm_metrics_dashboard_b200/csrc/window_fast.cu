@@ -543,7 +543,9 @@ window_fast_kernel(const WinParams p) {
         }
       }
     }
-    __syncthreads();                                              // S/T free for the next tile
+    // S/T must not be overwritten before every thread has read them.  With ALIGN the next tile's
+    // vote barrier (__syncthreads_and, before any shared-memory write) already orders that.
+    if (!ALIGN) __syncthreads();
   }
 }
 
