@@ -10,8 +10,9 @@
 //     drop; the telescoped form of (last - first) + pre-reset values, equal within a few ulp of
 //     the increments), so a window's increase is suffix + chunk totals + prefix like the sum, and
 //     no first/last value has to be fetched.  Junction deltas between chunks are formed on the
-//     fly while the chunk totals are folded.  Only windows whose first chunk part is empty (NaN
-//     runs) take a short out-of-line loop over chunk totals;
+//     fly while the chunk totals are folded; the fold also keeps the variant that starts inside the
+//     folded chunks, which is what a window needs whose first chunk part is empty (NaN runs and
+//     the start of every series);
 //   * divisions are replaced by two per-CTA tables in shared memory (1/n and 1000/(k*step));
 //   * the align stage starts from "one sample per step" as its guess and only binary-searches the
 //     staged timestamps when the guess is wrong; indices are 32-bit, shared memory is addressed
@@ -123,27 +124,6 @@ __device__ __noinline__ double align_one_global(const int64_t* __restrict__ ts, 
 
 __device__ __forceinline__ double delta_of(double cur, double prev) { return cur < prev ? cur : cur - prev; }
 
-// Increase of a window whose first chunk part [l, end of chunk lchunk] holds no sample: walk the
-// chunk totals forward from the first non-empty chunk before the own chunk t, forming junction
-// deltas on the way.  Cold (needs a NaN run).  Returns fpos (>= 0) and, in out[0..1], the delta sum
-// up to the own chunk and the last valid value before it; -1 when the window lies in the own chunk.
-__device__ __noinline__ int rate_skip_empty(const double* T_fv, const double* T_lv, const double* T_di,
-                                            const uint32_t* T_meta, int lchunk, int t, double* out) {
-  for (int k = lchunk + 1; k < t; ++k) {
-    const uint32_t m = T_meta[k];
-    if ((m >> 4) & 0xf) {
-      double acc = T_di[k], lv = T_lv[k];
-      for (int k2 = k + 1; k2 < t; ++k2) {
-        if ((T_meta[k2] >> 4) & 0xf) { acc += T_di[k2] + delta_of(T_fv[k2], lv); lv = T_lv[k2]; }
-      }
-      out[0] = acc;
-      out[1] = lv;
-      return k * E + (int)((m >> 8) & 7);
-    }
-  }
-  return -1;
-}
-
 // General tile (gaps, several samples per grid step, series ends): stage the samples that can
 // serve the tile in shared memory as 32-bit tile-relative timestamps + values, then guess / verify /
 // binary-search per thread and walk forward.  Out of line: regular tiles never come here, and the
@@ -242,8 +222,7 @@ window_fast_kernel(const WinParams p) {
   double* T_di = T_lv + NT;
   uint32_t* T_meta = reinterpret_cast<uint32_t*>(T_di + NT);
   int64_t* s_cursor = reinterpret_cast<int64_t*>(T_meta + NT);
-  double* s_cold = reinterpret_cast<double*>(s_cursor + 2);        // 2 doubles per thread for the cold rate path
-  double* rcp = s_cold + 2 * NT;                                   // rcp[n] = 1/n, n <= w
+  double* rcp = reinterpret_cast<double*>(s_cursor + 2);           // rcp[n] = 1/n, n <= w
   double* rdt = rcp + (p.w + 1);                                   // rdt[k] = 1000/(k*step_ms), k < w
 
   const int t = threadIdx.x;
@@ -475,6 +454,10 @@ window_fast_kernel(const WinParams p) {
       // fold the delta sums of the chunks between the window start and the own chunk, forming the
       // junction delta of every non-empty chunk with the last valid value before it
       double md = 0.0, md2 = 0.0;
+      // mdB / bfpos: the same fold over the near chunks, started inside them (no junction into the
+      // first non-empty one) -- what a window needs whose first chunk part holds no sample
+      double mdB = 0.0; int bfpos = -1;
+      double accF = 0.0; int fposF = -1;                          // ... and the same for "far" windows
       double clv = 0.0; int clpos = -1;                            // last valid value / position before the own chunk
       if (t - qa - 1 >= 0) {
         const uint32_t m = T_meta[t - qa - 1];
@@ -484,18 +467,25 @@ window_fast_kernel(const WinParams p) {
         const int k = t - qa;
         const uint32_t m = T_meta[k];
         if ((m >> 4) & 0xf) {
-          md2 = T_di[k] + (clpos >= 0 ? delta_of(T_fv[k], clv) : 0.0);
+          accF = T_di[k];
+          md2 = accF + (clpos >= 0 ? delta_of(T_fv[k], clv) : 0.0);
+          fposF = k * E + (int)((m >> 8) & 7);
           clv = T_lv[k]; clpos = k * E + (int)((m >> 12) & 7);
         }
       }
       for (int k = kfirst; k < t; ++k) {
         const uint32_t m = T_meta[k];
         if ((m >> 4) & 0xf) {
-          md += T_di[k] + (clpos >= 0 ? delta_of(T_fv[k], clv) : 0.0);
+          const double di = T_di[k];
+          const double j = clpos >= 0 ? delta_of(T_fv[k], clv) : 0.0;
+          md += di + j;
+          mdB += di + (bfpos >= 0 ? j : 0.0);
+          if (bfpos < 0) bfpos = k * E + (int)((m >> 8) & 7);
           clv = T_lv[k]; clpos = k * E + (int)((m >> 12) & 7);
         }
       }
       md2 += md;
+      if (fposF >= 0) accF += md; else { accF = mdB; fposF = bfpos; }
       const double Jc = (c_cn > 0 && clpos >= 0) ? delta_of(c_fv, clv) : 0.0;     // own chunk's junction delta
       double pd = 0.0, plv = 0.0;
       int pcn = 0, plpos = 0, pfpos = 0;
@@ -521,10 +511,9 @@ window_fast_kernel(const WinParams p) {
           if ((sm >> 4) & 0xf) {                                  // first chunk part holds a sample
             fpos = lchunk * E + lrow + (int)((sm >> 8) & 7);
             inc = S_d[si] + (far ? md2 : md) + pj;
-          } else {
-            fpos = rate_skip_empty(T_fv, T_lv, T_di, T_meta, lchunk, t, s_cold + 2 * t);
-            if (fpos >= 0)
-              inc = s_cold[2 * t] + pd + (pcn > 0 ? delta_of(c_fv, s_cold[2 * t + 1]) : 0.0);
+          } else {                                                // rare: NaN run or series start
+            fpos = far ? fposF : bfpos;
+            if (fpos >= 0) inc = (far ? accF : mdB) + pj;
             else { fpos = pcn > 0 ? pfpos : 0x7fffffff; inc = pd; }     // window inside the own chunk
           }
           const int lpos = pcn > 0 ? plpos : clpos;
@@ -567,7 +556,7 @@ int launch_fast(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
   p.chunks = (int32_t)((p.n_steps + p.chunk_len - 1) / p.chunk_len);
   const int64_t grid = p.n_series * p.chunks;
   if (grid > 0x7fffffffLL) return pmx_fail(PMX_E_LIMIT, "window kernel: n_series * chunks exceeds 2^31-1");
-  const size_t smem = TL::FIXED + size_t(2) * NT * 8 + size_t(2) * (p.w + 1) * 8 + 16;
+  const size_t smem = TL::FIXED + size_t(2) * (p.w + 1) * 8 + 16;
   PMX_CUDA(cudaFuncSetAttribute(window_fast_kernel<NT, ALIGN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   window_fast_kernel<NT, ALIGN><<<(unsigned)grid, NT, smem, st>>>(p);
   PMX_LAUNCH_CHECK();
