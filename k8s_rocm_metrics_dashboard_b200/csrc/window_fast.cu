@@ -368,26 +368,49 @@ window_fast_kernel(const WinParams p) {
     if (!do_roll && !do_rate) continue;
 
     // ---------------------------------------------------------------- in-chunk suffix scans
-    double c_fv;                                                  // chunk's first valid value
-    int c_cn;
+    // First as if all eight values were finite (no branches, constant counts); the chunk total
+    // tells whether that was true (any NaN or Inf makes the sum non-finite) and only then the
+    // general scan runs and overwrites what this thread stored.
+    double c_fv = a[0];                                           // chunk's first valid value
+    int c_cn = E;
     {
-      double ss = 0.0, smn = INF, smx = -INF, sd = 0.0, sfv = 0.0, lv = 0.0;
-      int scf = 0, scn = 0, foff = 0, lpos = 0;
+      double ss = a[E - 1], smn = a[E - 1], smx = a[E - 1], sd = 0.0;
+      {
+        const int si = (E - 1) * NT + t;
+        S_sum[si] = ss; S_mn[si] = smn; S_mx[si] = smx; S_d[si] = sd;
+        S_meta[si] = (uint16_t)(1 | (1 << 4));
+      }
 #pragma unroll
-      for (int r = E - 1; r >= 0; --r) {
+      for (int r = E - 2; r >= 0; --r) {
         const double v = a[r];
-        if (pmx_isfinite(v)) { ss += v; smn = dmin(smn, v); smx = dmax(smx, v); ++scf; }
-        if (v == v) {
-          if (scn > 0) sd += delta_of(sfv, v); else { lv = v; lpos = r; }
-          sfv = v; foff = r; ++scn;
-        }
+        ss += v; smn = dmin(smn, v); smx = dmax(smx, v);
+        sd += delta_of(a[r + 1], v);
         const int si = r * NT + t;
         S_sum[si] = ss; S_mn[si] = smn; S_mx[si] = smx; S_d[si] = sd;
-        S_meta[si] = (uint16_t)(scf | (scn << 4) | (((foff - r) & 7) << 8));
+        S_meta[si] = (uint16_t)((E - r) | ((E - r) << 4));
       }
-      T_sum[t] = ss; T_mn[t] = smn; T_mx[t] = smx; T_fv[t] = sfv; T_lv[t] = lv; T_di[t] = sd;
-      T_meta[t] = (uint32_t)(scf | (scn << 4) | (foff << 8) | (lpos << 12));
-      c_fv = sfv; c_cn = scn;
+      T_sum[t] = ss; T_mn[t] = smn; T_mx[t] = smx; T_fv[t] = a[0]; T_lv[t] = a[E - 1]; T_di[t] = sd;
+      T_meta[t] = (uint32_t)(E | (E << 4) | ((E - 1) << 12));
+      if (!pmx_isfinite(ss)) {
+        ss = 0.0; smn = INF; smx = -INF; sd = 0.0;
+        double sfv = 0.0, lv = 0.0;
+        int scf = 0, scn = 0, foff = 0, lpos = 0;
+#pragma unroll
+        for (int r = E - 1; r >= 0; --r) {
+          const double v = a[r];
+          if (pmx_isfinite(v)) { ss += v; smn = dmin(smn, v); smx = dmax(smx, v); ++scf; }
+          if (v == v) {
+            if (scn > 0) sd += delta_of(sfv, v); else { lv = v; lpos = r; }
+            sfv = v; foff = r; ++scn;
+          }
+          const int si = r * NT + t;
+          S_sum[si] = ss; S_mn[si] = smn; S_mx[si] = smx; S_d[si] = sd;
+          S_meta[si] = (uint16_t)(scf | (scn << 4) | (((foff - r) & 7) << 8));
+        }
+        T_sum[t] = ss; T_mn[t] = smn; T_mx[t] = smx; T_fv[t] = sfv; T_lv[t] = lv; T_di[t] = sd;
+        T_meta[t] = (uint32_t)(scf | (scn << 4) | (foff << 8) | (lpos << 12));
+        c_fv = sfv; c_cn = scn;
+      }
     }
     __syncthreads();
 
@@ -410,30 +433,41 @@ window_fast_kernel(const WinParams p) {
         mcf2 += m & 0xf; mcn2 += (m >> 4) & 0xf;
       }
       double ps = 0.0, pmn = INF, pmx = -INF; int pcf = 0, pcn = 0;
+      // The first qb outputs start one chunk further back ("far"): they use the fold that includes
+      // chunk t-qa and rows 8-qb.. of chunk t-qa-1.  qb is the same for the whole grid, so the
+      // change-over at r == qb is a uniform branch, not a select per point.
+      const int lcF = t - qa - 1 > 0 ? t - qa - 1 : 0, lcN = t - qa > 0 ? t - qa : 0;   // < 0: halo points, result unused
+      double cs = ms2, cmn = mmn2, cmx = mmx2; int ccf = mcf2, ccn = mcn2;
+      int sbase = (E - qb) * NT + lcF;                            // si = sbase + r * NT
+      if (qb == 0) { cs = ms; cmn = mmn; cmx = mmx; ccf = mcf; ccn = mcn; sbase = lcN; }
 #pragma unroll 1
       for (int h = 0; h < 2; ++h) {                               // two groups of four outputs (code size)
         double omn[4], omx[4], omean[4]; int ocnt[4];
+        unsigned bad = 0;                                         // outputs with fewer than `need` values
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const int r = 4 * h + q;
           const double v = h ? a[4 + q] : a[q];
           if (pmx_isfinite(v)) { ps += v; pmn = dmin(pmn, v); pmx = dmax(pmx, v); ++pcf; }
           pcn += (v == v) ? 1 : 0;
-          const bool far = r < qb;                                // window starts one chunk further back
-          int lchunk = far ? t - qa - 1 : t - qa;
-          const int lrow = far ? r - qb + E : r - qb;
-          if (lchunk < 0) lchunk = 0;                             // halo points only; result unused
-          const int si = lrow * NT + lchunk;
+          if (r == qb && r > 0) {
+            cs = ms; cmn = mmn; cmx = mmx; ccf = mcf; ccn = mcn; sbase = lcN - qb * NT;
+            asm volatile("" ::: "memory");                        // keep this a branch
+          }
+          const int si = sbase + r * NT;
           const uint32_t sm = S_meta[si];
-          const double ws = S_sum[si] + (far ? ms2 : ms) + ps;
-          const double wmn = dmin(dmin(S_mn[si], far ? mmn2 : mmn), pmn);
-          const double wmx = dmax(dmax(S_mx[si], far ? mmx2 : mmx), pmx);
-          const int wcf = (int)(sm & 0xf) + (far ? mcf2 : mcf) + pcf;
-          const bool ok = wcf >= need;
-          omean[q] = ok ? ws * rcp[wcf] : pmx_nan();
-          omn[q] = ok ? wmn : pmx_nan();
-          omx[q] = ok ? wmx : pmx_nan();
-          ocnt[q] = (int)((sm >> 4) & 0xf) + (far ? mcn2 : mcn) + pcn;
+          const double ws = S_sum[si] + cs + ps;
+          const int wcf = (int)(sm & 0xf) + ccf + pcf;
+          omn[q] = dmin(dmin(S_mn[si], cmn), pmn);
+          omx[q] = dmax(dmax(S_mx[si], cmx), pmx);
+          omean[q] = ws * rcp[wcf];
+          bad |= (wcf < need ? 1u : 0u) << q;
+          ocnt[q] = (int)((sm >> 4) & 0xf) + ccn + pcn;
+        }
+        if (bad) {                                                // rare: NaN runs
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            if ((bad >> q) & 1) { omn[q] = pmx_nan(); omx[q] = pmx_nan(); omean[q] = pmx_nan(); }
         }
         const int e = e0 + 4 * h;
         if (e >= HP && e + 3 < n_el) {                            // whole group inside the output range
@@ -487,39 +521,50 @@ window_fast_kernel(const WinParams p) {
       md2 += md;
       if (fposF >= 0) accF += md; else { accF = mdB; fposF = bfpos; }
       const double Jc = (c_cn > 0 && clpos >= 0) ? delta_of(c_fv, clv) : 0.0;     // own chunk's junction delta
-      double pd = 0.0, plv = 0.0;
+      double pd = 0.0, pj = 0.0, plv = 0.0;                       // own prefix without / with its junction delta
       int pcn = 0, plpos = 0, pfpos = 0;
+      const int lcF = t - qa - 1 > 0 ? t - qa - 1 : 0, lcN = t - qa > 0 ? t - qa : 0;
+      double cmd = md2, cacc = accF; int cfp = fposF;
+      int sbase = (E - qb) * NT + lcF;
+      if (qb == 0) { cmd = md; cacc = mdB; cfp = bfpos; sbase = lcN; }
 #pragma unroll 1
       for (int h = 0; h < 2; ++h) {
         double oinc[4], orate[4];
+        unsigned bad = 0;                                         // outputs with fewer than two samples
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const int r = 4 * h + q;
           const double v = h ? a[4 + q] : a[q];
           if (v == v) {
-            if (pcn > 0) pd += delta_of(v, plv); else pfpos = e0 + r;
+            if (pcn > 0) { const double d = delta_of(v, plv); pd += d; pj += d; }
+            else { pfpos = e0 + r; pj = Jc; }
             plv = v; plpos = e0 + r; ++pcn;
           }
-          const bool far = r < qb;
-          int lchunk = far ? t - qa - 1 : t - qa;
-          const int lrow = far ? r - qb + E : r - qb;
-          if (lchunk < 0) lchunk = 0;
-          const int si = lrow * NT + lchunk;
+          if (r == qb && r > 0) {
+            cmd = md; cacc = mdB; cfp = bfpos; sbase = lcN - qb * NT;
+            asm volatile("" ::: "memory");
+          }
+          const int si = sbase + r * NT;
           const uint32_t sm = S_meta[si];
           int fpos; double inc;
-          const double pj = pd + (pcn > 0 ? Jc : 0.0);            // own prefix incl. its junction
           if ((sm >> 4) & 0xf) {                                  // first chunk part holds a sample
-            fpos = lchunk * E + lrow + (int)((sm >> 8) & 7);
-            inc = S_d[si] + (far ? md2 : md) + pj;
+            fpos = e0 + r - H + (int)((sm >> 8) & 7);             // window start + offset of its first sample
+            inc = S_d[si] + cmd + pj;
           } else {                                                // rare: NaN run or series start
-            fpos = far ? fposF : bfpos;
-            if (fpos >= 0) inc = (far ? accF : mdB) + pj;
+            fpos = cfp;
+            if (fpos >= 0) inc = cacc + pj;
             else { fpos = pcn > 0 ? pfpos : 0x7fffffff; inc = pd; }     // window inside the own chunk
           }
           const int lpos = pcn > 0 ? plpos : clpos;
-          const bool have = lpos > fpos;
-          oinc[q] = have ? inc : pmx_nan();
-          orate[q] = have ? inc * rdt[have ? lpos - fpos : 0] : pmx_nan();
+          const int span = lpos - fpos;
+          oinc[q] = inc;
+          orate[q] = inc * rdt[span > 0 ? span : 0];
+          bad |= (span > 0 ? 0u : 1u) << q;
+        }
+        if (bad) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            if ((bad >> q) & 1) { oinc[q] = pmx_nan(); orate[q] = pmx_nan(); }
         }
         const int e = e0 + 4 * h;
         if (e >= HP && e + 3 < n_el) {

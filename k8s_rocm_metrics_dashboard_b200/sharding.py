@@ -106,7 +106,7 @@ class ShardedEngine:
                                       host["out"], lookback_ms)
         else:
             out = eng.fused(ts, val, off, start_ms, step_ms, n_steps, window_steps, lookback_ms, out=out)
-        sm, cnt, mn, mx, _ = eng.group_reduce(out["aligned"], None, n_seg, perm_goff=perm_goff)
+        sm, cnt, mn, mx, mean = eng.group_reduce(out["aligned"], None, n_seg, perm_goff=perm_goff)
         if self.world > 1:
             summary = combine_group_partials(sm, cnt, mn, mx, self.group)
             key = (n_seg, len(qs))
@@ -115,7 +115,7 @@ class ShardedEngine:
             q = eng.quantiles(out["aligned"], seg, n_seg, list(qs), group=self.group or _world_group(),
                               buffers=self._qbuf[key], row_order=perm_goff[0])
         else:
-            summary = combine_group_partials(sm, cnt, mn, mx, None)
+            summary = (sm, cnt, mn, mx, mean)          # one rank: the kernel's own result is the summary
             q = eng.quantiles(out["aligned"], seg, n_seg, list(qs), row_order=perm_goff[0])
         return out, summary, q
 
