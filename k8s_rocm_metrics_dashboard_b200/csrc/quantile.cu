@@ -16,6 +16,7 @@
 //
 // State per segment (uint64 words): [0] n, [1] reserved, then per target t: [2+2t] prefix,
 // [3+2t] remaining rank inside the prefix bucket.
+#include <stdlib.h>
 #include "pmx_common.cuh"
 
 namespace {
@@ -66,7 +67,7 @@ __device__ __forceinline__ void hist_add(unsigned int* h, bool hit, unsigned d, 
 
 // distinct prefixes of a segment's targets (lo/hi ranks and nearby quantiles usually share one)
 // s_urep[u] = first target that carries distinct prefix u: the kernels accumulate into that
-// target's global histogram only; hist_broadcast_kernel copies it to the other targets of u.
+// target's global histogram only; pick_kernel reads that one for every target of u.
 __device__ __forceinline__ void load_prefixes(const uint64_t* __restrict__ state, int sw, int sg, int n_t,
                                               int pass, uint64_t* s_uprefix, int* s_umap, int* s_urep,
                                               int* s_nu) {
@@ -90,7 +91,8 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
             int n_t, int pass, const uint64_t* __restrict__ state, int sw,
             unsigned long long* __restrict__ hist, int rows_per_cta, int64_t n_rows,
             const int32_t* __restrict__ order,
-            int mode, unsigned long long* __restrict__ cand, unsigned int* __restrict__ cand_cnt, unsigned cap) {
+            int mode, unsigned long long* __restrict__ cand, unsigned int* __restrict__ cand_cnt, unsigned cap,
+            unsigned int* __restrict__ cand_overflow) {
   extern __shared__ unsigned int sh[];                     // [n_uniq][BINS]
   __shared__ uint64_t s_uprefix[MAX_TARGETS];
   __shared__ int s_umap[MAX_TARGETS];
@@ -104,6 +106,7 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
   const int lane = threadIdx.x & 31;
   const int n_h = pass == 0 ? 1 : n_t;                     // histograms per segment in global memory
   int cur_seg = -1;
+  if (mode == 2 && *cand_overflow == 0) return;            // every candidate list is complete (the usual case)
 
   auto flush = [&](int sg) {
     __syncthreads();
@@ -174,7 +177,10 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
         if (mode == 1) {                                   // append to the candidate list, one atomic per warp
           const int leader = __ffs(any) - 1;
           unsigned base = 0;
-          if (lane == leader) base = atomicAdd(&cand_cnt[sg], (unsigned)__popc(any));
+          if (lane == leader) {
+            base = atomicAdd(&cand_cnt[sg], (unsigned)__popc(any));
+            if (base + (unsigned)__popc(any) > cap) *cand_overflow = 1u;
+          }
           base = __shfl_sync(0xffffffffu, base, leader);
           if (hits) {
             const unsigned pos = base + (unsigned)__popc(any & ((1u << lane) - 1u));
@@ -232,69 +238,83 @@ cand_hist_kernel(const unsigned long long* __restrict__ cand, const unsigned int
   }
 }
 
-// After the histogram kernels: targets that share a prefix share a histogram; copy the
-// representative's to the others.  grid (n_t, n_seg).
-__global__ void __launch_bounds__(256)
-hist_broadcast_kernel(unsigned long long* __restrict__ hist, const uint64_t* __restrict__ state, int sw, int n_t) {
-  const int k = blockIdx.x, sg = blockIdx.y;
-  const uint64_t* st = state + (size_t)sg * sw;
-  const uint64_t pf = st[2 + 2 * k];
-  int rep = k;
-  for (int j = 0; j < k; ++j) if (st[2 + 2 * j] == pf) { rep = j; break; }
-  if (rep == k) return;
-  const unsigned long long* src = hist + ((size_t)sg * n_t + rep) * BINS;
-  unsigned long long* dst = hist + ((size_t)sg * n_t + k) * BINS;
-  for (int i = threadIdx.x; i < BINS; i += blockDim.x) dst[i] = src[i];
-}
-
-// grid (n_t, n_seg); one CTA scans one histogram
+// One CTA per segment walks the segment's targets.  Targets that share a prefix share the
+// histogram of the first of them (the hist kernels fill only that one), so all old prefixes are
+// read before any is replaced.
 __global__ void __launch_bounds__(256)
 pick_kernel(const unsigned long long* __restrict__ hist, const double* __restrict__ q, int n_q,
             int pass, uint64_t* __restrict__ state, int sw) {
-  const int tg = blockIdx.x, sg = blockIdx.y;
+  const int sg = blockIdx.x;
   const int n_t = 2 * n_q;
   const int n_h = pass == 0 ? 1 : n_t;
-  const unsigned long long* h = hist + ((size_t)sg * n_h + (pass == 0 ? 0 : tg)) * BINS;
   uint64_t* st = state + (size_t)sg * sw;
-  __shared__ unsigned long long part[256];
-  __shared__ unsigned long long s_total;
+  __shared__ uint64_t s_old[MAX_TARGETS];
+  __shared__ unsigned long long s_warp[8];
+  __shared__ uint64_t s_pf[MAX_TARGETS], s_k[MAX_TARGETS];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x < n_t) {
+    const uint64_t old = pass == 0 ? 0 : st[2 + 2 * threadIdx.x];
+    s_old[threadIdx.x] = old;
+    s_pf[threadIdx.x] = old;                                // kept if no bin holds the rank (inconsistent counts)
+    s_k[threadIdx.x] = pass == 0 ? 0 : st[3 + 2 * threadIdx.x];
+  }
+  const unsigned long long n_known = pass == 0 ? 0 : st[0];
+  __syncthreads();
+  if (pass > 0 && n_known == 0) return;                     // empty segment: nothing to select
   constexpr int PER = BINS / 256;                          // 8 bins per thread
-  unsigned long long loc[PER]; unsigned long long sum = 0;
+  for (int tg = 0; tg < n_t; ++tg) {
+    // one scan per distinct prefix: tg is a representative if no earlier target shares its prefix
+    bool is_rep = true;
+    if (pass == 0) is_rep = tg == 0;
+    else for (int j = 0; j < tg; ++j) if (s_old[j] == s_old[tg]) { is_rep = false; break; }
+    if (!is_rep) continue;
+    const unsigned long long* h = hist + ((size_t)sg * n_h + tg) * BINS;
+    unsigned long long loc[PER]; unsigned long long sum = 0;
 #pragma unroll
-  for (int i = 0; i < PER; ++i) { loc[i] = h[threadIdx.x * PER + i]; sum += loc[i]; }
-  part[threadIdx.x] = sum;
-  __syncthreads();
-  if (threadIdx.x == 0) {                                  // 256-element exclusive scan, serial
-    unsigned long long acc = 0;
-    for (int i = 0; i < 256; ++i) { unsigned long long v = part[i]; part[i] = acc; acc += v; }
-    s_total = acc;
-  }
-  __syncthreads();
-  unsigned long long k;
-  if (pass == 0) {
-    const unsigned long long n = s_total;
-    if (threadIdx.x == 0 && tg == 0) { st[0] = n; st[1] = 0; }
-    if (n == 0) { if (threadIdx.x == 0) { st[2 + 2 * tg] = 0; st[3 + 2 * tg] = 0; } return; }
-    const double pos = (double)(n - 1) * q[tg >> 1];
-    unsigned long long lo = (unsigned long long)floor(pos);
-    if (lo > n - 1) lo = n - 1;
-    const unsigned long long hi = lo + 1 < n ? lo + 1 : n - 1;
-    k = (tg & 1) ? hi : lo;
-  } else {
-    if (st[0] == 0) return;
-    k = st[3 + 2 * tg];
-  }
-  // the bin b with cum[b] <= k < cum[b+1]
-  unsigned long long acc = part[threadIdx.x];
+    for (int i = 0; i < PER; ++i) { loc[i] = h[threadIdx.x * PER + i]; sum += loc[i]; }
+    // block-wide exclusive scan of the 256 partial sums
+    unsigned long long inc = sum;
 #pragma unroll
-  for (int i = 0; i < PER; ++i) {
-    if (k >= acc && k < acc + loc[i]) {
-      const uint64_t old = pass == 0 ? 0 : st[2 + 2 * tg];
-      st[2 + 2 * tg] = (old << digit_bits(pass)) | (uint64_t)(threadIdx.x * PER + i);
-      st[3 + 2 * tg] = k - acc;
+    for (int d = 1; d < 32; d <<= 1) {
+      const unsigned long long v = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane >= d) inc += v;
     }
-    acc += loc[i];
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    unsigned long long base = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) { const unsigned long long v = s_warp[w]; if (w < warp) base += v; total += v; }
+    if (pass == 0) {
+      if (threadIdx.x == 0) { st[0] = total; st[1] = 0; }
+      if (total == 0) { if (threadIdx.x < n_t) { st[2 + 2 * threadIdx.x] = 0; st[3 + 2 * threadIdx.x] = 0; } return; }
+    }
+    for (int j = tg; j < n_t; ++j) {                        // every target that shares this histogram
+      if (pass > 0 && s_old[j] != s_old[tg]) continue;
+      unsigned long long k;
+      if (pass == 0) {
+        const unsigned long long n = total;
+        const double pos = (double)(n - 1) * q[j >> 1];
+        unsigned long long lo = (unsigned long long)floor(pos);
+        if (lo > n - 1) lo = n - 1;
+        const unsigned long long hi = lo + 1 < n ? lo + 1 : n - 1;
+        k = (j & 1) ? hi : lo;
+      } else {
+        k = st[3 + 2 * j];                                  // written by an earlier pass only
+      }
+      // the bin b with cum[b] <= k < cum[b+1]
+      unsigned long long acc = base + inc - sum;
+#pragma unroll
+      for (int i = 0; i < PER; ++i) {
+        if (k >= acc && k < acc + loc[i]) {
+          s_pf[j] = (s_old[j] << digit_bits(pass)) | (uint64_t)(threadIdx.x * PER + i);
+          s_k[j] = k - acc;
+        }
+        acc += loc[i];
+      }
+    }
+    __syncthreads();                                        // s_warp is reused by the next scan
   }
+  if (threadIdx.x < n_t) { st[2 + 2 * threadIdx.x] = s_pf[threadIdx.x]; st[3 + 2 * threadIdx.x] = s_k[threadIdx.x]; }
 }
 
 __global__ void finish_kernel(const uint64_t* __restrict__ state, int sw, int64_t n_seg,
@@ -359,7 +379,7 @@ int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
     if (c > (1 << 20)) c = 1 << 20;
     if (c < 4096) c = 4096;
     cap = (unsigned)c;
-    const size_t hdr = ((size_t)n_seg * sizeof(unsigned int) + 255) & ~size_t(255);
+    const size_t hdr = ((size_t)(n_seg + 1) * sizeof(unsigned int) + 255) & ~size_t(255);   // counts + overflow flag
     unsigned char* scr = (unsigned char*)pmx_scratch(ctx, PMX_SCR_QCAND, hdr + (size_t)n_seg * cap * 8);
     if (!scr) return PMX_E_CUDA;
     cand_cnt = (unsigned int*)scr;
@@ -380,19 +400,16 @@ int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
   if (!d_row_order) n_rows = n_series;
   PMX_REQUIRE(n_rows >= 0 && n_rows <= n_series, "n_rows out of range");
   if (n_rows == 0) return PMX_OK;
-  int64_t want_ctas = (int64_t)ctx->sm_count * 16;
+  static int cta_mul = 0;
+  if (!cta_mul) { const char* e = getenv("PMX_HIST_CTAS_MUL"); cta_mul = e && atoi(e) > 0 ? atoi(e) : 16; }
+  int64_t want_ctas = (int64_t)ctx->sm_count * cta_mul;
   int64_t rows = (n_rows + want_ctas - 1) / want_ctas;
   if (rows < 1) rows = 1;
   const int64_t grid = (n_rows + rows - 1) / rows;
   hist_kernel<<<(unsigned)grid, 256, smem, st>>>(d_x, n_steps, d_seg, n_t, pass, d_state, state_words(n_q),
                                                 (unsigned long long*)d_hist, (int)rows, n_rows, d_row_order, mode,
-                                                cand, cand_cnt, cap);
+                                                cand, cand_cnt, cap, cand_cnt ? cand_cnt + n_seg : nullptr);
   PMX_LAUNCH_CHECK();
-  if (pass > 0) {
-    dim3 bgrid((unsigned)n_t, (unsigned)n_seg);
-    hist_broadcast_kernel<<<bgrid, 256, 0, st>>>((unsigned long long*)d_hist, d_state, state_words(n_q), n_t);
-    PMX_LAUNCH_CHECK();
-  }
   return PMX_OK;
 }
 
@@ -404,8 +421,7 @@ int pmx_quantile_pick(pmx_ctx* ctx, const uint64_t* d_hist, int64_t n_seg, const
   PMX_REQUIRE(pass >= 0 && pass < PMX_QUANTILE_PASSES, "pass out of range");
   if (n_seg == 0) return PMX_OK;
   PMX_REQUIRE(d_hist && d_q && d_state, "NULL buffer");
-  dim3 grid((unsigned)(2 * n_q), (unsigned)n_seg);
-  pick_kernel<<<grid, 256, 0, pmx_st(stream)>>>((const unsigned long long*)d_hist, d_q, (int)n_q, pass, d_state,
+  pick_kernel<<<(unsigned)n_seg, 256, 0, pmx_st(stream)>>>((const unsigned long long*)d_hist, d_q, (int)n_q, pass, d_state,
                                                state_words(n_q));
   PMX_LAUNCH_CHECK();
   return PMX_OK;

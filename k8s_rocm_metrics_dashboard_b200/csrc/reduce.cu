@@ -36,13 +36,33 @@ static __device__ __align__(256) unsigned char g_noalloc_partials[NOALLOC_MAX_SE
 constexpr int NOALLOC_MAX_DEVICES = 64;
 static Part* g_noalloc_addr[NOALLOC_MAX_DEVICES];      // device address of the array, per CUDA device
 
-// one CTA per series: partial (sum, min, max, count) over all steps -> part[s]
+__device__ __forceinline__ void ld4(const double* p, double& a, double& b, double& c, double& d) {
+  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p));
+}
+
+// one CTA per series: partial (sum, min, max, count) over all steps -> part[s].
+// The row is read as 32-byte groups (two per thread in flight) between a scalar head and tail; the
+// order in which a thread meets its values is fixed by the row's address and length alone.
 __global__ void __launch_bounds__(256)
 series_partial_kernel(const double* __restrict__ x, int64_t n_steps, Part* __restrict__ part) {
   const int64_t s = blockIdx.x;
   const double* xr = x + s * n_steps;
   Part p = part_identity();
-  for (int64_t j = threadIdx.x; j < n_steps; j += blockDim.x) part_add(p, xr[j]);
+  int64_t head = (int64_t)((0 - (reinterpret_cast<uintptr_t>(xr) >> 3)) & 3);   // values before a 32-byte boundary
+  if (head > n_steps) head = n_steps;
+  if ((int64_t)threadIdx.x < head) part_add(p, xr[threadIdx.x]);
+  const double* xb = xr + head;
+  const int64_t nb = (n_steps - head) >> 2;                                     // whole groups of four
+  for (int64_t g = threadIdx.x; g < nb; g += 2 * blockDim.x) {
+    double a0, a1, a2, a3, b0, b1, b2, b3;
+    const int64_t g2 = g + blockDim.x;
+    ld4(xb + 4 * g, a0, a1, a2, a3);
+    if (g2 < nb) ld4(xb + 4 * g2, b0, b1, b2, b3);
+    part_add(p, a0); part_add(p, a1); part_add(p, a2); part_add(p, a3);
+    if (g2 < nb) { part_add(p, b0); part_add(p, b1); part_add(p, b2); part_add(p, b3); }
+  }
+  const int64_t tail = head + 4 * nb + threadIdx.x;
+  if (tail < n_steps) part_add(p, xr[tail]);
 #pragma unroll
   for (int d = 16; d >= 1; d >>= 1) { Part q = part_shfl_down(p, d); part_merge(p, q); }
   __shared__ Part sh[8];

@@ -377,7 +377,7 @@ class Engine:
                 self._ptr(outs["n"]),
                 self._ptr(outs["lo"]), self._ptr(outs["hi"]), self._ptr(outs["x_lo"]), self._ptr(outs["x_hi"]),
                 self._ptr(outs["value"]), self._stream()))
-            self.launches += 4 * _abi.QUANTILE_PASSES - 3    # hist (two kernels from pass 3 on) + broadcast + pick + finish
+            self.launches += 3 * _abi.QUANTILE_PASSES - 2    # hist (two kernels from pass 3 on) + pick + finish
             return outs
         import torch.distributed as dist
         state, hist = buffers if buffers is not None else self.quantile_buffers(n_seg, n_q)
@@ -394,5 +394,5 @@ class Engine:
                                                 self._ptr(outs["n"]), self._ptr(outs["lo"]), self._ptr(outs["hi"]),
                                                 self._ptr(outs["x_lo"]), self._ptr(outs["x_hi"]),
                                                 self._ptr(outs["value"]), self._stream()))
-        self.launches += 4 * _abi.QUANTILE_PASSES - 3
+        self.launches += 3 * _abi.QUANTILE_PASSES - 2
         return outs
