@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libpmx.so")
+LIB_PATH = os.environ.get("PMX_LIB_PATH") or os.path.join(HERE, "libpmx.so")   # override: kernel experiments
 
 OK, E_INVALID, E_CUDA, E_VALUE, E_KEY, E_CAPACITY, E_JSON, E_LIMIT = 0, -1, -2, -3, -4, -5, -6, -7
 QUANTILE_BINS = 2048

@@ -239,7 +239,7 @@ window_fast_kernel(const WinParams p) {
   const int qa = H >> 3, qb = QB >= 0 ? QB : (H & 7);
   // shift the tile origin back so that tile element 0 sits on a 32-byte boundary of the row
   const int HP = H + (int)(((s * p.n_steps + c0 - H) % 4 + 4) % 4);
-  const int OUT = (NE - H - 3) & ~3;
+  const int OUT = (NE - HP) & ~3;                                 // >= the host's (NE - H - 3) & ~3: a full tile uses all NE points
   const bool do_roll = p.o_min || p.o_max || p.o_mean || p.o_cnt;
   const bool do_rate = p.o_inc || p.o_rate;
   const double INF = __longlong_as_double(0x7FF0000000000000LL);
