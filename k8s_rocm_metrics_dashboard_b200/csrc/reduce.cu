@@ -107,7 +107,28 @@ group_step_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* 
   const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= n_steps) return;
   Part r = part_identity();
-  for (int64_t k = goff[g]; k < goff[g + 1]; ++k) part_add(r, x[(int64_t)perm[k] * n_steps + j]);
+  // The next eight values are already on their way while the current eight are added in series
+  // order (the order of the additions is unchanged).
+  int64_t k = goff[g];
+  const int64_t k1 = goff[g + 1];
+  if (k + 8 <= k1) {
+    double v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) v[u] = x[(int64_t)perm[k + u] * n_steps + j];
+    k += 8;
+    for (; k + 8 <= k1; k += 8) {
+      double w[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) w[u] = x[(int64_t)perm[k + u] * n_steps + j];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) part_add(r, v[u]);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = w[u];
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) part_add(r, v[u]);
+  }
+  for (; k < k1; ++k) part_add(r, x[(int64_t)perm[k] * n_steps + j]);
   const bool any = r.cnt > 0;
   const int64_t o = g * n_steps + j;
   if (o_sum) o_sum[o] = r.sum;

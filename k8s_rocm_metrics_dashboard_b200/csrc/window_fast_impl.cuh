@@ -19,8 +19,9 @@
 //   * the align stage starts from "one sample per step" as its guess and only binary-searches the
 //     staged timestamps when the guess is wrong; indices are 32-bit, shared memory is addressed
 //     directly (no generic pointers).
-// Requests it does not cover (window_steps < 9 or > NE/2, n_resets / source-index outputs,
-// output rows not 32-byte aligned) go to the general kernel in window.cu.
+// Requests it does not cover (window_steps < 9 or > NE/2 with window outputs, n_resets, source
+// indices together with window outputs, output rows not 32-byte aligned) go to the general kernel
+// in window.cu.
 //
 // Shared memory per CTA (NT threads, NE = 8 NT points): four suffix arrays S_*[NE] (aliased with
 // the sample staging area and the aligned-value hand-off), chunk totals T_*[NT], the two tables.
@@ -112,15 +113,18 @@ __device__ int64_t floor_global(const int64_t* __restrict__ ts, int64_t n, int64
 // step): binary search of the series in global memory.  Cold.
 __device__ __noinline__ double align_one_global(const int64_t* __restrict__ ts, const double* __restrict__ val,
                                                 int64_t cur, int64_t len, int64_t g, int64_t lookback,
-                                                int64_t* idx_out) {
+                                                int64_t* idx_out, int32_t* src_out) {
   int64_t lo = cur, hi = len;
   while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if (ts[mid] <= g) lo = mid + 1; else hi = mid; }
   const int64_t idx = lo - 1;
   *idx_out = idx;
+  *src_out = -1;
   if (idx < 0) return pmx_nan();
   const double sample = val[idx];
-  if (g - ts[idx] < lookback && (unsigned long long)__double_as_longlong(sample) != PMX_STALE_NAN_BITS)
+  if (g - ts[idx] < lookback && (unsigned long long)__double_as_longlong(sample) != PMX_STALE_NAN_BITS) {
+    *src_out = (int32_t)idx;
     return sample;
+  }
   return pmx_nan();
 }
 
@@ -135,7 +139,8 @@ template <int NT>
 __device__ __noinline__ int64_t align_general_tile(const int64_t* __restrict__ gts0, const double* __restrict__ gv0,
                                                    int64_t len, int64_t cur, int shift, int elo, int64_t tbase,
                                                    int64_t step_ms, int64_t lookback_ms, int n_el, int OUT, int e0,
-                                                   int t, double* s_val, int* s_t, double* A, int64_t* s_cursor) {
+                                                   int t, double* s_val, int* s_t, double* A, int64_t* s_cursor,
+                                                   int32_t* IA) {
   using TL = FTile<NT>;
   const int step = (int)step_ms, lookback = (int)lookback_ms;
   const int64_t rem = len - cur;
@@ -159,12 +164,14 @@ __device__ __noinline__ int64_t align_general_tile(const int64_t* __restrict__ g
     for (int r = 0; r < E; ++r) {
       const int e = e0 + r;
       double v = pmx_nan();
+      int32_t src = -1;
       if (e >= elo && e < n_el) {
         int64_t idx;
-        v = align_one_global(gts0, gv0, cur, len, tbase + (int64_t)e * step_ms, lookback_ms, &idx);
+        v = align_one_global(gts0, gv0, cur, len, tbase + (int64_t)e * step_ms, lookback_ms, &idx, &src);
         if (e == e_cur) *s_cursor = idx;
       }
       A[r * NT + t] = v;
+      if (IA) IA[r * NT + t] = src;
     }
   } else {
     // guess: one sample per grid step; staged sample 0 is the floor of element elo (or the sample
@@ -182,6 +189,7 @@ __device__ __noinline__ int64_t align_general_tile(const int64_t* __restrict__ g
       const int e = e0 + r;
       const int g = e * step;
       double v = pmx_nan();
+      int32_t src = -1;
       if (e >= elo && e < n_el) {
         if (idx + 1 < ns && s_t[pad8(idx + 1)] <= g) {
           ++idx;
@@ -190,12 +198,15 @@ __device__ __noinline__ int64_t align_general_tile(const int64_t* __restrict__ g
         if (idx >= 0) {
           const double sample = s_val[pad8(idx)];
           if (g - s_t[pad8(idx)] < lookback &&
-              (unsigned long long)__double_as_longlong(sample) != PMX_STALE_NAN_BITS)
+              (unsigned long long)__double_as_longlong(sample) != PMX_STALE_NAN_BITS) {
             v = sample;
+            src = (int32_t)(cur + idx);
+          }
         }
         if (e == e_cur) *s_cursor = idx >= 0 ? cur + idx : -1;
       }
       A[r * NT + t] = v;
+      if (IA) IA[r * NT + t] = src;
     }
   }
   __syncthreads();                                                // staging dead, cursor visible
@@ -204,7 +215,8 @@ __device__ __noinline__ int64_t align_general_tile(const int64_t* __restrict__ g
 
 // QB = (window_steps - 1) & 7 as a compile-time constant (the output loops then unroll with every
 // "far / near" choice and every shared-memory row offset folded), or -1 for any window.
-template <int NT, bool ALIGN, int QB>
+// IDX: also write the source index of every aligned point (pmx_align; no window outputs then).
+template <int NT, bool ALIGN, int QB, bool IDX = false>
 __global__ void __launch_bounds__(NT, (NT == 256 ? 2 : PMX_FAST_CTAS_128))
 window_fast_kernel(const WinParams p) {
   using TL = FTile<NT>;
@@ -264,6 +276,7 @@ window_fast_kernel(const WinParams p) {
     const int64_t row = s * p.n_steps + j0;                       // multiple of 4
 
     double a[E];
+    int32_t src[IDX ? E : 1];                                     // series-relative sample index or -1
     if (ALIGN) {
       const int elo = j0 < 0 ? (int)(-j0) : 0;                    // first element with a grid point
       const int64_t tbase = p.start_ms + j0 * p.step_ms;          // grid time of tile element 0
@@ -339,8 +352,9 @@ window_fast_kernel(const WinParams p) {
 #pragma unroll
           for (int r = 0; r < E; ++r) {
             ok = ok && lo[r + 1] < st32;
-            a[r] = (lo[r] < lb32 && (unsigned long long)__double_as_longlong(vk[r]) != PMX_STALE_NAN_BITS)
-                       ? vk[r] : pmx_nan();
+            const bool valid = lo[r] < lb32 && (unsigned long long)__double_as_longlong(vk[r]) != PMX_STALE_NAN_BITS;
+            a[r] = valid ? vk[r] : pmx_nan();
+            if (IDX) src[r] = valid ? (int32_t)(k0 + r) : -1;
           }
           ok = ok && hor == 0;
         } else {
@@ -348,11 +362,14 @@ window_fast_kernel(const WinParams p) {
           for (int r = 0; r < E; ++r, g += p.step_ms) {
             const int e = e0 + r;
             double v = pmx_nan();
+            if (IDX) src[r] = -1;
             if (e >= elo && e < n_el) {
               ok = ok && tk[r] <= g && tk[r + 1] > g;
               if (k0 + r >= 0 && g - tk[r] < p.lookback_ms &&
-                  (unsigned long long)__double_as_longlong(vk[r]) != PMX_STALE_NAN_BITS)
+                  (unsigned long long)__double_as_longlong(vk[r]) != PMX_STALE_NAN_BITS) {
                 v = vk[r];
+                if (IDX) src[r] = (int32_t)(k0 + r);
+              }
             }
             a[r] = v;
           }
@@ -362,9 +379,14 @@ window_fast_kernel(const WinParams p) {
         cursor = cur + (OUT - elo - shift);
       } else {
         cursor = align_general_tile<NT>(p.ts + base, p.val + base, len, cur, shift, elo, tbase, p.step_ms,
-                                        p.lookback_ms, n_el, OUT, e0, t, s_val, s_t, A, s_cursor);
+                                        p.lookback_ms, n_el, OUT, e0, t, s_val, s_t, A, s_cursor,
+                                        IDX ? reinterpret_cast<int32_t*>(S_mx) : nullptr);
 #pragma unroll
         for (int r = 0; r < E; ++r) a[r] = A[r * NT + t];         // own elements: written by this thread
+        if (IDX) {
+#pragma unroll
+          for (int r = 0; r < E; ++r) src[r] = reinterpret_cast<int32_t*>(S_mx)[r * NT + t];
+        }
       }
       if (jt + OUT < c1) {                                        // pull the next tile's samples towards L2
         const int64_t ncur = cursor > 0 ? cursor : 0;
@@ -390,6 +412,10 @@ window_fast_kernel(const WinParams p) {
     if (p.o_aligned) {
       store4(p.o_aligned + row, e0, HP, n_el, a[0], a[1], a[2], a[3]);
       store4(p.o_aligned + row, e0 + 4, HP, n_el, a[4], a[5], a[6], a[7]);
+    }
+    if (IDX && p.o_idx) {
+      store4i(p.o_idx + row, e0, HP, n_el, src[0], src[1], src[2], src[3]);
+      store4i(p.o_idx + row, e0 + 4, HP, n_el, src[4], src[5], src[6], src[7]);
     }
     if (!do_roll && !do_rate) continue;
 
@@ -601,7 +627,7 @@ window_fast_kernel(const WinParams p) {
 
 bool aligned32(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 31) == 0; }
 
-template <int NT, bool ALIGN, int QB>
+template <int NT, bool ALIGN, int QB, bool IDX = false>
 int launch_fast(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
   using TL = FTile<NT>;
   const int out_per_tile = (TL::NE - (p.w - 1) - 3) & ~3;
@@ -618,8 +644,8 @@ int launch_fast(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
   const int64_t grid = p.n_series * p.chunks;
   if (grid > 0x7fffffffLL) return pmx_fail(PMX_E_LIMIT, "window kernel: n_series * chunks exceeds 2^31-1");
   const size_t smem = TL::FIXED + size_t(2) * (p.w + 1) * 8 + 16;
-  PMX_CUDA(cudaFuncSetAttribute(window_fast_kernel<NT, ALIGN, QB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  window_fast_kernel<NT, ALIGN, QB><<<(unsigned)grid, NT, smem, st>>>(p);
+  PMX_CUDA(cudaFuncSetAttribute(window_fast_kernel<NT, ALIGN, QB, IDX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  window_fast_kernel<NT, ALIGN, QB, IDX><<<(unsigned)grid, NT, smem, st>>>(p);
   PMX_LAUNCH_CHECK();
   return PMX_OK;
 }
@@ -630,13 +656,18 @@ template <bool ALIGN>
 int launch_window_fast(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
   const int nt = window_block_threads();
   const int H = p.w - 1;
-  if (H < 8 || H > nt * E / 2 - 4) return 1;
-  if (p.o_nres || p.o_idx || p.rate_mode != 0) return 1;
+  const bool windows = p.o_min || p.o_max || p.o_mean || p.o_cnt || p.o_inc || p.o_rate;
+  if ((windows && H < 8) || H > nt * E / 2 - 4) return 1;        // plain alignment takes any window
+  if (p.o_nres || p.rate_mode != 0) return 1;
+  if (p.o_idx && (windows || !ALIGN || nt != 128 || (reinterpret_cast<uintptr_t>(p.o_idx) & 15))) return 1;
   // tile-relative timestamps are 32-bit: a tile (plus the lookback) must span < 2^30 ms
   if (p.step_ms > 0x3fffffffLL / (nt * E + 8) || p.lookback_ms >= 0x3fffffffLL) return 1;
   if (!aligned32(p.o_aligned) || !aligned32(p.o_min) || !aligned32(p.o_max) || !aligned32(p.o_mean) ||
       !aligned32(p.o_inc) || !aligned32(p.o_rate) || (reinterpret_cast<uintptr_t>(p.o_cnt) & 15))
     return 1;
+  if constexpr (ALIGN) {
+    if (p.o_idx) return launch_fast<128, true, 0, true>(ctx, p, st);   // pmx_align with source indices
+  }
   if (nt == 128) {
     switch (H & 7) {                                              // one kernel per window phase
       case 0: return launch_fast<128, ALIGN, 0>(ctx, p, st);

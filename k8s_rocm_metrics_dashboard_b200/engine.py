@@ -205,12 +205,14 @@ class Engine:
         return mn, mx, mean, cnt
 
     # ------------------------------------------------------------------ K4
-    def rate(self, x, window_steps, step_ms, mode=0):
+    def rate(self, x, window_steps, step_ms, mode=0, want_resets=True):
+        """Increase / rate (and the number of counter resets) per trailing window of a dense
+        matrix.  ``want_resets=False`` skips n_resets, which only the general kernel produces."""
         t = self.torch
         x = self._dev(x, t.float64)
         S, T = x.shape
         inc, rt = self._empty((S, T), t.float64), self._empty((S, T), t.float64)
-        nres = self._empty((S, T), t.int32)
+        nres = self._empty((S, T), t.int32) if want_resets else None
         _abi.check(self.lib.pmx_rate(self.ctx, self._ptr(x), S, T, window_steps, step_ms, mode, self._ptr(inc),
                                      self._ptr(rt), self._ptr(nres), self._stream()))
         self.launches += 1
