@@ -186,7 +186,8 @@ int pmx_where_gt(pmx_ctx* ctx, const double* d_x, int64_t n, double threshold, d
 
 /* ---- X7  exact quantiles (K6) by radix select over order-preserving 64-bit keys.
  * Values of series s belong to segment d_seg[s] (or none if < 0).  State per segment:
- *   d_state: opaque uint64 [n_seg * (2 + 4*n_q)] owned by the caller, zeroed by pass 0.
+ *   d_state: opaque uint64 [n_seg * (3 + 4*n_q)] owned by the caller, zeroed before pass 0 or
+ *   filled by pmx_quantile_init.
  * One pass p = 0..PMX_QUANTILE_PASSES-1 is: pmx_quantile_hist (local histograms of the p-th
  * digit of the keys that match each target's prefix) -> [all-reduce d_hist across ranks, sum,
  * uint64] -> pmx_quantile_pick (device-side prefix scan: choose the bin holding each target
@@ -202,6 +203,15 @@ int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
                       const int32_t* d_seg, int64_t n_seg,
                       const int32_t* d_row_order, int64_t n_rows, int64_t n_q, int pass,
                       const uint64_t* d_state, uint64_t* d_hist, pmx_stream stream);
+/* Optional start from a group reduction.  With the count, minimum and maximum of every segment over
+ * ALL ranks (pmx_group_reduce on the same values, combined across ranks) the keys are taken
+ * relative to key(min) and the leading bits that key(max) - key(min) leaves zero are skipped, so
+ * pass 0 is not needed: after this call run passes 1..PMX_QUANTILE_PASSES (hist -> all-reduce ->
+ * pick) instead of 0..PASSES-1.  A pass does nothing for a segment whose keys are already resolved
+ * (min == max resolves at once; a range within a factor of two of one sign needs passes 1..5).
+ * d_min / d_max of an empty segment are ignored. */
+int pmx_quantile_init(pmx_ctx* ctx, const int64_t* d_count, const double* d_min, const double* d_max,
+                      int64_t n_seg, const double* d_q, int64_t n_q, uint64_t* d_state, pmx_stream stream);
 int pmx_quantile_pick(pmx_ctx* ctx, const uint64_t* d_hist, int64_t n_seg, const double* d_q,
                       int64_t n_q, int pass, uint64_t* d_state, pmx_stream stream);
 int pmx_quantile_finish(pmx_ctx* ctx, const uint64_t* d_state, int64_t n_seg, const double* d_q,

@@ -39,7 +39,36 @@ __device__ __forceinline__ double key_f64(uint64_t k) {
 }
 __host__ __device__ __forceinline__ int digit_shift(int pass) { return pass < 5 ? 53 - 11 * pass : 0; }
 __host__ __device__ __forceinline__ int digit_bits(int pass) { return pass < 5 ? 11 : 9; }
-__host__ __device__ __forceinline__ int state_words(int64_t n_q) { return 2 + 4 * (int)n_q; }
+
+// State of one segment: [0] number of values, [1] 0 for a selection that began with pass 0, or
+// (1 << 32) | Z for one that began from the segment's count / min / max (pmx_quantile_init),
+// [2] base key (the key of the minimum; 0 otherwise), then (prefix, remaining rank) per target.
+// A selection from count/min/max works on key - base, whose leading Z bits are zero for every
+// value of the segment, and starts behind them: pass p >= 1 takes bits [Z + 11(p-1), +11).
+constexpr int ST_HDR = 3;
+#define ST_PF(tg) (ST_HDR + 2 * (tg))
+#define ST_RK(tg) (ST_HDR + 2 * (tg) + 1)
+__host__ __device__ __forceinline__ int state_words(int64_t n_q) { return ST_HDR + 4 * (int)n_q; }
+
+struct Geom { int shift; int bits; int pshift; bool has_prefix; uint64_t base; };
+__device__ __forceinline__ Geom seg_geom(const uint64_t* st, int pass) {
+  Geom g;
+  const uint64_t w1 = st[1];
+  if (w1 >> 32) {
+    const int start = (int)(w1 & 0xff) + 11 * (pass - 1);         // key bits known before this pass
+    int bits = 64 - start;
+    if (bits > 11) bits = 11;
+    if (bits < 0 || pass < 1) bits = 0;                           // 0: nothing left to resolve
+    g.bits = bits; g.pshift = 64 - start; g.shift = 64 - start - bits;
+    if (g.shift < 0) g.shift = 0;
+    g.has_prefix = start > 0; g.base = st[2];
+  } else {
+    g.bits = pass < PMX_QUANTILE_PASSES ? digit_bits(pass) : 0;
+    g.shift = digit_shift(pass < 5 ? pass : 5);
+    g.pshift = 64 - 11 * pass; g.has_prefix = pass > 0; g.base = 0;
+  }
+  return g;
+}
 
 // Adds one key per lane to a CTA-private histogram.  All 32 lanes call this together (hit = this
 // lane contributes).  Lanes that fall into the same bin as the current leader are folded into one
@@ -74,7 +103,7 @@ __device__ __forceinline__ void load_prefixes(const uint64_t* __restrict__ state
   int nu = 0;
   if (pass == 0) { nu = 1; s_urep[0] = 0; }
   else for (int k = 0; k < n_t; ++k) {
-    const uint64_t pf = state[(size_t)sg * sw + 2 + 2 * k];
+    const uint64_t pf = state[(size_t)sg * sw + ST_PF(k)];
     int u = 0;
     while (u < nu && s_uprefix[u] != pf) ++u;
     if (u == nu) { s_uprefix[nu] = pf; s_urep[nu] = k; ++nu; }
@@ -99,10 +128,8 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
   __shared__ int s_urep[MAX_TARGETS];
   __shared__ int s_nu;
   __shared__ unsigned int s_bitmap[BINS / 32];             // previous digits carried by some target prefix
+  __shared__ Geom s_geom;                                  // where this pass looks in the current segment's keys
   const int64_t s0 = (int64_t)blockIdx.x * rows_per_cta;
-  const int shift = digit_shift(pass);
-  const unsigned mask = (1u << digit_bits(pass)) - 1u;
-  const int pshift = pass == 0 ? 0 : 64 - 11 * pass;       // key >> pshift == prefix  (pass >= 1)
   const int lane = threadIdx.x & 31;
   const int n_h = pass == 0 ? 1 : n_t;                     // histograms per segment in global memory
   int cur_seg = -1;
@@ -130,7 +157,10 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
       if (cur_seg >= 0) flush(cur_seg);
       __syncthreads();
       if (threadIdx.x < BINS / 32) s_bitmap[threadIdx.x] = 0;
-      if (threadIdx.x == 0) load_prefixes(state, sw, sg, n_t, pass, s_uprefix, s_umap, s_urep, &s_nu);
+      if (threadIdx.x == 0) {
+        load_prefixes(state, sw, sg, n_t, pass, s_uprefix, s_umap, s_urep, &s_nu);
+        s_geom = seg_geom(state + (size_t)sg * sw, pass);
+      }
       __syncthreads();
       if (pass > 0 && threadIdx.x < s_nu) {
         const unsigned pd = (unsigned)s_uprefix[threadIdx.x] & (BINS - 1);
@@ -141,6 +171,11 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
       __syncthreads();
     }
     const int nu = s_nu;
+    const Geom gm = s_geom;
+    if (gm.bits == 0) continue;                            // this segment's keys are fully resolved
+    const int shift = gm.shift, pshift = gm.pshift;
+    const unsigned mask = (1u << gm.bits) - 1u;
+    const uint64_t kbase = gm.base;
     const double* xr = x + s * n_steps;
     const bool vec = (reinterpret_cast<uintptr_t>(xr) & 15) == 0;
     // loop trips are warp-uniform; every lane has four elements in flight per trip
@@ -160,10 +195,10 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const bool valid = v[i] == v[i];
-        const uint64_t key = f64_key(v[i]);
+        const uint64_t key = f64_key(v[i]) - kbase;        // relative to the segment's base key
         const unsigned d = (unsigned)(key >> shift) & mask;
         if (pass == 0) { hist_add(sh, valid, d, lane, hist + (size_t)sg * BINS); continue; }
-        const uint64_t top = key >> pshift;
+        const uint64_t top = gm.has_prefix ? key >> pshift : 0;
         // cheap filter first: does any target prefix end in this key's previous digit?
         const unsigned pdig = (unsigned)top & (BINS - 1);
         const bool maybe = valid && (pass < 2 || ((s_bitmap[pdig >> 5] >> (pdig & 31)) & 1));
@@ -209,9 +244,10 @@ cand_hist_kernel(const unsigned long long* __restrict__ cand, const unsigned int
   const unsigned per = (n + gridDim.x - 1) / gridDim.x;
   const unsigned a = blockIdx.x * per, b = a + per < n ? a + per : n;
   if (a >= b) return;
-  const int shift = digit_shift(pass);
-  const unsigned mask = (1u << digit_bits(pass)) - 1u;
-  const int pshift = 64 - 11 * pass;
+  const Geom gm = seg_geom(state + (size_t)blockIdx.y * sw, pass);
+  if (gm.bits == 0) return;
+  const int shift = gm.shift, pshift = gm.pshift;
+  const unsigned mask = (1u << gm.bits) - 1u;
   const int lane = threadIdx.x & 31;
   if (threadIdx.x == 0) load_prefixes(state, sw, sg, n_t, pass, s_uprefix, s_umap, s_urep, &s_nu);
   __syncthreads();
@@ -224,7 +260,7 @@ cand_hist_kernel(const unsigned long long* __restrict__ cand, const unsigned int
     const bool in = i < b;
     const uint64_t key = in ? keys[i] : 0;
     const unsigned d = (unsigned)(key >> shift) & mask;
-    const uint64_t top = key >> pshift;
+    const uint64_t top = gm.has_prefix ? key >> pshift : 0;
     for (int u = 0; u < nu; ++u) hist_add(sh + u * BINS, in && top == s_uprefix[u], d, lane);
   }
   __syncthreads();
@@ -253,14 +289,15 @@ pick_kernel(const unsigned long long* __restrict__ hist, const double* __restric
   __shared__ uint64_t s_pf[MAX_TARGETS], s_k[MAX_TARGETS];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (threadIdx.x < n_t) {
-    const uint64_t old = pass == 0 ? 0 : st[2 + 2 * threadIdx.x];
+    const uint64_t old = pass == 0 ? 0 : st[ST_PF(threadIdx.x)];
     s_old[threadIdx.x] = old;
     s_pf[threadIdx.x] = old;                                // kept if no bin holds the rank (inconsistent counts)
-    s_k[threadIdx.x] = pass == 0 ? 0 : st[3 + 2 * threadIdx.x];
+    s_k[threadIdx.x] = pass == 0 ? 0 : st[ST_RK(threadIdx.x)];
   }
   const unsigned long long n_known = pass == 0 ? 0 : st[0];
+  const Geom gm = seg_geom(st, pass);
   __syncthreads();
-  if (pass > 0 && n_known == 0) return;                     // empty segment: nothing to select
+  if (pass > 0 && (n_known == 0 || gm.bits == 0)) return;   // empty segment, or nothing left to resolve
   constexpr int PER = BINS / 256;                          // 8 bins per thread
   for (int tg = 0; tg < n_t; ++tg) {
     // one scan per distinct prefix: tg is a representative if no earlier target shares its prefix
@@ -285,8 +322,8 @@ pick_kernel(const unsigned long long* __restrict__ hist, const double* __restric
 #pragma unroll
     for (int w = 0; w < 8; ++w) { const unsigned long long v = s_warp[w]; if (w < warp) base += v; total += v; }
     if (pass == 0) {
-      if (threadIdx.x == 0) { st[0] = total; st[1] = 0; }
-      if (total == 0) { if (threadIdx.x < n_t) { st[2 + 2 * threadIdx.x] = 0; st[3 + 2 * threadIdx.x] = 0; } return; }
+      if (threadIdx.x == 0) { st[0] = total; st[1] = 0; st[2] = 0; }
+      if (total == 0) { if (threadIdx.x < n_t) { st[ST_PF(threadIdx.x)] = 0; st[ST_RK(threadIdx.x)] = 0; } return; }
     }
     for (int j = tg; j < n_t; ++j) {                        // every target that shares this histogram
       if (pass > 0 && s_old[j] != s_old[tg]) continue;
@@ -299,14 +336,14 @@ pick_kernel(const unsigned long long* __restrict__ hist, const double* __restric
         const unsigned long long hi = lo + 1 < n ? lo + 1 : n - 1;
         k = (j & 1) ? hi : lo;
       } else {
-        k = st[3 + 2 * j];                                  // written by an earlier pass only
+        k = st[ST_RK(j)];                                  // written by an earlier pass only
       }
       // the bin b with cum[b] <= k < cum[b+1]
       unsigned long long acc = base + inc - sum;
 #pragma unroll
       for (int i = 0; i < PER; ++i) {
         if (k >= acc && k < acc + loc[i]) {
-          s_pf[j] = (s_old[j] << digit_bits(pass)) | (uint64_t)(threadIdx.x * PER + i);
+          s_pf[j] = (s_old[j] << gm.bits) | (uint64_t)(threadIdx.x * PER + i);
           s_k[j] = k - acc;
         }
         acc += loc[i];
@@ -314,7 +351,42 @@ pick_kernel(const unsigned long long* __restrict__ hist, const double* __restric
     }
     __syncthreads();                                        // s_warp is reused by the next scan
   }
-  if (threadIdx.x < n_t) { st[2 + 2 * threadIdx.x] = s_pf[threadIdx.x]; st[3 + 2 * threadIdx.x] = s_k[threadIdx.x]; }
+  if (threadIdx.x < n_t) { st[ST_PF(threadIdx.x)] = s_pf[threadIdx.x]; st[ST_RK(threadIdx.x)] = s_k[threadIdx.x]; }
+}
+
+// pmx_quantile_init: begin from what a group reduction already knows.  Every key of a segment lies
+// in [key(min), key(max)]; relative to key(min) the keys have Z = clz(key(max) - key(min)) leading
+// zero bits, so the passes start behind them and pass 0 is not needed.
+__global__ void init_kernel(const long long* __restrict__ count, const double* __restrict__ mn,
+                            const double* __restrict__ mx, const double* __restrict__ q, int n_q,
+                            uint64_t* __restrict__ state, int sw, int64_t n_seg) {
+  const int64_t sg = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (sg >= n_seg) return;
+  uint64_t* st = state + (size_t)sg * sw;
+  const long long n = count[sg];
+  int Z = 64; uint64_t base = 0;
+  if (n > 0) {
+    // a zero minimum may stand for -0.0 and a zero maximum for +0.0 (min/max do not order the two)
+    const double a = mn[sg], b = mx[sg];
+    const uint64_t ka = f64_key(a == 0.0 ? -0.0 : a), kb = f64_key(b == 0.0 ? 0.0 : b);
+    base = ka;
+    Z = kb > ka ? __clzll((long long)(kb - ka)) : 64;
+  }
+  st[0] = n > 0 ? (uint64_t)n : 0;
+  st[1] = (1ULL << 32) | (uint64_t)Z;
+  st[2] = base;
+  for (int tg = 0; tg < 2 * n_q; ++tg) {
+    unsigned long long k = 0;
+    if (n > 0) {
+      const double pos = (double)(n - 1) * q[tg >> 1];
+      unsigned long long lo = (unsigned long long)floor(pos);
+      if (lo > (unsigned long long)n - 1) lo = (unsigned long long)n - 1;
+      const unsigned long long hi = lo + 1 < (unsigned long long)n ? lo + 1 : (unsigned long long)n - 1;
+      k = (tg & 1) ? hi : lo;
+    }
+    st[ST_PF(tg)] = 0;
+    st[ST_RK(tg)] = k;
+  }
 }
 
 __global__ void finish_kernel(const uint64_t* __restrict__ state, int sw, int64_t n_seg,
@@ -339,8 +411,9 @@ __global__ void finish_kernel(const uint64_t* __restrict__ state, int sw, int64_
   if (lo > n - 1) lo = n - 1;
   const unsigned long long hi = lo + 1 < n ? lo + 1 : n - 1;
   const double t = pos - (double)lo;
-  const double a = key_f64(st[2 + 2 * (2 * qi)]);
-  const double b = key_f64(st[2 + 2 * (2 * qi + 1)]);
+  const uint64_t base = (st[1] >> 32) ? st[2] : 0;
+  const double a = key_f64(st[ST_PF(2 * qi)] + base);
+  const double b = key_f64(st[ST_PF(2 * qi + 1)] + base);
   // numpy _lerp: a + (b-a)*t, and b - (b-a)*(1-t) when t >= 0.5 (no FMA contraction)
   const double d = __dsub_rn(b, a);
   double v = __dadd_rn(a, __dmul_rn(d, t));
@@ -362,7 +435,7 @@ int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
   PMX_REQUIRE(ctx, "ctx is NULL");
   PMX_REQUIRE(n_series >= 0 && n_steps >= 0 && n_seg >= 0 && n_seg <= 65535, "bad sizes (n_seg <= 65535)");
   PMX_REQUIRE(n_q >= 1 && 2 * n_q <= MAX_TARGETS, "n_q must be in [1, 8]");
-  PMX_REQUIRE(pass >= 0 && pass < PMX_QUANTILE_PASSES, "pass out of range");
+  PMX_REQUIRE(pass >= 0 && pass <= PMX_QUANTILE_PASSES, "pass out of range");
   if (n_seg == 0) return PMX_OK;
   PMX_REQUIRE(d_hist && d_state, "NULL buffer");
   const int n_t = 2 * (int)n_q;
@@ -413,12 +486,25 @@ int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
   return PMX_OK;
 }
 
+int pmx_quantile_init(pmx_ctx* ctx, const int64_t* d_count, const double* d_min, const double* d_max,
+                      int64_t n_seg, const double* d_q, int64_t n_q, uint64_t* d_state, pmx_stream stream) {
+  PMX_REQUIRE(ctx, "ctx is NULL");
+  PMX_REQUIRE(n_seg >= 0 && n_seg <= 65535, "n_seg must be in [0, 65535]");
+  PMX_REQUIRE(n_q >= 1 && 2 * n_q <= MAX_TARGETS, "n_q must be in [1, 8]");
+  if (n_seg == 0) return PMX_OK;
+  PMX_REQUIRE(d_count && d_min && d_max && d_q && d_state, "NULL buffer");
+  init_kernel<<<(unsigned)((n_seg + 127) / 128), 128, 0, pmx_st(stream)>>>((const long long*)d_count, d_min, d_max, d_q,
+                                                                         (int)n_q, d_state, state_words(n_q), n_seg);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
 int pmx_quantile_pick(pmx_ctx* ctx, const uint64_t* d_hist, int64_t n_seg, const double* d_q,
                       int64_t n_q, int pass, uint64_t* d_state, pmx_stream stream) {
   PMX_REQUIRE(ctx, "ctx is NULL");
   PMX_REQUIRE(n_seg >= 0 && n_seg <= 65535, "n_seg must be in [0, 65535]");
   PMX_REQUIRE(n_q >= 1 && 2 * n_q <= MAX_TARGETS, "n_q must be in [1, 8]");
-  PMX_REQUIRE(pass >= 0 && pass < PMX_QUANTILE_PASSES, "pass out of range");
+  PMX_REQUIRE(pass >= 0 && pass <= PMX_QUANTILE_PASSES, "pass out of range");
   if (n_seg == 0) return PMX_OK;
   PMX_REQUIRE(d_hist && d_q && d_state, "NULL buffer");
   pick_kernel<<<(unsigned)n_seg, 256, 0, pmx_st(stream)>>>((const unsigned long long*)d_hist, d_q, (int)n_q, pass, d_state,

@@ -352,16 +352,20 @@ class Engine:
     # ------------------------------------------------------------------ K6
     def quantile_buffers(self, n_seg, n_q):
         t = self.torch
-        state = self.torch.zeros((n_seg, 2 + 4 * n_q), dtype=t.int64, device=self.device)
+        state = self.torch.zeros((n_seg, 3 + 4 * n_q), dtype=t.int64, device=self.device)
         hist = self._empty((n_seg * 2 * n_q, _abi.QUANTILE_BINS), t.int64)
         return state, hist
 
-    def quantiles(self, x, seg, n_seg, qs, group=None, buffers=None, row_order=None):
+    def quantiles(self, x, seg, n_seg, qs, group=None, buffers=None, row_order=None, summary=None):
         """Exact quantiles per segment.  x: [S,T] device; seg: int per series (host or device).
         With ``group`` (a torch.distributed process group over NCCL) the histograms of every pass
         are all-reduced, so the result is the quantile of the union of all ranks' values.
         ``row_order``: optional int32 device tensor of row indices grouped by segment (the perm of
-        ``group_index``); lets a CTA keep one set of histograms for long runs of rows."""
+        ``group_index``); lets a CTA keep one set of histograms for long runs of rows.
+        ``summary``: optional (count int64[n_seg], min f64[n_seg], max f64[n_seg]) device tensors of
+        each segment over ALL ranks (what ``group_reduce`` / ``combine_group_partials`` return for the
+        same values): the selection then starts behind the key bits that min and max share and
+        saves the first full pass."""
         t = self.torch
         x = self._dev(x, t.float64)
         S, T = x.shape
@@ -373,7 +377,7 @@ class Engine:
         outs = {"n": self._empty((n_seg,), t.int64), "lo": self._empty((n_seg, n_q), t.int64),
                 "hi": self._empty((n_seg, n_q), t.int64), "x_lo": self._empty((n_seg, n_q), t.float64),
                 "x_hi": self._empty((n_seg, n_q), t.float64), "value": self._empty((n_seg, n_q), t.float64)}
-        if group is None:
+        if group is None and summary is None:
             _abi.check(self.lib.pmx_quantile_select(
                 self.ctx, self._ptr(x), S, T, self._ptr(d_seg), n_seg, self._ptr(d_ord), n_rows, self._ptr(d_q), n_q,
                 self._ptr(outs["n"]),
@@ -381,20 +385,32 @@ class Engine:
                 self._ptr(outs["value"]), self._stream()))
             self.launches += 3 * _abi.QUANTILE_PASSES - 2    # hist (two kernels from pass 3 on) + pick + finish
             return outs
-        import torch.distributed as dist
         state, hist = buffers if buffers is not None else self.quantile_buffers(n_seg, n_q)
-        state.zero_()
-        for p in range(_abi.QUANTILE_PASSES):
+        if summary is None:
+            state.zero_()
+            passes = range(_abi.QUANTILE_PASSES)
+        else:
+            cnt, mn, mx = (self._dev(summary[0], t.int64), self._dev(summary[1], t.float64),
+                           self._dev(summary[2], t.float64))
+            if cnt.numel() != n_seg or mn.numel() != n_seg or mx.numel() != n_seg:
+                raise ValueError("summary tensors must have n_seg elements")
+            _abi.check(self.lib.pmx_quantile_init(self.ctx, self._ptr(cnt), self._ptr(mn), self._ptr(mx), n_seg,
+                                                  self._ptr(d_q), n_q, self._ptr(state), self._stream()))
+            self.launches += 1
+            passes = range(1, _abi.QUANTILE_PASSES + 1)
+        for p in passes:
             _abi.check(self.lib.pmx_quantile_hist(self.ctx, self._ptr(x), S, T, self._ptr(d_seg), n_seg,
                                                   self._ptr(d_ord), n_rows, n_q, p,
                                                   self._ptr(state), self._ptr(hist), self._stream()))
             n_h = n_seg * (1 if p == 0 else 2 * n_q)
-            dist.all_reduce(hist[:n_h], op=dist.ReduceOp.SUM, group=group)
+            if group is not None:
+                import torch.distributed as dist
+                dist.all_reduce(hist[:n_h], op=dist.ReduceOp.SUM, group=group)
             _abi.check(self.lib.pmx_quantile_pick(self.ctx, self._ptr(hist), n_seg, self._ptr(d_q), n_q, p,
                                                   self._ptr(state), self._stream()))
         _abi.check(self.lib.pmx_quantile_finish(self.ctx, self._ptr(state), n_seg, self._ptr(d_q), n_q,
                                                 self._ptr(outs["n"]), self._ptr(outs["lo"]), self._ptr(outs["hi"]),
                                                 self._ptr(outs["x_lo"]), self._ptr(outs["x_hi"]),
                                                 self._ptr(outs["value"]), self._stream()))
-        self.launches += 3 * _abi.QUANTILE_PASSES - 2
+        self.launches += 3 * _abi.QUANTILE_PASSES - 2 + (1 if summary is not None else 0)   # passes 1..6: one more candidate pass
         return outs

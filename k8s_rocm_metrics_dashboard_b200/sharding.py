@@ -94,6 +94,15 @@ class ShardedEngine:
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self._qbuf = {}
 
+    @staticmethod
+    def _qsummary(summary):
+        """(count, min, max) of the combined group summary for the quantile start, or None when
+        switched off (PMX_QUANTILE_SUMMARY=0: the selection then begins with pass 0)."""
+        import os
+        if os.environ.get("PMX_QUANTILE_SUMMARY", "1") == "0":
+            return None
+        return summary[1], summary[2], summary[3]
+
     def aggregate_step(self, ts, val, off, start_ms, step_ms, n_steps, window_steps, seg, n_seg, perm_goff,
                        qs=(0.5, 0.95, 0.99), out=None, lookback_ms=300_000, host=None):
         """fused align+rolling+rate on the shard, then per-metric sum/count/min/max/mean and exact
@@ -113,10 +122,14 @@ class ShardedEngine:
             if key not in self._qbuf:
                 self._qbuf[key] = eng.quantile_buffers(n_seg, len(qs))
             q = eng.quantiles(out["aligned"], seg, n_seg, list(qs), group=self.group or _world_group(),
-                              buffers=self._qbuf[key], row_order=perm_goff[0])
+                              buffers=self._qbuf[key], row_order=perm_goff[0], summary=self._qsummary(summary))
         else:
             summary = (sm, cnt, mn, mx, mean)          # one rank: the kernel's own result is the summary
-            q = eng.quantiles(out["aligned"], seg, n_seg, list(qs), row_order=perm_goff[0])
+            key = (n_seg, len(qs))
+            if key not in self._qbuf:
+                self._qbuf[key] = eng.quantile_buffers(n_seg, len(qs))
+            q = eng.quantiles(out["aligned"], seg, n_seg, list(qs), buffers=self._qbuf[key],
+                              row_order=perm_goff[0], summary=self._qsummary(summary))
         return out, summary, q
 
 

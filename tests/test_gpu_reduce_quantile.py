@@ -53,8 +53,23 @@ def _check_quantiles(eng, x, seg, n_seg, qs):
     _check_quantiles_1(eng, x, seg, n_seg, qs, group_index(np.asarray(seg), n_seg)[0])  # rows grouped by segment
 
 
-def _check_quantiles_1(eng, x, seg, n_seg, qs, order):
-    out = eng.quantiles(x, seg, n_seg, qs, row_order=order)
+    _check_quantiles_1(eng, x, seg, n_seg, qs, None, _summary(x, seg, n_seg))          # pass 0 replaced by count/min/max
+    _check_quantiles_1(eng, x, seg, n_seg, qs, group_index(np.asarray(seg), n_seg)[0], _summary(x, seg, n_seg))
+
+
+def _summary(x, seg, n_seg):
+    """count / min / max per segment the way a group reduction reports them (NaN when empty)."""
+    cnt = np.zeros(n_seg, dtype=np.int64); mn = np.full(n_seg, np.nan); mx = np.full(n_seg, np.nan)
+    for g in range(n_seg):
+        v = x[np.asarray(seg) == g]; v = v[~np.isnan(v)]
+        cnt[g] = v.size
+        if v.size:
+            mn[g] = v.min(); mx[g] = v.max()
+    return cnt, mn, mx
+
+
+def _check_quantiles_1(eng, x, seg, n_seg, qs, order, summary=None):
+    out = eng.quantiles(x, seg, n_seg, qs, row_order=order, summary=summary)
     for g in range(n_seg):
         o = O.quantiles(x[np.asarray(seg) == g], qs)
         assert int(_np(out["n"])[g]) == o["n"]
@@ -110,3 +125,29 @@ def test_quantiles_many_segments_use_row_major_schedule(eng):
     x = rng.normal(size=(300, 257)); x[rng.random(x.shape) < 0.1] = np.nan
     seg = np.arange(300, dtype=np.int32)
     _check_quantiles(eng, x, seg, 300, [0.5, 0.9])
+
+
+def test_quantiles_from_summary_signed_zero_constant_and_wide_segments(eng):
+    """The count/min/max start: a zero bound may hide the other zero's sign; a constant segment is
+    resolved by the bounds alone; a segment spanning both signs shares no key bits (all 6 passes);
+    a gauge-like range within a factor of four needs passes 1..5 only."""
+    rng = np.random.default_rng(21)
+    x = np.empty((8, 300))
+    x[0:2] = rng.choice([-0.0, 0.0, 1.5], size=(2, 300), p=[0.02, 0.02, 0.96])   # zeros of both signs below the ranks asked for
+    x[2:4] = 42.125                                                  # min == max
+    x[4:6] = rng.normal(size=(2, 300)) * 1e200                       # both signs, huge range
+    x[6:8] = 30 + 65 * rng.random((2, 300))                          # gauge-like
+    x[rng.random(x.shape) < 0.02] = np.nan
+    seg = np.repeat(np.arange(4), 2).astype(np.int32)
+    qs = [0.3, 0.5, 1.0]
+    for zero in (0.0, -0.0):
+        cnt, mn, mx = _summary(x, seg, 4)
+        if mn[0] == 0.0:
+            mn[0] = zero                                             # either sign is a legal report of the minimum
+        out = eng.quantiles(x, seg, 4, qs, summary=(cnt, mn, mx))
+        for g in range(4):
+            o = O.quantiles(x[seg == g], qs)
+            assert int(_np(out["n"])[g]) == o["n"]
+            assert_bits_equal(_np(out["x_lo"])[g], np.array(o["x_lo"]), "x_lo")
+            assert_bits_equal(_np(out["x_hi"])[g], np.array(o["x_hi"]), "x_hi")
+            assert_bits_equal(_np(out["value"])[g], np.array(o["value"]), "value")
