@@ -106,6 +106,26 @@ def main():
           f"{n1 / t_tok / 1e6:.1f} M samples/s, {len(body) / t_tok / 1e9:.2f} GB/s (text formatting took {t_fmt:.1f} s)")
     rows.append({"kernel": "X1 tokenizer (host C++, 1 core)", "samples": n1, "ms": t_tok * 1e3, "samples_per_s": n1 / t_tok,
                  "bytes_per_sample": len(body) / n1, "GBps": len(body) / t_tok / 1e9})
+    # X1 on the device: the body is copied once (pageable host memory here) and cut by pmx_tokenize_device
+    dtok = eng.tokenize_device(body)
+    assert dtok.n_samples == n1
+    t0 = time.perf_counter()
+    dtok = eng.tokenize_device(body)
+    t_dev = time.perf_counter() - t0
+    import ctypes as C
+    from k8s_rocm_metrics_dashboard_b200 import _abi
+    cap_s, cap_r = len(body) // 8 + 1, len(body) // 24 + 1
+    b_ts, b_val = torch.empty(cap_s, dtype=torch.int32, device=dev), torch.empty(cap_s, dtype=torch.int32, device=dev)
+    b_so = torch.empty(cap_r + 1, dtype=torch.int64, device=dev)
+    b_mo, b_ml = torch.empty(cap_r, dtype=torch.int32, device=dev), torch.empty(cap_r, dtype=torch.int32, device=dev)
+    b_st = torch.empty(4, dtype=torch.int64, device=dev)
+    pp = lambda x: C.c_void_p(x.data_ptr())
+    sec = timeit(lambda: _abi.check(eng.lib.pmx_tokenize_device(
+        eng.ctx, pp(dtok.d_text), len(body), pp(b_ts), pp(b_val), cap_s, pp(b_so), pp(b_mo), pp(b_ml), cap_r, pp(b_st),
+        C.c_void_p(torch.cuda.current_stream().cuda_stream))))
+    rec("X1 tokenizer (device kernels)", n1, len(body) / n1 + 8, sec,
+        f"{len(body) / sec / 1e9:.0f} GB/s of text; with H2D of the body and the label spans back: {n1 / t_dev / 1e6:.0f} M samples/s")
+    del b_ts, b_val, b_so, b_mo, b_ml, dtok
     text = torch.from_numpy(tok.flat.copy()).to(dev)
     voff = torch.from_numpy(tok.val_off.view(np.int32).copy()).to(dev)
     toff = torch.from_numpy(tok.ts_off.view(np.int32).copy()).to(dev)

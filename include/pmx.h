@@ -85,6 +85,22 @@ int pmx_tokenize_mt(const char* h_body, size_t len,
                     int64_t cap_series, char* h_extra, size_t cap_extra, int n_threads,
                     pmx_tokenize_result* res);
 
+/* The same cut on the GPU, for a body that is already in device memory (the
+ * host then never walks the text).  Accepts Prometheus' own compact encoding of a successful
+ * "matrix" or "vector" answer: no white space between tokens, every sample written [<number>,"<text>"],
+ * every series object beginning {"metric":{ .  Offsets have the meaning given above and index
+ * d_body itself (value tokens with JSON escapes are not decoded: pmx_parse_f64 then reports them).
+ * d_body must be 16-byte aligned and at most 4 GiB.  d_status (int64[4], device) receives
+ * [0] n_samples, [1] n_series, [2] 0 or an error (1 envelope not recognised, 2 '[' count does not
+ * match samples + series: white space, another shape, or "warnings"/"infos" arrays -- use
+ * pmx_tokenize for those, 3 capacity, 4 malformed sample, 5 unterminated label object), [3] a byte
+ * position or count for the error; outputs are valid only if [2] == 0.
+ * d_series_off needs cap_series + 1 entries.  Uses ctx scratch (36 bytes per 64 KiB of body). */
+int pmx_tokenize_device(pmx_ctx* ctx, const uint8_t* d_body, uint64_t len,
+                        uint32_t* d_ts_off, uint32_t* d_val_off, int64_t cap_samples,
+                        int64_t* d_series_off, uint32_t* d_metric_off, uint32_t* d_metric_len,
+                        int64_t cap_series, int64_t* d_status, pmx_stream stream);
+
 /* ---- X2 / H2  value decode (K1).  Replaces float(metric["value"][1]) at app.py:188: decimal
  * text -> binary64, correctly rounded, bit-exact with CPython float() for ASCII input (sign,
  * digits with single underscores, '.', exponent, inf/infinity/nan in any case, surrounding

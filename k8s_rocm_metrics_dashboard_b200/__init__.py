@@ -8,9 +8,9 @@ Numeric work runs in ``libpmx.so`` (hand-written sm_100a CUDA behind the C ABI i
 ``include/pmx.h``).  There is no CPU fallback: without the library or without a GPU the
 calls raise.
 """
-from .engine import DEFAULT_LOOKBACK_MS, Engine, Tokens, group_index, tokenize  # noqa: F401
+from .engine import DEFAULT_LOOKBACK_MS, DeviceTokens, Engine, Tokens, group_index, tokenize  # noqa: F401
 from .adapter import (aggregate_instant, aggregate_range, fetch_gpu_metrics,  # noqa: F401
                       selected_averages)
 
-__all__ = ["Engine", "Tokens", "tokenize", "group_index", "fetch_gpu_metrics", "aggregate_instant",
+__all__ = ["Engine", "Tokens", "DeviceTokens", "tokenize", "group_index", "fetch_gpu_metrics", "aggregate_instant",
            "aggregate_range", "selected_averages", "DEFAULT_LOOKBACK_MS"]

@@ -46,6 +46,7 @@ SIGNATURES = {
                             C.POINTER(TokenizeResult)]),
     "pmx_tokenize_mt": (_int, [_p, C.c_size_t, _p, _p, _i64, _p, _p, _p, _i64, _p, C.c_size_t, _int,
                                C.POINTER(TokenizeResult)]),
+    "pmx_tokenize_device": (_int, [_p, _p, _u64, _p, _p, _i64, _p, _p, _p, _i64, _p, _p]),
     "pmx_parse_f64": (_int, [_p, _p, _u64, _p, _i64, _p, _p, _p]),
     "pmx_parse_ts_ms": (_int, [_p, _p, _u64, _p, _i64, _p, _p, _p]),
     "pmx_align": (_int, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _p, _p, _p]),

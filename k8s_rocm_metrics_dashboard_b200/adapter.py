@@ -143,16 +143,33 @@ def fetch_gpu_metrics():
         return None, None
 
 
+def _range_tokens(eng, body, tokenizer):
+    """X1 for a range body.  ``tokenizer``: "device" (pmx_tokenize_device: Prometheus' compact
+    encoding only), "host" (pmx_tokenize: general JSON) or "auto" (device for bodies of 1 MiB and
+    more; a body the device scan refuses -- white space, warnings -- goes to the host walk)."""
+    if isinstance(body, str):
+        body = body.encode("utf-8")
+    if tokenizer == "host" or (tokenizer == "auto" and len(body) < (1 << 20)):
+        return tokenize(body)
+    if tokenizer == "device":
+        return eng.tokenize_device(body)
+    try:
+        return eng.tokenize_device(body)
+    except ValueError:
+        return tokenize(body)
+
+
 def aggregate_range(body, start_ms, step_ms, n_steps, window_ms, lookback_ms=DEFAULT_LOOKBACK_MS,
-                    quantiles=(0.5, 0.95, 0.99), as_frame=True, eng: Engine | None = None):
+                    quantiles=(0.5, 0.95, 0.99), as_frame=True, eng: Engine | None = None, tokenizer="auto"):
     """Range path: ``query_range`` matrix body -> per (series, step) tidy frame + per-metric summary.
 
     Returns (tidy, summary).  tidy columns: instance, gpu_id, metric_name, ts, value, roll_min,
     roll_max, roll_mean, rate.  summary: one row per metric name with sum/count/min/max/mean of the
     aligned values and the requested quantiles.  With ``as_frame=False`` both are dicts of arrays.
+    ``tokenizer``: where the body is cut into tokens, see ``_range_tokens``.
     """
     eng = eng or engine()
-    tok = tokenize(body)
+    tok = _range_tokens(eng, body, tokenizer)
     labels = tok.labels()
     ts, val = eng.parse(tok)
     w = int(window_ms // step_ms)

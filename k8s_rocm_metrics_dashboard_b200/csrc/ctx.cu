@@ -57,19 +57,19 @@ int pmx_ctx_create(int device, pmx_ctx** out) {
   if (!c) return pmx_fail(PMX_E_INVALID, "pmx_ctx_create: out of host memory");
   c->device = device;
   c->sm_count = prop.multiProcessorCount;
-  for (int i = 0; i < 3; ++i) { c->scratch[i] = nullptr; c->scratch_bytes[i] = 0; }
+  for (int i = 0; i < PMX_SCR_SLOTS; ++i) { c->scratch[i] = nullptr; c->scratch_bytes[i] = 0; }
   *out = c;
   return PMX_OK;
 }
 
 void pmx_ctx_destroy(pmx_ctx* ctx) {
   if (!ctx) return;
-  for (int i = 0; i < 3; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
+  for (int i = 0; i < PMX_SCR_SLOTS; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
   delete ctx;
 }
 
 size_t pmx_ctx_scratch_bytes(const pmx_ctx* ctx) {
-  return ctx ? ctx->scratch_bytes[0] + ctx->scratch_bytes[1] + ctx->scratch_bytes[2] : 0;
+  return ctx ? ctx->scratch_bytes[0] + ctx->scratch_bytes[1] + ctx->scratch_bytes[2] + ctx->scratch_bytes[3] : 0;
 }
 
 }  // extern "C"

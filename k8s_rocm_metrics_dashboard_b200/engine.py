@@ -39,6 +39,37 @@ class Tokens:
         return [json.loads(bytes(body[o:o + n])) if n else {} for o, n in self.metric_spans]
 
 
+@dataclass
+class DeviceTokens:
+    """Result of pmx_tokenize_device: the body and the per-sample offsets stay in device memory;
+    only the CSR offsets and the label spans (a few bytes per series) come back to the host."""
+    body: bytes                 # the host copy the labels are read from
+    d_text: object              # uint8 device tensor holding the body
+    d_ts_off: object            # int32 device tensor (uint32 offsets), N entries
+    d_val_off: object
+    series_off: np.ndarray      # int64[S+1] (host)
+    metric_spans: list
+    result_type: str
+
+    @property
+    def n_samples(self):
+        return int(self.series_off[-1]) if len(self.series_off) else 0
+
+    @property
+    def n_series(self):
+        return len(self.series_off) - 1
+
+    def labels(self):
+        import json
+        return [json.loads(self.body[o:o + n]) if n else {} for o, n in self.metric_spans]
+
+
+_TOKD_ERRORS = {1: "not a successful Prometheus matrix/vector answer in compact encoding",
+                2: "'[' count does not match samples + series (white space between tokens, or a shape other than [t,\"v\"])",
+                3: "capacity exceeded", 4: "malformed sample near byte {where}",
+                5: "unterminated label object near byte {where}"}
+
+
 def tokenize(body: bytes, threads=None) -> Tokens:
     """X1 on the host (C++, no Python objects per sample).  Raises ValueError on a malformed body.
     Bodies of 1 MiB and more are cut at series boundaries and walked by ``threads`` host threads
@@ -135,10 +166,41 @@ class Engine:
         return int(self.lib.pmx_ctx_scratch_bytes(self.ctx))
 
     # ------------------------------------------------------------------ K1
-    def parse(self, tok: Tokens, want_ts=True):
-        """Device decode of all value (and timestamp) tokens.  Returns (ts int64[N] | None, val float64[N]).
-        Raises ValueError naming the first malformed token, like float() at app.py:188."""
+    def tokenize_device(self, body: bytes) -> DeviceTokens:
+        """X1 on the GPU: one H2D copy of the body, then pmx_tokenize_device.  Raises ValueError when
+        the body is not in Prometheus' compact encoding (use ``tokenize`` for general JSON)."""
         t = self.torch
+        if isinstance(body, str):
+            body = body.encode("utf-8")
+        n = len(body)
+        import warnings
+        with warnings.catch_warnings():                    # read-only bytes view; it is only read
+            warnings.simplefilter("ignore", UserWarning)
+            text = t.frombuffer(body, dtype=t.uint8).to(self.device, non_blocking=True)
+        cap_s, cap_r = n // 8 + 1, n // 24 + 1
+        ts_off, val_off = self._empty((cap_s,), t.int32), self._empty((cap_s,), t.int32)
+        series_off = self._empty((cap_r + 1,), t.int64)
+        m_off, m_len = self._empty((cap_r,), t.int32), self._empty((cap_r,), t.int32)
+        status = self._empty((4,), t.int64)
+        _abi.check(self.lib.pmx_tokenize_device(self.ctx, self._ptr(text), n, self._ptr(ts_off), self._ptr(val_off), cap_s,
+                                                self._ptr(series_off), self._ptr(m_off), self._ptr(m_len), cap_r,
+                                                self._ptr(status), self._stream()))
+        self.launches += 3
+        ns, nr, err, where = status.cpu().tolist()
+        if err:
+            raise ValueError("pmx_tokenize_device: " + _TOKD_ERRORS.get(err, f"error {err}").format(where=where))
+        soff = series_off[:nr + 1].cpu().numpy()
+        spans = list(zip(m_off[:nr].cpu().numpy().view(np.uint32).tolist(), m_len[:nr].cpu().numpy().view(np.uint32).tolist()))
+        kind = "matrix" if body[42:48] == b"matrix" else "vector"
+        return DeviceTokens(body, text, ts_off[:ns], val_off[:ns], soff, spans, kind)
+
+    def parse(self, tok, want_ts=True):
+        """Device decode of all value (and timestamp) tokens.  Returns (ts int64[N] | None, val float64[N]).
+        Raises ValueError naming the first malformed token, like float() at app.py:188.
+        ``tok``: Tokens (host offsets, uploaded here) or DeviceTokens (already resident)."""
+        t = self.torch
+        if isinstance(tok, DeviceTokens):
+            return self._parse_device(tok, want_ts)
         import warnings
         with warnings.catch_warnings():                    # the body is a read-only bytes view; it is only read
             warnings.simplefilter("ignore", UserWarning)
@@ -164,6 +226,30 @@ class Engine:
             while end < len(tok.flat) and tok.flat[end] != 0x22:
                 end += 1
             raise ValueError(f"could not convert string to float: {bytes(tok.flat[o:end]).decode('utf-8', 'replace')!r}")
+        if want_ts and b[1] != _abi.INT64_MAX:
+            raise ValueError(f"malformed timestamp in sample {b[1]}")
+        return ts, val
+
+    def _parse_device(self, tok, want_ts):
+        t = self.torch
+        n = tok.n_samples
+        val = self._empty((n,), t.float64)
+        bad = self._empty((2,), t.int64)
+        text = tok.d_text
+        _abi.check(self.lib.pmx_parse_f64(self.ctx, self._ptr(text), text.numel(), self._ptr(tok.d_val_off), n,
+                                          self._ptr(val), self._ptr(bad[0:]), self._stream()))
+        self.launches += 2
+        ts = None
+        if want_ts:
+            ts = self._empty((n,), t.int64)
+            _abi.check(self.lib.pmx_parse_ts_ms(self.ctx, self._ptr(text), text.numel(), self._ptr(tok.d_ts_off), n,
+                                                self._ptr(ts), self._ptr(bad[1:]), self._stream()))
+            self.launches += 2
+        b = bad.cpu().tolist()
+        if b[0] != _abi.INT64_MAX:
+            o = int(tok.d_val_off[b[0]].item()) & 0xffffffff
+            end = tok.body.find(b'"', o)
+            raise ValueError(f"could not convert string to float: {tok.body[o:end].decode('utf-8', 'replace')!r}")
         if want_ts and b[1] != _abi.INT64_MAX:
             raise ValueError(f"malformed timestamp in sample {b[1]}")
         return ts, val

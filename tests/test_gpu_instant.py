@@ -85,13 +85,14 @@ def test_fetch_gpu_metrics_contract(eng, golden, monkeypatch):
     assert adapter.last_error == "Error fetching GPU metrics: float division by zero"
 
 
-def test_aggregate_range_tidy_frame(eng):
+@pytest.mark.parametrize("tokenizer", ["host", "device", "auto"])
+def test_aggregate_range_tidy_frame(eng, tokenizer):
     from oracle import prom_oracle as O
     import numpy as np
     from tests.util import assert_bits_equal, assert_close
     d = synth.dense(1, 2, 6, 120, seed=9, nan_frac=0.02)
     body = synth.to_matrix_json(d["labels"], d["ts"], d["val"], d["off"])
-    tidy, summary = adapter.aggregate_range(body, d["start_ms"], d["step_ms"], 120, 900_000, eng=eng)
+    tidy, summary = adapter.aggregate_range(body, d["start_ms"], d["step_ms"], 120, 900_000, eng=eng, tokenizer=tokenizer)
     assert list(tidy.columns) == ["instance", "gpu_id", "metric_name", "ts", "value", "roll_min", "roll_max",
                                   "roll_mean", "rate"]
     assert len(tidy) == 12 * 120
