@@ -159,13 +159,41 @@ def _range_tokens(eng, body, tokenizer):
         return tokenize(body)
 
 
+def _tidy_arrow(labels, grid, host, n_steps):
+    """The tidy frame as a pyarrow Table: the three label columns are
+    dictionary-encoded (int32 code per row, one string per distinct value) and the numeric columns
+    wrap the arrays that came off the device without a copy, so no per-row Python object or
+    fixed-width string is ever made.  ``Table.to_pandas()`` gives categorical label columns."""
+    import pyarrow as pa
+    S = len(labels)
+    cols = {}
+    for col, key in (("instance", "instance"), ("gpu_id", "gpu_id"), ("metric_name", "__name__")):
+        vals = [l.get(key, "") for l in labels]
+        uniq = sorted(set(vals))
+        code = {v: i for i, v in enumerate(uniq)}
+        idx = np.repeat(np.fromiter((code[v] for v in vals), dtype=np.int32, count=S), n_steps)
+        cols[col] = pa.DictionaryArray.from_arrays(pa.array(idx), pa.array(uniq, type=pa.string()))
+    cols["ts"] = pa.array(np.tile(grid, S))
+    for col, key in (("value", "aligned"), ("roll_min", "roll_min"), ("roll_max", "roll_max"),
+                     ("roll_mean", "roll_mean"), ("rate", "rate")):
+        cols[col] = pa.array(host[key].ravel())                    # float64 numpy -> arrow: zero copy
+    return pa.table(cols)
+
+
+def _summary_arrow(summary):
+    import pyarrow as pa
+    return pa.table({k: pa.array(list(v)) if k == "metric_name" else pa.array(np.asarray(v)) for k, v in summary.items()})
+
+
 def aggregate_range(body, start_ms, step_ms, n_steps, window_ms, lookback_ms=DEFAULT_LOOKBACK_MS,
                     quantiles=(0.5, 0.95, 0.99), as_frame=True, eng: Engine | None = None, tokenizer="auto"):
     """Range path: ``query_range`` matrix body -> per (series, step) tidy frame + per-metric summary.
 
     Returns (tidy, summary).  tidy columns: instance, gpu_id, metric_name, ts, value, roll_min,
     roll_max, roll_mean, rate.  summary: one row per metric name with sum/count/min/max/mean of the
-    aligned values and the requested quantiles.  With ``as_frame=False`` both are dicts of arrays.
+    aligned values and the requested quantiles.  With ``as_frame=False`` both are dicts of arrays,
+    with ``as_frame="arrow"`` pyarrow Tables (label columns dictionary-encoded, numeric columns
+    zero-copy).
     ``tokenizer``: where the body is cut into tokens, see ``_range_tokens``.
     """
     eng = eng or engine()
@@ -179,7 +207,8 @@ def aggregate_range(body, start_ms, step_ms, n_steps, window_ms, lookback_ms=DEF
     from .engine import group_index
     perm_goff = group_index(gid, len(names))
     sm, cnt, mn, mx, mean = eng.group_reduce(out["aligned"], None, len(names), perm_goff=perm_goff)
-    qd = eng.quantiles(out["aligned"], gid, len(names), list(quantiles), row_order=perm_goff[0])
+    qd = eng.quantiles(out["aligned"], gid, len(names), list(quantiles), row_order=perm_goff[0],
+                       summary=(cnt, mn, mx))
     host = {k: v.cpu().numpy() for k, v in out.items()}
     summary = {"metric_name": names, "sum": sm.cpu().numpy(), "count": cnt.cpu().numpy(),
                "min": mn.cpu().numpy(), "max": mx.cpu().numpy(), "mean": mean.cpu().numpy()}
@@ -188,6 +217,8 @@ def aggregate_range(body, start_ms, step_ms, n_steps, window_ms, lookback_ms=DEF
         summary[f"p{int(round(q * 100))}"] = qv[:, i]
     S = len(labels)
     grid = start_ms + step_ms * np.arange(n_steps, dtype=np.int64)
+    if as_frame == "arrow":
+        return _tidy_arrow(labels, grid, host, n_steps), _summary_arrow(summary)
     tidy = {"instance": np.repeat([l.get("instance", "") for l in labels], n_steps),
             "gpu_id": np.repeat([l.get("gpu_id", "") for l in labels], n_steps),
             "metric_name": np.repeat([l.get("__name__", "") for l in labels], n_steps),

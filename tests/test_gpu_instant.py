@@ -106,3 +106,26 @@ def test_aggregate_range_tidy_frame(eng, tokenizer):
         q = O.quantiles(ref["aligned"][rows], [0.5, 0.95, 0.99])
         assert_bits_equal(summary.loc[i, ["p50", "p95", "p99"]].to_numpy(dtype=np.float64), np.array(q["value"]))
         assert summary.loc[i, "count"] == q["n"]
+
+
+def test_aggregate_range_arrow_table_equals_the_frame(eng):
+    import numpy as np
+    d = synth.dense(2, 2, 6, 90, seed=11, nan_frac=0.02)
+    body = synth.to_matrix_json(d["labels"], d["ts"], d["val"], d["off"])
+    tidy, summary = adapter.aggregate_range(body, d["start_ms"], d["step_ms"], 90, 900_000, eng=eng)
+    at, asum = adapter.aggregate_range(body, d["start_ms"], d["step_ms"], 90, 900_000, eng=eng, as_frame="arrow")
+    assert at.column_names == list(tidy.columns) and at.num_rows == len(tidy)
+    import pyarrow as pa
+    assert all(pa.types.is_dictionary(at.schema.field(c).type) for c in ("instance", "gpu_id", "metric_name"))
+    back = at.to_pandas()
+    for c in ("instance", "gpu_id", "metric_name"):
+        assert back[c].astype(str).tolist() == tidy[c].astype(str).tolist()
+    for c in ("ts", "value", "roll_min", "roll_max", "roll_mean", "rate"):
+        np.testing.assert_array_equal(back[c].to_numpy(), tidy[c].to_numpy())
+    sb = asum.to_pandas()
+    assert list(sb.columns) == list(summary.columns)
+    for c in summary.columns:
+        if c == "metric_name":
+            assert sb[c].tolist() == summary[c].tolist()
+        else:
+            np.testing.assert_array_equal(sb[c].to_numpy(), summary[c].to_numpy())
