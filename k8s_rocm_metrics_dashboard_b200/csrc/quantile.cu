@@ -23,11 +23,6 @@ namespace {
 
 constexpr int BINS = PMX_QUANTILE_BINS;
 constexpr int MAX_TARGETS = 16;
-#ifndef PMX_HIST_SMEM_LANES
-#define PMX_HIST_SMEM_LANES 8       // of every 8 lanes, how many keep their increment in shared memory.
-                                    // 8 = all: sending 5 of 8 to the L2 atomic units measured 374 us vs 225 us
-                                    // for the all-match pass of config 2 (2048 hot addresses per segment)
-#endif
 
 __device__ __forceinline__ uint64_t f64_key(double v) {
   const uint64_t b = (uint64_t)__double_as_longlong(v);
@@ -50,7 +45,9 @@ constexpr int ST_HDR = 3;
 #define ST_RK(tg) (ST_HDR + 2 * (tg) + 1)
 __host__ __device__ __forceinline__ int state_words(int64_t n_q) { return ST_HDR + 4 * (int)n_q; }
 
-struct Geom { int shift; int bits; int pshift; bool has_prefix; uint64_t base; };
+// all_match: every value of the segment carries every target's prefix (no prefix yet, or only the
+// leading zero bits of a selection started from count/min/max), so nothing has to be compared.
+struct Geom { int shift; int bits; int pshift; bool has_prefix; bool all_match; uint64_t base; };
 __device__ __forceinline__ Geom seg_geom(const uint64_t* st, int pass) {
   Geom g;
   const uint64_t w1 = st[1];
@@ -61,11 +58,11 @@ __device__ __forceinline__ Geom seg_geom(const uint64_t* st, int pass) {
     if (bits < 0 || pass < 1) bits = 0;                           // 0: nothing left to resolve
     g.bits = bits; g.pshift = 64 - start; g.shift = 64 - start - bits;
     if (g.shift < 0) g.shift = 0;
-    g.has_prefix = start > 0; g.base = st[2];
+    g.has_prefix = start > 0; g.base = st[2]; g.all_match = pass == 1;
   } else {
     g.bits = pass < PMX_QUANTILE_PASSES ? digit_bits(pass) : 0;
     g.shift = digit_shift(pass < 5 ? pass : 5);
-    g.pshift = 64 - 11 * pass; g.has_prefix = pass > 0; g.base = 0;
+    g.pshift = 64 - 11 * pass; g.has_prefix = pass > 0; g.base = 0; g.all_match = pass == 0;
   }
   return g;
 }
@@ -73,25 +70,24 @@ __device__ __forceinline__ Geom seg_geom(const uint64_t* st, int pass) {
 // Adds one key per lane to a CTA-private histogram.  All 32 lanes call this together (hit = this
 // lane contributes).  Lanes that fall into the same bin as the current leader are folded into one
 // shared atomic (two rounds: gauge data puts a whole warp into one or two bins in the first
-// pass); what is left after that is spread over many bins and goes in lane by lane.
-__device__ __forceinline__ void hist_add(unsigned int* h, bool hit, unsigned d, int lane,
-                                         unsigned long long* g = nullptr) {
+// pass); what is left after that is spread over many bins and goes in lane by lane.  `spread`
+// counts the calls in a row in which the first round folded next to nothing: from four on the
+// rounds are skipped (they cost more instructions than the atomics they save) until a row ends.
+__device__ __forceinline__ void hist_add(unsigned int* h, bool hit, unsigned d, int lane, int& spread) {
   unsigned todo = __ballot_sync(0xffffffffu, hit);
+  if (spread < 4) {
 #pragma unroll
-  for (int round = 0; round < 2; ++round) {
-    if (todo == 0) return;
-    const int leader = __ffs(todo) - 1;
-    const unsigned dl = __shfl_sync(0xffffffffu, d, leader);
-    const unsigned peers = __ballot_sync(0xffffffffu, hit && d == dl) & todo;
-    if (lane == leader) atomicAdd(&h[dl], (unsigned)__popc(peers));
-    todo &= ~peers;
+    for (int round = 0; round < 2; ++round) {
+      if (todo == 0) return;
+      const int leader = __ffs(todo) - 1;
+      const unsigned dl = __shfl_sync(0xffffffffu, d, leader);
+      const unsigned peers = __ballot_sync(0xffffffffu, hit && d == dl) & todo;
+      if (lane == leader) atomicAdd(&h[dl], (unsigned)__popc(peers));
+      if (round == 0) spread = (__popc(peers) <= 2 && __popc(todo) >= 16) ? spread + 1 : 0;
+      todo &= ~peers;
+    }
   }
-  // spread regime: shared atomics retire about one lane every two cycles per SM.  Optionally part
-  // of the lanes can send their increment to the L2 atomic units instead (PMX_HIST_SMEM_LANES < 8)
-  if ((todo >> lane) & 1) {
-    if (g != nullptr && (lane & 7) >= PMX_HIST_SMEM_LANES) atomicAdd(&g[d], 1ULL);
-    else atomicAdd(&h[d], 1u);
-  }
+  if ((todo >> lane) & 1) atomicAdd(&h[d], 1u);
 }
 
 // distinct prefixes of a segment's targets (lo/hi ranks and nearby quantiles usually share one)
@@ -115,13 +111,15 @@ __device__ __forceinline__ void load_prefixes(const uint64_t* __restrict__ state
 // mode 0: histogram only; mode 1 (pass 2): also append matching keys to the segment's candidate
 // list; mode 2 (pass >= 3): skip segments whose candidate list is complete (cand_hist_kernel
 // serves them).
+template <int MODE>
 __global__ void __launch_bounds__(256)
 hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __restrict__ seg,
             int n_t, int pass, const uint64_t* __restrict__ state, int sw,
             unsigned long long* __restrict__ hist, int rows_per_cta, int64_t n_rows,
             const int32_t* __restrict__ order,
-            int mode, unsigned long long* __restrict__ cand, unsigned int* __restrict__ cand_cnt, unsigned cap,
+            unsigned long long* __restrict__ cand, unsigned int* __restrict__ cand_cnt, unsigned cap,
             unsigned int* __restrict__ cand_overflow) {
+  constexpr int mode = MODE;
   extern __shared__ unsigned int sh[];                     // [n_uniq][BINS]
   __shared__ uint64_t s_uprefix[MAX_TARGETS];
   __shared__ int s_umap[MAX_TARGETS];
@@ -173,42 +171,98 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
     const int nu = s_nu;
     const Geom gm = s_geom;
     if (gm.bits == 0) continue;                            // this segment's keys are fully resolved
-    const int shift = gm.shift, pshift = gm.pshift;
-    const unsigned mask = (1u << gm.bits) - 1u;
+    const int shift = gm.shift, pshift = gm.pshift, bits = gm.bits;
+    const unsigned mask = (1u << bits) - 1u;
     const uint64_t kbase = gm.base;
+    const bool all_match = gm.all_match;
+    const bool use_bitmap = pass >= 2;                     // the previous digit exists and is 11 bits wide
+    int spread = 0;
+    // previous digits of up to four distinct prefixes in registers (the usual case: lo/hi ranks and
+    // neighbouring quantiles share prefixes); more go through the shared bitmap
+    unsigned pd0 = 0xffffffffu, pd1 = 0xffffffffu, pd2 = 0xffffffffu, pd3 = 0xffffffffu;
+    if (nu > 0) pd0 = (unsigned)s_uprefix[0] & (BINS - 1);
+    if (nu > 1) pd1 = (unsigned)s_uprefix[1] & (BINS - 1);
+    if (nu > 2) pd2 = (unsigned)s_uprefix[2] & (BINS - 1);
+    if (nu > 3) pd3 = (unsigned)s_uprefix[3] & (BINS - 1);
+    const bool few = nu <= 4;
+    const unsigned kb_lo = (unsigned)kbase, kb_hi = (unsigned)(kbase >> 32);
     const double* xr = x + s * n_steps;
     const bool vec = (reinterpret_cast<uintptr_t>(xr) & 15) == 0;
-    // loop trips are warp-uniform; every lane has four elements in flight per trip
+    // Trips are warp-uniform: every lane works on four elements per trip (two 16-byte loads, the
+    // second half a CTA-width further) while the next trip's four are already on their way.  Full
+    // trips need no bounds checks; the last, partial one is loaded element by element.
     const int64_t per_trip = (int64_t)blockDim.x * 4;
-    for (int64_t j0 = 0; j0 < n_steps; j0 += per_trip) {
-      double v[4];
+    const int64_t n_full = vec ? n_steps / per_trip : 0;
+    const int64_t n_trips = (n_steps + per_trip - 1) / per_trip;
+    const double qnan = __longlong_as_double(0x7FF8000000000000LL);
+    auto load_tail = [&](int64_t j0, double* v) {
       const int64_t ja = j0 + 2 * threadIdx.x, jb = ja + 2 * blockDim.x;
-      const double qnan = __longlong_as_double(0x7FF8000000000000LL);
-      if (vec && jb + 1 < n_steps) {
-        const double2 a = *reinterpret_cast<const double2*>(xr + ja);
-        const double2 b = *reinterpret_cast<const double2*>(xr + jb);
-        v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
-      } else {
-        v[0] = ja < n_steps ? xr[ja] : qnan; v[1] = ja + 1 < n_steps ? xr[ja + 1] : qnan;
-        v[2] = jb < n_steps ? xr[jb] : qnan; v[3] = jb + 1 < n_steps ? xr[jb + 1] : qnan;
+      v[0] = ja < n_steps ? xr[ja] : qnan; v[1] = ja + 1 < n_steps ? xr[ja + 1] : qnan;
+      v[2] = jb < n_steps ? xr[jb] : qnan; v[3] = jb + 1 < n_steps ? xr[jb + 1] : qnan;
+    };
+    const double2* pa = reinterpret_cast<const double2*>(xr) + threadIdx.x;     // first half of this lane's trip
+    const int64_t half = blockDim.x, stride = 2 * (int64_t)blockDim.x;          // in double2 units
+    double vn[4];
+    if (n_full > 0) { const double2 a = pa[0], b = pa[half]; vn[0] = a.x; vn[1] = a.y; vn[2] = b.x; vn[3] = b.y; }
+    else load_tail(0, vn);
+    for (int64_t trip = 0; trip < n_trips; ++trip) {
+      double v[4] = {vn[0], vn[1], vn[2], vn[3]};
+      if (trip + 1 < n_full) {
+        pa += stride;
+        const double2 a = pa[0], b = pa[half];
+        vn[0] = a.x; vn[1] = a.y; vn[2] = b.x; vn[3] = b.y;
+      } else if (trip + 1 < n_trips) {
+        load_tail((trip + 1) * per_trip, vn);
       }
+      // order-preserving key relative to the segment's base key, in 32-bit halves:
+      // key = bits ^ (sign ? ~0 : msb), then key - kbase with borrow; w = 32-bit view of the key
+      // from bit `shift` up: the digit and, above it, the previous digit
+      unsigned r_lo[4], r_hi[4], w[4];
+      bool valid[4];
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        const bool valid = v[i] == v[i];
-        const uint64_t key = f64_key(v[i]) - kbase;        // relative to the segment's base key
-        const unsigned d = (unsigned)(key >> shift) & mask;
-        if (pass == 0) { hist_add(sh, valid, d, lane, hist + (size_t)sg * BINS); continue; }
-        const uint64_t top = gm.has_prefix ? key >> pshift : 0;
-        // cheap filter first: does any target prefix end in this key's previous digit?
-        const unsigned pdig = (unsigned)top & (BINS - 1);
-        const bool maybe = valid && (pass < 2 || ((s_bitmap[pdig >> 5] >> (pdig & 31)) & 1));
-        if (__ballot_sync(0xffffffffu, maybe) == 0) continue;   // common case from pass 2 on
+        valid[i] = v[i] == v[i];
+        const unsigned b_lo = (unsigned)__double2loint(v[i]), b_hi = (unsigned)__double2hiint(v[i]);
+        const unsigned sm = (unsigned)((int)b_hi >> 31);
+        const unsigned k_lo = b_lo ^ sm, k_hi = b_hi ^ (sm | 0x80000000u);
+        r_lo[i] = k_lo - kb_lo; r_hi[i] = k_hi - kb_hi - (k_lo < kb_lo ? 1u : 0u);
+        w[i] = shift < 32 ? __funnelshift_r(r_lo[i], r_hi[i], shift) : r_hi[i] >> (shift - 32);
+      }
+      if (all_match) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) hist_add(sh, valid[i], w[i] & mask, lane, spread);
+        continue;
+      }
+      // cheap filter first, for the four elements at once: does any target prefix end in the key's
+      // previous digit?  From pass 2 on hardly any key passes and the whole trip is skipped.
+      bool maybe[4];
+      bool some = false;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        maybe[i] = valid[i];
+        if (use_bitmap) {
+          const unsigned pdig = (w[i] >> bits) & (BINS - 1);
+          if (few) maybe[i] = valid[i] & ((pdig == pd0) | (pdig == pd1) | (pdig == pd2) | (pdig == pd3));
+          else { const unsigned bm = s_bitmap[pdig >> 5]; maybe[i] = valid[i] & ((bm >> (pdig & 31)) & 1u); }
+        }
+        some |= maybe[i];
+      }
+      if (__ballot_sync(0xffffffffu, some) == 0) continue;
+#pragma unroll 1
+      for (int i = 0; i < 4; ++i) {
+        const bool mb = i == 0 ? maybe[0] : i == 1 ? maybe[1] : i == 2 ? maybe[2] : maybe[3];
+        if (__ballot_sync(0xffffffffu, mb) == 0) continue;
+        const unsigned lo = i == 0 ? r_lo[0] : i == 1 ? r_lo[1] : i == 2 ? r_lo[2] : r_lo[3];
+        const unsigned hi = i == 0 ? r_hi[0] : i == 1 ? r_hi[1] : i == 2 ? r_hi[2] : r_hi[3];
+        const unsigned wi = i == 0 ? w[0] : i == 1 ? w[1] : i == 2 ? w[2] : w[3];
+        const unsigned d = wi & mask;
+        const uint64_t key = ((uint64_t)hi << 32) | lo;
+        const uint64_t top = key >> pshift;                // has_prefix holds here: pshift < 64
         unsigned hits = 0;                                 // bit u: this lane's key carries distinct prefix u
-        for (int u = 0; u < nu; ++u) hits |= (maybe && top == s_uprefix[u]) ? (1u << u) : 0u;
+        for (int u = 0; u < nu; ++u) hits |= (mb && top == s_uprefix[u]) ? (1u << u) : 0u;
         const unsigned any = __ballot_sync(0xffffffffu, hits != 0);
         if (any == 0) continue;
-        for (int u = 0; u < nu; ++u)
-          hist_add(sh + u * BINS, (hits >> u) & 1, d, lane, hist + ((size_t)sg * n_h + s_urep[u]) * BINS);
+        for (int u = 0; u < nu; ++u) hist_add(sh + u * BINS, (hits >> u) & 1, d, lane, spread);
         if (mode == 1) {                                   // append to the candidate list, one atomic per warp
           const int leader = __ffs(any) - 1;
           unsigned base = 0;
@@ -255,13 +309,14 @@ cand_hist_kernel(const unsigned long long* __restrict__ cand, const unsigned int
   for (int i = threadIdx.x; i < nu * BINS; i += blockDim.x) sh[i] = 0;
   __syncthreads();
   const unsigned long long* keys = cand + (size_t)sg * cap;
+  int spread = 0;
   for (unsigned i0 = a; i0 < b; i0 += blockDim.x) {
     const unsigned i = i0 + threadIdx.x;
     const bool in = i < b;
     const uint64_t key = in ? keys[i] : 0;
     const unsigned d = (unsigned)(key >> shift) & mask;
     const uint64_t top = gm.has_prefix ? key >> pshift : 0;
-    for (int u = 0; u < nu; ++u) hist_add(sh + u * BINS, in && top == s_uprefix[u], d, lane);
+    for (int u = 0; u < nu; ++u) hist_add(sh + u * BINS, in && top == s_uprefix[u], d, lane, spread);
   }
   __syncthreads();
   for (int u = 0; u < nu; ++u) {
@@ -461,7 +516,9 @@ int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
     if (pass == 2) PMX_CUDA(cudaMemsetAsync(cand_cnt, 0, hdr, st));
   }
   const size_t smem = (size_t)n_h * BINS * sizeof(unsigned int);
-  PMX_CUDA(cudaFuncSetAttribute(hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(MAX_TARGETS * BINS * sizeof(unsigned int))));
+  PMX_CUDA(cudaFuncSetAttribute(hist_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(MAX_TARGETS * BINS * sizeof(unsigned int))));
+  PMX_CUDA(cudaFuncSetAttribute(hist_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(MAX_TARGETS * BINS * sizeof(unsigned int))));
+  PMX_CUDA(cudaFuncSetAttribute(hist_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(MAX_TARGETS * BINS * sizeof(unsigned int))));
   if (mode == 2) {
     PMX_CUDA(cudaFuncSetAttribute(cand_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(MAX_TARGETS * BINS * sizeof(unsigned int))));
     dim3 grid(32, (unsigned)n_seg);
@@ -479,9 +536,19 @@ int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
   int64_t rows = (n_rows + want_ctas - 1) / want_ctas;
   if (rows < 1) rows = 1;
   const int64_t grid = (n_rows + rows - 1) / rows;
-  hist_kernel<<<(unsigned)grid, 256, smem, st>>>(d_x, n_steps, d_seg, n_t, pass, d_state, state_words(n_q),
-                                                (unsigned long long*)d_hist, (int)rows, n_rows, d_row_order, mode,
-                                                cand, cand_cnt, cap, cand_cnt ? cand_cnt + n_seg : nullptr);
+  unsigned int* overflow = cand_cnt ? cand_cnt + n_seg : nullptr;
+  if (mode == 0)
+    hist_kernel<0><<<(unsigned)grid, 256, smem, st>>>(d_x, n_steps, d_seg, n_t, pass, d_state, state_words(n_q),
+                                                     (unsigned long long*)d_hist, (int)rows, n_rows, d_row_order,
+                                                     cand, cand_cnt, cap, overflow);
+  else if (mode == 1)
+    hist_kernel<1><<<(unsigned)grid, 256, smem, st>>>(d_x, n_steps, d_seg, n_t, pass, d_state, state_words(n_q),
+                                                     (unsigned long long*)d_hist, (int)rows, n_rows, d_row_order,
+                                                     cand, cand_cnt, cap, overflow);
+  else
+    hist_kernel<2><<<(unsigned)grid, 256, smem, st>>>(d_x, n_steps, d_seg, n_t, pass, d_state, state_words(n_q),
+                                                     (unsigned long long*)d_hist, (int)rows, n_rows, d_row_order,
+                                                     cand, cand_cnt, cap, overflow);
   PMX_LAUNCH_CHECK();
   return PMX_OK;
 }
