@@ -228,6 +228,12 @@ int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
  * d_min / d_max of an empty segment are ignored. */
 int pmx_quantile_init(pmx_ctx* ctx, const int64_t* d_count, const double* d_min, const double* d_max,
                       int64_t n_seg, const double* d_q, int64_t n_q, uint64_t* d_state, pmx_stream stream);
+/* Single GPU only (the candidate lists of pass 2 are local): finish every segment whose list is
+ * complete in one launch -- all passes from_pass..PMX_QUANTILE_PASSES for that segment, from its list
+ * alone.  Call it after pass 2's pick with from_pass = 3, then issue the remaining passes as usual:
+ * they return at once for finished segments and serve the ones whose list overflowed (heavy ties). */
+int pmx_quantile_tail(pmx_ctx* ctx, int64_t n_seg, int64_t n_q, int from_pass, uint64_t* d_state,
+                      pmx_stream stream);
 int pmx_quantile_pick(pmx_ctx* ctx, const uint64_t* d_hist, int64_t n_seg, const double* d_q,
                       int64_t n_q, int pass, uint64_t* d_state, pmx_stream stream);
 int pmx_quantile_finish(pmx_ctx* ctx, const uint64_t* d_state, int64_t n_seg, const double* d_q,

@@ -41,6 +41,8 @@ __host__ __device__ __forceinline__ int digit_bits(int pass) { return pass < 5 ?
 // A selection from count/min/max works on key - base, whose leading Z bits are zero for every
 // value of the segment, and starts behind them: pass p >= 1 takes bits [Z + 11(p-1), +11).
 constexpr int ST_HDR = 3;
+constexpr unsigned TAIL_KEYS = 8192;     // keys pmx_quantile_tail keeps in shared memory per segment
+constexpr int ST_RESOLVED_BIT = 40;      // in word [1]: every target's key is complete
 #define ST_PF(tg) (ST_HDR + 2 * (tg))
 #define ST_RK(tg) (ST_HDR + 2 * (tg) + 1)
 __host__ __device__ __forceinline__ int state_words(int64_t n_q) { return ST_HDR + 4 * (int)n_q; }
@@ -51,7 +53,7 @@ struct Geom { int shift; int bits; int pshift; bool has_prefix; bool all_match; 
 __device__ __forceinline__ Geom seg_geom(const uint64_t* st, int pass) {
   Geom g;
   const uint64_t w1 = st[1];
-  if (w1 >> 32) {
+  if ((w1 >> 32) & 1) {
     const int start = (int)(w1 & 0xff) + 11 * (pass - 1);         // key bits known before this pass
     int bits = 64 - start;
     if (bits > 11) bits = 11;
@@ -64,6 +66,7 @@ __device__ __forceinline__ Geom seg_geom(const uint64_t* st, int pass) {
     g.shift = digit_shift(pass < 5 ? pass : 5);
     g.pshift = 64 - 11 * pass; g.has_prefix = pass > 0; g.base = 0; g.all_match = pass == 0;
   }
+  if ((w1 >> ST_RESOLVED_BIT) & 1) g.bits = 0;                  // pmx_quantile_tail finished this segment
   return g;
 }
 
@@ -329,6 +332,135 @@ cand_hist_kernel(const unsigned long long* __restrict__ cand, const unsigned int
   }
 }
 
+// All remaining passes of one segment in one CTA, from its candidate list alone (single GPU: the
+// list holds every key that still matches a target).  Segments whose list overflowed are left to
+// the per-pass kernels; the others are marked resolved, and those kernels return at once for them.
+__global__ void __launch_bounds__(256)
+tail_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __restrict__ cand_cnt,
+            unsigned cap, int n_t, int from_pass, uint64_t* __restrict__ state, int sw) {
+  extern __shared__ unsigned long long skeys[];            // TAIL_KEYS keys that still match a target
+  __shared__ unsigned int sh[BINS];
+  __shared__ uint64_t s_old[MAX_TARGETS], s_pf[MAX_TARGETS], s_k[MAX_TARGETS], s_nk[MAX_TARGETS];
+  __shared__ unsigned int s_warp[8];
+  __shared__ unsigned int s_cnt;
+  const int sg = blockIdx.x;
+  uint64_t* st = state + (size_t)sg * sw;
+  const unsigned n_list = cand_cnt[sg];
+  if (st[0] == 0 || n_list > cap) return;                   // empty segment / overflowed list
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x < n_t) {
+    s_pf[threadIdx.x] = st[ST_PF(threadIdx.x)];
+    s_k[threadIdx.x] = s_nk[threadIdx.x] = st[ST_RK(threadIdx.x)];
+  }
+  if (threadIdx.x == 0) s_cnt = 0;
+  __syncthreads();
+  // The list was cut with the prefixes known during pass 2; pass 2's pick has since added a digit.
+  // One sweep (eight loads in flight per thread) keeps the keys that match a target's prefix as
+  // it is now -- a few per target unless values repeat -- in shared memory; the passes run on those.
+  {
+    const Geom g0 = seg_geom(st, from_pass);
+    const unsigned long long* glist = cand + (size_t)sg * cap;
+    for (unsigned i0 = 0; i0 < n_list; i0 += blockDim.x * 8) {
+      unsigned long long kk[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const unsigned i = i0 + u * blockDim.x + threadIdx.x;
+        kk[u] = i < n_list ? glist[i] : ~0ULL;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const unsigned i = i0 + u * blockDim.x + threadIdx.x;
+        bool hit = false;
+        if (i < n_list && g0.bits > 0) {
+          const uint64_t top = kk[u] >> g0.pshift;
+          for (int tg = 0; tg < n_t; ++tg) hit |= top == s_pf[tg];
+        }
+        if (hit) { const unsigned pos = atomicAdd(&s_cnt, 1u); if (pos < TAIL_KEYS) skeys[pos] = kk[u]; }
+      }
+    }
+  }
+  __syncthreads();
+  const unsigned n = s_cnt;
+  if (n > TAIL_KEYS) return;                                // many repeated values: the per-pass kernels take it
+  const unsigned long long* keys = skeys;
+  if (n <= 512) {
+    // A short list is settled directly: among the keys that carry the same prefix, key i has
+    // r keys below it and e equal to it, and it is target t's order statistic iff r <= k_t < r + e.
+    const Geom g0 = seg_geom(st, from_pass);
+    if (g0.bits > 0) {
+      for (unsigned i = threadIdx.x; i < n; i += blockDim.x) {
+        const uint64_t ki = keys[i], top = ki >> g0.pshift;
+        unsigned r = 0, e = 0;
+        for (unsigned j = 0; j < n; ++j) {
+          const uint64_t kj = keys[j];
+          if ((kj >> g0.pshift) == top) { r += kj < ki; e += kj == ki; }
+        }
+        for (int tg = 0; tg < n_t; ++tg)
+          if (s_pf[tg] == top && s_k[tg] >= r && s_k[tg] < (unsigned long long)r + e) { s_nk[tg] = ki; }
+      }
+      __syncthreads();
+      // s_nk now holds the complete keys; they become the prefixes, the ranks are used up
+      if (threadIdx.x < n_t) { st[ST_PF(threadIdx.x)] = s_nk[threadIdx.x]; st[ST_RK(threadIdx.x)] = 0; }
+    }
+    if (threadIdx.x == 0) st[1] |= 1ULL << ST_RESOLVED_BIT;
+    return;
+  }
+  constexpr int PER = BINS / 256;
+  for (int pass = from_pass; pass <= PMX_QUANTILE_PASSES; ++pass) {
+    const Geom gm = seg_geom(st, pass);
+    if (gm.bits == 0) break;                                // uniform: nothing left to resolve
+    const unsigned mask = (1u << gm.bits) - 1u;
+    __syncthreads();
+    if (threadIdx.x < n_t) s_old[threadIdx.x] = s_pf[threadIdx.x];
+    __syncthreads();
+    for (int tg = 0; tg < n_t; ++tg) {
+      bool is_rep = true;
+      for (int j = 0; j < tg; ++j) if (s_old[j] == s_old[tg]) { is_rep = false; break; }
+      if (!is_rep) continue;                                // uniform
+      for (int i = threadIdx.x; i < BINS; i += blockDim.x) sh[i] = 0;
+      __syncthreads();
+      const uint64_t want = s_old[tg];
+      int spread = 0;
+      for (unsigned i0 = 0; i0 < n; i0 += blockDim.x) {
+        const unsigned i = i0 + threadIdx.x;
+        const bool in = i < n;
+        const uint64_t key = in ? keys[i] : 0;
+        hist_add(sh, in && (key >> gm.pshift) == want, (unsigned)(key >> gm.shift) & mask, lane, spread);
+      }
+      __syncthreads();
+      unsigned int loc[PER]; unsigned int sum = 0;
+#pragma unroll
+      for (int i = 0; i < PER; ++i) { loc[i] = sh[threadIdx.x * PER + i]; sum += loc[i]; }
+      unsigned int inc = sum;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) { const unsigned v = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += v; }
+      if (lane == 31) s_warp[warp] = inc;
+      __syncthreads();
+      unsigned int base = 0;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) if (w < warp) base += s_warp[w];
+      for (int j = tg; j < n_t; ++j) {                      // every target that shares this prefix
+        if (s_old[j] != want) continue;
+        const unsigned long long k = s_k[j];                // ranks are replaced only after the pass (s_nk)
+        unsigned long long acc = base + inc - sum;
+#pragma unroll
+        for (int i = 0; i < PER; ++i) {
+          if (k >= acc && k < acc + loc[i]) {
+            s_pf[j] = (want << gm.bits) | (uint64_t)(threadIdx.x * PER + i);   // prefixes are compared through s_old
+            s_nk[j] = k - acc;
+          }
+          acc += loc[i];
+        }
+      }
+      __syncthreads();                                      // sh and s_warp are reused by the next prefix
+    }
+    if (threadIdx.x < n_t) s_k[threadIdx.x] = s_nk[threadIdx.x];
+  }
+  __syncthreads();
+  if (threadIdx.x < n_t) { st[ST_PF(threadIdx.x)] = s_pf[threadIdx.x]; st[ST_RK(threadIdx.x)] = s_k[threadIdx.x]; }
+  if (threadIdx.x == 0) st[1] |= 1ULL << ST_RESOLVED_BIT;
+}
+
 // One CTA per segment walks the segment's targets.  Targets that share a prefix share the
 // histogram of the first of them (the hist kernels fill only that one), so all old prefixes are
 // read before any is replaced.
@@ -466,7 +598,7 @@ __global__ void finish_kernel(const uint64_t* __restrict__ state, int sw, int64_
   if (lo > n - 1) lo = n - 1;
   const unsigned long long hi = lo + 1 < n ? lo + 1 : n - 1;
   const double t = pos - (double)lo;
-  const uint64_t base = (st[1] >> 32) ? st[2] : 0;
+  const uint64_t base = ((st[1] >> 32) & 1) ? st[2] : 0;
   const double a = key_f64(st[ST_PF(2 * qi)] + base);
   const double b = key_f64(st[ST_PF(2 * qi + 1)] + base);
   // numpy _lerp: a + (b-a)*t, and b - (b-a)*(1-t) when t >= 0.5 (no FMA contraction)
@@ -481,6 +613,22 @@ __global__ void finish_kernel(const uint64_t* __restrict__ state, int sw, int64_
 }
 
 }  // namespace
+
+// candidate lists in ctx scratch: [n_seg counts, overflow flag | padding][n_seg * cap keys]
+static int cand_layout(pmx_ctx* ctx, int64_t n_seg, unsigned* cap, unsigned int** cand_cnt, unsigned long long** cand,
+                       size_t* hdr_bytes) {
+  int64_t c = ((int64_t)256 << 20) / 8 / n_seg;
+  if (c > (1 << 20)) c = 1 << 20;
+  if (c < 4096) c = 4096;
+  *cap = (unsigned)c;
+  const size_t hdr = ((size_t)(n_seg + 1) * sizeof(unsigned int) + 255) & ~size_t(255);
+  unsigned char* scr = (unsigned char*)pmx_scratch(ctx, PMX_SCR_QCAND, hdr + (size_t)n_seg * c * 8);
+  if (!scr) return PMX_E_CUDA;
+  *cand_cnt = (unsigned int*)scr;
+  *cand = (unsigned long long*)(scr + hdr);
+  if (hdr_bytes) *hdr_bytes = hdr;
+  return PMX_OK;
+}
 
 extern "C" {
 
@@ -503,15 +651,8 @@ int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
   unsigned cap = 0; unsigned int* cand_cnt = nullptr; unsigned long long* cand = nullptr;
   int mode = 0;
   if (pass >= 2) {
-    int64_t c = ((int64_t)256 << 20) / 8 / n_seg;
-    if (c > (1 << 20)) c = 1 << 20;
-    if (c < 4096) c = 4096;
-    cap = (unsigned)c;
-    const size_t hdr = ((size_t)(n_seg + 1) * sizeof(unsigned int) + 255) & ~size_t(255);   // counts + overflow flag
-    unsigned char* scr = (unsigned char*)pmx_scratch(ctx, PMX_SCR_QCAND, hdr + (size_t)n_seg * cap * 8);
-    if (!scr) return PMX_E_CUDA;
-    cand_cnt = (unsigned int*)scr;
-    cand = (unsigned long long*)(scr + hdr);
+    size_t hdr;
+    if (int rc = cand_layout(ctx, n_seg, &cap, &cand_cnt, &cand, &hdr)) return rc;
     mode = pass == 2 ? 1 : 2;
     if (pass == 2) PMX_CUDA(cudaMemsetAsync(cand_cnt, 0, hdr, st));
   }
@@ -549,6 +690,23 @@ int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
     hist_kernel<2><<<(unsigned)grid, 256, smem, st>>>(d_x, n_steps, d_seg, n_t, pass, d_state, state_words(n_q),
                                                      (unsigned long long*)d_hist, (int)rows, n_rows, d_row_order,
                                                      cand, cand_cnt, cap, overflow);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
+int pmx_quantile_tail(pmx_ctx* ctx, int64_t n_seg, int64_t n_q, int from_pass, uint64_t* d_state, pmx_stream stream) {
+  PMX_REQUIRE(ctx, "ctx is NULL");
+  PMX_REQUIRE(n_seg >= 0 && n_seg <= 65535, "n_seg must be in [0, 65535]");
+  PMX_REQUIRE(n_q >= 1 && 2 * n_q <= MAX_TARGETS, "n_q must be in [1, 8]");
+  PMX_REQUIRE(from_pass >= 3 && from_pass <= PMX_QUANTILE_PASSES, "from_pass must follow pass 2 (which builds the candidate lists)");
+  if (n_seg == 0) return PMX_OK;
+  PMX_REQUIRE(d_state, "NULL buffer");
+  unsigned cap; unsigned int* cand_cnt; unsigned long long* cand;
+  if (int rc = cand_layout(ctx, n_seg, &cap, &cand_cnt, &cand, nullptr)) return rc;
+  const size_t smem = (size_t)TAIL_KEYS * sizeof(unsigned long long);
+  PMX_CUDA(cudaFuncSetAttribute(tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  tail_kernel<<<(unsigned)n_seg, 256, smem, pmx_st(stream)>>>(cand, cand_cnt, cap, 2 * (int)n_q, from_pass, d_state,
+                                                            state_words(n_q));
   PMX_LAUNCH_CHECK();
   return PMX_OK;
 }
@@ -612,6 +770,10 @@ int pmx_quantile_select(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64
   uint64_t* hist = (uint64_t*)(scr + state_bytes);
   PMX_CUDA(cudaMemsetAsync(state, 0, state_bytes, pmx_st(stream)));
   for (int pass = 0; pass < PMX_QUANTILE_PASSES; ++pass) {
+    if (pass == 3 && n_series > 0 && n_steps > 0) {         // the lists of pass 2 settle most segments at once
+      const int rc = pmx_quantile_tail(ctx, n_seg, n_q, 3, state, stream);
+      if (rc) return rc;
+    }
     int rc = pmx_quantile_hist(ctx, d_x, n_series, n_steps, d_seg, n_seg, d_row_order, n_rows, n_q, pass, state, hist,
                                stream);
     if (rc) return rc;

@@ -469,7 +469,7 @@ class Engine:
                 self._ptr(outs["n"]),
                 self._ptr(outs["lo"]), self._ptr(outs["hi"]), self._ptr(outs["x_lo"]), self._ptr(outs["x_hi"]),
                 self._ptr(outs["value"]), self._stream()))
-            self.launches += 3 * _abi.QUANTILE_PASSES - 2    # hist (two kernels from pass 3 on) + pick + finish
+            self.launches += 3 * _abi.QUANTILE_PASSES - 1    # hist (two kernels from pass 3 on) + pick + tail + finish
             return outs
         state, hist = buffers if buffers is not None else self.quantile_buffers(n_seg, n_q)
         if summary is None:
@@ -494,6 +494,9 @@ class Engine:
                 dist.all_reduce(hist[:n_h], op=dist.ReduceOp.SUM, group=group)
             _abi.check(self.lib.pmx_quantile_pick(self.ctx, self._ptr(hist), n_seg, self._ptr(d_q), n_q, p,
                                                   self._ptr(state), self._stream()))
+            if p == 2 and group is None and S > 0 and T > 0:   # one rank: the candidate lists hold everything
+                _abi.check(self.lib.pmx_quantile_tail(self.ctx, n_seg, n_q, 3, self._ptr(state), self._stream()))
+                self.launches += 1
         _abi.check(self.lib.pmx_quantile_finish(self.ctx, self._ptr(state), n_seg, self._ptr(d_q), n_q,
                                                 self._ptr(outs["n"]), self._ptr(outs["lo"]), self._ptr(outs["hi"]),
                                                 self._ptr(outs["x_lo"]), self._ptr(outs["x_hi"]),
