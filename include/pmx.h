@@ -32,6 +32,7 @@ extern "C" {
 #define PMX_QUANTILE_DIGIT_BITS 11           /* radix-select digit: 2048-bin histograms      */
 #define PMX_QUANTILE_BINS 2048
 #define PMX_QUANTILE_PASSES 6                /* 11+11+11+11+11+9 = 64 key bits               */
+#define PMX_QUANTILE_GATHER_ROW 1024   /* uint64 words per segment and rank in pmx_quantile_tail_filter rows */
 
 typedef enum pmx_status {
   PMX_OK = 0,
@@ -234,6 +235,16 @@ int pmx_quantile_init(pmx_ctx* ctx, const int64_t* d_count, const double* d_min,
  * they return at once for finished segments and serve the ones whose list overflowed (heavy ties). */
 int pmx_quantile_tail(pmx_ctx* ctx, int64_t n_seg, int64_t n_q, int from_pass, uint64_t* d_state,
                       pmx_stream stream);
+/* The same for several GPUs, after pass 2's pick: every rank writes the keys of its lists that match
+ * a target as it stands now (d_rows: uint64 [n_seg * PMX_QUANTILE_GATHER_ROW], row = count, keys),
+ * the rows are all-gathered ([n_ranks][n_seg][ROW], rank-major), and pmx_quantile_tail_merge settles
+ * every segment from the union on every rank alike.  *d_unresolved (device int32) counts the
+ * segments that did not fit (many repeated values); if it is 0 -- the same on all ranks -- passes
+ * from_pass.. and their all-reduces can be left out, otherwise they run as usual. */
+int pmx_quantile_tail_filter(pmx_ctx* ctx, int64_t n_seg, int64_t n_q, int from_pass, const uint64_t* d_state,
+                             uint64_t* d_rows, pmx_stream stream);
+int pmx_quantile_tail_merge(pmx_ctx* ctx, const uint64_t* d_rows_all, int n_ranks, int64_t n_seg, int64_t n_q,
+                            int from_pass, uint64_t* d_state, int32_t* d_unresolved, pmx_stream stream);
 int pmx_quantile_pick(pmx_ctx* ctx, const uint64_t* d_hist, int64_t n_seg, const double* d_q,
                       int64_t n_q, int pass, uint64_t* d_state, pmx_stream stream);
 int pmx_quantile_finish(pmx_ctx* ctx, const uint64_t* d_state, int64_t n_seg, const double* d_q,

@@ -15,6 +15,7 @@ LIB_PATH = os.environ.get("PMX_LIB_PATH") or os.path.join(HERE, "libpmx.so")   #
 OK, E_INVALID, E_CUDA, E_VALUE, E_KEY, E_CAPACITY, E_JSON, E_LIMIT = 0, -1, -2, -3, -4, -5, -6, -7
 QUANTILE_BINS = 2048
 QUANTILE_PASSES = 6
+QUANTILE_GATHER_ROW = 1024
 INT64_MAX = (1 << 63) - 1
 
 
@@ -65,6 +66,8 @@ SIGNATURES = {
     "pmx_quantile_hist": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _i64, _i64, _int, _p, _p, _p]),
     "pmx_quantile_init": (_int, [_p, _p, _p, _p, _i64, _p, _i64, _p, _p]),
     "pmx_quantile_tail": (_int, [_p, _i64, _i64, _int, _p, _p]),
+    "pmx_quantile_tail_filter": (_int, [_p, _i64, _i64, _int, _p, _p, _p]),
+    "pmx_quantile_tail_merge": (_int, [_p, _p, _int, _i64, _i64, _int, _p, _p, _p]),
     "pmx_quantile_pick": (_int, [_p, _p, _i64, _p, _i64, _int, _p, _p]),
     "pmx_quantile_finish": (_int, [_p, _p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _p]),
     "pmx_quantile_select": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _p]),

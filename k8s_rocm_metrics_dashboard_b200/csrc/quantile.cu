@@ -42,6 +42,8 @@ __host__ __device__ __forceinline__ int digit_bits(int pass) { return pass < 5 ?
 // value of the segment, and starts behind them: pass p >= 1 takes bits [Z + 11(p-1), +11).
 constexpr int ST_HDR = 3;
 constexpr unsigned TAIL_KEYS = 8192;     // keys pmx_quantile_tail keeps in shared memory per segment
+constexpr unsigned GATHER_ROW = PMX_QUANTILE_GATHER_ROW;   // per segment and rank: count, then up to ROW-1 keys
+constexpr unsigned GATHER_KEYS = GATHER_ROW - 1;
 constexpr int ST_RESOLVED_BIT = 40;      // in word [1]: every target's key is complete
 #define ST_PF(tg) (ST_HDR + 2 * (tg))
 #define ST_RK(tg) (ST_HDR + 2 * (tg) + 1)
@@ -335,9 +337,16 @@ cand_hist_kernel(const unsigned long long* __restrict__ cand, const unsigned int
 // All remaining passes of one segment in one CTA, from its candidate list alone (single GPU: the
 // list holds every key that still matches a target).  Segments whose list overflowed are left to
 // the per-pass kernels; the others are marked resolved, and those kernels return at once for them.
+//
+// GATHERED = true: the keys come from the rows pmx_quantile_tail_filter wrote on every rank, after an
+// all-gather ([n_ranks][n_seg][ROW], row = count then keys): each rank settles every segment from the
+// union, identically.  A segment that does not fit (a rank kept more than GATHER_KEYS keys, or the
+// union exceeds TAIL_KEYS) is counted in *unresolved and left to the per-pass protocol.
+template <bool GATHERED>
 __global__ void __launch_bounds__(256)
 tail_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __restrict__ cand_cnt,
-            unsigned cap, int n_t, int from_pass, uint64_t* __restrict__ state, int sw) {
+            unsigned cap, int n_t, int from_pass, uint64_t* __restrict__ state, int sw,
+            const unsigned long long* __restrict__ rows, int n_ranks, unsigned int* __restrict__ unresolved) {
   extern __shared__ unsigned long long skeys[];            // TAIL_KEYS keys that still match a target
   __shared__ unsigned int sh[BINS];
   __shared__ uint64_t s_old[MAX_TARGETS], s_pf[MAX_TARGETS], s_k[MAX_TARGETS], s_nk[MAX_TARGETS];
@@ -345,7 +354,7 @@ tail_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __r
   __shared__ unsigned int s_cnt;
   const int sg = blockIdx.x;
   uint64_t* st = state + (size_t)sg * sw;
-  const unsigned n_list = cand_cnt[sg];
+  const unsigned n_list = GATHERED ? 0u : cand_cnt[sg];
   if (st[0] == 0 || n_list > cap) return;                   // empty segment / overflowed list
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (threadIdx.x < n_t) {
@@ -357,7 +366,22 @@ tail_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __r
   // The list was cut with the prefixes known during pass 2; pass 2's pick has since added a digit.
   // One sweep (eight loads in flight per thread) keeps the keys that match a target's prefix as
   // it is now -- a few per target unless values repeat -- in shared memory; the passes run on those.
-  {
+  if (GATHERED) {
+    unsigned total = 0; bool fits = true;
+    for (int r = 0; r < n_ranks; ++r) {
+      const unsigned long long c = rows[((size_t)r * gridDim.x + sg) * GATHER_ROW];
+      if (c > GATHER_KEYS) fits = false; else total += (unsigned)c;
+    }
+    if (!fits || total > TAIL_KEYS) { if (threadIdx.x == 0) atomicAdd(unresolved, 1u); return; }
+    unsigned off = 0;
+    for (int r = 0; r < n_ranks; ++r) {
+      const unsigned long long* row = rows + ((size_t)r * gridDim.x + sg) * GATHER_ROW;
+      const unsigned c = (unsigned)row[0];
+      for (unsigned i = threadIdx.x; i < c; i += blockDim.x) skeys[off + i] = row[1 + i];
+      off += c;
+    }
+    if (threadIdx.x == 0) s_cnt = total;
+  } else {
     const Geom g0 = seg_geom(st, from_pass);
     const unsigned long long* glist = cand + (size_t)sg * cap;
     for (unsigned i0 = 0; i0 < n_list; i0 += blockDim.x * 8) {
@@ -459,6 +483,48 @@ tail_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __r
   __syncthreads();
   if (threadIdx.x < n_t) { st[ST_PF(threadIdx.x)] = s_pf[threadIdx.x]; st[ST_RK(threadIdx.x)] = s_k[threadIdx.x]; }
   if (threadIdx.x == 0) st[1] |= 1ULL << ST_RESOLVED_BIT;
+}
+
+// Multi-GPU form of the tail, step 1: every rank writes, per segment, the keys of its candidate
+// list that match a target's prefix as it is now (row = count, keys).  The count is ~0 when the
+// list itself overflowed and may exceed GATHER_KEYS (then only the first GATHER_KEYS keys are there).
+__global__ void __launch_bounds__(256)
+tail_filter_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __restrict__ cand_cnt,
+                   unsigned cap, int n_t, int from_pass, const uint64_t* __restrict__ state, int sw,
+                   unsigned long long* __restrict__ rows) {
+  __shared__ uint64_t s_pf[MAX_TARGETS];
+  __shared__ unsigned int s_cnt;
+  const int sg = blockIdx.x;
+  const uint64_t* st = state + (size_t)sg * sw;
+  unsigned long long* row = rows + (size_t)sg * GATHER_ROW;
+  const unsigned n_list = cand_cnt[sg];
+  if (st[0] == 0) { if (threadIdx.x == 0) row[0] = 0; return; }
+  if (n_list > cap) { if (threadIdx.x == 0) row[0] = ~0ULL; return; }
+  if (threadIdx.x < n_t) s_pf[threadIdx.x] = st[ST_PF(threadIdx.x)];
+  if (threadIdx.x == 0) s_cnt = 0;
+  __syncthreads();
+  const Geom g0 = seg_geom(st, from_pass);
+  const unsigned long long* glist = cand + (size_t)sg * cap;
+  for (unsigned i0 = 0; i0 < n_list; i0 += blockDim.x * 8) {
+    unsigned long long kk[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const unsigned i = i0 + u * blockDim.x + threadIdx.x;
+      kk[u] = i < n_list ? glist[i] : ~0ULL;
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const unsigned i = i0 + u * blockDim.x + threadIdx.x;
+      bool hit = false;
+      if (i < n_list && g0.bits > 0) {
+        const uint64_t top = kk[u] >> g0.pshift;
+        for (int tg = 0; tg < n_t; ++tg) hit |= top == s_pf[tg];
+      }
+      if (hit) { const unsigned pos = atomicAdd(&s_cnt, 1u); if (pos < GATHER_KEYS) row[1 + pos] = kk[u]; }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) row[0] = s_cnt;
 }
 
 // One CTA per segment walks the segment's targets.  Targets that share a prefix share the
@@ -704,9 +770,46 @@ int pmx_quantile_tail(pmx_ctx* ctx, int64_t n_seg, int64_t n_q, int from_pass, u
   unsigned cap; unsigned int* cand_cnt; unsigned long long* cand;
   if (int rc = cand_layout(ctx, n_seg, &cap, &cand_cnt, &cand, nullptr)) return rc;
   const size_t smem = (size_t)TAIL_KEYS * sizeof(unsigned long long);
-  PMX_CUDA(cudaFuncSetAttribute(tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  tail_kernel<<<(unsigned)n_seg, 256, smem, pmx_st(stream)>>>(cand, cand_cnt, cap, 2 * (int)n_q, from_pass, d_state,
-                                                            state_words(n_q));
+  PMX_CUDA(cudaFuncSetAttribute(tail_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  tail_kernel<false><<<(unsigned)n_seg, 256, smem, pmx_st(stream)>>>(cand, cand_cnt, cap, 2 * (int)n_q, from_pass, d_state,
+                                                                   state_words(n_q), nullptr, 1, nullptr);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
+int pmx_quantile_tail_filter(pmx_ctx* ctx, int64_t n_seg, int64_t n_q, int from_pass, const uint64_t* d_state,
+                             uint64_t* d_rows, pmx_stream stream) {
+  PMX_REQUIRE(ctx, "ctx is NULL");
+  PMX_REQUIRE(n_seg >= 0 && n_seg <= 65535, "n_seg must be in [0, 65535]");
+  PMX_REQUIRE(n_q >= 1 && 2 * n_q <= MAX_TARGETS, "n_q must be in [1, 8]");
+  PMX_REQUIRE(from_pass >= 3 && from_pass <= PMX_QUANTILE_PASSES, "from_pass must follow pass 2 (which builds the candidate lists)");
+  if (n_seg == 0) return PMX_OK;
+  PMX_REQUIRE(d_state && d_rows, "NULL buffer");
+  unsigned cap; unsigned int* cand_cnt; unsigned long long* cand;
+  if (int rc = cand_layout(ctx, n_seg, &cap, &cand_cnt, &cand, nullptr)) return rc;
+  tail_filter_kernel<<<(unsigned)n_seg, 256, 0, pmx_st(stream)>>>(cand, cand_cnt, cap, 2 * (int)n_q, from_pass, d_state,
+                                                                state_words(n_q), (unsigned long long*)d_rows);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
+int pmx_quantile_tail_merge(pmx_ctx* ctx, const uint64_t* d_rows_all, int n_ranks, int64_t n_seg, int64_t n_q,
+                            int from_pass, uint64_t* d_state, int32_t* d_unresolved, pmx_stream stream) {
+  PMX_REQUIRE(ctx, "ctx is NULL");
+  PMX_REQUIRE(n_seg >= 0 && n_seg <= 65535, "n_seg must be in [0, 65535]");
+  PMX_REQUIRE(n_q >= 1 && 2 * n_q <= MAX_TARGETS, "n_q must be in [1, 8]");
+  PMX_REQUIRE(n_ranks >= 1, "n_ranks must be positive");
+  PMX_REQUIRE(from_pass >= 3 && from_pass <= PMX_QUANTILE_PASSES, "from_pass must follow pass 2");
+  PMX_REQUIRE(d_unresolved, "NULL buffer");
+  cudaStream_t st = pmx_st(stream);
+  PMX_CUDA(cudaMemsetAsync(d_unresolved, 0, sizeof(int32_t), st));
+  if (n_seg == 0) return PMX_OK;
+  PMX_REQUIRE(d_state && d_rows_all, "NULL buffer");
+  const size_t smem = (size_t)TAIL_KEYS * sizeof(unsigned long long);
+  PMX_CUDA(cudaFuncSetAttribute(tail_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  tail_kernel<true><<<(unsigned)n_seg, 256, smem, st>>>(nullptr, nullptr, 0xffffffffu, 2 * (int)n_q, from_pass, d_state,
+                                                      state_words(n_q), (const unsigned long long*)d_rows_all, n_ranks,
+                                                      (unsigned int*)d_unresolved);
   PMX_LAUNCH_CHECK();
   return PMX_OK;
 }

@@ -442,6 +442,16 @@ class Engine:
         hist = self._empty((n_seg * 2 * n_q, _abi.QUANTILE_BINS), t.int64)
         return state, hist
 
+    def _tail_buffers(self, n_seg, world):
+        t = self.torch
+        key = (n_seg, world)
+        cache = self.__dict__.setdefault("_tailbuf", {})
+        if key not in cache:
+            row = _abi.QUANTILE_GATHER_ROW
+            cache[key] = (self._empty((n_seg * row,), t.int64), self._empty((world * n_seg * row,), t.int64),
+                          self._empty((1,), t.int32))
+        return cache[key]
+
     def quantiles(self, x, seg, n_seg, qs, group=None, buffers=None, row_order=None, summary=None):
         """Exact quantiles per segment.  x: [S,T] device; seg: int per series (host or device).
         With ``group`` (a torch.distributed process group over NCCL) the histograms of every pass
@@ -485,6 +495,7 @@ class Engine:
             self.launches += 1
             passes = range(1, _abi.QUANTILE_PASSES + 1)
         for p in passes:
+            self.launches += 3 if p >= 3 else 2             # hist (two kernels from pass 3 on) + pick
             _abi.check(self.lib.pmx_quantile_hist(self.ctx, self._ptr(x), S, T, self._ptr(d_seg), n_seg,
                                                   self._ptr(d_ord), n_rows, n_q, p,
                                                   self._ptr(state), self._ptr(hist), self._stream()))
@@ -497,9 +508,28 @@ class Engine:
             if p == 2 and group is None and S > 0 and T > 0:   # one rank: the candidate lists hold everything
                 _abi.check(self.lib.pmx_quantile_tail(self.ctx, n_seg, n_q, 3, self._ptr(state), self._stream()))
                 self.launches += 1
+            elif p == 2 and group is not None:
+                # several ranks: gather the few keys that still match a target and settle every segment
+                # on every rank alike; the later passes (and their all-reduces) run only if a segment
+                # did not fit, which all ranks see in the same counter
+                import torch.distributed as dist
+                world = dist.get_world_size(group)
+                rows, gathered, unresolved = self._tail_buffers(n_seg, world)
+                if S > 0 and T > 0:
+                    _abi.check(self.lib.pmx_quantile_tail_filter(self.ctx, n_seg, n_q, 3, self._ptr(state),
+                                                                 self._ptr(rows), self._stream()))
+                    self.launches += 1
+                else:
+                    rows.zero_()
+                dist.all_gather_into_tensor(gathered, rows, group=group)
+                _abi.check(self.lib.pmx_quantile_tail_merge(self.ctx, self._ptr(gathered), world, n_seg, n_q, 3,
+                                                            self._ptr(state), self._ptr(unresolved), self._stream()))
+                self.launches += 1
+                if int(unresolved.item()) == 0:
+                    break
         _abi.check(self.lib.pmx_quantile_finish(self.ctx, self._ptr(state), n_seg, self._ptr(d_q), n_q,
                                                 self._ptr(outs["n"]), self._ptr(outs["lo"]), self._ptr(outs["hi"]),
                                                 self._ptr(outs["x_lo"]), self._ptr(outs["x_hi"]),
                                                 self._ptr(outs["value"]), self._stream()))
-        self.launches += 3 * _abi.QUANTILE_PASSES - 2 + (1 if summary is not None else 0)   # passes 1..6: one more candidate pass
+        self.launches += 1                                  # finish
         return outs
