@@ -54,13 +54,18 @@ def combine_group_partials(sm, cnt, mn, mx, group=None):
     mn = torch.where(cnt > 0, mn, torch.full_like(mn, inf))
     mx = torch.where(cnt > 0, mx, torch.full_like(mx, -inf))
     if dist.is_initialized() and dist.get_world_size(group) > 1:
-        # two collectives instead of four: the exchanges are latency-bound (a few KB each)
-        add = torch.stack([sm, cnt.to(sm.dtype)])            # counts stay exact in float64 below 2^53
-        ext = torch.stack([-mn, mx])                         # min(x) = -max(-x)
-        dist.all_reduce(add, op=dist.ReduceOp.SUM, group=group)
-        dist.all_reduce(ext, op=dist.ReduceOp.MAX, group=group)
-        sm, cnt = add[0], add[1].round().to(cnt.dtype)
-        mn, mx = -ext[0], ext[1]
+        # one collective: the exchange is latency-bound (a few KB), so everything travels in one
+        # all-gather and is folded locally, from identical data on every rank (sums are then
+        # bit-identical across ranks whatever the collective's internal order)
+        world = dist.get_world_size(group)
+        packed = torch.stack([sm, cnt.to(sm.dtype), mn, mx]).contiguous()   # counts exact in float64 below 2^53
+        parts = [torch.empty_like(packed) for _ in range(world)]
+        dist.all_gather(parts, packed, group=group)         # (all_gather_into_tensor is not in gloo)
+        gathered = torch.stack(parts)
+        both = gathered[:, 0:2].sum(dim=0)                  # same data and layout on every rank: same result
+        sm, cnt = both[0], both[1].round().to(cnt.dtype)
+        mn = gathered[:, 2].min(dim=0).values
+        mx = gathered[:, 3].max(dim=0).values
     nan = torch.full_like(mn, float("nan"))
     any_ = cnt > 0
     mean = torch.where(any_, sm / cnt.to(sm.dtype).clamp(min=1), nan)
