@@ -10,12 +10,15 @@
 // After the last pass every target's prefix IS the key of the wanted order statistic.  Targets
 // per segment: for each q the ranks lo = floor((n-1)q) and hi = min(lo+1, n-1), then numpy's
 // _lerp.  No sample ever moves between GPUs; a pass exchanges 16 KiB per target.
-// Passes 0-2 read every value.  Pass 2 also copies the keys that still match a target prefix
-// (22 bits known by then) into a per-segment candidate list; passes 3-5 read only that list.
-// A segment whose list overflows (heavy ties) keeps reading the full data.
+// Passes 0-2 read every value (with pmx_quantile_init there is no pass 0: keys are taken relative
+// to the segment's minimum and the bits its range leaves zero are skipped).  Pass 2 also copies
+// the keys that still match a target prefix into a per-segment candidate list; later passes read
+// only that list -- all of them at once in pmx_quantile_tail (one GPU) or after an all-gather of
+// the few keys left (pmx_quantile_tail_filter / _merge).  A segment whose list overflows (many
+// repeated values) keeps reading the full data in the per-pass kernels.
 //
-// State per segment (uint64 words): [0] n, [1] reserved, then per target t: [2+2t] prefix,
-// [3+2t] remaining rank inside the prefix bucket.
+// State per segment (uint64 words): [0] n, [1] how the selection began and whether it is finished,
+// [2] base key, then per target t: [3+2t] prefix, [4+2t] remaining rank inside the prefix bucket.
 #include <stdlib.h>
 #include "pmx_common.cuh"
 

@@ -2,11 +2,13 @@
 
 Series are independent for decode / align / rolling / rate, so ranks never exchange samples.
 The only exchange steps are
-  * per-group partials (sum, count, min, max) -- one all-reduce each (SUM, SUM, MIN, MAX) over
-    ``n_groups`` numbers, for groups that span ranks (cluster-wide per-metric groups);
-  * exact quantiles -- per pass, the 2048-bin histograms of every (segment, target) are summed
-    with one all-reduce (16 KiB per histogram), then every rank picks the same bin on its
-    own device (pmx_quantile_pick): no sample movement, no host round trip inside the passes.
+  * per-group partials (sum, count, min, max) -- one all-gather of 4 x ``n_groups`` numbers, folded
+    locally from identical data on every rank, for groups that span ranks (per-metric groups);
+  * exact quantiles -- for the first passes the 2048-bin histograms of every (segment, target) are
+    summed with one all-reduce per pass (16 KiB per histogram) and every rank picks the same bin
+    on its own device (pmx_quantile_pick); after pass 2 the few keys that still match a target are
+    all-gathered and every rank settles the segments from the union (Engine.quantiles).  No
+    sample moves between ranks apart from those few keys.
 ``torch.distributed`` (NCCL over NVLink/NVSwitch on GPUs, gloo in the CPU tests) is the plumbing.
 The combine logic is written against tensors and a process group so that the world_size-2
 gloo tests exercise exactly this code with CPU tensors.
@@ -77,8 +79,9 @@ def distributed_quantiles(hist_fn, pick_fn, finish_fn, n_seg, n_q, group=None, p
 
     hist_fn(pass) -> int64 tensor [n_hist, 2048] of LOCAL counts (n_hist = n_seg for pass 0,
     n_seg*2*n_q afterwards); pick_fn(pass, reduced_hist) advances the per-target state;
-    finish_fn() returns the result.  The GPU engine plugs its kernels in (Engine.quantiles does
-    the same inline); the gloo tests plug in a numpy restatement."""
+    finish_fn() returns the result.  This is the per-pass form, which Engine.quantiles runs for
+    the first passes (and for all of them when a segment's remaining keys do not fit the gathered
+    rows); the gloo tests plug in a numpy restatement."""
     import torch.distributed as dist
     for p in range(passes):
         h = hist_fn(p)

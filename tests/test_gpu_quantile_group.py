@@ -1,0 +1,68 @@
+"""The several-GPU form of the quantile selection on one GPU: a one-rank NCCL group makes
+Engine.quantiles take the per-pass protocol with its collectives (histogram all-reduce, row
+all-gather, pmx_quantile_tail_filter / pmx_quantile_tail_merge) instead of the single-call path.
+The N > 1 runs are tests/multi_gpu_check.py under torchrun."""
+import numpy as np
+import pytest
+
+from k8s_rocm_metrics_dashboard_b200 import group_index
+from oracle import prom_oracle as O
+from tests.util import assert_bits_equal
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def world1():
+    import torch.distributed as dist
+    if dist.is_initialized():
+        yield dist.group.WORLD
+        return
+    dist.init_process_group(backend="nccl", init_method="tcp://127.0.0.1:29577", world_size=1, rank=0)
+    yield dist.group.WORLD
+    dist.destroy_process_group()
+
+
+def _check(eng, group, x, seg, n_seg, qs, summary):
+    out = eng.quantiles(x, seg, n_seg, qs, group=group, row_order=group_index(np.asarray(seg), n_seg)[0], summary=summary)
+    for g in range(n_seg):
+        o = O.quantiles(x[np.asarray(seg) == g], qs)
+        assert int(out["n"].cpu().numpy()[g]) == o["n"]
+        assert_bits_equal(out["x_lo"].cpu().numpy()[g], np.array(o["x_lo"]), "x_lo")
+        assert_bits_equal(out["x_hi"].cpu().numpy()[g], np.array(o["x_hi"]), "x_hi")
+        assert_bits_equal(out["value"].cpu().numpy()[g], np.array(o["value"]), "value")
+
+
+def _summary(x, seg, n_seg):
+    cnt = np.zeros(n_seg, dtype=np.int64); mn = np.full(n_seg, np.nan); mx = np.full(n_seg, np.nan)
+    for g in range(n_seg):
+        v = x[np.asarray(seg) == g]; v = v[~np.isnan(v)]
+        cnt[g] = v.size
+        if v.size:
+            mn[g] = v.min(); mx[g] = v.max()
+    return cnt, mn, mx
+
+
+def test_group_protocol_settles_segments_from_gathered_rows(eng, world1):
+    rng = np.random.default_rng(31)
+    x = np.concatenate([30 + 65 * rng.random((40, 900)),                      # gauge-like
+                        np.cumsum(rng.random((40, 900)) * 1e4, axis=1),       # counters
+                        rng.normal(size=(8, 900))])                           # both signs
+    x[rng.random(x.shape) < 0.01] = np.nan
+    seg = np.array([0] * 40 + [1] * 40 + [2] * 7 + [-1], dtype=np.int32)
+    for summary in (None, _summary(x, seg, 3)):
+        _check(eng, world1, x, seg, 3, [0.5, 0.95, 0.99], summary)
+        _check(eng, world1, x, seg, 3, [0.0, 1.0], summary)
+
+
+def test_group_protocol_falls_back_to_passes_when_rows_do_not_fit(eng, world1):
+    """More repeated values than a row (1023 keys) or the merge buffer holds: the merge reports the
+    segment as unresolved and passes 3.. run with their all-reduces."""
+    rng = np.random.default_rng(32)
+    x = np.full((64, 2048), 7.25)                          # 131 072 copies of one value ...
+    x[:, ::5] = rng.normal(size=x[:, ::5].shape) + 7       # ... among values around it
+    y = rng.normal(size=(4, 2048))
+    z = np.concatenate([x, y])
+    seg = np.array([0] * 64 + [1] * 4, dtype=np.int32)
+    for summary in (None, _summary(z, seg, 2)):
+        _check(eng, world1, z, seg, 2, [0.5, 0.9], summary)
