@@ -10,7 +10,7 @@ calls raise.
 """
 from .engine import DEFAULT_LOOKBACK_MS, DeviceTokens, Engine, Tokens, group_index, tokenize  # noqa: F401
 from .adapter import (aggregate_instant, aggregate_range, fetch_gpu_metrics,  # noqa: F401
-                      selected_averages)
+                      fetch_gpu_metrics_range, merge_range_chunks, range_traces, selected_averages)
 
 __all__ = ["Engine", "Tokens", "DeviceTokens", "tokenize", "group_index", "fetch_gpu_metrics", "aggregate_instant",
-           "aggregate_range", "selected_averages", "DEFAULT_LOOKBACK_MS"]
+           "aggregate_range", "selected_averages", "fetch_gpu_metrics_range", "merge_range_chunks", "range_traces", "DEFAULT_LOOKBACK_MS"]

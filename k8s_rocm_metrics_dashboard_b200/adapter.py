@@ -200,8 +200,15 @@ def aggregate_range(body, start_ms, step_ms, n_steps, window_ms, lookback_ms=DEF
     tok = _range_tokens(eng, body, tokenizer)
     labels = tok.labels()
     ts, val = eng.parse(tok)
+    return _aggregate_series(eng, labels, ts, val, tok.series_off, start_ms, step_ms, n_steps, window_ms,
+                             lookback_ms, quantiles, as_frame)
+
+
+def _aggregate_series(eng, labels, ts, val, series_off, start_ms, step_ms, n_steps, window_ms, lookback_ms,
+                      quantiles, as_frame):
+    """The range path behind the tokens: CSR samples (device) -> tidy frame + per-metric summary."""
     w = int(window_ms // step_ms)
-    out = eng.fused(ts, val, tok.series_off, start_ms, step_ms, n_steps, w, lookback_ms)
+    out = eng.fused(ts, val, series_off, start_ms, step_ms, n_steps, w, lookback_ms)
     names = sorted({l.get("__name__", "") for l in labels})
     gid = np.array([names.index(l.get("__name__", "")) for l in labels], dtype=np.int32)
     from .engine import group_index
@@ -228,3 +235,119 @@ def aggregate_range(body, start_ms, step_ms, n_steps, window_ms, lookback_ms=DEF
     if not as_frame:
         return tidy, summary
     return pd.DataFrame(tidy), pd.DataFrame(summary)
+
+
+# ----------------------------------------------------------------------------- range client
+PROMETHEUS_MAX_POINTS = 11_000     # Prometheus refuses query_range answers with more points per series
+
+
+def _range_endpoint():
+    ep = PROMETHEUS_METRICS_ENDPOINT
+    return ep + "_range" if ep.endswith("/query") else ep.rstrip("/") + "/query_range"
+
+
+def merge_range_chunks(eng, chunks):
+    """Concatenate the answers to consecutive sub-ranges of one query_range into one CSR.
+
+    ``chunks``: [(labels, ts, val, series_off)] in time order, ts/val device tensors.  A series is
+    identified by its label set; it may be missing from some chunks.  Returns (labels, ts, val,
+    series_off) with every series' samples in time order.  Sample order inside a series follows
+    the chunk order, so the chunks must not overlap in time."""
+    import json
+    t = eng.torch
+    index, labels = {}, []
+    for lab, _, _, _ in chunks:
+        for l in lab:
+            k = json.dumps(l, sort_keys=True, separators=(",", ":"))
+            if k not in index:
+                index[k] = len(labels)
+                labels.append(l)
+    S = len(labels)
+    total = np.zeros(S + 1, dtype=np.int64)
+    gids = []
+    for lab, _, _, off in chunks:
+        g = np.fromiter((index[json.dumps(l, sort_keys=True, separators=(",", ":"))] for l in lab), dtype=np.int64,
+                        count=len(lab))
+        gids.append(g)
+        np.add.at(total, g + 1, np.diff(np.asarray(off, dtype=np.int64)))
+    series_off = np.cumsum(total)
+    n = int(series_off[-1])
+    ts_all = eng._empty((n,), t.int64)
+    val_all = eng._empty((n,), t.float64)
+    filled = np.zeros(S, dtype=np.int64)                 # samples of each series already placed
+    for (lab, ts, val, off), g in zip(chunks, gids):
+        off = np.asarray(off, dtype=np.int64)
+        lens = np.diff(off)
+        if len(lens) == 0 or int(off[-1]) == 0:
+            continue
+        # destination of sample i of local series s: series_off[g] + filled[g] + (i - off[s])
+        shift = t.as_tensor(series_off[g] + filled[g] - off[:-1], device=eng.device)
+        dest = t.repeat_interleave(shift, t.as_tensor(lens, device=eng.device)) + t.arange(int(off[-1]), device=eng.device)
+        ts_all.index_copy_(0, dest, ts)
+        val_all.index_copy_(0, dest, val)
+        filled[g] += lens
+    return labels, ts_all, val_all, series_off
+
+
+def fetch_gpu_metrics_range(start_s, end_s, step_s, window_s, lookback_s=DEFAULT_LOOKBACK_MS // 1000,
+                            quantiles=(0.5, 0.95, 0.99), as_frame=True, session=None,
+                            max_points=PROMETHEUS_MAX_POINTS, eng: Engine | None = None, tokenizer="auto"):
+    """The range counterpart of ``fetch_gpu_metrics`` (app.py:153-227): the same host lookup and metric
+    selector, sent to ``/api/v1/query_range`` in sub-ranges of at most ``max_points`` steps (Prometheus'
+    limit per series), merged per label set and aggregated on the GPU.  Returns ``(tidy, summary)`` as
+    ``aggregate_range`` does, or ``(None, None)`` after reporting the error, like the reference.
+    ``session``: anything with ``get(url=..., params=...)`` (default: the ``requests`` module)."""
+    try:
+        import json
+        if session is None:
+            import requests as session
+        q1 = f"kube_pod_info{{pod=~\".*{PROMETHEUS_METRICS_PODNAME}.*\"}}"
+        r1 = session.get(url=PROMETHEUS_METRICS_ENDPOINT, params={"query": q1})
+        r1.raise_for_status()
+        host_ip = json.loads(r1.text)["data"]["result"][0]["metric"]["host_ip"]
+        q2 = ("{__name__=~\"amd_gpu_edge_temperature|amd_gpu_gfx_activity|amd_gpu_average_package_power|"
+              "amd_gpu_used_vram|amd_gpu_total_vram\", instance=~\"" + host_ip + ":.+\"}")
+        eng = eng or engine()
+        n_steps = int((end_s - start_s) // step_s) + 1
+        chunks = []
+        for k0 in range(0, n_steps, max_points):
+            k1 = min(k0 + max_points, n_steps) - 1
+            r = session.get(url=_range_endpoint(), params={"query": q2, "start": start_s + k0 * step_s,
+                                                            "end": start_s + k1 * step_s, "step": step_s})
+            r.raise_for_status()
+            body = r.content if hasattr(r, "content") else r.text
+            tok = _range_tokens(eng, body, tokenizer)
+            if tok.result_type != "matrix":
+                raise ValueError("query_range must answer with resultType matrix")
+            ts, val = eng.parse(tok) if tok.n_samples else (eng._empty((0,), eng.torch.int64), eng._empty((0,), eng.torch.float64))
+            chunks.append((tok.labels(), ts, val, tok.series_off))
+        labels, ts, val, off = merge_range_chunks(eng, chunks) if len(chunks) != 1 else chunks[0]
+        return _aggregate_series(eng, labels, ts, val, off, int(round(start_s * 1000)), int(round(step_s * 1000)), n_steps,
+                                 int(round(window_s * 1000)), int(round(lookback_s * 1000)), quantiles, as_frame)
+    except Exception as e:  # noqa: BLE001  -- the reference swallows everything (app.py:225-227)
+        _report(f"Error fetching GPU metrics: {str(e)}")
+        return None, None
+
+
+def range_traces(tidy, column="value", metric=None):
+    """Plotly-style line traces from a tidy frame (pandas DataFrame, dict of arrays or pyarrow Table):
+    one ``{"type": "scatter", "mode": "lines", "name", "x", "y"}`` per (instance, gpu_id, metric),
+    sliced from the frame's arrays (rows of one series are contiguous); ``create_visualization``
+    (app.py:234-245) stays as it is and these traces feed ``go.Figure(data=...)``."""
+    if hasattr(tidy, "to_pandas"):
+        tidy = tidy.to_pandas()
+    cols = {k: np.asarray(tidy[k]) for k in ("instance", "gpu_id", "metric_name", "ts", column)}
+    n = len(cols["ts"])
+    if n == 0:
+        return []
+    key = np.char.add(np.char.add(cols["instance"].astype(str), "/gpu"), cols["gpu_id"].astype(str))
+    full = np.char.add(np.char.add(key, " "), cols["metric_name"].astype(str))
+    cut = np.flatnonzero(full[1:] != full[:-1]) + 1
+    starts = np.concatenate([[0], cut]); ends = np.concatenate([cut, [n]])
+    traces = []
+    for a, b in zip(starts, ends):
+        if metric is not None and cols["metric_name"][a] != metric:
+            continue
+        traces.append({"type": "scatter", "mode": "lines", "name": str(full[a]),
+                       "x": cols["ts"][a:b], "y": cols[column][a:b]})
+    return traces
