@@ -70,7 +70,7 @@ def main():
     rec("K3 rolling min/max/mean", N, 32, timeit(lambda: eng.rolling(al, W, want_count=False)))
     rec("K3 rolling + count", N, 36, timeit(lambda: eng.rolling(al, W)))
     rec("K4 rate+increase", N, 24, timeit(lambda: eng.rate(al, W, synth.STEP_MS, want_resets=False)))
-    rec("K4 rate+increase+n_resets (general)", N, 28, timeit(lambda: eng.rate(al, W, synth.STEP_MS)))
+    rec("K4 rate+increase+n_resets", N, 28, timeit(lambda: eng.rate(al, W, synth.STEP_MS)))
     gid = (np.arange(S) % 12).astype(np.int32)
     pg = group_index(gid, 12)
     pg = (torch.as_tensor(pg[0], device=dev), torch.as_tensor(pg[1], device=dev))

@@ -19,9 +19,9 @@
 //   * the align stage starts from "one sample per step" as its guess and only binary-searches the
 //     staged timestamps when the guess is wrong; indices are 32-bit, shared memory is addressed
 //     directly (no generic pointers).
-// Requests it does not cover (window_steps < 9 or > NE/2 with window outputs, n_resets, source
-// indices together with window outputs, output rows not 32-byte aligned) go to the general kernel
-// in window.cu.
+// Requests it does not cover (window_steps < 9 or > NE/2 with window outputs, n_resets on sample
+// input, extrapolated rates, source indices together with window outputs, output rows not 32-byte
+// aligned) go to the general kernel in window.cu.
 //
 // Shared memory per CTA (NT threads, NE = 8 NT points): four suffix arrays S_*[NE] (aliased with
 // the sample staging area and the aligned-value hand-off), chunk totals T_*[NT], the two tables.
@@ -216,7 +216,10 @@ __device__ __noinline__ int64_t align_general_tile(const int64_t* __restrict__ g
 // QB = (window_steps - 1) & 7 as a compile-time constant (the output loops then unroll with every
 // "far / near" choice and every shared-memory row offset folded), or -1 for any window.
 // IDX: also write the source index of every aligned point (pmx_align; no window outputs then).
-template <int NT, bool ALIGN, int QB, bool IDX = false>
+// NRES: also count the counter resets of every window (pmx_rate's n_resets): wherever a delta is
+// formed, "current < previous" is counted beside it -- in-chunk counts ride in spare bits of the
+// meta words (S_meta 11..13, T_meta 16..18), the folds keep integer twins of their sums.
+template <int NT, bool ALIGN, int QB, bool IDX = false, bool NRES = false>
 __global__ void __launch_bounds__(NT, (NT == 256 ? 2 : PMX_FAST_CTAS_128))
 window_fast_kernel(const WinParams p) {
   using TL = FTile<NT>;
@@ -253,7 +256,7 @@ window_fast_kernel(const WinParams p) {
   const int HP = H + (int)(((s * p.n_steps + c0 - H) % 4 + 4) % 4);
   const int OUT = (NE - HP) & ~3;                                 // >= the host's (NE - H - 3) & ~3: a full tile uses all NE points
   const bool do_roll = p.o_min || p.o_max || p.o_mean || p.o_cnt;
-  const bool do_rate = p.o_inc || p.o_rate;
+  const bool do_rate = p.o_inc || p.o_rate || (NRES && p.o_nres);
   const double INF = __longlong_as_double(0x7FF0000000000000LL);
   const int need = p.min_periods > 1 ? p.min_periods : 1;
 
@@ -427,6 +430,7 @@ window_fast_kernel(const WinParams p) {
     int c_cn = E;
     {
       double ss = a[E - 1], smn = a[E - 1], smx = a[E - 1], sd = 0.0;
+      int snr = 0;                                                // resets inside the suffix (NRES)
       {
         const int si = (E - 1) * NT + t;
         S_sum[si] = ss; S_mn[si] = smn; S_mx[si] = smx; S_d[si] = sd;
@@ -437,14 +441,15 @@ window_fast_kernel(const WinParams p) {
         const double v = a[r];
         ss += v; smn = dmin(smn, v); smx = dmax(smx, v);
         sd += delta_of(a[r + 1], v);
+        if (NRES) snr += a[r + 1] < v ? 1 : 0;
         const int si = r * NT + t;
         S_sum[si] = ss; S_mn[si] = smn; S_mx[si] = smx; S_d[si] = sd;
-        S_meta[si] = (uint16_t)((E - r) | ((E - r) << 4));
+        S_meta[si] = (uint16_t)((E - r) | ((E - r) << 4) | (NRES ? snr << 11 : 0));
       }
       T_sum[t] = ss; T_mn[t] = smn; T_mx[t] = smx; T_fv[t] = a[0]; T_lv[t] = a[E - 1]; T_di[t] = sd;
-      T_meta[t] = (uint32_t)(E | (E << 4) | ((E - 1) << 12));
+      T_meta[t] = (uint32_t)(E | (E << 4) | ((E - 1) << 12) | (NRES ? snr << 16 : 0));
       if (!pmx_isfinite(ss)) {
-        ss = 0.0; smn = INF; smx = -INF; sd = 0.0;
+        ss = 0.0; smn = INF; smx = -INF; sd = 0.0; snr = 0;
         double sfv = 0.0, lv = 0.0;
         int scf = 0, scn = 0, foff = 0, lpos = 0;
 #pragma unroll
@@ -452,15 +457,15 @@ window_fast_kernel(const WinParams p) {
           const double v = a[r];
           if (pmx_isfinite(v)) { ss += v; smn = dmin(smn, v); smx = dmax(smx, v); ++scf; }
           if (v == v) {
-            if (scn > 0) sd += delta_of(sfv, v); else { lv = v; lpos = r; }
+            if (scn > 0) { sd += delta_of(sfv, v); if (NRES) snr += sfv < v ? 1 : 0; } else { lv = v; lpos = r; }
             sfv = v; foff = r; ++scn;
           }
           const int si = r * NT + t;
           S_sum[si] = ss; S_mn[si] = smn; S_mx[si] = smx; S_d[si] = sd;
-          S_meta[si] = (uint16_t)(scf | (scn << 4) | (((foff - r) & 7) << 8));
+          S_meta[si] = (uint16_t)(scf | (scn << 4) | (((foff - r) & 7) << 8) | (NRES ? snr << 11 : 0));
         }
         T_sum[t] = ss; T_mn[t] = smn; T_mx[t] = smx; T_fv[t] = sfv; T_lv[t] = lv; T_di[t] = sd;
-        T_meta[t] = (uint32_t)(scf | (scn << 4) | (foff << 8) | (lpos << 12));
+        T_meta[t] = (uint32_t)(scf | (scn << 4) | (foff << 8) | (lpos << 12) | (NRES ? snr << 16 : 0));
         c_fv = sfv; c_cn = scn;
       }
     }
@@ -538,6 +543,7 @@ window_fast_kernel(const WinParams p) {
       // first non-empty one) -- what a window needs whose first chunk part holds no sample
       double mdB = 0.0; int bfpos = -1;
       double accF = 0.0; int fposF = -1;                          // ... and the same for "far" windows
+      int mr = 0, mr2 = 0, mrB = 0, mrF = 0;                       // NRES: reset counts beside md, md2, mdB, accF
       double clv = 0.0; int clpos = -1;                            // last valid value / position before the own chunk
       if (t - qa - 1 >= 0) {
         const uint32_t m = T_meta[t - qa - 1];
@@ -549,6 +555,7 @@ window_fast_kernel(const WinParams p) {
         if ((m >> 4) & 0xf) {
           accF = T_di[k];
           md2 = accF + (clpos >= 0 ? delta_of(T_fv[k], clv) : 0.0);
+          if (NRES) { mrF = (int)((m >> 16) & 7); mr2 = mrF + ((clpos >= 0 && T_fv[k] < clv) ? 1 : 0); }
           fposF = k * E + (int)((m >> 8) & 7);
           clv = T_lv[k]; clpos = k * E + (int)((m >> 12) & 7);
         }
@@ -560,27 +567,38 @@ window_fast_kernel(const WinParams p) {
           const double j = clpos >= 0 ? delta_of(T_fv[k], clv) : 0.0;
           md += di + j;
           mdB += di + (bfpos >= 0 ? j : 0.0);
+          if (NRES) {
+            const int nr = (int)((m >> 16) & 7), jr = (clpos >= 0 && T_fv[k] < clv) ? 1 : 0;
+            mr += nr + jr;
+            mrB += nr + (bfpos >= 0 ? jr : 0);
+          }
           if (bfpos < 0) bfpos = k * E + (int)((m >> 8) & 7);
           clv = T_lv[k]; clpos = k * E + (int)((m >> 12) & 7);
         }
       }
       md2 += md;
+      if (NRES) { mr2 += mr; if (fposF >= 0) mrF += mr; else mrF = mrB; }
       if (fposF >= 0) accF += md; else { accF = mdB; fposF = bfpos; }
       const double Jc = (c_cn > 0 && clpos >= 0) ? delta_of(c_fv, clv) : 0.0;     // own chunk's junction delta
+      const int Jr = (NRES && c_cn > 0 && clpos >= 0 && c_fv < clv) ? 1 : 0;       // ... and whether it is a reset
       double pd = 0.0, pj = 0.0, plv = 0.0;                       // own prefix without / with its junction delta
       int pcn = 0, plpos = 0, pfpos = 0;
+      int pr = 0, pjr = 0;                                        // NRES: resets in the own prefix without / with the junction
       const int lcF = t - qa - 1 > 0 ? t - qa - 1 : 0, lcN = t - qa > 0 ? t - qa : 0;
 #pragma unroll(QB >= 0 ? 2 : 1)
       for (int h = 0; h < 2; ++h) {
         double oinc[4], orate[4];
+        int onres[NRES ? 4 : 1];
         unsigned bad = 0;                                         // outputs with fewer than two samples
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const int r = 4 * h + q;
           const double v = QB >= 0 ? a[r] : (h ? a[4 + q] : a[q]);
           if (v == v) {
-            if (pcn > 0) { const double d = delta_of(v, plv); pd += d; pj += d; }
-            else { pfpos = e0 + r; pj = Jc; }
+            if (pcn > 0) {
+              const double d = delta_of(v, plv); pd += d; pj += d;
+              if (NRES) { const int dr = v < plv ? 1 : 0; pr += dr; pjr += dr; }
+            } else { pfpos = e0 + r; pj = Jc; if (NRES) pjr = Jr; }
             plv = v; plpos = e0 + r; ++pcn;
           }
           const bool far = r < qb;
@@ -589,16 +607,19 @@ window_fast_kernel(const WinParams p) {
           const int cfp = far ? fposF : bfpos;
           const uint32_t sm = S_meta[si];
           int fpos; double inc;
+          int nres = 0;
           if ((sm >> 4) & 0xf) {                                  // first chunk part holds a sample
             fpos = e0 + r - H + (int)((sm >> 8) & 7);             // window start + offset of its first sample
             inc = S_d[si] + cmd + pj;
+            if (NRES) nres = (int)((sm >> 11) & 7) + (far ? mr2 : mr) + pjr;
           } else {                                                // rare: NaN run or series start
             fpos = cfp;
-            if (fpos >= 0) inc = cacc + pj;
-            else { fpos = pcn > 0 ? pfpos : 0x7fffffff; inc = pd; }     // window inside the own chunk
+            if (fpos >= 0) { inc = cacc + pj; if (NRES) nres = (far ? mrF : mrB) + pjr; }
+            else { fpos = pcn > 0 ? pfpos : 0x7fffffff; inc = pd; if (NRES) nres = pr; }   // window inside the own chunk
           }
           const int lpos = pcn > 0 ? plpos : clpos;
           const int span = lpos - fpos;
+          if (NRES) onres[q] = span > 0 ? nres : 0;
           oinc[q] = inc;
           orate[q] = inc * rdt[span > 0 ? span : 0];
           bad |= (span > 0 ? 0u : 1u) << q;
@@ -613,9 +634,11 @@ window_fast_kernel(const WinParams p) {
           const int64_t o = row + e;
           if (p.o_inc) st4(p.o_inc + o, oinc[0], oinc[1], oinc[2], oinc[3]);
           if (p.o_rate) st4(p.o_rate + o, orate[0], orate[1], orate[2], orate[3]);
+          if (NRES && p.o_nres) *reinterpret_cast<int4*>(p.o_nres + o) = make_int4(onres[0], onres[1], onres[2], onres[3]);
         } else if (e + 3 >= HP && e < n_el) {
           if (p.o_inc) store4_edge(p.o_inc + row, e, HP, n_el, oinc[0], oinc[1], oinc[2], oinc[3]);
           if (p.o_rate) store4_edge(p.o_rate + row, e, HP, n_el, orate[0], orate[1], orate[2], orate[3]);
+          if (NRES) store4i(p.o_nres ? p.o_nres + row : nullptr, e, HP, n_el, onres[0], onres[1], onres[2], onres[3]);
         }
       }
     }
@@ -627,7 +650,7 @@ window_fast_kernel(const WinParams p) {
 
 bool aligned32(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 31) == 0; }
 
-template <int NT, bool ALIGN, int QB, bool IDX = false>
+template <int NT, bool ALIGN, int QB, bool IDX = false, bool NRES = false>
 int launch_fast(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
   using TL = FTile<NT>;
   const int out_per_tile = (TL::NE - (p.w - 1) - 3) & ~3;
@@ -644,8 +667,8 @@ int launch_fast(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
   const int64_t grid = p.n_series * p.chunks;
   if (grid > 0x7fffffffLL) return pmx_fail(PMX_E_LIMIT, "window kernel: n_series * chunks exceeds 2^31-1");
   const size_t smem = TL::FIXED + size_t(2) * (p.w + 1) * 8 + 16;
-  PMX_CUDA(cudaFuncSetAttribute(window_fast_kernel<NT, ALIGN, QB, IDX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  window_fast_kernel<NT, ALIGN, QB, IDX><<<(unsigned)grid, NT, smem, st>>>(p);
+  PMX_CUDA(cudaFuncSetAttribute(window_fast_kernel<NT, ALIGN, QB, IDX, NRES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  window_fast_kernel<NT, ALIGN, QB, IDX, NRES><<<(unsigned)grid, NT, smem, st>>>(p);
   PMX_LAUNCH_CHECK();
   return PMX_OK;
 }
@@ -658,7 +681,9 @@ int launch_window_fast(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
   const int H = p.w - 1;
   const bool windows = p.o_min || p.o_max || p.o_mean || p.o_cnt || p.o_inc || p.o_rate;
   if ((windows && H < 8) || H > nt * E / 2 - 4) return 1;        // plain alignment takes any window
-  if (p.o_nres || p.rate_mode != 0) return 1;
+  if (p.rate_mode != 0) return 1;
+  // reset counts: instantiated for dense input (pmx_rate) only
+  if (p.o_nres && (ALIGN || nt != 128 || (reinterpret_cast<uintptr_t>(p.o_nres) & 15))) return 1;
   if (p.o_idx && (windows || !ALIGN || nt != 128 || (reinterpret_cast<uintptr_t>(p.o_idx) & 15))) return 1;
   // tile-relative timestamps are 32-bit: a tile (plus the lookback) must span < 2^30 ms
   if (p.step_ms > 0x3fffffffLL / (nt * E + 8) || p.lookback_ms >= 0x3fffffffLL) return 1;
@@ -667,6 +692,20 @@ int launch_window_fast(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
     return 1;
   if constexpr (ALIGN) {
     if (p.o_idx) return launch_fast<128, true, 0, true>(ctx, p, st);   // pmx_align with source indices
+  }
+  if constexpr (!ALIGN) {
+    if (p.o_nres) {
+      switch (H & 7) {
+        case 0: return launch_fast<128, false, 0, false, true>(ctx, p, st);
+        case 1: return launch_fast<128, false, 1, false, true>(ctx, p, st);
+        case 2: return launch_fast<128, false, 2, false, true>(ctx, p, st);
+        case 3: return launch_fast<128, false, 3, false, true>(ctx, p, st);
+        case 4: return launch_fast<128, false, 4, false, true>(ctx, p, st);
+        case 5: return launch_fast<128, false, 5, false, true>(ctx, p, st);
+        case 6: return launch_fast<128, false, 6, false, true>(ctx, p, st);
+        default: return launch_fast<128, false, 7, false, true>(ctx, p, st);
+      }
+    }
   }
   if (nt == 128) {
     switch (H & 7) {                                              // one kernel per window phase

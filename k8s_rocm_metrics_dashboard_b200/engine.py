@@ -293,7 +293,7 @@ class Engine:
     # ------------------------------------------------------------------ K4
     def rate(self, x, window_steps, step_ms, mode=0, want_resets=True):
         """Increase / rate (and the number of counter resets) per trailing window of a dense
-        matrix.  ``want_resets=False`` skips n_resets, which only the general kernel produces."""
+        matrix.  ``want_resets=False`` skips the n_resets output (4 bytes per point less to write)."""
         t = self.torch
         x = self._dev(x, t.float64)
         S, T = x.shape
