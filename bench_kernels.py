@@ -79,6 +79,21 @@ def main():
     seg = torch.as_tensor(gid, device=dev)
     rec("K6 quantiles p50/p95/p99 x12", N, 24, timeit(lambda: eng.quantiles(al, seg, 12, [0.5, 0.95, 0.99], row_order=pg[0])),
         "3 full passes + candidate lists")
+    # one refresh of the series cache (one new grid point per series) against the full pass
+    from k8s_rocm_metrics_dashboard_b200.cache import SeriesCache
+    labs = synth.series_labels(64, 8, 12)
+    keep = 200
+    cache = SeriesCache(eng, synth.START_MS, synth.STEP_MS, W, capacity=256, max_series=S)
+    cache.append(labs, ts.view(S, T)[:, T - keep:].reshape(-1).contiguous(), val.view(S, T)[:, T - keep:].reshape(-1).contiguous(),
+                 np.arange(S + 1, dtype=np.int64) * keep)
+    upto = synth.START_MS + (T - 1) * synth.STEP_MS + synth.STEP_MS - 1
+
+    def one_refresh():
+        cache.next_step = T - 1
+        cache.refresh(upto)
+    sec = timeit(one_refresh)
+    rec("series cache: refresh of 1 new step", S, 56 * (W + 20), sec, f"{S} series, window {W}; the full-range fused pass above does the same in {rows[0]['ms']:.3f} ms")
+    del cache
     # config 4: all counters with resets
     ts4, val4, off4 = synth.dense_device(S, T, 12, seed=2, all_counters=True, reset_prob=1e-3, nan_frac=0.0, device=dev)
     rec("fused (cfg4 counters + resets)", N, 56, timeit(lambda: eng.fused(ts4, val4, off4, synth.START_MS, synth.STEP_MS, T, W, out=out)))

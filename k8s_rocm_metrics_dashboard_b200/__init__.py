@@ -9,8 +9,9 @@ Numeric work runs in ``libpmx.so`` (hand-written sm_100a CUDA behind the C ABI i
 calls raise.
 """
 from .engine import DEFAULT_LOOKBACK_MS, DeviceTokens, Engine, Tokens, group_index, tokenize  # noqa: F401
+from .cache import SeriesCache  # noqa: F401
 from .adapter import (aggregate_instant, aggregate_range, fetch_gpu_metrics,  # noqa: F401
                       fetch_gpu_metrics_range, merge_range_chunks, range_traces, selected_averages)
 
 __all__ = ["Engine", "Tokens", "DeviceTokens", "tokenize", "group_index", "fetch_gpu_metrics", "aggregate_instant",
-           "aggregate_range", "selected_averages", "fetch_gpu_metrics_range", "merge_range_chunks", "range_traces", "DEFAULT_LOOKBACK_MS"]
+           "aggregate_range", "selected_averages", "fetch_gpu_metrics_range", "merge_range_chunks", "range_traces", "SeriesCache", "DEFAULT_LOOKBACK_MS"]
