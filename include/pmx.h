@@ -201,6 +201,18 @@ int pmx_ratio_pct(pmx_ctx* ctx, const double* d_num, int64_t num_stride, const d
 int pmx_where_gt(pmx_ctx* ctx, const double* d_x, int64_t n, double threshold, double* d_out,
                  pmx_stream stream);
 
+/* ---- Series cache (no counterpart in the reference, which re-processes the
+ * whole range on every refresh, app.py:24/:486).  Samples of series s live ascending in row s of a
+ * [n_series][cap] slab, d_count[s] of them held.  pmx_slab_tail_lengths: d_first[s] = number of held
+ * samples with ts <= threshold_ms, d_len[s] = the rest.  With d_off = exclusive cumulative sum of
+ * d_len (n_series + 1 entries, made by the caller), pmx_slab_tail_gather copies every series' tail
+ * to d_out_*[d_off[s] ..): a CSR that pmx_fused_align_rolling_rate takes as it is. */
+int pmx_slab_tail_lengths(pmx_ctx* ctx, const int64_t* d_ts, const int64_t* d_count, int64_t n_series, int64_t cap,
+                          int64_t threshold_ms, int64_t* d_first, int64_t* d_len, pmx_stream stream);
+int pmx_slab_tail_gather(pmx_ctx* ctx, const int64_t* d_ts, const double* d_val, const int64_t* d_first,
+                         const int64_t* d_off, int64_t n_series, int64_t cap, int64_t* d_out_ts, double* d_out_val,
+                         pmx_stream stream);
+
 /* ---- X7  exact quantiles (K6) by radix select over order-preserving 64-bit keys.
  * Values of series s belong to segment d_seg[s] (or none if < 0).  State per segment:
  *   d_state: opaque uint64 [n_seg * (3 + 4*n_q)] owned by the caller, zeroed before pass 0 or

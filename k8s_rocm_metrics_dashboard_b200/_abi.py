@@ -63,6 +63,8 @@ SIGNATURES = {
     "pmx_pivot_gather": (_int, [_p, _p, _p, _i64, _p, _p]),
     "pmx_ratio_pct": (_int, [_p, _p, _i64, _p, _i64, _i64, _p, _i64, _p, _p]),
     "pmx_where_gt": (_int, [_p, _p, _i64, C.c_double, _p, _p]),
+    "pmx_slab_tail_lengths": (_int, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p]),
+    "pmx_slab_tail_gather": (_int, [_p, _p, _p, _p, _p, _i64, _i64, _p, _p, _p]),
     "pmx_quantile_hist": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _i64, _i64, _int, _p, _p, _p]),
     "pmx_quantile_init": (_int, [_p, _p, _p, _p, _i64, _p, _i64, _p, _p]),
     "pmx_quantile_tail": (_int, [_p, _i64, _i64, _int, _p, _p]),

@@ -9,8 +9,8 @@ have become due plus the ``window_steps - 1`` points before them (their windows 
 far), on a compact CSR gathered from the tails of the slabs.  Work per refresh is proportional to
 series x (window + new points) instead of series x range.
 
-Memory moves (slab append, tail gather) are torch index operations; decode, alignment, windows and
-rates are libpmx.so kernels, as everywhere else.
+The slab append is a handful of torch index operations; the tail gather, decode, alignment, windows
+and rates are libpmx.so kernels.
 """
 from __future__ import annotations
 
@@ -142,16 +142,23 @@ class SeriesCache:
         n = j_end - a + 1
         g0 = self.start_ms + a * self.step_ms
         S = self._rows
-        ts, val, cnt = self.ts[:S], self.val[:S], self.cnt[:S]
-        pos = t.arange(self.cap, device=dev)[None, :]
-        held = pos < cnt[:, None]
-        # a sample can serve a grid point >= g0 only if it is newer than g0 - lookback
-        first = (held & (ts <= g0 - self.lookback_ms)).sum(dim=1)
-        lens = cnt - first
+        # a sample can serve a grid point >= g0 only if it is newer than g0 - lookback: the tails of
+        # the slab rows from there on, gathered into one CSR (two kernels and a cumulative sum; the
+        # compact buffers are sized for full rows, so no count has to come back to the host)
+        from . import _abi
+        p = eng._ptr
+        first, lens = eng._empty((S,), t.int64), eng._empty((S,), t.int64)
+        _abi.check(eng.lib.pmx_slab_tail_lengths(eng.ctx, p(self.ts), p(self.cnt), S, self.cap, g0 - self.lookback_ms,
+                                                 p(first), p(lens), eng._stream()))
         off = t.zeros((S + 1,), dtype=t.int64, device=dev)
-        off[1:] = t.cumsum(lens, 0)
-        take = held & (pos >= first[:, None])
-        ts_c, val_c = ts[take], val[take]                           # row-major: series after series, ascending
+        t.cumsum(lens, 0, out=off[1:])
+        if getattr(self, "_compact_rows", 0) < S:
+            self._ts_c, self._val_c = eng._empty((S * self.cap,), t.int64), eng._empty((S * self.cap,), t.float64)
+            self._compact_rows = S
+        ts_c, val_c = self._ts_c, self._val_c
+        _abi.check(eng.lib.pmx_slab_tail_gather(eng.ctx, p(self.ts), p(self.val), p(first), p(off), S, self.cap,
+                                                p(ts_c), p(val_c), eng._stream()))
+        eng.launches += 2
         out = eng.fused(ts_c, val_c, off, g0, self.step_ms, n, self.w, self.lookback_ms)
         res = {key: v[:, n - k:] for key, v in out.items()}
         res["first_step"] = self.next_step
