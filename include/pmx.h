@@ -241,12 +241,12 @@ int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
  * d_min / d_max of an empty segment are ignored. */
 int pmx_quantile_init(pmx_ctx* ctx, const int64_t* d_count, const double* d_min, const double* d_max,
                       int64_t n_seg, const double* d_q, int64_t n_q, uint64_t* d_state, pmx_stream stream);
-/* Single GPU only (the candidate lists of pass 2 are local): finish every segment whose list is
- * complete in one launch -- all passes from_pass..PMX_QUANTILE_PASSES for that segment, from its list
- * alone.  Call it after pass 2's pick with from_pass = 3, then issue the remaining passes as usual:
- * they return at once for finished segments and serve the ones whose list overflowed (heavy ties). */
-int pmx_quantile_tail(pmx_ctx* ctx, int64_t n_seg, int64_t n_q, int from_pass, uint64_t* d_state,
-                      pmx_stream stream);
+/* Single GPU only (the candidate lists of pass 2 are local): finish every segment in one launch --
+ * all passes from_pass..PMX_QUANTILE_PASSES, one CTA per segment, from the segment's candidate list;
+ * a segment whose list overflowed (very many repeated values) is finished by its CTA from d_x
+ * itself, slowly.  Call it after pass 2's pick with from_pass = 3; no further pass is needed. */
+int pmx_quantile_tail(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps, const int32_t* d_seg,
+                      int64_t n_seg, int64_t n_q, int from_pass, uint64_t* d_state, pmx_stream stream);
 /* The same for several GPUs, after pass 2's pick: every rank writes the keys of its lists that match
  * a target as it stands now (d_rows: uint64 [n_seg * PMX_QUANTILE_GATHER_ROW], row = count, keys),
  * the rows are all-gathered ([n_ranks][n_seg][ROW], rank-major), and pmx_quantile_tail_merge settles

@@ -67,7 +67,7 @@ SIGNATURES = {
     "pmx_slab_tail_gather": (_int, [_p, _p, _p, _p, _p, _i64, _i64, _p, _p, _p]),
     "pmx_quantile_hist": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _i64, _i64, _int, _p, _p, _p]),
     "pmx_quantile_init": (_int, [_p, _p, _p, _p, _i64, _p, _i64, _p, _p]),
-    "pmx_quantile_tail": (_int, [_p, _i64, _i64, _int, _p, _p]),
+    "pmx_quantile_tail": (_int, [_p, _p, _i64, _i64, _p, _i64, _i64, _int, _p, _p]),
     "pmx_quantile_tail_filter": (_int, [_p, _i64, _i64, _int, _p, _p, _p]),
     "pmx_quantile_tail_merge": (_int, [_p, _p, _int, _i64, _i64, _int, _p, _p, _p]),
     "pmx_quantile_pick": (_int, [_p, _p, _i64, _p, _i64, _int, _p, _p]),

@@ -349,7 +349,8 @@ template <bool GATHERED>
 __global__ void __launch_bounds__(256)
 tail_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __restrict__ cand_cnt,
             unsigned cap, int n_t, int from_pass, uint64_t* __restrict__ state, int sw,
-            const unsigned long long* __restrict__ rows, int n_ranks, unsigned int* __restrict__ unresolved) {
+            const unsigned long long* __restrict__ rows, int n_ranks, unsigned int* __restrict__ unresolved,
+            const double* __restrict__ x, int64_t n_series, int64_t n_steps, const int32_t* __restrict__ seg) {
   extern __shared__ unsigned long long skeys[];            // TAIL_KEYS keys that still match a target
   __shared__ unsigned int sh[BINS];
   __shared__ uint64_t s_old[MAX_TARGETS], s_pf[MAX_TARGETS], s_k[MAX_TARGETS], s_nk[MAX_TARGETS];
@@ -358,7 +359,11 @@ tail_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __r
   const int sg = blockIdx.x;
   uint64_t* st = state + (size_t)sg * sw;
   const unsigned n_list = GATHERED ? 0u : cand_cnt[sg];
-  if (st[0] == 0 || n_list > cap) return;                   // empty segment / overflowed list
+  if (st[0] == 0) return;                                   // empty segment
+  // One GPU: a segment whose list overflowed (or whose surviving keys do not fit shared memory:
+  // many repeated values) is finished from the data itself, by this one CTA -- slow, rare, and it
+  // spares every selection the per-pass kernels.
+  bool from_data = !GATHERED && n_list > cap;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (threadIdx.x < n_t) {
     s_pf[threadIdx.x] = st[ST_PF(threadIdx.x)];
@@ -384,7 +389,7 @@ tail_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __r
       off += c;
     }
     if (threadIdx.x == 0) s_cnt = total;
-  } else {
+  } else if (!from_data) {
     const Geom g0 = seg_geom(st, from_pass);
     const unsigned long long* glist = cand + (size_t)sg * cap;
     for (unsigned i0 = 0; i0 < n_list; i0 += blockDim.x * 8) {
@@ -408,9 +413,12 @@ tail_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __r
   }
   __syncthreads();
   const unsigned n = s_cnt;
-  if (n > TAIL_KEYS) return;                                // many repeated values: the per-pass kernels take it
+  if (n > TAIL_KEYS) {
+    if (GATHERED) return;                                   // (not reached: the merge checked the counts)
+    from_data = true;
+  }
   const unsigned long long* keys = skeys;
-  if (n <= 512) {
+  if (!from_data && n <= 512) {
     // A short list is settled directly: among the keys that carry the same prefix, key i has
     // r keys below it and e equal to it, and it is target t's order statistic iff r <= k_t < r + e.
     const Geom g0 = seg_geom(st, from_pass);
@@ -448,11 +456,24 @@ tail_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __r
       __syncthreads();
       const uint64_t want = s_old[tg];
       int spread = 0;
-      for (unsigned i0 = 0; i0 < n; i0 += blockDim.x) {
-        const unsigned i = i0 + threadIdx.x;
-        const bool in = i < n;
-        const uint64_t key = in ? keys[i] : 0;
-        hist_add(sh, in && (key >> gm.pshift) == want, (unsigned)(key >> gm.shift) & mask, lane, spread);
+      if (!from_data) {
+        for (unsigned i0 = 0; i0 < n; i0 += blockDim.x) {
+          const unsigned i = i0 + threadIdx.x;
+          const bool in = i < n;
+          const uint64_t key = in ? keys[i] : 0;
+          hist_add(sh, in && (key >> gm.pshift) == want, (unsigned)(key >> gm.shift) & mask, lane, spread);
+        }
+      } else {
+        for (int64_t r = 0; r < n_series; ++r) {
+          if (seg[r] != sg) continue;                       // uniform
+          const double* xr = x + r * n_steps;
+          for (int64_t j0 = 0; j0 < n_steps; j0 += blockDim.x) {
+            const int64_t j = j0 + threadIdx.x;
+            const double v = j < n_steps ? xr[j] : pmx_nan();
+            const uint64_t key = f64_key(v) - gm.base;
+            hist_add(sh, v == v && (key >> gm.pshift) == want, (unsigned)(key >> gm.shift) & mask, lane, spread);
+          }
+        }
       }
       __syncthreads();
       unsigned int loc[PER]; unsigned int sum = 0;
@@ -763,19 +784,21 @@ int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
   return PMX_OK;
 }
 
-int pmx_quantile_tail(pmx_ctx* ctx, int64_t n_seg, int64_t n_q, int from_pass, uint64_t* d_state, pmx_stream stream) {
+int pmx_quantile_tail(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps, const int32_t* d_seg,
+                      int64_t n_seg, int64_t n_q, int from_pass, uint64_t* d_state, pmx_stream stream) {
   PMX_REQUIRE(ctx, "ctx is NULL");
   PMX_REQUIRE(n_seg >= 0 && n_seg <= 65535, "n_seg must be in [0, 65535]");
   PMX_REQUIRE(n_q >= 1 && 2 * n_q <= MAX_TARGETS, "n_q must be in [1, 8]");
   PMX_REQUIRE(from_pass >= 3 && from_pass <= PMX_QUANTILE_PASSES, "from_pass must follow pass 2 (which builds the candidate lists)");
   if (n_seg == 0) return PMX_OK;
-  PMX_REQUIRE(d_state, "NULL buffer");
+  PMX_REQUIRE(d_state && d_x && d_seg && n_series > 0 && n_steps > 0, "NULL buffer or empty data");
   unsigned cap; unsigned int* cand_cnt; unsigned long long* cand;
   if (int rc = cand_layout(ctx, n_seg, &cap, &cand_cnt, &cand, nullptr)) return rc;
   const size_t smem = (size_t)TAIL_KEYS * sizeof(unsigned long long);
   PMX_CUDA(cudaFuncSetAttribute(tail_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   tail_kernel<false><<<(unsigned)n_seg, 256, smem, pmx_st(stream)>>>(cand, cand_cnt, cap, 2 * (int)n_q, from_pass, d_state,
-                                                                   state_words(n_q), nullptr, 1, nullptr);
+                                                                   state_words(n_q), nullptr, 1, nullptr, d_x, n_series,
+                                                                   n_steps, d_seg);
   PMX_LAUNCH_CHECK();
   return PMX_OK;
 }
@@ -812,7 +835,7 @@ int pmx_quantile_tail_merge(pmx_ctx* ctx, const uint64_t* d_rows_all, int n_rank
   PMX_CUDA(cudaFuncSetAttribute(tail_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   tail_kernel<true><<<(unsigned)n_seg, 256, smem, st>>>(nullptr, nullptr, 0xffffffffu, 2 * (int)n_q, from_pass, d_state,
                                                       state_words(n_q), (const unsigned long long*)d_rows_all, n_ranks,
-                                                      (unsigned int*)d_unresolved);
+                                                      (unsigned int*)d_unresolved, nullptr, 0, 0, nullptr);
   PMX_LAUNCH_CHECK();
   return PMX_OK;
 }
@@ -875,15 +898,17 @@ int pmx_quantile_select(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64
   uint64_t* state = (uint64_t*)scr;
   uint64_t* hist = (uint64_t*)(scr + state_bytes);
   PMX_CUDA(cudaMemsetAsync(state, 0, state_bytes, pmx_st(stream)));
-  for (int pass = 0; pass < PMX_QUANTILE_PASSES; ++pass) {
-    if (pass == 3 && n_series > 0 && n_steps > 0) {         // the lists of pass 2 settle most segments at once
-      const int rc = pmx_quantile_tail(ctx, n_seg, n_q, 3, state, stream);
-      if (rc) return rc;
-    }
+  // passes 0..2 over the data; the candidate lists of pass 2 then settle every segment in one launch
+  const bool data = n_series > 0 && n_steps > 0;
+  for (int pass = 0; pass < (data ? 3 : PMX_QUANTILE_PASSES); ++pass) {
     int rc = pmx_quantile_hist(ctx, d_x, n_series, n_steps, d_seg, n_seg, d_row_order, n_rows, n_q, pass, state, hist,
                                stream);
     if (rc) return rc;
     rc = pmx_quantile_pick(ctx, hist, n_seg, d_q, n_q, pass, state, stream);
+    if (rc) return rc;
+  }
+  if (data) {
+    const int rc = pmx_quantile_tail(ctx, d_x, n_series, n_steps, d_seg, n_seg, n_q, 3, state, stream);
     if (rc) return rc;
   }
   return pmx_quantile_finish(ctx, state, n_seg, d_q, n_q, d_n, d_lo, d_hi, d_x_lo, d_x_hi, d_value, stream);

@@ -479,7 +479,7 @@ class Engine:
                 self._ptr(outs["n"]),
                 self._ptr(outs["lo"]), self._ptr(outs["hi"]), self._ptr(outs["x_lo"]), self._ptr(outs["x_hi"]),
                 self._ptr(outs["value"]), self._stream()))
-            self.launches += 3 * _abi.QUANTILE_PASSES - 1    # hist (two kernels from pass 3 on) + pick + tail + finish
+            self.launches += 8                                  # three passes of hist + pick, tail, finish
             return outs
         state, hist = buffers if buffers is not None else self.quantile_buffers(n_seg, n_q)
         if summary is None:
@@ -505,9 +505,11 @@ class Engine:
                 dist.all_reduce(hist[:n_h], op=dist.ReduceOp.SUM, group=group)
             _abi.check(self.lib.pmx_quantile_pick(self.ctx, self._ptr(hist), n_seg, self._ptr(d_q), n_q, p,
                                                   self._ptr(state), self._stream()))
-            if p == 2 and group is None and S > 0 and T > 0:   # one rank: the candidate lists hold everything
-                _abi.check(self.lib.pmx_quantile_tail(self.ctx, n_seg, n_q, 3, self._ptr(state), self._stream()))
+            if p == 2 and group is None and S > 0 and T > 0:   # one rank: the candidate lists settle the rest
+                _abi.check(self.lib.pmx_quantile_tail(self.ctx, self._ptr(x), S, T, self._ptr(d_seg), n_seg, n_q, 3,
+                                                      self._ptr(state), self._stream()))
                 self.launches += 1
+                break
             elif p == 2 and group is not None:
                 # several ranks: gather the few keys that still match a target and settle every segment
                 # on every rank alike; the later passes (and their all-reduces) run only if a segment
