@@ -115,6 +115,31 @@ def align(ts, val, off, start_ms, step_ms, n_steps, lookback_ms=DEFAULT_LOOKBACK
     return out, idx_out
 
 
+def bucket(ts, val, off, start_ms, step_ms, n_steps):
+    """Bucket down-sampling, the second form of SURVEY X3: ``Series.resample('<step>')`` bins
+    ``[start + j*step, start + (j+1)*step)`` labelled left; per bin the LAST non-NaN sample, the MEAN
+    of the non-NaN samples (summed in time order) and their COUNT.  A stale marker is a NaN like any
+    other here (pandas knows no markers).  Empty bin: NaN / NaN / 0.
+    Returns (last float64[S, n_steps], mean float64[S, n_steps], count int32[S, n_steps]).
+    """
+    S = len(off) - 1
+    last = np.full((S, n_steps), np.nan); mean = np.full((S, n_steps), np.nan)
+    cnt = np.zeros((S, n_steps), dtype=np.int32)
+    for s in range(S):
+        a, b = int(off[s]), int(off[s + 1])
+        t, v = ts[a:b], val[a:b]
+        j = (t - start_ms) // step_ms
+        ok = (j >= 0) & (j < n_steps) & ~np.isnan(v)
+        sums = np.zeros(n_steps)
+        for jj, vv in zip(j[ok].tolist(), v[ok].tolist()):
+            sums[jj] += vv
+            cnt[s, jj] += 1
+            last[s, jj] = vv
+        with np.errstate(invalid="ignore", divide="ignore"):
+            mean[s] = np.where(cnt[s] > 0, sums / cnt[s], np.nan)
+    return last, mean, cnt
+
+
 # --------------------------------------------------------------------------- X4
 def _windows(x, w):
     """[S, T] -> [S, T, w] trailing windows (t-w, t], left-padded with NaN."""
