@@ -148,7 +148,10 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "samples/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "note": "CPU arm runs on rank 0's host cores only, whatever N is"},
+            "config": {"workload": WORKLOAD, "series_per_step": n_series, "steps_per_series": N_STEPS,
+                       "note": f"CPU arm: each step is a {n_series}-series sample of the {N_SERIES}-series workload "
+                               "(a per-sample rate; the full workload would take minutes per step); it runs on "
+                               "rank 0's host cores only, whatever N is"},
             "cpu_baseline": {"value": v, "unit": "samples/s", "cores": cores, "kind": "port",
                              "sample": f"{n_series} of {N_SERIES} series x {N_STEPS} steps ({n} samples) per step, "
                                        f"pandas {_pandas_version()} fan-out over {cores} processes"},
@@ -189,6 +192,57 @@ def instant_path_times(eng):
         return {"error": str(e)[:200]}
 
 
+def config3_block(eng, sh, world, rank, barrier, steps=5):
+    """One config-3 shard per GPU (16 384 series x 40 320 steps, 16 metrics): ms per step of the whole
+    aggregate step, device-timed, max over ranks; and the same step without the exchange between
+    ranks (what one GPU alone does on its shard), so that the cost of the collectives is visible in
+    one run.  Data is generated on the device."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from k8s_rocm_metrics_dashboard_b200 import group_index, synth
+    from k8s_rocm_metrics_dashboard_b200.sharding import ShardedEngine
+    S3, T3, M3 = 16384, 40320, 16
+    dev = eng.device
+    ts, val, off = synth.dense_device(S3, T3, M3, seed=3000 + rank, nan_frac=1e-3, device=dev)
+    gid = (np.arange(S3) % M3).astype(np.int32)
+    seg = torch.as_tensor(gid, device=dev)
+    perm, goff = group_index(gid, M3)
+    pg = (torch.as_tensor(perm, device=dev), torch.as_tensor(goff, device=dev))
+    out = {k: torch.empty((S3, T3), dtype=torch.float64, device=dev)
+           for k in ("aligned", "roll_min", "roll_max", "roll_mean", "rate")}
+    alone = ShardedEngine.__new__(ShardedEngine)
+    alone.eng, alone.group, alone.world, alone.rank, alone._qbuf = eng, None, 1, 0, {}
+
+    def timed(engine_like):
+        def one():
+            engine_like.aggregate_step(ts, val, off, START_MS, STEP_MS, T3, WINDOW_STEPS, seg, M3, pg, QS, out=out,
+                                       lookback_ms=LOOKBACK_MS, defer_check=True)
+        for _ in range(2):
+            one()
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(steps):
+            one()
+        b.record()
+        barrier()
+        tt = torch.tensor([a.elapsed_time(b) / steps], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return float(tt.item())
+
+    ms = timed(sh)
+    ms_alone = timed(alone) if world > 1 else ms
+    ok = eng.deferred_ok(wait=True)
+    n = S3 * T3
+    return {"workload": f"config3 shard per GPU: {S3} series x {T3} steps x {M3} metrics ({n} samples); at 8 GPUs this is "
+                        "config 3 (5,284,823,040 samples)",
+            "ms_per_step": ms, "samples_per_s": world * n / (ms * 1e-3), "steps": steps,
+            "ms_per_step_without_exchange": ms_alone, "exchange_efficiency": ms_alone / ms,
+            "deferred_checks_ok": ok}
+
+
 def _pandas_version():
     import pandas
     return pandas.__version__
@@ -224,14 +278,27 @@ def run_engine(args):
            for k in ("aligned", "roll_min", "roll_max", "roll_mean", "rate")}
     n_samples = S * T
 
+    checks = {"ok": True}
+
     def step():
-        return sh.aggregate_step(ts, val, off, START_MS, STEP_MS, T, WINDOW_STEPS, seg, N_METRICS, perm_goff,
-                                 QS, out=out, lookback_ms=LOOKBACK_MS)
+        # no host synchronisation inside the step: whether every segment fitted the key exchange of
+        # the cluster-wide quantiles is a device counter, looked at one step later (Engine.deferred_ok)
+        r = sh.aggregate_step(ts, val, off, START_MS, STEP_MS, T, WINDOW_STEPS, seg, N_METRICS, perm_goff,
+                              QS, out=out, lookback_ms=LOOKBACK_MS, defer_check=True)
+        checks["ok"] = eng.deferred_ok(wait=False) and checks["ok"]
+        return r
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    # ---- parity before timing: every rank's shard of a small config against the oracle on the union
+    parity = None
+    if world > 1 and not args.no_parity_check:
+        from tests.multi_gpu_check import parity_check
+        parity = parity_check(eng, sh, rank, world)
+        barrier()
 
     sampler = ClockSampler(local) if rank == 0 else None
     for _ in range(max(args.warmup, 3)):
@@ -262,6 +329,7 @@ def run_engine(args):
     ev1.record()
     barrier()
     w1 = time.time()
+    checks["ok"] = eng.deferred_ok(wait=True) and checks["ok"]
     eng.fused = orig_fused
     launches = eng.launches - l0
     ms = ev0.elapsed_time(ev1)
@@ -312,6 +380,17 @@ def run_engine(args):
     h2d = (h_ts.numel() + h_val.numel() + h_off.numel()) * 8
     d2h = sum(v.numel() for v in h_out.values()) * 8 + h_sum.numel() * 8
 
+    # ---- config 3 (1024 nodes x 8 GPUs x 16 metrics, 7 d @ 15 s) = 16 384 series x 40 320 steps per GPU on
+    # 8 GPUs: the same step on that shard, with and without the exchange between ranks
+    cfg3 = None
+    ns_cpu = 768                                                 # the CPU baseline's sample: keep it, free the rest
+    c_ts, c_val = h_ts[:ns_cpu * T].numpy().copy(), h_val[:ns_cpu * T].numpy().copy()
+    c_off = h_off[:ns_cpu + 1].numpy().copy()
+    if not args.no_config3:
+        del ts, val, off, out, h_ts, h_val, h_off, h_out, d_ts, d_val, d_off, host
+        torch.cuda.empty_cache()
+        cfg3 = config3_block(eng, sh, world, rank, barrier)
+
     if rank == 0:
         peak, which = measured_peak()
         achieved = n_samples * FUSED_BYTES_PER_SAMPLE / (fused_ms * 1e-3) / 1e9
@@ -324,10 +403,7 @@ def run_engine(args):
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             from oracle import prom_oracle  # noqa: F401  (checker timed as the CPU baseline)
-            ns = 768
-            sl = slice(0, ns * T)
-            c_ts, c_val = h_ts[sl].numpy(), h_val[sl].numpy()
-            c_off = h_off[:ns + 1].numpy()
+            ns = ns_cpu
             sec = cpu_time_pandas(c_ts, c_val, c_off, gid[:ns], 1)
             cpu = {"value": ns * T / sec, "unit": "samples/s", "cores": 1, "kind": "port",
                    "sample": f"first {ns} of {S} series x {T} steps of the same device data ({ns * T} samples), "
@@ -348,7 +424,8 @@ def run_engine(args):
                 "cpu_baseline": cpu,
                 "e2e": {"value": world * n_samples * e2e_steps / e2e_s, "unit": "samples/s",
                         "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps},
-                "gpu_launches": launches, "clocks": clocks, "instant_path": instant}
+                "gpu_launches": launches, "clocks": clocks, "instant_path": instant,
+                "deferred_checks_ok": checks["ok"], "parity_check": parity, "config3": cfg3}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -366,6 +443,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="engine", choices=["engine", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity-check", action="store_true")
+    ap.add_argument("--no-config3", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -185,6 +185,18 @@ int pmx_group_reduce_noalloc(const double* d_x, int64_t n_series, int64_t n_step
                              double* d_sum, int64_t* d_count, double* d_min, double* d_max,
                              double* d_mean, pmx_stream stream);
 
+/* ---- group partials across ranks.  Per-card groups are rank-local; per-metric groups
+ * span ranks (the reference's own per-column statistics, app.py:216-221, seen cluster-wide).
+ * pmx_group_pack writes one rank's partials as 4 x n doubles (sum, count, min or +inf, max or
+ * -inf); after ONE all-gather of those buffers pmx_group_combine folds d_gathered[n_ranks][4][n] in
+ * rank order into the outputs of pmx_group_reduce (empty group: sum 0, count 0, NaN).  Every rank
+ * folds the same data in the same order, so all ranks hold identical bits. */
+int pmx_group_pack(const double* d_sum, const int64_t* d_count, const double* d_min,
+                   const double* d_max, int64_t n, double* d_packed, pmx_stream stream);
+int pmx_group_combine(const double* d_gathered, int n_ranks, int64_t n, double* d_sum,
+                      int64_t* d_count, double* d_min, double* d_max, double* d_mean,
+                      pmx_stream stream);
+
 /* ---- H5 / H6 / H9  the per-card steps of the instant path.
  * pmx_pivot_gather: long -> wide (df.pivot at app.py:207): out[cell] = val[src[cell]] or NaN when
  *   src[cell] < 0 (missing cell).  Duplicate (gpu_id, metric) keys are detected by the adapter
@@ -232,6 +244,15 @@ int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
                       const int32_t* d_seg, int64_t n_seg,
                       const int32_t* d_row_order, int64_t n_rows, int64_t n_q, int pass,
                       const uint64_t* d_state, uint64_t* d_hist, pmx_stream stream);
+/* The pass that builds the candidate lists is 2 by default; pmx_quantile_hist_lp lets the caller move
+ * it to 3 (one more full pass, far fewer candidates), which pmx_quantile_list_pass recommends for
+ * segments of more than ~6 M values.  All ranks of a selection must use the same list_pass, and the
+ * tail calls (from_pass = list_pass + 1 or later) follow it. */
+int pmx_quantile_list_pass(int64_t n_series, int64_t n_steps, int64_t n_seg);
+int pmx_quantile_hist_lp(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
+                         const int32_t* d_seg, int64_t n_seg,
+                         const int32_t* d_row_order, int64_t n_rows, int64_t n_q, int pass, int list_pass,
+                         const uint64_t* d_state, uint64_t* d_hist, pmx_stream stream);
 /* Optional start from a group reduction.  With the count, minimum and maximum of every segment over
  * ALL ranks (pmx_group_reduce on the same values, combined across ranks) the keys are taken
  * relative to key(min) and the leading bits that key(max) - key(min) leaves zero are skipped, so

@@ -60,12 +60,16 @@ SIGNATURES = {
     "pmx_group_index": (_int, [_p, _i64, _i64, _p, _p]),
     "pmx_group_reduce": (_int, [_p, _p, _i64, _i64, _p, _p, _i64, _int, _p, _p, _p, _p, _p, _p]),
     "pmx_group_reduce_noalloc": (_int, [_p, _i64, _i64, _p, _p, _i64, _p, _p, _p, _p, _p, _p]),
+    "pmx_group_pack": (_int, [_p, _p, _p, _p, _i64, _p, _p]),
+    "pmx_group_combine": (_int, [_p, _int, _i64, _p, _p, _p, _p, _p, _p]),
     "pmx_pivot_gather": (_int, [_p, _p, _p, _i64, _p, _p]),
     "pmx_ratio_pct": (_int, [_p, _p, _i64, _p, _i64, _i64, _p, _i64, _p, _p]),
     "pmx_where_gt": (_int, [_p, _p, _i64, C.c_double, _p, _p]),
     "pmx_slab_tail_lengths": (_int, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p]),
     "pmx_slab_tail_gather": (_int, [_p, _p, _p, _p, _p, _i64, _i64, _p, _p, _p]),
     "pmx_quantile_hist": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _i64, _i64, _int, _p, _p, _p]),
+    "pmx_quantile_hist_lp": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _i64, _i64, _int, _int, _p, _p, _p]),
+    "pmx_quantile_list_pass": (_int, [_i64, _i64, _i64]),
     "pmx_quantile_init": (_int, [_p, _p, _p, _p, _i64, _p, _i64, _p, _p]),
     "pmx_quantile_tail": (_int, [_p, _p, _i64, _i64, _p, _i64, _i64, _int, _p, _p]),
     "pmx_quantile_tail_filter": (_int, [_p, _i64, _i64, _int, _p, _p, _p]),

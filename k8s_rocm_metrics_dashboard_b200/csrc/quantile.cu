@@ -46,7 +46,7 @@ __host__ __device__ __forceinline__ int digit_bits(int pass) { return pass < 5 ?
 constexpr int ST_HDR = 3;
 constexpr unsigned TAIL_KEYS = 8192;     // keys pmx_quantile_tail keeps in shared memory per segment
 constexpr unsigned GATHER_ROW = PMX_QUANTILE_GATHER_ROW;   // per segment and rank: count, then up to ROW-1 keys
-constexpr unsigned GATHER_KEYS = GATHER_ROW - 1;
+constexpr unsigned GATHER_KEYS = GATHER_ROW - 1 - 2 * MAX_TARGETS;   // ... and, at the row's end, min and max key per target
 constexpr int ST_RESOLVED_BIT = 40;      // in word [1]: every target's key is complete
 #define ST_PF(tg) (ST_HDR + 2 * (tg))
 #define ST_RK(tg) (ST_HDR + 2 * (tg) + 1)
@@ -356,6 +356,10 @@ tail_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __r
   __shared__ uint64_t s_old[MAX_TARGETS], s_pf[MAX_TARGETS], s_k[MAX_TARGETS], s_nk[MAX_TARGETS];
   __shared__ unsigned int s_warp[8];
   __shared__ unsigned int s_cnt;
+  // smallest and largest key that matches each target's prefix: equal means every remaining key of
+  // that target is the same value (repeated readings), and the target is settled whatever its rank
+  __shared__ unsigned long long s_tmin[MAX_TARGETS], s_tmax[MAX_TARGETS];
+  __shared__ int s_done[MAX_TARGETS];
   const int sg = blockIdx.x;
   uint64_t* st = state + (size_t)sg * sw;
   const unsigned n_list = GATHERED ? 0u : cand_cnt[sg];
@@ -368,6 +372,7 @@ tail_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __r
   if (threadIdx.x < n_t) {
     s_pf[threadIdx.x] = st[ST_PF(threadIdx.x)];
     s_k[threadIdx.x] = s_nk[threadIdx.x] = st[ST_RK(threadIdx.x)];
+    s_tmin[threadIdx.x] = ~0ULL; s_tmax[threadIdx.x] = 0; s_done[threadIdx.x] = 0;
   }
   if (threadIdx.x == 0) s_cnt = 0;
   __syncthreads();
@@ -380,7 +385,25 @@ tail_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __r
       const unsigned long long c = rows[((size_t)r * gridDim.x + sg) * GATHER_ROW];
       if (c > GATHER_KEYS) fits = false; else total += (unsigned)c;
     }
-    if (!fits || total > TAIL_KEYS) { if (threadIdx.x == 0) atomicAdd(unresolved, 1u); return; }
+    if (threadIdx.x < n_t) {
+      unsigned long long lo = ~0ULL, hi = 0;
+      for (int r = 0; r < n_ranks; ++r) {
+        const unsigned long long* row = rows + ((size_t)r * gridDim.x + sg) * GATHER_ROW;
+        const unsigned long long a = row[GATHER_ROW - 2 * MAX_TARGETS + threadIdx.x], b = row[GATHER_ROW - MAX_TARGETS + threadIdx.x];
+        lo = a < lo ? a : lo; hi = b > hi ? b : hi;
+      }
+      s_tmin[threadIdx.x] = lo; s_tmax[threadIdx.x] = hi;
+    }
+    __syncthreads();
+    if (!fits || total > TAIL_KEYS) {
+      // the keys do not fit -- but targets whose remaining keys are all one value need no keys
+      bool all = true;
+      for (int tg = 0; tg < n_t; ++tg) all = all && s_tmin[tg] == s_tmax[tg];
+      if (!all) { if (threadIdx.x == 0) atomicAdd(unresolved, 1u); return; }
+      if (threadIdx.x < n_t) { st[ST_PF(threadIdx.x)] = s_tmin[threadIdx.x]; st[ST_RK(threadIdx.x)] = 0; }
+      if (threadIdx.x == 0) st[1] |= 1ULL << ST_RESOLVED_BIT;
+      return;
+    }
     unsigned off = 0;
     for (int r = 0; r < n_ranks; ++r) {
       const unsigned long long* row = rows + ((size_t)r * gridDim.x + sg) * GATHER_ROW;
@@ -407,18 +430,37 @@ tail_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __r
           const uint64_t top = kk[u] >> g0.pshift;
           for (int tg = 0; tg < n_t; ++tg) hit |= top == s_pf[tg];
         }
-        if (hit) { const unsigned pos = atomicAdd(&s_cnt, 1u); if (pos < TAIL_KEYS) skeys[pos] = kk[u]; }
+        if (hit) {
+          const unsigned pos = atomicAdd(&s_cnt, 1u); if (pos < TAIL_KEYS) skeys[pos] = kk[u];
+          const uint64_t top = kk[u] >> g0.pshift;
+          for (int tg = 0; tg < n_t; ++tg)
+            if (top == s_pf[tg]) {                           // plain reads first: both only ever move one way
+              if (kk[u] < *(volatile unsigned long long*)&s_tmin[tg]) atomicMin(&s_tmin[tg], kk[u]);
+              if (kk[u] > *(volatile unsigned long long*)&s_tmax[tg]) atomicMax(&s_tmax[tg], kk[u]);
+            }
+        }
       }
     }
   }
   __syncthreads();
   const unsigned n = s_cnt;
+  // Too many keys still match for shared memory (repeated values, or a narrow value range that
+  // two digits did not split): targets whose keys are all equal are settled at once; for the
+  // others the remaining passes read the candidate list itself (or, if that overflowed, the data).
+  bool from_list = false;
   if (n > TAIL_KEYS) {
     if (GATHERED) return;                                   // (not reached: the merge checked the counts)
-    from_data = true;
+    if (threadIdx.x < n_t && s_tmin[threadIdx.x] == s_tmax[threadIdx.x]) {
+      s_done[threadIdx.x] = 1; s_pf[threadIdx.x] = s_tmin[threadIdx.x]; s_k[threadIdx.x] = s_nk[threadIdx.x] = 0;
+    }
+    __syncthreads();
+    from_list = true;
+  }
+  if (from_data) {                                          // overflowed list: the same shortcut needs one sweep of the data
+    from_list = false;
   }
   const unsigned long long* keys = skeys;
-  if (!from_data && n <= 512) {
+  if (!from_data && !from_list && n <= 512) {
     // A short list is settled directly: among the keys that carry the same prefix, key i has
     // r keys below it and e equal to it, and it is target t's order statistic iff r <= k_t < r + e.
     const Geom g0 = seg_geom(st, from_pass);
@@ -449,14 +491,27 @@ tail_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __r
     if (threadIdx.x < n_t) s_old[threadIdx.x] = s_pf[threadIdx.x];
     __syncthreads();
     for (int tg = 0; tg < n_t; ++tg) {
+      if (s_done[tg]) continue;                             // settled by equal keys
       bool is_rep = true;
-      for (int j = 0; j < tg; ++j) if (s_old[j] == s_old[tg]) { is_rep = false; break; }
+      for (int j = 0; j < tg; ++j) if (!s_done[j] && s_old[j] == s_old[tg]) { is_rep = false; break; }
       if (!is_rep) continue;                                // uniform
       for (int i = threadIdx.x; i < BINS; i += blockDim.x) sh[i] = 0;
       __syncthreads();
       const uint64_t want = s_old[tg];
       int spread = 0;
-      if (!from_data) {
+      if (from_list) {
+        const unsigned long long* glist = cand + (size_t)sg * cap;
+        for (unsigned i0 = 0; i0 < n_list; i0 += blockDim.x * 4) {
+          unsigned long long kk[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) { const unsigned i = i0 + u * blockDim.x + threadIdx.x; kk[u] = i < n_list ? glist[i] : ~0ULL; }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const unsigned i = i0 + u * blockDim.x + threadIdx.x;
+            hist_add(sh, i < n_list && (kk[u] >> gm.pshift) == want, (unsigned)(kk[u] >> gm.shift) & mask, lane, spread);
+          }
+        }
+      } else if (!from_data) {
         for (unsigned i0 = 0; i0 < n; i0 += blockDim.x) {
           const unsigned i = i0 + threadIdx.x;
           const bool in = i < n;
@@ -488,7 +543,7 @@ tail_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __r
 #pragma unroll
       for (int w = 0; w < 8; ++w) if (w < warp) base += s_warp[w];
       for (int j = tg; j < n_t; ++j) {                      // every target that shares this prefix
-        if (s_old[j] != want) continue;
+        if (s_done[j] || s_old[j] != want) continue;
         const unsigned long long k = s_k[j];                // ranks are replaced only after the pass (s_nk)
         unsigned long long acc = base + inc - sum;
 #pragma unroll
@@ -517,13 +572,22 @@ tail_filter_kernel(const unsigned long long* __restrict__ cand, const unsigned i
                    unsigned cap, int n_t, int from_pass, const uint64_t* __restrict__ state, int sw,
                    unsigned long long* __restrict__ rows) {
   __shared__ uint64_t s_pf[MAX_TARGETS];
+  __shared__ unsigned long long s_tmin[MAX_TARGETS], s_tmax[MAX_TARGETS];
   __shared__ unsigned int s_cnt;
   const int sg = blockIdx.x;
   const uint64_t* st = state + (size_t)sg * sw;
   unsigned long long* row = rows + (size_t)sg * GATHER_ROW;
   const unsigned n_list = cand_cnt[sg];
+  if (threadIdx.x < MAX_TARGETS) {                          // no key of this rank matches: neutral for min / max
+    row[GATHER_ROW - 2 * MAX_TARGETS + threadIdx.x] = ~0ULL; row[GATHER_ROW - MAX_TARGETS + threadIdx.x] = 0;
+    s_tmin[threadIdx.x] = ~0ULL; s_tmax[threadIdx.x] = 0;
+  }
   if (st[0] == 0) { if (threadIdx.x == 0) row[0] = 0; return; }
-  if (n_list > cap) { if (threadIdx.x == 0) row[0] = ~0ULL; return; }
+  if (n_list > cap) {                                       // an overflowed list says nothing about equal keys either
+    if (threadIdx.x == 0) row[0] = ~0ULL;
+    if (threadIdx.x < MAX_TARGETS) { row[GATHER_ROW - 2 * MAX_TARGETS + threadIdx.x] = 0; row[GATHER_ROW - MAX_TARGETS + threadIdx.x] = ~0ULL; }
+    return;
+  }
   if (threadIdx.x < n_t) s_pf[threadIdx.x] = st[ST_PF(threadIdx.x)];
   if (threadIdx.x == 0) s_cnt = 0;
   __syncthreads();
@@ -544,11 +608,23 @@ tail_filter_kernel(const unsigned long long* __restrict__ cand, const unsigned i
         const uint64_t top = kk[u] >> g0.pshift;
         for (int tg = 0; tg < n_t; ++tg) hit |= top == s_pf[tg];
       }
-      if (hit) { const unsigned pos = atomicAdd(&s_cnt, 1u); if (pos < GATHER_KEYS) row[1 + pos] = kk[u]; }
+      if (hit) {
+        const unsigned pos = atomicAdd(&s_cnt, 1u); if (pos < GATHER_KEYS) row[1 + pos] = kk[u];
+        const uint64_t top = kk[u] >> g0.pshift;
+        for (int tg = 0; tg < n_t; ++tg)
+          if (top == s_pf[tg]) {
+            if (kk[u] < *(volatile unsigned long long*)&s_tmin[tg]) atomicMin(&s_tmin[tg], kk[u]);
+            if (kk[u] > *(volatile unsigned long long*)&s_tmax[tg]) atomicMax(&s_tmax[tg], kk[u]);
+          }
+      }
     }
   }
   __syncthreads();
   if (threadIdx.x == 0) row[0] = s_cnt;
+  if (threadIdx.x < n_t) {
+    row[GATHER_ROW - 2 * MAX_TARGETS + threadIdx.x] = s_tmin[threadIdx.x];
+    row[GATHER_ROW - MAX_TARGETS + threadIdx.x] = s_tmax[threadIdx.x];
+  }
 }
 
 // One CTA per segment walks the segment's targets.  Targets that share a prefix share the
@@ -725,7 +801,24 @@ extern "C" {
 int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
                       const int32_t* d_seg, int64_t n_seg, const int32_t* d_row_order, int64_t n_rows,
                       int64_t n_q, int pass, const uint64_t* d_state, uint64_t* d_hist, pmx_stream stream) {
+  return pmx_quantile_hist_lp(ctx, d_x, n_series, n_steps, d_seg, n_seg, d_row_order, n_rows, n_q, pass, 2, d_state,
+                              d_hist, stream);
+}
+
+int pmx_quantile_list_pass(int64_t n_series, int64_t n_steps, int64_t n_seg) {
+  // candidates after pass p number about n * (share of a 2^(11 p) th of the key range) per target; a
+  // list holds 2^20 keys.  Counter-like values (half of them inside one binary exponent) reach
+  // ~n/40 per distinct prefix after one digit, so segments beyond a few million values wait a digit.
+  if (n_seg <= 0) return 2;
+  return (n_series * n_steps) / n_seg > ((int64_t)6 << 20) ? 3 : 2;
+}
+
+int pmx_quantile_hist_lp(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
+                         const int32_t* d_seg, int64_t n_seg, const int32_t* d_row_order, int64_t n_rows,
+                         int64_t n_q, int pass, int list_pass, const uint64_t* d_state, uint64_t* d_hist,
+                         pmx_stream stream) {
   PMX_REQUIRE(ctx, "ctx is NULL");
+  PMX_REQUIRE(list_pass == 2 || list_pass == 3, "list_pass must be 2 or 3");
   PMX_REQUIRE(n_series >= 0 && n_steps >= 0 && n_seg >= 0 && n_seg <= 65535, "bad sizes (n_seg <= 65535)");
   PMX_REQUIRE(n_q >= 1 && 2 * n_q <= MAX_TARGETS, "n_q must be in [1, 8]");
   PMX_REQUIRE(pass >= 0 && pass <= PMX_QUANTILE_PASSES, "pass out of range");
@@ -740,11 +833,11 @@ int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
   // candidate lists (ctx scratch; they live from pass 2 to pass 5 of one selection)
   unsigned cap = 0; unsigned int* cand_cnt = nullptr; unsigned long long* cand = nullptr;
   int mode = 0;
-  if (pass >= 2) {
+  if (pass >= list_pass) {
     size_t hdr;
     if (int rc = cand_layout(ctx, n_seg, &cap, &cand_cnt, &cand, &hdr)) return rc;
-    mode = pass == 2 ? 1 : 2;
-    if (pass == 2) PMX_CUDA(cudaMemsetAsync(cand_cnt, 0, hdr, st));
+    mode = pass == list_pass ? 1 : 2;
+    if (pass == list_pass) PMX_CUDA(cudaMemsetAsync(cand_cnt, 0, hdr, st));
   }
   const size_t smem = (size_t)n_h * BINS * sizeof(unsigned int);
   PMX_CUDA(cudaFuncSetAttribute(hist_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(MAX_TARGETS * BINS * sizeof(unsigned int))));

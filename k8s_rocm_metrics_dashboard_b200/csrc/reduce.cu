@@ -138,6 +138,40 @@ group_step_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* 
   if (o_mean) o_mean[o] = any ? r.sum / (double)r.cnt : pmx_nan();
 }
 
+
+// Multi-GPU exchange of group partials: pack puts one rank's (sum, count, min, max)
+// into one buffer of 4 x n doubles (empty groups: min +inf, max -inf; counts are exact in a
+// double below 2^53), one all-gather moves the buffers, combine folds the ranks in rank order
+// from identical data on every rank, so every rank ends with the same bits.
+__global__ void group_pack_kernel(const double* __restrict__ sum, const int64_t* __restrict__ cnt,
+                                  const double* __restrict__ mn, const double* __restrict__ mx, int64_t n,
+                                  double* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double INF = __longlong_as_double(0x7FF0000000000000LL);
+  const int64_t c = cnt[i];
+  out[i] = sum[i]; out[n + i] = (double)c;
+  out[2 * n + i] = c > 0 ? mn[i] : INF; out[3 * n + i] = c > 0 ? mx[i] : -INF;
+}
+__global__ void group_combine_kernel(const double* __restrict__ all, int world, int64_t n, double* o_sum,
+                                     int64_t* o_cnt, double* o_min, double* o_max, double* o_mean) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  Part r = part_identity();
+  double c = 0.0;
+  for (int w = 0; w < world; ++w) {
+    const double* b = all + (size_t)w * 4 * n;
+    r.sum += b[i]; c += b[n + i]; r.mn = fmin(r.mn, b[2 * n + i]); r.mx = fmax(r.mx, b[3 * n + i]);
+  }
+  r.cnt = (long long)(c + 0.5);
+  const bool any = r.cnt > 0;
+  if (o_sum) o_sum[i] = r.sum;
+  if (o_cnt) o_cnt[i] = r.cnt;
+  if (o_min) o_min[i] = any ? r.mn : pmx_nan();
+  if (o_max) o_max[i] = any ? r.mx : pmx_nan();
+  if (o_mean) o_mean[i] = any ? r.sum / (double)r.cnt : pmx_nan();
+}
+
 }  // namespace
 
 extern "C" {
@@ -236,6 +270,27 @@ int pmx_group_reduce_noalloc(const double* d_x, int64_t n_series, int64_t n_step
   }
   group_fold_kernel<<<(unsigned)((n_groups + 3) / 4), 128, 0, st>>>(part, d_perm, d_goff, n_groups, d_sum, d_count,
                                                                   d_min, d_max, d_mean);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
+int pmx_group_pack(const double* d_sum, const int64_t* d_count, const double* d_min, const double* d_max,
+                   int64_t n, double* d_packed, pmx_stream stream) {
+  if (n < 0) return pmx_fail(PMX_E_INVALID, "pmx_group_pack: negative size");
+  if (n == 0) return PMX_OK;
+  if (!d_sum || !d_count || !d_min || !d_max || !d_packed) return pmx_fail(PMX_E_INVALID, "pmx_group_pack: NULL buffer");
+  group_pack_kernel<<<(unsigned)((n + 255) / 256), 256, 0, pmx_st(stream)>>>(d_sum, d_count, d_min, d_max, n, d_packed);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
+int pmx_group_combine(const double* d_gathered, int n_ranks, int64_t n, double* d_sum, int64_t* d_count,
+                      double* d_min, double* d_max, double* d_mean, pmx_stream stream) {
+  if (n < 0 || n_ranks < 1) return pmx_fail(PMX_E_INVALID, "pmx_group_combine: bad sizes");
+  if (n == 0) return PMX_OK;
+  if (!d_gathered) return pmx_fail(PMX_E_INVALID, "pmx_group_combine: NULL buffer");
+  group_combine_kernel<<<(unsigned)((n + 255) / 256), 256, 0, pmx_st(stream)>>>(d_gathered, n_ranks, n, d_sum, d_count,
+                                                                                d_min, d_max, d_mean);
   PMX_LAUNCH_CHECK();
   return PMX_OK;
 }

@@ -403,6 +403,28 @@ class Engine:
         self.launches += 1 if per_step else 2
         return sm, cnt, mn, mx, mean
 
+    def group_combine(self, sm, cnt, mn, mx, group):
+        """Partials of ``group_reduce`` on every rank -> the same reduction over all ranks' series:
+        pmx_group_pack, ONE all-gather, pmx_group_combine (rank order, identical bits everywhere)."""
+        import torch.distributed as dist
+        t = self.torch
+        world = dist.get_world_size(group)
+        n = sm.numel()
+        key = (n, world)
+        cache = self.__dict__.setdefault("_combuf", {})
+        if key not in cache:
+            cache[key] = (self._empty((4 * n,), t.float64), self._empty((world * 4 * n,), t.float64))
+        packed, gathered = cache[key]
+        _abi.check(self.lib.pmx_group_pack(self._ptr(sm), self._ptr(cnt), self._ptr(mn), self._ptr(mx), n,
+                                           self._ptr(packed), self._stream()))
+        dist.all_gather_into_tensor(gathered, packed, group=group)
+        o_sm, o_mn, o_mx, o_mean = (t.empty_like(sm) for _ in range(4))
+        o_cnt = t.empty_like(cnt)
+        _abi.check(self.lib.pmx_group_combine(self._ptr(gathered), world, n, self._ptr(o_sm), self._ptr(o_cnt),
+                                              self._ptr(o_mn), self._ptr(o_mx), self._ptr(o_mean), self._stream()))
+        self.launches += 2
+        return o_sm, o_cnt, o_mn, o_mx, o_mean
+
     # ------------------------------------------------------------------ instant-path steps
     def pivot_gather(self, val, cell_src):
         t = self.torch
@@ -436,6 +458,21 @@ class Engine:
         return out
 
     # ------------------------------------------------------------------ K6
+    def deferred_ok(self, wait=True):
+        """Looks at the counters of earlier ``quantiles(..., defer_check=True)`` calls.  Returns True
+        when every finished one was exact.  ``wait=False`` leaves calls whose copy has not arrived
+        pending (nothing blocks); ``wait=True`` waits for all of them."""
+        pend = self.__dict__.get("_deferred", [])
+        ok, keep = True, []
+        for ev, flag in pend:
+            if not wait and not ev.query():
+                keep.append((ev, flag))
+                continue
+            ev.synchronize()
+            ok = ok and int(flag[0]) == 0
+        self._deferred = keep
+        return ok
+
     def quantile_buffers(self, n_seg, n_q):
         t = self.torch
         state = self.torch.zeros((n_seg, 3 + 4 * n_q), dtype=t.int64, device=self.device)
@@ -452,7 +489,8 @@ class Engine:
                           self._empty((1,), t.int32))
         return cache[key]
 
-    def quantiles(self, x, seg, n_seg, qs, group=None, buffers=None, row_order=None, summary=None):
+    def quantiles(self, x, seg, n_seg, qs, group=None, buffers=None, row_order=None, summary=None, defer_check=False,
+                  list_pass=None):
         """Exact quantiles per segment.  x: [S,T] device; seg: int per series (host or device).
         With ``group`` (a torch.distributed process group over NCCL) the histograms of every pass
         are all-reduced, so the result is the quantile of the union of all ranks' values.
@@ -461,7 +499,16 @@ class Engine:
         ``summary``: optional (count int64[n_seg], min f64[n_seg], max f64[n_seg]) device tensors of
         each segment over ALL ranks (what ``group_reduce`` / ``combine_group_partials`` return for the
         same values): the selection then starts behind the key bits that min and max share and
-        saves the first full pass."""
+        saves the first full pass.
+        ``defer_check`` (several ranks only): after pass 2 the ranks exchange the few keys that still
+        match a target; whether every segment fitted that exchange is a counter on the device.  By
+        default the host reads it (one synchronisation per call) and runs the per-pass protocol if it
+        is not zero.  With ``defer_check=True`` the call finishes the selection at once, copies the
+        counter to pinned host memory behind the stream and leaves looking at it to
+        ``deferred_ok()``: the outputs are exact iff that returns True (nothing is recomputed;
+        a caller that needs the slow path repeats the call without ``defer_check``).
+        ``list_pass``: the pass that keeps the keys still matching a target (2 or 3; default: what
+        pmx_quantile_list_pass recommends for this shape).  All ranks must use the same value."""
         t = self.torch
         x = self._dev(x, t.float64)
         S, T = x.shape
@@ -494,23 +541,29 @@ class Engine:
                                                   self._ptr(d_q), n_q, self._ptr(state), self._stream()))
             self.launches += 1
             passes = range(1, _abi.QUANTILE_PASSES + 1)
+        # Several ranks starting from count/min/max: one more digit (read from the candidate lists) before
+        # the keys are exchanged, so that 33 key bits are settled by then and a rank's row is short
+        # whatever the value range looks like
+        if list_pass is None:
+            list_pass = int(self.lib.pmx_quantile_list_pass(S, T, n_seg)) if summary is not None else 2
+        tail_after = 3 if (group is not None and summary is not None) else list_pass
         for p in passes:
             self.launches += 3 if p >= 3 else 2             # hist (two kernels from pass 3 on) + pick
-            _abi.check(self.lib.pmx_quantile_hist(self.ctx, self._ptr(x), S, T, self._ptr(d_seg), n_seg,
-                                                  self._ptr(d_ord), n_rows, n_q, p,
-                                                  self._ptr(state), self._ptr(hist), self._stream()))
+            _abi.check(self.lib.pmx_quantile_hist_lp(self.ctx, self._ptr(x), S, T, self._ptr(d_seg), n_seg,
+                                                     self._ptr(d_ord), n_rows, n_q, p, list_pass,
+                                                     self._ptr(state), self._ptr(hist), self._stream()))
             n_h = n_seg * (1 if p == 0 else 2 * n_q)
             if group is not None:
                 import torch.distributed as dist
                 dist.all_reduce(hist[:n_h], op=dist.ReduceOp.SUM, group=group)
             _abi.check(self.lib.pmx_quantile_pick(self.ctx, self._ptr(hist), n_seg, self._ptr(d_q), n_q, p,
                                                   self._ptr(state), self._stream()))
-            if p == 2 and group is None and S > 0 and T > 0:   # one rank: the candidate lists settle the rest
-                _abi.check(self.lib.pmx_quantile_tail(self.ctx, self._ptr(x), S, T, self._ptr(d_seg), n_seg, n_q, 3,
+            if p == tail_after and group is None and S > 0 and T > 0:   # one rank: the candidate lists settle the rest
+                _abi.check(self.lib.pmx_quantile_tail(self.ctx, self._ptr(x), S, T, self._ptr(d_seg), n_seg, n_q, p + 1,
                                                       self._ptr(state), self._stream()))
                 self.launches += 1
                 break
-            elif p == 2 and group is not None:
+            elif p == tail_after and group is not None:
                 # several ranks: gather the few keys that still match a target and settle every segment
                 # on every rank alike; the later passes (and their all-reduces) run only if a segment
                 # did not fit, which all ranks see in the same counter
@@ -518,15 +571,22 @@ class Engine:
                 world = dist.get_world_size(group)
                 rows, gathered, unresolved = self._tail_buffers(n_seg, world)
                 if S > 0 and T > 0:
-                    _abi.check(self.lib.pmx_quantile_tail_filter(self.ctx, n_seg, n_q, 3, self._ptr(state),
+                    _abi.check(self.lib.pmx_quantile_tail_filter(self.ctx, n_seg, n_q, p + 1, self._ptr(state),
                                                                  self._ptr(rows), self._stream()))
                     self.launches += 1
                 else:
                     rows.zero_()
                 dist.all_gather_into_tensor(gathered, rows, group=group)
-                _abi.check(self.lib.pmx_quantile_tail_merge(self.ctx, self._ptr(gathered), world, n_seg, n_q, 3,
+                _abi.check(self.lib.pmx_quantile_tail_merge(self.ctx, self._ptr(gathered), world, n_seg, n_q, p + 1,
                                                             self._ptr(state), self._ptr(unresolved), self._stream()))
                 self.launches += 1
+                if defer_check:
+                    pend = self.__dict__.setdefault("_deferred", [])
+                    flag = t.empty((1,), dtype=t.int32).pin_memory()
+                    flag.copy_(unresolved, non_blocking=True)
+                    ev = t.cuda.Event(); ev.record()
+                    pend.append((ev, flag))
+                    break
                 if int(unresolved.item()) == 0:
                     break
         _abi.check(self.lib.pmx_quantile_finish(self.ctx, self._ptr(state), n_seg, self._ptr(d_q), n_q,

@@ -45,13 +45,18 @@ def shard_csr(ts, val, off, owner, rank):
     return ts[idx], val[idx], new_off, mine
 
 
-def combine_group_partials(sm, cnt, mn, mx, group=None):
-    """All-reduce per-group partials in place and return (sum, count, min, max, mean).
+def combine_group_partials(sm, cnt, mn, mx, group=None, engine=None):
+    """Combine per-group partials of all ranks and return (sum, count, min, max, mean).
 
     Inputs are torch tensors of shape [G] (or [G,T]) as produced by ``Engine.group_reduce`` on the
-    local shard: empty groups carry sum 0, count 0, min/max NaN."""
+    local shard: empty groups carry sum 0, count 0, min/max NaN.  With ``engine`` and device
+    tensors the exchange is two kernels of the library around one all-gather
+    (``Engine.group_combine``); the tensor form below is what the CPU (gloo) tests run."""
     import torch
     import torch.distributed as dist
+    if engine is not None and sm.is_cuda and dist.is_initialized() and dist.get_world_size(group) > 1:
+        return engine.group_combine(sm.contiguous(), cnt.contiguous(), mn.contiguous(), mx.contiguous(),
+                                    group or _world_group())
     inf = float("inf")
     mn = torch.where(cnt > 0, mn, torch.full_like(mn, inf))
     mx = torch.where(cnt > 0, mx, torch.full_like(mx, -inf))
@@ -112,11 +117,13 @@ class ShardedEngine:
         return summary[1], summary[2], summary[3]
 
     def aggregate_step(self, ts, val, off, start_ms, step_ms, n_steps, window_steps, seg, n_seg, perm_goff,
-                       qs=(0.5, 0.95, 0.99), out=None, lookback_ms=300_000, host=None):
+                       qs=(0.5, 0.95, 0.99), out=None, lookback_ms=300_000, host=None, defer_check=False):
         """fused align+rolling+rate on the shard, then per-metric sum/count/min/max/mean and exact
         quantiles of the aligned values over ALL ranks.  ``seg``: metric id per local series.
         With ``host`` = {"dev": device buffers, "out": pinned host outputs} the inputs are pinned host
-        tensors and the copies are pipelined with the kernel (Engine.fused_from_host)."""
+        tensors and the copies are pipelined with the kernel (Engine.fused_from_host).
+        ``defer_check``: see ``Engine.quantiles`` -- no host synchronisation inside the step; the
+        caller asks ``Engine.deferred_ok()`` later."""
         eng = self.eng
         if host is not None:        # ts/val/off are pinned host tensors; results also go to host["out"]
             out = eng.fused_from_host(ts, val, off, start_ms, step_ms, n_steps, window_steps, host["dev"],
@@ -125,12 +132,13 @@ class ShardedEngine:
             out = eng.fused(ts, val, off, start_ms, step_ms, n_steps, window_steps, lookback_ms, out=out)
         sm, cnt, mn, mx, mean = eng.group_reduce(out["aligned"], None, n_seg, perm_goff=perm_goff)
         if self.world > 1:
-            summary = combine_group_partials(sm, cnt, mn, mx, self.group)
+            summary = combine_group_partials(sm, cnt, mn, mx, self.group, engine=eng)
             key = (n_seg, len(qs))
             if key not in self._qbuf:
                 self._qbuf[key] = eng.quantile_buffers(n_seg, len(qs))
             q = eng.quantiles(out["aligned"], seg, n_seg, list(qs), group=self.group or _world_group(),
-                              buffers=self._qbuf[key], row_order=perm_goff[0], summary=self._qsummary(summary))
+                              buffers=self._qbuf[key], row_order=perm_goff[0], summary=self._qsummary(summary),
+                              defer_check=defer_check)
         else:
             summary = (sm, cnt, mn, mx, mean)          # one rank: the kernel's own result is the summary
             key = (n_seg, len(qs))

@@ -2,7 +2,7 @@
 import numpy as np
 import pytest
 
-from k8s_rocm_metrics_dashboard_b200 import synth
+from k8s_rocm_metrics_dashboard_b200 import group_index, synth
 from oracle import prom_oracle as O
 from tests.util import assert_bits_equal, assert_close, assert_exact_or_nan
 
@@ -151,3 +151,30 @@ def test_quantiles_from_summary_signed_zero_constant_and_wide_segments(eng):
             assert_bits_equal(_np(out["x_lo"])[g], np.array(o["x_lo"]), "x_lo")
             assert_bits_equal(_np(out["x_hi"])[g], np.array(o["x_hi"]), "x_hi")
             assert_bits_equal(_np(out["value"])[g], np.array(o["value"]), "value")
+
+
+@pytest.mark.parametrize("start", ["summary", "pass0"])
+def test_quantiles_heavy_ties_integer_gauges(eng, start):
+    """Integer-valued gauges (the reference's amd_gpu_gfx_activity is 0..100): thousands of equal keys
+    per target survive every digit.  Targets whose remaining keys are all one value are settled
+    at once; a segment that mixes such ties with spread values runs its last passes on the
+    candidate list."""
+    rng = np.random.default_rng(5)
+    S, T, G = 768, 2880, 12
+    x = rng.integers(0, 101, (S, T)).astype(np.float64)
+    x[1::12] = np.round(rng.uniform(0, 100, x[1::12].shape), 1)            # 1001 distinct values
+    x[2::12] = np.where(rng.random(x[2::12].shape) < 0.9, 50.0, rng.normal(50, 1e-7, x[2::12].shape))   # ties + near-ties
+    x[rng.random(x.shape) < 0.01] = np.nan
+    gid = (np.arange(S) % G).astype(np.int32)
+    pg = group_index(gid, G)
+    qs = [0.5, 0.95, 0.99]
+    if start == "summary":
+        sm, cnt, mn, mx, _ = eng.group_reduce(x, None, G, perm_goff=pg)
+        q = eng.quantiles(x, gid, G, qs, row_order=pg[0], summary=(cnt, mn, mx))
+    else:
+        q = eng.quantiles(x, gid, G, qs, row_order=pg[0])
+    for g in range(G):
+        o = O.quantiles(x[gid == g], qs)
+        assert int(q["n"][g]) == o["n"]
+        for k in ("x_lo", "x_hi", "value"):
+            assert_bits_equal(q[k][g].cpu().numpy(), np.array(o[k]), f"{k} group {g}")
