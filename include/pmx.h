@@ -122,6 +122,17 @@ int pmx_align(pmx_ctx* ctx, const int64_t* d_ts, const double* d_val, const int6
               int64_t n_series, int64_t start_ms, int64_t step_ms, int64_t n_steps,
               int64_t lookback_ms, double* d_out_val, int32_t* d_out_idx, pmx_stream stream);
 
+/* ---- X3, second form: bucket down-sampling (the reference never reads a
+ * timestamp -- app.py:188 takes value[1] only -- so this is the survey's spec, pinned to
+ * Series.resample(...).last()/.mean()/.count() in tests/golden/range_golden.npz).
+ * Bin j covers [start_ms + j*step_ms, start_ms + (j+1)*step_ms), labelled by its left edge.  Per bin:
+ * d_last = the last non-NaN sample (NaN if none), d_mean = mean of the non-NaN samples summed in
+ * time order, d_count = their number.  Stale markers are NaNs here.  Any output may be NULL.
+ * At most 65535 series per call. */
+int pmx_bucket(pmx_ctx* ctx, const int64_t* d_ts, const double* d_val, const int64_t* d_off,
+               int64_t n_series, int64_t start_ms, int64_t step_ms, int64_t n_steps,
+               double* d_last, double* d_mean, int32_t* d_count, pmx_stream stream);
+
 /* ---- X4  rolling min/max/mean/count (K3) over the trailing `window_steps` points of a dense
  * [S,T] matrix (pandas rolling('<W>') on a regular index: window (t-W, t], NaN skipped,
  * +-inf excluded from min/max/mean but counted, stat = NaN below min_periods finite points). */
@@ -179,7 +190,9 @@ int pmx_group_reduce(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t 
  * partials live in a fixed 2 MiB array inside the library (held by every GPU that loads it):
  * at most 65536 series (PMX_E_LIMIT beyond); no ctx; the first call on a device looks the array's
  * address up once and should be made outside stream capture; all calls share the array, so calls
- * that overlap on the GPU race.  Results equal pmx_group_reduce's. */
+ * that overlap on the GPU race.  The kernels run on the CURRENT device: make the device that owns
+ * `stream` and the buffers current first (a stream of another device is a CUDA error here, not a
+ * diagnosis).  Results equal pmx_group_reduce's. */
 int pmx_group_reduce_noalloc(const double* d_x, int64_t n_series, int64_t n_steps,
                              const int32_t* d_perm, const int64_t* d_goff, int64_t n_groups,
                              double* d_sum, int64_t* d_count, double* d_min, double* d_max,

@@ -10,12 +10,13 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.environ.get("PMX_LIB_PATH") or os.path.join(HERE, "libpmx.so")   # override: kernel experiments
+LIB_PATH = os.path.join(HERE, "libpmx.so")
 
 OK, E_INVALID, E_CUDA, E_VALUE, E_KEY, E_CAPACITY, E_JSON, E_LIMIT = 0, -1, -2, -3, -4, -5, -6, -7
 QUANTILE_BINS = 2048
 QUANTILE_PASSES = 6
 QUANTILE_GATHER_ROW = 1024
+FUSED_MAX_WINDOW_STEPS = 513     # pmx_fused_align_rolling_rate: window_steps - 1 <= 512
 INT64_MAX = (1 << 63) - 1
 
 
@@ -51,6 +52,7 @@ SIGNATURES = {
     "pmx_parse_f64": (_int, [_p, _p, _u64, _p, _i64, _p, _p, _p]),
     "pmx_parse_ts_ms": (_int, [_p, _p, _u64, _p, _i64, _p, _p, _p]),
     "pmx_align": (_int, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _p, _p, _p]),
+    "pmx_bucket": (_int, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _p, _p, _p, _p]),
     "pmx_rolling": (_int, [_p, _p, _i64, _i64, _i64, _i64, _p, _p, _p, _p, _p]),
     "pmx_rolling_ragged": (_int, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _p, _p, _p, _p, _p]),
     "pmx_rate": (_int, [_p, _p, _i64, _i64, _i64, _i64, _int, _p, _p, _p, _p]),

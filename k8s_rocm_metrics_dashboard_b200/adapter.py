@@ -23,15 +23,21 @@ from .engine import DEFAULT_LOOKBACK_MS, Engine, tokenize
 PROMETHEUS_METRICS_ENDPOINT = os.environ.get("PROMETHEUS_METRICS_ENDPOINT", "http://localhost:9090/api/v1/query")
 PROMETHEUS_METRICS_PODNAME = os.environ.get("PROMETHEUS_METRICS_PODNAME", "prometheus")
 
-_engine = None
+import threading
+
+_local = threading.local()
 last_error = None          # message of the last failure (what the reference passes to st.error)
 
 
 def engine() -> Engine:
-    global _engine
-    if _engine is None:
-        _engine = Engine()
-    return _engine
+    """The calling thread's Engine.  Streamlit runs every browser session's script on a thread of
+    its own (app.py:326-331: each session loops on fetch_gpu_metrics), and a pmx_ctx serves one
+    caller at a time (its scratch is reallocated under a concurrent user), so every thread gets
+    its own ctx; they share the device."""
+    eng = getattr(_local, "engine", None)
+    if eng is None:
+        eng = _local.engine = Engine()
+    return eng
 
 
 def _report(msg):
@@ -54,14 +60,24 @@ def aggregate_instant(body, eng: Engine | None = None):
     labels = tok.labels()
     if tok.result_type != "vector":
         raise ValueError("instant path expects resultType vector")
-    # app.py:183-194: label access order is gpu_id, __name__, float(value), card_model
-    _, val = eng.parse(tok, want_ts=False) if tok.n_samples else (None, eng._empty((0,), t.float64))
+    # app.py:183-194 walks the series in order and touches gpu_id, __name__, float(value), card_model:
+    # the first failure in THAT order is the one the reference reports.  All values are decoded in
+    # one launch; a malformed one is held back until the walk reaches its series.
+    bad, val = None, None
+    try:
+        _, val = eng.parse(tok, want_ts=False) if tok.n_samples else (None, eng._empty((0,), t.float64))
+    except ValueError as e:
+        bad = e
     models, keys = {}, []
     for i, lab in enumerate(labels):
         gid, name = lab["gpu_id"], lab["__name__"]
+        if bad is not None and getattr(bad, "sample_index", 0) == i:
+            raise bad
         keys.append((gid, name))
         if gid not in models:
             models[gid] = lab["card_model"]
+    if bad is not None:
+        raise bad
     if not keys:
         raise KeyError("gpu_id")                                      # pivot on an empty frame (app.py:207)
     if len(set(keys)) != len(keys):
@@ -182,11 +198,12 @@ def _tidy_arrow(labels, grid, host, n_steps):
 
 def _summary_arrow(summary):
     import pyarrow as pa
-    return pa.table({k: pa.array(list(v)) if k == "metric_name" else pa.array(np.asarray(v)) for k, v in summary.items()})
+    return pa.table({k: pa.array(list(v)) if isinstance(v, list) else pa.array(np.asarray(v)) for k, v in summary.items()})
 
 
 def aggregate_range(body, start_ms, step_ms, n_steps, window_ms, lookback_ms=DEFAULT_LOOKBACK_MS,
-                    quantiles=(0.5, 0.95, 0.99), as_frame=True, eng: Engine | None = None, tokenizer="auto"):
+                    quantiles=(0.5, 0.95, 0.99), as_frame=True, eng: Engine | None = None, tokenizer="auto",
+                    group_keys=("__name__",)):
     """Range path: ``query_range`` matrix body -> per (series, step) tidy frame + per-metric summary.
 
     Returns (tidy, summary).  tidy columns: instance, gpu_id, metric_name, ts, value, roll_min,
@@ -195,30 +212,42 @@ def aggregate_range(body, start_ms, step_ms, n_steps, window_ms, lookback_ms=DEF
     with ``as_frame="arrow"`` pyarrow Tables (label columns dictionary-encoded, numeric columns
     zero-copy).
     ``tokenizer``: where the body is cut into tokens, see ``_range_tokens``.
+    ``group_keys``: the labels that form a summary group -- ``("__name__",)`` is one row per metric
+    over the whole answer (what app.py:216-221 computes for one node's instant vector),
+    ``("instance", "__name__")`` per node and metric, ``("instance", "gpu_id", "__name__")`` per card
+    (SURVEY X6's ``groupby(['instance','gpu_id','__name__'])``); rows come in sorted key order.
     """
     eng = eng or engine()
     tok = _range_tokens(eng, body, tokenizer)
     labels = tok.labels()
     ts, val = eng.parse(tok)
     return _aggregate_series(eng, labels, ts, val, tok.series_off, start_ms, step_ms, n_steps, window_ms,
-                             lookback_ms, quantiles, as_frame)
+                             lookback_ms, quantiles, as_frame, group_keys)
+
+
+def _summary_column(key):
+    return "metric_name" if key == "__name__" else key
 
 
 def _aggregate_series(eng, labels, ts, val, series_off, start_ms, step_ms, n_steps, window_ms, lookback_ms,
-                      quantiles, as_frame):
-    """The range path behind the tokens: CSR samples (device) -> tidy frame + per-metric summary."""
+                      quantiles, as_frame, group_keys=("__name__",)):
+    """The range path behind the tokens: CSR samples (device) -> tidy frame + per-group summary."""
     w = int(window_ms // step_ms)
     out = eng.fused(ts, val, series_off, start_ms, step_ms, n_steps, w, lookback_ms)
-    names = sorted({l.get("__name__", "") for l in labels})
-    gid = np.array([names.index(l.get("__name__", "")) for l in labels], dtype=np.int32)
+    group_keys = tuple(group_keys)
+    tuples = [tuple(l.get(k, "") for k in group_keys) for l in labels]
+    names = sorted(set(tuples))
+    where = {n: i for i, n in enumerate(names)}
+    gid = np.fromiter((where[tp] for tp in tuples), dtype=np.int32, count=len(tuples))
     from .engine import group_index
     perm_goff = group_index(gid, len(names))
     sm, cnt, mn, mx, mean = eng.group_reduce(out["aligned"], None, len(names), perm_goff=perm_goff)
     qd = eng.quantiles(out["aligned"], gid, len(names), list(quantiles), row_order=perm_goff[0],
                        summary=(cnt, mn, mx))
     host = {k: v.cpu().numpy() for k, v in out.items()}
-    summary = {"metric_name": names, "sum": sm.cpu().numpy(), "count": cnt.cpu().numpy(),
-               "min": mn.cpu().numpy(), "max": mx.cpu().numpy(), "mean": mean.cpu().numpy()}
+    summary = {_summary_column(k): [n[i] for n in names] for i, k in enumerate(group_keys)}
+    summary.update({"sum": sm.cpu().numpy(), "count": cnt.cpu().numpy(),
+                    "min": mn.cpu().numpy(), "max": mx.cpu().numpy(), "mean": mean.cpu().numpy()})
     qv = qd["value"].cpu().numpy()
     for i, q in enumerate(quantiles):
         summary[f"p{int(round(q * 100))}"] = qv[:, i]
@@ -291,7 +320,8 @@ def merge_range_chunks(eng, chunks):
 
 def fetch_gpu_metrics_range(start_s, end_s, step_s, window_s, lookback_s=DEFAULT_LOOKBACK_MS // 1000,
                             quantiles=(0.5, 0.95, 0.99), as_frame=True, session=None,
-                            max_points=PROMETHEUS_MAX_POINTS, eng: Engine | None = None, tokenizer="auto"):
+                            max_points=PROMETHEUS_MAX_POINTS, eng: Engine | None = None, tokenizer="auto",
+                            group_keys=("__name__",)):
     """The range counterpart of ``fetch_gpu_metrics`` (app.py:153-227): the same host lookup and metric
     selector, sent to ``/api/v1/query_range`` in sub-ranges of at most ``max_points`` steps (Prometheus'
     limit per series), merged per label set and aggregated on the GPU.  Returns ``(tidy, summary)`` as
@@ -323,7 +353,8 @@ def fetch_gpu_metrics_range(start_s, end_s, step_s, window_s, lookback_s=DEFAULT
             chunks.append((tok.labels(), ts, val, tok.series_off))
         labels, ts, val, off = merge_range_chunks(eng, chunks) if len(chunks) != 1 else chunks[0]
         return _aggregate_series(eng, labels, ts, val, off, int(round(start_s * 1000)), int(round(step_s * 1000)), n_steps,
-                                 int(round(window_s * 1000)), int(round(lookback_s * 1000)), quantiles, as_frame)
+                                 int(round(window_s * 1000)), int(round(lookback_s * 1000)), quantiles, as_frame,
+                                 group_keys)
     except Exception as e:  # noqa: BLE001  -- the reference swallows everything (app.py:225-227)
         _report(f"Error fetching GPU metrics: {str(e)}")
         return None, None

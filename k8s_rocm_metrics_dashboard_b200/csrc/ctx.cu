@@ -22,6 +22,15 @@ int pmx_cuda_fail(cudaError_t e, const char* what) {
 
 void* pmx_scratch(pmx_ctx* ctx, int slot, size_t bytes) {
   if (bytes <= ctx->scratch_bytes[slot]) return ctx->scratch[slot];
+  // the block belongs to the ctx's device whatever device the caller has current; a caller on
+  // another device gets its launch refused below instead of scratch on the wrong GPU
+  int cur = -1;
+  cudaGetDevice(&cur);
+  if (cur != ctx->device) {
+    pmx_fail(PMX_E_INVALID, "ctx belongs to device %d but device %d is current: make the ctx's device current "
+             "(cudaSetDevice / torch.cuda.device) around calls that use it", ctx->device, cur);
+    return nullptr;
+  }
   // cudaFree synchronises the device, so work still using the old block has finished.
   if (ctx->scratch[slot]) cudaFree(ctx->scratch[slot]);
   ctx->scratch[slot] = nullptr;
@@ -48,9 +57,8 @@ int pmx_ctx_create(int device, pmx_ctx** out) {
     return pmx_fail(PMX_E_CUDA, "pmx_ctx_create: no CUDA device available (%s); this engine has no CPU path",
                     e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
   if (device < 0 || device >= n) return pmx_fail(PMX_E_INVALID, "pmx_ctx_create: device %d out of range [0,%d)", device, n);
-  PMX_CUDA(cudaSetDevice(device));
   cudaDeviceProp prop;
-  PMX_CUDA(cudaGetDeviceProperties(&prop, device));
+  PMX_CUDA(cudaGetDeviceProperties(&prop, device));        // (does not change the caller's current device)
   if (prop.major < 10)
     return pmx_fail(PMX_E_CUDA, "pmx_ctx_create: device %d is sm_%d%d; libpmx is built for sm_100a only", device, prop.major, prop.minor);
   pmx_ctx* c = new (std::nothrow) pmx_ctx();

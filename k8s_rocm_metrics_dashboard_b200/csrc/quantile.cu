@@ -854,9 +854,7 @@ int pmx_quantile_hist_lp(pmx_ctx* ctx, const double* d_x, int64_t n_series, int6
   if (!d_row_order) n_rows = n_series;
   PMX_REQUIRE(n_rows >= 0 && n_rows <= n_series, "n_rows out of range");
   if (n_rows == 0) return PMX_OK;
-  static int cta_mul = 0;
-  if (!cta_mul) { const char* e = getenv("PMX_HIST_CTAS_MUL"); cta_mul = e && atoi(e) > 0 ? atoi(e) : 16; }
-  int64_t want_ctas = (int64_t)ctx->sm_count * cta_mul;
+  int64_t want_ctas = (int64_t)ctx->sm_count * 16;         // measured: fewer, longer CTAs are slower
   int64_t rows = (n_rows + want_ctas - 1) / want_ctas;
   if (rows < 1) rows = 1;
   const int64_t grid = (n_rows + rows - 1) / rows;

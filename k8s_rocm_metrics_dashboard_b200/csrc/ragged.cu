@@ -35,7 +35,7 @@ ragged_window_kernel(const RParams p) {
         if (u != u) continue;
         ++wcn;
         if (pmx_isfinite(u)) { ws += u; wmn = fmin(wmn, u); wmx = fmax(wmx, u); ++wcf; }
-        if (cnt > 0) { const bool reset = u < lv; rs += reset ? lv : 0.0; nres += reset ? 1 : 0; }
+        if (cnt > 0) { const bool reset = u < lv; rs += reset ? u : u - lv; nres += reset ? 1 : 0; }   // sum of deltas
         else { fv = u; ft = t[k]; }
         lv = u; lt = t[k]; ++cnt;
       }
@@ -50,7 +50,7 @@ ragged_window_kernel(const RParams p) {
       if (do_rate) {
         double inc = pmx_nan(), rate = pmx_nan();
         if (cnt >= 2) {
-          inc = (lv - fv) + rs;
+          inc = rs;
           const double dt = (double)(lt - ft) / 1000.0;
           rate = dt != 0.0 ? inc / dt : pmx_nan();
           if (p.rate_mode == 1 && dt != 0.0)                 // window (ti - W, ti]
@@ -67,10 +67,8 @@ ragged_window_kernel(const RParams p) {
 
 int launch(pmx_ctx* ctx, const RParams& p, cudaStream_t st) {
   if (p.n_series == 0) return PMX_OK;
-  static int direct_only = -1;                            // PMX_RAGGED_DIRECT=1 keeps the first-version kernel
-  if (direct_only < 0) { const char* e = getenv("PMX_RAGGED_DIRECT"); direct_only = (e && atoi(e)) ? 1 : 0; }
-  if (!direct_only) {
-    const int rc = pmxr::launch_ragged_fast(ctx, p, st);
+  {
+    const int rc = pmxr::launch_ragged_fast(ctx, p, st);   // the tiled kernel when it applies
     if (rc != 1) return rc;
   }
   int64_t blocks = (p.n_series + 7) / 8;                 // 8 warps per CTA

@@ -222,9 +222,15 @@ __global__ void __launch_bounds__(TT)
 tokd_emit_kernel(const uint8_t* __restrict__ body, uint64_t len, const ChunkBase* __restrict__ bases,
                  uint32_t* __restrict__ ts_off, uint32_t* __restrict__ val_off,
                  int64_t* __restrict__ series_off, uint32_t* __restrict__ metric_off,
-                 uint32_t* __restrict__ metric_len, int64_t* __restrict__ status) {
+                 uint32_t* __restrict__ metric_len, int64_t cap_samples, int64_t cap_series,
+                 int64_t* __restrict__ status) {
   __shared__ unsigned s_warp[TT / 32];
-  if (status[ST_ERROR] != 0) return;                        // the scan already refused the body
+  __shared__ int s_refused;
+  // The scan may have refused the body, and other CTAs of this kernel may report an error while
+  // this one starts: one thread looks, everybody leaves together (the scans below need all warps).
+  if (threadIdx.x == 0) s_refused = status[ST_ERROR] != 0;
+  __syncthreads();
+  if (s_refused) return;
   const uint64_t c0 = (uint64_t)blockIdx.x * CHUNK;
   const ChunkBase cb = bases[blockIdx.x];
   unsigned run = cb.in_string;
@@ -264,7 +270,7 @@ tokd_emit_kernel(const uint8_t* __restrict__ body, uint64_t len, const ChunkBase
         uint64_t e = p + 2;
         while (e < len && e < p + 48 && body[e] != ',') ++e;
         if (e + 1 >= len || body[e] != ',' || body[e + 1] != '"') { report(status, ERR_SAMPLE, p); }
-        else { ts_off[si] = (uint32_t)(p + 1); val_off[si] = (uint32_t)(e + 2); }
+        else if (si >= 0 && si < cap_samples) { ts_off[si] = (uint32_t)(p + 1); val_off[si] = (uint32_t)(e + 2); }
         ++si;
       } else {
         // {"metric":{...},...} : the label object begins 10 bytes in and ends at the first '}'
@@ -280,9 +286,11 @@ tokd_emit_kernel(const uint8_t* __restrict__ body, uint64_t len, const ChunkBase
           ++e;
         }
         if (e >= len) report(status, ERR_LABELS, p);
-        series_off[ri] = si;
-        metric_off[ri] = (uint32_t)m0;
-        metric_len[ri] = (uint32_t)(e - m0 + 1);
+        if (ri >= 0 && ri < cap_series) {                   // the counts were checked against the capacities; a
+          series_off[ri] = si;                              // body that changes under the kernel must still not
+          metric_off[ri] = (uint32_t)m0;                    // write past the arrays
+          metric_len[ri] = (uint32_t)(e - m0 + 1);
+        }
         ++ri;
       }
     }
@@ -317,7 +325,7 @@ int pmx_tokenize_device(pmx_ctx* ctx, const uint8_t* d_body, uint64_t len,
   tokd_scan_kernel<<<1, 1024, 0, st>>>(d_body, len, sums, bases, n_chunks, cap_samples, cap_series, d_series_off, d_status);
   PMX_LAUNCH_CHECK();
   tokd_emit_kernel<<<(unsigned)n_chunks, TT, 0, st>>>(d_body, len, bases, d_ts_off, d_val_off, d_series_off, d_metric_off,
-                                                    d_metric_len, d_status);
+                                                    d_metric_len, cap_samples, cap_series, d_status);
   PMX_LAUNCH_CHECK();
   return PMX_OK;
 }

@@ -94,7 +94,9 @@ __device__ __forceinline__ void warp_store(T* wbuf, const T (&v)[E], T* __restri
   __syncwarp();
 }
 
-// ordered monoid of the rate computation over a run of grid points
+// ordered monoid of the rate computation over a run of grid points.  rs = sum of the per-sample
+// deltas x_i - x_{i-1} (x_i itself after a drop) between the run's first and last sample: the
+// telescoped form of (last - first) + pre-reset values, without its cancellation after a reset
 struct RateAgg {
   int cnt, nres, fpos, lpos;
   double fv, lv, rs;
@@ -108,14 +110,14 @@ __device__ __forceinline__ RateAgg rate_combine(const RateAgg& A, const RateAgg&
   C.cnt = A.cnt + B.cnt;
   C.nres = A.nres + B.nres + (reset ? 1 : 0);
   C.fpos = A.fpos; C.fv = A.fv; C.lpos = B.lpos; C.lv = B.lv;
-  C.rs = A.rs + B.rs + (reset ? A.lv : 0.0);
+  C.rs = A.rs + B.rs + (reset ? B.fv : B.fv - A.lv);
   return C;
 }
 __device__ __forceinline__ void rate_append(RateAgg& P, double v, int pos) {
   if (pmx_isnan(v)) return;
   if (P.cnt > 0) {
     const bool reset = v < P.lv;
-    P.rs += reset ? P.lv : 0.0;
+    P.rs += reset ? v : v - P.lv;
     P.nres += reset ? 1 : 0;
   } else { P.fv = v; P.fpos = pos; }
   P.lv = v; P.lpos = pos; P.cnt++;
@@ -317,7 +319,7 @@ window_kernel(const WinParams p) {
         for (int r = E - 1; r >= 0; --r) {
           const double v = a[r];
           if (!pmx_isnan(v)) {
-            if (cnt > 0) { const bool reset = fv < v; rs += reset ? v : 0.0; nres += reset ? 1 : 0; }
+            if (cnt > 0) { const bool reset = fv < v; rs += reset ? fv : fv - v; nres += reset ? 1 : 0; }
             else { lv = v; lpos = r; }
             fv = v; fpos = r; cnt++;
           }
@@ -372,7 +374,7 @@ window_kernel(const WinParams p) {
           }
           double inc = pmx_nan(), rate = pmx_nan();
           if (W.cnt >= 2) {
-            inc = (W.lv - W.fv) + W.rs;
+            inc = W.rs;
             const double dt = (double)((int64_t)(W.lpos - W.fpos) * p.step_ms) / 1000.0;
             rate = inc / dt;
             if (p.rate_mode == 1) {
@@ -423,7 +425,7 @@ window_naive_kernel(const WinParams p) {
     if (p.o_cnt) p.o_cnt[o] = wcn;
     double inc = pmx_nan(), rate = pmx_nan();
     if (W.cnt >= 2) {
-      inc = (W.lv - W.fv) + W.rs;
+      inc = W.rs;
       const double dt = (double)((int64_t)(W.lpos - W.fpos) * p.step_ms) / 1000.0;
       rate = inc / dt;
       if (p.rate_mode == 1) {                              // positions are relative to lo; window (j - w, j]
@@ -473,14 +475,7 @@ int dispatch_window(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
 }  // namespace
 
 namespace pmxw {
-int window_block_threads() {
-  static int nt = 0;
-  if (!nt) {
-    const char* e = getenv("PMX_WINDOW_THREADS");
-    nt = (e && atoi(e) == 256) ? 256 : 128;
-  }
-  return nt;
-}
+int window_block_threads() { return 128; }                 // (256-thread CTAs: 2 per SM, measured slower)
 }  // namespace pmxw
 
 extern "C" {

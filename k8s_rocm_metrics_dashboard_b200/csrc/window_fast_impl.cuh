@@ -655,9 +655,9 @@ int launch_fast(const pmx_ctx* ctx, WinParams p, cudaStream_t st) {
   using TL = FTile<NT>;
   const int out_per_tile = (TL::NE - (p.w - 1) - 3) & ~3;
   const int64_t tiles = (p.n_steps + out_per_tile - 1) / out_per_tile;
-  static int tmul = 0;
-  if (!tmul) { const char* e = getenv("PMX_FAST_TARGET_MUL"); tmul = e ? atoi(e) : 16; }
-  const int64_t target = (int64_t)ctx->sm_count * tmul;
+  // CTAs wanted: 16 per SM.  Measured on config 2 (6144 series): more, shorter CTAs are slower (every
+  // CTA pays ~2 us of table set-up and cursor search: 0.523 / 0.533 / 0.543 / 0.612 ms at 16 / 64 / 128 / 256)
+  const int64_t target = (int64_t)ctx->sm_count * 16;
   int64_t chunks = (target + p.n_series - 1) / p.n_series;
   if (chunks > tiles) chunks = tiles;
   if (chunks < 1) chunks = 1;

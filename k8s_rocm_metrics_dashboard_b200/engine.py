@@ -225,7 +225,9 @@ class Engine:
             end = o
             while end < len(tok.flat) and tok.flat[end] != 0x22:
                 end += 1
-            raise ValueError(f"could not convert string to float: {bytes(tok.flat[o:end]).decode('utf-8', 'replace')!r}")
+            err = ValueError(f"could not convert string to float: {bytes(tok.flat[o:end]).decode('utf-8', 'replace')!r}")
+            err.sample_index = int(b[0])
+            raise err
         if want_ts and b[1] != _abi.INT64_MAX:
             raise ValueError(f"malformed timestamp in sample {b[1]}")
         return ts, val
@@ -249,7 +251,9 @@ class Engine:
         if b[0] != _abi.INT64_MAX:
             o = int(tok.d_val_off[b[0]].item()) & 0xffffffff
             end = tok.body.find(b'"', o)
-            raise ValueError(f"could not convert string to float: {tok.body[o:end].decode('utf-8', 'replace')!r}")
+            err = ValueError(f"could not convert string to float: {tok.body[o:end].decode('utf-8', 'replace')!r}")
+            err.sample_index = int(b[0])
+            raise err
         if want_ts and b[1] != _abi.INT64_MAX:
             raise ValueError(f"malformed timestamp in sample {b[1]}")
         return ts, val
@@ -265,6 +269,23 @@ class Engine:
                                       n_steps, lookback_ms, self._ptr(out), self._ptr(idx), self._stream()))
         self.launches += 1
         return out, idx
+
+    def bucket(self, ts, val, off, start_ms, step_ms, n_steps):
+        """X3, second form: ``resample('<step>')`` bins [t, t+step) labelled left -> (last, mean, count)
+        of the non-NaN samples of every bin, [S, n_steps] each."""
+        t = self.torch
+        ts, val, off = self._dev(ts, t.int64), self._dev(val, t.float64), self._dev(off, t.int64)
+        S = off.numel() - 1
+        last, mean = self._empty((S, n_steps), t.float64), self._empty((S, n_steps), t.float64)
+        cnt = self._empty((S, n_steps), t.int32)
+        for a in range(0, S, 65535):                                  # grid.y limit of the kernel
+            b = min(S, a + 65535)
+            _abi.check(self.lib.pmx_bucket(self.ctx, self._ptr(ts), self._ptr(val), C.c_void_p(off.data_ptr() + 8 * a), b - a,
+                                           start_ms, step_ms, n_steps, C.c_void_p(last.data_ptr() + 8 * a * n_steps),
+                                           C.c_void_p(mean.data_ptr() + 8 * a * n_steps),
+                                           C.c_void_p(cnt.data_ptr() + 4 * a * n_steps), self._stream()))
+            self.launches += 1
+        return last, mean, cnt
 
     # ------------------------------------------------------------------ K3
     def rolling(self, x, window_steps, min_periods=1, want_count=True):
@@ -323,8 +344,21 @@ class Engine:
         """X3+X4+X5 in one kernel.  ``out`` may hold preallocated [S, n_steps] float64 tensors
         (keys aligned, roll_min, roll_max, roll_mean, rate) to avoid allocation in a timed loop."""
         t = self.torch
+        if window_steps < 1:
+            raise ValueError(f"window_steps must be >= 1 (got {window_steps}: a window shorter than the step)")
         ts, val, off = self._dev(ts, t.int64), self._dev(val, t.float64), self._dev(off, t.int64)
         S = off.numel() - 1
+        if window_steps - 1 > _abi.FUSED_MAX_WINDOW_STEPS - 1:
+            # longer than the fused kernel's tile allows (e.g. 1 h at a 5 s step): the three kernels
+            al, _ = self.align(ts, val, off, start_ms, step_ms, n_steps, lookback_ms, want_idx=False)
+            mn, mx, mean, _ = self.rolling(al, window_steps, min_periods, want_count=False)
+            _, rt, _ = self.rate(al, window_steps, step_ms, want_resets=False)
+            res = {"aligned": al, "roll_min": mn, "roll_max": mx, "roll_mean": mean, "rate": rt}
+            if out is not None:
+                for k, v in res.items():
+                    out[k].copy_(v)
+                return out
+            return res
         if out is None:
             out = {k: self._empty((S, n_steps), t.float64)
                    for k in ("aligned", "roll_min", "roll_max", "roll_mean", "rate")}

@@ -109,11 +109,7 @@ class ShardedEngine:
 
     @staticmethod
     def _qsummary(summary):
-        """(count, min, max) of the combined group summary for the quantile start, or None when
-        switched off (PMX_QUANTILE_SUMMARY=0: the selection then begins with pass 0)."""
-        import os
-        if os.environ.get("PMX_QUANTILE_SUMMARY", "1") == "0":
-            return None
+        """(count, min, max) of the combined group summary: where the quantile selection starts."""
         return summary[1], summary[2], summary[3]
 
     def aggregate_step(self, ts, val, off, start_ms, step_ms, n_steps, window_steps, seg, n_seg, perm_goff,

@@ -237,7 +237,8 @@ def _rate_series(k, x, t_of, lo_of, T_out, mode=0, win_end_ms=None, range_ms=Non
     """Shared body: k = positions of non-NaN samples, x their values.
 
     For output j the window holds the non-NaN samples with position in [lo_of(j), j].
-    increase = (x_last - x_first) + sum_{resets m>first} x_{m-1}   
+    increase = (x_last - x_first) + sum_{resets m>first} x_{m-1}   (SURVEY X5), evaluated exactly and
+    rounded once
     mode 0: rate = increase / ((t_last - t_first)/1000)
     mode 1: Prometheus extrapolation over the window (win_end_ms(j) - range_ms, win_end_ms(j)]
     """
@@ -257,7 +258,12 @@ def _rate_series(k, x, t_of, lo_of, T_out, mode=0, win_end_ms=None, range_ms=Non
         r = math.fsum(rterm[p + 1:q + 1])
         nres[j] = int(reset[p + 1:q + 1].sum())
         with np.errstate(invalid="ignore", over="ignore", divide="ignore"):
-            inc[j] = (x[q] - x[p]) + r
+            # the formula's value rounded ONCE (after a reset "x_last - x_first" alone is a huge
+            # negative number whose rounding error would be the oracle's, not the kernel's)
+            if math.isfinite(x[q]) and math.isfinite(x[p]) and math.isfinite(r):
+                inc[j] = math.fsum((x[q], -x[p], *rterm[p + 1:q + 1]))
+            else:
+                inc[j] = (x[q] - x[p]) + r
             dt = (t_of(k[q]) - t_of(k[p])) / 1000.0
             rate[j] = inc[j] / dt if dt != 0 else np.nan
             if mode == 1 and dt != 0:

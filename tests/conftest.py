@@ -12,6 +12,15 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
 
 
+def pytest_terminal_summary(terminalreporter):
+    """Worst observed error of every tolerance comparison, relative to max(|oracle|, scale)."""
+    from tests.util import WORST
+    if WORST:
+        terminalreporter.write_line("parity: worst |got - oracle| / max(|oracle|, scale) per comparison (bar 1e-12)")
+        for what, w in sorted(WORST.items()):
+            terminalreporter.write_line(f"  {what:44s} {w:.3e}")
+
+
 @pytest.fixture(scope="session")
 def eng():
     import torch

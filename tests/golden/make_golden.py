@@ -159,6 +159,13 @@ def instant_golden():
     cases.append(instant_case(mod, errors, "missing_cell", lab2, val2))
     body = synth.to_vector_json(lab, synth.START_MS, values).replace(b'"' + synth.format_value(values[4]).encode() + b'"', b'"12abc"', 1)
     cases.append(instant_case(mod, errors, "malformed_value", lab, values, body=body))
+    # two failures in one body: the reference reports the one its series walk meets first
+    lab2 = [dict(l) for l in lab]; del lab2[2]["gpu_id"]
+    body = synth.to_vector_json(lab2, synth.START_MS, values).replace(b'"' + synth.format_value(values[9]).encode() + b'"', b'"9x"', 1)
+    cases.append(instant_case(mod, errors, "missing_label_before_malformed_value", lab2, values, body=body))
+    lab2 = [dict(l) for l in lab]; del lab2[9]["__name__"]
+    body = synth.to_vector_json(lab2, synth.START_MS, values).replace(b'"' + synth.format_value(values[2]).encode() + b'"', b'"2x"', 1)
+    cases.append(instant_case(mod, errors, "malformed_value_before_missing_label", lab2, values, body=body))
     cases.append(instant_case(mod, errors, "empty_result", [], []))
     body = synth.to_vector_json(lab, synth.START_MS, values).replace(b'"' + synth.format_value(values[0]).encode() + b'"', b'" 4_2.5e0\\t"', 1)
     cases.append(instant_case(mod, errors, "python_float_grammar", lab, values, body=body))

@@ -72,7 +72,7 @@ def test_fetch_gpu_metrics_contract(eng, golden, monkeypatch):
         return Resp(bodies["kube"] if params["query"].startswith("kube_pod_info") else bodies["gpu"])
 
     monkeypatch.setitem(sys.modules, "requests", types.SimpleNamespace(get=fake_get))
-    monkeypatch.setattr(adapter, "_engine", eng)
+    monkeypatch.setattr(adapter._local, "engine", eng, raising=False)
     piv, stats = adapter.fetch_gpu_metrics()
     assert piv is not None and list(piv.index) == case["pivot"]["index"]
     assert len(calls) == 2 and 'instance=~"10.0.0.1:.+"' in calls[1] and "amd_gpu_total_vram" in calls[1]
@@ -129,3 +129,67 @@ def test_aggregate_range_arrow_table_equals_the_frame(eng):
             assert sb[c].tolist() == summary[c].tolist()
         else:
             np.testing.assert_array_equal(sb[c].to_numpy(), summary[c].to_numpy())
+
+
+def test_four_sessions_refresh_concurrently(golden):
+    """Streamlit runs every browser session on its own script thread and each loops on
+    fetch_gpu_metrics (app.py:326-331): four threads call the drop-in at the same time on different
+    bodies, each through the engine of ITS thread (adapter.engine()), many times over; every
+    result must equal what the unmodified reference returned for that body."""
+    import threading
+    cases = [c for c in golden["cases"] if "error" not in c][:4]
+    errors, engines = [], set()
+
+    def session(case):
+        try:
+            engines.add(id(adapter.engine()))
+            for _ in range(25):
+                piv, stats = adapter.aggregate_instant(case["body"].encode())
+                assert list(piv.index) == case["pivot"]["index"]
+                for gid, rowd in case["pivot"]["cells"].items():
+                    for c, v in rowd.items():
+                        cell = piv.loc[gid, c]
+                        assert zero_eq(fbits(cell), v) if isinstance(cell, float) else cell == v, (case["name"], gid, c)
+                for k in ("mean", "max", "min"):
+                    for c, v in case["stats"][k].items():
+                        assert zero_eq(fbits(stats[k][c]), v), (case["name"], k, c)
+                avg = adapter.selected_averages(piv, case["selected"])
+                for c, v in case["averages"].items():
+                    assert zero_eq(fbits(avg[c]), v), (case["name"], "avg", c)
+        except Exception as e:  # noqa: BLE001
+            errors.append(f"{case['name']}: {type(e).__name__}: {e}")
+
+    threads = [threading.Thread(target=session, args=(c,)) for c in cases]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errors, errors
+    assert len(engines) == len(cases), "every session thread must have its own engine (pmx_ctx)"
+
+
+def test_aggregate_range_group_keys_per_node_and_per_card(eng):
+    """SURVEY X6 on the range path: groupby(['instance','gpu_id','__name__']) and per node -- what
+    app.py:335-345 does for the selected cards of an instant vector -- against pandas' groupby."""
+    import numpy as np
+    import pandas as pd
+    from oracle import prom_oracle as O
+    from tests.util import assert_bits_equal
+    d = synth.dense(3, 4, 6, 150, seed=21, nan_frac=0.03)
+    body = synth.to_matrix_json(d["labels"], d["ts"], d["val"], d["off"])
+    al, _ = O.align(d["ts"], d["val"], d["off"], d["start_ms"], d["step_ms"], 150)
+    for keys in (("instance", "gpu_id", "__name__"), ("instance", "__name__"), ("__name__",)):
+        _, summary = adapter.aggregate_range(body, d["start_ms"], d["step_ms"], 150, 900_000, eng=eng, group_keys=keys)
+        cols = {k: np.repeat([l[k] for l in d["labels"]], 150) for k in keys}
+        g = pd.DataFrame({**cols, "value": al.ravel()}).groupby(list(keys), sort=True)["value"]
+        agg = g.agg(["sum", "count", "min", "max", "mean"])
+        q = g.quantile([0.5, 0.95, 0.99]).unstack()
+        assert len(summary) == len(agg)
+        for i, k in enumerate(keys):
+            exp = [idx[i] if isinstance(idx, tuple) else idx for idx in agg.index]
+            assert list(summary["metric_name" if k == "__name__" else k]) == exp
+        assert np.array_equal(summary["count"].to_numpy(), agg["count"].to_numpy())
+        assert np.array_equal(summary["min"].to_numpy(), agg["min"].to_numpy())
+        assert np.array_equal(summary["max"].to_numpy(), agg["max"].to_numpy())
+        np.testing.assert_allclose(summary["mean"].to_numpy(), agg["mean"].to_numpy(), rtol=1e-12)
+        assert_bits_equal(summary[["p50", "p95", "p99"]].to_numpy(dtype=np.float64), q.to_numpy(), f"quantiles by {keys}")

@@ -85,6 +85,17 @@ def test_chunked_range_equals_one_body(eng):
                       ref[0].sort_values(["instance", "gpu_id", "metric_name", "ts"], kind="stable").reset_index(drop=True))
         _frames_equal(summary, ref[1], rtol=1e-12)     # a series first seen in a later chunk is summed last
     assert len(whole[0]) == len(ref[0])
+    # the chunked answer against the oracle on the same samples (series 3 starts late)
+    from oracle import prom_oracle as O
+    from tests.util import assert_bits_equal, assert_close
+    olabels, ots, oval, ooff = O.tokenize_matrix(fake.body(start_s - step_s, end_s))
+    oref = O.aggregate_range(ots, oval, ooff, d["start_ms"], d["step_ms"], 300, 900_000)
+    for s, lab in enumerate(olabels):
+        rows = tidy[(tidy["instance"] == lab["instance"]) & (tidy["gpu_id"] == lab["gpu_id"]) & (tidy["metric_name"] == lab["__name__"])]
+        assert_bits_equal(rows["value"].to_numpy(), oref["aligned"][s], "chunked aligned")
+        assert_close(rows["roll_mean"].to_numpy(), oref["roll_mean"][s], scale=O.rolling_scale(oref["aligned"][s:s + 1], 60)[0],
+                     what="chunked roll_mean")
+        assert_close(rows["rate"].to_numpy(), oref["rate"][s], rtol=1e-12, what="chunked rate")
 
 
 def test_range_traces_slice_the_frame_per_series(eng):

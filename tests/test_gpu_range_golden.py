@@ -104,3 +104,24 @@ def test_ragged_config5(eng, G):
     inc, rt, nr = eng.rate(al, w, step)
     assert np.array_equal(_np(nr), G["c5/grid_n_resets"])
     assert_close(_np(inc), G["c5/grid_increase"], scale=O.rate_scale(gal, w), rtol=1e-12)
+
+
+@pytest.mark.parametrize("name", ["c2", "c5"])
+def test_bucket_downsampling(eng, G, name):
+    start, step, T = (int(x) for x in G[f"{name}/bucket_params"])
+    last, mean, cnt = eng.bucket(G[f"{name}/ts"], G[f"{name}/val"], G[f"{name}/off"], start, step, T)
+    assert np.array_equal(_np(cnt), G[f"{name}/bucket_count"]), "resample().count"
+    assert_exact_or_nan(_np(last), G[f"{name}/bucket_last"], "resample().last")
+    assert_close(_np(mean), G[f"{name}/bucket_mean"], rtol=1e-12, what="resample().mean")
+
+
+def test_bucket_random_against_the_oracle(eng):
+    from k8s_rocm_metrics_dashboard_b200 import synth
+    d = synth.ragged(200, seed=9, mean_len=300, nan_frac=0.05, stale_frac=0.02, gap_frac=0.03)
+    t0 = int(d["ts"].min())
+    for start, step, T in ((t0 - 100_000, 60_000, 700), (t0 + 7, 15_000, 2000), (t0, 3_600_000, 5), (t0 + 10**9, 1000, 10)):
+        last, mean, cnt = eng.bucket(d["ts"], d["val"], d["off"], start, step, T)
+        ol, om, oc = O.bucket(d["ts"], d["val"], d["off"], start, step, T)
+        assert np.array_equal(_np(cnt), oc)
+        assert_exact_or_nan(_np(last), ol, "last")
+        assert_bits_equal(np.nan_to_num(_np(mean)), np.nan_to_num(om), "mean: the same sequential sum")

@@ -41,7 +41,7 @@ def _compare(got, ref, order, w, step_ms):
         assert_bits_equal(got[k], ref[k][order], k)
     # sums are formed from different tile positions in the two runs: 1e-12 of the window's magnitude
     assert_close(got["roll_mean"], ref["roll_mean"][order], scale=O.rolling_scale(al, w), what="roll_mean")
-    assert_close(got["rate"], ref["rate"][order], scale=O.rate_scale(al, w) * w * 1000.0 / step_ms, what="rate")
+    assert_close(got["rate"], ref["rate"][order], rtol=1e-12, what="cache rate")
 
 
 @pytest.mark.parametrize("w", [20, 60])
@@ -68,6 +68,9 @@ def test_incremental_refresh_equals_one_pass(eng, w):
     got = {k: np.concatenate(v, axis=1) for k, v in cols.items()}
     assert got["aligned"].shape == (24, 400)
     _compare(got, ref, order, w, step)
+    # ... and against the oracle itself, not only against the one-pass kernel
+    oref = O.aggregate_range(d["ts"], d["val"], d["off"], start, step, n_steps, w * step)
+    _compare(got, {k: oref[k] for k in KEYS}, order, w, step)
 
 
 def test_series_that_start_later_and_device_tokenizer(eng):

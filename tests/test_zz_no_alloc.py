@@ -50,6 +50,12 @@ def test_noalloc_matches_group_reduce_on_two_calls_in_a_row(eng):
         assert np.array_equal(got[1], ref[1])                  # counts
         _same(got[2], ref[2], 0.0); _same(got[3], ref[3], 0.0)  # min / max exact
         _same(got[0], ref[0], 1e-12); _same(got[4], ref[4], 1e-12)
+        # ... and against the oracle, not only against the sibling entry point
+        from oracle import prom_oracle as O
+        osm, ocnt, omn, omx, omean = O.group_reduce(x, gid, G)
+        assert np.array_equal(got[1], ocnt)
+        _same(got[2], omn, 0.0); _same(got[3], omx, 0.0)
+        _same(got[0], osm, 1e-12); _same(got[4], omean, 1e-12)
 
 
 def test_noalloc_rejects_more_series_than_its_fixed_array(eng):
