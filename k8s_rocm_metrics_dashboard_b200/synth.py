@@ -156,6 +156,39 @@ def ragged(n_series, seed=0, mean_len=400, max_len=5760, nan_frac=1e-3, stale_fr
     return {"labels": labels, "ts": ts, "val": val, "off": off}
 
 
+def ragged_device(n_series, seed=0, mean_len=400, max_len=5760, nan_frac=1e-3, stale_frac=5e-4,
+                  gap_frac=0.01, device="cuda"):
+    """Config 5 at its stated size (1 000 000 series, ~400 M samples) generated on the GPU with
+    torch (plumbing only; seeded): the distributions of ``ragged``.  Returns (ts int64[N],
+    val float64[N], off int64[S+1]) on the device."""
+    import math
+    import torch
+    g = torch.Generator(device=device); g.manual_seed(seed)
+    u = torch.rand(n_series, generator=g, device=device, dtype=torch.float64).clamp_(1e-12, 1.0)
+    lens = torch.floor(torch.log(u) / math.log1p(-1.0 / mean_len)).to(torch.int64) + 2      # 1 + Geometric(1/mean)
+    lens.clamp_(1, max_len)
+    off = torch.zeros(n_series + 1, dtype=torch.int64, device=device)
+    torch.cumsum(lens, 0, out=off[1:])
+    N = int(off[-1])
+    gaps = STEP_MS + torch.randint(-2000, 2001, (N,), generator=g, device=device, dtype=torch.int64)
+    stretch = torch.rand(N, generator=g, device=device) < gap_frac
+    long = torch.randint(6 * 60_000, 30 * 60_000 + 1, (N,), generator=g, device=device, dtype=torch.int64)
+    gaps = torch.where(stretch, long, gaps)
+    del stretch, long
+    gaps[off[:-1]] = 0
+    csum = torch.cumsum(gaps, 0)
+    del gaps
+    start = START_MS + torch.randint(0, 3_600_000, (n_series,), generator=g, device=device, dtype=torch.int64)
+    ts = csum + torch.repeat_interleave(start - csum[off[:-1]], lens)
+    del csum
+    val = torch.round(torch.rand(N, generator=g, device=device, dtype=torch.float64) * 1e6) / 1e3
+    val = torch.where(torch.rand(N, generator=g, device=device) < nan_frac, torch.full_like(val, float("nan")), val)
+    stale = torch.rand(N, generator=g, device=device) < stale_frac
+    bits = val.view(torch.int64)
+    bits[stale] = STALE_NAN_BITS
+    return ts.contiguous(), val.contiguous(), off
+
+
 # ----------------------------------------------------------------------------- text
 def format_value(v):
     """Prometheus value text: shortest round-trip decimal, ``NaN``, ``+Inf``, ``-Inf``."""
