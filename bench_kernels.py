@@ -100,7 +100,7 @@ def main():
     del ts4, val4, off4
 
     # ---- K1 parse: config-1-shaped text, tiled to ~40 M samples
-    d1 = synth.dense(8, 8, 12, 2880, seed=3, nan_frac=1e-3, kinds="ttk")
+    d1 = synth.dense(16, 8, 12, 5760, seed=3, nan_frac=1e-3, kinds="ttk")      # 8.8 M samples, ~240 MB of text (> L2)
     t0 = time.perf_counter()
     body = synth.to_matrix_json(d1["labels"], d1["ts"], d1["val"], d1["off"])
     t_fmt = time.perf_counter() - t0
@@ -152,27 +152,27 @@ def main():
     st = lambda: C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
     def parse():
-        _abi.check(eng.lib.pmx_parse_f64(eng.ctx, p(text), text.numel(), p(voff), n1, p(pv), p(bad), st()))
-        _abi.check(eng.lib.pmx_parse_ts_ms(eng.ctx, p(text), text.numel(), p(toff), n1, p(pt), C.c_void_p(bad.data_ptr() + 8), st()))
+        _abi.check(eng.lib.pmx_parse_samples(eng.ctx, p(text), text.numel(), p(toff), p(voff), n1, p(pt), p(pv), p(bad), st()))
     lv = float(np.mean([len(synth.format_value(v)) for v in d1["val"][:20000]]))
     lt = float(np.mean([len(synth.format_ts(v)) for v in d1["ts"][:20000]]))
     rec("K1 parse value+timestamp", n1, lv + lt + 24, timeit(parse), f"mean token bytes {lv:.1f}+{lt:.1f}; working set {len(body) / 1e6:.0f} MB")
     del text, voff, toff, pv, pt
 
-    # ---- config 5: ragged series (scaled: 200 k series, ~80 M samples)
-    d5 = synth.ragged(200_000, seed=5)
-    r_ts, r_val, r_off = (torch.as_tensor(d5[k], device=dev) for k in ("ts", "val", "off"))
-    n5 = int(d5["off"][-1])
-    rec("ragged rolling (cfg5, 200k series)", n5, 44, timeit(lambda: eng.rolling_ragged(r_ts, r_val, r_off, 900_000), iters=3, warm=1))
-    rec("ragged rate (cfg5, 200k series)", n5, 36, timeit(lambda: eng.rate_ragged(r_ts, r_val, r_off, 900_000, want_resets=False), iters=3, warm=1))
-    t0i = int(d5["ts"].min())
-    outr = None
-    rec("fused on ragged cfg5 -> 15 s grid", 200_000 * 640, 56,
-        timeit(lambda: eng.fused(r_ts, r_val, r_off, t0i, 15_000, 640, 60), iters=3, warm=1), "per GRID point; 640 steps")
-    del r_ts, r_val, r_off, outr
+    # ---- config 5 at its stated size: 1 000 000 ragged series (~400 M samples), generated on the device
+    del ts, val, off, out, al
+    torch.cuda.empty_cache()
+    r_ts, r_val, r_off = synth.ragged_device(1_000_000, seed=5, device=dev)
+    n5 = int(r_off[-1])
+    rec("ragged rolling (cfg5, 1M series)", n5, 44, timeit(lambda: eng.rolling_ragged(r_ts, r_val, r_off, 900_000), iters=3, warm=1))
+    rec("ragged rate (cfg5, 1M series)", n5, 36, timeit(lambda: eng.rate_ragged(r_ts, r_val, r_off, 900_000, want_resets=False), iters=3, warm=1))
+    t0i = int(r_ts.min())
+    rec("fused on ragged cfg5 -> 15 s grid", 1_000_000 * 480, 56,
+        timeit(lambda: eng.fused(r_ts, r_val, r_off, t0i, 15_000, 480, 60), iters=3, warm=1), "per GRID point; 480 steps (2 h)")
+    rec("bucket 15 s -> 1 min (cfg5)", n5, 16 + 20 * 480 * 1_000_000 / 4 / n5, timeit(lambda: eng.bucket(r_ts, r_val, r_off, t0i, 60_000, 120), iters=3, warm=1),
+        "resample().last/mean/count; 120 one-minute bins per series")
+    del r_ts, r_val, r_off
 
     if args.big:
-        del ts, val, off, out, al
         torch.cuda.empty_cache()
         S3, T3 = 16384, 40320
         ts, val, off = synth.dense_device(S3, T3, 16, seed=4, device=dev)

@@ -106,7 +106,9 @@ int pmx_tokenize_device(pmx_ctx* ctx, const uint8_t* d_body, uint64_t len,
  * text -> binary64, correctly rounded, bit-exact with CPython float() for ASCII input (sign,
  * digits with single underscores, '.', exponent, inf/infinity/nan in any case, surrounding
  * ASCII whitespace).  d_first_bad (device int64, required) receives the smallest index of a
- * malformed token or INT64_MAX; the adapter turns it into ValueError. */
+ * malformed token, or a number >= n (0x7f7f7f7f7f7f7f7f) when there is none; the adapter turns an
+ * index into ValueError.  d_text should be 16-byte aligned (then the common token shapes are
+ * decoded from 16-byte loads; any alignment is accepted). */
 int pmx_parse_f64(pmx_ctx* ctx, const uint8_t* d_text, uint64_t text_len,
                   const uint32_t* d_val_off, int64_t n, double* d_out,
                   int64_t* d_first_bad, pmx_stream stream);
@@ -114,6 +116,12 @@ int pmx_parse_f64(pmx_ctx* ctx, const uint8_t* d_text, uint64_t text_len,
 int pmx_parse_ts_ms(pmx_ctx* ctx, const uint8_t* d_text, uint64_t text_len,
                     const uint32_t* d_ts_off, int64_t n, int64_t* d_out,
                     int64_t* d_first_bad, pmx_stream stream);
+/* Both tokens of every sample in one launch (what a matrix body needs: app.py:188 reads the value,
+ * the range path also the timestamp).  d_first_bad: int64[2], [0] for values, [1] for timestamps,
+ * as above.  Either output (with its offsets) may be NULL. */
+int pmx_parse_samples(pmx_ctx* ctx, const uint8_t* d_text, uint64_t text_len,
+                      const uint32_t* d_ts_off, const uint32_t* d_val_off, int64_t n,
+                      int64_t* d_out_ts, double* d_out_val, int64_t* d_first_bad, pmx_stream stream);
 
 /* ---- X3  step-aligned resample (K2).  grid g_j = start + j*step.  For each series and j:
  * idx = (last sample with ts <= g_j); valid iff it exists, g_j - ts[idx] < lookback and the

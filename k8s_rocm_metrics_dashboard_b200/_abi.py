@@ -51,6 +51,7 @@ SIGNATURES = {
     "pmx_tokenize_device": (_int, [_p, _p, _u64, _p, _p, _i64, _p, _p, _p, _i64, _p, _p]),
     "pmx_parse_f64": (_int, [_p, _p, _u64, _p, _i64, _p, _p, _p]),
     "pmx_parse_ts_ms": (_int, [_p, _p, _u64, _p, _i64, _p, _p, _p]),
+    "pmx_parse_samples": (_int, [_p, _p, _u64, _p, _p, _i64, _p, _p, _p, _p]),
     "pmx_align": (_int, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _p, _p, _p]),
     "pmx_bucket": (_int, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _p, _p, _p, _p]),
     "pmx_rolling": (_int, [_p, _p, _i64, _i64, _i64, _i64, _p, _p, _p, _p, _p]),

@@ -206,21 +206,10 @@ class Engine:
             warnings.simplefilter("ignore", UserWarning)
             text = t.from_numpy(tok.flat).to(self.device)
         n = tok.n_samples
-        val = self._empty((n,), t.float64)
-        bad = self._empty((2,), t.int64)
         voff = t.from_numpy(tok.val_off.view(np.int32)).to(self.device)
-        _abi.check(self.lib.pmx_parse_f64(self.ctx, self._ptr(text), text.numel(), self._ptr(voff), n,
-                                          self._ptr(val), self._ptr(bad[0:]), self._stream()))
-        self.launches += 2
-        ts = None
-        if want_ts:
-            ts = self._empty((n,), t.int64)
-            toff = t.from_numpy(tok.ts_off.view(np.int32)).to(self.device)
-            _abi.check(self.lib.pmx_parse_ts_ms(self.ctx, self._ptr(text), text.numel(), self._ptr(toff), n,
-                                                self._ptr(ts), self._ptr(bad[1:]), self._stream()))
-            self.launches += 2
-        b = bad.cpu().tolist()
-        if b[0] != _abi.INT64_MAX:
+        toff = t.from_numpy(tok.ts_off.view(np.int32)).to(self.device) if want_ts else None
+        ts, val, b = self._parse_launch(text, toff, voff, n, want_ts)
+        if b[0] < n:
             o = int(tok.val_off[b[0]])
             end = o
             while end < len(tok.flat) and tok.flat[end] != 0x22:
@@ -228,33 +217,32 @@ class Engine:
             err = ValueError(f"could not convert string to float: {bytes(tok.flat[o:end]).decode('utf-8', 'replace')!r}")
             err.sample_index = int(b[0])
             raise err
-        if want_ts and b[1] != _abi.INT64_MAX:
+        if want_ts and b[1] < n:
             raise ValueError(f"malformed timestamp in sample {b[1]}")
         return ts, val
 
-    def _parse_device(self, tok, want_ts):
+    def _parse_launch(self, text, toff, voff, n, want_ts):
+        """pmx_parse_samples: one launch for both tokens of every sample.  Returns (ts | None, val,
+        [first bad value index, first bad timestamp index]) -- an index >= n means none."""
         t = self.torch
-        n = tok.n_samples
         val = self._empty((n,), t.float64)
+        ts = self._empty((n,), t.int64) if want_ts else None
         bad = self._empty((2,), t.int64)
-        text = tok.d_text
-        _abi.check(self.lib.pmx_parse_f64(self.ctx, self._ptr(text), text.numel(), self._ptr(tok.d_val_off), n,
-                                          self._ptr(val), self._ptr(bad[0:]), self._stream()))
-        self.launches += 2
-        ts = None
-        if want_ts:
-            ts = self._empty((n,), t.int64)
-            _abi.check(self.lib.pmx_parse_ts_ms(self.ctx, self._ptr(text), text.numel(), self._ptr(tok.d_ts_off), n,
-                                                self._ptr(ts), self._ptr(bad[1:]), self._stream()))
-            self.launches += 2
-        b = bad.cpu().tolist()
-        if b[0] != _abi.INT64_MAX:
+        _abi.check(self.lib.pmx_parse_samples(self.ctx, self._ptr(text), text.numel(), self._ptr(toff), self._ptr(voff), n,
+                                              self._ptr(ts), self._ptr(val), self._ptr(bad), self._stream()))
+        self.launches += 1
+        return ts, val, bad.cpu().tolist()
+
+    def _parse_device(self, tok, want_ts):
+        n = tok.n_samples
+        ts, val, b = self._parse_launch(tok.d_text, tok.d_ts_off if want_ts else None, tok.d_val_off, n, want_ts)
+        if b[0] < n:
             o = int(tok.d_val_off[b[0]].item()) & 0xffffffff
             end = tok.body.find(b'"', o)
             err = ValueError(f"could not convert string to float: {tok.body[o:end].decode('utf-8', 'replace')!r}")
             err.sample_index = int(b[0])
             raise err
-        if want_ts and b[1] != _abi.INT64_MAX:
+        if want_ts and b[1] < n:
             raise ValueError(f"malformed timestamp in sample {b[1]}")
         return ts, val
 

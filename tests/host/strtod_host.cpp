@@ -16,3 +16,19 @@ extern "C" int host_parse_ts_ms(const uint8_t* p, int64_t len, int64_t* out) {
 extern "C" void host_parse_many(const uint8_t* buf, const int64_t* off, int64_t n, uint64_t* bits, int32_t* status) {
   for (int64_t i = 0; i < n; ++i) status[i] = pmx::parse_f64(buf + off[i], off[i + 1] - off[i], pmx_pow5_128, bits + i);
 }
+
+// the window form of the common case (csrc/strtod_fast.h): status 0 = decoded, 1 = left to the byte-wise path
+#include "../../k8s_rocm_metrics_dashboard_b200/csrc/strtod_fast.h"
+#include <string.h>
+extern "C" int host_fast_f64(const uint8_t* p, int64_t len, uint64_t* bits) {
+  uint64_t W[4] = {0, 0, 0, 0};
+  if (len >= 24) return pmx::FAST_FALLBACK;
+  memcpy(W, p, (size_t)len);
+  return pmx::fast_f64(W, (int)len, pmx_pow5_128, bits);
+}
+extern "C" int host_fast_ts_ms(const uint8_t* p, int64_t len, int64_t* out) {
+  uint64_t W[4] = {0, 0, 0, 0};
+  if (len >= 24) return pmx::FAST_FALLBACK;
+  memcpy(W, p, (size_t)len);
+  return pmx::fast_ts_ms(W, (int)len, out);
+}

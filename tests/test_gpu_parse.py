@@ -41,7 +41,7 @@ def test_float_golden_bit_exact(eng, golden_dir):
          if all(ord(c) < 128 for c in t)]
     good = [(t, e) for t, e in g if e != "ValueError"]
     got, first_bad = _parse_each(eng, [t for t, _ in good])
-    assert first_bad == (1 << 63) - 1
+    assert first_bad >= len(good)                              # no malformed token
     exp = np.array([int(e, 16) for _, e in good], dtype=np.uint64)
     bad = np.flatnonzero(got.view(np.uint64) != exp)
     assert len(bad) == 0, [good[i][0][:60] for i in bad[:5]]
@@ -68,7 +68,7 @@ def test_random_reprs_and_long_mantissas(eng):
         nd = rnd.choice([17, 19, 20, 30, 100, 400, 800])
         toks.append("".join(rnd.choice("0123456789") for _ in range(nd)) + "e%d" % rnd.randint(-340 - nd, 300 - nd))
     got, fb = _parse_each(eng, toks)
-    assert fb == (1 << 63) - 1
+    assert fb >= len(toks)
     exp = np.array([struct.unpack("<Q", struct.pack("<d", float(t)))[0] for t in toks], dtype=np.uint64)
     bad = np.flatnonzero(got.view(np.uint64) != exp)
     assert len(bad) == 0, [toks[i][:60] for i in bad[:5]]

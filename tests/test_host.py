@@ -212,3 +212,46 @@ def test_tokenizer_multithreaded_reports_errors_like_single_walk():
             tokenize(broken, threads=th)
     not_canonical = b' ' + body                                  # leading space: plain walk serves it
     assert tokenize(not_canonical, threads=8).n_samples == 192 * 400
+
+
+def test_fast_window_decode_on_host_matches_python_float(host_lib, golden_dir):
+    """csrc/strtod_fast.h (what K1 runs on [-]digits[.digits] tokens of at most 32 bytes): every token
+    it accepts must give float()'s bits / the exact milliseconds; everything else must be handed on."""
+    import random
+    from decimal import Decimal
+    lib = host_lib
+    lib.host_fast_f64.argtypes = [C.c_char_p, C.c_int64, C.POINTER(C.c_uint64)]
+    lib.host_fast_ts_ms.argtypes = [C.c_char_p, C.c_int64, C.POINTER(C.c_int64)]
+    rnd = random.Random(11)
+    toks = [t for t, _ in json.load(open(os.path.join(golden_dir, "float_golden.json"))) if all(ord(c) < 128 for c in t)]
+    for _ in range(60000):
+        k = rnd.random()
+        if k < 0.3:
+            toks.append(repr(round(rnd.uniform(0, 1000), 3)))
+        elif k < 0.5:
+            toks.append(repr(rnd.uniform(0, 1e9)))
+        elif k < 0.6:
+            toks.append(str(rnd.randrange(0, 10 ** rnd.randrange(1, 21))))
+        elif k < 0.75:
+            x = struct.unpack("<d", struct.pack("<Q", rnd.getrandbits(64)))[0]
+            toks.append(repr(x))
+        else:
+            nd = rnd.randrange(1, 22); d = "".join(rnd.choice("0123456789") for _ in range(nd)); p = rnd.randrange(0, nd + 1)
+            toks.append(("-" if rnd.random() < 0.3 else "") + d[:p] + ("." + d[p:] if p < nd else ""))
+    decoded = 0
+    for tk in toks:
+        raw = tk.encode()
+        b = C.c_uint64()
+        if lib.host_fast_f64(raw, len(raw), C.byref(b)) == 0:
+            decoded += 1
+            assert b.value == struct.unpack("<Q", struct.pack("<d", float(tk)))[0], repr(tk)
+    assert decoded > 40000                                    # the common shapes do take this path
+    for _ in range(20000):
+        s = rnd.randrange(0, 4 * 10 ** 9); f = rnd.randrange(0, 1000); nf = rnd.randrange(0, 4)
+        tk = f"{s}" if nf == 0 else f"{s}.{f:03d}"[:len(str(s)) + 1 + nf]
+        tk = ("-" if rnd.random() < 0.1 else "") + tk
+        o = C.c_int64()
+        if lib.host_fast_ts_ms(tk.encode(), len(tk), C.byref(o)) == 0:
+            assert o.value == int(Decimal(tk) * 1000), tk
+    for tk in ("1.2345", "12345678901234567", "1e3", "", "-", "1.", ".5", " 1"):     # not this path's business
+        assert lib.host_fast_ts_ms(tk.encode(), len(tk), C.byref(C.c_int64())) == 1 or tk == "12345678901234567"
