@@ -246,6 +246,22 @@ int pmx_slab_tail_gather(pmx_ctx* ctx, const int64_t* d_ts, const double* d_val,
                          const int64_t* d_off, int64_t n_series, int64_t cap, int64_t* d_out_ts, double* d_out_val,
                          pmx_stream stream);
 
+/* pmx_slab_append: the decoded samples of a new answer (CSR d_new_ts / d_new_val / d_in_off over n_in
+ * series, d_in_row[i] = slab row of series i or -1 to ignore it) are appended to their rows: samples
+ * not newer than the row's newest are skipped (answers may overlap), a full row drops its oldest.
+ * If a dropped sample is newer than needed_from_ms (a grid point not yet produced still needs it)
+ * NOTHING is appended.  d_status (int64[2]): [0] rows that would have lost such a sample (0 = the
+ * append happened), [1] samples stored.  d_work: 2 * n_in int64 of scratch owned by the caller.
+ * pmx_csr_copy: series s of (d_ts, d_val, d_off) is copied to d_out_*[d_dst[s] ..) -- how the range
+ * client concatenates the answers to consecutive sub-ranges per label set. */
+int pmx_slab_append(pmx_ctx* ctx, int64_t* d_ts, double* d_val, int64_t* d_count, int64_t cap,
+                    const int64_t* d_new_ts, const double* d_new_val, const int64_t* d_in_off,
+                    const int64_t* d_in_row, int64_t n_in, int64_t needed_from_ms, int64_t* d_work,
+                    int64_t* d_status, pmx_stream stream);
+int pmx_csr_copy(pmx_ctx* ctx, const int64_t* d_ts, const double* d_val, const int64_t* d_off,
+                 const int64_t* d_dst, int64_t n_series, int64_t* d_out_ts, double* d_out_val,
+                 pmx_stream stream);
+
 /* ---- X7  exact quantiles (K6) by radix select over order-preserving 64-bit keys.
  * Values of series s belong to segment d_seg[s] (or none if < 0).  State per segment:
  *   d_state: opaque uint64 [n_seg * (3 + 4*n_q)] owned by the caller, zeroed before pass 0 or

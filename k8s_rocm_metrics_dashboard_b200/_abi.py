@@ -70,6 +70,8 @@ SIGNATURES = {
     "pmx_where_gt": (_int, [_p, _p, _i64, C.c_double, _p, _p]),
     "pmx_slab_tail_lengths": (_int, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p]),
     "pmx_slab_tail_gather": (_int, [_p, _p, _p, _p, _p, _i64, _i64, _p, _p, _p]),
+    "pmx_slab_append": (_int, [_p, _p, _p, _p, _i64, _p, _p, _p, _p, _i64, _i64, _p, _p, _p]),
+    "pmx_csr_copy": (_int, [_p, _p, _p, _p, _p, _i64, _p, _p, _p]),
     "pmx_quantile_hist": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _i64, _i64, _int, _p, _p, _p]),
     "pmx_quantile_hist_lp": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _i64, _i64, _int, _int, _p, _p, _p]),
     "pmx_quantile_list_pass": (_int, [_i64, _i64, _i64]),

@@ -304,16 +304,17 @@ def merge_range_chunks(eng, chunks):
     ts_all = eng._empty((n,), t.int64)
     val_all = eng._empty((n,), t.float64)
     filled = np.zeros(S, dtype=np.int64)                 # samples of each series already placed
+    from . import _abi
     for (lab, ts, val, off), g in zip(chunks, gids):
         off = np.asarray(off, dtype=np.int64)
         lens = np.diff(off)
         if len(lens) == 0 or int(off[-1]) == 0:
             continue
-        # destination of sample i of local series s: series_off[g] + filled[g] + (i - off[s])
-        shift = t.as_tensor(series_off[g] + filled[g] - off[:-1], device=eng.device)
-        dest = t.repeat_interleave(shift, t.as_tensor(lens, device=eng.device)) + t.arange(int(off[-1]), device=eng.device)
-        ts_all.index_copy_(0, dest, ts)
-        val_all.index_copy_(0, dest, val)
+        # local series s goes to series_off[g] + filled[g]: one kernel copies every series to its place
+        d = t.as_tensor(np.concatenate([off, series_off[g] + filled[g]]), device=eng.device)
+        _abi.check(eng.lib.pmx_csr_copy(eng.ctx, eng._ptr(ts), eng._ptr(val), eng._ptr(d), eng._ptr(d[len(off):]), len(lens),
+                                        eng._ptr(ts_all), eng._ptr(val_all), eng._stream()))
+        eng.launches += 1
         filled[g] += lens
     return labels, ts_all, val_all, series_off
 

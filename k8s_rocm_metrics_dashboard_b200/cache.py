@@ -9,8 +9,7 @@ have become due plus the ``window_steps - 1`` points before them (their windows 
 far), on a compact CSR gathered from the tails of the slabs.  Work per refresh is proportional to
 series x (window + new points) instead of series x range.
 
-The slab append is a handful of torch index operations; the tail gather, decode, alignment, windows
-and rates are libpmx.so kernels.
+The slab append, the tail gather, decode, alignment, windows and rates are libpmx.so kernels.
 """
 from __future__ import annotations
 
@@ -23,10 +22,13 @@ from .engine import DEFAULT_LOOKBACK_MS, Engine, tokenize
 
 class SeriesCache:
     def __init__(self, eng: Engine, start_ms, step_ms, window_steps, lookback_ms=DEFAULT_LOOKBACK_MS,
-                 capacity=None, max_series=1024):
+                 capacity=None, max_series=1024, rank=0, world=1):
         """``capacity``: samples kept per series (default: enough for one window plus the lookback
-        at one sample per step, doubled).  ``max_series``: initial number of slab rows (grows)."""
+        at one sample per step, doubled).  ``max_series``: initial number of slab rows (grows).
+        ``rank`` / ``world``: this cache holds the series with ``label_hash % world == rank`` -- the
+        partition of ``sharding.partition`` -- and ignores the others in what it is given."""
         self.eng = eng
+        self.rank, self.world = int(rank), int(world)
         self.t = eng.torch
         self.start_ms, self.step_ms, self.w, self.lookback_ms = int(start_ms), int(step_ms), int(window_steps), int(lookback_ms)
         need = self.w + self.lookback_ms // self.step_ms + 2
@@ -78,54 +80,43 @@ class SeriesCache:
         return self.append(tok.labels(), ts_new, val_new, tok.series_off)
 
     def append(self, labels, ts_new, val_new, series_off):
-        """The same from decoded samples: CSR over ``labels`` (device tensors, host offsets)."""
+        """The same from decoded samples: CSR over ``labels`` (device tensors, host offsets).  One call
+        of the library (pmx_slab_append: a plan kernel and an in-place move) and one read of its two
+        status words.  With ``world > 1`` only the series whose label hash belongs to this rank are
+        stored (the others are another rank's shard)."""
         eng, t, dev = self.eng, self.t, self.eng.device
+        from . import _abi
         off = np.asarray(series_off, dtype=np.int64)
-        lens = np.diff(off)
-        rows = np.fromiter((self._row_of(l) for l in labels), dtype=np.int64, count=len(labels))
-        if len(np.unique(rows)) != len(rows):
-            raise ValueError("the same label set appears twice in one body")
-        keep = lens > 0
-        rows, lens, off0 = rows[keep], lens[keep], off[:-1][keep]
-        if len(rows) == 0:
+        n_in = len(labels)
+        if n_in == 0 or int(off[-1]) == 0:
             return 0
-        d_rows = t.as_tensor(rows, device=dev)
-        d_len = t.as_tensor(lens, device=dev)
-        d_off = t.as_tensor(off0, device=dev)
-        cnt_old = self.cnt[d_rows]
-        # skip what the series already holds: new samples are ascending, so it is a prefix
-        last = t.where(cnt_old > 0, self.ts[d_rows, (cnt_old - 1).clamp(min=0)],
-                       t.full_like(cnt_old, -(1 << 62)))
-        sample_series = t.repeat_interleave(t.arange(len(rows), device=dev), d_len)
-        flat = t.repeat_interleave(d_off, d_len) + (t.arange(int(lens.sum()), device=dev)
-                                                    - t.repeat_interleave(t.cumsum(d_len, 0) - d_len, d_len))
-        stale = (ts_new[flat] <= last[sample_series]).to(t.int64)
-        skip = t.zeros_like(d_len).index_add_(0, sample_series, stale)
-        d_off, d_len = d_off + skip, d_len - skip
-        total = cnt_old + d_len
-        new_total = total.clamp(max=self.cap)
-        drop = total - new_total                                   # oldest samples that fall out of the slab
-        if bool((drop > 0).any()):
-            # a sample still needed by a grid point that has not been produced must not fall out
-            needed_from = self.start_ms + (self.next_step - (self.w - 1)) * self.step_ms - self.lookback_ms
-            newest_lost = self.ts[d_rows, (drop - 1).clamp(min=0, max=self.cap - 1)]    # meaningful while drop <= cnt_old
-            lost = (drop > 0) & ((drop > cnt_old) | (newest_lost > needed_from))
-            if bool(lost.any()):
-                raise OverflowError("SeriesCache: capacity too small for the samples between two refreshes; "
-                                    "call refresh() more often or raise capacity")
-        pos = t.arange(self.cap, device=dev)[None, :]
-        q = pos + drop[:, None]                                    # index into [old | new] of what lands at pos
-        from_old = q < cnt_old[:, None]
-        valid = pos < new_total[:, None]
-        old_ts = self.ts[d_rows[:, None], q.clamp(max=self.cap - 1)]
-        old_val = self.val[d_rows[:, None], q.clamp(max=self.cap - 1)]
-        nidx = (d_off[:, None] + (q - cnt_old[:, None])).clamp(min=0, max=ts_new.numel() - 1)
-        new_ts = t.where(from_old, old_ts, ts_new[nidx])
-        new_val = t.where(from_old, old_val, val_new[nidx])
-        self.ts[d_rows] = t.where(valid, new_ts, t.zeros_like(new_ts))
-        self.val[d_rows] = t.where(valid, new_val, t.full_like(new_val, float("nan")))
-        self.cnt[d_rows] = new_total
-        return int(d_len.sum().item())
+        if self.world > 1:
+            from .sharding import label_hash
+            rows = np.fromiter((self._row_of(l) if label_hash(l) % self.world == self.rank else -1 for l in labels),
+                               dtype=np.int64, count=n_in)
+        else:
+            rows = np.fromiter((self._row_of(l) for l in labels), dtype=np.int64, count=n_in)
+        mine = rows[rows >= 0]
+        if len(np.unique(mine)) != len(mine):
+            raise ValueError("the same label set appears twice in one body")
+        # one upload: [offsets | rows]; scratch and status live with the cache
+        host = np.concatenate([off, rows])
+        d_in = t.as_tensor(host, device=dev)
+        if getattr(self, "_work_n", 0) < n_in:
+            self._work, self._work_n = eng._empty((2 * n_in,), t.int64), n_in
+            self._status = eng._empty((2,), t.int64)
+        # a sample still needed by a grid point that has not been produced must not fall out
+        needed_from = self.start_ms + (self.next_step - (self.w - 1)) * self.step_ms - self.lookback_ms
+        p = eng._ptr
+        _abi.check(eng.lib.pmx_slab_append(eng.ctx, p(self.ts), p(self.val), p(self.cnt), self.cap, p(ts_new), p(val_new),
+                                           p(d_in), p(d_in[n_in + 1:]), n_in, needed_from, p(self._work), p(self._status),
+                                           eng._stream()))
+        eng.launches += 2
+        lost, stored = self._status.cpu().tolist()
+        if lost:
+            raise OverflowError("SeriesCache: capacity too small for the samples between two refreshes; "
+                                "call refresh() more often or raise capacity")
+        return int(stored)
 
     # ------------------------------------------------------------------ refresh
     def refresh(self, upto_ms):
@@ -165,3 +156,25 @@ class SeriesCache:
         res["ts"] = self.start_ms + self.step_ms * np.arange(self.next_step, j_end + 1, dtype=np.int64)
         self.next_step = j_end + 1
         return res
+
+    def refresh_summary(self, upto_ms, sharded, names, qs=(0.5, 0.95, 0.99)):
+        """``refresh`` plus the per-metric summary of the NEW grid points over all ranks: sum / count /
+        min / max / mean and exact quantiles through ``sharded`` (a ``ShardedEngine``; its process
+        group spans the ranks whose caches partition the series).  ``names``: the metric names in
+        the order of the summary rows, the same list on every rank.  Every rank must call this
+        together (ranks without a due point or without series take part with empty data)."""
+        t, eng = self.t, self.eng
+        from .engine import group_index
+        res = self.refresh(upto_ms)
+        where = {n: i for i, n in enumerate(names)}
+        if res is None:
+            k = max(0, (int(upto_ms) - self.start_ms) // self.step_ms - self.next_step + 1)
+            x = eng._empty((0, max(k, 1)), t.float64)
+            gid = np.zeros(0, dtype=np.int32)
+        else:
+            x = res["aligned"].contiguous()
+            gid = np.fromiter((where[l.get("__name__", "")] for l in self.labels), dtype=np.int32, count=len(self.labels))
+        pg = group_index(gid, len(names))
+        summary, q = sharded.summarize(x, gid, len(names), pg, qs)
+        return res, summary, q
+

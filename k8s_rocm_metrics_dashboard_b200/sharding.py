@@ -112,6 +112,24 @@ class ShardedEngine:
         """(count, min, max) of the combined group summary: where the quantile selection starts."""
         return summary[1], summary[2], summary[3]
 
+    def summarize(self, x, seg, n_seg, perm_goff, qs=(0.5, 0.95, 0.99), defer_check=False):
+        """Per-segment sum / count / min / max / mean and exact quantiles of the [S, T] device matrix ``x`` over
+        ALL ranks (every rank calls this with its own rows; S may be 0).  Returns (summary, quantiles)."""
+        eng = self.eng
+        sm, cnt, mn, mx, mean = eng.group_reduce(x, None, n_seg, perm_goff=perm_goff)
+        key = (n_seg, len(qs))
+        if key not in self._qbuf:
+            self._qbuf[key] = eng.quantile_buffers(n_seg, len(qs))
+        if self.world > 1:
+            summary = combine_group_partials(sm, cnt, mn, mx, self.group, engine=eng)
+            q = eng.quantiles(x, seg, n_seg, list(qs), group=self.group or _world_group(), buffers=self._qbuf[key],
+                              row_order=perm_goff[0], summary=self._qsummary(summary), defer_check=defer_check)
+        else:
+            summary = (sm, cnt, mn, mx, mean)          # one rank: the kernel's own result is the summary
+            q = eng.quantiles(x, seg, n_seg, list(qs), buffers=self._qbuf[key], row_order=perm_goff[0],
+                              summary=self._qsummary(summary))
+        return summary, q
+
     def aggregate_step(self, ts, val, off, start_ms, step_ms, n_steps, window_steps, seg, n_seg, perm_goff,
                        qs=(0.5, 0.95, 0.99), out=None, lookback_ms=300_000, host=None, defer_check=False):
         """fused align+rolling+rate on the shard, then per-metric sum/count/min/max/mean and exact
@@ -126,23 +144,9 @@ class ShardedEngine:
                                       host["out"], lookback_ms)
         else:
             out = eng.fused(ts, val, off, start_ms, step_ms, n_steps, window_steps, lookback_ms, out=out)
-        sm, cnt, mn, mx, mean = eng.group_reduce(out["aligned"], None, n_seg, perm_goff=perm_goff)
-        if self.world > 1:
-            summary = combine_group_partials(sm, cnt, mn, mx, self.group, engine=eng)
-            key = (n_seg, len(qs))
-            if key not in self._qbuf:
-                self._qbuf[key] = eng.quantile_buffers(n_seg, len(qs))
-            q = eng.quantiles(out["aligned"], seg, n_seg, list(qs), group=self.group or _world_group(),
-                              buffers=self._qbuf[key], row_order=perm_goff[0], summary=self._qsummary(summary),
-                              defer_check=defer_check)
-        else:
-            summary = (sm, cnt, mn, mx, mean)          # one rank: the kernel's own result is the summary
-            key = (n_seg, len(qs))
-            if key not in self._qbuf:
-                self._qbuf[key] = eng.quantile_buffers(n_seg, len(qs))
-            q = eng.quantiles(out["aligned"], seg, n_seg, list(qs), buffers=self._qbuf[key],
-                              row_order=perm_goff[0], summary=self._qsummary(summary))
+        summary, q = self.summarize(out["aligned"], seg, n_seg, perm_goff, qs, defer_check)
         return out, summary, q
+
 
 
 def _world_group():

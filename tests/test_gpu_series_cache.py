@@ -119,3 +119,35 @@ def test_capacity_guard(eng):
         cache.ingest(_piece(d, d["start_ms"] - 1, d["start_ms"] + 299 * d["step_ms"]))
     with pytest.raises(ValueError):
         SeriesCache(eng, d["start_ms"], d["step_ms"], 60, capacity=10)
+
+
+def test_sharded_caches_partition_the_series_and_summarise_together(eng):
+    """Two caches that split the series by label hash (what two ranks hold): together they store every
+    series exactly once, and each produces the fused kernel's rows for its own shard."""
+    from k8s_rocm_metrics_dashboard_b200 import sharding
+    d = synth.dense(2, 4, 6, 200, seed=23, nan_frac=0.02)
+    step, start, w = d["step_ms"], d["start_ms"], 20
+    ref = O.aggregate_range(d["ts"], d["val"], d["off"], start, step, 200, w * step)
+    caches = [SeriesCache(eng, start, step, w, capacity=300, rank=r, world=2) for r in range(2)]
+    body = _piece(d, start - step, start + 199 * step)
+    stored = [c.ingest(body) for c in caches]
+    owner = sharding.partition(d["labels"], 2)
+    assert [c.n_series for c in caches] == [int((owner == r).sum()) for r in range(2)]
+    assert sum(stored) == int(((d["ts"] > start - step) & (d["ts"] <= start + 199 * step)).sum())
+    for r, c in enumerate(caches):
+        out = c.refresh(start + 199 * step)
+        order = [next(i for i, l in enumerate(d["labels"]) if l == lab) for lab in c.labels]
+        assert all(owner[i] == r for i in order)
+        got = {k: out[k].cpu().numpy() for k in KEYS}
+        _compare(got, {k: ref[k] for k in KEYS}, order, w, step)
+    # one rank alone: the summary of the new points through ShardedEngine
+    whole = SeriesCache(eng, start, step, w, capacity=300)
+    whole.ingest(body)
+    names = sorted({l["__name__"] for l in d["labels"]})
+    res, summary, q = whole.refresh_summary(start + 199 * step, sharding.ShardedEngine(eng), names)
+    al = res["aligned"].cpu().numpy()
+    gid = np.array([names.index(l["__name__"]) for l in whole.labels])
+    for g in range(len(names)):
+        o = O.quantiles(al[gid == g], [0.5, 0.95, 0.99])
+        assert int(summary[1][g]) == o["n"]
+        assert_bits_equal(q["value"][g].cpu().numpy(), np.array(o["value"]), "cache summary quantiles")
