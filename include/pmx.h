@@ -86,6 +86,21 @@ int pmx_tokenize_mt(const char* h_body, size_t len,
                     int64_t cap_series, char* h_extra, size_t cap_extra, int n_threads,
                     pmx_tokenize_result* res);
 
+/* The interned label table (replaces the dicts json.loads builds at app.py:178 and
+ * app.py:186-194 reads).  For the n_series "metric" objects whose byte spans the tokenizers return,
+ * every distinct string -- label name or value, JSON escapes decoded -- gets an id in order of first
+ * appearance: string i is h_strings[h_str_off[i] .. h_str_off[i+1]) (UTF-8).  Series s has the pairs
+ * h_pair_off[s] .. h_pair_off[s+1] of (h_key_id, h_val_id), in the order of its object.  A label
+ * column (all series' gpu_id, say) is then one pass over int32 pairs.  HOST code.
+ * Capacities: cap_pairs >= total labels, cap_strings >= bytes of distinct strings (len always
+ * suffices), cap_distinct + 1 entries in h_str_off; PMX_E_CAPACITY names what was too small. */
+typedef struct pmx_labels_result { int64_t n_pairs, n_strings, strings_len; } pmx_labels_result;
+int pmx_labels_intern(const char* h_body, size_t len, const uint32_t* h_metric_off,
+                      const uint32_t* h_metric_len, int64_t n_series, int64_t* h_pair_off,
+                      int32_t* h_key_id, int32_t* h_val_id, int64_t cap_pairs, char* h_strings,
+                      size_t cap_strings, int64_t* h_str_off, int64_t cap_distinct,
+                      pmx_labels_result* res);
+
 /* The same cut on the GPU, for a body that is already in device memory (the
  * host then never walks the text).  Accepts Prometheus' own compact encoding of a successful
  * "matrix" or "vector" answer: no white space between tokens, every sample written [<number>,"<text>"],

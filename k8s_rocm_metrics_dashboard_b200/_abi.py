@@ -27,6 +27,10 @@ class PmxError(RuntimeError):
         self.message = message
 
 
+class LabelsResult(C.Structure):
+    _fields_ = [("n_pairs", C.c_int64), ("n_strings", C.c_int64), ("strings_len", C.c_int64)]
+
+
 class TokenizeResult(C.Structure):
     _fields_ = [("n_samples", C.c_int64), ("n_series", C.c_int64), ("extra_len", C.c_int64),
                 ("result_type", C.c_int32)]
@@ -48,6 +52,8 @@ SIGNATURES = {
                             C.POINTER(TokenizeResult)]),
     "pmx_tokenize_mt": (_int, [_p, C.c_size_t, _p, _p, _i64, _p, _p, _p, _i64, _p, C.c_size_t, _int,
                                C.POINTER(TokenizeResult)]),
+    "pmx_labels_intern": (_int, [_p, C.c_size_t, _p, _p, _i64, _p, _p, _p, _i64, _p, C.c_size_t, _p, _i64,
+                                 C.POINTER(LabelsResult)]),
     "pmx_tokenize_device": (_int, [_p, _p, _u64, _p, _p, _i64, _p, _p, _p, _i64, _p, _p]),
     "pmx_parse_f64": (_int, [_p, _p, _u64, _p, _i64, _p, _p, _p]),
     "pmx_parse_ts_ms": (_int, [_p, _p, _u64, _p, _i64, _p, _p, _p]),

@@ -184,7 +184,7 @@ def _tidy_arrow(labels, grid, host, n_steps):
     S = len(labels)
     cols = {}
     for col, key in (("instance", "instance"), ("gpu_id", "gpu_id"), ("metric_name", "__name__")):
-        vals = [l.get(key, "") for l in labels]
+        vals = _label_values(labels, key)
         uniq = sorted(set(vals))
         code = {v: i for i, v in enumerate(uniq)}
         idx = np.repeat(np.fromiter((code[v] for v in vals), dtype=np.int32, count=S), n_steps)
@@ -225,6 +225,40 @@ def aggregate_range(body, start_ms, step_ms, n_steps, window_ms, lookback_ms=DEF
                              lookback_ms, quantiles, as_frame, group_keys)
 
 
+def _label_values(labels, key):
+    """Label ``key`` of every series as a list of str ("" where missing): from the interned table when
+    there is one, from the dicts otherwise."""
+    if hasattr(labels, "values") and hasattr(labels, "column"):
+        return labels.values(key)
+    return [l.get(key, "") for l in labels]
+
+
+def _group_ids(labels, group_keys):
+    """Sorted distinct key tuples and the group id of every series.  With an interned label table
+    this is integer work (ids ranked by their strings, np.unique over rows); no per-series dict."""
+    if hasattr(labels, "column"):
+        order = np.argsort(np.array(labels.strings + [""], dtype=object), kind="stable")
+        rank = np.empty(len(order), dtype=np.int64)
+        rank[order] = np.arange(len(order))
+        empty = len(labels.strings)                                   # stands for "" when a label is missing
+        if "" in labels._id:
+            empty = labels._id[""]
+        cols = []
+        for k in group_keys:
+            ids = labels.column(k).astype(np.int64)
+            ids[ids < 0] = empty
+            cols.append(rank[ids])
+        mat = np.stack(cols, axis=1) if cols else np.zeros((len(labels), 0), dtype=np.int64)
+        uniq, inv = np.unique(mat, axis=0, return_inverse=True)
+        strings = labels.strings + [""]
+        names = [tuple(strings[order[r]] for r in row) for row in uniq.tolist()]
+        return names, inv.reshape(-1).astype(np.int32)
+    tuples = [tuple(l.get(k, "") for k in group_keys) for l in labels]
+    names = sorted(set(tuples))
+    where = {n: i for i, n in enumerate(names)}
+    return names, np.fromiter((where[tp] for tp in tuples), dtype=np.int32, count=len(tuples))
+
+
 def _summary_column(key):
     return "metric_name" if key == "__name__" else key
 
@@ -235,10 +269,7 @@ def _aggregate_series(eng, labels, ts, val, series_off, start_ms, step_ms, n_ste
     w = int(window_ms // step_ms)
     out = eng.fused(ts, val, series_off, start_ms, step_ms, n_steps, w, lookback_ms)
     group_keys = tuple(group_keys)
-    tuples = [tuple(l.get(k, "") for k in group_keys) for l in labels]
-    names = sorted(set(tuples))
-    where = {n: i for i, n in enumerate(names)}
-    gid = np.fromiter((where[tp] for tp in tuples), dtype=np.int32, count=len(tuples))
+    names, gid = _group_ids(labels, group_keys)
     from .engine import group_index
     perm_goff = group_index(gid, len(names))
     sm, cnt, mn, mx, mean = eng.group_reduce(out["aligned"], None, len(names), perm_goff=perm_goff)
@@ -255,9 +286,9 @@ def _aggregate_series(eng, labels, ts, val, series_off, start_ms, step_ms, n_ste
     grid = start_ms + step_ms * np.arange(n_steps, dtype=np.int64)
     if as_frame == "arrow":
         return _tidy_arrow(labels, grid, host, n_steps), _summary_arrow(summary)
-    tidy = {"instance": np.repeat([l.get("instance", "") for l in labels], n_steps),
-            "gpu_id": np.repeat([l.get("gpu_id", "") for l in labels], n_steps),
-            "metric_name": np.repeat([l.get("__name__", "") for l in labels], n_steps),
+    tidy = {"instance": np.repeat(_label_values(labels, "instance"), n_steps),
+            "gpu_id": np.repeat(_label_values(labels, "gpu_id"), n_steps),
+            "metric_name": np.repeat(_label_values(labels, "__name__"), n_steps),
             "ts": np.tile(grid, S), "value": host["aligned"].ravel(), "roll_min": host["roll_min"].ravel(),
             "roll_max": host["roll_max"].ravel(), "roll_mean": host["roll_mean"].ravel(),
             "rate": host["rate"].ravel()}

@@ -15,6 +15,83 @@ from . import _abi
 DEFAULT_LOOKBACK_MS = 300_000
 
 
+class LabelTable:
+    """The label sets of all series, interned (pmx_labels_intern): ``strings`` holds every distinct
+    label name / value once, series s owns the pairs ``pair_off[s]:pair_off[s+1]`` of
+    (``key_id``, ``val_id``).  Behaves like the list of dicts ``json.loads`` would give (len, index,
+    iteration build the dict of one series on demand); ``column(name)`` is the vectorised form."""
+
+    def __init__(self, strings, pair_off, key_id, val_id):
+        self.strings, self.pair_off, self.key_id, self.val_id = strings, pair_off, key_id, val_id
+        self._id = {s: i for i, s in enumerate(strings)}
+
+    def __len__(self):
+        return len(self.pair_off) - 1
+
+    def __getitem__(self, s):
+        if isinstance(s, slice):
+            return [self[i] for i in range(*s.indices(len(self)))]
+        if s < 0:
+            s += len(self)
+        a, b = int(self.pair_off[s]), int(self.pair_off[s + 1])
+        st = self.strings
+        return {st[k]: st[v] for k, v in zip(self.key_id[a:b].tolist(), self.val_id[a:b].tolist())}
+
+    def __iter__(self):
+        return (self[i] for i in range(len(self)))
+
+    def __eq__(self, other):
+        try:
+            return len(self) == len(other) and all(a == b for a, b in zip(self, other))
+        except TypeError:
+            return NotImplemented
+
+    __hash__ = None
+
+    def column(self, name):
+        """int32[n_series]: the string id of label ``name`` in every series, -1 where it is missing."""
+        out = np.full(len(self), -1, dtype=np.int32)
+        k = self._id.get(name)
+        if k is None:
+            return out
+        hit = np.flatnonzero(self.key_id == k)
+        series = np.searchsorted(self.pair_off, hit, side="right") - 1
+        out[series] = self.val_id[hit]
+        return out
+
+    def values(self, name, missing=""):
+        """The label ``name`` of every series as a list of str (``missing`` where absent)."""
+        ids = self.column(name)
+        st = self.strings
+        return [st[i] if i >= 0 else missing for i in ids.tolist()]
+
+
+def _label_table(body, spans):
+    """pmx_labels_intern on the metric spans of a body (bytes or uint8 array)."""
+    lib = _abi.lib()
+    n = len(spans)
+    raw = body if isinstance(body, (bytes, bytearray)) else body.tobytes()
+    m_off = np.fromiter((o for o, _ in spans), dtype=np.uint32, count=n)
+    m_len = np.fromiter((l for _, l in spans), dtype=np.uint32, count=n)
+    total = int(m_len.sum())
+    cap_pairs = total // 6 + 1                               # "k":"v", is at least 8 bytes; be generous
+    pair_off = np.empty(n + 1, dtype=np.int64)
+    key_id, val_id = np.empty(cap_pairs, dtype=np.int32), np.empty(cap_pairs, dtype=np.int32)
+    strings = np.empty(max(total, 1), dtype=np.uint8)
+    cap_distinct = cap_pairs * 2 + 1
+    str_off = np.empty(cap_distinct + 1, dtype=np.int64)
+    res = _abi.LabelsResult()
+    rc = lib.pmx_labels_intern(raw, len(raw), m_off.ctypes.data, m_len.ctypes.data, n, pair_off.ctypes.data,
+                               key_id.ctypes.data, val_id.ctypes.data, cap_pairs, strings.ctypes.data, strings.size,
+                               str_off.ctypes.data, cap_distinct, C.byref(res))
+    if rc != _abi.OK:
+        raise ValueError(lib.pmx_last_error().decode("utf-8", "replace"))
+    blob = strings[:res.strings_len].tobytes()
+    so = str_off[:res.n_strings + 1].tolist()
+    st = [blob[so[i]:so[i + 1]].decode("utf-8", "surrogatepass") for i in range(res.n_strings)]
+    return LabelTable(st, pair_off, key_id[:res.n_pairs].copy(), val_id[:res.n_pairs].copy())
+
+
 @dataclass
 class Tokens:
     """Host-side result of pmx_tokenize: the flat byte buffer and per-sample offsets."""
@@ -34,9 +111,8 @@ class Tokens:
         return len(self.series_off) - 1
 
     def labels(self):
-        import json
-        body = self.flat
-        return [json.loads(bytes(body[o:o + n])) if n else {} for o, n in self.metric_spans]
+        """The label sets, interned (``LabelTable``: indexes and iterates like a list of dicts)."""
+        return _label_table(self.flat, self.metric_spans)
 
 
 @dataclass
@@ -60,8 +136,8 @@ class DeviceTokens:
         return len(self.series_off) - 1
 
     def labels(self):
-        import json
-        return [json.loads(self.body[o:o + n]) if n else {} for o, n in self.metric_spans]
+        """The label sets, interned (``LabelTable``: indexes and iterates like a list of dicts)."""
+        return _label_table(self.body, self.metric_spans)
 
 
 _TOKD_ERRORS = {1: "not a successful Prometheus matrix/vector answer in compact encoding",

@@ -255,3 +255,25 @@ def test_fast_window_decode_on_host_matches_python_float(host_lib, golden_dir):
             assert o.value == int(Decimal(tk) * 1000), tk
     for tk in ("1.2345", "12345678901234567", "1e3", "", "-", "1.", ".5", " 1"):     # not this path's business
         assert lib.host_fast_ts_ms(tk.encode(), len(tk), C.byref(C.c_int64())) == 1 or tk == "12345678901234567"
+
+
+def test_interned_label_table_equals_json_loads():
+    """pmx_labels_intern (X1's label table): the same dicts json.loads builds (app.py:178), escapes and
+    non-ASCII included; a column is one integer array; group ids need no per-series dict."""
+    from k8s_rocm_metrics_dashboard_b200.adapter import _group_ids
+    d = synth.dense(3, 4, 6, 3, seed=1)
+    d["labels"][2]["weird"] = 'a"b\\cé中\U0001F600\n\t/'
+    del d["labels"][5]["gpu_id"]
+    d["labels"][7][""] = ""
+    body = synth.to_matrix_json(d["labels"], d["ts"], d["val"], d["off"])
+    table = tokenize(body).labels()
+    ref = [s["metric"] for s in json.loads(body)["data"]["result"]]
+    assert len(table) == len(ref) and list(table) == ref and table == ref
+    assert table[-1] == ref[-1] and table[1:3] == ref[1:3]
+    assert len(table.strings) == len(set(table.strings))                      # every string once
+    assert table.values("gpu_id", missing="?") == [l.get("gpu_id", "?") for l in ref]
+    assert (table.column("no_such_label") == -1).all()
+    for keys in (("__name__",), ("instance", "gpu_id", "__name__"), ("instance", "__name__")):
+        n1, g1 = _group_ids(table, keys)
+        n2, g2 = _group_ids(ref, keys)
+        assert n1 == n2 and np.array_equal(g1, g2), keys
