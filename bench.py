@@ -218,13 +218,12 @@ def config3_block(eng, sh, world, rank, barrier, steps=5):
     pg = (torch.as_tensor(perm, device=dev), torch.as_tensor(goff, device=dev))
     out = {k: torch.empty((S3, T3), dtype=torch.float64, device=dev)
            for k in ("aligned", "roll_min", "roll_max", "roll_mean", "rate")}
-    alone = ShardedEngine.__new__(ShardedEngine)
-    alone.eng, alone.group, alone.world, alone.rank, alone._qbuf = eng, None, 1, 0, {}
+    alone = ShardedEngine(eng, local_only=True)
 
     def timed(engine_like):
         def one():
             engine_like.aggregate_step(ts, val, off, START_MS, STEP_MS, T3, WINDOW_STEPS, seg, M3, pg, QS, out=out,
-                                       lookback_ms=LOOKBACK_MS, defer_check=True)
+                                       lookback_ms=LOOKBACK_MS, defer_check=True, graph=True)
         for _ in range(2):
             one()
         barrier()
@@ -331,7 +330,7 @@ def run_engine(args):
         # no host synchronisation inside the step: whether every segment fitted the key exchange of
         # the cluster-wide quantiles is a device counter, looked at one step later (Engine.deferred_ok)
         r = sh.aggregate_step(ts, val, off, START_MS, STEP_MS, T, WINDOW_STEPS, seg, N_METRICS, perm_goff,
-                              QS, out=out, lookback_ms=LOOKBACK_MS, defer_check=True)
+                              QS, out=out, lookback_ms=LOOKBACK_MS, defer_check=True, graph=True)
         checks["ok"] = eng.deferred_ok(wait=False) and checks["ok"]
         return r
 

@@ -571,6 +571,15 @@ class Engine:
         self._deferred = keep
         return ok
 
+    def _quantile_levels(self, qs):
+        """The quantile levels as a device tensor, uploaded once per distinct tuple (a pageable
+        host-to-device copy in every call would also forbid capturing the step in a CUDA graph)."""
+        key = tuple(float(q) for q in qs)
+        cache = self.__dict__.setdefault("_qlevels", {})
+        if key not in cache:
+            cache[key] = self._dev(np.asarray(key, dtype=np.float64), self.torch.float64)
+        return cache[key]
+
     def quantile_buffers(self, n_seg, n_q):
         t = self.torch
         state = self.torch.zeros((n_seg, 3 + 4 * n_q), dtype=t.int64, device=self.device)
@@ -614,7 +623,7 @@ class Engine:
         d_ord = self._dev(row_order, t.int32) if row_order is not None else None
         n_rows = d_ord.numel() if d_ord is not None else 0
         n_q = len(qs)
-        d_q = self._dev(np.asarray(qs, dtype=np.float64), t.float64)
+        d_q = self._quantile_levels(qs)
         outs = {"n": self._empty((n_seg,), t.int64), "lo": self._empty((n_seg, n_q), t.int64),
                 "hi": self._empty((n_seg, n_q), t.int64), "x_lo": self._empty((n_seg, n_q), t.float64),
                 "x_hi": self._empty((n_seg, n_q), t.float64), "value": self._empty((n_seg, n_q), t.float64)}

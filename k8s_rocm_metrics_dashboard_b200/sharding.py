@@ -99,13 +99,17 @@ def distributed_quantiles(hist_fn, pick_fn, finish_fn, n_seg, n_q, group=None, p
 class ShardedEngine:
     """Engine + process group: the aggregate step on this rank's shard with cluster-wide summaries."""
 
-    def __init__(self, engine, group=None):
+    def __init__(self, engine, group=None, local_only=False):
+        """``local_only``: behave as one rank whatever the process group says (no exchange)."""
         import torch.distributed as dist
         self.eng = engine
         self.group = group
-        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
-        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        alone = local_only or not dist.is_initialized()
+        self.world = 1 if alone else dist.get_world_size(group)
+        self.rank = 0 if alone else dist.get_rank(group)
         self._qbuf = {}
+        self._graphs = {}
+        self._graph_launches = 9                                # kernels of ours inside one replay
 
     @staticmethod
     def _qsummary(summary):
@@ -130,21 +134,56 @@ class ShardedEngine:
                               summary=self._qsummary(summary))
         return summary, q
 
+    def summarize_graph(self, x, seg, n_seg, perm_goff, qs=(0.5, 0.95, 0.99)):
+        """``summarize`` replayed from a CUDA graph (one rank): the nine small launches behind the fused
+        kernel (partials, fold, init, two histogram passes with their picks, tail, finish) are
+        launch-bound, so they are captured once per (buffer, shape) and replayed.  ``x``, ``seg`` and
+        ``perm_goff`` must be the same device tensors on every call (the graph reads them in
+        place); the returned tensors are the graph's own and are overwritten by the next replay.
+        Falls back to the eager path when capture is not possible."""
+        t = self.eng.torch
+        key = (x.data_ptr(), tuple(x.shape), seg.data_ptr(), n_seg, perm_goff[0].data_ptr(), perm_goff[1].data_ptr(), tuple(qs))
+        hit = self._graphs.get(key)
+        if hit is None:
+            for _ in range(2):                                  # scratch grows and kernels load outside the capture
+                self.summarize(x, seg, n_seg, perm_goff, qs)
+            t.cuda.synchronize()
+            try:
+                g = t.cuda.CUDAGraph()
+                with t.cuda.graph(g, capture_error_mode="thread_local"):
+                    res = self.summarize(x, seg, n_seg, perm_goff, qs)
+                hit = (g, res, (x, seg, perm_goff))             # the inputs stay alive with the graph
+            except Exception:  # noqa: BLE001  -- capture refused: stay eager
+                t.cuda.synchronize()
+                hit = (None, None, None)
+            self._graphs[key] = hit
+        if hit[0] is None:
+            return self.summarize(x, seg, n_seg, perm_goff, qs)
+        hit[0].replay()
+        self.eng.launches += self._graph_launches
+        return hit[1]
+
     def aggregate_step(self, ts, val, off, start_ms, step_ms, n_steps, window_steps, seg, n_seg, perm_goff,
-                       qs=(0.5, 0.95, 0.99), out=None, lookback_ms=300_000, host=None, defer_check=False):
+                       qs=(0.5, 0.95, 0.99), out=None, lookback_ms=300_000, host=None, defer_check=False,
+                       graph=False):
         """fused align+rolling+rate on the shard, then per-metric sum/count/min/max/mean and exact
         quantiles of the aligned values over ALL ranks.  ``seg``: metric id per local series.
         With ``host`` = {"dev": device buffers, "out": pinned host outputs} the inputs are pinned host
         tensors and the copies are pipelined with the kernel (Engine.fused_from_host).
         ``defer_check``: see ``Engine.quantiles`` -- no host synchronisation inside the step; the
-        caller asks ``Engine.deferred_ok()`` later."""
+        caller asks ``Engine.deferred_ok()`` later.
+        ``graph`` (one rank, with ``out`` given): the launches behind the fused kernel are replayed
+        from a CUDA graph (``summarize_graph``)."""
         eng = self.eng
         if host is not None:        # ts/val/off are pinned host tensors; results also go to host["out"]
             out = eng.fused_from_host(ts, val, off, start_ms, step_ms, n_steps, window_steps, host["dev"],
                                       host["out"], lookback_ms)
         else:
             out = eng.fused(ts, val, off, start_ms, step_ms, n_steps, window_steps, lookback_ms, out=out)
-        summary, q = self.summarize(out["aligned"], seg, n_seg, perm_goff, qs, defer_check)
+        if graph and self.world == 1 and host is None:
+            summary, q = self.summarize_graph(out["aligned"], seg, n_seg, perm_goff, qs)
+        else:
+            summary, q = self.summarize(out["aligned"], seg, n_seg, perm_goff, qs, defer_check)
         return out, summary, q
 
 
