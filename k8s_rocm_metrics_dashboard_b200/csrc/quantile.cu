@@ -10,12 +10,14 @@
 // After the last pass every target's prefix IS the key of the wanted order statistic.  Targets
 // per segment: for each q the ranks lo = floor((n-1)q) and hi = min(lo+1, n-1), then numpy's
 // _lerp.  No sample ever moves between GPUs; a pass exchanges 16 KiB per target.
-// Passes 0-2 read every value (with pmx_quantile_init there is no pass 0: keys are taken relative
-// to the segment's minimum and the bits its range leaves zero are skipped).  Pass 2 also copies
-// the keys that still match a target prefix into a per-segment candidate list; later passes read
-// only that list -- all of them at once in pmx_quantile_tail (one GPU) or after an all-gather of
-// the few keys left (pmx_quantile_tail_filter / _merge).  A segment whose list overflows (many
-// repeated values) keeps reading the full data in the per-pass kernels.
+// The passes before the list pass (2, or 3 for very long segments) histogram every value (with
+// pmx_quantile_init there is no pass 0: keys are taken relative to the segment's minimum and the
+// bits its range leaves zero are skipped).  The list pass reads the data once more, only to copy the
+// keys that still match a target prefix into a per-segment candidate list (collect_kernel: no
+// histogram, the speed of the read); its digit and all later ones come from that list -- the rest at
+// once in pmx_quantile_tail (one GPU) or after an all-gather of the few keys left
+// (pmx_quantile_tail_filter / _merge).  A segment whose list overflows (many repeated values)
+// keeps reading the full data in the per-pass kernels.
 //
 // State per segment (uint64 words): [0] n, [1] how the selection began and whether it is finished,
 // [2] base key, then per target t: [3+2t] prefix, [4+2t] remaining rank inside the prefix bucket.
@@ -75,27 +77,13 @@ __device__ __forceinline__ Geom seg_geom(const uint64_t* st, int pass) {
   return g;
 }
 
-// Adds one key per lane to a CTA-private histogram.  All 32 lanes call this together (hit = this
-// lane contributes).  Lanes that fall into the same bin as the current leader are folded into one
-// shared atomic (two rounds: gauge data puts a whole warp into one or two bins in the first
-// pass); what is left after that is spread over many bins and goes in lane by lane.  `spread`
-// counts the calls in a row in which the first round folded next to nothing: from four on the
-// rounds are skipped (they cost more instructions than the atomics they save) until a row ends.
-__device__ __forceinline__ void hist_add(unsigned int* h, bool hit, unsigned d, int lane, int& spread) {
-  unsigned todo = __ballot_sync(0xffffffffu, hit);
-  if (spread < 4) {
-#pragma unroll
-    for (int round = 0; round < 2; ++round) {
-      if (todo == 0) return;
-      const int leader = __ffs(todo) - 1;
-      const unsigned dl = __shfl_sync(0xffffffffu, d, leader);
-      const unsigned peers = __ballot_sync(0xffffffffu, hit && d == dl) & todo;
-      if (lane == leader) atomicAdd(&h[dl], (unsigned)__popc(peers));
-      if (round == 0) spread = (__popc(peers) <= 2 && __popc(todo) >= 16) ? spread + 1 : 0;
-      todo &= ~peers;
-    }
-  }
-  if ((todo >> lane) & 1) atomicAdd(&h[d], 1u);
+// Adds one key per lane to a CTA-private histogram: a plain shared-memory atomic.  The hardware
+// folds the lanes of a warp that hit one address (ATOMS.POPC.INC), and on B200 that beats every
+// warp-level folding scheme (leader rounds, match_any, run merging) on spread, repeated and
+// constant digits alike -- tools/micro/hist_variants.cu: 59 / 47 / 47 us for 35 M values against
+// 59 / 70 / 70 us for two leader rounds.
+__device__ __forceinline__ void hist_add(unsigned int* h, bool hit, unsigned d) {
+  if (hit) atomicAdd(&h[d], 1u);
 }
 
 // distinct prefixes of a segment's targets (lo/hi ranks and nearby quantiles usually share one)
@@ -116,9 +104,8 @@ __device__ __forceinline__ void load_prefixes(const uint64_t* __restrict__ state
   *s_nu = nu;
 }
 
-// mode 0: histogram only; mode 1 (pass 2): also append matching keys to the segment's candidate
-// list; mode 2 (pass >= 3): skip segments whose candidate list is complete (cand_hist_kernel
-// serves them).
+// mode 0: histogram of every row; mode 2 (the list pass and later): only segments whose candidate
+// list overflowed -- cand_hist_kernel serves the others from their lists.
 template <int MODE>
 __global__ void __launch_bounds__(256)
 hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __restrict__ seg,
@@ -184,7 +171,6 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
     const uint64_t kbase = gm.base;
     const bool all_match = gm.all_match;
     const bool use_bitmap = pass >= 2;                     // the previous digit exists and is 11 bits wide
-    int spread = 0;
     // previous digits of up to four distinct prefixes in registers (the usual case: lo/hi ranks and
     // neighbouring quantiles share prefixes); more go through the shared bitmap
     unsigned pd0 = 0xffffffffu, pd1 = 0xffffffffu, pd2 = 0xffffffffu, pd3 = 0xffffffffu;
@@ -238,7 +224,7 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
       }
       if (all_match) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) hist_add(sh, valid[i], w[i] & mask, lane, spread);
+        for (int i = 0; i < 4; ++i) hist_add(sh, valid[i], w[i] & mask);
         continue;
       }
       // cheap filter first, for the four elements at once: does any target prefix end in the key's
@@ -270,21 +256,130 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
         for (int u = 0; u < nu; ++u) hits |= (mb && top == s_uprefix[u]) ? (1u << u) : 0u;
         const unsigned any = __ballot_sync(0xffffffffu, hits != 0);
         if (any == 0) continue;
-        for (int u = 0; u < nu; ++u) hist_add(sh + u * BINS, (hits >> u) & 1, d, lane, spread);
-        if (mode == 1) {                                   // append to the candidate list, one atomic per warp
-          const int leader = __ffs(any) - 1;
-          unsigned base = 0;
-          if (lane == leader) {
-            base = atomicAdd(&cand_cnt[sg], (unsigned)__popc(any));
-            if (base + (unsigned)__popc(any) > cap) *cand_overflow = 1u;
-          }
-          base = __shfl_sync(0xffffffffu, base, leader);
-          if (hits) {
-            const unsigned pos = base + (unsigned)__popc(any & ((1u << lane) - 1u));
-            if (pos < cap) cand[(size_t)sg * cap + pos] = key;
-          }
-        }
+        for (int u = 0; u < nu; ++u) hist_add(sh + u * BINS, (hits >> u) & 1, d);
       }
+    }
+  }
+  if (cur_seg >= 0) flush(cur_seg);
+}
+
+// The list pass without a histogram: every key that carries a target's prefix (as the passes before
+// `pass` left it) is appended to its segment's candidate list, and nothing else happens -- no
+// shared-memory histograms, so twice the CTAs fit an SM and the sweep runs at the speed of the
+// read.  cand_hist_kernel then takes this pass's digit from the lists.  Hits are staged per warp in
+// shared memory and leave as one global atomic + coalesced stores per ~200 keys.
+constexpr int COLLECT_WBUF = 256;                            // staged keys per warp; a trip adds at most 128
+__global__ void __launch_bounds__(256)
+collect_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __restrict__ seg,
+               int n_t, int pass, const uint64_t* __restrict__ state, int sw, int rows_per_cta, int64_t n_rows,
+               const int32_t* __restrict__ order, unsigned long long* __restrict__ cand,
+               unsigned int* __restrict__ cand_cnt, unsigned cap, unsigned int* __restrict__ cand_overflow) {
+  __shared__ uint64_t s_uprefix[MAX_TARGETS];
+  __shared__ int s_umap[MAX_TARGETS];
+  __shared__ int s_urep[MAX_TARGETS];
+  __shared__ int s_nu;
+  __shared__ Geom s_geom;
+  __shared__ unsigned long long s_buf[8][COLLECT_WBUF];
+  const int64_t s0 = (int64_t)blockIdx.x * rows_per_cta;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  unsigned long long* wbuf = s_buf[warp];
+  unsigned wcnt = 0;                                         // keys staged by this warp (warp-uniform)
+  int cur_seg = -1;
+  auto flush = [&](int sg) {
+    if (wcnt == 0) return;
+    unsigned base = 0;
+    if (lane == 0) {
+      base = atomicAdd(&cand_cnt[sg], wcnt);
+      if (base + wcnt > cap) *cand_overflow = 1u;
+    }
+    base = __shfl_sync(0xffffffffu, base, 0);
+    __syncwarp();
+    for (unsigned i = lane; i < wcnt; i += 32)
+      if (base + i < cap) cand[(size_t)sg * cap + base + i] = wbuf[i];
+    __syncwarp();
+    wcnt = 0;
+  };
+  for (int r = 0; r < rows_per_cta; ++r) {
+    if (s0 + r >= n_rows) break;
+    const int64_t s = order ? (int64_t)order[s0 + r] : s0 + r;
+    const int sg = seg[s];
+    if (sg < 0) continue;
+    if (sg != cur_seg) {
+      if (cur_seg >= 0) flush(cur_seg);
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        load_prefixes(state, sw, sg, n_t, pass, s_uprefix, s_umap, s_urep, &s_nu);
+        s_geom = seg_geom(state + (size_t)sg * sw, pass);
+      }
+      cur_seg = sg;
+      __syncthreads();
+    }
+    const int nu = s_nu;
+    const Geom gm = s_geom;
+    if (gm.bits == 0 || !gm.has_prefix) continue;            // nothing left to resolve / no prefix to match yet
+    const int pshift = gm.pshift;
+    const unsigned kb_lo = (unsigned)gm.base, kb_hi = (unsigned)(gm.base >> 32);
+    // up to four distinct prefixes in registers (lo/hi ranks and neighbouring quantiles share them);
+    // ~0 never equals the top bits of a key
+    const bool few = nu <= 4;
+    const uint64_t p0 = nu > 0 ? s_uprefix[0] : ~0ULL, p1 = nu > 1 ? s_uprefix[1] : ~0ULL,
+                   p2 = nu > 2 ? s_uprefix[2] : ~0ULL, p3 = nu > 3 ? s_uprefix[3] : ~0ULL;
+    const bool top32 = pshift >= 32;                         // the known bits sit in the key's high word
+    const unsigned q0 = (unsigned)p0, q1 = (unsigned)p1, q2 = (unsigned)p2, q3 = (unsigned)p3;
+    const double* xr = x + s * n_steps;
+    const bool vec = (reinterpret_cast<uintptr_t>(xr) & 15) == 0;
+    const int64_t per_trip = (int64_t)blockDim.x * 4;
+    const int64_t n_full = vec ? n_steps / per_trip : 0;
+    const int64_t n_trips = (n_steps + per_trip - 1) / per_trip;
+    const double qnan = __longlong_as_double(0x7FF8000000000000LL);
+    auto load_tail = [&](int64_t j0, double* v) {
+      const int64_t ja = j0 + 2 * threadIdx.x, jb = ja + 2 * blockDim.x;
+      v[0] = ja < n_steps ? xr[ja] : qnan; v[1] = ja + 1 < n_steps ? xr[ja + 1] : qnan;
+      v[2] = jb < n_steps ? xr[jb] : qnan; v[3] = jb + 1 < n_steps ? xr[jb + 1] : qnan;
+    };
+    const double2* pa = reinterpret_cast<const double2*>(xr) + threadIdx.x;
+    const int64_t half = blockDim.x, stride = 2 * (int64_t)blockDim.x;
+    double vn[4];
+    if (n_full > 0) { const double2 a = pa[0], b = pa[half]; vn[0] = a.x; vn[1] = a.y; vn[2] = b.x; vn[3] = b.y; }
+    else load_tail(0, vn);
+    for (int64_t trip = 0; trip < n_trips; ++trip) {
+      double v[4] = {vn[0], vn[1], vn[2], vn[3]};
+      if (trip + 1 < n_full) {
+        pa += stride;
+        const double2 a = pa[0], b = pa[half];
+        vn[0] = a.x; vn[1] = a.y; vn[2] = b.x; vn[3] = b.y;
+      } else if (trip + 1 < n_trips) {
+        load_tail((trip + 1) * per_trip, vn);
+      }
+      unsigned r_lo[4], r_hi[4];
+      bool hit[4];
+      bool some = false;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const unsigned b_lo = (unsigned)__double2loint(v[i]), b_hi = (unsigned)__double2hiint(v[i]);
+        const unsigned sm = (unsigned)((int)b_hi >> 31);
+        const unsigned k_lo = b_lo ^ sm, k_hi = b_hi ^ (sm | 0x80000000u);
+        r_lo[i] = k_lo - kb_lo; r_hi[i] = k_hi - kb_hi - (k_lo < kb_lo ? 1u : 0u);
+        bool h;
+        if (top32 && few) {
+          const unsigned top = r_hi[i] >> (pshift - 32);
+          h = (top == q0) | (top == q1) | (top == q2) | (top == q3);
+        } else {
+          const uint64_t top = (((uint64_t)r_hi[i] << 32) | r_lo[i]) >> pshift;
+          if (few) h = (top == p0) | (top == p1) | (top == p2) | (top == p3);
+          else { h = false; for (int u = 0; u < nu; ++u) h |= top == s_uprefix[u]; }
+        }
+        hit[i] = h & (v[i] == v[i]);
+        some |= hit[i];
+      }
+      if (__ballot_sync(0xffffffffu, some) == 0) continue;   // the usual trip: no key of this warp matches
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const unsigned any = __ballot_sync(0xffffffffu, hit[i]);
+        if (hit[i]) wbuf[wcnt + (unsigned)__popc(any & ((1u << lane) - 1u))] = ((uint64_t)r_hi[i] << 32) | r_lo[i];
+        wcnt += (unsigned)__popc(any);
+      }
+      if (wcnt > COLLECT_WBUF - 128) flush(sg);
     }
   }
   if (cur_seg >= 0) flush(cur_seg);
@@ -317,14 +412,13 @@ cand_hist_kernel(const unsigned long long* __restrict__ cand, const unsigned int
   for (int i = threadIdx.x; i < nu * BINS; i += blockDim.x) sh[i] = 0;
   __syncthreads();
   const unsigned long long* keys = cand + (size_t)sg * cap;
-  int spread = 0;
   for (unsigned i0 = a; i0 < b; i0 += blockDim.x) {
     const unsigned i = i0 + threadIdx.x;
     const bool in = i < b;
     const uint64_t key = in ? keys[i] : 0;
     const unsigned d = (unsigned)(key >> shift) & mask;
     const uint64_t top = gm.has_prefix ? key >> pshift : 0;
-    for (int u = 0; u < nu; ++u) hist_add(sh + u * BINS, in && top == s_uprefix[u], d, lane, spread);
+    for (int u = 0; u < nu; ++u) hist_add(sh + u * BINS, in && top == s_uprefix[u], d);
   }
   __syncthreads();
   for (int u = 0; u < nu; ++u) {
@@ -498,7 +592,6 @@ tail_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __r
       for (int i = threadIdx.x; i < BINS; i += blockDim.x) sh[i] = 0;
       __syncthreads();
       const uint64_t want = s_old[tg];
-      int spread = 0;
       if (from_list) {
         const unsigned long long* glist = cand + (size_t)sg * cap;
         for (unsigned i0 = 0; i0 < n_list; i0 += blockDim.x * 4) {
@@ -508,7 +601,7 @@ tail_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __r
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             const unsigned i = i0 + u * blockDim.x + threadIdx.x;
-            hist_add(sh, i < n_list && (kk[u] >> gm.pshift) == want, (unsigned)(kk[u] >> gm.shift) & mask, lane, spread);
+            hist_add(sh, i < n_list && (kk[u] >> gm.pshift) == want, (unsigned)(kk[u] >> gm.shift) & mask);
           }
         }
       } else if (!from_data) {
@@ -516,7 +609,7 @@ tail_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __r
           const unsigned i = i0 + threadIdx.x;
           const bool in = i < n;
           const uint64_t key = in ? keys[i] : 0;
-          hist_add(sh, in && (key >> gm.pshift) == want, (unsigned)(key >> gm.shift) & mask, lane, spread);
+          hist_add(sh, in && (key >> gm.pshift) == want, (unsigned)(key >> gm.shift) & mask);
         }
       } else {
         for (int64_t r = 0; r < n_series; ++r) {
@@ -526,7 +619,7 @@ tail_kernel(const unsigned long long* __restrict__ cand, const unsigned int* __r
             const int64_t j = j0 + threadIdx.x;
             const double v = j < n_steps ? xr[j] : pmx_nan();
             const uint64_t key = f64_key(v) - gm.base;
-            hist_add(sh, v == v && (key >> gm.pshift) == want, (unsigned)(key >> gm.shift) & mask, lane, spread);
+            hist_add(sh, v == v && (key >> gm.pshift) == want, (unsigned)(key >> gm.shift) & mask);
           }
         }
       }
@@ -836,20 +929,12 @@ int pmx_quantile_hist_lp(pmx_ctx* ctx, const double* d_x, int64_t n_series, int6
   if (pass >= list_pass) {
     size_t hdr;
     if (int rc = cand_layout(ctx, n_seg, &cap, &cand_cnt, &cand, &hdr)) return rc;
-    mode = pass == list_pass ? 1 : 2;
+    mode = 2;
     if (pass == list_pass) PMX_CUDA(cudaMemsetAsync(cand_cnt, 0, hdr, st));
   }
   const size_t smem = (size_t)n_h * BINS * sizeof(unsigned int);
   PMX_CUDA(cudaFuncSetAttribute(hist_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(MAX_TARGETS * BINS * sizeof(unsigned int))));
-  PMX_CUDA(cudaFuncSetAttribute(hist_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(MAX_TARGETS * BINS * sizeof(unsigned int))));
   PMX_CUDA(cudaFuncSetAttribute(hist_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(MAX_TARGETS * BINS * sizeof(unsigned int))));
-  if (mode == 2) {
-    PMX_CUDA(cudaFuncSetAttribute(cand_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(MAX_TARGETS * BINS * sizeof(unsigned int))));
-    dim3 grid(32, (unsigned)n_seg);
-    cand_hist_kernel<<<grid, 256, smem, st>>>(cand, cand_cnt, cap, n_t, pass, d_state, state_words(n_q),
-                                            (unsigned long long*)d_hist);
-    PMX_LAUNCH_CHECK();
-  }
   // a CTA sweeps consecutive rows so that a segment's private histogram is flushed rarely
   if (!d_row_order) n_rows = n_series;
   PMX_REQUIRE(n_rows >= 0 && n_rows <= n_series, "n_rows out of range");
@@ -859,12 +944,21 @@ int pmx_quantile_hist_lp(pmx_ctx* ctx, const double* d_x, int64_t n_series, int6
   if (rows < 1) rows = 1;
   const int64_t grid = (n_rows + rows - 1) / rows;
   unsigned int* overflow = cand_cnt ? cand_cnt + n_seg : nullptr;
+  if (pass == list_pass) {
+    // the list pass reads the data once, only to cut the lists; its digit then comes from the lists
+    collect_kernel<<<(unsigned)grid, 256, 0, st>>>(d_x, n_steps, d_seg, n_t, pass, d_state, state_words(n_q), (int)rows,
+                                                   n_rows, d_row_order, cand, cand_cnt, cap, overflow);
+    PMX_LAUNCH_CHECK();
+  }
+  if (mode == 2) {
+    PMX_CUDA(cudaFuncSetAttribute(cand_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(MAX_TARGETS * BINS * sizeof(unsigned int))));
+    dim3 grid(32, (unsigned)n_seg);
+    cand_hist_kernel<<<grid, 256, smem, st>>>(cand, cand_cnt, cap, n_t, pass, d_state, state_words(n_q),
+                                            (unsigned long long*)d_hist);
+    PMX_LAUNCH_CHECK();
+  }
   if (mode == 0)
     hist_kernel<0><<<(unsigned)grid, 256, smem, st>>>(d_x, n_steps, d_seg, n_t, pass, d_state, state_words(n_q),
-                                                     (unsigned long long*)d_hist, (int)rows, n_rows, d_row_order,
-                                                     cand, cand_cnt, cap, overflow);
-  else if (mode == 1)
-    hist_kernel<1><<<(unsigned)grid, 256, smem, st>>>(d_x, n_steps, d_seg, n_t, pass, d_state, state_words(n_q),
                                                      (unsigned long long*)d_hist, (int)rows, n_rows, d_row_order,
                                                      cand, cand_cnt, cap, overflow);
   else

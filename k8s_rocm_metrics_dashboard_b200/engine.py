@@ -633,7 +633,7 @@ class Engine:
                 self._ptr(outs["n"]),
                 self._ptr(outs["lo"]), self._ptr(outs["hi"]), self._ptr(outs["x_lo"]), self._ptr(outs["x_hi"]),
                 self._ptr(outs["value"]), self._stream()))
-            self.launches += 8                                  # three passes of hist + pick, tail, finish
+            self.launches += 10                                 # hist + pick (two passes), collect + list hist (two kernels) + pick, tail, finish
             return outs
         state, hist = buffers if buffers is not None else self.quantile_buffers(n_seg, n_q)
         if summary is None:
@@ -655,7 +655,8 @@ class Engine:
             list_pass = int(self.lib.pmx_quantile_list_pass(S, T, n_seg)) if summary is not None else 2
         tail_after = 3 if (group is not None and summary is not None) else list_pass
         for p in passes:
-            self.launches += 3 if p >= 3 else 2             # hist (two kernels from pass 3 on) + pick
+            # hist + pick; from the list pass on the digit comes from the lists (two kernels), and the list pass itself collects first
+            self.launches += 2 if p < list_pass else (4 if p == list_pass else 3)
             _abi.check(self.lib.pmx_quantile_hist_lp(self.ctx, self._ptr(x), S, T, self._ptr(d_seg), n_seg,
                                                      self._ptr(d_ord), n_rows, n_q, p, list_pass,
                                                      self._ptr(state), self._ptr(hist), self._stream()))

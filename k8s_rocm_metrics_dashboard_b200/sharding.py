@@ -109,7 +109,6 @@ class ShardedEngine:
         self.rank = 0 if alone else dist.get_rank(group)
         self._qbuf = {}
         self._graphs = {}
-        self._graph_launches = 9                                # kernels of ours inside one replay
 
     @staticmethod
     def _qsummary(summary):
@@ -135,8 +134,8 @@ class ShardedEngine:
         return summary, q
 
     def summarize_graph(self, x, seg, n_seg, perm_goff, qs=(0.5, 0.95, 0.99)):
-        """``summarize`` replayed from a CUDA graph (one rank): the nine small launches behind the fused
-        kernel (partials, fold, init, two histogram passes with their picks, tail, finish) are
+        """``summarize`` replayed from a CUDA graph (one rank): the small launches behind the fused kernel
+        (partials, fold, init, the histogram / list passes with their picks, tail, finish) are
         launch-bound, so they are captured once per (buffer, shape) and replayed.  ``x``, ``seg`` and
         ``perm_goff`` must be the same device tensors on every call (the graph reads them in
         place); the returned tensors are the graph's own and are overwritten by the next replay.
@@ -146,21 +145,24 @@ class ShardedEngine:
         hit = self._graphs.get(key)
         if hit is None:
             for _ in range(2):                                  # scratch grows and kernels load outside the capture
+                before = self.eng.launches
                 self.summarize(x, seg, n_seg, perm_goff, qs)
+            n_launches = self.eng.launches - before             # kernels of ours inside one replay
             t.cuda.synchronize()
             try:
                 g = t.cuda.CUDAGraph()
                 with t.cuda.graph(g, capture_error_mode="thread_local"):
                     res = self.summarize(x, seg, n_seg, perm_goff, qs)
-                hit = (g, res, (x, seg, perm_goff))             # the inputs stay alive with the graph
+                self.eng.launches -= n_launches                 # the capture launched nothing
+                hit = (g, res, (x, seg, perm_goff), n_launches)  # the inputs stay alive with the graph
             except Exception:  # noqa: BLE001  -- capture refused: stay eager
                 t.cuda.synchronize()
-                hit = (None, None, None)
+                hit = (None, None, None, 0)
             self._graphs[key] = hit
         if hit[0] is None:
             return self.summarize(x, seg, n_seg, perm_goff, qs)
         hit[0].replay()
-        self.eng.launches += self._graph_launches
+        self.eng.launches += hit[3]
         return hit[1]
 
     def aggregate_step(self, ts, val, off, start_ms, step_ms, n_steps, window_steps, seg, n_seg, perm_goff,
