@@ -335,6 +335,25 @@ int pmx_quantile_pick(pmx_ctx* ctx, const uint64_t* d_hist, int64_t n_seg, const
 int pmx_quantile_finish(pmx_ctx* ctx, const uint64_t* d_state, int64_t n_seg, const double* d_q,
                         int64_t n_q, int64_t* d_n, int64_t* d_lo, int64_t* d_hi,
                         double* d_x_lo, double* d_x_hi, double* d_value, pmx_stream stream);
+/* One GPU: the per-segment summary of pmx_group_reduce(per_step = 0) AND the exact quantiles of
+ * pmx_quantile_select from ONE sweep of d_x (plus a sample of 1/32 of it).  Replaces, for the range
+ * matrices, what app.py:216-221 and :335-345 compute for the instant vector (mean / max / min per
+ * metric) together with SURVEY X7's Series.quantile -- the reference has no counterpart of the
+ * quantiles.  A sample fixes a bracket of two data values around each quantile; the sweep forms
+ * the per-series partial sums (same order as pmx_group_reduce: d_sum .. d_mean agree bit for bit),
+ * counts what lies below / on the bounds and copies the keys strictly inside; the order statistics
+ * are then selected from those few keys.  The result is exact whenever the counts confirm the
+ * brackets; *d_failed (device int32) is the number of (segment, quantile) pairs for which they did
+ * not -- a sample more than five standard deviations off, or more than 256 MiB / n_seg of keys
+ * inside one segment's brackets -- and those pairs hold NaN: when it is not zero, use
+ * pmx_group_reduce + the pmx_quantile_* passes instead.  d_perm / d_goff: the CSR over series of
+ * pmx_group_reduce; d_seg[s] = group of series s (or -1); n_q in [1, 4] (else PMX_E_LIMIT).
+ * Outputs as in pmx_group_reduce and pmx_quantile_finish (each may be NULL except d_count). */
+int pmx_summary_quantiles(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
+                          const int32_t* d_seg, int64_t n_seg, const int32_t* d_perm, const int64_t* d_goff,
+                          const double* d_q, int64_t n_q, double* d_sum, int64_t* d_count, double* d_min,
+                          double* d_max, double* d_mean, int64_t* d_n, int64_t* d_lo, int64_t* d_hi,
+                          double* d_x_lo, double* d_x_hi, double* d_value, int32_t* d_failed, pmx_stream stream);
 /* Single-GPU convenience: all passes back to back (no collective); hist/state in ctx scratch. */
 int pmx_quantile_select(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
                         const int32_t* d_seg, int64_t n_seg,

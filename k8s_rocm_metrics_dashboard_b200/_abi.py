@@ -88,6 +88,7 @@ SIGNATURES = {
     "pmx_quantile_pick": (_int, [_p, _p, _i64, _p, _i64, _int, _p, _p]),
     "pmx_quantile_finish": (_int, [_p, _p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _p]),
     "pmx_quantile_select": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _p]),
+    "pmx_summary_quantiles": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _p, _p, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
 }
 
 _lib = None

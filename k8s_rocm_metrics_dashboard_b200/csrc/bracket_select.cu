@@ -1,0 +1,601 @@
+// bracket_select.cu -- per-segment summary (sum / count / min / max / mean) AND exact quantiles of an
+// [S, T] matrix in ONE sweep of the data (SURVEY X6 + X7 on one GPU; the pandas forms are
+// groupby(...).agg(['sum','count','min','max','mean']) and Series.quantile, which the reference's
+// app.py:216-221 / :335-345 do for the instant vector).
+//
+// A radix selection reads the data once per digit, after a first read for the summary.  Here a
+// small sample (one value per 32 steps of every row, at a hashed position) fixes, per quantile, a
+// bracket [lo, hi] of two sample VALUES that holds the wanted order statistics unless the sample is
+// off by more than five standard deviations.  One sweep of the data then
+//   (a) forms the per-series partial sums exactly as pmx_group_reduce does (reduce_part.cuh),
+//   (b) counts, per bracket, the values below lo, equal to lo and equal to hi, and
+//   (c) copies the keys of the values strictly inside (lo, hi) -- a few per cent -- to a list.
+// The order statistic of rank k is lo, hi, or the (k - below - equal_lo)-th smallest key of the list:
+// exact whenever the counts place k inside the bracket, which the last kernel checks.  A segment
+// where they do not (or whose list overflowed) is counted in *d_failed and gets NaN; the caller then
+// runs the per-pass selection (pmx_group_reduce + pmx_quantile_*), which needs no luck.
+// Repeated values cost nothing: bounds are data values, and what equals a bound is counted, not
+// copied.  -0.0 and +0.0 compare equal in (b); when a bound is zero the sweep also counts the
+// negative zeros so that the run of zeros can be split in key order (-0.0 first).
+#include <math.h>
+#include "pmx_common.cuh"
+#include "quantile_keys.cuh"
+#include "reduce_part.cuh"
+#include <cooperative_groups.h>
+
+namespace {
+
+constexpr int BS_MAX_Q = 4;
+constexpr int BS_BINS = 2048;
+constexpr int BS_STRIDE = 32;                    // one sampled value per this many steps of a row
+constexpr double BS_SIGMAS = 5.0;
+constexpr int BS_SMALL = 256;                    // a bucket this small is ranked directly
+constexpr int BS_WBUF = 576;                     // values a warp can stage: 256 kept + a trip of 8 per lane + head and tail
+
+struct BsSeg {                                   // per segment
+  double lo[BS_MAX_Q], hi[BS_MAX_Q];             // bracket bounds: sample values, or -inf / +inf
+  unsigned long long below[BS_MAX_Q], eq_lo[BS_MAX_Q], eq_hi[BS_MAX_Q];
+  unsigned long long neg_zero;                   // -0.0 values (counted only when a bound is zero)
+  unsigned int list_n;                           // keys appended to the list (may exceed its capacity)
+  unsigned int zero_bound;
+};
+
+__device__ __forceinline__ uint64_t bs_hash(uint64_t h) {
+  h ^= h >> 33; h *= 0xff51afd7ed558ccdULL; h ^= h >> 33; h *= 0xc4ceb9fe1a85ec53ULL; h ^= h >> 33;
+  return h;
+}
+
+// sample slot (row, i): one hashed position in the i-th stretch of BS_STRIDE steps of the row
+__global__ void __launch_bounds__(256)
+bs_sample_kernel(const double* __restrict__ x, int64_t T, int64_t n_series, int64_t P, double* __restrict__ samp) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n_series * P) return;
+  const int64_t row = idx / P, i = idx - row * P;
+  const int64_t first = i * BS_STRIDE;
+  const int64_t span = T - first < BS_STRIDE ? T - first : BS_STRIDE;
+  const int64_t pos = first + (int64_t)(bs_hash((uint64_t)row * 0x9E3779B97F4A7C15ULL + (uint64_t)i) % (uint64_t)span);
+  samp[idx] = x[row * T + pos];
+}
+
+// block-wide exclusive scan of BS_BINS counters by 1024 threads, two bins (c0, c1) each; returns
+// this thread's exclusive base.  s_warp: 32 words.
+__device__ __forceinline__ unsigned bs_scan2(unsigned c0, unsigned c1, unsigned* s_warp) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned sum = c0 + c1;
+  unsigned inc = sum;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) { const unsigned v = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += v; }
+  __syncthreads();                               // s_warp may still be read from the previous scan
+  if (lane == 31) s_warp[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {                               // exclusive scan of the 32 warp totals
+    const unsigned t = s_warp[lane];
+    unsigned w = t;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const unsigned v = __shfl_up_sync(0xffffffffu, w, d); if (lane >= d) w += v; }
+    s_warp[lane] = w - t;
+  }
+  __syncthreads();
+  return s_warp[warp] + inc - sum;
+}
+__device__ __forceinline__ unsigned bs_scan(const unsigned* h, unsigned* s_warp, unsigned& c0, unsigned& c1) {
+  c0 = h[2 * threadIdx.x]; c1 = h[2 * threadIdx.x + 1];
+  return bs_scan2(c0, c1, s_warp);
+}
+
+// A cluster of BS_CL CTAs per segment: the sample values of the brackets.  Every CTA keeps an
+// eighth of the segment's sample as keys in its shared memory; histograms and extremes are
+// exchanged through distributed shared memory, and every CTA repeats the (cheap) scans and picks,
+// so nothing has to be broadcast.  For quantile q of m valid sample values the bracket is
+// [value of sample rank floor(q(m-1) - d), value of sample rank ceil(q(m-1) + d) + 1],
+// d = 5 sqrt(m q (1-q)) + 3, rounded outwards to the smallest / largest sample value that shares the
+// first 22 significant key bits with it (two histogram sweeps instead of six); a rank outside the
+// sample leaves that side open (-inf / +inf).  Also clears the segment's counters.
+constexpr int BS_CL = 8;
+constexpr unsigned BS_KCAP = 12288;              // keys per CTA (96 KiB); a larger sample is thinned
+__global__ void __cluster_dims__(BS_CL, 1, 1) __launch_bounds__(1024)
+bs_bounds_kernel(const double* __restrict__ samp, int64_t P, const int32_t* __restrict__ perm,
+                 const int64_t* __restrict__ goff, const double* __restrict__ q, int n_q, BsSeg* __restrict__ segs) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  extern __shared__ __align__(16) unsigned char bs_smem[];
+  unsigned long long* sk = reinterpret_cast<unsigned long long*>(bs_smem);            // [BS_KCAP]
+  unsigned int* sh_hist = reinterpret_cast<unsigned int*>(sk + BS_KCAP);              // [2 n_q][BS_BINS]
+  __shared__ unsigned int s_warp[32];
+  __shared__ unsigned long long x_min, x_max, x_key[2 * BS_MAX_Q];                    // read by the other CTAs
+  __shared__ unsigned int x_n;
+  __shared__ unsigned long long s_key[2 * BS_MAX_Q];
+  __shared__ long long s_rank[2 * BS_MAX_Q];     // sample rank wanted (-1: open side)
+  __shared__ unsigned int s_bin1[2 * BS_MAX_Q], s_bin2[2 * BS_MAX_Q];
+  __shared__ int s_u[2 * BS_MAX_Q], s_nu;
+  __shared__ unsigned int s_ubin[2 * BS_MAX_Q];
+  const int g = blockIdx.x / BS_CL;
+  const unsigned rank = cluster.block_rank();
+  const int n_t = 2 * n_q;
+  const int64_t k0 = goff[g], rows = goff[g + 1] - k0;
+  // slots of the segment: (row r of the group, slot i of the row); thinned to BS_CL * BS_KCAP at most
+  const uint64_t slots = (uint64_t)rows * (uint64_t)P;
+  const uint64_t skip = (slots + (uint64_t)BS_CL * BS_KCAP - 1) / ((uint64_t)BS_CL * BS_KCAP) > 0
+                            ? (slots + (uint64_t)BS_CL * BS_KCAP - 1) / ((uint64_t)BS_CL * BS_KCAP) : 1;
+  const uint64_t used = (slots + skip - 1) / skip;                                   // <= BS_CL * BS_KCAP
+  const unsigned per = (unsigned)((used + BS_CL - 1) / BS_CL);                        // <= BS_KCAP
+  if (threadIdx.x == 0) { x_min = ~0ULL; x_max = 0; x_n = 0; }
+  __syncthreads();
+  {
+    unsigned long long mn = ~0ULL, mx = 0;
+    const uint64_t a = (uint64_t)rank * per, b = a + per < used ? a + per : used;
+    for (uint64_t u = a + threadIdx.x; u < b; u += blockDim.x) {
+      const uint64_t idx = u * skip;
+      uint64_t r, i;
+      if (slots <= 0xffffffffULL) { r = (unsigned)idx / (unsigned)P; i = (unsigned)idx - (unsigned)r * (unsigned)P; }
+      else { r = idx / (uint64_t)P; i = idx - r * (uint64_t)P; }
+      const double v = samp[(int64_t)perm[k0 + (int64_t)r] * P + (int64_t)i];
+      if (v != v) continue;
+      const uint64_t key = f64_key(v);
+      sk[atomicAdd(&x_n, 1u)] = key;
+      mn = key < mn ? key : mn; mx = key > mx ? key : mx;
+    }
+    if (mn != ~0ULL) { atomicMin(&x_min, mn); atomicMax(&x_max, mx); }
+  }
+  cluster.sync();
+  const unsigned n_local = x_n;
+  unsigned m = 0; uint64_t kmin = ~0ULL, kmax = 0;
+  for (int r = 0; r < BS_CL; ++r) {
+    m += *cluster.map_shared_rank(&x_n, r);
+    const uint64_t a = *cluster.map_shared_rank(&x_min, r), b = *cluster.map_shared_rank(&x_max, r);
+    kmin = a < kmin ? a : kmin; kmax = b > kmax ? b : kmax;
+  }
+  if (threadIdx.x < n_t) {
+    const int j = threadIdx.x >> 1;
+    long long r = -1;
+    if (m > 0) {
+      const double qq = q[j], a = qq * (double)(m - 1), d = BS_SIGMAS * sqrt((double)m * qq * (1.0 - qq)) + 3.0;
+      if (threadIdx.x & 1) { const double h = ceil(a + d) + 1.0; r = h > (double)(m - 1) ? -1 : (long long)h; }
+      else { const double l = floor(a - d); r = l < 0.0 ? -1 : (long long)l; }
+    }
+    s_rank[threadIdx.x] = r;
+    x_key[threadIdx.x] = (threadIdx.x & 1) ? 0ULL : ~0ULL;       // max / min accumulators of the last sweep
+    s_bin1[threadIdx.x] = 0; s_bin2[threadIdx.x] = 0;
+  }
+  __syncthreads();
+  const bool spread = m > 0 && kmax > kmin;
+  const int Z = spread ? __clzll((long long)(kmax - kmin)) : 0;
+  if (spread) {
+    // first 11 significant bits: one histogram for all ranks
+    for (int i = threadIdx.x; i < BS_BINS; i += blockDim.x) sh_hist[i] = 0;
+    __syncthreads();
+    for (unsigned i = threadIdx.x; i < n_local; i += blockDim.x) atomicAdd(&sh_hist[(unsigned)(((sk[i] - kmin) << Z) >> 53)], 1u);
+    cluster.sync();
+    {
+      long long rr[2 * BS_MAX_Q];                // read before the scan's barriers: the finder of a rank rewrites it
+#pragma unroll
+      for (int t = 0; t < 2 * BS_MAX_Q; ++t) rr[t] = t < n_t ? s_rank[t] : -1;
+      unsigned c0 = 0, c1 = 0;
+      for (int r = 0; r < BS_CL; ++r) {
+        const uint2 c = *reinterpret_cast<const uint2*>(cluster.map_shared_rank(sh_hist, r) + 2 * threadIdx.x);
+        c0 += c.x; c1 += c.y;
+      }
+      const unsigned base = bs_scan2(c0, c1, s_warp);
+#pragma unroll
+      for (int t = 0; t < 2 * BS_MAX_Q; ++t) {
+        const long long r = rr[t];
+        if (r < 0) continue;
+        if ((unsigned long long)r >= base && (unsigned long long)r < base + c0) { s_bin1[t] = 2 * threadIdx.x; s_rank[t] = r - base; }
+        else if ((unsigned long long)r >= base + c0 && (unsigned long long)r < base + c0 + c1) { s_bin1[t] = 2 * threadIdx.x + 1; s_rank[t] = r - base - c0; }
+      }
+    }
+    cluster.sync();                              // every CTA has read every histogram
+    // next 11 bits: one histogram per distinct first digit among the ranks
+    if (threadIdx.x == 0) {
+      int nu = 0;
+      for (int t = 0; t < n_t; ++t) {
+        s_u[t] = -1;
+        if (s_rank[t] < 0) continue;
+        int u = 0;
+        while (u < nu && s_ubin[u] != s_bin1[t]) ++u;
+        if (u == nu) s_ubin[nu++] = s_bin1[t];
+        s_u[t] = u;
+      }
+      s_nu = nu;
+    }
+    __syncthreads();
+    const int nu = s_nu;
+    for (int i = threadIdx.x; i < nu * BS_BINS; i += blockDim.x) sh_hist[i] = 0;
+    __syncthreads();
+    unsigned ub[2 * BS_MAX_Q];
+#pragma unroll
+    for (int u = 0; u < 2 * BS_MAX_Q; ++u) ub[u] = u < nu ? s_ubin[u] : 0xffffffffu;
+    for (unsigned i = threadIdx.x; i < n_local; i += blockDim.x) {
+      const uint64_t rel = (sk[i] - kmin) << Z;
+      const unsigned d1 = (unsigned)(rel >> 53), d2 = (unsigned)(rel >> 42) & (BS_BINS - 1);
+#pragma unroll
+      for (int u = 0; u < 2 * BS_MAX_Q; ++u) if (d1 == ub[u]) atomicAdd(&sh_hist[u * BS_BINS + d2], 1u);
+    }
+    cluster.sync();
+    for (int u = 0; u < nu; ++u) {
+      unsigned c0 = 0, c1 = 0;
+      for (int r = 0; r < BS_CL; ++r) {
+        const uint2 c = *reinterpret_cast<const uint2*>(cluster.map_shared_rank(sh_hist, r) + u * BS_BINS + 2 * threadIdx.x);
+        c0 += c.x; c1 += c.y;
+      }
+      const unsigned base = bs_scan2(c0, c1, s_warp);
+      for (int t = 0; t < n_t; ++t) {
+        if (s_u[t] != u) continue;
+        const unsigned long long r = (unsigned long long)s_rank[t];
+        if (r >= base && r < base + c0) s_bin2[t] = 2 * threadIdx.x;
+        else if (r >= base + c0 && r < base + c0 + c1) s_bin2[t] = 2 * threadIdx.x + 1;
+      }
+    }
+    __syncthreads();
+    // outwards to a sample value: the smallest key of the bucket for a lower bound, the largest for an upper
+    unsigned tp[2 * BS_MAX_Q];                    // 22-bit prefix of each closed rank (an open one matches nothing)
+#pragma unroll
+    for (int t = 0; t < 2 * BS_MAX_Q; ++t) tp[t] = (t < n_t && s_rank[t] >= 0) ? ((s_bin1[t] << 11) | s_bin2[t]) : 0xffffffffu;
+    for (unsigned i = threadIdx.x; i < n_local; i += blockDim.x) {
+      const uint64_t key = sk[i];
+      const unsigned pf = (unsigned)(((key - kmin) << Z) >> 42);
+#pragma unroll
+      for (int t = 0; t < 2 * BS_MAX_Q; ++t) {
+        if (pf != tp[t]) continue;
+        if (t & 1) { if (key > *(volatile unsigned long long*)&x_key[t]) atomicMax(&x_key[t], key); }
+        else { if (key < *(volatile unsigned long long*)&x_key[t]) atomicMin(&x_key[t], key); }
+      }
+    }
+    cluster.sync();
+    if (threadIdx.x < n_t) {
+      unsigned long long k = (threadIdx.x & 1) ? 0ULL : ~0ULL;
+      for (int r = 0; r < BS_CL; ++r) {
+        const unsigned long long o = *cluster.map_shared_rank(&x_key[threadIdx.x], r);
+        k = (threadIdx.x & 1) ? (o > k ? o : k) : (o < k ? o : k);
+      }
+      s_key[threadIdx.x] = k;
+    }
+  } else if (threadIdx.x < n_t) {
+    s_key[threadIdx.x] = kmin;                   // every sample value is the same (or there is none)
+  }
+  cluster.sync();                                // no CTA leaves while its shared memory may still be read
+  if (rank == 0 && threadIdx.x == 0) {
+    BsSeg& b = segs[g];
+    const double INF = __longlong_as_double(0x7FF0000000000000LL);
+    unsigned zb = 0;
+    for (int j = 0; j < BS_MAX_Q; ++j) {
+      double lo = pmx_nan(), hi = pmx_nan();
+      if (j < n_q) {
+        lo = s_rank[2 * j] < 0 ? -INF : key_f64(s_key[2 * j]);
+        hi = s_rank[2 * j + 1] < 0 ? INF : key_f64(s_key[2 * j + 1]);
+        if (lo == 0.0 || hi == 0.0) zb = 1;
+      }
+      b.lo[j] = lo; b.hi[j] = hi; b.below[j] = 0; b.eq_lo[j] = 0; b.eq_hi[j] = 0;
+    }
+    b.neg_zero = 0; b.list_n = 0; b.zero_bound = zb;
+  }
+}
+
+// The sweep: one CTA per series.  Partial sums in pmx_group_reduce's order, bracket counters, and the
+// keys strictly inside a bracket appended to the segment's list (staged per warp).
+template <int NB>
+__global__ void __launch_bounds__(PMX_ROW_THREADS)
+bs_sweep_kernel(const double* __restrict__ x, int64_t T, const int32_t* __restrict__ seg, Part* __restrict__ part,
+                BsSeg* __restrict__ segs, unsigned long long* __restrict__ lists, unsigned cap) {
+  __shared__ Part sh_part[8];
+  constexpr int NW = PMX_ROW_THREADS / 32;
+  __shared__ unsigned long long s_buf[NW][BS_WBUF];
+  __shared__ unsigned int s_cnt[NW][3 * NB + 1];
+  const int64_t s = blockIdx.x;
+  const int g = seg[s];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  double lo[NB], hi[NB];
+  bool zb = false;
+#pragma unroll
+  for (int j = 0; j < NB; ++j) { lo[j] = pmx_nan(); hi[j] = pmx_nan(); }
+  if (g >= 0) {
+#pragma unroll
+    for (int j = 0; j < NB; ++j) { lo[j] = segs[g].lo[j]; hi[j] = segs[g].hi[j]; }
+    zb = segs[g].zero_bound != 0;
+  }
+  unsigned c_lt[NB], c_el[NB], c_eh[NB], c_nz = 0;
+#pragma unroll
+  for (int j = 0; j < NB; ++j) { c_lt[j] = 0; c_el[j] = 0; c_eh[j] = 0; }
+  unsigned long long* wbuf = s_buf[warp];
+  unsigned wcnt = 0;                             // warp-uniform
+  // The warp's staged values (all inside a closed bracket [lo, hi]) are sorted out 32 at a time, every
+  // lane busy: equal to a bound -> counted; strictly inside -> its key stays, compacted in place;
+  // then one atomic reserves the room in the segment's list and the keys leave coalesced.
+  auto flush = [&]() {
+    if (wcnt == 0) return;
+    unsigned nmid = 0;
+    for (unsigned i0 = 0; i0 < wcnt; i0 += 32) {
+      const unsigned i = i0 + lane;
+      const double v = i < wcnt ? __longlong_as_double((long long)wbuf[i]) : pmx_nan();
+      bool mid = false;
+#pragma unroll
+      for (int j = 0; j < NB; ++j) {
+        if (v == lo[j]) ++c_el[j];
+        if (v == hi[j]) ++c_eh[j];
+        mid |= v > lo[j] && v < hi[j];
+      }
+      if (zb && (unsigned long long)__double_as_longlong(v) == 0x8000000000000000ULL) ++c_nz;
+      const unsigned any = __ballot_sync(0xffffffffu, mid);
+      __syncwarp();                              // every lane has read its value: slots <= i0 + 31 may be rewritten
+      if (mid) wbuf[nmid + (unsigned)__popc(any & ((1u << lane) - 1u))] = f64_key(v);
+      nmid += (unsigned)__popc(any);
+    }
+    __syncwarp();
+    if (nmid) {
+      unsigned base = 0;
+      if (lane == 0) base = atomicAdd(&segs[g].list_n, nmid);
+      base = __shfl_sync(0xffffffffu, base, 0);
+      for (unsigned i = lane; i < nmid; i += 32)
+        if (base + i < cap) lists[(size_t)g * cap + base + i] = wbuf[i];
+    }
+    __syncwarp();
+    wcnt = 0;
+  };
+  // Per value: one comparison and one counter per bracket (below lo) and one comparison more to see
+  // whether it lies in a closed bracket [lo, hi] -- a few per cent of the values, or the repeats of
+  // a bound; those are staged as they are.  NaN fails every comparison.
+  const Part mine = row_partial(x + s * T, T, [&](double v) {
+    bool in = false;
+#pragma unroll
+    for (int j = 0; j < NB; ++j) {
+      const bool lt = v < lo[j];
+      if (lt) ++c_lt[j];
+      in |= !lt && v <= hi[j];
+    }
+    const unsigned any = __ballot_sync(0xffffffffu, in);
+    if (any) {
+      if (in) wbuf[wcnt + (unsigned)__popc(any & ((1u << lane) - 1u))] = (unsigned long long)__double_as_longlong(v);
+      wcnt += (unsigned)__popc(any);
+    }
+  }, [&]() { if (wcnt > 256) flush(); });
+  const Part r = cta_part(mine, sh_part);
+  if (threadIdx.x == 0) part[s] = r;
+  if (g < 0) return;
+  flush();
+  // counters: warp sums, then one 64-bit atomic per counter and CTA
+#pragma unroll
+  for (int j = 0; j < NB; ++j) {
+    const unsigned a = __reduce_add_sync(0xffffffffu, c_lt[j]), b = __reduce_add_sync(0xffffffffu, c_el[j]),
+                   c = __reduce_add_sync(0xffffffffu, c_eh[j]);
+    if (lane == 0) { s_cnt[warp][3 * j] = a; s_cnt[warp][3 * j + 1] = b; s_cnt[warp][3 * j + 2] = c; }
+  }
+  {
+    const unsigned z = __reduce_add_sync(0xffffffffu, c_nz);
+    if (lane == 0) s_cnt[warp][3 * NB] = z;
+  }
+  __syncthreads();
+  if (threadIdx.x < 3 * NB + 1) {
+    unsigned long long tot = 0;
+    for (int w = 0; w < NW; ++w) tot += s_cnt[w][threadIdx.x];
+    if (tot) {
+      BsSeg& b = segs[g];
+      unsigned long long* dst = threadIdx.x == 3 * NB ? &b.neg_zero
+                               : (threadIdx.x % 3 == 0 ? &b.below[threadIdx.x / 3]
+                                  : threadIdx.x % 3 == 1 ? &b.eq_lo[threadIdx.x / 3] : &b.eq_hi[threadIdx.x / 3]);
+      atomicAdd(dst, tot);
+    }
+  }
+}
+
+// CTA (quantile j, segment g): place the two ranks of quantile j in their bracket and, where they
+// fall strictly inside, select them from the list; write the outputs of pmx_quantile_finish.
+__global__ void __launch_bounds__(1024)
+bs_resolve_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __restrict__ lists, unsigned cap,
+                  const int64_t* __restrict__ count, const double* __restrict__ q, int n_q,
+                  int64_t* o_n, int64_t* o_lo, int64_t* o_hi, double* o_xlo, double* o_xhi, double* o_val,
+                  unsigned int* __restrict__ failed) {
+  __shared__ unsigned int sh_hist[2][BS_BINS];
+  __shared__ unsigned int s_warp[32];
+  __shared__ unsigned long long s_keys[2 * BS_SMALL];
+  __shared__ unsigned int s_nk, s_mid;
+  __shared__ int s_zone[2];                      // 0 fail, 1 lo, 2 inside, 3 hi
+  __shared__ unsigned long long s_r[2];          // rank inside the list (zone 2) or inside the run of zeros
+  __shared__ unsigned long long s_pf[2], s_ans[2];
+  __shared__ unsigned int s_cb[2];               // keys in the rank's current bucket
+  const int j = blockIdx.x, g = blockIdx.y;
+  const int64_t out = (int64_t)g * n_q + j;
+  const long long n = count[g];
+  if (j == 0 && threadIdx.x == 0 && o_n) o_n[g] = n;
+  auto write = [&](long long klo, long long khi, double a, double b, double v) {
+    if (o_lo) o_lo[out] = klo;
+    if (o_hi) o_hi[out] = khi;
+    if (o_xlo) o_xlo[out] = a;
+    if (o_xhi) o_xhi[out] = b;
+    if (o_val) o_val[out] = v;
+  };
+  if (n <= 0) { if (threadIdx.x == 0) write(-1, -1, pmx_nan(), pmx_nan(), pmx_nan()); return; }
+  const BsSeg& B = segs[g];
+  const double lo = B.lo[j], hi = B.hi[j];
+  const uint64_t klo = f64_key(lo), khi = f64_key(hi);
+  const unsigned long long c_lt = B.below[j], c_el = B.eq_lo[j], c_eh = hi == lo ? 0 : B.eq_hi[j], c_nz = B.neg_zero;
+  const unsigned list_n = B.list_n;
+  const bool overflow = list_n > cap;
+  const unsigned n_list = overflow ? cap : list_n;
+  const unsigned long long* keys = lists + (size_t)g * cap;
+  const double pos = (double)(n - 1) * q[j];
+  unsigned long long k0 = (unsigned long long)floor(pos);
+  if (k0 > (unsigned long long)n - 1) k0 = (unsigned long long)n - 1;
+  const unsigned long long k1 = k0 + 1 < (unsigned long long)n ? k0 + 1 : (unsigned long long)n - 1;
+  const double tt = pos - (double)k0;
+  auto inside = [&](uint64_t key) -> bool { const double v = key_f64(key); return v > lo && v < hi; };   // as the sweep saw it
+  // every key of the list, eight loads in flight per thread
+  auto for_keys = [&](auto&& f) {
+    for (unsigned i0 = 0; i0 < n_list; i0 += blockDim.x * 8) {
+      unsigned long long kk[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) { const unsigned i = i0 + u * blockDim.x + threadIdx.x; kk[u] = i < n_list ? keys[i] : 0ULL; }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) { const unsigned i = i0 + u * blockDim.x + threadIdx.x; if (i < n_list) f(kk[u]); }
+    }
+  };
+  const int Z = khi > klo ? __clzll((long long)(khi - klo)) : 0;
+  // first sweep of the list: the keys strictly inside this bracket, and their first digit
+  for (int i = threadIdx.x; i < BS_BINS; i += blockDim.x) sh_hist[0][i] = 0;
+  if (threadIdx.x == 0) { s_mid = 0; s_nk = 0; }
+  __syncthreads();
+  {
+    unsigned c = 0;
+    for_keys([&](uint64_t key) {
+      if (inside(key)) { ++c; atomicAdd(&sh_hist[0][(unsigned)(((key - klo) << Z) >> 53)], 1u); }
+    });
+    c = __reduce_add_sync(0xffffffffu, c);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(&s_mid, c);
+  }
+  __syncthreads();
+  const unsigned long long c_mid = s_mid;
+  if (threadIdx.x < 2) {
+    const unsigned long long k = threadIdx.x ? k1 : k0;
+    int zone = 0; unsigned long long r = 0;
+    if (k < c_lt) zone = 0;
+    else if (k < c_lt + c_el) { zone = 1; r = k - c_lt; }
+    else if (overflow) zone = 0;                 // the list is cut short: nothing beyond lo can be placed
+    else if (k < c_lt + c_el + c_mid) { zone = 2; r = k - c_lt - c_el; }
+    else if (k < c_lt + c_el + c_mid + c_eh) { zone = 3; r = k - c_lt - c_el - c_mid; }
+    s_zone[threadIdx.x] = zone; s_r[threadIdx.x] = r; s_pf[threadIdx.x] = 0; s_cb[threadIdx.x] = 0;
+    // a bound that is zero stands for the run of -0.0 (first in key order) and +0.0 values
+    if (zone == 1) s_ans[threadIdx.x] = lo == 0.0 ? f64_key(r < c_nz ? -0.0 : 0.0) : klo;
+    if (zone == 3) s_ans[threadIdx.x] = hi == 0.0 ? f64_key(r < c_nz ? -0.0 : 0.0) : khi;
+  }
+  __syncthreads();
+  if (s_zone[0] == 0 || s_zone[1] == 0) {
+    if (threadIdx.x == 0) { atomicAdd(failed, 1u); write((long long)k0, (long long)k1, pmx_nan(), pmx_nan(), pmx_nan()); }
+    return;
+  }
+  if (s_zone[0] == 2 || s_zone[1] == 2) {
+    // radix passes over the inside keys until every wanted rank sits in a bucket of <= BS_SMALL keys
+    int used = 0;                                // digit bits consumed so far
+    for (int pass = 0;; ++pass) {
+      const int bits = 64 - used >= 11 ? 11 : 64 - used;             // of this pass (the low Z bits of rel are zero)
+      const int n_h = (pass == 0 || s_pf[0] == s_pf[1] || s_zone[0] != 2 || s_zone[1] != 2) ? 1 : 2;
+      if (pass > 0) {
+        for (int i = threadIdx.x; i < n_h * BS_BINS; i += blockDim.x) (&sh_hist[0][0])[i] = 0;
+        __syncthreads();
+        const uint64_t p0 = s_zone[0] == 2 ? s_pf[0] : s_pf[1], p1 = s_zone[1] == 2 ? s_pf[1] : s_pf[0];
+        for_keys([&](uint64_t key) {
+          if (!inside(key)) return;
+          const uint64_t rel = (key - klo) << Z;
+          const uint64_t top = rel >> (64 - used);
+          const unsigned d = (unsigned)((rel << used) >> (64 - bits));
+          if (top == p0) atomicAdd(&sh_hist[0][d], 1u);
+          else if (n_h == 2 && top == p1) atomicAdd(&sh_hist[1][d], 1u);
+        });
+        __syncthreads();
+      }
+      for (int h = 0; h < n_h; ++h) {
+        // read before the scan's barriers: the thread that finds a rank's bin rewrites rank and prefix
+        const unsigned long long r0 = s_r[0], r1 = s_r[1], f0 = s_pf[0], f1 = s_pf[1];
+        unsigned c0, c1;
+        const unsigned base = bs_scan(sh_hist[h], s_warp, c0, c1);
+        for (int t = 0; t < 2; ++t) {
+          if (s_zone[t] != 2) continue;
+          const int ht = (n_h == 2 && t == 1) ? 1 : 0;               // the histogram that serves rank t
+          if (ht != h) continue;
+          const unsigned long long r = t ? r1 : r0, f = t ? f1 : f0;
+          if (r >= base && r < (unsigned long long)base + c0) { s_pf[t] = (f << bits) | (2 * threadIdx.x); s_r[t] = r - base; s_cb[t] = c0; }
+          else if (r >= (unsigned long long)base + c0 && r < (unsigned long long)base + c0 + c1) {
+            s_pf[t] = (f << bits) | (2 * threadIdx.x + 1); s_r[t] = r - base - c0; s_cb[t] = c1;
+          }
+        }
+        __syncthreads();
+      }
+      used += bits;
+      const bool small = (s_zone[0] != 2 || s_cb[0] <= BS_SMALL) && (s_zone[1] != 2 || s_cb[1] <= BS_SMALL);
+      if (small || used >= 64 - Z) break;
+    }
+    if (used >= 64 - Z) {
+      // every bit is settled: the prefix is the key (all keys of the bucket are equal)
+      if (threadIdx.x < 2 && s_zone[threadIdx.x] == 2) s_ans[threadIdx.x] = ((s_pf[threadIdx.x] << (64 - used)) >> Z) + klo;
+    } else {
+      // gather the buckets and rank them directly
+      const uint64_t p0 = s_zone[0] == 2 ? s_pf[0] : s_pf[1], p1 = s_zone[1] == 2 ? s_pf[1] : s_pf[0];
+      for_keys([&](uint64_t key) {
+        if (!inside(key)) return;
+        const uint64_t top = ((key - klo) << Z) >> (64 - used);
+        if (top == p0 || top == p1) { const unsigned at = atomicAdd(&s_nk, 1u); if (at < 2 * BS_SMALL) s_keys[at] = key; }
+      });
+      __syncthreads();
+      const unsigned nk = s_nk < 2 * BS_SMALL ? s_nk : 2 * BS_SMALL;
+      for (unsigned i = threadIdx.x; i < nk; i += blockDim.x) {
+        const uint64_t ki = s_keys[i], top = ((ki - klo) << Z) >> (64 - used);
+        unsigned less = 0, eq = 0;
+        for (unsigned u = 0; u < nk; ++u) {
+          const uint64_t ku = s_keys[u];
+          if ((((ku - klo) << Z) >> (64 - used)) == top) { less += ku < ki; eq += ku == ki; }
+        }
+        for (int t = 0; t < 2; ++t)
+          if (s_zone[t] == 2 && s_pf[t] == top && s_r[t] >= less && s_r[t] < (unsigned long long)less + eq) s_ans[t] = ki;
+      }
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const double a = key_f64(s_ans[0]), b = key_f64(s_ans[1]);
+    // numpy _lerp: a + (b-a)*t, and b - (b-a)*(1-t) when t >= 0.5 (no FMA contraction)
+    const double d = __dsub_rn(b, a);
+    double v = __dadd_rn(a, __dmul_rn(d, tt));
+    if (tt >= 0.5) v = __dsub_rn(b, __dmul_rn(d, __dsub_rn(1.0, tt)));
+    write((long long)k0, (long long)k1, a, b, v);
+  }
+}
+
+}  // namespace
+
+extern "C" int pmx_summary_quantiles(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
+                                     const int32_t* d_seg, int64_t n_seg, const int32_t* d_perm, const int64_t* d_goff,
+                                     const double* d_q, int64_t n_q, double* d_sum, int64_t* d_count, double* d_min,
+                                     double* d_max, double* d_mean, int64_t* d_n, int64_t* d_lo, int64_t* d_hi,
+                                     double* d_x_lo, double* d_x_hi, double* d_value, int32_t* d_failed,
+                                     pmx_stream stream) {
+  PMX_REQUIRE(ctx, "ctx is NULL");
+  PMX_REQUIRE(n_series >= 0 && n_steps >= 0 && n_seg >= 0 && n_seg <= 65535, "bad sizes (n_seg <= 65535)");
+  if (n_q < 1 || n_q > BS_MAX_Q) return pmx_fail(PMX_E_LIMIT, "pmx_summary_quantiles: n_q must be in [1, %d]; use pmx_quantile_select", BS_MAX_Q);
+  PMX_REQUIRE(d_failed, "d_failed is NULL");
+  cudaStream_t st = pmx_st(stream);
+  PMX_CUDA(cudaMemsetAsync(d_failed, 0, sizeof(int32_t), st));
+  if (n_seg == 0) return PMX_OK;
+  PMX_REQUIRE(d_goff && d_q && d_count, "NULL buffer");
+  PMX_REQUIRE(n_series == 0 || (d_x && d_seg && d_perm), "NULL buffer");
+  // scratch: per-series partials | per-segment brackets and counters | sample | lists
+  const int64_t P = (n_steps + BS_STRIDE - 1) / BS_STRIDE;
+  Part* part = nullptr;
+  if (n_series > 0) {
+    part = (Part*)pmx_scratch(ctx, PMX_SCR_PARTIALS, (size_t)n_series * sizeof(Part));
+    if (!part) return PMX_E_CUDA;
+  }
+  int64_t cap = ((int64_t)256 << 20) / 8 / n_seg;
+  if (cap > (1 << 22)) cap = 1 << 22;
+  if (cap < 4096) cap = 4096;
+  const size_t seg_bytes = ((size_t)n_seg * sizeof(BsSeg) + 255) & ~size_t(255);
+  const size_t samp_bytes = ((size_t)n_series * (P > 0 ? P : 1) * 8 + 255) & ~size_t(255);
+  unsigned char* scr = (unsigned char*)pmx_scratch(ctx, PMX_SCR_BRACKET, seg_bytes + samp_bytes + (size_t)n_seg * cap * 8);
+  if (!scr) return PMX_E_CUDA;
+  BsSeg* segs = (BsSeg*)scr;
+  double* samp = (double*)(scr + seg_bytes);
+  unsigned long long* lists = (unsigned long long*)(scr + seg_bytes + samp_bytes);
+  const bool data = n_series > 0 && n_steps > 0;
+  if (data) {
+    const int64_t slots = n_series * P;
+    bs_sample_kernel<<<(unsigned)((slots + 255) / 256), 256, 0, st>>>(d_x, n_steps, n_series, P, samp);
+    PMX_LAUNCH_CHECK();
+  }
+  const size_t smem = (size_t)BS_KCAP * 8 + (size_t)2 * n_q * BS_BINS * sizeof(unsigned int);
+  PMX_CUDA(cudaFuncSetAttribute(bs_bounds_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)(BS_KCAP * 8 + 2 * BS_MAX_Q * BS_BINS * sizeof(unsigned int))));
+  bs_bounds_kernel<<<(unsigned)(n_seg * BS_CL), 1024, smem, st>>>(samp, data ? P : 0, d_perm, d_goff, d_q, (int)n_q, segs);
+  PMX_LAUNCH_CHECK();
+  if (data) {
+    switch (n_q) {
+      case 1: bs_sweep_kernel<1><<<(unsigned)n_series, PMX_ROW_THREADS, 0, st>>>(d_x, n_steps, d_seg, part, segs, lists, (unsigned)cap); break;
+      case 2: bs_sweep_kernel<2><<<(unsigned)n_series, PMX_ROW_THREADS, 0, st>>>(d_x, n_steps, d_seg, part, segs, lists, (unsigned)cap); break;
+      case 3: bs_sweep_kernel<3><<<(unsigned)n_series, PMX_ROW_THREADS, 0, st>>>(d_x, n_steps, d_seg, part, segs, lists, (unsigned)cap); break;
+      default: bs_sweep_kernel<4><<<(unsigned)n_series, PMX_ROW_THREADS, 0, st>>>(d_x, n_steps, d_seg, part, segs, lists, (unsigned)cap); break;
+    }
+    PMX_LAUNCH_CHECK();
+  }
+  if (int rc = pmx_internal_group_fold(part, d_perm, d_goff, n_seg, d_sum, d_count, d_min, d_max, d_mean, st)) return rc;
+  dim3 grid((unsigned)n_q, (unsigned)n_seg);
+  bs_resolve_kernel<<<grid, 1024, 0, st>>>(segs, lists, (unsigned)cap, d_count, d_q, (int)n_q, d_n, d_lo, d_hi, d_x_lo, d_x_hi,
+                                           d_value, (unsigned int*)d_failed);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}

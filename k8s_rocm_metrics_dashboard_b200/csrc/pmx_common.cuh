@@ -11,11 +11,11 @@ struct pmx_ctx {
   // grow-only device scratch, one block per purpose so that they can live side by side:
   // 0 = per-series partials of pmx_group_reduce, 1 = state + histograms of pmx_quantile_select,
   // 2 = candidate keys kept between the passes of a quantile selection, 3 = per-chunk summaries of
-  // pmx_tokenize_device
-  void* scratch[4];
-  size_t scratch_bytes[4];
+  // pmx_tokenize_device, 4 = brackets, sample and lists of pmx_summary_quantiles
+  void* scratch[5];
+  size_t scratch_bytes[5];
 };
-enum { PMX_SCR_PARTIALS = 0, PMX_SCR_QSELECT = 1, PMX_SCR_QCAND = 2, PMX_SCR_TOKENIZE = 3, PMX_SCR_SLOTS = 4 };
+enum { PMX_SCR_PARTIALS = 0, PMX_SCR_QSELECT = 1, PMX_SCR_QCAND = 2, PMX_SCR_TOKENIZE = 3, PMX_SCR_BRACKET = 4, PMX_SCR_SLOTS = 5 };
 
 // error plumbing (ctx.cu)
 int pmx_fail(int code, const char* fmt, ...);

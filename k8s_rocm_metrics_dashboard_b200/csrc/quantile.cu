@@ -23,20 +23,13 @@
 // [2] base key, then per target t: [3+2t] prefix, [4+2t] remaining rank inside the prefix bucket.
 #include <stdlib.h>
 #include "pmx_common.cuh"
+#include "quantile_keys.cuh"
 
 namespace {
 
 constexpr int BINS = PMX_QUANTILE_BINS;
 constexpr int MAX_TARGETS = 16;
 
-__device__ __forceinline__ uint64_t f64_key(double v) {
-  const uint64_t b = (uint64_t)__double_as_longlong(v);
-  return (b >> 63) ? ~b : (b | 0x8000000000000000ULL);
-}
-__device__ __forceinline__ double key_f64(uint64_t k) {
-  const uint64_t b = (k >> 63) ? (k & 0x7fffffffffffffffULL) : ~k;
-  return __longlong_as_double((long long)b);
-}
 __host__ __device__ __forceinline__ int digit_shift(int pass) { return pass < 5 ? 53 - 11 * pass : 0; }
 __host__ __device__ __forceinline__ int digit_bits(int pass) { return pass < 5 ? 11 : 9; }
 

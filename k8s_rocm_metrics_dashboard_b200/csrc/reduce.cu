@@ -5,28 +5,12 @@
 // series order -- the order pandas' object-dtype column reductions use at app.py:218-220.
 #include <math.h>
 #include "pmx_common.cuh"
+#include "reduce_part.cuh"
 
 namespace {
 
-struct Part { double sum; double mn; double mx; long long cnt; };
-
 __device__ __forceinline__ void part_add(Part& p, double v) {
   if (v == v) { p.sum += v; p.mn = fmin(p.mn, v); p.mx = fmax(p.mx, v); p.cnt++; }
-}
-__device__ __forceinline__ void part_merge(Part& a, const Part& b) {
-  a.sum += b.sum; a.mn = fmin(a.mn, b.mn); a.mx = fmax(a.mx, b.mx); a.cnt += b.cnt;
-}
-__device__ __forceinline__ Part part_identity() {
-  const double INF = __longlong_as_double(0x7FF0000000000000LL);
-  return Part{0.0, INF, -INF, 0};
-}
-__device__ __forceinline__ Part part_shfl_down(const Part& p, int d) {
-  Part q;
-  q.sum = __shfl_down_sync(0xffffffffu, p.sum, d);
-  q.mn = __shfl_down_sync(0xffffffffu, p.mn, d);
-  q.mx = __shfl_down_sync(0xffffffffu, p.mx, d);
-  q.cnt = __shfl_down_sync(0xffffffffu, p.cnt, d);
-  return q;
 }
 
 // Scratch of pmx_group_reduce_noalloc: lives in the library image, so no allocation is ever made
@@ -36,61 +20,13 @@ static __device__ __align__(256) unsigned char g_noalloc_partials[NOALLOC_MAX_SE
 constexpr int NOALLOC_MAX_DEVICES = 64;
 static Part* g_noalloc_addr[NOALLOC_MAX_DEVICES];      // device address of the array, per CUDA device
 
-__device__ __forceinline__ void ld4(const double* p, double& a, double& b, double& c, double& d) {
-  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p));
-}
-
-// one CTA per series: partial (sum, min, max, count) over all steps -> part[s].
-// The row is read as 32-byte groups (two per thread in flight) between a scalar head and tail; the
-// order in which a thread meets its values is fixed by the row's address and length alone.
-// The inner loop is branch-free: a NaN adds +0.0 (the sum starts at +0.0 and can never be -0.0, so
-// that changes no bit), fails both comparisons and is not counted -- 11 instructions per value
-// instead of the 38 of the fmin/fmax/int64 form, which kept this read at 0.75 of the copy rate.
-struct Acc { double sum, mn, mx; int cnt; };
-__device__ __forceinline__ void acc_add(Acc& p, double v) {
-  const bool ok = v == v;
-  p.sum += ok ? v : 0.0;
-  p.mn = v < p.mn ? v : p.mn;
-  p.mx = v > p.mx ? v : p.mx;
-  p.cnt += ok ? 1 : 0;
-}
-__global__ void __launch_bounds__(256)
+// one CTA per series: partial (sum, min, max, count) over all steps -> part[s]  (reduce_part.cuh)
+__global__ void __launch_bounds__(PMX_ROW_THREADS)
 series_partial_kernel(const double* __restrict__ x, int64_t n_steps, Part* __restrict__ part) {
   const int64_t s = blockIdx.x;
-  const double* xr = x + s * n_steps;
-  Part p = part_identity();
-  int64_t head = (int64_t)((0 - (reinterpret_cast<uintptr_t>(xr) >> 3)) & 3);   // values before a 32-byte boundary
-  if (head > n_steps) head = n_steps;
-  if ((int64_t)threadIdx.x < head) part_add(p, xr[threadIdx.x]);
-  const double* xb = xr + head;
-  const int64_t nb = (n_steps - head) >> 2;                                     // whole groups of four
-  // counts are kept in 32 bits for 2^28 groups at a time (a thread meets at most 2^31 values in between)
-  for (int64_t g0 = 0; g0 < nb; g0 += (int64_t)1 << 28) {
-    const int64_t g1 = g0 + ((int64_t)1 << 28) < nb ? g0 + ((int64_t)1 << 28) : nb;
-    Acc a{p.sum, p.mn, p.mx, 0};
-    for (int64_t g = g0 + threadIdx.x; g < g1; g += 2 * blockDim.x) {
-      double a0, a1, a2, a3, b0, b1, b2, b3;
-      const int64_t g2 = g + blockDim.x;
-      ld4(xb + 4 * g, a0, a1, a2, a3);
-      if (g2 < g1) ld4(xb + 4 * g2, b0, b1, b2, b3);
-      acc_add(a, a0); acc_add(a, a1); acc_add(a, a2); acc_add(a, a3);
-      if (g2 < g1) { acc_add(a, b0); acc_add(a, b1); acc_add(a, b2); acc_add(a, b3); }
-    }
-    p.sum = a.sum; p.mn = a.mn; p.mx = a.mx; p.cnt += a.cnt;
-  }
-  const int64_t tail = head + 4 * nb + threadIdx.x;
-  if (tail < n_steps) part_add(p, xr[tail]);
-#pragma unroll
-  for (int d = 16; d >= 1; d >>= 1) { Part q = part_shfl_down(p, d); part_merge(p, q); }
   __shared__ Part sh[8];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (lane == 0) sh[warp] = p;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    Part r = sh[0];
-    for (int w = 1; w < (int)(blockDim.x >> 5); ++w) part_merge(r, sh[w]);
-    part[s] = r;
-  }
+  const Part r = cta_part(row_partial(x + s * n_steps, n_steps, [](double) {}, []() {}), sh);
+  if (threadIdx.x == 0) part[s] = r;
 }
 
 // one warp per group: lane l folds the partials of the group's series l, l+32, ... in order, then
@@ -191,6 +127,16 @@ __global__ void group_combine_kernel(const double* __restrict__ all, int world, 
 
 }  // namespace
 
+int pmx_internal_group_fold(const Part* part, const int32_t* d_perm, const int64_t* d_goff, int64_t n_groups,
+                            double* d_sum, int64_t* d_count, double* d_min, double* d_max, double* d_mean,
+                            cudaStream_t st) {
+  if (n_groups <= 0) return PMX_OK;
+  group_fold_kernel<<<(unsigned)((n_groups + 3) / 4), 128, 0, st>>>(part, d_perm, d_goff, n_groups, d_sum, d_count,
+                                                                      d_min, d_max, d_mean);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
 extern "C" {
 
 int pmx_group_index(const int32_t* h_group_id, int64_t n_series, int64_t n_groups, int32_t* h_perm,
@@ -238,7 +184,7 @@ int pmx_group_reduce(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t 
   if (n_series > 0) {
     part = (Part*)pmx_scratch(ctx, PMX_SCR_PARTIALS, (size_t)n_series * sizeof(Part));
     if (!part) return PMX_E_CUDA;
-    series_partial_kernel<<<(unsigned)n_series, 256, 0, st>>>(d_x, n_steps, part);
+    series_partial_kernel<<<(unsigned)n_series, PMX_ROW_THREADS, 0, st>>>(d_x, n_steps, part);
     PMX_LAUNCH_CHECK();
   }
   group_fold_kernel<<<(unsigned)((n_groups + 3) / 4), 128, 0, st>>>(part, d_perm, d_goff, n_groups, d_sum, d_count,
@@ -282,7 +228,7 @@ int pmx_group_reduce_noalloc(const double* d_x, int64_t n_series, int64_t n_step
   Part* part = g_noalloc_addr[dev];
   cudaStream_t st = pmx_st(stream);
   if (n_series > 0) {
-    series_partial_kernel<<<(unsigned)n_series, 256, 0, st>>>(d_x, n_steps, part);
+    series_partial_kernel<<<(unsigned)n_series, PMX_ROW_THREADS, 0, st>>>(d_x, n_steps, part);
     PMX_LAUNCH_CHECK();
   }
   group_fold_kernel<<<(unsigned)((n_groups + 3) / 4), 128, 0, st>>>(part, d_perm, d_goff, n_groups, d_sum, d_count,

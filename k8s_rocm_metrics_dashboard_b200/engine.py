@@ -556,6 +556,42 @@ class Engine:
         return out
 
     # ------------------------------------------------------------------ K6
+    def summary_quantiles(self, x, seg, n_seg, qs, perm_goff):
+        """One GPU: ``group_reduce(x, ..., perm_goff)`` and ``quantiles(x, seg, n_seg, qs)`` from ONE sweep
+        of ``x`` (pmx_summary_quantiles: sampled brackets, counted and verified on the device).  Returns
+        ((sum, count, min, max, mean), quantiles dict, failed) -- ``failed`` is an int32 device tensor [1]:
+        the outputs are exact iff it is 0 (else some quantiles are NaN and the per-pass selection has to
+        run).  At most four quantile levels."""
+        t = self.torch
+        x = self._dev(x, t.float64)
+        S, T = x.shape
+        d_seg = self._dev(seg, t.int32)
+        d_perm, d_goff = self._dev(perm_goff[0], t.int32), self._dev(perm_goff[1], t.int64)
+        n_q = len(qs)
+        d_q = self._quantile_levels(qs)
+        sm, mn, mx, mean = (self._empty((n_seg,), t.float64) for _ in range(4))
+        cnt = self._empty((n_seg,), t.int64)
+        outs = {"n": self._empty((n_seg,), t.int64), "lo": self._empty((n_seg, n_q), t.int64),
+                "hi": self._empty((n_seg, n_q), t.int64), "x_lo": self._empty((n_seg, n_q), t.float64),
+                "x_hi": self._empty((n_seg, n_q), t.float64), "value": self._empty((n_seg, n_q), t.float64)}
+        failed = self._empty((1,), t.int32)
+        _abi.check(self.lib.pmx_summary_quantiles(
+            self.ctx, self._ptr(x), S, T, self._ptr(d_seg), n_seg, self._ptr(d_perm), self._ptr(d_goff), self._ptr(d_q), n_q,
+            self._ptr(sm), self._ptr(cnt), self._ptr(mn), self._ptr(mx), self._ptr(mean), self._ptr(outs["n"]),
+            self._ptr(outs["lo"]), self._ptr(outs["hi"]), self._ptr(outs["x_lo"]), self._ptr(outs["x_hi"]),
+            self._ptr(outs["value"]), self._ptr(failed), self._stream()))
+        self.launches += 5 if S > 0 and T > 0 else 3        # sample, bounds, sweep, fold, resolve
+        return (sm, cnt, mn, mx, mean), outs, failed
+
+    def defer_flag(self, counter):
+        """Copies a device int32 counter to pinned host memory behind the stream; ``deferred_ok`` looks at it."""
+        t = self.torch
+        pool = self.__dict__.setdefault("_flag_pool", [])
+        flag = pool.pop() if pool else t.empty((1,), dtype=t.int32).pin_memory()
+        flag.copy_(counter, non_blocking=True)
+        ev = t.cuda.Event(); ev.record()
+        self.__dict__.setdefault("_deferred", []).append((ev, flag))
+
     def deferred_ok(self, wait=True):
         """Looks at the counters of earlier ``quantiles(..., defer_check=True)`` calls.  Returns True
         when every finished one was exact.  ``wait=False`` leaves calls whose copy has not arrived
@@ -568,6 +604,7 @@ class Engine:
                 continue
             ev.synchronize()
             ok = ok and int(flag[0]) == 0
+            self.__dict__.setdefault("_flag_pool", []).append(flag)
         self._deferred = keep
         return ok
 
@@ -689,11 +726,7 @@ class Engine:
                                                             self._ptr(state), self._ptr(unresolved), self._stream()))
                 self.launches += 1
                 if defer_check:
-                    pend = self.__dict__.setdefault("_deferred", [])
-                    flag = t.empty((1,), dtype=t.int32).pin_memory()
-                    flag.copy_(unresolved, non_blocking=True)
-                    ev = t.cuda.Event(); ev.record()
-                    pend.append((ev, flag))
+                    self.defer_flag(unresolved)
                     break
                 if int(unresolved.item()) == 0:
                     break

@@ -115,10 +115,22 @@ class ShardedEngine:
         """(count, min, max) of the combined group summary: where the quantile selection starts."""
         return summary[1], summary[2], summary[3]
 
-    def summarize(self, x, seg, n_seg, perm_goff, qs=(0.5, 0.95, 0.99), defer_check=False):
+    def summarize(self, x, seg, n_seg, perm_goff, qs=(0.5, 0.95, 0.99), defer_check=False, _unchecked=False):
         """Per-segment sum / count / min / max / mean and exact quantiles of the [S, T] device matrix ``x`` over
-        ALL ranks (every rank calls this with its own rows; S may be 0).  Returns (summary, quantiles)."""
+        ALL ranks (every rank calls this with its own rows; S may be 0).  Returns (summary, quantiles).
+        One rank and at most four levels: one sweep of ``x`` (``Engine.summary_quantiles``); its brackets
+        are verified on the device, and the per-pass selection runs if the check fails (with
+        ``defer_check`` the check is left to ``Engine.deferred_ok``, see ``Engine.quantiles``)."""
         eng = self.eng
+        if self.world == 1 and 1 <= len(qs) <= 4:
+            summary, q, failed = eng.summary_quantiles(x, seg, n_seg, qs, perm_goff)
+            if _unchecked:
+                return summary, q, failed
+            if defer_check:
+                eng.defer_flag(failed)
+                return summary, q
+            if int(failed.item()) == 0:
+                return summary, q
         sm, cnt, mn, mx, mean = eng.group_reduce(x, None, n_seg, perm_goff=perm_goff)
         key = (n_seg, len(qs))
         if key not in self._qbuf:
@@ -131,28 +143,28 @@ class ShardedEngine:
             summary = (sm, cnt, mn, mx, mean)          # one rank: the kernel's own result is the summary
             q = eng.quantiles(x, seg, n_seg, list(qs), buffers=self._qbuf[key], row_order=perm_goff[0],
                               summary=self._qsummary(summary))
-        return summary, q
+        return (summary, q, None) if _unchecked else (summary, q)
 
-    def summarize_graph(self, x, seg, n_seg, perm_goff, qs=(0.5, 0.95, 0.99)):
+    def summarize_graph(self, x, seg, n_seg, perm_goff, qs=(0.5, 0.95, 0.99), defer_check=False):
         """``summarize`` replayed from a CUDA graph (one rank): the small launches behind the fused kernel
-        (partials, fold, init, the histogram / list passes with their picks, tail, finish) are
-        launch-bound, so they are captured once per (buffer, shape) and replayed.  ``x``, ``seg`` and
+        are launch-bound, so they are captured once per (buffer, shape) and replayed.  ``x``, ``seg`` and
         ``perm_goff`` must be the same device tensors on every call (the graph reads them in
         place); the returned tensors are the graph's own and are overwritten by the next replay.
-        Falls back to the eager path when capture is not possible."""
+        Falls back to the eager path when capture is not possible, and to the eager per-pass selection
+        when the replayed sweep reports a failed bracket."""
         t = self.eng.torch
         key = (x.data_ptr(), tuple(x.shape), seg.data_ptr(), n_seg, perm_goff[0].data_ptr(), perm_goff[1].data_ptr(), tuple(qs))
         hit = self._graphs.get(key)
         if hit is None:
             for _ in range(2):                                  # scratch grows and kernels load outside the capture
                 before = self.eng.launches
-                self.summarize(x, seg, n_seg, perm_goff, qs)
+                self.summarize(x, seg, n_seg, perm_goff, qs, _unchecked=True)
             n_launches = self.eng.launches - before             # kernels of ours inside one replay
             t.cuda.synchronize()
             try:
                 g = t.cuda.CUDAGraph()
                 with t.cuda.graph(g, capture_error_mode="thread_local"):
-                    res = self.summarize(x, seg, n_seg, perm_goff, qs)
+                    res = self.summarize(x, seg, n_seg, perm_goff, qs, _unchecked=True)
                 self.eng.launches -= n_launches                 # the capture launched nothing
                 hit = (g, res, (x, seg, perm_goff), n_launches)  # the inputs stay alive with the graph
             except Exception:  # noqa: BLE001  -- capture refused: stay eager
@@ -160,10 +172,16 @@ class ShardedEngine:
                 hit = (None, None, None, 0)
             self._graphs[key] = hit
         if hit[0] is None:
-            return self.summarize(x, seg, n_seg, perm_goff, qs)
+            return self.summarize(x, seg, n_seg, perm_goff, qs, defer_check=defer_check)
         hit[0].replay()
         self.eng.launches += hit[3]
-        return hit[1]
+        summary, q, failed = hit[1]
+        if failed is not None:
+            if defer_check:
+                self.eng.defer_flag(failed)
+            elif int(failed.item()) != 0:
+                return self.summarize(x, seg, n_seg, perm_goff, qs)   # (finds the failure again and runs the passes)
+        return summary, q
 
     def aggregate_step(self, ts, val, off, start_ms, step_ms, n_steps, window_steps, seg, n_seg, perm_goff,
                        qs=(0.5, 0.95, 0.99), out=None, lookback_ms=300_000, host=None, defer_check=False,
@@ -183,7 +201,7 @@ class ShardedEngine:
         else:
             out = eng.fused(ts, val, off, start_ms, step_ms, n_steps, window_steps, lookback_ms, out=out)
         if graph and self.world == 1 and host is None:
-            summary, q = self.summarize_graph(out["aligned"], seg, n_seg, perm_goff, qs)
+            summary, q = self.summarize_graph(out["aligned"], seg, n_seg, perm_goff, qs, defer_check=defer_check)
         else:
             summary, q = self.summarize(out["aligned"], seg, n_seg, perm_goff, qs, defer_check)
         return out, summary, q
