@@ -377,9 +377,12 @@ bs_sweep_kernel(const double* __restrict__ x, int64_t T, const int32_t* __restri
   }
 }
 
-// CTA (quantile j, segment g): place the two ranks of quantile j in their bracket and, where they
-// fall strictly inside, select them from the list; write the outputs of pmx_quantile_finish.
-__global__ void __launch_bounds__(1024)
+// A cluster of BS_RC CTAs per (quantile j, segment g): place the two ranks of quantile j in their
+// bracket and, where they fall strictly inside, select them from the list; write the outputs of
+// pmx_quantile_finish.  Every CTA sweeps a quarter of the list; counts and histograms are summed over
+// distributed shared memory and every CTA repeats the scans and picks; CTA 0 ranks the last few keys.
+constexpr int BS_RC = 4;
+__global__ void __cluster_dims__(BS_RC, 1, 1) __launch_bounds__(1024)
 bs_resolve_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __restrict__ lists, unsigned cap,
                   const int64_t* __restrict__ count, const double* __restrict__ q, int n_q,
                   int64_t* o_n, int64_t* o_lo, int64_t* o_hi, double* o_xlo, double* o_xhi, double* o_val,
@@ -387,15 +390,18 @@ bs_resolve_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __re
   __shared__ unsigned int sh_hist[2][BS_BINS];
   __shared__ unsigned int s_warp[32];
   __shared__ unsigned long long s_keys[2 * BS_SMALL];
-  __shared__ unsigned int s_nk, s_mid;
+  __shared__ unsigned int s_nk, s_mid;          // read by the other CTAs of the cluster, as are sh_hist and s_keys
   __shared__ int s_zone[2];                      // 0 fail, 1 lo, 2 inside, 3 hi
   __shared__ unsigned long long s_r[2];          // rank inside the list (zone 2) or inside the run of zeros
   __shared__ unsigned long long s_pf[2], s_ans[2];
   __shared__ unsigned int s_cb[2];               // keys in the rank's current bucket
-  const int j = blockIdx.x, g = blockIdx.y;
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  const unsigned crank = cluster.block_rank();
+  const int j = blockIdx.x / BS_RC, g = blockIdx.y;
   const int64_t out = (int64_t)g * n_q + j;
   const long long n = count[g];
-  if (j == 0 && threadIdx.x == 0 && o_n) o_n[g] = n;
+  if (j == 0 && crank == 0 && threadIdx.x == 0 && o_n) o_n[g] = n;
   auto write = [&](long long klo, long long khi, double a, double b, double v) {
     if (o_lo) o_lo[out] = klo;
     if (o_hi) o_hi[out] = khi;
@@ -403,7 +409,7 @@ bs_resolve_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __re
     if (o_xhi) o_xhi[out] = b;
     if (o_val) o_val[out] = v;
   };
-  if (n <= 0) { if (threadIdx.x == 0) write(-1, -1, pmx_nan(), pmx_nan(), pmx_nan()); return; }
+  if (n <= 0) { if (crank == 0 && threadIdx.x == 0) write(-1, -1, pmx_nan(), pmx_nan(), pmx_nan()); return; }
   const BsSeg& B = segs[g];
   const double lo = B.lo[j], hi = B.hi[j];
   const uint64_t klo = f64_key(lo), khi = f64_key(hi);
@@ -418,14 +424,26 @@ bs_resolve_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __re
   const unsigned long long k1 = k0 + 1 < (unsigned long long)n ? k0 + 1 : (unsigned long long)n - 1;
   const double tt = pos - (double)k0;
   auto inside = [&](uint64_t key) -> bool { const double v = key_f64(key); return v > lo && v < hi; };   // as the sweep saw it
-  // every key of the list, eight loads in flight per thread
+  // every key of this CTA's part of the list, eight loads in flight per thread
+  const unsigned part_n = (n_list + BS_RC - 1) / BS_RC;
+  const unsigned k_a = crank * part_n < n_list ? crank * part_n : n_list;
+  const unsigned k_b = k_a + part_n < n_list ? k_a + part_n : n_list;
   auto for_keys = [&](auto&& f) {
-    for (unsigned i0 = 0; i0 < n_list; i0 += blockDim.x * 8) {
+    for (unsigned i0 = k_a; i0 < k_b; i0 += blockDim.x * 8) {
       unsigned long long kk[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) { const unsigned i = i0 + u * blockDim.x + threadIdx.x; kk[u] = i < n_list ? keys[i] : 0ULL; }
+      for (int u = 0; u < 8; ++u) { const unsigned i = i0 + u * blockDim.x + threadIdx.x; kk[u] = i < k_b ? keys[i] : 0ULL; }
 #pragma unroll
-      for (int u = 0; u < 8; ++u) { const unsigned i = i0 + u * blockDim.x + threadIdx.x; if (i < n_list) f(kk[u]); }
+      for (int u = 0; u < 8; ++u) { const unsigned i = i0 + u * blockDim.x + threadIdx.x; if (i < k_b) f(kk[u]); }
+    }
+  };
+  // the histogram h summed over the cluster: this thread's two bins
+  auto hist2 = [&](int h, unsigned& c0, unsigned& c1) {
+    c0 = 0; c1 = 0;
+#pragma unroll
+    for (int r = 0; r < BS_RC; ++r) {
+      const uint2 c = *reinterpret_cast<const uint2*>(cluster.map_shared_rank(&sh_hist[h][0], r) + 2 * threadIdx.x);
+      c0 += c.x; c1 += c.y;
     }
   };
   const int Z = khi > klo ? __clzll((long long)(khi - klo)) : 0;
@@ -441,8 +459,9 @@ bs_resolve_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __re
     c = __reduce_add_sync(0xffffffffu, c);
     if ((threadIdx.x & 31) == 0 && c) atomicAdd(&s_mid, c);
   }
-  __syncthreads();
-  const unsigned long long c_mid = s_mid;
+  cluster.sync();
+  unsigned long long c_mid = 0;
+  for (int r = 0; r < BS_RC; ++r) c_mid += *cluster.map_shared_rank(&s_mid, r);
   if (threadIdx.x < 2) {
     const unsigned long long k = threadIdx.x ? k1 : k0;
     int zone = 0; unsigned long long r = 0;
@@ -457,8 +476,9 @@ bs_resolve_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __re
     if (zone == 3) s_ans[threadIdx.x] = hi == 0.0 ? f64_key(r < c_nz ? -0.0 : 0.0) : khi;
   }
   __syncthreads();
-  if (s_zone[0] == 0 || s_zone[1] == 0) {
-    if (threadIdx.x == 0) { atomicAdd(failed, 1u); write((long long)k0, (long long)k1, pmx_nan(), pmx_nan(), pmx_nan()); }
+  if (s_zone[0] == 0 || s_zone[1] == 0) {        // the same in every CTA of the cluster
+    if (crank == 0 && threadIdx.x == 0) { atomicAdd(failed, 1u); write((long long)k0, (long long)k1, pmx_nan(), pmx_nan(), pmx_nan()); }
+    cluster.sync();                              // nobody leaves while its counters may still be read
     return;
   }
   if (s_zone[0] == 2 || s_zone[1] == 2) {
@@ -479,13 +499,14 @@ bs_resolve_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __re
           if (top == p0) atomicAdd(&sh_hist[0][d], 1u);
           else if (n_h == 2 && top == p1) atomicAdd(&sh_hist[1][d], 1u);
         });
-        __syncthreads();
+        cluster.sync();
       }
       for (int h = 0; h < n_h; ++h) {
         // read before the scan's barriers: the thread that finds a rank's bin rewrites rank and prefix
         const unsigned long long r0 = s_r[0], r1 = s_r[1], f0 = s_pf[0], f1 = s_pf[1];
         unsigned c0, c1;
-        const unsigned base = bs_scan(sh_hist[h], s_warp, c0, c1);
+        hist2(h, c0, c1);
+        const unsigned base = bs_scan2(c0, c1, s_warp);
         for (int t = 0; t < 2; ++t) {
           if (s_zone[t] != 2) continue;
           const int ht = (n_h == 2 && t == 1) ? 1 : 0;               // the histogram that serves rank t
@@ -499,6 +520,7 @@ bs_resolve_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __re
         __syncthreads();
       }
       used += bits;
+      cluster.sync();                            // every CTA has read every histogram before any is cleared
       const bool small = (s_zone[0] != 2 || s_cb[0] <= BS_SMALL) && (s_zone[1] != 2 || s_cb[1] <= BS_SMALL);
       if (small || used >= 64 - Z) break;
     }
@@ -513,8 +535,20 @@ bs_resolve_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __re
         const uint64_t top = ((key - klo) << Z) >> (64 - used);
         if (top == p0 || top == p1) { const unsigned at = atomicAdd(&s_nk, 1u); if (at < 2 * BS_SMALL) s_keys[at] = key; }
       });
-      __syncthreads();
-      const unsigned nk = s_nk < 2 * BS_SMALL ? s_nk : 2 * BS_SMALL;
+      cluster.sync();
+      // CTA 0 takes the other CTAs' keys behind its own (the buckets hold <= 2 BS_SMALL keys together)
+      unsigned nk = s_nk < 2 * BS_SMALL ? s_nk : 2 * BS_SMALL;
+      if (crank == 0) {
+        for (int r = 1; r < BS_RC; ++r) {
+          const unsigned nr = *cluster.map_shared_rank(&s_nk, r);
+          const unsigned long long* rk = cluster.map_shared_rank(&s_keys[0], r);
+          for (unsigned i = threadIdx.x; i < nr; i += blockDim.x) if (nk + i < 2 * BS_SMALL) s_keys[nk + i] = rk[i];
+          nk = nk + nr < 2 * BS_SMALL ? nk + nr : 2 * BS_SMALL;
+        }
+        __syncthreads();
+      } else {
+        nk = 0;
+      }
       for (unsigned i = threadIdx.x; i < nk; i += blockDim.x) {
         const uint64_t ki = s_keys[i], top = ((ki - klo) << Z) >> (64 - used);
         unsigned less = 0, eq = 0;
@@ -528,7 +562,8 @@ bs_resolve_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __re
     }
     __syncthreads();
   }
-  if (threadIdx.x == 0) {
+  cluster.sync();                                // nobody leaves while its shared memory may still be read
+  if (crank == 0 && threadIdx.x == 0) {
     const double a = key_f64(s_ans[0]), b = key_f64(s_ans[1]);
     // numpy _lerp: a + (b-a)*t, and b - (b-a)*(1-t) when t >= 0.5 (no FMA contraction)
     const double d = __dsub_rn(b, a);
@@ -593,7 +628,7 @@ extern "C" int pmx_summary_quantiles(pmx_ctx* ctx, const double* d_x, int64_t n_
     PMX_LAUNCH_CHECK();
   }
   if (int rc = pmx_internal_group_fold(part, d_perm, d_goff, n_seg, d_sum, d_count, d_min, d_max, d_mean, st)) return rc;
-  dim3 grid((unsigned)n_q, (unsigned)n_seg);
+  dim3 grid((unsigned)n_q * BS_RC, (unsigned)n_seg);
   bs_resolve_kernel<<<grid, 1024, 0, st>>>(segs, lists, (unsigned)cap, d_count, d_q, (int)n_q, d_n, d_lo, d_hi, d_x_lo, d_x_hi,
                                            d_value, (unsigned int*)d_failed);
   PMX_LAUNCH_CHECK();

@@ -39,7 +39,19 @@ group_fold_kernel(const Part* __restrict__ part, const int32_t* __restrict__ per
   const int lane = threadIdx.x & 31;
   if (g >= n_groups) return;
   Part r = part_identity();
-  for (int64_t k = goff[g] + lane; k < goff[g + 1]; k += 32) part_merge(r, part[perm[k]]);
+  // eight partials on their way at a time; they are merged in the order k, k + 32, ... as before
+  const int64_t k1 = goff[g + 1];
+  int64_t k = goff[g] + lane;
+  for (; k + 7 * 32 < k1; k += 8 * 32) {
+    int32_t idx[8]; Part p[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) idx[u] = perm[k + 32 * u];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) p[u] = part[idx[u]];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) part_merge(r, p[u]);
+  }
+  for (; k < k1; k += 32) part_merge(r, part[perm[k]]);
 #pragma unroll
   for (int d = 16; d >= 1; d >>= 1) { Part q = part_shfl_down(r, d); part_merge(r, q); }
   if (lane != 0) return;

@@ -16,6 +16,10 @@ for l in open(dis):
         line_of[int(m.group(1), 16)] = cur
 rows = list(csv.reader(open(src)))
 hdr = rows[1]; data = rows[2:]
+for _k, _r in enumerate(data):                      # several launches in one export: keep the first
+    if _r and _r[0] == "Kernel Name":
+        data = data[:_k]
+        break
 ia = hdr.index("Address"); ie = hdr.index("Instructions Executed"); isamp = hdr.index("# Samples")
 stalls = [h for h in hdr if h.startswith("stall_") and "Not Issued" not in h]
 sidx = [hdr.index(h) for h in stalls]
