@@ -38,7 +38,20 @@ struct BsSeg {                                   // per segment
   unsigned long long neg_zero;                   // -0.0 values (counted only when a bound is zero)
   unsigned int list_n;                           // keys appended to the list (may exceed its capacity)
   unsigned int zero_bound;
+  unsigned int sample_m;                         // valid sample values the bounds were taken from
+  unsigned int overflow;                         // several ranks: some rank's list overflowed
+  double gmin, gmax;                             // several ranks: smallest / largest value of the segment over all ranks
 };
+
+// Several ranks take one digit only, so it has to spread the keys inside the bracket: the digit is
+// taken relative to the bracket clipped to the segment's value range (an open side would otherwise
+// stretch the key range to +-inf and put every key into one bucket).
+__device__ __forceinline__ void bs_digit_geom(const BsSeg& B, int j, uint64_t* kbase, int* Z) {
+  const double lo = B.lo[j] > B.gmin ? B.lo[j] : B.gmin, hi = B.hi[j] < B.gmax ? B.hi[j] : B.gmax;
+  const uint64_t a = f64_key(lo), b = f64_key(hi);
+  *kbase = a;
+  *Z = b > a ? __clzll((long long)(b - a)) : 0;
+}
 
 __device__ __forceinline__ uint64_t bs_hash(uint64_t h) {
   h ^= h >> 33; h *= 0xff51afd7ed558ccdULL; h ^= h >> 33; h *= 0xc4ceb9fe1a85ec53ULL; h ^= h >> 33;
@@ -78,11 +91,6 @@ __device__ __forceinline__ unsigned bs_scan2(unsigned c0, unsigned c1, unsigned*
   __syncthreads();
   return s_warp[warp] + inc - sum;
 }
-__device__ __forceinline__ unsigned bs_scan(const unsigned* h, unsigned* s_warp, unsigned& c0, unsigned& c1) {
-  c0 = h[2 * threadIdx.x]; c1 = h[2 * threadIdx.x + 1];
-  return bs_scan2(c0, c1, s_warp);
-}
-
 // A cluster of BS_CL CTAs per segment: the sample values of the brackets.  Every CTA keeps an
 // eighth of the segment's sample as keys in its shared memory; histograms and extremes are
 // exchanged through distributed shared memory, and every CTA repeats the (cheap) scans and picks,
@@ -267,7 +275,7 @@ bs_bounds_kernel(const double* __restrict__ samp, int64_t P, const int32_t* __re
       }
       b.lo[j] = lo; b.hi[j] = hi; b.below[j] = 0; b.eq_lo[j] = 0; b.eq_hi[j] = 0;
     }
-    b.neg_zero = 0; b.list_n = 0; b.zero_bound = zb;
+    b.neg_zero = 0; b.list_n = 0; b.zero_bound = zb; b.sample_m = m; b.overflow = 0;
   }
 }
 
@@ -573,7 +581,419 @@ bs_resolve_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __re
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Several ranks (one process per GPU, rows sharded): every rank samples its own rows and proposes
+// brackets; the hull of the proposals (the global quantile lies between the smallest and the largest
+// local one) is what all ranks sweep with; counters and summary partials are combined in rank order;
+// the first digit of the keys inside a bracket is histogrammed and all-reduced; every rank then
+// contributes the few keys of the buckets that hold the wanted ranks, and all ranks settle every
+// quantile alike from the gathered rows.  Four small collectives, one sweep of the data.
+constexpr int BS_BOUNDS_W = 2 * BS_MAX_Q + 1;    // per segment: lo[4], hi[4], sample size
+constexpr int BS_PACK_W = 4 + 3 * BS_MAX_Q + 2;  // sum, count, min, max | below, eq_lo, eq_hi | -0.0 count, overflow
+constexpr unsigned BS_ROWK = 1024;               // keys a rank can contribute per (segment, quantile)
+constexpr unsigned BS_ROW_W = 5 + BS_ROWK;       // count, (min, max) of either rank's bucket, keys
+
+struct BsPick {                                  // per (segment, quantile): where its two ranks fall
+  int zone[2];                                   // -1 empty segment, 0 fail, 1 lo, 2 inside, 3 hi
+  unsigned int bin[2];                           // zone 2: first two digits (22 bits) of the bucket
+  unsigned long long r[2];                       // zone 2: rank inside the bucket
+  unsigned long long ans[2];                     // zones 1 and 3: the key
+  unsigned long long k0, k1;
+  double tt;
+};
+
+__global__ void bs_export_bounds_kernel(const BsSeg* __restrict__ segs, int64_t n_seg, double* __restrict__ out) {
+  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= n_seg) return;
+  for (int j = 0; j < BS_MAX_Q; ++j) { out[g * BS_BOUNDS_W + j] = segs[g].lo[j]; out[g * BS_BOUNDS_W + BS_MAX_Q + j] = segs[g].hi[j]; }
+  out[g * BS_BOUNDS_W + 2 * BS_MAX_Q] = (double)segs[g].sample_m;
+}
+
+// hull over the ranks that hold sample values of the segment; counters were cleared by bs_bounds_kernel
+__global__ void bs_merge_bounds_kernel(const double* __restrict__ all, int world, int64_t n_seg, int n_q,
+                                       BsSeg* __restrict__ segs) {
+  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= n_seg) return;
+  const double INF = __longlong_as_double(0x7FF0000000000000LL);
+  unsigned zb = 0;
+  for (int j = 0; j < n_q; ++j) {
+    double lo = INF, hi = -INF; bool any = false;
+    for (int w = 0; w < world; ++w) {
+      const double* b = all + ((size_t)w * n_seg + g) * BS_BOUNDS_W;
+      if (b[2 * BS_MAX_Q] > 0.0) { any = true; lo = b[j] < lo ? b[j] : lo; hi = b[BS_MAX_Q + j] > hi ? b[BS_MAX_Q + j] : hi; }
+    }
+    if (!any) { lo = -INF; hi = INF; }
+    segs[g].lo[j] = lo; segs[g].hi[j] = hi;
+    if (lo == 0.0 || hi == 0.0) zb = 1;
+  }
+  segs[g].zero_bound = zb;
+}
+
+__global__ void bs_pack_kernel(const BsSeg* __restrict__ segs, const double* __restrict__ sum, const int64_t* __restrict__ cnt,
+                               const double* __restrict__ mn, const double* __restrict__ mx, int64_t n_seg, unsigned cap,
+                               unsigned long long* __restrict__ out) {
+  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= n_seg) return;
+  const double INF = __longlong_as_double(0x7FF0000000000000LL);
+  unsigned long long* o = out + g * BS_PACK_W;
+  const int64_t c = cnt[g];
+  o[0] = (unsigned long long)__double_as_longlong(sum[g]);
+  o[1] = (unsigned long long)c;
+  o[2] = (unsigned long long)__double_as_longlong(c > 0 ? mn[g] : INF);
+  o[3] = (unsigned long long)__double_as_longlong(c > 0 ? mx[g] : -INF);
+  for (int j = 0; j < BS_MAX_Q; ++j) {
+    o[4 + j] = segs[g].below[j]; o[4 + BS_MAX_Q + j] = segs[g].eq_lo[j]; o[4 + 2 * BS_MAX_Q + j] = segs[g].eq_hi[j];
+  }
+  o[4 + 3 * BS_MAX_Q] = segs[g].neg_zero;
+  o[5 + 3 * BS_MAX_Q] = segs[g].list_n > cap ? 1 : 0;
+}
+
+// summary in rank order (as pmx_group_combine), counters summed into segs
+__global__ void bs_combine_kernel(const unsigned long long* __restrict__ all, int world, int64_t n_seg, BsSeg* __restrict__ segs,
+                                  double* o_sum, int64_t* o_cnt, double* o_min, double* o_max, double* o_mean) {
+  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= n_seg) return;
+  Part r = part_identity();
+  unsigned long long cn[3 * BS_MAX_Q + 2];
+  for (int i = 0; i < 3 * BS_MAX_Q + 2; ++i) cn[i] = 0;
+  for (int w = 0; w < world; ++w) {
+    const unsigned long long* b = all + ((size_t)w * n_seg + g) * BS_PACK_W;
+    r.sum += __longlong_as_double((long long)b[0]); r.cnt += (long long)b[1];
+    r.mn = fmin(r.mn, __longlong_as_double((long long)b[2])); r.mx = fmax(r.mx, __longlong_as_double((long long)b[3]));
+    for (int i = 0; i < 3 * BS_MAX_Q + 2; ++i) cn[i] += b[4 + i];
+  }
+  for (int j = 0; j < BS_MAX_Q; ++j) {
+    segs[g].below[j] = cn[j]; segs[g].eq_lo[j] = cn[BS_MAX_Q + j]; segs[g].eq_hi[j] = cn[2 * BS_MAX_Q + j];
+  }
+  segs[g].neg_zero = cn[3 * BS_MAX_Q];
+  segs[g].overflow = cn[3 * BS_MAX_Q + 1] ? 1u : 0u;
+  segs[g].gmin = r.mn; segs[g].gmax = r.mx;
+  const bool any = r.cnt > 0;
+  if (o_sum) o_sum[g] = r.sum;
+  if (o_cnt) o_cnt[g] = r.cnt;
+  if (o_min) o_min[g] = any ? r.mn : pmx_nan();
+  if (o_max) o_max[g] = any ? r.mx : pmx_nan();
+  if (o_mean) o_mean[g] = any ? r.sum / (double)r.cnt : pmx_nan();
+}
+
+// A digit of this rank's keys strictly inside bracket j: grid (4 n_q, n_seg).  SECOND = false: the first
+// 11 bits, one histogram per (segment, quantile).  SECOND = true: the next 11 bits of the keys whose
+// first digit is that of rank t's bucket, one histogram per (segment, quantile, t).
+template <bool SECOND>
+__global__ void __launch_bounds__(1024)
+bs_midhist_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __restrict__ lists, unsigned cap, int n_q,
+                  const BsPick* __restrict__ picks, unsigned int* __restrict__ hist) {
+  __shared__ unsigned int sh[(SECOND ? 2 : 1) * BS_BINS];
+  const int j = blockIdx.x >> 2, quarter = blockIdx.x & 3, g = blockIdx.y;
+  const BsSeg& B = segs[g];
+  const double lo = B.lo[j], hi = B.hi[j];
+  uint64_t klo; int Z;
+  bs_digit_geom(B, j, &klo, &Z);
+  const unsigned n_list = B.list_n > cap ? cap : B.list_n;
+  const unsigned long long* keys = lists + (size_t)g * cap;
+  const unsigned part_n = (n_list + 3) / 4;
+  const unsigned k_a = quarter * part_n < n_list ? quarter * part_n : n_list;
+  const unsigned k_b = k_a + part_n < n_list ? k_a + part_n : n_list;
+  if (k_a >= k_b) return;
+  unsigned b0 = 0xffffffffu, b1 = 0xffffffffu;
+  if (SECOND) {
+    const BsPick& P = picks[(size_t)g * n_q + j];
+    if (P.zone[0] == 2) b0 = P.bin[0];
+    if (P.zone[1] == 2) b1 = P.bin[1];
+    if (b0 == 0xffffffffu && b1 == 0xffffffffu) return;
+  }
+  for (int i = threadIdx.x; i < (SECOND ? 2 : 1) * BS_BINS; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  for (unsigned i0 = k_a; i0 < k_b; i0 += blockDim.x * 8) {
+    unsigned long long kk[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) { const unsigned i = i0 + u * blockDim.x + threadIdx.x; kk[u] = i < k_b ? keys[i] : 0ULL; }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const unsigned i = i0 + u * blockDim.x + threadIdx.x;
+      if (i >= k_b) continue;
+      const double v = key_f64(kk[u]);
+      if (!(v > lo && v < hi)) continue;
+      const uint64_t rel = (kk[u] - klo) << Z;
+      const unsigned d1 = (unsigned)(rel >> 53);
+      if (!SECOND) { atomicAdd(&sh[d1], 1u); continue; }
+      const unsigned d2 = (unsigned)(rel >> 42) & (BS_BINS - 1);
+      if (d1 == b0) atomicAdd(&sh[d2], 1u);
+      if (d1 == b1) atomicAdd(&sh[BS_BINS + d2], 1u);
+    }
+  }
+  __syncthreads();
+  constexpr int NH = SECOND ? 2 : 1;
+  unsigned int* dst = hist + ((size_t)g * n_q + j) * NH * BS_BINS;
+  for (int i = threadIdx.x; i < NH * BS_BINS; i += blockDim.x) { const unsigned c = sh[i]; if (c) atomicAdd(&dst[i], c); }
+}
+
+// CTA (j, g), after the all-reduce of the first histograms: place the two ranks of quantile j (as
+// bs_resolve_kernel does, from the combined counters) and pick the first digit of their buckets.
+__global__ void __launch_bounds__(1024)
+bs_pick1_kernel(const BsSeg* __restrict__ segs, const unsigned int* __restrict__ hist, const int64_t* __restrict__ count,
+                const double* __restrict__ q, int n_q, BsPick* __restrict__ picks) {
+  __shared__ unsigned int s_warp[32];
+  __shared__ BsPick s_p;
+  __shared__ unsigned int s_tot;
+  const int j = blockIdx.x, g = blockIdx.y;
+  BsPick* pick = picks + (size_t)g * n_q + j;
+  const long long n = count[g];
+  if (n <= 0) { if (threadIdx.x == 0) { pick->zone[0] = pick->zone[1] = -1; } return; }
+  const BsSeg& B = segs[g];
+  const double lo = B.lo[j], hi = B.hi[j];
+  const uint64_t klo = f64_key(lo), khi = f64_key(hi);
+  const unsigned long long c_lt = B.below[j], c_el = B.eq_lo[j], c_eh = hi == lo ? 0 : B.eq_hi[j], c_nz = B.neg_zero;
+  const bool overflow = B.overflow != 0;
+  const unsigned int* h = hist + ((size_t)g * n_q + j) * BS_BINS;
+  const unsigned c0 = h[2 * threadIdx.x], c1 = h[2 * threadIdx.x + 1];
+  const unsigned base = bs_scan2(c0, c1, s_warp);
+  if (threadIdx.x == blockDim.x - 1) s_tot = base + c0 + c1;      // all keys inside the bracket, over all ranks
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned long long c_mid = s_tot;
+    const double pos = (double)(n - 1) * q[j];
+    unsigned long long k0 = (unsigned long long)floor(pos);
+    if (k0 > (unsigned long long)n - 1) k0 = (unsigned long long)n - 1;
+    const unsigned long long k1 = k0 + 1 < (unsigned long long)n ? k0 + 1 : (unsigned long long)n - 1;
+    s_p.k0 = k0; s_p.k1 = k1; s_p.tt = pos - (double)k0;
+    for (int t = 0; t < 2; ++t) {
+      const unsigned long long k = t ? k1 : k0;
+      int zone = 0; unsigned long long r = 0, ans = 0;
+      if (k < c_lt) zone = 0;
+      else if (k < c_lt + c_el) { zone = 1; r = k - c_lt; ans = lo == 0.0 ? f64_key(r < c_nz ? -0.0 : 0.0) : klo; }
+      else if (overflow) zone = 0;
+      else if (k < c_lt + c_el + c_mid) { zone = 2; r = k - c_lt - c_el; }
+      else if (k < c_lt + c_el + c_mid + c_eh) { zone = 3; r = k - c_lt - c_el - c_mid; ans = hi == 0.0 ? f64_key(r < c_nz ? -0.0 : 0.0) : khi; }
+      s_p.zone[t] = zone; s_p.r[t] = r; s_p.ans[t] = ans; s_p.bin[t] = 0xffffffffu;
+    }
+  }
+  __syncthreads();
+  const unsigned long long r0 = s_p.r[0], r1 = s_p.r[1];
+  const int z0 = s_p.zone[0], z1 = s_p.zone[1];
+  __syncthreads();
+  for (int t = 0; t < 2; ++t) {
+    if ((t ? z1 : z0) != 2) continue;
+    const unsigned long long r = t ? r1 : r0;
+    if (r >= base && r < (unsigned long long)base + c0) { s_p.bin[t] = 2 * threadIdx.x; s_p.r[t] = r - base; }
+    else if (r >= (unsigned long long)base + c0 && r < (unsigned long long)base + c0 + c1) { s_p.bin[t] = 2 * threadIdx.x + 1; s_p.r[t] = r - base - c0; }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) *pick = s_p;
+}
+
+// CTA (j, g), after the all-reduce of the second histograms: the second digit of either bucket, and
+// this rank's keys of the buckets (22 bits now) into its row: count | min, max of either bucket | keys.
+__global__ void __launch_bounds__(1024)
+bs_pick2_rows_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __restrict__ lists, unsigned cap,
+                     const unsigned int* __restrict__ hist2, int n_q, BsPick* __restrict__ picks,
+                     unsigned long long* __restrict__ rows) {
+  __shared__ unsigned int s_warp[32];
+  __shared__ unsigned int s_bin[2], s_cnt;
+  __shared__ unsigned long long s_r[2], s_mm[4];
+  const int j = blockIdx.x, g = blockIdx.y;
+  unsigned long long* row = rows + ((size_t)g * n_q + j) * BS_ROW_W;
+  BsPick* pick = picks + (size_t)g * n_q + j;
+  const BsPick P = *pick;
+  if (threadIdx.x == 0) { s_cnt = 0; s_mm[0] = s_mm[2] = ~0ULL; s_mm[1] = s_mm[3] = 0; s_bin[0] = s_bin[1] = 0xffffffffu; }
+  if (P.zone[0] != 2 && P.zone[1] != 2) {
+    if (threadIdx.x == 0) { row[0] = 0; row[1] = row[3] = ~0ULL; row[2] = row[4] = 0; }
+    return;
+  }
+  __syncthreads();
+  for (int t = 0; t < 2; ++t) {
+    if (P.zone[t] != 2) continue;                                   // uniform
+    const unsigned int* h = hist2 + (((size_t)g * n_q + j) * 2 + t) * BS_BINS;
+    const unsigned c0 = h[2 * threadIdx.x], c1 = h[2 * threadIdx.x + 1];
+    const unsigned base = bs_scan2(c0, c1, s_warp);
+    const unsigned long long r = P.r[t];
+    if (r >= base && r < (unsigned long long)base + c0) { s_bin[t] = (P.bin[t] << 11) | (2 * threadIdx.x); s_r[t] = r - base; }
+    else if (r >= (unsigned long long)base + c0 && r < (unsigned long long)base + c0 + c1) { s_bin[t] = (P.bin[t] << 11) | (2 * threadIdx.x + 1); s_r[t] = r - base - c0; }
+    __syncthreads();
+  }
+  const unsigned b0 = s_bin[0], b1 = s_bin[1];
+  const BsSeg& B = segs[g];
+  const double lo = B.lo[j], hi = B.hi[j];
+  uint64_t kbase; int Z;
+  bs_digit_geom(B, j, &kbase, &Z);
+  const unsigned n_list = B.list_n > cap ? cap : B.list_n;
+  const unsigned long long* keys = lists + (size_t)g * cap;
+  for (unsigned i0 = 0; i0 < n_list; i0 += blockDim.x * 8) {
+    unsigned long long kk[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) { const unsigned i = i0 + u * blockDim.x + threadIdx.x; kk[u] = i < n_list ? keys[i] : 0ULL; }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const unsigned i = i0 + u * blockDim.x + threadIdx.x;
+      if (i >= n_list) continue;
+      const double v = key_f64(kk[u]);
+      if (!(v > lo && v < hi)) continue;
+      const unsigned d = (unsigned)(((kk[u] - kbase) << Z) >> 42);
+      if (d != b0 && d != b1) continue;
+      const unsigned at = atomicAdd(&s_cnt, 1u);
+      if (at < BS_ROWK) row[5 + at] = kk[u];
+      const int t = d == b0 ? 0 : 1;
+      if (kk[u] < *(volatile unsigned long long*)&s_mm[2 * t]) atomicMin(&s_mm[2 * t], kk[u]);
+      if (kk[u] > *(volatile unsigned long long*)&s_mm[2 * t + 1]) atomicMax(&s_mm[2 * t + 1], kk[u]);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    row[0] = s_cnt; row[1] = s_mm[0]; row[2] = s_mm[1]; row[3] = s_mm[2]; row[4] = s_mm[3];
+    if (b0 == b1 && b0 != 0xffffffffu) { row[3] = s_mm[0]; row[4] = s_mm[1]; }   // both ranks in one bucket
+    if (P.zone[0] == 2) { pick->bin[0] = b0; pick->r[0] = s_r[0]; }
+    if (P.zone[1] == 2) { pick->bin[1] = b1; pick->r[1] = s_r[1]; }
+  }
+}
+
+// CTA (j, g), after the all-gather of the rows ([world][n_seg][n_q][ROW]): every rank settles every
+// quantile alike.  A bucket whose keys are all equal needs no keys; otherwise the gathered keys are
+// ranked directly.  What does not fit (a rank kept more than BS_ROWK keys of distinct values) fails.
+__global__ void __launch_bounds__(256)
+bs_final_kernel(const BsSeg* __restrict__ segs, const BsPick* __restrict__ picks, const unsigned long long* __restrict__ rows_all,
+                int world, int64_t n_seg, int n_q, const int64_t* __restrict__ count,
+                int64_t* o_n, int64_t* o_lo, int64_t* o_hi, double* o_xlo, double* o_xhi, double* o_val,
+                unsigned int* __restrict__ failed) {
+  constexpr unsigned KMAX = 4096;
+  __shared__ unsigned long long s_keys[KMAX];
+  __shared__ unsigned long long s_ans[2];
+  __shared__ int s_ok[2];
+  const int j = blockIdx.x, g = blockIdx.y;
+  const int64_t out = (int64_t)g * n_q + j;
+  const BsPick P = picks[out];
+  if (j == 0 && threadIdx.x == 0 && o_n) o_n[g] = count[g];
+  auto write = [&](long long klo, long long khi, double a, double b, double v) {
+    if (o_lo) o_lo[out] = klo;
+    if (o_hi) o_hi[out] = khi;
+    if (o_xlo) o_xlo[out] = a;
+    if (o_xhi) o_xhi[out] = b;
+    if (o_val) o_val[out] = v;
+  };
+  if (P.zone[0] < 0) { if (threadIdx.x == 0) write(-1, -1, pmx_nan(), pmx_nan(), pmx_nan()); return; }
+  bool fail = P.zone[0] == 0 || P.zone[1] == 0;
+  const BsSeg& B = segs[g];
+  uint64_t klo; int Z;
+  bs_digit_geom(B, j, &klo, &Z);
+  if (threadIdx.x < 2) {
+    const int t = threadIdx.x;
+    s_ok[t] = 1; s_ans[t] = P.ans[t];
+    if (P.zone[t] == 2) {
+      unsigned long long mn = ~0ULL, mx = 0;
+      for (int w = 0; w < world; ++w) {
+        const unsigned long long* row = rows_all + (((size_t)w * n_seg + g) * n_q + j) * BS_ROW_W;
+        mn = row[1 + 2 * t] < mn ? row[1 + 2 * t] : mn; mx = row[2 + 2 * t] > mx ? row[2 + 2 * t] : mx;
+      }
+      if (mn == mx) s_ans[t] = mn; else s_ok[t] = 0;             // all keys of the bucket are one value
+    }
+  }
+  __syncthreads();
+  if (!fail && (!s_ok[0] || !s_ok[1])) {
+    // the keys themselves: every rank's row, in rank order
+    unsigned total = 0; bool fits = true;
+    for (int w = 0; w < world; ++w) {
+      const unsigned long long c = rows_all[(((size_t)w * n_seg + g) * n_q + j) * BS_ROW_W];
+      if (c > BS_ROWK) fits = false; else total += (unsigned)c;
+    }
+    if (!fits || total > KMAX) fail = true;
+    else {
+      unsigned off = 0;
+      for (int w = 0; w < world; ++w) {
+        const unsigned long long* row = rows_all + (((size_t)w * n_seg + g) * n_q + j) * BS_ROW_W;
+        const unsigned c = (unsigned)row[0];
+        for (unsigned i = threadIdx.x; i < c; i += blockDim.x) s_keys[off + i] = row[5 + i];
+        off += c;
+      }
+      __syncthreads();
+      for (unsigned i = threadIdx.x; i < total; i += blockDim.x) {
+        const uint64_t ki = s_keys[i];
+        const unsigned d = (unsigned)(((ki - klo) << Z) >> 42);
+        unsigned less = 0, eq = 0;
+        for (unsigned u = 0; u < total; ++u) {
+          const uint64_t ku = s_keys[u];
+          if ((unsigned)(((ku - klo) << Z) >> 42) == d) { less += ku < ki; eq += ku == ki; }
+        }
+        for (int t = 0; t < 2; ++t)
+          if (P.zone[t] == 2 && !s_ok[t] && P.bin[t] == d && P.r[t] >= less && P.r[t] < (unsigned long long)less + eq) s_ans[t] = ki;
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (fail) { atomicAdd(failed, 1u); write((long long)P.k0, (long long)P.k1, pmx_nan(), pmx_nan(), pmx_nan()); return; }
+    const double a = key_f64(s_ans[0]), b = key_f64(s_ans[1]);
+    const double d = __dsub_rn(b, a);
+    double v = __dadd_rn(a, __dmul_rn(d, P.tt));
+    if (P.tt >= 0.5) v = __dsub_rn(b, __dmul_rn(d, __dsub_rn(1.0, P.tt)));
+    write((long long)P.k0, (long long)P.k1, a, b, v);
+  }
+}
+
 }  // namespace
+
+// scratch of one selection: per-series partials (slot PMX_SCR_PARTIALS); per-segment brackets and
+// counters | local fold outputs | picks | sample | lists (slot PMX_SCR_BRACKET)
+struct BsScratch {
+  Part* part; BsSeg* segs; double* f_sum; int64_t* f_cnt; double* f_min; double* f_max; BsPick* picks;
+  double* samp; unsigned long long* lists; int64_t cap; int64_t P;
+};
+static int bs_scratch(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg, int64_t n_q, BsScratch* S) {
+  S->P = (n_steps + BS_STRIDE - 1) / BS_STRIDE;
+  S->part = nullptr;
+  if (n_series > 0) {
+    S->part = (Part*)pmx_scratch(ctx, PMX_SCR_PARTIALS, (size_t)n_series * sizeof(Part));
+    if (!S->part) return PMX_E_CUDA;
+  }
+  int64_t cap = ((int64_t)256 << 20) / 8 / n_seg;
+  if (cap > (1 << 22)) cap = 1 << 22;
+  if (cap < 4096) cap = 4096;
+  S->cap = cap;
+  auto up = [](size_t b) { return (b + 255) & ~size_t(255); };
+  const size_t seg_bytes = up((size_t)n_seg * sizeof(BsSeg)), fold_bytes = up((size_t)n_seg * 8);
+  const size_t pick_bytes = up((size_t)n_seg * BS_MAX_Q * sizeof(BsPick));
+  const size_t samp_bytes = up((size_t)(n_series > 0 ? n_series : 1) * (S->P > 0 ? S->P : 1) * 8);
+  unsigned char* scr = (unsigned char*)pmx_scratch(ctx, PMX_SCR_BRACKET, seg_bytes + 4 * fold_bytes + pick_bytes + samp_bytes +
+                                                                         (size_t)n_seg * cap * 8);
+  if (!scr) return PMX_E_CUDA;
+  S->segs = (BsSeg*)scr; scr += seg_bytes;
+  S->f_sum = (double*)scr; scr += fold_bytes;
+  S->f_cnt = (int64_t*)scr; scr += fold_bytes;
+  S->f_min = (double*)scr; scr += fold_bytes;
+  S->f_max = (double*)scr; scr += fold_bytes;
+  S->picks = (BsPick*)scr; scr += pick_bytes;
+  S->samp = (double*)scr; scr += samp_bytes;
+  S->lists = (unsigned long long*)scr;
+  (void)n_q;
+  return PMX_OK;
+}
+// sample + brackets of this rank's rows
+static int bs_launch_bounds(const BsScratch& S, const double* d_x, int64_t n_series, int64_t n_steps, int64_t n_seg,
+                            const int32_t* d_perm, const int64_t* d_goff, const double* d_q, int64_t n_q, cudaStream_t st) {
+  const bool data = n_series > 0 && n_steps > 0;
+  if (data) {
+    const int64_t slots = n_series * S.P;
+    bs_sample_kernel<<<(unsigned)((slots + 255) / 256), 256, 0, st>>>(d_x, n_steps, n_series, S.P, S.samp);
+    PMX_LAUNCH_CHECK();
+  }
+  const size_t smem = (size_t)BS_KCAP * 8 + (size_t)2 * n_q * BS_BINS * sizeof(unsigned int);
+  PMX_CUDA(cudaFuncSetAttribute(bs_bounds_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)(BS_KCAP * 8 + 2 * BS_MAX_Q * BS_BINS * sizeof(unsigned int))));
+  bs_bounds_kernel<<<(unsigned)(n_seg * BS_CL), 1024, smem, st>>>(S.samp, data ? S.P : 0, d_perm, d_goff, d_q, (int)n_q, S.segs);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+static int bs_launch_sweep(const BsScratch& S, const double* d_x, int64_t n_series, int64_t n_steps, const int32_t* d_seg,
+                           int64_t n_q, cudaStream_t st) {
+  if (n_series <= 0 || n_steps <= 0) return PMX_OK;
+  const unsigned cap = (unsigned)S.cap;
+  switch (n_q) {
+    case 1: bs_sweep_kernel<1><<<(unsigned)n_series, PMX_ROW_THREADS, 0, st>>>(d_x, n_steps, d_seg, S.part, S.segs, S.lists, cap); break;
+    case 2: bs_sweep_kernel<2><<<(unsigned)n_series, PMX_ROW_THREADS, 0, st>>>(d_x, n_steps, d_seg, S.part, S.segs, S.lists, cap); break;
+    case 3: bs_sweep_kernel<3><<<(unsigned)n_series, PMX_ROW_THREADS, 0, st>>>(d_x, n_steps, d_seg, S.part, S.segs, S.lists, cap); break;
+    default: bs_sweep_kernel<4><<<(unsigned)n_series, PMX_ROW_THREADS, 0, st>>>(d_x, n_steps, d_seg, S.part, S.segs, S.lists, cap); break;
+  }
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
 
 extern "C" int pmx_summary_quantiles(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
                                      const int32_t* d_seg, int64_t n_seg, const int32_t* d_perm, const int64_t* d_goff,
@@ -590,43 +1010,11 @@ extern "C" int pmx_summary_quantiles(pmx_ctx* ctx, const double* d_x, int64_t n_
   if (n_seg == 0) return PMX_OK;
   PMX_REQUIRE(d_goff && d_q && d_count, "NULL buffer");
   PMX_REQUIRE(n_series == 0 || (d_x && d_seg && d_perm), "NULL buffer");
-  // scratch: per-series partials | per-segment brackets and counters | sample | lists
-  const int64_t P = (n_steps + BS_STRIDE - 1) / BS_STRIDE;
-  Part* part = nullptr;
-  if (n_series > 0) {
-    part = (Part*)pmx_scratch(ctx, PMX_SCR_PARTIALS, (size_t)n_series * sizeof(Part));
-    if (!part) return PMX_E_CUDA;
-  }
-  int64_t cap = ((int64_t)256 << 20) / 8 / n_seg;
-  if (cap > (1 << 22)) cap = 1 << 22;
-  if (cap < 4096) cap = 4096;
-  const size_t seg_bytes = ((size_t)n_seg * sizeof(BsSeg) + 255) & ~size_t(255);
-  const size_t samp_bytes = ((size_t)n_series * (P > 0 ? P : 1) * 8 + 255) & ~size_t(255);
-  unsigned char* scr = (unsigned char*)pmx_scratch(ctx, PMX_SCR_BRACKET, seg_bytes + samp_bytes + (size_t)n_seg * cap * 8);
-  if (!scr) return PMX_E_CUDA;
-  BsSeg* segs = (BsSeg*)scr;
-  double* samp = (double*)(scr + seg_bytes);
-  unsigned long long* lists = (unsigned long long*)(scr + seg_bytes + samp_bytes);
-  const bool data = n_series > 0 && n_steps > 0;
-  if (data) {
-    const int64_t slots = n_series * P;
-    bs_sample_kernel<<<(unsigned)((slots + 255) / 256), 256, 0, st>>>(d_x, n_steps, n_series, P, samp);
-    PMX_LAUNCH_CHECK();
-  }
-  const size_t smem = (size_t)BS_KCAP * 8 + (size_t)2 * n_q * BS_BINS * sizeof(unsigned int);
-  PMX_CUDA(cudaFuncSetAttribute(bs_bounds_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)(BS_KCAP * 8 + 2 * BS_MAX_Q * BS_BINS * sizeof(unsigned int))));
-  bs_bounds_kernel<<<(unsigned)(n_seg * BS_CL), 1024, smem, st>>>(samp, data ? P : 0, d_perm, d_goff, d_q, (int)n_q, segs);
-  PMX_LAUNCH_CHECK();
-  if (data) {
-    switch (n_q) {
-      case 1: bs_sweep_kernel<1><<<(unsigned)n_series, PMX_ROW_THREADS, 0, st>>>(d_x, n_steps, d_seg, part, segs, lists, (unsigned)cap); break;
-      case 2: bs_sweep_kernel<2><<<(unsigned)n_series, PMX_ROW_THREADS, 0, st>>>(d_x, n_steps, d_seg, part, segs, lists, (unsigned)cap); break;
-      case 3: bs_sweep_kernel<3><<<(unsigned)n_series, PMX_ROW_THREADS, 0, st>>>(d_x, n_steps, d_seg, part, segs, lists, (unsigned)cap); break;
-      default: bs_sweep_kernel<4><<<(unsigned)n_series, PMX_ROW_THREADS, 0, st>>>(d_x, n_steps, d_seg, part, segs, lists, (unsigned)cap); break;
-    }
-    PMX_LAUNCH_CHECK();
-  }
+  BsScratch S;
+  if (int rc = bs_scratch(ctx, n_series, n_steps, n_seg, n_q, &S)) return rc;
+  if (int rc = bs_launch_bounds(S, d_x, n_series, n_steps, n_seg, d_perm, d_goff, d_q, n_q, st)) return rc;
+  if (int rc = bs_launch_sweep(S, d_x, n_series, n_steps, d_seg, n_q, st)) return rc;
+  Part* part = S.part; BsSeg* segs = S.segs; unsigned long long* lists = S.lists; const int64_t cap = S.cap;
   if (int rc = pmx_internal_group_fold(part, d_perm, d_goff, n_seg, d_sum, d_count, d_min, d_max, d_mean, st)) return rc;
   dim3 grid((unsigned)n_q * BS_RC, (unsigned)n_seg);
   bs_resolve_kernel<<<grid, 1024, 0, st>>>(segs, lists, (unsigned)cap, d_count, d_q, (int)n_q, d_n, d_lo, d_hi, d_x_lo, d_x_hi,
@@ -634,3 +1022,120 @@ extern "C" int pmx_summary_quantiles(pmx_ctx* ctx, const double* d_x, int64_t n_
   PMX_LAUNCH_CHECK();
   return PMX_OK;
 }
+
+// ---- several ranks: the same selection in five calls with four collectives between them ----------
+extern "C" {
+
+int pmx_bsel_widths(int* bounds_w, int* pack_w, int* row_w) {
+  if (bounds_w) *bounds_w = BS_BOUNDS_W;
+  if (pack_w) *pack_w = BS_PACK_W;
+  if (row_w) *row_w = (int)BS_ROW_W;
+  return PMX_OK;
+}
+
+#define BS_COMMON_CHECKS()                                                                                        \
+  PMX_REQUIRE(ctx, "ctx is NULL");                                                                                \
+  PMX_REQUIRE(n_seg >= 0 && n_seg <= 65535, "n_seg must be in [0, 65535]");                                        \
+  if (n_q < 1 || n_q > BS_MAX_Q) return pmx_fail(PMX_E_LIMIT, "%s: n_q must be in [1, %d]", __func__, BS_MAX_Q);   \
+  if (n_seg == 0) return PMX_OK
+
+int pmx_bsel_begin(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps, const int32_t* d_seg, int64_t n_seg,
+                   const int32_t* d_perm, const int64_t* d_goff, const double* d_q, int64_t n_q, double* d_bounds,
+                   pmx_stream stream) {
+  BS_COMMON_CHECKS();
+  PMX_REQUIRE(n_series >= 0 && n_steps >= 0, "bad sizes");
+  PMX_REQUIRE(d_goff && d_q && d_bounds, "NULL buffer");
+  PMX_REQUIRE(n_series == 0 || (d_x && d_seg && d_perm), "NULL buffer");
+  cudaStream_t st = pmx_st(stream);
+  BsScratch S;
+  if (int rc = bs_scratch(ctx, n_series, n_steps, n_seg, n_q, &S)) return rc;
+  if (int rc = bs_launch_bounds(S, d_x, n_series, n_steps, n_seg, d_perm, d_goff, d_q, n_q, st)) return rc;
+  bs_export_bounds_kernel<<<(unsigned)((n_seg + 127) / 128), 128, 0, st>>>(S.segs, n_seg, d_bounds);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
+int pmx_bsel_sweep(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps, const int32_t* d_seg, int64_t n_seg,
+                   const int32_t* d_perm, const int64_t* d_goff, int64_t n_q, const double* d_bounds_all, int n_ranks,
+                   uint64_t* d_packed, pmx_stream stream) {
+  BS_COMMON_CHECKS();
+  PMX_REQUIRE(n_ranks >= 1 && d_bounds_all && d_packed && d_goff, "NULL buffer or bad rank count");
+  cudaStream_t st = pmx_st(stream);
+  BsScratch S;
+  if (int rc = bs_scratch(ctx, n_series, n_steps, n_seg, n_q, &S)) return rc;
+  bs_merge_bounds_kernel<<<(unsigned)((n_seg + 127) / 128), 128, 0, st>>>(d_bounds_all, n_ranks, n_seg, (int)n_q, S.segs);
+  PMX_LAUNCH_CHECK();
+  if (int rc = bs_launch_sweep(S, d_x, n_series, n_steps, d_seg, n_q, st)) return rc;
+  if (int rc = pmx_internal_group_fold(S.part, d_perm, d_goff, n_seg, S.f_sum, S.f_cnt, S.f_min, S.f_max, nullptr, st)) return rc;
+  bs_pack_kernel<<<(unsigned)((n_seg + 127) / 128), 128, 0, st>>>(S.segs, S.f_sum, S.f_cnt, S.f_min, S.f_max, n_seg, (unsigned)S.cap,
+                                                                  (unsigned long long*)d_packed);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
+int pmx_bsel_hist(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg, int64_t n_q, const uint64_t* d_packed_all,
+                  int n_ranks, double* d_sum, int64_t* d_count, double* d_min, double* d_max, double* d_mean, uint32_t* d_hist,
+                  pmx_stream stream) {
+  BS_COMMON_CHECKS();
+  PMX_REQUIRE(n_ranks >= 1 && d_packed_all && d_count && d_hist, "NULL buffer or bad rank count");
+  cudaStream_t st = pmx_st(stream);
+  BsScratch S;
+  if (int rc = bs_scratch(ctx, n_series, n_steps, n_seg, n_q, &S)) return rc;
+  bs_combine_kernel<<<(unsigned)((n_seg + 127) / 128), 128, 0, st>>>((const unsigned long long*)d_packed_all, n_ranks, n_seg, S.segs,
+                                                                     d_sum, d_count, d_min, d_max, d_mean);
+  PMX_LAUNCH_CHECK();
+  PMX_CUDA(cudaMemsetAsync(d_hist, 0, (size_t)n_seg * n_q * BS_BINS * sizeof(uint32_t), st));
+  dim3 grid((unsigned)n_q * 4, (unsigned)n_seg);
+  bs_midhist_kernel<false><<<grid, 1024, 0, st>>>(S.segs, S.lists, (unsigned)S.cap, (int)n_q, nullptr, d_hist);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
+int pmx_bsel_hist2(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg, const double* d_q, int64_t n_q,
+                   const uint32_t* d_hist, const int64_t* d_count, uint32_t* d_hist2, pmx_stream stream) {
+  BS_COMMON_CHECKS();
+  PMX_REQUIRE(d_q && d_hist && d_count && d_hist2, "NULL buffer");
+  cudaStream_t st = pmx_st(stream);
+  BsScratch S;
+  if (int rc = bs_scratch(ctx, n_series, n_steps, n_seg, n_q, &S)) return rc;
+  dim3 grid((unsigned)n_q, (unsigned)n_seg);
+  bs_pick1_kernel<<<grid, 1024, 0, st>>>(S.segs, d_hist, d_count, d_q, (int)n_q, S.picks);
+  PMX_LAUNCH_CHECK();
+  PMX_CUDA(cudaMemsetAsync(d_hist2, 0, (size_t)n_seg * n_q * 2 * BS_BINS * sizeof(uint32_t), st));
+  dim3 grid4((unsigned)n_q * 4, (unsigned)n_seg);
+  bs_midhist_kernel<true><<<grid4, 1024, 0, st>>>(S.segs, S.lists, (unsigned)S.cap, (int)n_q, S.picks, d_hist2);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
+int pmx_bsel_rows(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg, int64_t n_q, const uint32_t* d_hist2,
+                  uint64_t* d_rows, pmx_stream stream) {
+  BS_COMMON_CHECKS();
+  PMX_REQUIRE(d_hist2 && d_rows, "NULL buffer");
+  BsScratch S;
+  if (int rc = bs_scratch(ctx, n_series, n_steps, n_seg, n_q, &S)) return rc;
+  dim3 grid((unsigned)n_q, (unsigned)n_seg);
+  bs_pick2_rows_kernel<<<grid, 1024, 0, pmx_st(stream)>>>(S.segs, S.lists, (unsigned)S.cap, d_hist2, (int)n_q, S.picks,
+                                                         (unsigned long long*)d_rows);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
+int pmx_bsel_finish(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg, int64_t n_q, const uint64_t* d_rows_all,
+                    int n_ranks, const int64_t* d_count, int64_t* d_n, int64_t* d_lo, int64_t* d_hi, double* d_x_lo,
+                    double* d_x_hi, double* d_value, int32_t* d_failed, pmx_stream stream) {
+  PMX_REQUIRE(d_failed, "d_failed is NULL");
+  cudaStream_t st = pmx_st(stream);
+  PMX_CUDA(cudaMemsetAsync(d_failed, 0, sizeof(int32_t), st));
+  BS_COMMON_CHECKS();
+  PMX_REQUIRE(n_ranks >= 1 && d_rows_all && d_count, "NULL buffer or bad rank count");
+  BsScratch S;
+  if (int rc = bs_scratch(ctx, n_series, n_steps, n_seg, n_q, &S)) return rc;
+  dim3 grid((unsigned)n_q, (unsigned)n_seg);
+  bs_final_kernel<<<grid, 256, 0, st>>>(S.segs, S.picks, (const unsigned long long*)d_rows_all, n_ranks, n_seg, (int)n_q, d_count,
+                                        d_n, d_lo, d_hi, d_x_lo, d_x_hi, d_value, (unsigned int*)d_failed);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
+}  // extern "C"

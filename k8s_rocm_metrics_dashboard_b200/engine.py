@@ -583,6 +583,60 @@ class Engine:
         self.launches += 5 if S > 0 and T > 0 else 3        # sample, bounds, sweep, fold, resolve
         return (sm, cnt, mn, mx, mean), outs, failed
 
+    def summary_quantiles_ranks(self, x, seg, n_seg, qs, perm_goff, group):
+        """``summary_quantiles`` over ALL ranks of ``group`` (every rank passes its own rows): six library
+        calls with five small collectives between them (brackets, counters + partial summaries, two
+        histograms, the keys of the buckets that hold the wanted ranks), one sweep of ``x`` on every rank.
+        Returns ((sum, count, min, max, mean) over all ranks, quantiles dict, failed) -- ``failed`` is the
+        same on every rank."""
+        import ctypes as C
+        import torch.distributed as dist
+        t = self.torch
+        x = self._dev(x, t.float64)
+        S, T = x.shape
+        d_seg = self._dev(seg, t.int32)
+        d_perm, d_goff = self._dev(perm_goff[0], t.int32), self._dev(perm_goff[1], t.int64)
+        n_q = len(qs)
+        d_q = self._quantile_levels(qs)
+        world = dist.get_world_size(group)
+        key = (n_seg, n_q, world)
+        cache = self.__dict__.setdefault("_bsel", {})
+        if key not in cache:
+            w = [C.c_int(0) for _ in range(3)]
+            _abi.check(self.lib.pmx_bsel_widths(C.byref(w[0]), C.byref(w[1]), C.byref(w[2])))
+            bw, pw, rw = (int(v.value) for v in w)
+            cache[key] = {
+                "bounds": self._empty((n_seg * bw,), t.float64), "bounds_all": self._empty((world * n_seg * bw,), t.float64),
+                "packed": self._empty((n_seg * pw,), t.int64), "packed_all": self._empty((world * n_seg * pw,), t.int64),
+                "hist": self._empty((n_seg * n_q * _abi.QUANTILE_BINS,), t.int32),
+                "hist2": self._empty((n_seg * n_q * 2 * _abi.QUANTILE_BINS,), t.int32),
+                "rows": self._empty((n_seg * n_q * rw,), t.int64), "rows_all": self._empty((world * n_seg * n_q * rw,), t.int64)}
+        b = cache[key]
+        sm, mn, mx, mean = (self._empty((n_seg,), t.float64) for _ in range(4))
+        cnt = self._empty((n_seg,), t.int64)
+        outs = {"n": self._empty((n_seg,), t.int64), "lo": self._empty((n_seg, n_q), t.int64),
+                "hi": self._empty((n_seg, n_q), t.int64), "x_lo": self._empty((n_seg, n_q), t.float64),
+                "x_hi": self._empty((n_seg, n_q), t.float64), "value": self._empty((n_seg, n_q), t.float64)}
+        failed = self._empty((1,), t.int32)
+        lib, p, st = self.lib, self._ptr, self._stream
+        _abi.check(lib.pmx_bsel_begin(self.ctx, p(x), S, T, p(d_seg), n_seg, p(d_perm), p(d_goff), p(d_q), n_q, p(b["bounds"]), st()))
+        dist.all_gather_into_tensor(b["bounds_all"], b["bounds"], group=group)
+        _abi.check(lib.pmx_bsel_sweep(self.ctx, p(x), S, T, p(d_seg), n_seg, p(d_perm), p(d_goff), n_q, p(b["bounds_all"]), world,
+                                      p(b["packed"]), st()))
+        dist.all_gather_into_tensor(b["packed_all"], b["packed"], group=group)
+        _abi.check(lib.pmx_bsel_hist(self.ctx, S, T, n_seg, n_q, p(b["packed_all"]), world, p(sm), p(cnt), p(mn), p(mx), p(mean),
+                                     p(b["hist"]), st()))
+        dist.all_reduce(b["hist"], op=dist.ReduceOp.SUM, group=group)
+        _abi.check(lib.pmx_bsel_hist2(self.ctx, S, T, n_seg, p(d_q), n_q, p(b["hist"]), p(cnt), p(b["hist2"]), st()))
+        dist.all_reduce(b["hist2"], op=dist.ReduceOp.SUM, group=group)
+        _abi.check(lib.pmx_bsel_rows(self.ctx, S, T, n_seg, n_q, p(b["hist2"]), p(b["rows"]), st()))
+        dist.all_gather_into_tensor(b["rows_all"], b["rows"], group=group)
+        _abi.check(lib.pmx_bsel_finish(self.ctx, S, T, n_seg, n_q, p(b["rows_all"]), world, p(cnt), p(outs["n"]), p(outs["lo"]),
+                                       p(outs["hi"]), p(outs["x_lo"]), p(outs["x_hi"]), p(outs["value"]), p(failed), st()))
+        # sample, bounds, export | merge, sweep, fold, pack | combine, histogram | pick, histogram | pick | final
+        self.launches += (14 if S > 0 and T > 0 else 12)
+        return (sm, cnt, mn, mx, mean), outs, failed
+
     def defer_flag(self, counter):
         """Copies a device int32 counter to pinned host memory behind the stream; ``deferred_ok`` looks at it."""
         t = self.torch

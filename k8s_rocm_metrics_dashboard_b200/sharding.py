@@ -122,8 +122,11 @@ class ShardedEngine:
         are verified on the device, and the per-pass selection runs if the check fails (with
         ``defer_check`` the check is left to ``Engine.deferred_ok``, see ``Engine.quantiles``)."""
         eng = self.eng
-        if self.world == 1 and 1 <= len(qs) <= 4:
-            summary, q, failed = eng.summary_quantiles(x, seg, n_seg, qs, perm_goff)
+        if 1 <= len(qs) <= 4:
+            if self.world == 1:
+                summary, q, failed = eng.summary_quantiles(x, seg, n_seg, qs, perm_goff)
+            else:                                       # ``failed`` is the same on every rank: they fall back together
+                summary, q, failed = eng.summary_quantiles_ranks(x, seg, n_seg, qs, perm_goff, self.group or _world_group())
             if _unchecked:
                 return summary, q, failed
             if defer_check:

@@ -66,3 +66,27 @@ def test_group_protocol_falls_back_to_passes_when_rows_do_not_fit(eng, world1):
     seg = np.array([0] * 64 + [1] * 4, dtype=np.int32)
     for summary in (None, _summary(z, seg, 2)):
         _check(eng, world1, z, seg, 2, [0.5, 0.9], summary)
+
+
+@pytest.mark.parametrize("kind", ["uniform", "integers", "zeros", "counters", "nan_heavy", "constant"])
+def test_bracket_selection_over_ranks_equals_one_sweep(eng, world1, kind):
+    """Engine.summary_quantiles_ranks (five calls, four collectives) on a one-rank group gives what
+    pmx_summary_quantiles and the per-pass selection give, bit for bit."""
+    from tests.test_gpu_summary_quantiles import KINDS, QS, _data, _same
+    t = eng.torch
+    rng = np.random.default_rng(KINDS.index(kind) + 300)
+    S, T, M = 64, 4100, 5
+    x = _data(kind, S, T, rng)
+    gid = (np.arange(S) % M).astype(np.int32)
+    gid[5] = -1
+    perm, goff = group_index(gid, M)
+    pg = (t.as_tensor(perm, device=eng.device), t.as_tensor(goff, device=eng.device))
+    dx, seg = t.as_tensor(x, device=eng.device), t.as_tensor(gid, device=eng.device)
+    summ, q, failed = eng.summary_quantiles_ranks(dx, seg, M, QS, pg, world1)
+    assert int(failed.item()) == 0
+    ref_s = eng.group_reduce(dx, None, M, perm_goff=pg)
+    ref_q = eng.quantiles(dx, seg, M, list(QS), row_order=pg[0], summary=(ref_s[1], ref_s[2], ref_s[3]))
+    _same(summ, q, ref_s, ref_q, f"ranks {kind}")
+    s1, q1, f1 = eng.summary_quantiles(dx, seg, M, QS, pg)
+    assert int(f1.item()) == 0
+    _same(summ, q, s1, q1, f"ranks vs one sweep {kind}")
