@@ -133,7 +133,10 @@ bs_bounds_kernel(const double* __restrict__ samp, int64_t P, const int32_t* __re
     unsigned long long mn = ~0ULL, mx = 0;
     const uint64_t a = (uint64_t)rank * per, b = a + per < used ? a + per : used;
     for (uint64_t u = a + threadIdx.x; u < b; u += blockDim.x) {
-      const uint64_t idx = u * skip;
+      // a hashed slot of every `skip` consecutive ones: a fixed phase would take the same stretches of
+      // time from every row, and rows that move together (counters) would leave gaps in the sample
+      uint64_t idx = u * skip + (skip > 1 ? bs_hash(u + ((uint64_t)g << 40)) % skip : 0);
+      if (idx >= slots) idx = slots - 1;
       uint64_t r, i;
       if (slots <= 0xffffffffULL) { r = (unsigned)idx / (unsigned)P; i = (unsigned)idx - (unsigned)r * (unsigned)P; }
       else { r = idx / (uint64_t)P; i = idx - r * (uint64_t)P; }

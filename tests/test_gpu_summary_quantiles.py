@@ -162,3 +162,24 @@ def test_more_than_four_levels_use_the_passes(eng):
         assert_bits_equal(q["value"][g].cpu().numpy(), np.array(o["value"]), "five levels")
     with pytest.raises(Exception):
         eng.summary_quantiles(t.as_tensor(x, device=eng.device), t.as_tensor(gid, device=eng.device), 3, qs, pg)
+
+
+def test_thinned_sample_of_rows_that_move_together(eng):
+    """More than 98 304 sample slots per segment: the bounds use a thinned sample.  Counters that rise
+    together make every stretch of time one narrow cluster of values, so a thinning with a fixed
+    phase would miss whole ranges (config 3's counters did); the phase is hashed."""
+    t = eng.torch
+    S, T, M = 512, 16384, 2                                        # 256 rows x 512 slots = 131 072 slots per segment
+    g = t.Generator(device=eng.device); g.manual_seed(21)
+    slope = 4000.0 + 2000.0 * t.rand((S, 1), generator=g, device=eng.device, dtype=t.float64)
+    x = slope * t.arange(T, device=eng.device, dtype=t.float64)[None, :] + t.rand((S, T), generator=g, device=eng.device, dtype=t.float64)
+    gid = (np.arange(S) % M).astype(np.int32)
+    perm, goff = group_index(gid, M)
+    pg = (t.as_tensor(perm, device=eng.device), t.as_tensor(goff, device=eng.device))
+    seg = t.as_tensor(gid, device=eng.device)
+    for qs in (QS, (0.01, 0.25, 0.75, 0.999)):
+        summ, q, failed = eng.summary_quantiles(x, seg, M, qs, pg)
+        assert int(failed.item()) == 0
+        ref_s = eng.group_reduce(x, None, M, perm_goff=pg)
+        ref_q = eng.quantiles(x, seg, M, list(qs), row_order=pg[0], summary=(ref_s[1], ref_s[2], ref_s[3]))
+        _same(summ, q, ref_s, ref_q, f"thinned {qs}")
