@@ -336,7 +336,7 @@ int pmx_quantile_finish(pmx_ctx* ctx, const uint64_t* d_state, int64_t n_seg, co
                         int64_t n_q, int64_t* d_n, int64_t* d_lo, int64_t* d_hi,
                         double* d_x_lo, double* d_x_hi, double* d_value, pmx_stream stream);
 /* One GPU: the per-segment summary of pmx_group_reduce(per_step = 0) AND the exact quantiles of
- * pmx_quantile_select from ONE sweep of d_x (plus a sample of 1/32 of it).  Replaces, for the range
+ * pmx_quantile_select from ONE sweep of d_x (plus a sample of 1/64 of it).  Replaces, for the range
  * matrices, what app.py:216-221 and :335-345 compute for the instant vector (mean / max / min per
  * metric) together with SURVEY X7's Series.quantile -- the reference has no counterpart of the
  * quantiles.  A sample fixes a bracket of two data values around each quantile; the sweep forms

@@ -4,7 +4,7 @@
 // app.py:216-221 / :335-345 do for the instant vector).
 //
 // A radix selection reads the data once per digit, after a first read for the summary.  Here a
-// small sample (one value per 32 steps of every row, at a hashed position) fixes, per quantile, a
+// small sample (one value per 64 steps of every row, at a hashed position) fixes, per quantile, a
 // bracket [lo, hi] of two sample VALUES that holds the wanted order statistics unless the sample is
 // off by more than five standard deviations.  One sweep of the data then
 //   (a) forms the per-series partial sums exactly as pmx_group_reduce does (reduce_part.cuh),
@@ -27,7 +27,7 @@ namespace {
 
 constexpr int BS_MAX_Q = 4;
 constexpr int BS_BINS = 2048;
-constexpr int BS_STRIDE = 32;                    // one sampled value per this many steps of a row
+constexpr int BS_STRIDE = 64;                    // one sampled value per this many steps of a row
 constexpr double BS_SIGMAS = 5.0;
 constexpr int BS_SMALL = 256;                    // a bucket this small is ranked directly
 constexpr int BS_WBUF = 576;                     // values a warp can stage: 256 kept + a trip of 8 per lane + head and tail
@@ -600,6 +600,8 @@ struct BsPick {                                  // per (segment, quantile): whe
   int zone[2];                                   // -1 empty segment, 0 fail, 1 lo, 2 inside, 3 hi
   unsigned int bin[2];                           // zone 2: first two digits (22 bits) of the bucket
   unsigned long long r[2];                       // zone 2: rank inside the bucket
+  unsigned int bin2[2];                          // ... after the second digit (22 bits)
+  unsigned long long r2[2];
   unsigned long long ans[2];                     // zones 1 and 3: the key
   unsigned long long k0, k1;
   double tt;
@@ -785,68 +787,72 @@ bs_pick1_kernel(const BsSeg* __restrict__ segs, const unsigned int* __restrict__
   if (threadIdx.x == 0) *pick = s_p;
 }
 
-// CTA (j, g), after the all-reduce of the second histograms: the second digit of either bucket, and
-// this rank's keys of the buckets (22 bits now) into its row: count | min, max of either bucket | keys.
+// Four CTAs per (j, g), after the all-reduce of the second histograms: the second digit of either
+// bucket, and this rank's keys of the buckets (22 bits now) into its row, which the caller cleared:
+// count | ~min, max of rank 0's bucket | ~min, max of rank 1's bucket | keys  (the minimum is kept
+// complemented so that zero is neutral for all four).
 __global__ void __launch_bounds__(1024)
 bs_pick2_rows_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __restrict__ lists, unsigned cap,
                      const unsigned int* __restrict__ hist2, int n_q, BsPick* __restrict__ picks,
                      unsigned long long* __restrict__ rows) {
   __shared__ unsigned int s_warp[32];
-  __shared__ unsigned int s_bin[2], s_cnt;
+  __shared__ unsigned int s_bin[2];
   __shared__ unsigned long long s_r[2], s_mm[4];
-  const int j = blockIdx.x, g = blockIdx.y;
+  const int j = blockIdx.x >> 2, quarter = blockIdx.x & 3, g = blockIdx.y;
   unsigned long long* row = rows + ((size_t)g * n_q + j) * BS_ROW_W;
   BsPick* pick = picks + (size_t)g * n_q + j;
-  const BsPick P = *pick;
-  if (threadIdx.x == 0) { s_cnt = 0; s_mm[0] = s_mm[2] = ~0ULL; s_mm[1] = s_mm[3] = 0; s_bin[0] = s_bin[1] = 0xffffffffu; }
-  if (P.zone[0] != 2 && P.zone[1] != 2) {
-    if (threadIdx.x == 0) { row[0] = 0; row[1] = row[3] = ~0ULL; row[2] = row[4] = 0; }
-    return;
-  }
+  const int z0 = pick->zone[0], z1 = pick->zone[1];
+  if (z0 != 2 && z1 != 2) return;
+  const unsigned bin_a = pick->bin[0], bin_b = pick->bin[1];
+  const unsigned long long ra = pick->r[0], rb = pick->r[1];
+  if (threadIdx.x == 0) { s_mm[0] = s_mm[1] = s_mm[2] = s_mm[3] = 0; s_bin[0] = s_bin[1] = 0xffffffffu; }
   __syncthreads();
   for (int t = 0; t < 2; ++t) {
-    if (P.zone[t] != 2) continue;                                   // uniform
+    if ((t ? z1 : z0) != 2) continue;                               // uniform
     const unsigned int* h = hist2 + (((size_t)g * n_q + j) * 2 + t) * BS_BINS;
     const unsigned c0 = h[2 * threadIdx.x], c1 = h[2 * threadIdx.x + 1];
     const unsigned base = bs_scan2(c0, c1, s_warp);
-    const unsigned long long r = P.r[t];
-    if (r >= base && r < (unsigned long long)base + c0) { s_bin[t] = (P.bin[t] << 11) | (2 * threadIdx.x); s_r[t] = r - base; }
-    else if (r >= (unsigned long long)base + c0 && r < (unsigned long long)base + c0 + c1) { s_bin[t] = (P.bin[t] << 11) | (2 * threadIdx.x + 1); s_r[t] = r - base - c0; }
+    const unsigned long long r = t ? rb : ra;
+    const unsigned b1st = t ? bin_b : bin_a;
+    if (r >= base && r < (unsigned long long)base + c0) { s_bin[t] = (b1st << 11) | (2 * threadIdx.x); s_r[t] = r - base; }
+    else if (r >= (unsigned long long)base + c0 && r < (unsigned long long)base + c0 + c1) { s_bin[t] = (b1st << 11) | (2 * threadIdx.x + 1); s_r[t] = r - base - c0; }
     __syncthreads();
   }
   const unsigned b0 = s_bin[0], b1 = s_bin[1];
+  if (quarter == 0 && threadIdx.x == 0) {
+    if (z0 == 2) { pick->bin2[0] = b0; pick->r2[0] = s_r[0]; }
+    if (z1 == 2) { pick->bin2[1] = b1; pick->r2[1] = s_r[1]; }
+  }
   const BsSeg& B = segs[g];
   const double lo = B.lo[j], hi = B.hi[j];
   uint64_t kbase; int Z;
   bs_digit_geom(B, j, &kbase, &Z);
   const unsigned n_list = B.list_n > cap ? cap : B.list_n;
   const unsigned long long* keys = lists + (size_t)g * cap;
-  for (unsigned i0 = 0; i0 < n_list; i0 += blockDim.x * 8) {
+  const unsigned part_n = (n_list + 3) / 4;
+  const unsigned k_a = quarter * part_n < n_list ? quarter * part_n : n_list;
+  const unsigned k_b = k_a + part_n < n_list ? k_a + part_n : n_list;
+  for (unsigned i0 = k_a; i0 < k_b; i0 += blockDim.x * 8) {
     unsigned long long kk[8];
 #pragma unroll
-    for (int u = 0; u < 8; ++u) { const unsigned i = i0 + u * blockDim.x + threadIdx.x; kk[u] = i < n_list ? keys[i] : 0ULL; }
+    for (int u = 0; u < 8; ++u) { const unsigned i = i0 + u * blockDim.x + threadIdx.x; kk[u] = i < k_b ? keys[i] : 0ULL; }
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
       const unsigned i = i0 + u * blockDim.x + threadIdx.x;
-      if (i >= n_list) continue;
+      if (i >= k_b) continue;
       const double v = key_f64(kk[u]);
       if (!(v > lo && v < hi)) continue;
       const unsigned d = (unsigned)(((kk[u] - kbase) << Z) >> 42);
       if (d != b0 && d != b1) continue;
-      const unsigned at = atomicAdd(&s_cnt, 1u);
+      const unsigned long long at = atomicAdd(&row[0], 1ULL);
       if (at < BS_ROWK) row[5 + at] = kk[u];
       const int t = d == b0 ? 0 : 1;
-      if (kk[u] < *(volatile unsigned long long*)&s_mm[2 * t]) atomicMin(&s_mm[2 * t], kk[u]);
+      if (~kk[u] > *(volatile unsigned long long*)&s_mm[2 * t]) atomicMax(&s_mm[2 * t], ~kk[u]);
       if (kk[u] > *(volatile unsigned long long*)&s_mm[2 * t + 1]) atomicMax(&s_mm[2 * t + 1], kk[u]);
     }
   }
   __syncthreads();
-  if (threadIdx.x == 0) {
-    row[0] = s_cnt; row[1] = s_mm[0]; row[2] = s_mm[1]; row[3] = s_mm[2]; row[4] = s_mm[3];
-    if (b0 == b1 && b0 != 0xffffffffu) { row[3] = s_mm[0]; row[4] = s_mm[1]; }   // both ranks in one bucket
-    if (P.zone[0] == 2) { pick->bin[0] = b0; pick->r[0] = s_r[0]; }
-    if (P.zone[1] == 2) { pick->bin[1] = b1; pick->r[1] = s_r[1]; }
-  }
+  if (threadIdx.x < 4 && s_mm[threadIdx.x]) atomicMax(&row[1 + threadIdx.x], s_mm[threadIdx.x]);
 }
 
 // CTA (j, g), after the all-gather of the rows ([world][n_seg][n_q][ROW]): every rank settles every
@@ -882,9 +888,10 @@ bs_final_kernel(const BsSeg* __restrict__ segs, const BsPick* __restrict__ picks
     s_ok[t] = 1; s_ans[t] = P.ans[t];
     if (P.zone[t] == 2) {
       unsigned long long mn = ~0ULL, mx = 0;
+      const int ts = (t == 1 && P.zone[0] == 2 && P.bin2[0] == P.bin2[1]) ? 0 : t;   // one bucket for both ranks: filed under rank 0
       for (int w = 0; w < world; ++w) {
         const unsigned long long* row = rows_all + (((size_t)w * n_seg + g) * n_q + j) * BS_ROW_W;
-        mn = row[1 + 2 * t] < mn ? row[1 + 2 * t] : mn; mx = row[2 + 2 * t] > mx ? row[2 + 2 * t] : mx;
+        mn = ~row[1 + 2 * ts] < mn ? ~row[1 + 2 * ts] : mn; mx = row[2 + 2 * ts] > mx ? row[2 + 2 * ts] : mx;
       }
       if (mn == mx) s_ans[t] = mn; else s_ok[t] = 0;             // all keys of the bucket are one value
     }
@@ -916,7 +923,7 @@ bs_final_kernel(const BsSeg* __restrict__ segs, const BsPick* __restrict__ picks
           if ((unsigned)(((ku - klo) << Z) >> 42) == d) { less += ku < ki; eq += ku == ki; }
         }
         for (int t = 0; t < 2; ++t)
-          if (P.zone[t] == 2 && !s_ok[t] && P.bin[t] == d && P.r[t] >= less && P.r[t] < (unsigned long long)less + eq) s_ans[t] = ki;
+          if (P.zone[t] == 2 && !s_ok[t] && P.bin2[t] == d && P.r2[t] >= less && P.r2[t] < (unsigned long long)less + eq) s_ans[t] = ki;
       }
     }
   }
@@ -1117,7 +1124,8 @@ int pmx_bsel_rows(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg
   PMX_REQUIRE(d_hist2 && d_rows, "NULL buffer");
   BsScratch S;
   if (int rc = bs_scratch(ctx, n_series, n_steps, n_seg, n_q, &S)) return rc;
-  dim3 grid((unsigned)n_q, (unsigned)n_seg);
+  PMX_CUDA(cudaMemsetAsync(d_rows, 0, (size_t)n_seg * n_q * BS_ROW_W * 8, pmx_st(stream)));
+  dim3 grid((unsigned)n_q * 4, (unsigned)n_seg);
   bs_pick2_rows_kernel<<<grid, 1024, 0, pmx_st(stream)>>>(S.segs, S.lists, (unsigned)S.cap, d_hist2, (int)n_q, S.picks,
                                                          (unsigned long long*)d_rows);
   PMX_LAUNCH_CHECK();

@@ -169,7 +169,7 @@ def test_thinned_sample_of_rows_that_move_together(eng):
     together make every stretch of time one narrow cluster of values, so a thinning with a fixed
     phase would miss whole ranges (config 3's counters did); the phase is hashed."""
     t = eng.torch
-    S, T, M = 512, 16384, 2                                        # 256 rows x 512 slots = 131 072 slots per segment
+    S, T, M = 512, 32768, 2                                        # 256 rows x 512 slots = 131 072 slots per segment
     g = t.Generator(device=eng.device); g.manual_seed(21)
     slope = 4000.0 + 2000.0 * t.rand((S, 1), generator=g, device=eng.device, dtype=t.float64)
     x = slope * t.arange(T, device=eng.device, dtype=t.float64)[None, :] + t.rand((S, T), generator=g, device=eng.device, dtype=t.float64)
