@@ -119,6 +119,35 @@ def cpu_time_pandas(ts, val, off, gid, procs):
         return time.perf_counter() - t0
 
 
+def cpu_other_configs():
+    """The pandas whole-step on a stated slice of configs 3, 4 and 5: one process, a few
+    seconds each.  Returns a list of {config, value, unit, cores, kind, sample}."""
+    import numpy as np
+    from oracle import prom_oracle as O
+    from k8s_rocm_metrics_dashboard_b200 import synth
+    out = []
+
+    def run(name, d, n_steps, step_ms, window_ms, what):
+        S = len(d["off"]) - 1
+        gid = (np.arange(S) % N_METRICS).astype(np.int32)
+        t0 = time.perf_counter()
+        O.aggregate_step_pandas(d["ts"], d["val"], d["off"], d["start_ms"], step_ms, n_steps, window_ms, gid, N_METRICS, QS,
+                                LOOKBACK_MS)
+        sec = time.perf_counter() - t0
+        n = int(d["off"][-1])
+        out.append({"config": name, "value": n / sec, "unit": "samples/s", "cores": 1, "kind": "port",
+                    "sample": f"{what} ({n} samples, {sec:.1f} s), pandas {_pandas_version()} single process"})
+
+    d = synth.dense(1, 8, 16, 40320, seed=3, nan_frac=1e-3, kinds="ttk")
+    run("config3", d, 40320, d["step_ms"], WINDOW_STEPS * d["step_ms"], "1 of 1024 nodes: 128 series x 40320 steps")
+    d = synth.dense(8, 8, 8, 5760, seed=4, all_counters=True, reset_prob=1e-3)
+    run("config4", d, 5760, d["step_ms"], WINDOW_STEPS * d["step_ms"], "8 of 64 nodes (8 metrics each): 512 counter series with resets x 5760 steps")
+    d = synth.ragged(4000, seed=5)
+    d.setdefault("start_ms", int(d["ts"].min()))
+    run("config5", d, 480, 15000, WINDOW_STEPS * 15000, "4000 of 1 000 000 ragged series resampled to a 15 s grid of 480 steps")
+    return out
+
+
 def host_sample(n_series, seed=0):
     """Config-2-shaped series on the host (same generator family as the device data)."""
     import numpy as np
@@ -456,7 +485,12 @@ def run_engine(args):
                              f"pandas {_pandas_version()} single process, host has {os.cpu_count()} cores"}
         instant = None
         e2e_text = None
+        cpu_other = None
         if world == 1 and not args.no_cpu_baseline:
+            try:
+                cpu_other = cpu_other_configs()
+            except Exception as e:  # noqa: BLE001
+                cpu_other = [{"error": str(e)[:200]}]
             instant = instant_path_times(eng)
             try:
                 e2e_text = e2e_text_block(eng)
@@ -472,7 +506,7 @@ def run_engine(args):
                              "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": traffic, "peak_source": which, "avg_launch_ms": fused_ms,
                              "algorithmic_bytes_per_launch": n_samples * FUSED_BYTES_PER_SAMPLE},
-                "cpu_baseline": cpu,
+                "cpu_baseline": cpu, "cpu_baseline_other": cpu_other,
                 "e2e": {"value": world * n_samples * e2e_steps / e2e_s, "unit": "samples/s",
                         "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps},
                 "gpu_launches": launches, "clocks": clocks, "instant_path": instant,
