@@ -355,19 +355,19 @@ int pmx_summary_quantiles(pmx_ctx* ctx, const double* d_x, int64_t n_series, int
                           double* d_max, double* d_mean, int64_t* d_n, int64_t* d_lo, int64_t* d_hi,
                           double* d_x_lo, double* d_x_hi, double* d_value, int32_t* d_failed, pmx_stream stream);
 /* The same for several ranks (one process per GPU, series sharded; no counterpart in the
- * reference, which is one process): six calls with five small collectives between them, one sweep
+ * reference, which is one process): five calls with four small collectives between them, one sweep
  * of the data on every rank.  All ranks pass the same n_seg, d_q and n_q, and each its own rows
- * (n_series may be 0).  State between the calls lives in ctx scratch, so the six calls of one
+ * (n_series may be 0).  State between the calls lives in ctx scratch, so the five calls of one
  * selection must not interleave with another selection on the same ctx.
  *   pmx_bsel_begin   sample + this rank's brackets -> d_bounds [n_seg * bounds_w] f64
  *                    all-gather d_bounds -> [n_ranks][n_seg * bounds_w]
- *   pmx_bsel_sweep   hull of the brackets, the sweep, this rank's partial summary and counters
- *                    -> d_packed [n_seg * pack_w] (64-bit words); all-gather -> [n_ranks][...]
+ *   pmx_bsel_sweep   hull of the brackets, the sweep, this rank's partial summary and counters and
+ *                    the first digit of its keys inside every bracket
+ *                    -> d_packed [n_seg * (pack_w + n_q * PMX_QUANTILE_BINS / 2)] 64-bit words
+ *                    all-gather d_packed -> [n_ranks][...]
  *   pmx_bsel_hist    summary of all ranks in rank order (d_sum .. d_mean, as pmx_group_combine),
- *                    counters summed, first digit of this rank's keys inside every bracket
- *                    -> d_hist [n_seg * n_q * PMX_QUANTILE_BINS] u32; all-reduce (sum)
- *   pmx_bsel_hist2   place every wanted rank and pick the first digit of its bucket; second digit
- *                    of this rank's keys in those buckets
+ *                    counters and first digits summed, every wanted rank placed, second digit of
+ *                    this rank's keys in the buckets that hold them
  *                    -> d_hist2 [n_seg * n_q * 2 * PMX_QUANTILE_BINS] u32; all-reduce (sum)
  *   pmx_bsel_rows    second digit of every bucket; this rank's keys of the buckets (22 bits)
  *                    -> d_rows [n_seg * n_q * row_w] u64; all-gather -> [n_ranks][...]
@@ -381,11 +381,9 @@ int pmx_bsel_begin(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_
 int pmx_bsel_sweep(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps, const int32_t* d_seg, int64_t n_seg,
                    const int32_t* d_perm, const int64_t* d_goff, int64_t n_q, const double* d_bounds_all, int n_ranks,
                    uint64_t* d_packed, pmx_stream stream);
-int pmx_bsel_hist(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg, int64_t n_q, const uint64_t* d_packed_all,
-                  int n_ranks, double* d_sum, int64_t* d_count, double* d_min, double* d_max, double* d_mean, uint32_t* d_hist,
-                  pmx_stream stream);
-int pmx_bsel_hist2(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg, const double* d_q, int64_t n_q,
-                   const uint32_t* d_hist, const int64_t* d_count, uint32_t* d_hist2, pmx_stream stream);
+int pmx_bsel_hist(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg, const double* d_q, int64_t n_q,
+                  const uint64_t* d_packed_all, int n_ranks, double* d_sum, int64_t* d_count, double* d_min, double* d_max,
+                  double* d_mean, uint32_t* d_hist2, pmx_stream stream);
 int pmx_bsel_rows(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg, int64_t n_q, const uint32_t* d_hist2,
                   uint64_t* d_rows, pmx_stream stream);
 int pmx_bsel_finish(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg, int64_t n_q, const uint64_t* d_rows_all,

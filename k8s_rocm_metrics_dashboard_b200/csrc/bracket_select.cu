@@ -40,17 +40,29 @@ struct BsSeg {                                   // per segment
   unsigned int zero_bound;
   unsigned int sample_m;                         // valid sample values the bounds were taken from
   unsigned int overflow;                         // several ranks: some rank's list overflowed
-  double gmin, gmax;                             // several ranks: smallest / largest value of the segment over all ranks
+  double smin, smax;                             // smallest / largest sample value of this rank
+  double gmin, gmax;                             // several ranks: smallest / largest sample value over all ranks
+  unsigned long long n_valid;                    // values that are not NaN (this rank's rows)
 };
 
-// Several ranks take one digit only, so it has to spread the keys inside the bracket: the digit is
-// taken relative to the bracket clipped to the segment's value range (an open side would otherwise
-// stretch the key range to +-inf and put every key into one bucket).
-__device__ __forceinline__ void bs_digit_geom(const BsSeg& B, int j, uint64_t* kbase, int* Z) {
+// Several ranks take two digits only, so they have to spread the keys inside the bracket: the digits
+// are taken relative to the bracket clipped to the range of the sample values of all ranks (an open
+// side would otherwise stretch the key range to +-inf and put every key into one bucket).  Keys
+// beyond the clipped range (values the samples did not see) fall into the first / last bucket: any
+// monotone map of the keys partitions them correctly.
+struct BsGeom { uint64_t kbase, range; int Z; };
+__device__ __forceinline__ BsGeom bs_digit_geom(const BsSeg& B, int j) {
   const double lo = B.lo[j] > B.gmin ? B.lo[j] : B.gmin, hi = B.hi[j] < B.gmax ? B.hi[j] : B.gmax;
   const uint64_t a = f64_key(lo), b = f64_key(hi);
-  *kbase = a;
-  *Z = b > a ? __clzll((long long)(b - a)) : 0;
+  BsGeom G;
+  G.kbase = a; G.range = b > a ? b - a : 0;
+  G.Z = G.range ? __clzll((long long)G.range) : 0;
+  return G;
+}
+__device__ __forceinline__ uint64_t bs_rel(const BsGeom& G, uint64_t key) {      // 64 bits, the digits from the top
+  uint64_t r = key > G.kbase ? key - G.kbase : 0;
+  r = r > G.range ? G.range : r;
+  return r << G.Z;
 }
 
 __device__ __forceinline__ uint64_t bs_hash(uint64_t h) {
@@ -278,7 +290,8 @@ bs_bounds_kernel(const double* __restrict__ samp, int64_t P, const int32_t* __re
       }
       b.lo[j] = lo; b.hi[j] = hi; b.below[j] = 0; b.eq_lo[j] = 0; b.eq_hi[j] = 0;
     }
-    b.neg_zero = 0; b.list_n = 0; b.zero_bound = zb; b.sample_m = m; b.overflow = 0;
+    b.neg_zero = 0; b.list_n = 0; b.zero_bound = zb; b.sample_m = m; b.overflow = 0; b.n_valid = 0;
+    b.smin = m ? key_f64(kmin) : INF; b.smax = m ? key_f64(kmax) : -INF; b.gmin = -INF; b.gmax = INF;
   }
 }
 
@@ -362,6 +375,7 @@ bs_sweep_kernel(const double* __restrict__ x, int64_t T, const int32_t* __restri
   const Part r = cta_part(mine, sh_part);
   if (threadIdx.x == 0) part[s] = r;
   if (g < 0) return;
+  if (threadIdx.x == 0 && r.cnt) atomicAdd(&segs[g].n_valid, (unsigned long long)r.cnt);
   flush();
   // counters: warp sums, then one 64-bit atomic per counter and CTA
 #pragma unroll
@@ -395,9 +409,11 @@ bs_sweep_kernel(const double* __restrict__ x, int64_t T, const int32_t* __restri
 constexpr int BS_RC = 4;
 __global__ void __cluster_dims__(BS_RC, 1, 1) __launch_bounds__(1024)
 bs_resolve_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __restrict__ lists, unsigned cap,
-                  const int64_t* __restrict__ count, const double* __restrict__ q, int n_q,
+                  const double* __restrict__ q, int n_q,
                   int64_t* o_n, int64_t* o_lo, int64_t* o_hi, double* o_xlo, double* o_xhi, double* o_val,
-                  unsigned int* __restrict__ failed) {
+                  unsigned int* __restrict__ failed, const Part* __restrict__ part, const int32_t* __restrict__ perm,
+                  const int64_t* __restrict__ goff, double* o_sum, int64_t* o_cnt, double* o_min, double* o_max,
+                  double* o_mean) {
   __shared__ unsigned int sh_hist[2][BS_BINS];
   __shared__ unsigned int s_warp[32];
   __shared__ unsigned long long s_keys[2 * BS_SMALL];
@@ -410,8 +426,14 @@ bs_resolve_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __re
   cg::cluster_group cluster = cg::this_cluster();
   const unsigned crank = cluster.block_rank();
   const int j = blockIdx.x / BS_RC, g = blockIdx.y;
+  if (j == n_q) {
+    // the last cluster of every segment folds the per-series partials into the summary (one warp,
+    // the order of pmx_group_reduce) while the others select: it costs no time of its own
+    if (crank == 0 && threadIdx.x < 32) group_fold_warp(part, perm, goff, g, threadIdx.x, o_sum, o_cnt, o_min, o_max, o_mean);
+    return;
+  }
   const int64_t out = (int64_t)g * n_q + j;
-  const long long n = count[g];
+  const long long n = (long long)segs[g].n_valid;
   if (j == 0 && crank == 0 && threadIdx.x == 0 && o_n) o_n[g] = n;
   auto write = [&](long long klo, long long khi, double a, double b, double v) {
     if (o_lo) o_lo[out] = klo;
@@ -591,7 +613,7 @@ bs_resolve_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __re
 // the first digit of the keys inside a bracket is histogrammed and all-reduced; every rank then
 // contributes the few keys of the buckets that hold the wanted ranks, and all ranks settle every
 // quantile alike from the gathered rows.  Four small collectives, one sweep of the data.
-constexpr int BS_BOUNDS_W = 2 * BS_MAX_Q + 1;    // per segment: lo[4], hi[4], sample size
+constexpr int BS_BOUNDS_W = 2 * BS_MAX_Q + 3;    // per segment: lo[4], hi[4], sample size, smallest and largest sample value
 constexpr int BS_PACK_W = 4 + 3 * BS_MAX_Q + 2;  // sum, count, min, max | below, eq_lo, eq_hi | -0.0 count, overflow
 constexpr unsigned BS_ROWK = 1024;               // keys a rank can contribute per (segment, quantile)
 constexpr unsigned BS_ROW_W = 5 + BS_ROWK;       // count, (min, max) of either rank's bucket, keys
@@ -612,6 +634,7 @@ __global__ void bs_export_bounds_kernel(const BsSeg* __restrict__ segs, int64_t 
   if (g >= n_seg) return;
   for (int j = 0; j < BS_MAX_Q; ++j) { out[g * BS_BOUNDS_W + j] = segs[g].lo[j]; out[g * BS_BOUNDS_W + BS_MAX_Q + j] = segs[g].hi[j]; }
   out[g * BS_BOUNDS_W + 2 * BS_MAX_Q] = (double)segs[g].sample_m;
+  out[g * BS_BOUNDS_W + 2 * BS_MAX_Q + 1] = segs[g].smin; out[g * BS_BOUNDS_W + 2 * BS_MAX_Q + 2] = segs[g].smax;
 }
 
 // hull over the ranks that hold sample values of the segment; counters were cleared by bs_bounds_kernel
@@ -632,6 +655,13 @@ __global__ void bs_merge_bounds_kernel(const double* __restrict__ all, int world
     if (lo == 0.0 || hi == 0.0) zb = 1;
   }
   segs[g].zero_bound = zb;
+  double gmin = INF, gmax = -INF;
+  for (int w = 0; w < world; ++w) {
+    const double* b = all + ((size_t)w * n_seg + g) * BS_BOUNDS_W;
+    if (b[2 * BS_MAX_Q] > 0.0) { gmin = b[2 * BS_MAX_Q + 1] < gmin ? b[2 * BS_MAX_Q + 1] : gmin; gmax = b[2 * BS_MAX_Q + 2] > gmax ? b[2 * BS_MAX_Q + 2] : gmax; }
+  }
+  if (!(gmin <= gmax)) { gmin = -INF; gmax = INF; }
+  segs[g].gmin = gmin; segs[g].gmax = gmax;
 }
 
 __global__ void bs_pack_kernel(const BsSeg* __restrict__ segs, const double* __restrict__ sum, const int64_t* __restrict__ cnt,
@@ -654,7 +684,8 @@ __global__ void bs_pack_kernel(const BsSeg* __restrict__ segs, const double* __r
 }
 
 // summary in rank order (as pmx_group_combine), counters summed into segs
-__global__ void bs_combine_kernel(const unsigned long long* __restrict__ all, int world, int64_t n_seg, BsSeg* __restrict__ segs,
+__global__ void bs_combine_kernel(const unsigned long long* __restrict__ all, int world, int64_t n_seg, int64_t n_q,
+                                  BsSeg* __restrict__ segs,
                                   double* o_sum, int64_t* o_cnt, double* o_min, double* o_max, double* o_mean) {
   const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= n_seg) return;
@@ -662,7 +693,8 @@ __global__ void bs_combine_kernel(const unsigned long long* __restrict__ all, in
   unsigned long long cn[3 * BS_MAX_Q + 2];
   for (int i = 0; i < 3 * BS_MAX_Q + 2; ++i) cn[i] = 0;
   for (int w = 0; w < world; ++w) {
-    const unsigned long long* b = all + ((size_t)w * n_seg + g) * BS_PACK_W;
+    const size_t per_rank = (size_t)n_seg * BS_PACK_W + (size_t)n_seg * n_q * BS_BINS / 2;   // packed words, then the first histograms
+    const unsigned long long* b = all + (size_t)w * per_rank + (size_t)g * BS_PACK_W;
     r.sum += __longlong_as_double((long long)b[0]); r.cnt += (long long)b[1];
     r.mn = fmin(r.mn, __longlong_as_double((long long)b[2])); r.mx = fmax(r.mx, __longlong_as_double((long long)b[3]));
     for (int i = 0; i < 3 * BS_MAX_Q + 2; ++i) cn[i] += b[4 + i];
@@ -672,13 +704,25 @@ __global__ void bs_combine_kernel(const unsigned long long* __restrict__ all, in
   }
   segs[g].neg_zero = cn[3 * BS_MAX_Q];
   segs[g].overflow = cn[3 * BS_MAX_Q + 1] ? 1u : 0u;
-  segs[g].gmin = r.mn; segs[g].gmax = r.mx;
   const bool any = r.cnt > 0;
   if (o_sum) o_sum[g] = r.sum;
   if (o_cnt) o_cnt[g] = r.cnt;
   if (o_min) o_min[g] = any ? r.mn : pmx_nan();
   if (o_max) o_max[g] = any ? r.mx : pmx_nan();
   if (o_mean) o_mean[g] = any ? r.sum / (double)r.cnt : pmx_nan();
+}
+
+// first histograms of all ranks (behind the packed words of every rank) -> their sum
+__global__ void bs_sum_hist_kernel(const unsigned long long* __restrict__ all, int world, int64_t n_seg, int n_q,
+                                   unsigned int* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t n = n_seg * n_q * BS_BINS;
+  if (i >= n) return;
+  const size_t per_rank = (size_t)n_seg * BS_PACK_W + (size_t)n / 2;          // 64-bit words
+  unsigned c = 0;
+  for (int w = 0; w < world; ++w)
+    c += reinterpret_cast<const unsigned int*>(all + (size_t)w * per_rank + (size_t)n_seg * BS_PACK_W)[i];
+  out[i] = c;
 }
 
 // A digit of this rank's keys strictly inside bracket j: grid (4 n_q, n_seg).  SECOND = false: the first
@@ -692,8 +736,7 @@ bs_midhist_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __re
   const int j = blockIdx.x >> 2, quarter = blockIdx.x & 3, g = blockIdx.y;
   const BsSeg& B = segs[g];
   const double lo = B.lo[j], hi = B.hi[j];
-  uint64_t klo; int Z;
-  bs_digit_geom(B, j, &klo, &Z);
+  const BsGeom G = bs_digit_geom(B, j);
   const unsigned n_list = B.list_n > cap ? cap : B.list_n;
   const unsigned long long* keys = lists + (size_t)g * cap;
   const unsigned part_n = (n_list + 3) / 4;
@@ -719,7 +762,7 @@ bs_midhist_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __re
       if (i >= k_b) continue;
       const double v = key_f64(kk[u]);
       if (!(v > lo && v < hi)) continue;
-      const uint64_t rel = (kk[u] - klo) << Z;
+      const uint64_t rel = bs_rel(G, kk[u]);
       const unsigned d1 = (unsigned)(rel >> 53);
       if (!SECOND) { atomicAdd(&sh[d1], 1u); continue; }
       const unsigned d2 = (unsigned)(rel >> 42) & (BS_BINS - 1);
@@ -825,8 +868,7 @@ bs_pick2_rows_kernel(const BsSeg* __restrict__ segs, const unsigned long long* _
   }
   const BsSeg& B = segs[g];
   const double lo = B.lo[j], hi = B.hi[j];
-  uint64_t kbase; int Z;
-  bs_digit_geom(B, j, &kbase, &Z);
+  const BsGeom G = bs_digit_geom(B, j);
   const unsigned n_list = B.list_n > cap ? cap : B.list_n;
   const unsigned long long* keys = lists + (size_t)g * cap;
   const unsigned part_n = (n_list + 3) / 4;
@@ -842,7 +884,7 @@ bs_pick2_rows_kernel(const BsSeg* __restrict__ segs, const unsigned long long* _
       if (i >= k_b) continue;
       const double v = key_f64(kk[u]);
       if (!(v > lo && v < hi)) continue;
-      const unsigned d = (unsigned)(((kk[u] - kbase) << Z) >> 42);
+      const unsigned d = (unsigned)(bs_rel(G, kk[u]) >> 42);
       if (d != b0 && d != b1) continue;
       const unsigned long long at = atomicAdd(&row[0], 1ULL);
       if (at < BS_ROWK) row[5 + at] = kk[u];
@@ -881,8 +923,7 @@ bs_final_kernel(const BsSeg* __restrict__ segs, const BsPick* __restrict__ picks
   if (P.zone[0] < 0) { if (threadIdx.x == 0) write(-1, -1, pmx_nan(), pmx_nan(), pmx_nan()); return; }
   bool fail = P.zone[0] == 0 || P.zone[1] == 0;
   const BsSeg& B = segs[g];
-  uint64_t klo; int Z;
-  bs_digit_geom(B, j, &klo, &Z);
+  const BsGeom G = bs_digit_geom(B, j);
   if (threadIdx.x < 2) {
     const int t = threadIdx.x;
     s_ok[t] = 1; s_ans[t] = P.ans[t];
@@ -916,11 +957,11 @@ bs_final_kernel(const BsSeg* __restrict__ segs, const BsPick* __restrict__ picks
       __syncthreads();
       for (unsigned i = threadIdx.x; i < total; i += blockDim.x) {
         const uint64_t ki = s_keys[i];
-        const unsigned d = (unsigned)(((ki - klo) << Z) >> 42);
+        const unsigned d = (unsigned)(bs_rel(G, ki) >> 42);
         unsigned less = 0, eq = 0;
         for (unsigned u = 0; u < total; ++u) {
           const uint64_t ku = s_keys[u];
-          if ((unsigned)(((ku - klo) << Z) >> 42) == d) { less += ku < ki; eq += ku == ki; }
+          if ((unsigned)(bs_rel(G, ku) >> 42) == d) { less += ku < ki; eq += ku == ki; }
         }
         for (int t = 0; t < 2; ++t)
           if (P.zone[t] == 2 && !s_ok[t] && P.bin2[t] == d && P.r2[t] >= less && P.r2[t] < (unsigned long long)less + eq) s_ans[t] = ki;
@@ -943,7 +984,7 @@ bs_final_kernel(const BsSeg* __restrict__ segs, const BsPick* __restrict__ picks
 // scratch of one selection: per-series partials (slot PMX_SCR_PARTIALS); per-segment brackets and
 // counters | local fold outputs | picks | sample | lists (slot PMX_SCR_BRACKET)
 struct BsScratch {
-  Part* part; BsSeg* segs; double* f_sum; int64_t* f_cnt; double* f_min; double* f_max; BsPick* picks;
+  Part* part; BsSeg* segs; double* f_sum; int64_t* f_cnt; double* f_min; double* f_max; BsPick* picks; unsigned int* hist1;
   double* samp; unsigned long long* lists; int64_t cap; int64_t P;
 };
 static int bs_scratch(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg, int64_t n_q, BsScratch* S) {
@@ -960,8 +1001,9 @@ static int bs_scratch(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n
   auto up = [](size_t b) { return (b + 255) & ~size_t(255); };
   const size_t seg_bytes = up((size_t)n_seg * sizeof(BsSeg)), fold_bytes = up((size_t)n_seg * 8);
   const size_t pick_bytes = up((size_t)n_seg * BS_MAX_Q * sizeof(BsPick));
+  const size_t hist_bytes = up((size_t)n_seg * BS_MAX_Q * BS_BINS * sizeof(unsigned int));
   const size_t samp_bytes = up((size_t)(n_series > 0 ? n_series : 1) * (S->P > 0 ? S->P : 1) * 8);
-  unsigned char* scr = (unsigned char*)pmx_scratch(ctx, PMX_SCR_BRACKET, seg_bytes + 4 * fold_bytes + pick_bytes + samp_bytes +
+  unsigned char* scr = (unsigned char*)pmx_scratch(ctx, PMX_SCR_BRACKET, seg_bytes + 4 * fold_bytes + pick_bytes + hist_bytes + samp_bytes +
                                                                          (size_t)n_seg * cap * 8);
   if (!scr) return PMX_E_CUDA;
   S->segs = (BsSeg*)scr; scr += seg_bytes;
@@ -970,6 +1012,7 @@ static int bs_scratch(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n
   S->f_min = (double*)scr; scr += fold_bytes;
   S->f_max = (double*)scr; scr += fold_bytes;
   S->picks = (BsPick*)scr; scr += pick_bytes;
+  S->hist1 = (unsigned int*)scr; scr += hist_bytes;
   S->samp = (double*)scr; scr += samp_bytes;
   S->lists = (unsigned long long*)scr;
   (void)n_q;
@@ -1025,10 +1068,10 @@ extern "C" int pmx_summary_quantiles(pmx_ctx* ctx, const double* d_x, int64_t n_
   if (int rc = bs_launch_bounds(S, d_x, n_series, n_steps, n_seg, d_perm, d_goff, d_q, n_q, st)) return rc;
   if (int rc = bs_launch_sweep(S, d_x, n_series, n_steps, d_seg, n_q, st)) return rc;
   Part* part = S.part; BsSeg* segs = S.segs; unsigned long long* lists = S.lists; const int64_t cap = S.cap;
-  if (int rc = pmx_internal_group_fold(part, d_perm, d_goff, n_seg, d_sum, d_count, d_min, d_max, d_mean, st)) return rc;
-  dim3 grid((unsigned)n_q * BS_RC, (unsigned)n_seg);
-  bs_resolve_kernel<<<grid, 1024, 0, st>>>(segs, lists, (unsigned)cap, d_count, d_q, (int)n_q, d_n, d_lo, d_hi, d_x_lo, d_x_hi,
-                                           d_value, (unsigned int*)d_failed);
+  dim3 grid((unsigned)(n_q + 1) * BS_RC, (unsigned)n_seg);       // n_q selecting clusters + one that folds the summary
+  bs_resolve_kernel<<<grid, 1024, 0, st>>>(segs, lists, (unsigned)cap, d_q, (int)n_q, d_n, d_lo, d_hi, d_x_lo, d_x_hi,
+                                           d_value, (unsigned int*)d_failed, part, d_perm, d_goff, d_sum, d_count, d_min,
+                                           d_max, d_mean);
   PMX_LAUNCH_CHECK();
   return PMX_OK;
 }
@@ -1080,36 +1123,32 @@ int pmx_bsel_sweep(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_
   bs_pack_kernel<<<(unsigned)((n_seg + 127) / 128), 128, 0, st>>>(S.segs, S.f_sum, S.f_cnt, S.f_min, S.f_max, n_seg, (unsigned)S.cap,
                                                                   (unsigned long long*)d_packed);
   PMX_LAUNCH_CHECK();
+  // first digit of this rank's keys inside every bracket, behind the packed words (it needs only the
+  // brackets and the sample range, so it travels with the counters)
+  unsigned int* h1 = (unsigned int*)(d_packed + (size_t)n_seg * BS_PACK_W);
+  PMX_CUDA(cudaMemsetAsync(h1, 0, (size_t)n_seg * n_q * BS_BINS * sizeof(unsigned int), st));
+  dim3 grid((unsigned)n_q * 4, (unsigned)n_seg);
+  bs_midhist_kernel<false><<<grid, 1024, 0, st>>>(S.segs, S.lists, (unsigned)S.cap, (int)n_q, nullptr, h1);
+  PMX_LAUNCH_CHECK();
   return PMX_OK;
 }
 
-int pmx_bsel_hist(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg, int64_t n_q, const uint64_t* d_packed_all,
-                  int n_ranks, double* d_sum, int64_t* d_count, double* d_min, double* d_max, double* d_mean, uint32_t* d_hist,
-                  pmx_stream stream) {
+int pmx_bsel_hist(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg, const double* d_q, int64_t n_q,
+                  const uint64_t* d_packed_all, int n_ranks, double* d_sum, int64_t* d_count, double* d_min, double* d_max,
+                  double* d_mean, uint32_t* d_hist2, pmx_stream stream) {
   BS_COMMON_CHECKS();
-  PMX_REQUIRE(n_ranks >= 1 && d_packed_all && d_count && d_hist, "NULL buffer or bad rank count");
+  PMX_REQUIRE(n_ranks >= 1 && d_q && d_packed_all && d_count && d_hist2, "NULL buffer or bad rank count");
   cudaStream_t st = pmx_st(stream);
   BsScratch S;
   if (int rc = bs_scratch(ctx, n_series, n_steps, n_seg, n_q, &S)) return rc;
-  bs_combine_kernel<<<(unsigned)((n_seg + 127) / 128), 128, 0, st>>>((const unsigned long long*)d_packed_all, n_ranks, n_seg, S.segs,
+  bs_combine_kernel<<<(unsigned)((n_seg + 127) / 128), 128, 0, st>>>((const unsigned long long*)d_packed_all, n_ranks, n_seg, n_q, S.segs,
                                                                      d_sum, d_count, d_min, d_max, d_mean);
   PMX_LAUNCH_CHECK();
-  PMX_CUDA(cudaMemsetAsync(d_hist, 0, (size_t)n_seg * n_q * BS_BINS * sizeof(uint32_t), st));
-  dim3 grid((unsigned)n_q * 4, (unsigned)n_seg);
-  bs_midhist_kernel<false><<<grid, 1024, 0, st>>>(S.segs, S.lists, (unsigned)S.cap, (int)n_q, nullptr, d_hist);
+  const int64_t nh = n_seg * n_q * BS_BINS;
+  bs_sum_hist_kernel<<<(unsigned)((nh + 255) / 256), 256, 0, st>>>((const unsigned long long*)d_packed_all, n_ranks, n_seg, (int)n_q, S.hist1);
   PMX_LAUNCH_CHECK();
-  return PMX_OK;
-}
-
-int pmx_bsel_hist2(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg, const double* d_q, int64_t n_q,
-                   const uint32_t* d_hist, const int64_t* d_count, uint32_t* d_hist2, pmx_stream stream) {
-  BS_COMMON_CHECKS();
-  PMX_REQUIRE(d_q && d_hist && d_count && d_hist2, "NULL buffer");
-  cudaStream_t st = pmx_st(stream);
-  BsScratch S;
-  if (int rc = bs_scratch(ctx, n_series, n_steps, n_seg, n_q, &S)) return rc;
   dim3 grid((unsigned)n_q, (unsigned)n_seg);
-  bs_pick1_kernel<<<grid, 1024, 0, st>>>(S.segs, d_hist, d_count, d_q, (int)n_q, S.picks);
+  bs_pick1_kernel<<<grid, 1024, 0, st>>>(S.segs, S.hist1, d_count, d_q, (int)n_q, S.picks);
   PMX_LAUNCH_CHECK();
   PMX_CUDA(cudaMemsetAsync(d_hist2, 0, (size_t)n_seg * n_q * 2 * BS_BINS * sizeof(uint32_t), st));
   dim3 grid4((unsigned)n_q * 4, (unsigned)n_seg);

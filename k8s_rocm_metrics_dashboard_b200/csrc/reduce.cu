@@ -29,38 +29,14 @@ series_partial_kernel(const double* __restrict__ x, int64_t n_steps, Part* __res
   if (threadIdx.x == 0) part[s] = r;
 }
 
-// one warp per group: lane l folds the partials of the group's series l, l+32, ... in order, then
-// a fixed shuffle tree combines the 32 lanes -- the order never depends on timing.
+// one warp per group (group_fold_warp, reduce_part.cuh)
 __global__ void __launch_bounds__(128)
 group_fold_kernel(const Part* __restrict__ part, const int32_t* __restrict__ perm,
                   const int64_t* __restrict__ goff, int64_t n_groups,
                   double* o_sum, int64_t* o_cnt, double* o_min, double* o_max, double* o_mean) {
   const int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
   if (g >= n_groups) return;
-  Part r = part_identity();
-  // eight partials on their way at a time; they are merged in the order k, k + 32, ... as before
-  const int64_t k1 = goff[g + 1];
-  int64_t k = goff[g] + lane;
-  for (; k + 7 * 32 < k1; k += 8 * 32) {
-    int32_t idx[8]; Part p[8];
-#pragma unroll
-    for (int u = 0; u < 8; ++u) idx[u] = perm[k + 32 * u];
-#pragma unroll
-    for (int u = 0; u < 8; ++u) p[u] = part[idx[u]];
-#pragma unroll
-    for (int u = 0; u < 8; ++u) part_merge(r, p[u]);
-  }
-  for (; k < k1; k += 32) part_merge(r, part[perm[k]]);
-#pragma unroll
-  for (int d = 16; d >= 1; d >>= 1) { Part q = part_shfl_down(r, d); part_merge(r, q); }
-  if (lane != 0) return;
-  const bool any = r.cnt > 0;
-  if (o_sum) o_sum[g] = r.sum;
-  if (o_cnt) o_cnt[g] = r.cnt;
-  if (o_min) o_min[g] = any ? r.mn : pmx_nan();
-  if (o_max) o_max[g] = any ? r.mx : pmx_nan();
-  if (o_mean) o_mean[g] = any ? r.sum / (double)r.cnt : pmx_nan();
+  group_fold_warp(part, perm, goff, g, threadIdx.x & 31, o_sum, o_cnt, o_min, o_max, o_mean);
 }
 
 // per-step form: thread per (group, step), series visited sequentially in group order

@@ -93,6 +93,36 @@ __device__ __forceinline__ Part cta_part(Part p, Part* sh) {
   return r;
 }
 
+// One warp folds the partials of group g: lane l takes the group's series l, l + 32, ... in order
+// (eight on their way at a time), then a fixed shuffle tree combines the 32 lanes -- the order never
+// depends on timing.  Lane 0 writes the outputs that are not NULL.
+__device__ __forceinline__ void group_fold_warp(const Part* __restrict__ part, const int32_t* __restrict__ perm,
+                                                const int64_t* __restrict__ goff, int64_t g, int lane, double* o_sum,
+                                                int64_t* o_cnt, double* o_min, double* o_max, double* o_mean) {
+  Part r = part_identity();
+  const int64_t k1 = goff[g + 1];
+  int64_t k = goff[g] + lane;
+  for (; k + 7 * 32 < k1; k += 8 * 32) {
+    int32_t idx[8]; Part p[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) idx[u] = perm[k + 32 * u];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) p[u] = part[idx[u]];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) part_merge(r, p[u]);
+  }
+  for (; k < k1; k += 32) part_merge(r, part[perm[k]]);
+#pragma unroll
+  for (int d = 16; d >= 1; d >>= 1) { Part q = part_shfl_down(r, d); part_merge(r, q); }
+  if (lane != 0) return;
+  const bool any = r.cnt > 0;
+  if (o_sum) o_sum[g] = r.sum;
+  if (o_cnt) o_cnt[g] = r.cnt;
+  if (o_min) o_min[g] = any ? r.mn : pmx_nan();
+  if (o_max) o_max[g] = any ? r.mx : pmx_nan();
+  if (o_mean) o_mean[g] = any ? r.sum / (double)r.cnt : pmx_nan();
+}
+
 // threads of a CTA that walks one row (series_partial_kernel and bs_sweep_kernel: the same walk)
 constexpr int PMX_ROW_THREADS = 128;
 

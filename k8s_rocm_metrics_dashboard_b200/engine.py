@@ -580,13 +580,14 @@ class Engine:
             self._ptr(sm), self._ptr(cnt), self._ptr(mn), self._ptr(mx), self._ptr(mean), self._ptr(outs["n"]),
             self._ptr(outs["lo"]), self._ptr(outs["hi"]), self._ptr(outs["x_lo"]), self._ptr(outs["x_hi"]),
             self._ptr(outs["value"]), self._ptr(failed), self._stream()))
-        self.launches += 5 if S > 0 and T > 0 else 3        # sample, bounds, sweep, fold, resolve
+        self.launches += 4 if S > 0 and T > 0 else 2        # sample, bounds, sweep, resolve (which also folds the summary)
         return (sm, cnt, mn, mx, mean), outs, failed
 
     def summary_quantiles_ranks(self, x, seg, n_seg, qs, perm_goff, group):
-        """``summary_quantiles`` over ALL ranks of ``group`` (every rank passes its own rows): six library
-        calls with five small collectives between them (brackets, counters + partial summaries, two
-        histograms, the keys of the buckets that hold the wanted ranks), one sweep of ``x`` on every rank.
+        """``summary_quantiles`` over ALL ranks of ``group`` (every rank passes its own rows): five library
+        calls with four small collectives between them (brackets; counters + partial summaries + first
+        histogram; second histogram; the keys of the buckets that hold the wanted ranks), one sweep of
+        ``x`` on every rank.
         Returns ((sum, count, min, max, mean) over all ranks, quantiles dict, failed) -- ``failed`` is the
         same on every rank."""
         import ctypes as C
@@ -607,8 +608,9 @@ class Engine:
             bw, pw, rw = (int(v.value) for v in w)
             cache[key] = {
                 "bounds": self._empty((n_seg * bw,), t.float64), "bounds_all": self._empty((world * n_seg * bw,), t.float64),
-                "packed": self._empty((n_seg * pw,), t.int64), "packed_all": self._empty((world * n_seg * pw,), t.int64),
-                "hist": self._empty((n_seg * n_q * _abi.QUANTILE_BINS,), t.int32),
+                # counters and partial summaries, then the first histograms (u32 pairs)
+                "packed": self._empty((n_seg * (pw + n_q * _abi.QUANTILE_BINS // 2),), t.int64),
+                "packed_all": self._empty((world * n_seg * (pw + n_q * _abi.QUANTILE_BINS // 2),), t.int64),
                 "hist2": self._empty((n_seg * n_q * 2 * _abi.QUANTILE_BINS,), t.int32),
                 "rows": self._empty((n_seg * n_q * rw,), t.int64), "rows_all": self._empty((world * n_seg * n_q * rw,), t.int64)}
         b = cache[key]
@@ -624,17 +626,15 @@ class Engine:
         _abi.check(lib.pmx_bsel_sweep(self.ctx, p(x), S, T, p(d_seg), n_seg, p(d_perm), p(d_goff), n_q, p(b["bounds_all"]), world,
                                       p(b["packed"]), st()))
         dist.all_gather_into_tensor(b["packed_all"], b["packed"], group=group)
-        _abi.check(lib.pmx_bsel_hist(self.ctx, S, T, n_seg, n_q, p(b["packed_all"]), world, p(sm), p(cnt), p(mn), p(mx), p(mean),
-                                     p(b["hist"]), st()))
-        dist.all_reduce(b["hist"], op=dist.ReduceOp.SUM, group=group)
-        _abi.check(lib.pmx_bsel_hist2(self.ctx, S, T, n_seg, p(d_q), n_q, p(b["hist"]), p(cnt), p(b["hist2"]), st()))
+        _abi.check(lib.pmx_bsel_hist(self.ctx, S, T, n_seg, p(d_q), n_q, p(b["packed_all"]), world, p(sm), p(cnt), p(mn), p(mx),
+                                     p(mean), p(b["hist2"]), st()))
         dist.all_reduce(b["hist2"], op=dist.ReduceOp.SUM, group=group)
         _abi.check(lib.pmx_bsel_rows(self.ctx, S, T, n_seg, n_q, p(b["hist2"]), p(b["rows"]), st()))
         dist.all_gather_into_tensor(b["rows_all"], b["rows"], group=group)
         _abi.check(lib.pmx_bsel_finish(self.ctx, S, T, n_seg, n_q, p(b["rows_all"]), world, p(cnt), p(outs["n"]), p(outs["lo"]),
                                        p(outs["hi"]), p(outs["x_lo"]), p(outs["x_hi"]), p(outs["value"]), p(failed), st()))
-        # sample, bounds, export | merge, sweep, fold, pack | combine, histogram | pick, histogram | pick | final
-        self.launches += (14 if S > 0 and T > 0 else 12)
+        # sample, bounds, export | merge, sweep, fold, pack, histogram | combine, sum, pick, histogram | pick | final
+        self.launches += (15 if S > 0 and T > 0 else 13)
         return (sm, cnt, mn, mx, mean), outs, failed
 
     def defer_flag(self, counter):
