@@ -354,6 +354,21 @@ int pmx_summary_quantiles(pmx_ctx* ctx, const double* d_x, int64_t n_series, int
                           const double* d_q, int64_t n_q, double* d_sum, int64_t* d_count, double* d_min,
                           double* d_max, double* d_mean, int64_t* d_n, int64_t* d_lo, int64_t* d_hi,
                           double* d_x_lo, double* d_x_hi, double* d_value, int32_t* d_failed, pmx_stream stream);
+/* pmx_summary_quantiles in two halves, for callers that have the series' raw samples before the
+ * matrix exists (the aggregate step: the fused kernel is still producing the aligned matrix).
+ * pmx_summary_brackets_csr takes the brackets from the raw samples (d_val / d_off: the CSR of
+ * pmx_fused_align_rolling_rate; one sample per 64 grid steps at the same relative position) -- the
+ * brackets are hints that the sweep verifies, so they need not come from the matrix itself; it can
+ * run on another stream beside the fused kernel.  pmx_summary_sweep then does the rest on the
+ * matrix (same arguments and results as pmx_summary_quantiles; same n_series, n_steps, n_seg, d_q,
+ * n_q as the brackets call, which must have completed in stream order). */
+int pmx_summary_brackets_csr(pmx_ctx* ctx, const double* d_val, const int64_t* d_off, int64_t n_series, int64_t n_steps,
+                             int64_t n_seg, const int32_t* d_perm, const int64_t* d_goff, const double* d_q, int64_t n_q,
+                             pmx_stream stream);
+int pmx_summary_sweep(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps, const int32_t* d_seg, int64_t n_seg,
+                      const int32_t* d_perm, const int64_t* d_goff, const double* d_q, int64_t n_q, double* d_sum,
+                      int64_t* d_count, double* d_min, double* d_max, double* d_mean, int64_t* d_n, int64_t* d_lo,
+                      int64_t* d_hi, double* d_x_lo, double* d_x_hi, double* d_value, int32_t* d_failed, pmx_stream stream);
 /* The same for several ranks (one process per GPU, series sharded; no counterpart in the
  * reference, which is one process): five calls with four small collectives between them, one sweep
  * of the data on every rank.  All ranks pass the same n_seg, d_q and n_q, and each its own rows

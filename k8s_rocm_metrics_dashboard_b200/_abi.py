@@ -95,6 +95,8 @@ SIGNATURES = {
     "pmx_bsel_rows": (_int, [_p, _i64, _i64, _i64, _i64, _p, _p, _p]),
     "pmx_bsel_finish": (_int, [_p, _i64, _i64, _i64, _i64, _p, _int, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "pmx_summary_quantiles": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _p, _p, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "pmx_summary_sweep": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _p, _p, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "pmx_summary_brackets_csr": (_int, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p, _i64, _p]),
 }
 
 _lib = None

@@ -82,6 +82,26 @@ bs_sample_kernel(const double* __restrict__ x, int64_t T, int64_t n_series, int6
   samp[idx] = x[row * T + pos];
 }
 
+// The same slots filled from the series' raw samples (CSR) instead of the aligned matrix: slot i of
+// a row takes the sample at the same relative position in the series.  The brackets are only hints
+// that the sweep verifies, and a series' samples have the distribution of its grid points, so the
+// brackets can be ready before the matrix exists (the aggregate step computes them beside the fused kernel).
+__global__ void __launch_bounds__(256)
+bs_sample_csr_kernel(const double* __restrict__ val, const int64_t* __restrict__ off, int64_t T, int64_t n_series, int64_t P,
+                     double* __restrict__ samp) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n_series * P) return;
+  const int64_t row = idx / P, i = idx - row * P;
+  const int64_t a = off[row], len = off[row + 1] - a;
+  if (len <= 0) { samp[idx] = pmx_nan(); return; }
+  const int64_t first = i * BS_STRIDE;
+  const int64_t span = T - first < BS_STRIDE ? T - first : BS_STRIDE;
+  const int64_t step = first + (int64_t)(bs_hash((uint64_t)row * 0x9E3779B97F4A7C15ULL + (uint64_t)i) % (uint64_t)span);
+  int64_t k = (int64_t)((double)step * (double)len / (double)T);
+  k = k < 0 ? 0 : (k > len - 1 ? len - 1 : k);
+  samp[idx] = val[a + k];
+}
+
 // block-wide exclusive scan of BS_BINS counters by 1024 threads, two bins (c0, c1) each; returns
 // this thread's exclusive base.  s_warp: 32 words.
 __device__ __forceinline__ unsigned bs_scan2(unsigned c0, unsigned c1, unsigned* s_warp) {
@@ -144,7 +164,7 @@ bs_bounds_kernel(const double* __restrict__ samp, int64_t P, const int32_t* __re
   {
     unsigned long long mn = ~0ULL, mx = 0;
     const uint64_t a = (uint64_t)rank * per, b = a + per < used ? a + per : used;
-    for (uint64_t u = a + threadIdx.x; u < b; u += blockDim.x) {
+    auto slot_value = [&](uint64_t u) -> double {
       // a hashed slot of every `skip` consecutive ones: a fixed phase would take the same stretches of
       // time from every row, and rows that move together (counters) would leave gaps in the sample
       uint64_t idx = u * skip + (skip > 1 ? bs_hash(u + ((uint64_t)g << 40)) % skip : 0);
@@ -152,13 +172,27 @@ bs_bounds_kernel(const double* __restrict__ samp, int64_t P, const int32_t* __re
       uint64_t r, i;
       if (slots <= 0xffffffffULL) { r = (unsigned)idx / (unsigned)P; i = (unsigned)idx - (unsigned)r * (unsigned)P; }
       else { r = idx / (uint64_t)P; i = idx - r * (uint64_t)P; }
-      const double v = samp[(int64_t)perm[k0 + (int64_t)r] * P + (int64_t)i];
-      if (v != v) continue;
-      const uint64_t key = f64_key(v);
-      sk[atomicAdd(&x_n, 1u)] = key;
-      mn = key < mn ? key : mn; mx = key > mx ? key : mx;
+      return samp[(int64_t)perm[k0 + (int64_t)r] * P + (int64_t)i];
+    };
+    for (uint64_t u0 = a + threadIdx.x; u0 < b; u0 += 4 * (uint64_t)blockDim.x) {          // four loads in flight
+      double v[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { const uint64_t u = u0 + (uint64_t)k * blockDim.x; v[k] = u < b ? slot_value(u) : pmx_nan(); }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (v[k] != v[k]) continue;
+        const uint64_t key = f64_key(v[k]);
+        sk[atomicAdd(&x_n, 1u)] = key;
+        mn = key < mn ? key : mn; mx = key > mx ? key : mx;
+      }
     }
-    if (mn != ~0ULL) { atomicMin(&x_min, mn); atomicMax(&x_max, mx); }
+    // one pair of 64-bit atomics per warp
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) {
+      const unsigned long long a2 = __shfl_xor_sync(0xffffffffu, mn, d), b2 = __shfl_xor_sync(0xffffffffu, mx, d);
+      mn = a2 < mn ? a2 : mn; mx = b2 > mx ? b2 : mx;
+    }
+    if ((threadIdx.x & 31) == 0 && mn != ~0ULL) { atomicMin(&x_min, mn); atomicMax(&x_max, mx); }
   }
   cluster.sync();
   const unsigned n_local = x_n;
@@ -629,6 +663,14 @@ struct BsPick {                                  // per (segment, quantile): whe
   double tt;
 };
 
+// the counters of a sweep (bs_bounds_kernel clears them too; a sweep that reuses brackets starts here)
+__global__ void bs_clear_kernel(BsSeg* __restrict__ segs, int64_t n_seg) {
+  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= n_seg) return;
+  for (int j = 0; j < BS_MAX_Q; ++j) { segs[g].below[j] = 0; segs[g].eq_lo[j] = 0; segs[g].eq_hi[j] = 0; }
+  segs[g].neg_zero = 0; segs[g].list_n = 0; segs[g].n_valid = 0; segs[g].overflow = 0;
+}
+
 __global__ void bs_export_bounds_kernel(const BsSeg* __restrict__ segs, int64_t n_seg, double* __restrict__ out) {
   const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= n_seg) return;
@@ -1020,11 +1062,15 @@ static int bs_scratch(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n
 }
 // sample + brackets of this rank's rows
 static int bs_launch_bounds(const BsScratch& S, const double* d_x, int64_t n_series, int64_t n_steps, int64_t n_seg,
-                            const int32_t* d_perm, const int64_t* d_goff, const double* d_q, int64_t n_q, cudaStream_t st) {
+                            const int32_t* d_perm, const int64_t* d_goff, const double* d_q, int64_t n_q, cudaStream_t st,
+                            const int64_t* d_csr_off = nullptr) {
   const bool data = n_series > 0 && n_steps > 0;
   if (data) {
     const int64_t slots = n_series * S.P;
-    bs_sample_kernel<<<(unsigned)((slots + 255) / 256), 256, 0, st>>>(d_x, n_steps, n_series, S.P, S.samp);
+    if (d_csr_off)          // d_x holds the series' samples back to back
+      bs_sample_csr_kernel<<<(unsigned)((slots + 255) / 256), 256, 0, st>>>(d_x, d_csr_off, n_steps, n_series, S.P, S.samp);
+    else
+      bs_sample_kernel<<<(unsigned)((slots + 255) / 256), 256, 0, st>>>(d_x, n_steps, n_series, S.P, S.samp);
     PMX_LAUNCH_CHECK();
   }
   const size_t smem = (size_t)BS_KCAP * 8 + (size_t)2 * n_q * BS_BINS * sizeof(unsigned int);
@@ -1048,12 +1094,12 @@ static int bs_launch_sweep(const BsScratch& S, const double* d_x, int64_t n_seri
   return PMX_OK;
 }
 
-extern "C" int pmx_summary_quantiles(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
-                                     const int32_t* d_seg, int64_t n_seg, const int32_t* d_perm, const int64_t* d_goff,
-                                     const double* d_q, int64_t n_q, double* d_sum, int64_t* d_count, double* d_min,
-                                     double* d_max, double* d_mean, int64_t* d_n, int64_t* d_lo, int64_t* d_hi,
-                                     double* d_x_lo, double* d_x_hi, double* d_value, int32_t* d_failed,
-                                     pmx_stream stream) {
+static int bs_summary(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
+                      const int32_t* d_seg, int64_t n_seg, const int32_t* d_perm, const int64_t* d_goff,
+                      const double* d_q, int64_t n_q, double* d_sum, int64_t* d_count, double* d_min,
+                      double* d_max, double* d_mean, int64_t* d_n, int64_t* d_lo, int64_t* d_hi,
+                      double* d_x_lo, double* d_x_hi, double* d_value, int32_t* d_failed,
+                      pmx_stream stream, bool brackets_ready) {
   PMX_REQUIRE(ctx, "ctx is NULL");
   PMX_REQUIRE(n_series >= 0 && n_steps >= 0 && n_seg >= 0 && n_seg <= 65535, "bad sizes (n_seg <= 65535)");
   if (n_q < 1 || n_q > BS_MAX_Q) return pmx_fail(PMX_E_LIMIT, "pmx_summary_quantiles: n_q must be in [1, %d]; use pmx_quantile_select", BS_MAX_Q);
@@ -1065,7 +1111,12 @@ extern "C" int pmx_summary_quantiles(pmx_ctx* ctx, const double* d_x, int64_t n_
   PMX_REQUIRE(n_series == 0 || (d_x && d_seg && d_perm), "NULL buffer");
   BsScratch S;
   if (int rc = bs_scratch(ctx, n_series, n_steps, n_seg, n_q, &S)) return rc;
-  if (int rc = bs_launch_bounds(S, d_x, n_series, n_steps, n_seg, d_perm, d_goff, d_q, n_q, st)) return rc;
+  if (!brackets_ready) {
+    if (int rc = bs_launch_bounds(S, d_x, n_series, n_steps, n_seg, d_perm, d_goff, d_q, n_q, st)) return rc;
+  } else {
+    bs_clear_kernel<<<(unsigned)((n_seg + 127) / 128), 128, 0, st>>>(S.segs, n_seg);
+    PMX_LAUNCH_CHECK();
+  }
   if (int rc = bs_launch_sweep(S, d_x, n_series, n_steps, d_seg, n_q, st)) return rc;
   Part* part = S.part; BsSeg* segs = S.segs; unsigned long long* lists = S.lists; const int64_t cap = S.cap;
   dim3 grid((unsigned)(n_q + 1) * BS_RC, (unsigned)n_seg);       // n_q selecting clusters + one that folds the summary
@@ -1186,6 +1237,37 @@ int pmx_bsel_finish(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_s
                                         d_n, d_lo, d_hi, d_x_lo, d_x_hi, d_value, (unsigned int*)d_failed);
   PMX_LAUNCH_CHECK();
   return PMX_OK;
+}
+
+}  // extern "C"
+
+extern "C" {
+
+int pmx_summary_quantiles(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps, const int32_t* d_seg, int64_t n_seg,
+                          const int32_t* d_perm, const int64_t* d_goff, const double* d_q, int64_t n_q, double* d_sum,
+                          int64_t* d_count, double* d_min, double* d_max, double* d_mean, int64_t* d_n, int64_t* d_lo,
+                          int64_t* d_hi, double* d_x_lo, double* d_x_hi, double* d_value, int32_t* d_failed, pmx_stream stream) {
+  return bs_summary(ctx, d_x, n_series, n_steps, d_seg, n_seg, d_perm, d_goff, d_q, n_q, d_sum, d_count, d_min, d_max, d_mean, d_n,
+                    d_lo, d_hi, d_x_lo, d_x_hi, d_value, d_failed, stream, false);
+}
+
+int pmx_summary_brackets_csr(pmx_ctx* ctx, const double* d_val, const int64_t* d_off, int64_t n_series, int64_t n_steps,
+                             int64_t n_seg, const int32_t* d_perm, const int64_t* d_goff, const double* d_q, int64_t n_q,
+                             pmx_stream stream) {
+  BS_COMMON_CHECKS();
+  PMX_REQUIRE(n_series >= 0 && n_steps >= 0, "bad sizes");
+  PMX_REQUIRE(d_goff && d_q && (n_series == 0 || (d_val && d_off && d_perm)), "NULL buffer");
+  BsScratch S;
+  if (int rc = bs_scratch(ctx, n_series, n_steps, n_seg, n_q, &S)) return rc;
+  return bs_launch_bounds(S, d_val, n_series, n_steps, n_seg, d_perm, d_goff, d_q, n_q, pmx_st(stream), d_off);
+}
+
+int pmx_summary_sweep(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps, const int32_t* d_seg, int64_t n_seg,
+                      const int32_t* d_perm, const int64_t* d_goff, const double* d_q, int64_t n_q, double* d_sum,
+                      int64_t* d_count, double* d_min, double* d_max, double* d_mean, int64_t* d_n, int64_t* d_lo,
+                      int64_t* d_hi, double* d_x_lo, double* d_x_hi, double* d_value, int32_t* d_failed, pmx_stream stream) {
+  return bs_summary(ctx, d_x, n_series, n_steps, d_seg, n_seg, d_perm, d_goff, d_q, n_q, d_sum, d_count, d_min, d_max, d_mean, d_n,
+                    d_lo, d_hi, d_x_lo, d_x_hi, d_value, d_failed, stream, true);
 }
 
 }  // extern "C"

@@ -556,7 +556,21 @@ class Engine:
         return out
 
     # ------------------------------------------------------------------ K6
-    def summary_quantiles(self, x, seg, n_seg, qs, perm_goff):
+    def summary_brackets_csr(self, val, off, n_steps, n_seg, qs, perm_goff):
+        """First half of ``summary_quantiles`` from the series' raw samples (CSR ``val`` / ``off``): sample and
+        brackets, on the current stream -- e.g. a side stream beside the fused kernel.  Follow with
+        ``summary_quantiles(x, ..., brackets_ready=True)`` on the aligned matrix of the same series, steps,
+        segments and levels, ordered behind this call."""
+        t = self.torch
+        val, off = self._dev(val, t.float64), self._dev(off, t.int64)
+        d_perm, d_goff = self._dev(perm_goff[0], t.int32), self._dev(perm_goff[1], t.int64)
+        S = off.numel() - 1
+        _abi.check(self.lib.pmx_summary_brackets_csr(self.ctx, self._ptr(val), self._ptr(off), S, n_steps, n_seg, self._ptr(d_perm),
+                                                     self._ptr(d_goff), self._ptr(self._quantile_levels(qs)), len(qs),
+                                                     self._stream()))
+        self.launches += 2 if S > 0 and n_steps > 0 else 1
+
+    def summary_quantiles(self, x, seg, n_seg, qs, perm_goff, brackets_ready=False):
         """One GPU: ``group_reduce(x, ..., perm_goff)`` and ``quantiles(x, seg, n_seg, qs)`` from ONE sweep
         of ``x`` (pmx_summary_quantiles: sampled brackets, counted and verified on the device).  Returns
         ((sum, count, min, max, mean), quantiles dict, failed) -- ``failed`` is an int32 device tensor [1]:
@@ -575,12 +589,14 @@ class Engine:
                 "hi": self._empty((n_seg, n_q), t.int64), "x_lo": self._empty((n_seg, n_q), t.float64),
                 "x_hi": self._empty((n_seg, n_q), t.float64), "value": self._empty((n_seg, n_q), t.float64)}
         failed = self._empty((1,), t.int32)
-        _abi.check(self.lib.pmx_summary_quantiles(
+        fn = self.lib.pmx_summary_sweep if brackets_ready else self.lib.pmx_summary_quantiles
+        _abi.check(fn(
             self.ctx, self._ptr(x), S, T, self._ptr(d_seg), n_seg, self._ptr(d_perm), self._ptr(d_goff), self._ptr(d_q), n_q,
             self._ptr(sm), self._ptr(cnt), self._ptr(mn), self._ptr(mx), self._ptr(mean), self._ptr(outs["n"]),
             self._ptr(outs["lo"]), self._ptr(outs["hi"]), self._ptr(outs["x_lo"]), self._ptr(outs["x_hi"]),
             self._ptr(outs["value"]), self._ptr(failed), self._stream()))
-        self.launches += 4 if S > 0 and T > 0 else 2        # sample, bounds, sweep, resolve (which also folds the summary)
+        # sample, bounds, sweep, resolve (which also folds the summary)
+        self.launches += (4 if S > 0 and T > 0 else 2) - (0 if not brackets_ready else (1 if S > 0 and T > 0 else 0))   # (a clear instead)
         return (sm, cnt, mn, mx, mean), outs, failed
 
     def summary_quantiles_ranks(self, x, seg, n_seg, qs, perm_goff, group):

@@ -115,16 +115,18 @@ class ShardedEngine:
         """(count, min, max) of the combined group summary: where the quantile selection starts."""
         return summary[1], summary[2], summary[3]
 
-    def summarize(self, x, seg, n_seg, perm_goff, qs=(0.5, 0.95, 0.99), defer_check=False, _unchecked=False):
+    def summarize(self, x, seg, n_seg, perm_goff, qs=(0.5, 0.95, 0.99), defer_check=False, _unchecked=False,
+                  brackets_ready=False):
         """Per-segment sum / count / min / max / mean and exact quantiles of the [S, T] device matrix ``x`` over
         ALL ranks (every rank calls this with its own rows; S may be 0).  Returns (summary, quantiles).
         One rank and at most four levels: one sweep of ``x`` (``Engine.summary_quantiles``); its brackets
         are verified on the device, and the per-pass selection runs if the check fails (with
-        ``defer_check`` the check is left to ``Engine.deferred_ok``, see ``Engine.quantiles``)."""
+        ``defer_check`` the check is left to ``Engine.deferred_ok``, see ``Engine.quantiles``).
+        ``brackets_ready`` (one rank): ``Engine.summary_brackets_csr`` already ran for these series."""
         eng = self.eng
         if 1 <= len(qs) <= 4:
             if self.world == 1:
-                summary, q, failed = eng.summary_quantiles(x, seg, n_seg, qs, perm_goff)
+                summary, q, failed = eng.summary_quantiles(x, seg, n_seg, qs, perm_goff, brackets_ready=brackets_ready)
             else:                                       # ``failed`` is the same on every rank: they fall back together
                 summary, q, failed = eng.summary_quantiles_ranks(x, seg, n_seg, qs, perm_goff, self.group or _world_group())
             if _unchecked:
@@ -148,7 +150,7 @@ class ShardedEngine:
                               summary=self._qsummary(summary))
         return (summary, q, None) if _unchecked else (summary, q)
 
-    def summarize_graph(self, x, seg, n_seg, perm_goff, qs=(0.5, 0.95, 0.99), defer_check=False):
+    def summarize_graph(self, x, seg, n_seg, perm_goff, qs=(0.5, 0.95, 0.99), defer_check=False, brackets_ready=False):
         """``summarize`` replayed from a CUDA graph (one rank): the small launches behind the fused kernel
         are launch-bound, so they are captured once per (buffer, shape) and replayed.  ``x``, ``seg`` and
         ``perm_goff`` must be the same device tensors on every call (the graph reads them in
@@ -156,18 +158,19 @@ class ShardedEngine:
         Falls back to the eager path when capture is not possible, and to the eager per-pass selection
         when the replayed sweep reports a failed bracket."""
         t = self.eng.torch
-        key = (x.data_ptr(), tuple(x.shape), seg.data_ptr(), n_seg, perm_goff[0].data_ptr(), perm_goff[1].data_ptr(), tuple(qs))
+        key = (x.data_ptr(), tuple(x.shape), seg.data_ptr(), n_seg, perm_goff[0].data_ptr(), perm_goff[1].data_ptr(), tuple(qs),
+               brackets_ready)
         hit = self._graphs.get(key)
         if hit is None:
             for _ in range(2):                                  # scratch grows and kernels load outside the capture
                 before = self.eng.launches
-                self.summarize(x, seg, n_seg, perm_goff, qs, _unchecked=True)
+                self.summarize(x, seg, n_seg, perm_goff, qs, _unchecked=True, brackets_ready=brackets_ready)
             n_launches = self.eng.launches - before             # kernels of ours inside one replay
             t.cuda.synchronize()
             try:
                 g = t.cuda.CUDAGraph()
                 with t.cuda.graph(g, capture_error_mode="thread_local"):
-                    res = self.summarize(x, seg, n_seg, perm_goff, qs, _unchecked=True)
+                    res = self.summarize(x, seg, n_seg, perm_goff, qs, _unchecked=True, brackets_ready=brackets_ready)
                 self.eng.launches -= n_launches                 # the capture launched nothing
                 hit = (g, res, (x, seg, perm_goff), n_launches)  # the inputs stay alive with the graph
             except Exception:  # noqa: BLE001  -- capture refused: stay eager
@@ -175,7 +178,7 @@ class ShardedEngine:
                 hit = (None, None, None, 0)
             self._graphs[key] = hit
         if hit[0] is None:
-            return self.summarize(x, seg, n_seg, perm_goff, qs, defer_check=defer_check)
+            return self.summarize(x, seg, n_seg, perm_goff, qs, defer_check=defer_check, brackets_ready=brackets_ready)
         hit[0].replay()
         self.eng.launches += hit[3]
         summary, q, failed = hit[1]
@@ -202,13 +205,29 @@ class ShardedEngine:
             out = eng.fused_from_host(ts, val, off, start_ms, step_ms, n_steps, window_steps, host["dev"],
                                       host["out"], lookback_ms)
         else:
+            # one rank: the brackets of the quantile selection come from the raw samples on a side
+            # stream while the fused kernel runs (they are hints; the sweep verifies them)
+            pre = (self.world == 1 and 1 <= len(qs) <= 4 and getattr(val, "is_cuda", False) and getattr(off, "is_cuda", False)
+                   and off.numel() > 1 and n_steps > 0)
+            if pre:
+                t = eng.torch
+                cur = t.cuda.current_stream()
+                if self.__dict__.get("_side") is None:
+                    self._side = t.cuda.Stream()
+                self._side.wait_stream(cur)
+                with t.cuda.stream(self._side):
+                    eng.summary_brackets_csr(val, off, n_steps, n_seg, qs, perm_goff)
+                ready = self._side.record_event()
             out = eng.fused(ts, val, off, start_ms, step_ms, n_steps, window_steps, lookback_ms, out=out)
+            if pre:
+                cur.wait_event(ready)
         # (one rank only: with NCCL collectives inside the capture the step gained 2 % on two GPUs and the
         # processes no longer shut down cleanly)
+        pre = host is None and pre
         if graph and self.world == 1 and host is None:
-            summary, q = self.summarize_graph(out["aligned"], seg, n_seg, perm_goff, qs, defer_check=defer_check)
+            summary, q = self.summarize_graph(out["aligned"], seg, n_seg, perm_goff, qs, defer_check=defer_check, brackets_ready=pre)
         else:
-            summary, q = self.summarize(out["aligned"], seg, n_seg, perm_goff, qs, defer_check)
+            summary, q = self.summarize(out["aligned"], seg, n_seg, perm_goff, qs, defer_check, brackets_ready=pre)
         return out, summary, q
 
 

@@ -183,3 +183,33 @@ def test_thinned_sample_of_rows_that_move_together(eng):
         ref_s = eng.group_reduce(x, None, M, perm_goff=pg)
         ref_q = eng.quantiles(x, seg, M, list(qs), row_order=pg[0], summary=(ref_s[1], ref_s[2], ref_s[3]))
         _same(summ, q, ref_s, ref_q, f"thinned {qs}")
+
+
+def test_brackets_from_the_raw_samples(eng):
+    """pmx_summary_brackets_csr + pmx_summary_sweep: brackets taken from the series' raw samples (ragged CSR,
+    gaps, NaN) instead of the aligned matrix give the same exact results -- they are only hints."""
+    from k8s_rocm_metrics_dashboard_b200 import synth
+    t = eng.torch
+    d = synth.dense(2, 8, 6, 3000, seed=31, nan_frac=0.01)
+    S, T, M = len(d["off"]) - 1, 3000, 6
+    # thin the series unevenly: the raw samples are no longer one per grid step
+    keep = np.ones(len(d["ts"]), dtype=bool)
+    rng = np.random.default_rng(5)
+    keep[rng.random(len(keep)) < 0.15] = False
+    lens = np.array([keep[int(d["off"][s]):int(d["off"][s + 1])].sum() for s in range(S)])
+    ts, val, off = d["ts"][keep], d["val"][keep], np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    al, _ = eng.align(ts, val, off, d["start_ms"], d["step_ms"], T, want_idx=False)
+    gid = (np.arange(S) % M).astype(np.int32)
+    perm, goff = group_index(gid, M)
+    pg = (t.as_tensor(perm, device=eng.device), t.as_tensor(goff, device=eng.device))
+    seg = t.as_tensor(gid, device=eng.device)
+    eng.summary_brackets_csr(t.as_tensor(val, device=eng.device), t.as_tensor(off, device=eng.device), T, M, QS, pg)
+    summ, q, failed = eng.summary_quantiles(al, seg, M, QS, pg, brackets_ready=True)
+    assert int(failed.item()) == 0
+    s1, q1, f1 = eng.summary_quantiles(al, seg, M, QS, pg)
+    assert int(f1.item()) == 0
+    _same(summ, q, s1, q1, "brackets from raw samples")
+    x = al.cpu().numpy()
+    for g in range(M):
+        o = O.quantiles(x[gid == g], QS)
+        assert_bits_equal(q["value"][g].cpu().numpy(), np.array(o["value"]), "oracle")
