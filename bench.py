@@ -409,6 +409,15 @@ def run_engine(args):
     launches = eng.launches - l0
     ms = ev0.elapsed_time(ev1)
     fused_ms = sum(a.elapsed_time(b) for a, b in fe) / len(fe)
+    # the same kernel with the GPU to itself (inside the step, on one rank, the bracket kernels of the
+    # summary run beside it on a side stream): reported next to the in-step figure, not instead of it
+    fa = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(20)]
+    for e0, e1 in fa:
+        e0.record()
+        eng.fused(ts, val, off, START_MS, STEP_MS, T, WINDOW_STEPS, LOOKBACK_MS, out=out)
+        e1.record()
+    torch.cuda.synchronize()
+    fused_alone_ms = sum(a.elapsed_time(b) for a, b in fa[2:]) / len(fa[2:])
     tt = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -505,7 +514,12 @@ def run_engine(args):
                 "roofline": {"bound": "hbm", "kernel": "window_fast_kernel<128,true> (fused align+rolling+rate)",
                              "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": traffic, "peak_source": which, "avg_launch_ms": fused_ms,
-                             "algorithmic_bytes_per_launch": n_samples * FUSED_BYTES_PER_SAMPLE},
+                             "algorithmic_bytes_per_launch": n_samples * FUSED_BYTES_PER_SAMPLE,
+                             "alone": {"avg_launch_ms": fused_alone_ms,
+                                       "achieved": n_samples * FUSED_BYTES_PER_SAMPLE / (fused_alone_ms * 1e-3) / 1e9,
+                                       "frac": n_samples * FUSED_BYTES_PER_SAMPLE / (fused_alone_ms * 1e-3) / 1e9 / peak,
+                                       "note": "same launches outside the timed region, nothing else on the GPU; inside the step "
+                                               "(one rank) the bracket kernels of the summary share the GPU with it"}},
                 "cpu_baseline": cpu, "cpu_baseline_other": cpu_other,
                 "e2e": {"value": world * n_samples * e2e_steps / e2e_s, "unit": "samples/s",
                         "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps},

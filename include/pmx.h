@@ -393,6 +393,10 @@ int pmx_bsel_widths(int* bounds_w, int* pack_w, int* row_w);
 int pmx_bsel_begin(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps, const int32_t* d_seg, int64_t n_seg,
                    const int32_t* d_perm, const int64_t* d_goff, const double* d_q, int64_t n_q, double* d_bounds,
                    pmx_stream stream);
+/* pmx_bsel_begin from the series' raw samples (as pmx_summary_brackets_csr): may run beside the fused kernel */
+int pmx_bsel_begin_csr(pmx_ctx* ctx, const double* d_val, const int64_t* d_off, int64_t n_series, int64_t n_steps, int64_t n_seg,
+                       const int32_t* d_perm, const int64_t* d_goff, const double* d_q, int64_t n_q, double* d_bounds,
+                       pmx_stream stream);
 int pmx_bsel_sweep(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps, const int32_t* d_seg, int64_t n_seg,
                    const int32_t* d_perm, const int64_t* d_goff, int64_t n_q, const double* d_bounds_all, int n_ranks,
                    uint64_t* d_packed, pmx_stream stream);

@@ -90,6 +90,7 @@ SIGNATURES = {
     "pmx_quantile_select": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _p]),
     "pmx_bsel_widths": (_int, [_p, _p, _p]),
     "pmx_bsel_begin": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _p, _p, _i64, _p, _p]),
+    "pmx_bsel_begin_csr": (_int, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p, _i64, _p, _p]),
     "pmx_bsel_sweep": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _p, _i64, _p, _int, _p, _p]),
     "pmx_bsel_hist": (_int, [_p, _i64, _i64, _i64, _p, _i64, _p, _int, _p, _p, _p, _p, _p, _p, _p]),
     "pmx_bsel_rows": (_int, [_p, _i64, _i64, _i64, _i64, _p, _p, _p]),

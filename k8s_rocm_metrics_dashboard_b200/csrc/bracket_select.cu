@@ -1159,6 +1159,21 @@ int pmx_bsel_begin(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_
   return PMX_OK;
 }
 
+int pmx_bsel_begin_csr(pmx_ctx* ctx, const double* d_val, const int64_t* d_off, int64_t n_series, int64_t n_steps, int64_t n_seg,
+                       const int32_t* d_perm, const int64_t* d_goff, const double* d_q, int64_t n_q, double* d_bounds,
+                       pmx_stream stream) {
+  BS_COMMON_CHECKS();
+  PMX_REQUIRE(n_series >= 0 && n_steps >= 0, "bad sizes");
+  PMX_REQUIRE(d_goff && d_q && d_bounds && (n_series == 0 || (d_val && d_off && d_perm)), "NULL buffer");
+  cudaStream_t st = pmx_st(stream);
+  BsScratch S;
+  if (int rc = bs_scratch(ctx, n_series, n_steps, n_seg, n_q, &S)) return rc;
+  if (int rc = bs_launch_bounds(S, d_val, n_series, n_steps, n_seg, d_perm, d_goff, d_q, n_q, st, d_off)) return rc;
+  bs_export_bounds_kernel<<<(unsigned)((n_seg + 127) / 128), 128, 0, st>>>(S.segs, n_seg, d_bounds);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
 int pmx_bsel_sweep(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps, const int32_t* d_seg, int64_t n_seg,
                    const int32_t* d_perm, const int64_t* d_goff, int64_t n_q, const double* d_bounds_all, int n_ranks,
                    uint64_t* d_packed, pmx_stream stream) {

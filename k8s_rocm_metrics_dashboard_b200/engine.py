@@ -599,7 +599,39 @@ class Engine:
         self.launches += (4 if S > 0 and T > 0 else 2) - (0 if not brackets_ready else (1 if S > 0 and T > 0 else 0))   # (a clear instead)
         return (sm, cnt, mn, mx, mean), outs, failed
 
-    def summary_quantiles_ranks(self, x, seg, n_seg, qs, perm_goff, group):
+    def _bsel_buffers(self, n_seg, n_q, world):
+        import ctypes as C
+        t = self.torch
+        key = (n_seg, n_q, world)
+        cache = self.__dict__.setdefault("_bsel", {})
+        if key not in cache:
+            w = [C.c_int(0) for _ in range(3)]
+            _abi.check(self.lib.pmx_bsel_widths(C.byref(w[0]), C.byref(w[1]), C.byref(w[2])))
+            bw, pw, rw = (int(v.value) for v in w)
+            cache[key] = {
+                "bounds": self._empty((n_seg * bw,), t.float64), "bounds_all": self._empty((world * n_seg * bw,), t.float64),
+                # counters and partial summaries, then the first histograms (u32 pairs)
+                "packed": self._empty((n_seg * (pw + n_q * _abi.QUANTILE_BINS // 2),), t.int64),
+                "packed_all": self._empty((world * n_seg * (pw + n_q * _abi.QUANTILE_BINS // 2),), t.int64),
+                "hist2": self._empty((n_seg * n_q * 2 * _abi.QUANTILE_BINS,), t.int32),
+                "rows": self._empty((n_seg * n_q * rw,), t.int64), "rows_all": self._empty((world * n_seg * n_q * rw,), t.int64)}
+        return cache[key]
+
+    def summary_begin_csr_ranks(self, val, off, n_steps, n_seg, qs, perm_goff, group):
+        """First call of ``summary_quantiles_ranks`` from the series' raw samples, on the current stream (a side
+        stream beside the fused kernel); pass ``begun=True`` to ``summary_quantiles_ranks`` afterwards."""
+        import torch.distributed as dist
+        t = self.torch
+        val, off = self._dev(val, t.float64), self._dev(off, t.int64)
+        d_perm, d_goff = self._dev(perm_goff[0], t.int32), self._dev(perm_goff[1], t.int64)
+        S = off.numel() - 1
+        b = self._bsel_buffers(n_seg, len(qs), dist.get_world_size(group))
+        _abi.check(self.lib.pmx_bsel_begin_csr(self.ctx, self._ptr(val), self._ptr(off), S, n_steps, n_seg, self._ptr(d_perm),
+                                               self._ptr(d_goff), self._ptr(self._quantile_levels(qs)), len(qs),
+                                               self._ptr(b["bounds"]), self._stream()))
+        self.launches += 3 if S > 0 and n_steps > 0 else 2
+
+    def summary_quantiles_ranks(self, x, seg, n_seg, qs, perm_goff, group, begun=False):
         """``summary_quantiles`` over ALL ranks of ``group`` (every rank passes its own rows): five library
         calls with four small collectives between them (brackets; counters + partial summaries + first
         histogram; second histogram; the keys of the buckets that hold the wanted ranks), one sweep of
@@ -616,20 +648,7 @@ class Engine:
         n_q = len(qs)
         d_q = self._quantile_levels(qs)
         world = dist.get_world_size(group)
-        key = (n_seg, n_q, world)
-        cache = self.__dict__.setdefault("_bsel", {})
-        if key not in cache:
-            w = [C.c_int(0) for _ in range(3)]
-            _abi.check(self.lib.pmx_bsel_widths(C.byref(w[0]), C.byref(w[1]), C.byref(w[2])))
-            bw, pw, rw = (int(v.value) for v in w)
-            cache[key] = {
-                "bounds": self._empty((n_seg * bw,), t.float64), "bounds_all": self._empty((world * n_seg * bw,), t.float64),
-                # counters and partial summaries, then the first histograms (u32 pairs)
-                "packed": self._empty((n_seg * (pw + n_q * _abi.QUANTILE_BINS // 2),), t.int64),
-                "packed_all": self._empty((world * n_seg * (pw + n_q * _abi.QUANTILE_BINS // 2),), t.int64),
-                "hist2": self._empty((n_seg * n_q * 2 * _abi.QUANTILE_BINS,), t.int32),
-                "rows": self._empty((n_seg * n_q * rw,), t.int64), "rows_all": self._empty((world * n_seg * n_q * rw,), t.int64)}
-        b = cache[key]
+        b = self._bsel_buffers(n_seg, n_q, world)
         sm, mn, mx, mean = (self._empty((n_seg,), t.float64) for _ in range(4))
         cnt = self._empty((n_seg,), t.int64)
         outs = {"n": self._empty((n_seg,), t.int64), "lo": self._empty((n_seg, n_q), t.int64),
@@ -637,7 +656,8 @@ class Engine:
                 "x_hi": self._empty((n_seg, n_q), t.float64), "value": self._empty((n_seg, n_q), t.float64)}
         failed = self._empty((1,), t.int32)
         lib, p, st = self.lib, self._ptr, self._stream
-        _abi.check(lib.pmx_bsel_begin(self.ctx, p(x), S, T, p(d_seg), n_seg, p(d_perm), p(d_goff), p(d_q), n_q, p(b["bounds"]), st()))
+        if not begun:
+            _abi.check(lib.pmx_bsel_begin(self.ctx, p(x), S, T, p(d_seg), n_seg, p(d_perm), p(d_goff), p(d_q), n_q, p(b["bounds"]), st()))
         dist.all_gather_into_tensor(b["bounds_all"], b["bounds"], group=group)
         _abi.check(lib.pmx_bsel_sweep(self.ctx, p(x), S, T, p(d_seg), n_seg, p(d_perm), p(d_goff), n_q, p(b["bounds_all"]), world,
                                       p(b["packed"]), st()))
@@ -650,7 +670,7 @@ class Engine:
         _abi.check(lib.pmx_bsel_finish(self.ctx, S, T, n_seg, n_q, p(b["rows_all"]), world, p(cnt), p(outs["n"]), p(outs["lo"]),
                                        p(outs["hi"]), p(outs["x_lo"]), p(outs["x_hi"]), p(outs["value"]), p(failed), st()))
         # sample, bounds, export | merge, sweep, fold, pack, histogram | combine, sum, pick, histogram | pick | final
-        self.launches += (15 if S > 0 and T > 0 else 13)
+        self.launches += (15 if S > 0 and T > 0 else 13) - (0 if not begun else (3 if S > 0 and T > 0 else 2))
         return (sm, cnt, mn, mx, mean), outs, failed
 
     def defer_flag(self, counter):

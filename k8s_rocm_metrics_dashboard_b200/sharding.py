@@ -122,13 +122,15 @@ class ShardedEngine:
         One rank and at most four levels: one sweep of ``x`` (``Engine.summary_quantiles``); its brackets
         are verified on the device, and the per-pass selection runs if the check fails (with
         ``defer_check`` the check is left to ``Engine.deferred_ok``, see ``Engine.quantiles``).
-        ``brackets_ready`` (one rank): ``Engine.summary_brackets_csr`` already ran for these series."""
+        ``brackets_ready``: ``Engine.summary_brackets_csr`` (one rank) or ``summary_begin_csr_ranks`` (several; then
+        on EVERY rank) already ran for these series."""
         eng = self.eng
         if 1 <= len(qs) <= 4:
             if self.world == 1:
                 summary, q, failed = eng.summary_quantiles(x, seg, n_seg, qs, perm_goff, brackets_ready=brackets_ready)
             else:                                       # ``failed`` is the same on every rank: they fall back together
-                summary, q, failed = eng.summary_quantiles_ranks(x, seg, n_seg, qs, perm_goff, self.group or _world_group())
+                summary, q, failed = eng.summary_quantiles_ranks(x, seg, n_seg, qs, perm_goff, self.group or _world_group(),
+                                                                 begun=brackets_ready)
             if _unchecked:
                 return summary, q, failed
             if defer_check:
@@ -205,10 +207,10 @@ class ShardedEngine:
             out = eng.fused_from_host(ts, val, off, start_ms, step_ms, n_steps, window_steps, host["dev"],
                                       host["out"], lookback_ms)
         else:
-            # one rank: the brackets of the quantile selection come from the raw samples on a side
-            # stream while the fused kernel runs (they are hints; the sweep verifies them)
-            pre = (self.world == 1 and 1 <= len(qs) <= 4 and getattr(val, "is_cuda", False) and getattr(off, "is_cuda", False)
-                   and off.numel() > 1 and n_steps > 0)
+            # the brackets of the quantile selection come from the raw samples on a side stream while the
+            # fused kernel runs (they are hints; the sweep verifies them)
+            pre = (1 <= len(qs) <= 4 and getattr(val, "is_cuda", False) and getattr(off, "is_cuda", False) and n_steps > 0
+                   and (self.world > 1 or off.numel() > 1))
             if pre:
                 t = eng.torch
                 cur = t.cuda.current_stream()
@@ -216,7 +218,10 @@ class ShardedEngine:
                     self._side = t.cuda.Stream()
                 self._side.wait_stream(cur)
                 with t.cuda.stream(self._side):
-                    eng.summary_brackets_csr(val, off, n_steps, n_seg, qs, perm_goff)
+                    if self.world == 1:
+                        eng.summary_brackets_csr(val, off, n_steps, n_seg, qs, perm_goff)
+                    else:
+                        eng.summary_begin_csr_ranks(val, off, n_steps, n_seg, qs, perm_goff, self.group or _world_group())
                 ready = self._side.record_event()
             out = eng.fused(ts, val, off, start_ms, step_ms, n_steps, window_steps, lookback_ms, out=out)
             if pre:
