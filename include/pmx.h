@@ -290,8 +290,9 @@ int pmx_csr_copy(pmx_ctx* ctx, const int64_t* d_ts, const double* d_val, const i
  * d_row_order (optional, n_rows entries): the rows to visit, grouped by segment -- the d_perm of
  * pmx_group_index serves; a CTA then switches its private histograms rarely.  NULL = all rows in
  * storage order.
- * Pass 2 keeps the keys that still match a target in ctx scratch (<= 2^20 per segment) and passes
- * 3-5 read only those; one selection at a time per ctx, passes in order 0..5. */
+ * Pass 2 (the list pass) reads the data only to keep the keys that still match a target in ctx
+ * scratch (<= 2^20 per segment); its digit and those of passes 3-5 are read from those lists; one
+ * selection at a time per ctx, passes in order 0..5. */
 int pmx_quantile_hist(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
                       const int32_t* d_seg, int64_t n_seg,
                       const int32_t* d_row_order, int64_t n_rows, int64_t n_q, int pass,
