@@ -135,7 +135,8 @@ constexpr int BS_CL = 8;
 constexpr unsigned BS_KCAP = 12288;              // keys per CTA (96 KiB); a larger sample is thinned
 __global__ void __cluster_dims__(BS_CL, 1, 1) __launch_bounds__(1024)
 bs_bounds_kernel(const double* __restrict__ samp, int64_t P, const int32_t* __restrict__ perm,
-                 const int64_t* __restrict__ goff, const double* __restrict__ q, int n_q, BsSeg* __restrict__ segs) {
+                 const int64_t* __restrict__ goff, const double* __restrict__ q, int n_q, BsSeg* __restrict__ segs,
+                 double* __restrict__ exported) {
   namespace cg = cooperative_groups;
   cg::cluster_group cluster = cg::this_cluster();
   extern __shared__ __align__(16) unsigned char bs_smem[];
@@ -326,6 +327,11 @@ bs_bounds_kernel(const double* __restrict__ samp, int64_t P, const int32_t* __re
     }
     b.neg_zero = 0; b.list_n = 0; b.zero_bound = zb; b.sample_m = m; b.overflow = 0; b.n_valid = 0;
     b.smin = m ? key_f64(kmin) : INF; b.smax = m ? key_f64(kmax) : -INF; b.gmin = -INF; b.gmax = INF;
+    if (exported) {                              // several ranks: what this rank proposes (lo[4], hi[4], sample size, sample range)
+      double* o = exported + (size_t)g * (2 * BS_MAX_Q + 3);
+      for (int j = 0; j < BS_MAX_Q; ++j) { o[j] = b.lo[j]; o[BS_MAX_Q + j] = b.hi[j]; }
+      o[2 * BS_MAX_Q] = (double)m; o[2 * BS_MAX_Q + 1] = b.smin; o[2 * BS_MAX_Q + 2] = b.smax;
+    }
   }
 }
 
@@ -671,14 +677,6 @@ __global__ void bs_clear_kernel(BsSeg* __restrict__ segs, int64_t n_seg) {
   segs[g].neg_zero = 0; segs[g].list_n = 0; segs[g].n_valid = 0; segs[g].overflow = 0;
 }
 
-__global__ void bs_export_bounds_kernel(const BsSeg* __restrict__ segs, int64_t n_seg, double* __restrict__ out) {
-  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (g >= n_seg) return;
-  for (int j = 0; j < BS_MAX_Q; ++j) { out[g * BS_BOUNDS_W + j] = segs[g].lo[j]; out[g * BS_BOUNDS_W + BS_MAX_Q + j] = segs[g].hi[j]; }
-  out[g * BS_BOUNDS_W + 2 * BS_MAX_Q] = (double)segs[g].sample_m;
-  out[g * BS_BOUNDS_W + 2 * BS_MAX_Q + 1] = segs[g].smin; out[g * BS_BOUNDS_W + 2 * BS_MAX_Q + 2] = segs[g].smax;
-}
-
 // hull over the ranks that hold sample values of the segment; counters were cleared by bs_bounds_kernel
 __global__ void bs_merge_bounds_kernel(const double* __restrict__ all, int world, int64_t n_seg, int n_q,
                                        BsSeg* __restrict__ segs) {
@@ -706,11 +704,16 @@ __global__ void bs_merge_bounds_kernel(const double* __restrict__ all, int world
   segs[g].gmin = gmin; segs[g].gmax = gmax;
 }
 
-__global__ void bs_pack_kernel(const BsSeg* __restrict__ segs, const double* __restrict__ sum, const int64_t* __restrict__ cnt,
-                               const double* __restrict__ mn, const double* __restrict__ mx, int64_t n_seg, unsigned cap,
-                               unsigned long long* __restrict__ out) {
-  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+// one warp per segment: fold this rank's per-series partials (the order of pmx_group_reduce), then pack
+__global__ void __launch_bounds__(128)
+bs_pack_kernel(const BsSeg* __restrict__ segs, const Part* __restrict__ part, const int32_t* __restrict__ perm,
+               const int64_t* __restrict__ goff, double* __restrict__ sum, int64_t* __restrict__ cnt,
+               double* __restrict__ mn, double* __restrict__ mx, int64_t n_seg, unsigned cap,
+               unsigned long long* __restrict__ out) {
+  const int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (g >= n_seg) return;
+  group_fold_warp(part, perm, goff, g, threadIdx.x & 31, sum, cnt, mn, mx, nullptr);
+  if ((threadIdx.x & 31) != 0) return;           // lane 0 wrote the fold's results and reads them back
   const double INF = __longlong_as_double(0x7FF0000000000000LL);
   unsigned long long* o = out + g * BS_PACK_W;
   const int64_t c = cnt[g];
@@ -723,48 +726,6 @@ __global__ void bs_pack_kernel(const BsSeg* __restrict__ segs, const double* __r
   }
   o[4 + 3 * BS_MAX_Q] = segs[g].neg_zero;
   o[5 + 3 * BS_MAX_Q] = segs[g].list_n > cap ? 1 : 0;
-}
-
-// summary in rank order (as pmx_group_combine), counters summed into segs
-__global__ void bs_combine_kernel(const unsigned long long* __restrict__ all, int world, int64_t n_seg, int64_t n_q,
-                                  BsSeg* __restrict__ segs,
-                                  double* o_sum, int64_t* o_cnt, double* o_min, double* o_max, double* o_mean) {
-  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (g >= n_seg) return;
-  Part r = part_identity();
-  unsigned long long cn[3 * BS_MAX_Q + 2];
-  for (int i = 0; i < 3 * BS_MAX_Q + 2; ++i) cn[i] = 0;
-  for (int w = 0; w < world; ++w) {
-    const size_t per_rank = (size_t)n_seg * BS_PACK_W + (size_t)n_seg * n_q * BS_BINS / 2;   // packed words, then the first histograms
-    const unsigned long long* b = all + (size_t)w * per_rank + (size_t)g * BS_PACK_W;
-    r.sum += __longlong_as_double((long long)b[0]); r.cnt += (long long)b[1];
-    r.mn = fmin(r.mn, __longlong_as_double((long long)b[2])); r.mx = fmax(r.mx, __longlong_as_double((long long)b[3]));
-    for (int i = 0; i < 3 * BS_MAX_Q + 2; ++i) cn[i] += b[4 + i];
-  }
-  for (int j = 0; j < BS_MAX_Q; ++j) {
-    segs[g].below[j] = cn[j]; segs[g].eq_lo[j] = cn[BS_MAX_Q + j]; segs[g].eq_hi[j] = cn[2 * BS_MAX_Q + j];
-  }
-  segs[g].neg_zero = cn[3 * BS_MAX_Q];
-  segs[g].overflow = cn[3 * BS_MAX_Q + 1] ? 1u : 0u;
-  const bool any = r.cnt > 0;
-  if (o_sum) o_sum[g] = r.sum;
-  if (o_cnt) o_cnt[g] = r.cnt;
-  if (o_min) o_min[g] = any ? r.mn : pmx_nan();
-  if (o_max) o_max[g] = any ? r.mx : pmx_nan();
-  if (o_mean) o_mean[g] = any ? r.sum / (double)r.cnt : pmx_nan();
-}
-
-// first histograms of all ranks (behind the packed words of every rank) -> their sum
-__global__ void bs_sum_hist_kernel(const unsigned long long* __restrict__ all, int world, int64_t n_seg, int n_q,
-                                   unsigned int* __restrict__ out) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const int64_t n = n_seg * n_q * BS_BINS;
-  if (i >= n) return;
-  const size_t per_rank = (size_t)n_seg * BS_PACK_W + (size_t)n / 2;          // 64-bit words
-  unsigned c = 0;
-  for (int w = 0; w < world; ++w)
-    c += reinterpret_cast<const unsigned int*>(all + (size_t)w * per_rank + (size_t)n_seg * BS_PACK_W)[i];
-  out[i] = c;
 }
 
 // A digit of this rank's keys strictly inside bracket j: grid (4 n_q, n_seg).  SECOND = false: the first
@@ -821,22 +782,55 @@ bs_midhist_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __re
 // CTA (j, g), after the all-reduce of the first histograms: place the two ranks of quantile j (as
 // bs_resolve_kernel does, from the combined counters) and pick the first digit of their buckets.
 __global__ void __launch_bounds__(1024)
-bs_pick1_kernel(const BsSeg* __restrict__ segs, const unsigned int* __restrict__ hist, const int64_t* __restrict__ count,
-                const double* __restrict__ q, int n_q, BsPick* __restrict__ picks) {
+bs_pick1_kernel(BsSeg* __restrict__ segs, const unsigned long long* __restrict__ all, int world, int64_t n_seg,
+                const double* __restrict__ q, int n_q, BsPick* __restrict__ picks,
+                double* o_sum, int64_t* o_cnt, double* o_min, double* o_max, double* o_mean) {
   __shared__ unsigned int s_warp[32];
   __shared__ BsPick s_p;
   __shared__ unsigned int s_tot;
+  __shared__ unsigned long long s_cn[3 * BS_MAX_Q + 2];
+  __shared__ long long s_n;
   const int j = blockIdx.x, g = blockIdx.y;
   BsPick* pick = picks + (size_t)g * n_q + j;
-  const long long n = count[g];
+  // what every rank packed, in rank order: the counters (one thread each), the summary (one thread),
+  // and this thread's two bins of the first histogram -- every CTA of the segment gets the same numbers
+  const size_t per_rank = (size_t)n_seg * BS_PACK_W + (size_t)n_seg * n_q * BS_BINS / 2;   // 64-bit words
+  if (threadIdx.x < 3 * BS_MAX_Q + 2) {
+    unsigned long long c = 0;
+    for (int w = 0; w < world; ++w) c += all[(size_t)w * per_rank + (size_t)g * BS_PACK_W + 4 + threadIdx.x];
+    s_cn[threadIdx.x] = c;
+  } else if (threadIdx.x == 32) {
+    Part r = part_identity();
+    for (int w = 0; w < world; ++w) {
+      const unsigned long long* b = all + (size_t)w * per_rank + (size_t)g * BS_PACK_W;
+      r.sum += __longlong_as_double((long long)b[0]); r.cnt += (long long)b[1];
+      r.mn = fmin(r.mn, __longlong_as_double((long long)b[2])); r.mx = fmax(r.mx, __longlong_as_double((long long)b[3]));
+    }
+    s_n = r.cnt;
+    if (j == 0) {
+      const bool any = r.cnt > 0;
+      if (o_sum) o_sum[g] = r.sum;
+      if (o_cnt) o_cnt[g] = r.cnt;
+      if (o_min) o_min[g] = any ? r.mn : pmx_nan();
+      if (o_max) o_max[g] = any ? r.mx : pmx_nan();
+      if (o_mean) o_mean[g] = any ? r.sum / (double)r.cnt : pmx_nan();
+    }
+  }
+  unsigned c0 = 0, c1 = 0;
+  for (int w = 0; w < world; ++w) {
+    const uint2 c = *reinterpret_cast<const uint2*>(reinterpret_cast<const unsigned int*>(all + (size_t)w * per_rank + (size_t)n_seg * BS_PACK_W) +
+                                                    ((size_t)g * n_q + j) * BS_BINS + 2 * threadIdx.x);
+    c0 += c.x; c1 += c.y;
+  }
+  __syncthreads();
+  const long long n = s_n;
   if (n <= 0) { if (threadIdx.x == 0) { pick->zone[0] = pick->zone[1] = -1; } return; }
   const BsSeg& B = segs[g];
   const double lo = B.lo[j], hi = B.hi[j];
   const uint64_t klo = f64_key(lo), khi = f64_key(hi);
-  const unsigned long long c_lt = B.below[j], c_el = B.eq_lo[j], c_eh = hi == lo ? 0 : B.eq_hi[j], c_nz = B.neg_zero;
-  const bool overflow = B.overflow != 0;
-  const unsigned int* h = hist + ((size_t)g * n_q + j) * BS_BINS;
-  const unsigned c0 = h[2 * threadIdx.x], c1 = h[2 * threadIdx.x + 1];
+  const unsigned long long c_lt = s_cn[j], c_el = s_cn[BS_MAX_Q + j], c_eh = hi == lo ? 0 : s_cn[2 * BS_MAX_Q + j],
+                           c_nz = s_cn[3 * BS_MAX_Q];
+  const bool overflow = s_cn[3 * BS_MAX_Q + 1] != 0;
   const unsigned base = bs_scan2(c0, c1, s_warp);
   if (threadIdx.x == blockDim.x - 1) s_tot = base + c0 + c1;      // all keys inside the bracket, over all ranks
   __syncthreads();
@@ -1026,7 +1020,7 @@ bs_final_kernel(const BsSeg* __restrict__ segs, const BsPick* __restrict__ picks
 // scratch of one selection: per-series partials (slot PMX_SCR_PARTIALS); per-segment brackets and
 // counters | local fold outputs | picks | sample | lists (slot PMX_SCR_BRACKET)
 struct BsScratch {
-  Part* part; BsSeg* segs; double* f_sum; int64_t* f_cnt; double* f_min; double* f_max; BsPick* picks; unsigned int* hist1;
+  Part* part; BsSeg* segs; double* f_sum; int64_t* f_cnt; double* f_min; double* f_max; BsPick* picks;
   double* samp; unsigned long long* lists; int64_t cap; int64_t P;
 };
 static int bs_scratch(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg, int64_t n_q, BsScratch* S) {
@@ -1043,9 +1037,8 @@ static int bs_scratch(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n
   auto up = [](size_t b) { return (b + 255) & ~size_t(255); };
   const size_t seg_bytes = up((size_t)n_seg * sizeof(BsSeg)), fold_bytes = up((size_t)n_seg * 8);
   const size_t pick_bytes = up((size_t)n_seg * BS_MAX_Q * sizeof(BsPick));
-  const size_t hist_bytes = up((size_t)n_seg * BS_MAX_Q * BS_BINS * sizeof(unsigned int));
   const size_t samp_bytes = up((size_t)(n_series > 0 ? n_series : 1) * (S->P > 0 ? S->P : 1) * 8);
-  unsigned char* scr = (unsigned char*)pmx_scratch(ctx, PMX_SCR_BRACKET, seg_bytes + 4 * fold_bytes + pick_bytes + hist_bytes + samp_bytes +
+  unsigned char* scr = (unsigned char*)pmx_scratch(ctx, PMX_SCR_BRACKET, seg_bytes + 4 * fold_bytes + pick_bytes + samp_bytes +
                                                                          (size_t)n_seg * cap * 8);
   if (!scr) return PMX_E_CUDA;
   S->segs = (BsSeg*)scr; scr += seg_bytes;
@@ -1054,7 +1047,6 @@ static int bs_scratch(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n
   S->f_min = (double*)scr; scr += fold_bytes;
   S->f_max = (double*)scr; scr += fold_bytes;
   S->picks = (BsPick*)scr; scr += pick_bytes;
-  S->hist1 = (unsigned int*)scr; scr += hist_bytes;
   S->samp = (double*)scr; scr += samp_bytes;
   S->lists = (unsigned long long*)scr;
   (void)n_q;
@@ -1063,7 +1055,7 @@ static int bs_scratch(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n
 // sample + brackets of this rank's rows
 static int bs_launch_bounds(const BsScratch& S, const double* d_x, int64_t n_series, int64_t n_steps, int64_t n_seg,
                             const int32_t* d_perm, const int64_t* d_goff, const double* d_q, int64_t n_q, cudaStream_t st,
-                            const int64_t* d_csr_off = nullptr) {
+                            const int64_t* d_csr_off = nullptr, double* d_exported = nullptr) {
   const bool data = n_series > 0 && n_steps > 0;
   if (data) {
     const int64_t slots = n_series * S.P;
@@ -1076,7 +1068,8 @@ static int bs_launch_bounds(const BsScratch& S, const double* d_x, int64_t n_ser
   const size_t smem = (size_t)BS_KCAP * 8 + (size_t)2 * n_q * BS_BINS * sizeof(unsigned int);
   PMX_CUDA(cudaFuncSetAttribute(bs_bounds_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)(BS_KCAP * 8 + 2 * BS_MAX_Q * BS_BINS * sizeof(unsigned int))));
-  bs_bounds_kernel<<<(unsigned)(n_seg * BS_CL), 1024, smem, st>>>(S.samp, data ? S.P : 0, d_perm, d_goff, d_q, (int)n_q, S.segs);
+  bs_bounds_kernel<<<(unsigned)(n_seg * BS_CL), 1024, smem, st>>>(S.samp, data ? S.P : 0, d_perm, d_goff, d_q, (int)n_q, S.segs,
+                                                                  d_exported);
   PMX_LAUNCH_CHECK();
   return PMX_OK;
 }
@@ -1153,10 +1146,7 @@ int pmx_bsel_begin(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_
   cudaStream_t st = pmx_st(stream);
   BsScratch S;
   if (int rc = bs_scratch(ctx, n_series, n_steps, n_seg, n_q, &S)) return rc;
-  if (int rc = bs_launch_bounds(S, d_x, n_series, n_steps, n_seg, d_perm, d_goff, d_q, n_q, st)) return rc;
-  bs_export_bounds_kernel<<<(unsigned)((n_seg + 127) / 128), 128, 0, st>>>(S.segs, n_seg, d_bounds);
-  PMX_LAUNCH_CHECK();
-  return PMX_OK;
+  return bs_launch_bounds(S, d_x, n_series, n_steps, n_seg, d_perm, d_goff, d_q, n_q, st, nullptr, d_bounds);
 }
 
 int pmx_bsel_begin_csr(pmx_ctx* ctx, const double* d_val, const int64_t* d_off, int64_t n_series, int64_t n_steps, int64_t n_seg,
@@ -1168,10 +1158,7 @@ int pmx_bsel_begin_csr(pmx_ctx* ctx, const double* d_val, const int64_t* d_off, 
   cudaStream_t st = pmx_st(stream);
   BsScratch S;
   if (int rc = bs_scratch(ctx, n_series, n_steps, n_seg, n_q, &S)) return rc;
-  if (int rc = bs_launch_bounds(S, d_val, n_series, n_steps, n_seg, d_perm, d_goff, d_q, n_q, st, d_off)) return rc;
-  bs_export_bounds_kernel<<<(unsigned)((n_seg + 127) / 128), 128, 0, st>>>(S.segs, n_seg, d_bounds);
-  PMX_LAUNCH_CHECK();
-  return PMX_OK;
+  return bs_launch_bounds(S, d_val, n_series, n_steps, n_seg, d_perm, d_goff, d_q, n_q, st, d_off, d_bounds);
 }
 
 int pmx_bsel_sweep(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps, const int32_t* d_seg, int64_t n_seg,
@@ -1185,9 +1172,8 @@ int pmx_bsel_sweep(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_
   bs_merge_bounds_kernel<<<(unsigned)((n_seg + 127) / 128), 128, 0, st>>>(d_bounds_all, n_ranks, n_seg, (int)n_q, S.segs);
   PMX_LAUNCH_CHECK();
   if (int rc = bs_launch_sweep(S, d_x, n_series, n_steps, d_seg, n_q, st)) return rc;
-  if (int rc = pmx_internal_group_fold(S.part, d_perm, d_goff, n_seg, S.f_sum, S.f_cnt, S.f_min, S.f_max, nullptr, st)) return rc;
-  bs_pack_kernel<<<(unsigned)((n_seg + 127) / 128), 128, 0, st>>>(S.segs, S.f_sum, S.f_cnt, S.f_min, S.f_max, n_seg, (unsigned)S.cap,
-                                                                  (unsigned long long*)d_packed);
+  bs_pack_kernel<<<(unsigned)((n_seg + 3) / 4), 128, 0, st>>>(S.segs, S.part, d_perm, d_goff, S.f_sum, S.f_cnt, S.f_min, S.f_max, n_seg,
+                                                              (unsigned)S.cap, (unsigned long long*)d_packed);
   PMX_LAUNCH_CHECK();
   // first digit of this rank's keys inside every bracket, behind the packed words (it needs only the
   // brackets and the sample range, so it travels with the counters)
@@ -1207,14 +1193,9 @@ int pmx_bsel_hist(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg
   cudaStream_t st = pmx_st(stream);
   BsScratch S;
   if (int rc = bs_scratch(ctx, n_series, n_steps, n_seg, n_q, &S)) return rc;
-  bs_combine_kernel<<<(unsigned)((n_seg + 127) / 128), 128, 0, st>>>((const unsigned long long*)d_packed_all, n_ranks, n_seg, n_q, S.segs,
-                                                                     d_sum, d_count, d_min, d_max, d_mean);
-  PMX_LAUNCH_CHECK();
-  const int64_t nh = n_seg * n_q * BS_BINS;
-  bs_sum_hist_kernel<<<(unsigned)((nh + 255) / 256), 256, 0, st>>>((const unsigned long long*)d_packed_all, n_ranks, n_seg, (int)n_q, S.hist1);
-  PMX_LAUNCH_CHECK();
   dim3 grid((unsigned)n_q, (unsigned)n_seg);
-  bs_pick1_kernel<<<grid, 1024, 0, st>>>(S.segs, S.hist1, d_count, d_q, (int)n_q, S.picks);
+  bs_pick1_kernel<<<grid, 1024, 0, st>>>(S.segs, (const unsigned long long*)d_packed_all, n_ranks, n_seg, d_q, (int)n_q, S.picks,
+                                         d_sum, d_count, d_min, d_max, d_mean);
   PMX_LAUNCH_CHECK();
   PMX_CUDA(cudaMemsetAsync(d_hist2, 0, (size_t)n_seg * n_q * 2 * BS_BINS * sizeof(uint32_t), st));
   dim3 grid4((unsigned)n_q * 4, (unsigned)n_seg);

@@ -629,7 +629,7 @@ class Engine:
         _abi.check(self.lib.pmx_bsel_begin_csr(self.ctx, self._ptr(val), self._ptr(off), S, n_steps, n_seg, self._ptr(d_perm),
                                                self._ptr(d_goff), self._ptr(self._quantile_levels(qs)), len(qs),
                                                self._ptr(b["bounds"]), self._stream()))
-        self.launches += 3 if S > 0 and n_steps > 0 else 2
+        self.launches += 2 if S > 0 and n_steps > 0 else 1
 
     def summary_quantiles_ranks(self, x, seg, n_seg, qs, perm_goff, group, begun=False):
         """``summary_quantiles`` over ALL ranks of ``group`` (every rank passes its own rows): five library
@@ -669,8 +669,8 @@ class Engine:
         dist.all_gather_into_tensor(b["rows_all"], b["rows"], group=group)
         _abi.check(lib.pmx_bsel_finish(self.ctx, S, T, n_seg, n_q, p(b["rows_all"]), world, p(cnt), p(outs["n"]), p(outs["lo"]),
                                        p(outs["hi"]), p(outs["x_lo"]), p(outs["x_hi"]), p(outs["value"]), p(failed), st()))
-        # sample, bounds, export | merge, sweep, fold, pack, histogram | combine, sum, pick, histogram | pick | final
-        self.launches += (15 if S > 0 and T > 0 else 13) - (0 if not begun else (3 if S > 0 and T > 0 else 2))
+        # sample, bounds | merge, sweep, fold + pack, histogram | pick, histogram | pick | final
+        self.launches += (10 if S > 0 and T > 0 else 7) - (0 if not begun else (2 if S > 0 and T > 0 else 1))
         return (sm, cnt, mn, mx, mean), outs, failed
 
     def defer_flag(self, counter):
