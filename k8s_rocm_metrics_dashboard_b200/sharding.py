@@ -110,6 +110,18 @@ class ShardedEngine:
         self._qbuf = {}
         self._graphs = {}
 
+    # The one-sweep selection spends a cluster of CTAs per segment on the brackets and another per
+    # (segment, level) on the last keys, ~40 us each whatever the segment holds: it pays for long
+    # segments (per-metric groups: millions of values), not for thousands of short ones (per-card groups).
+    ONE_SWEEP_MIN_VALUES_PER_SEGMENT = 1 << 18
+
+    def one_sweep_pays(self, n_series, n_steps, n_seg):
+        """Several ranks must all take the same path, and their shards differ in size: there the answer
+        depends on the number of segments alone."""
+        if self.world > 1:
+            return 0 < n_seg <= 64
+        return n_seg > 0 and n_series * n_steps >= n_seg * self.ONE_SWEEP_MIN_VALUES_PER_SEGMENT
+
     @staticmethod
     def _qsummary(summary):
         """(count, min, max) of the combined group summary: where the quantile selection starts."""
@@ -125,7 +137,7 @@ class ShardedEngine:
         ``brackets_ready``: ``Engine.summary_brackets_csr`` (one rank) or ``summary_begin_csr_ranks`` (several; then
         on EVERY rank) already ran for these series."""
         eng = self.eng
-        if 1 <= len(qs) <= 4:
+        if 1 <= len(qs) <= 4 and self.one_sweep_pays(x.shape[0], x.shape[1], n_seg):
             if self.world == 1:
                 summary, q, failed = eng.summary_quantiles(x, seg, n_seg, qs, perm_goff, brackets_ready=brackets_ready)
             else:                                       # ``failed`` is the same on every rank: they fall back together
@@ -210,7 +222,7 @@ class ShardedEngine:
             # the brackets of the quantile selection come from the raw samples on a side stream while the
             # fused kernel runs (they are hints; the sweep verifies them)
             pre = (1 <= len(qs) <= 4 and getattr(val, "is_cuda", False) and getattr(off, "is_cuda", False) and n_steps > 0
-                   and (self.world > 1 or off.numel() > 1))
+                   and (self.world > 1 or off.numel() > 1) and self.one_sweep_pays(off.numel() - 1, n_steps, n_seg))
             if pre:
                 t = eng.torch
                 cur = t.cuda.current_stream()

@@ -138,6 +138,8 @@ def test_overflowing_list_is_reported_and_summarize_falls_back(eng):
     summ, q, failed, ref_s, ref_q = _both(eng, x, gid, M)
     assert failed > 0
     sh = sharding.ShardedEngine(eng, local_only=True)
+    assert not sh.one_sweep_pays(S, T, M)                          # thousands of short segments: summarize would not even try
+    sh.ONE_SWEEP_MIN_VALUES_PER_SEGMENT = 0                        # ... so make it
     perm, goff = group_index(gid, M)
     pg = (t.as_tensor(perm, device=eng.device), t.as_tensor(goff, device=eng.device))
     s2, q2 = sh.summarize(t.as_tensor(x, device=eng.device), t.as_tensor(gid, device=eng.device), M, pg, QS)
