@@ -41,9 +41,9 @@ struct Smem {
   int64_t ts[NSP];
   double S_sum[NE], S_mn[NE], S_mx[NE], S_d[NE];
   double T_sum[NT], T_mn[NT], T_mx[NT], T_fv[NT], T_lv[NT], T_di[NT], T_tj[NT];
-  double cold[4 * NT];
   uint32_t T_meta[NT];
-  int B[BMAX];
+  uint16_t B[BMAX];                  // tile-relative (0 .. NE): 16 bits do; with the direct folds returning in
+                                     // registers the CTA needs 52.7 KB instead of 59 and four fit an SM
   uint16_t S_meta[NE];
   int nb;
   int overflow;
@@ -51,11 +51,14 @@ struct Smem {
   int64_t next_off_sc;
 };
 
-// Direct fold of one output from global memory.  Cold.  out[0..3] = min, max, mean, count (roll)
+// Direct fold of one output from global memory.  Cold.  Returns min, max, mean, count (roll)
 // or increase, rate (rate); `what` 0 = rolling, 1 = rate.
-__device__ __noinline__ void fold_direct(const int64_t* __restrict__ ts, const double* __restrict__ val,
-                                         int64_t sstart, int64_t f, int64_t window_ms, int need, int what,
-                                         double* out) {
+struct Folded { double v[4]; };
+__device__ __noinline__ Folded fold_direct(const int64_t* __restrict__ ts, const double* __restrict__ val,
+                                           int64_t sstart, int64_t f, int64_t window_ms, int need, int what) {
+  Folded res;
+  double* out = res.v;
+  out[0] = out[1] = out[2] = out[3] = 0.0;
   const int64_t edge = ts[f] - window_ms;
   int64_t lo = sstart, hi = f;
   while (lo < hi) { const int64_t m = (lo + hi) >> 1; if (ts[m] <= edge) lo = m + 1; else hi = m; }
@@ -83,6 +86,7 @@ __device__ __noinline__ void fold_direct(const int64_t* __restrict__ ts, const d
     out[0] = cnt >= 2 ? acc : pmx_nan();
     out[1] = have ? acc * 1000.0 / (double)(lt - ft) : pmx_nan();
   }
+  return res;
 }
 
 __global__ void __launch_bounds__(NT, 4)
@@ -136,7 +140,7 @@ ragged_fast_kernel(const RParams p, int64_t n_tiles, int tiles_per_cta) {
         int64_t v = s <= p.n_series ? p.off[s] - tile_lo : (int64_t)NE;
         if (v > NE) v = NE;
         if (v < 0) v = 0;                                    // empty series before the tile start
-        sm.B[i] = (int)v;
+        sm.B[i] = (uint16_t)v;
         __syncthreads();
         const bool done = sm.B[nb + NT - 1] >= NE;
         nb += NT;
@@ -252,9 +256,9 @@ ragged_fast_kernel(const RParams p, int64_t n_tiles, int tiles_per_cta) {
         const int l = wl[r];
         double ws, wmn, wmx; int wcf, wcn;
         if (l < 0) {                                       // direct fold from global memory
-          fold_direct(p.ts, p.val, tile_lo + sr[r], obase + r, p.window_ms, need, 0, sm.cold + 4 * t);
-          omn[r & 3] = sm.cold[4 * t]; omx[r & 3] = sm.cold[4 * t + 1]; omean[r & 3] = sm.cold[4 * t + 2];
-          ocnt[r & 3] = (int)sm.cold[4 * t + 3];
+          const Folded fd = fold_direct(p.ts, p.val, tile_lo + sr[r], obase + r, p.window_ms, need, 0);
+          omn[r & 3] = fd.v[0]; omx[r & 3] = fd.v[1]; omean[r & 3] = fd.v[2];
+          ocnt[r & 3] = (int)fd.v[3];
         } else {
         const int cl = l >> 3;
         if (cl == t) {                                     // window inside the own chunk
@@ -348,8 +352,8 @@ ragged_fast_kernel(const RParams p, int64_t n_tiles, int tiles_per_cta) {
           } else direct = true;                            // NaN run at the window start
         }
         if (direct) {
-          fold_direct(p.ts, p.val, tile_lo + sr[r], obase + r, p.window_ms, need, 1, sm.cold + 4 * t);
-          oinc[r & 3] = sm.cold[4 * t]; orate[r & 3] = sm.cold[4 * t + 1];
+          const Folded fd = fold_direct(p.ts, p.val, tile_lo + sr[r], obase + r, p.window_ms, need, 1);
+          oinc[r & 3] = fd.v[0]; orate[r & 3] = fd.v[1];
         } else {
           const bool have = lpos > fpos;
           double rate = pmx_nan();
