@@ -70,7 +70,11 @@ def _label_table(body, spans):
     """pmx_labels_intern on the metric spans of a body (bytes or uint8 array)."""
     lib = _abi.lib()
     n = len(spans)
-    raw = body if isinstance(body, (bytes, bytearray)) else body.tobytes()
+    if isinstance(body, (bytes, bytearray)):
+        raw, raw_len = body, len(body)
+    else:                                                    # uint8 array (e.g. the view of a pinned tensor): no copy
+        arr = np.ascontiguousarray(body, dtype=np.uint8)
+        raw, raw_len = C.c_void_p(arr.ctypes.data), arr.size
     m_off = np.fromiter((o for o, _ in spans), dtype=np.uint32, count=n)
     m_len = np.fromiter((l for _, l in spans), dtype=np.uint32, count=n)
     total = int(m_len.sum())
@@ -81,7 +85,7 @@ def _label_table(body, spans):
     cap_distinct = cap_pairs * 2 + 1
     str_off = np.empty(cap_distinct + 1, dtype=np.int64)
     res = _abi.LabelsResult()
-    rc = lib.pmx_labels_intern(raw, len(raw), m_off.ctypes.data, m_len.ctypes.data, n, pair_off.ctypes.data,
+    rc = lib.pmx_labels_intern(raw, raw_len, m_off.ctypes.data, m_len.ctypes.data, n, pair_off.ctypes.data,
                                key_id.ctypes.data, val_id.ctypes.data, cap_pairs, strings.ctypes.data, strings.size,
                                str_off.ctypes.data, cap_distinct, C.byref(res))
     if rc != _abi.OK:
@@ -242,17 +246,27 @@ class Engine:
         return int(self.lib.pmx_ctx_scratch_bytes(self.ctx))
 
     # ------------------------------------------------------------------ K1
-    def tokenize_device(self, body: bytes) -> DeviceTokens:
+    def tokenize_device(self, body) -> DeviceTokens:
         """X1 on the GPU: one H2D copy of the body, then pmx_tokenize_device.  Raises ValueError when
-        the body is not in Prometheus' compact encoding (use ``tokenize`` for general JSON)."""
+        the body is not in Prometheus' compact encoding (use ``tokenize`` for general JSON).
+        ``body``: bytes / str, or a uint8 CPU tensor -- a PINNED one (e.g. filled by
+        ``response.raw.readinto``) is copied at the full PCIe rate instead of through a staging
+        buffer (131 MB: 2.4 ms instead of ~11 ms)."""
         t = self.torch
         if isinstance(body, str):
             body = body.encode("utf-8")
-        n = len(body)
-        import warnings
-        with warnings.catch_warnings():                    # read-only bytes view; it is only read
-            warnings.simplefilter("ignore", UserWarning)
-            text = t.frombuffer(body, dtype=t.uint8).to(self.device, non_blocking=True)
+        if isinstance(body, t.Tensor):
+            if body.dtype != t.uint8 or body.is_cuda or body.dim() != 1:
+                raise ValueError("tokenize_device: a tensor body must be a 1-D uint8 CPU tensor")
+            n = body.numel()
+            text = body.to(self.device, non_blocking=True)
+            body = body.numpy()                            # host view for the labels (shares the memory)
+        else:
+            n = len(body)
+            import warnings
+            with warnings.catch_warnings():                # read-only bytes view; it is only read
+                warnings.simplefilter("ignore", UserWarning)
+                text = t.frombuffer(body, dtype=t.uint8).to(self.device, non_blocking=True)
         cap_s, cap_r = n // 8 + 1, n // 24 + 1
         ts_off, val_off = self._empty((cap_s,), t.int32), self._empty((cap_s,), t.int32)
         series_off = self._empty((cap_r + 1,), t.int64)
@@ -267,7 +281,7 @@ class Engine:
             raise ValueError("pmx_tokenize_device: " + _TOKD_ERRORS.get(err, f"error {err}").format(where=where))
         soff = series_off[:nr + 1].cpu().numpy()
         spans = list(zip(m_off[:nr].cpu().numpy().view(np.uint32).tolist(), m_len[:nr].cpu().numpy().view(np.uint32).tolist()))
-        kind = "matrix" if body[42:48] == b"matrix" else "vector"
+        kind = "matrix" if bytes(body[42:48]) == b"matrix" else "vector"
         return DeviceTokens(body, text, ts_off[:ns], val_off[:ns], soff, spans, kind)
 
     def parse(self, tok, want_ts=True):
@@ -314,8 +328,9 @@ class Engine:
         ts, val, b = self._parse_launch(tok.d_text, tok.d_ts_off if want_ts else None, tok.d_val_off, n, want_ts)
         if b[0] < n:
             o = int(tok.d_val_off[b[0]].item()) & 0xffffffff
-            end = tok.body.find(b'"', o)
-            err = ValueError(f"could not convert string to float: {tok.body[o:end].decode('utf-8', 'replace')!r}")
+            tail = bytes(tok.body[o:o + 4096])               # (bytes, or the uint8 view of a pinned body)
+            end = tail.find(b'"')
+            err = ValueError(f"could not convert string to float: {tail[:end if end >= 0 else len(tail)].decode('utf-8', 'replace')!r}")
             err.sample_index = int(b[0])
             raise err
         if want_ts and b[1] < n:

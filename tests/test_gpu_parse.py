@@ -95,3 +95,23 @@ def test_empty_and_bad_timestamp(eng):
     tok = tokenize(_body(["1"], ts="1.23456"))
     with pytest.raises(ValueError, match="timestamp"):
         eng.parse(tok)
+
+
+def test_pinned_tensor_body_equals_bytes_body(eng):
+    """tokenize_device takes the body as a pinned uint8 tensor too (full-rate H2D): same tokens, same labels,
+    and a malformed value is reported as for a bytes body."""
+    import torch
+    from k8s_rocm_metrics_dashboard_b200 import synth
+    d = synth.dense(1, 2, 3, 50, seed=3)
+    body = synth.to_matrix_json(d["labels"], d["ts"], d["val"], d["off"])
+    pinned = torch.frombuffer(bytearray(body), dtype=torch.uint8).pin_memory()
+    a, b = eng.tokenize_device(body), eng.tokenize_device(pinned)
+    assert np.array_equal(a.series_off, b.series_off) and a.metric_spans == b.metric_spans and a.result_type == b.result_type
+    assert list(a.labels()) == list(b.labels())
+    ta, va = eng.parse(a); tb, vb = eng.parse(b)
+    assert torch.equal(ta, tb) and torch.equal(va.view(torch.int64), vb.view(torch.int64))
+    bad = bytearray(body)
+    k = bad.find(b'"', bad.find(b'"values":[[') + 11) + 1
+    bad[k] = ord("x")
+    with pytest.raises(ValueError, match="could not convert string to float"):
+        eng.parse(eng.tokenize_device(torch.frombuffer(bad, dtype=torch.uint8).pin_memory()))
