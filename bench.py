@@ -286,7 +286,7 @@ def e2e_text_block(eng, steps=5):
     calls ``adapter.aggregate_range`` makes, without building the pandas frame."""
     import numpy as np
     import torch
-    from k8s_rocm_metrics_dashboard_b200 import group_index, synth
+    from k8s_rocm_metrics_dashboard_b200 import adapter, group_index, synth
     d = synth.dense(8, 8, N_METRICS, N_STEPS, seed=7, nan_frac=1e-3, kinds="ttk")
     body = synth.to_matrix_json(d["labels"], d["ts"], d["val"], d["off"])
     n = len(d["ts"])
@@ -298,8 +298,7 @@ def e2e_text_block(eng, steps=5):
         nonlocal out
         tok = eng.tokenize_device(pinned)                                 # H2D of the body + the cut
         labels = tok.labels()
-        names = sorted({l["__name__"] for l in labels})
-        gid = np.array([names.index(l["__name__"]) for l in labels], dtype=np.int32)
+        names, gid = adapter._group_ids(labels, ("__name__",))             # integer work on the interned table, as aggregate_range does
         ts, val = eng.parse(tok)
         out = eng.fused(ts, val, tok.series_off, START_MS, STEP_MS, N_STEPS, WINDOW_STEPS, LOOKBACK_MS, out=out)
         pg = group_index(gid, len(names))
