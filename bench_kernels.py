@@ -78,7 +78,10 @@ def main():
     rec("K5 group reduce per step [12,T]", N, 8, timeit(lambda: eng.group_reduce(al, None, 12, per_step=True, perm_goff=pg)))
     seg = torch.as_tensor(gid, device=dev)
     rec("K6 quantiles p50/p95/p99 x12", N, 24, timeit(lambda: eng.quantiles(al, seg, 12, [0.5, 0.95, 0.99], row_order=pg[0])),
-        "3 full passes + candidate lists")
+        "2 full histogram passes + the list pass (no summary given: pass 0 included)")
+    rec("K5+K6 summary + p50/p95/p99 x12, one sweep", N, 8,
+        timeit(lambda: eng.summary_quantiles(al, seg, 12, (0.5, 0.95, 0.99), pg)),
+        "pmx_summary_quantiles: sample, brackets, ONE read of the matrix, select (all serial here; in the step the first two run beside the fused kernel)")
     # one refresh of the series cache (one new grid point per series) against the full pass
     from k8s_rocm_metrics_dashboard_b200.cache import SeriesCache
     labs = synth.series_labels(64, 8, 12)
