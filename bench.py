@@ -341,7 +341,7 @@ def run_engine(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     eng = Engine(local)
-    sh = ShardedEngine(eng)
+    sh = ShardedEngine(eng, peer_exchange=not args.no_peer_exchange)
     dev = eng.device
 
     S, T = N_SERIES, N_STEPS
@@ -545,6 +545,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity-check", action="store_true")
     ap.add_argument("--no-config3", action="store_true")
+    ap.add_argument("--no-peer-exchange", action="store_true", help="several ranks: NCCL calls instead of stores into peer memory")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

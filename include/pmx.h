@@ -384,7 +384,8 @@ int pmx_summary_sweep(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t
  *   pmx_bsel_hist    summary of all ranks in rank order (d_sum .. d_mean, as pmx_group_combine),
  *                    counters and first digits summed, every wanted rank placed, second digit of
  *                    this rank's keys in the buckets that hold them
- *                    -> d_hist2 [n_seg * n_q * 2 * PMX_QUANTILE_BINS] u32; all-reduce (sum)
+ *                    -> d_hist2 [n_seg * n_q * 2 * PMX_QUANTILE_BINS] u32; all-reduce (sum), or
+ *                    all-gather and let pmx_bsel_rows add the n_hist = n_ranks copies
  *   pmx_bsel_rows    second digit of every bucket; this rank's keys of the buckets (22 bits)
  *                    -> d_rows [n_seg * n_q * row_w] u64; all-gather -> [n_ranks][...]
  *   pmx_bsel_finish  outputs of pmx_quantile_finish; *d_failed as in pmx_summary_quantiles -- it
@@ -405,10 +406,20 @@ int pmx_bsel_hist(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg
                   const uint64_t* d_packed_all, int n_ranks, double* d_sum, int64_t* d_count, double* d_min, double* d_max,
                   double* d_mean, uint32_t* d_hist2, pmx_stream stream);
 int pmx_bsel_rows(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg, int64_t n_q, const uint32_t* d_hist2,
-                  uint64_t* d_rows, pmx_stream stream);
+                  int n_hist, uint64_t* d_rows, pmx_stream stream);
 int pmx_bsel_finish(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg, int64_t n_q, const uint64_t* d_rows_all,
                     int n_ranks, const int64_t* d_count, int64_t* d_n, int64_t* d_lo, int64_t* d_hi, double* d_x_lo,
                     double* d_x_hi, double* d_value, int32_t* d_failed, pmx_stream stream);
+/* The all-gather of the pmx_bsel_* exchanges as stores into peer memory (no counterpart in the
+ * reference).  d_peer_base: device array of n_ranks addresses -- the receive buffer of every rank as
+ * mapped into THIS process (symmetric memory; Python: torch.distributed._symmetric_memory's
+ * buffer_ptrs_dev).  Stores nbytes from d_src into [dst_offset_bytes + rank * nbytes, + nbytes) of
+ * every rank's buffer, own included; sizes, offsets and d_src multiples of 16 bytes.  The caller
+ * follows it with a barrier of all ranks before anyone reads, and does not write the same region
+ * again before every rank has read it (the exchanges of one step use regions of their own, and a
+ * rank that starts the next step has passed this step's last barrier).  Ordinary stores only. */
+int pmx_peer_put(const void* d_src, const uint64_t* d_peer_base, int n_ranks, int rank, uint64_t dst_offset_bytes,
+                 uint64_t nbytes, pmx_stream stream);
 /* Single-GPU convenience: all passes back to back (no collective); hist/state in ctx scratch. */
 int pmx_quantile_select(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_steps,
                         const int32_t* d_seg, int64_t n_seg,

@@ -88,12 +88,13 @@ SIGNATURES = {
     "pmx_quantile_pick": (_int, [_p, _p, _i64, _p, _i64, _int, _p, _p]),
     "pmx_quantile_finish": (_int, [_p, _p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _p]),
     "pmx_quantile_select": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _p]),
+    "pmx_peer_put": (_int, [_p, _p, _int, _int, C.c_uint64, C.c_uint64, _p]),
     "pmx_bsel_widths": (_int, [_p, _p, _p]),
     "pmx_bsel_begin": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _p, _p, _i64, _p, _p]),
     "pmx_bsel_begin_csr": (_int, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p, _i64, _p, _p]),
     "pmx_bsel_sweep": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _p, _i64, _p, _int, _p, _p]),
     "pmx_bsel_hist": (_int, [_p, _i64, _i64, _i64, _p, _i64, _p, _int, _p, _p, _p, _p, _p, _p, _p]),
-    "pmx_bsel_rows": (_int, [_p, _i64, _i64, _i64, _i64, _p, _p, _p]),
+    "pmx_bsel_rows": (_int, [_p, _i64, _i64, _i64, _i64, _p, _int, _p, _p]),
     "pmx_bsel_finish": (_int, [_p, _i64, _i64, _i64, _i64, _p, _int, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "pmx_summary_quantiles": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _p, _p, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "pmx_summary_sweep": (_int, [_p, _p, _i64, _i64, _p, _i64, _p, _p, _p, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),

@@ -8,7 +8,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libpmx.so")
-SOURCES = ["ctx.cu", "tokenize.cu", "labels.cu", "tokenize_device.cu", "parse.cu", "window.cu", "window_fast.cu", "window_fast_dense.cu", "bucket.cu", "ragged.cu", "ragged_fast.cu", "reduce.cu", "quantile.cu", "bracket_select.cu", "elementwise.cu", "slab.cu"]
+SOURCES = ["ctx.cu", "tokenize.cu", "labels.cu", "tokenize_device.cu", "parse.cu", "window.cu", "window_fast.cu", "window_fast_dense.cu", "bucket.cu", "ragged.cu", "ragged_fast.cu", "reduce.cu", "quantile.cu", "bracket_select.cu", "elementwise.cu", "slab.cu", "peer.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-fmad=false",          # bit-parity with numpy/pandas: no silent FMA contraction
               "-Xcompiler", "-fPIC,-O3", "-Xptxas", "-v"]

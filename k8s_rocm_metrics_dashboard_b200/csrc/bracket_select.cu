@@ -30,6 +30,7 @@ constexpr int BS_BINS = 2048;
 constexpr int BS_STRIDE = 64;                    // one sampled value per this many steps of a row
 constexpr double BS_SIGMAS = 5.0;
 constexpr int BS_SMALL = 256;                    // a bucket this small is ranked directly
+constexpr int BS_BOUNDS_W = 2 * BS_MAX_Q + 4;    // several ranks, per segment: lo[4], hi[4], sample size, smallest and largest sample value, pad
 constexpr int BS_WBUF = 576;                     // values a warp can stage: 256 kept + a trip of 8 per lane + head and tail
 
 struct BsSeg {                                   // per segment
@@ -328,9 +329,9 @@ bs_bounds_kernel(const double* __restrict__ samp, int64_t P, const int32_t* __re
     b.neg_zero = 0; b.list_n = 0; b.zero_bound = zb; b.sample_m = m; b.overflow = 0; b.n_valid = 0;
     b.smin = m ? key_f64(kmin) : INF; b.smax = m ? key_f64(kmax) : -INF; b.gmin = -INF; b.gmax = INF;
     if (exported) {                              // several ranks: what this rank proposes (lo[4], hi[4], sample size, sample range)
-      double* o = exported + (size_t)g * (2 * BS_MAX_Q + 3);
+      double* o = exported + (size_t)g * BS_BOUNDS_W;
       for (int j = 0; j < BS_MAX_Q; ++j) { o[j] = b.lo[j]; o[BS_MAX_Q + j] = b.hi[j]; }
-      o[2 * BS_MAX_Q] = (double)m; o[2 * BS_MAX_Q + 1] = b.smin; o[2 * BS_MAX_Q + 2] = b.smax;
+      o[2 * BS_MAX_Q] = (double)m; o[2 * BS_MAX_Q + 1] = b.smin; o[2 * BS_MAX_Q + 2] = b.smax; o[2 * BS_MAX_Q + 3] = 0.0;
     }
   }
 }
@@ -653,10 +654,9 @@ bs_resolve_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __re
 // the first digit of the keys inside a bracket is histogrammed and all-reduced; every rank then
 // contributes the few keys of the buckets that hold the wanted ranks, and all ranks settle every
 // quantile alike from the gathered rows.  Four small collectives, one sweep of the data.
-constexpr int BS_BOUNDS_W = 2 * BS_MAX_Q + 3;    // per segment: lo[4], hi[4], sample size, smallest and largest sample value
 constexpr int BS_PACK_W = 4 + 3 * BS_MAX_Q + 2;  // sum, count, min, max | below, eq_lo, eq_hi | -0.0 count, overflow
 constexpr unsigned BS_ROWK = 1024;               // keys a rank can contribute per (segment, quantile)
-constexpr unsigned BS_ROW_W = 5 + BS_ROWK;       // count, (min, max) of either rank's bucket, keys
+constexpr unsigned BS_ROW_W = 5 + BS_ROWK + 1;   // count, (min, max) of either rank's bucket, keys, pad (rows stay multiples of 16 bytes)
 
 struct BsPick {                                  // per (segment, quantile): where its two ranks fall
   int zone[2];                                   // -1 empty segment, 0 fail, 1 lo, 2 inside, 3 hi
@@ -872,7 +872,7 @@ bs_pick1_kernel(BsSeg* __restrict__ segs, const unsigned long long* __restrict__
 // complemented so that zero is neutral for all four).
 __global__ void __launch_bounds__(1024)
 bs_pick2_rows_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __restrict__ lists, unsigned cap,
-                     const unsigned int* __restrict__ hist2, int n_q, BsPick* __restrict__ picks,
+                     const unsigned int* __restrict__ hist2, int n_hist, int64_t n_seg, int n_q, BsPick* __restrict__ picks,
                      unsigned long long* __restrict__ rows) {
   __shared__ unsigned int s_warp[32];
   __shared__ unsigned int s_bin[2];
@@ -888,8 +888,13 @@ bs_pick2_rows_kernel(const BsSeg* __restrict__ segs, const unsigned long long* _
   __syncthreads();
   for (int t = 0; t < 2; ++t) {
     if ((t ? z1 : z0) != 2) continue;                               // uniform
-    const unsigned int* h = hist2 + (((size_t)g * n_q + j) * 2 + t) * BS_BINS;
-    const unsigned c0 = h[2 * threadIdx.x], c1 = h[2 * threadIdx.x + 1];
+    // the second histograms: already summed (n_hist = 1: an all-reduce did it) or one copy per rank
+    unsigned c0 = 0, c1 = 0;
+    for (int w = 0; w < n_hist; ++w) {
+      const uint2 c = *reinterpret_cast<const uint2*>(hist2 + (size_t)w * n_seg * n_q * 2 * BS_BINS +
+                                                      (((size_t)g * n_q + j) * 2 + t) * BS_BINS + 2 * threadIdx.x);
+      c0 += c.x; c1 += c.y;
+    }
     const unsigned base = bs_scan2(c0, c1, s_warp);
     const unsigned long long r = t ? rb : ra;
     const unsigned b1st = t ? bin_b : bin_a;
@@ -1205,14 +1210,14 @@ int pmx_bsel_hist(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg
 }
 
 int pmx_bsel_rows(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg, int64_t n_q, const uint32_t* d_hist2,
-                  uint64_t* d_rows, pmx_stream stream) {
+                  int n_hist, uint64_t* d_rows, pmx_stream stream) {
   BS_COMMON_CHECKS();
-  PMX_REQUIRE(d_hist2 && d_rows, "NULL buffer");
+  PMX_REQUIRE(d_hist2 && d_rows && n_hist >= 1, "NULL buffer or bad histogram count");
   BsScratch S;
   if (int rc = bs_scratch(ctx, n_series, n_steps, n_seg, n_q, &S)) return rc;
   PMX_CUDA(cudaMemsetAsync(d_rows, 0, (size_t)n_seg * n_q * BS_ROW_W * 8, pmx_st(stream)));
   dim3 grid((unsigned)n_q * 4, (unsigned)n_seg);
-  bs_pick2_rows_kernel<<<grid, 1024, 0, pmx_st(stream)>>>(S.segs, S.lists, (unsigned)S.cap, d_hist2, (int)n_q, S.picks,
+  bs_pick2_rows_kernel<<<grid, 1024, 0, pmx_st(stream)>>>(S.segs, S.lists, (unsigned)S.cap, d_hist2, n_hist, n_seg, (int)n_q, S.picks,
                                                          (unsigned long long*)d_rows);
   PMX_LAUNCH_CHECK();
   return PMX_OK;

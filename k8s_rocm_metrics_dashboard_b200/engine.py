@@ -646,11 +646,19 @@ class Engine:
                                                self._ptr(b["bounds"]), self._stream()))
         self.launches += 2 if S > 0 and n_steps > 0 else 1
 
-    def summary_quantiles_ranks(self, x, seg, n_seg, qs, perm_goff, group, begun=False):
+    def bsel_region_bytes(self, n_seg, n_q):
+        """Bytes per rank of the four exchanges of ``summary_quantiles_ranks`` (for ``sharding.PeerExchange``)."""
+        b = self._bsel_buffers(n_seg, n_q, 1)
+        return {"bounds": b["bounds"].numel() * 8, "packed": b["packed"].numel() * 8, "hist2": b["hist2"].numel() * 4,
+                "rows": b["rows"].numel() * 8}
+
+    def summary_quantiles_ranks(self, x, seg, n_seg, qs, perm_goff, group, begun=False, peer=None):
         """``summary_quantiles`` over ALL ranks of ``group`` (every rank passes its own rows): five library
         calls with four small collectives between them (brackets; counters + partial summaries + first
         histogram; second histogram; the keys of the buckets that hold the wanted ranks), one sweep of
-        ``x`` on every rank.
+        ``x`` on every rank.  ``peer``: a ``sharding.PeerExchange`` with the regions of
+        ``bsel_region_bytes`` -- the exchanges then are stores into peer memory + a device-side barrier
+        instead of NCCL calls (and the second histograms are gathered and added by the next kernel).
         Returns ((sum, count, min, max, mean) over all ranks, quantiles dict, failed) -- ``failed`` is the
         same on every rank."""
         import ctypes as C
@@ -673,16 +681,32 @@ class Engine:
         lib, p, st = self.lib, self._ptr, self._stream
         if not begun:
             _abi.check(lib.pmx_bsel_begin(self.ctx, p(x), S, T, p(d_seg), n_seg, p(d_perm), p(d_goff), p(d_q), n_q, p(b["bounds"]), st()))
-        dist.all_gather_into_tensor(b["bounds_all"], b["bounds"], group=group)
-        _abi.check(lib.pmx_bsel_sweep(self.ctx, p(x), S, T, p(d_seg), n_seg, p(d_perm), p(d_goff), n_q, p(b["bounds_all"]), world,
+        if peer is not None:
+            bounds_all = peer.all_gather("bounds", b["bounds"])
+        else:
+            dist.all_gather_into_tensor(b["bounds_all"], b["bounds"], group=group)
+            bounds_all = b["bounds_all"]
+        _abi.check(lib.pmx_bsel_sweep(self.ctx, p(x), S, T, p(d_seg), n_seg, p(d_perm), p(d_goff), n_q, p(bounds_all), world,
                                       p(b["packed"]), st()))
-        dist.all_gather_into_tensor(b["packed_all"], b["packed"], group=group)
-        _abi.check(lib.pmx_bsel_hist(self.ctx, S, T, n_seg, p(d_q), n_q, p(b["packed_all"]), world, p(sm), p(cnt), p(mn), p(mx),
+        if peer is not None:
+            packed_all = peer.all_gather("packed", b["packed"])
+        else:
+            dist.all_gather_into_tensor(b["packed_all"], b["packed"], group=group)
+            packed_all = b["packed_all"]
+        _abi.check(lib.pmx_bsel_hist(self.ctx, S, T, n_seg, p(d_q), n_q, p(packed_all), world, p(sm), p(cnt), p(mn), p(mx),
                                      p(mean), p(b["hist2"]), st()))
-        dist.all_reduce(b["hist2"], op=dist.ReduceOp.SUM, group=group)
-        _abi.check(lib.pmx_bsel_rows(self.ctx, S, T, n_seg, n_q, p(b["hist2"]), p(b["rows"]), st()))
-        dist.all_gather_into_tensor(b["rows_all"], b["rows"], group=group)
-        _abi.check(lib.pmx_bsel_finish(self.ctx, S, T, n_seg, n_q, p(b["rows_all"]), world, p(cnt), p(outs["n"]), p(outs["lo"]),
+        if peer is not None:
+            hist2, n_hist = peer.all_gather("hist2", b["hist2"]), world
+        else:
+            dist.all_reduce(b["hist2"], op=dist.ReduceOp.SUM, group=group)
+            hist2, n_hist = b["hist2"], 1
+        _abi.check(lib.pmx_bsel_rows(self.ctx, S, T, n_seg, n_q, p(hist2), n_hist, p(b["rows"]), st()))
+        if peer is not None:
+            rows_all = peer.all_gather("rows", b["rows"])
+        else:
+            dist.all_gather_into_tensor(b["rows_all"], b["rows"], group=group)
+            rows_all = b["rows_all"]
+        _abi.check(lib.pmx_bsel_finish(self.ctx, S, T, n_seg, n_q, p(rows_all), world, p(cnt), p(outs["n"]), p(outs["lo"]),
                                        p(outs["hi"]), p(outs["x_lo"]), p(outs["x_hi"]), p(outs["value"]), p(failed), st()))
         # sample, bounds | merge, sweep, fold + pack, histogram | pick, histogram | pick | final
         self.launches += (10 if S > 0 and T > 0 else 7) - (0 if not begun else (2 if S > 0 and T > 0 else 1))

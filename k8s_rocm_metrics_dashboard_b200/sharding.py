@@ -96,11 +96,60 @@ def distributed_quantiles(hist_fn, pick_fn, finish_fn, n_seg, n_q, group=None, p
     return finish_fn()
 
 
+class PeerExchange:
+    """All-gathers of a few hundred KiB as stores into peer memory (``pmx_peer_put``) followed by a
+    device-side barrier, instead of NCCL calls of 20-40 us fixed latency each.  Every rank's receive
+    buffer is symmetric memory (``torch.distributed._symmetric_memory``): CUDA VMM handles are
+    exchanged once at construction, after that a rank "sends" by storing its block into slot ``rank``
+    of every rank's buffer over NVLink.  Every named exchange has a region of its own; one step uses
+    each region once, and a rank that starts the next step has passed this step's last barrier, so a
+    region is never written while another rank still reads it.  Construction raises when symmetric
+    memory cannot be set up (callers then stay with NCCL)."""
+
+    def __init__(self, engine, group, regions):
+        """``regions``: {name: bytes per rank}."""
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        t = engine.torch
+        self.eng, self.group = engine, group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.off, total = {}, 0
+        for name, nbytes in regions.items():
+            nbytes = (int(nbytes) + 15) & ~15
+            self.off[name] = (total, nbytes)
+            total += self.world * nbytes
+        self.buf = symm.empty(total, dtype=t.uint8, device=engine.device)
+        self.hdl = symm.rendezvous(self.buf, group)
+        self.peers = t.tensor([int(p) for p in self.hdl.buffer_ptrs], dtype=t.int64, device=engine.device)
+        self.channel = {name: i for i, name in enumerate(regions)}
+
+    def all_gather(self, name, src):
+        """``src``: contiguous device tensor of this region's size (or smaller, a multiple of 16 bytes).  Returns
+        the gathered blocks, rank-major, as a tensor of ``src``'s dtype viewing this rank's buffer."""
+        t = self.eng.torch
+        off, cap = self.off[name]
+        nbytes = src.numel() * src.element_size()
+        if nbytes > cap or nbytes % 16:
+            raise ValueError(f"PeerExchange.all_gather({name}): {nbytes} bytes do not fit the region of {cap} (multiples of 16)")
+        _abi_check(self.eng.lib.pmx_peer_put(self.eng._ptr(src), self.eng._ptr(self.peers), self.world, self.rank, off, nbytes,
+                                             self.eng._stream()))
+        self.hdl.barrier(channel=self.channel[name])
+        self.eng.launches += 1
+        return self.buf[off:off + self.world * nbytes].view(src.dtype)
+
+
+def _abi_check(rc):
+    from . import _abi
+    _abi.check(rc)
+
+
 class ShardedEngine:
     """Engine + process group: the aggregate step on this rank's shard with cluster-wide summaries."""
 
-    def __init__(self, engine, group=None, local_only=False):
-        """``local_only``: behave as one rank whatever the process group says (no exchange)."""
+    def __init__(self, engine, group=None, local_only=False, peer_exchange=True):
+        """``local_only``: behave as one rank whatever the process group says (no exchange).
+        ``peer_exchange``: several ranks exchange through peer memory (``PeerExchange``) where symmetric
+        memory is available; False keeps the NCCL calls."""
         import torch.distributed as dist
         self.eng = engine
         self.group = group
@@ -109,6 +158,8 @@ class ShardedEngine:
         self.rank = 0 if alone else dist.get_rank(group)
         self._qbuf = {}
         self._graphs = {}
+        self._peers = {}
+        self.peer_exchange = peer_exchange
 
     # The one-sweep selection spends a cluster of CTAs per segment on the brackets and another per
     # (segment, level) on the last keys, ~40 us each whatever the segment holds: it pays for long
@@ -121,6 +172,26 @@ class ShardedEngine:
         if self.world > 1:
             return 0 < n_seg <= 64
         return n_seg > 0 and n_series * n_steps >= n_seg * self.ONE_SWEEP_MIN_VALUES_PER_SEGMENT
+
+    def _peer(self, n_seg, n_q):
+        """The peer-memory exchange for this shape, set up at first use (a collective: every rank calls it at the
+        same point); None -- on every rank alike -- where symmetric memory is not available: NCCL then."""
+        key = (n_seg, n_q)
+        if not self.peer_exchange:
+            return None
+        if key not in self._peers:
+            import torch.distributed as dist
+            t = self.eng.torch
+            group = self.group or _world_group()
+            peer = None
+            try:
+                peer = PeerExchange(self.eng, group, self.eng.bsel_region_bytes(n_seg, n_q))
+            except Exception:  # noqa: BLE001  -- no symmetric memory here
+                peer = None
+            ok = t.tensor([1 if peer is not None else 0], dtype=t.int32, device=self.eng.device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+            self._peers[key] = peer if int(ok.item()) == 1 else None
+        return self._peers[key]
 
     @staticmethod
     def _qsummary(summary):
@@ -142,7 +213,7 @@ class ShardedEngine:
                 summary, q, failed = eng.summary_quantiles(x, seg, n_seg, qs, perm_goff, brackets_ready=brackets_ready)
             else:                                       # ``failed`` is the same on every rank: they fall back together
                 summary, q, failed = eng.summary_quantiles_ranks(x, seg, n_seg, qs, perm_goff, self.group or _world_group(),
-                                                                 begun=brackets_ready)
+                                                                 begun=brackets_ready, peer=self._peer(n_seg, len(qs)))
             if _unchecked:
                 return summary, q, failed
             if defer_check:

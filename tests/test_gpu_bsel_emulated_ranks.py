@@ -16,7 +16,7 @@ from tests.util import assert_bits_equal
 pytestmark = pytest.mark.gpu
 
 
-def _run_ranks(engines, shards, gids, M, qs):
+def _run_ranks(engines, shards, gids, M, qs, gathered_hist=False):
     """shards[r]: [S_r, T] host matrix of rank r (S_r may be 0); returns per rank (summary, q, failed)."""
     t = engines[0].torch
     W, n_q = len(engines), len(qs)
@@ -51,11 +51,14 @@ def _run_ranks(engines, shards, gids, M, qs):
         _abi.check(e.lib.pmx_bsel_hist(e.ctx, s["x"].shape[0], T, M, p(e, s["q"]), n_q, p(e, packed_all), W, p(e, sm), p(e, cnt),
                                        p(e, mn), p(e, mx), p(e, mean), p(e, s["hist2"]), e._stream()))
         res.append([(sm, cnt, mn, mx, mean)])
-    hist2 = st[0]["hist2"].clone()
-    for s in st[1:]:
-        hist2 += s["hist2"]
+    if gathered_hist:                                              # all-gather: the rows call adds the copies
+        hist2, n_hist = t.cat([s["hist2"] for s in st]), W
+    else:                                                          # all-reduce
+        hist2, n_hist = st[0]["hist2"].clone(), 1
+        for s in st[1:]:
+            hist2 += s["hist2"]
     for e, s in zip(engines, st):
-        _abi.check(e.lib.pmx_bsel_rows(e.ctx, s["x"].shape[0], T, M, n_q, p(e, hist2), p(e, s["rows"]), e._stream()))
+        _abi.check(e.lib.pmx_bsel_rows(e.ctx, s["x"].shape[0], T, M, n_q, p(e, hist2), n_hist, p(e, s["rows"]), e._stream()))
     rows_all = t.cat([s["rows"] for s in st])
     for e, s, r in zip(engines, st, res):
         outs = {"n": t.empty(M, dtype=t.int64, device=e.device), "lo": t.empty((M, n_q), dtype=t.int64, device=e.device),
@@ -111,7 +114,7 @@ def test_ranks_with_different_distributions(eng, ranks):
     lo = rng.normal(10.0, 1.0, (16, T)); hi = rng.normal(50.0, 5.0, (24, T))
     shards = [lo, np.zeros((0, T)), hi]
     gids = [(np.arange(16) % M).astype(np.int32), np.zeros(0, dtype=np.int32), (np.arange(24) % M).astype(np.int32)]
-    res = _run_ranks(ranks, shards, gids, M, QS)
+    res = _run_ranks(ranks, shards, gids, M, QS, gathered_hist=True)
     x = np.concatenate([lo, hi]); gid = np.concatenate([gids[0], gids[2]])
     for summ, q, failed in res:
         assert failed == 0

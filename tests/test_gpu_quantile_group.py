@@ -90,3 +90,28 @@ def test_bracket_selection_over_ranks_equals_one_sweep(eng, world1, kind):
     s1, q1, f1 = eng.summary_quantiles(dx, seg, M, QS, pg)
     assert int(f1.item()) == 0
     _same(summ, q, s1, q1, f"ranks vs one sweep {kind}")
+
+
+def test_peer_memory_exchange_on_a_one_rank_group(eng, world1):
+    """sharding.PeerExchange (stores into symmetric memory + device-side barrier instead of NCCL all-gathers)
+    under Engine.summary_quantiles_ranks: same results as with the NCCL calls.  One rank here; the N > 1 runs
+    are tests/multi_gpu_check.py and bench.py's parity_check."""
+    from k8s_rocm_metrics_dashboard_b200 import sharding
+    from tests.test_gpu_summary_quantiles import QS, _data, _same
+    t = eng.torch
+    rng = np.random.default_rng(900)
+    S, T, M = 48, 3000, 4
+    x = _data("uniform", S, T, rng)
+    gid = (np.arange(S) % M).astype(np.int32)
+    perm, goff = group_index(gid, M)
+    pg = (t.as_tensor(perm, device=eng.device), t.as_tensor(goff, device=eng.device))
+    dx, seg = t.as_tensor(x, device=eng.device), t.as_tensor(gid, device=eng.device)
+    try:
+        peer = sharding.PeerExchange(eng, world1, eng.bsel_region_bytes(M, len(QS)))
+    except Exception as e:  # noqa: BLE001
+        pytest.skip(f"symmetric memory not available here: {e}")
+    for _ in range(3):                                             # the regions are reused step after step
+        s1, q1, f1 = eng.summary_quantiles_ranks(dx, seg, M, QS, pg, world1, peer=peer)
+    s0, q0, f0 = eng.summary_quantiles_ranks(dx, seg, M, QS, pg, world1)
+    assert int(f1.item()) == 0 and int(f0.item()) == 0
+    _same(s1, q1, s0, q0, "peer exchange vs NCCL")
