@@ -704,14 +704,15 @@ __global__ void bs_merge_bounds_kernel(const double* __restrict__ all, int world
   segs[g].gmin = gmin; segs[g].gmax = gmax;
 }
 
-// one warp per segment: fold this rank's per-series partials (the order of pmx_group_reduce), then pack
-__global__ void __launch_bounds__(128)
-bs_pack_kernel(const BsSeg* __restrict__ segs, const Part* __restrict__ part, const int32_t* __restrict__ perm,
-               const int64_t* __restrict__ goff, double* __restrict__ sum, int64_t* __restrict__ cnt,
-               double* __restrict__ mn, double* __restrict__ mx, int64_t n_seg, unsigned cap,
-               unsigned long long* __restrict__ out) {
-  const int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (g >= n_seg) return;
+// one warp folds this rank's per-series partials of segment g (the order of pmx_group_reduce), then packs
+struct BsPackArgs {
+  const Part* part; const int32_t* perm; const int64_t* goff; double* sum; int64_t* cnt; double* mn; double* mx;
+  unsigned cap; unsigned long long* out;
+};
+__device__ __forceinline__ void bs_fold_pack_warp(const BsSeg* __restrict__ segs, const BsPackArgs& A, int64_t g) {
+  const Part* part = A.part; const int32_t* perm = A.perm; const int64_t* goff = A.goff;
+  double* sum = A.sum; int64_t* cnt = A.cnt; double* mn = A.mn; double* mx = A.mx;
+  const unsigned cap = A.cap; unsigned long long* out = A.out;
   group_fold_warp(part, perm, goff, g, threadIdx.x & 31, sum, cnt, mn, mx, nullptr);
   if ((threadIdx.x & 31) != 0) return;           // lane 0 wrote the fold's results and reads them back
   const double INF = __longlong_as_double(0x7FF0000000000000LL);
@@ -734,9 +735,15 @@ bs_pack_kernel(const BsSeg* __restrict__ segs, const Part* __restrict__ part, co
 template <bool SECOND>
 __global__ void __launch_bounds__(1024)
 bs_midhist_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __restrict__ lists, unsigned cap, int n_q,
-                  const BsPick* __restrict__ picks, unsigned int* __restrict__ hist) {
+                  const BsPick* __restrict__ picks, unsigned int* __restrict__ hist, const BsPackArgs pack) {
   __shared__ unsigned int sh[(SECOND ? 2 : 1) * BS_BINS];
   const int j = blockIdx.x >> 2, quarter = blockIdx.x & 3, g = blockIdx.y;
+  if (!SECOND && j == n_q) {
+    // one more block per segment (first histogram only): its first warp folds and packs this rank's
+    // partial summary and counters while the others histogram -- no launch and no time of its own
+    if (quarter == 0 && threadIdx.x < 32) bs_fold_pack_warp(segs, pack, g);
+    return;
+  }
   const BsSeg& B = segs[g];
   const double lo = B.lo[j], hi = B.hi[j];
   const BsGeom G = bs_digit_geom(B, j);
@@ -1177,15 +1184,13 @@ int pmx_bsel_sweep(pmx_ctx* ctx, const double* d_x, int64_t n_series, int64_t n_
   bs_merge_bounds_kernel<<<(unsigned)((n_seg + 127) / 128), 128, 0, st>>>(d_bounds_all, n_ranks, n_seg, (int)n_q, S.segs);
   PMX_LAUNCH_CHECK();
   if (int rc = bs_launch_sweep(S, d_x, n_series, n_steps, d_seg, n_q, st)) return rc;
-  bs_pack_kernel<<<(unsigned)((n_seg + 3) / 4), 128, 0, st>>>(S.segs, S.part, d_perm, d_goff, S.f_sum, S.f_cnt, S.f_min, S.f_max, n_seg,
-                                                              (unsigned)S.cap, (unsigned long long*)d_packed);
-  PMX_LAUNCH_CHECK();
   // first digit of this rank's keys inside every bracket, behind the packed words (it needs only the
   // brackets and the sample range, so it travels with the counters)
   unsigned int* h1 = (unsigned int*)(d_packed + (size_t)n_seg * BS_PACK_W);
   PMX_CUDA(cudaMemsetAsync(h1, 0, (size_t)n_seg * n_q * BS_BINS * sizeof(unsigned int), st));
-  dim3 grid((unsigned)n_q * 4, (unsigned)n_seg);
-  bs_midhist_kernel<false><<<grid, 1024, 0, st>>>(S.segs, S.lists, (unsigned)S.cap, (int)n_q, nullptr, h1);
+  dim3 grid((unsigned)n_q * 4 + 1, (unsigned)n_seg);            // + one block per segment that folds and packs
+  const BsPackArgs pack{S.part, d_perm, d_goff, S.f_sum, S.f_cnt, S.f_min, S.f_max, (unsigned)S.cap, (unsigned long long*)d_packed};
+  bs_midhist_kernel<false><<<grid, 1024, 0, st>>>(S.segs, S.lists, (unsigned)S.cap, (int)n_q, nullptr, h1, pack);
   PMX_LAUNCH_CHECK();
   return PMX_OK;
 }
@@ -1204,7 +1209,7 @@ int pmx_bsel_hist(pmx_ctx* ctx, int64_t n_series, int64_t n_steps, int64_t n_seg
   PMX_LAUNCH_CHECK();
   PMX_CUDA(cudaMemsetAsync(d_hist2, 0, (size_t)n_seg * n_q * 2 * BS_BINS * sizeof(uint32_t), st));
   dim3 grid4((unsigned)n_q * 4, (unsigned)n_seg);
-  bs_midhist_kernel<true><<<grid4, 1024, 0, st>>>(S.segs, S.lists, (unsigned)S.cap, (int)n_q, S.picks, d_hist2);
+  bs_midhist_kernel<true><<<grid4, 1024, 0, st>>>(S.segs, S.lists, (unsigned)S.cap, (int)n_q, S.picks, d_hist2, BsPackArgs{});
   PMX_LAUNCH_CHECK();
   return PMX_OK;
 }

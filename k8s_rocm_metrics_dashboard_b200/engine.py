@@ -708,8 +708,8 @@ class Engine:
             rows_all = b["rows_all"]
         _abi.check(lib.pmx_bsel_finish(self.ctx, S, T, n_seg, n_q, p(rows_all), world, p(cnt), p(outs["n"]), p(outs["lo"]),
                                        p(outs["hi"]), p(outs["x_lo"]), p(outs["x_hi"]), p(outs["value"]), p(failed), st()))
-        # sample, bounds | merge, sweep, fold + pack, histogram | pick, histogram | pick | final
-        self.launches += (10 if S > 0 and T > 0 else 7) - (0 if not begun else (2 if S > 0 and T > 0 else 1))
+        # sample, bounds | merge, sweep, histogram (+ fold and pack) | pick, histogram | pick | final
+        self.launches += (9 if S > 0 and T > 0 else 6) - (0 if not begun else (2 if S > 0 and T > 0 else 1))
         return (sm, cnt, mn, mx, mean), outs, failed
 
     def defer_flag(self, counter):
