@@ -652,13 +652,40 @@ class Engine:
         return {"bounds": b["bounds"].numel() * 8, "packed": b["packed"].numel() * 8, "hist2": b["hist2"].numel() * 4,
                 "rows": b["rows"].numel() * 8}
 
-    def summary_quantiles_ranks(self, x, seg, n_seg, qs, perm_goff, group, begun=False, peer=None):
+    def _stage(self, cache, key, fn):
+        """Run ``fn`` (a fixed sequence of kernel launches on fixed buffers, no collective inside): eagerly
+        twice, then captured into a CUDA graph and replayed -- the launches between two exchanges are
+        launch-bound.  Stays eager if the capture is refused."""
+        t = self.torch
+        ent = cache.setdefault(key, [0, None])
+        if ent[1] is not None:
+            ent[1].replay()
+            return
+        if ent[0] != 2:
+            fn()
+            ent[0] += 1
+            return
+        try:
+            g = t.cuda.CUDAGraph()
+            with t.cuda.graph(g, capture_error_mode="thread_local"):
+                fn()
+            ent[1] = g
+            g.replay()
+        except Exception:  # noqa: BLE001
+            t.cuda.synchronize()
+            ent[0] = 3                                         # never again
+            fn()
+
+    def summary_quantiles_ranks(self, x, seg, n_seg, qs, perm_goff, group, begun=False, peer=None, stage_graphs=False):
         """``summary_quantiles`` over ALL ranks of ``group`` (every rank passes its own rows): five library
         calls with four small collectives between them (brackets; counters + partial summaries + first
         histogram; second histogram; the keys of the buckets that hold the wanted ranks), one sweep of
         ``x`` on every rank.  ``peer``: a ``sharding.PeerExchange`` with the regions of
         ``bsel_region_bytes`` -- the exchanges then are stores into peer memory + a device-side barrier
         instead of NCCL calls (and the second histograms are gathered and added by the next kernel).
+        ``stage_graphs``: ``x``, ``seg`` and ``perm_goff`` are the same device tensors on every call; the
+        launches between two exchanges are then replayed from CUDA graphs and the results live in buffers
+        that the next call overwrites.
         Returns ((sum, count, min, max, mean) over all ranks, quantiles dict, failed) -- ``failed`` is the
         same on every rank."""
         import ctypes as C
@@ -672,13 +699,31 @@ class Engine:
         d_q = self._quantile_levels(qs)
         world = dist.get_world_size(group)
         b = self._bsel_buffers(n_seg, n_q, world)
-        sm, mn, mx, mean = (self._empty((n_seg,), t.float64) for _ in range(4))
-        cnt = self._empty((n_seg,), t.int64)
-        outs = {"n": self._empty((n_seg,), t.int64), "lo": self._empty((n_seg, n_q), t.int64),
-                "hi": self._empty((n_seg, n_q), t.int64), "x_lo": self._empty((n_seg, n_q), t.float64),
-                "x_hi": self._empty((n_seg, n_q), t.float64), "value": self._empty((n_seg, n_q), t.float64)}
-        failed = self._empty((1,), t.int32)
+
+        def results():
+            return {"sm": self._empty((n_seg,), t.float64), "mn": self._empty((n_seg,), t.float64),
+                    "mx": self._empty((n_seg,), t.float64), "mean": self._empty((n_seg,), t.float64),
+                    "cnt": self._empty((n_seg,), t.int64), "failed": self._empty((1,), t.int32),
+                    "outs": {"n": self._empty((n_seg,), t.int64), "lo": self._empty((n_seg, n_q), t.int64),
+                             "hi": self._empty((n_seg, n_q), t.int64), "x_lo": self._empty((n_seg, n_q), t.float64),
+                             "x_hi": self._empty((n_seg, n_q), t.float64), "value": self._empty((n_seg, n_q), t.float64)}}
+        gkey = None
+        if stage_graphs:
+            gkey = (x.data_ptr(), S, T, d_seg.data_ptr(), d_perm.data_ptr(), d_goff.data_ptr(), n_seg, tuple(qs), world, peer is not None)
+            graphs = b.setdefault("graphs", {})
+            if ("res", gkey) not in graphs:
+                graphs[("res", gkey)] = results()
+            R = graphs[("res", gkey)]
+        else:
+            R = results()
+        sm, mn, mx, mean, cnt, failed, outs = R["sm"], R["mn"], R["mx"], R["mean"], R["cnt"], R["failed"], R["outs"]
         lib, p, st = self.lib, self._ptr, self._stream
+
+        def stage(name, fn):
+            if gkey is None:
+                fn()
+            else:
+                self._stage(b["graphs"], (name, gkey), fn)
         if not begun:
             _abi.check(lib.pmx_bsel_begin(self.ctx, p(x), S, T, p(d_seg), n_seg, p(d_perm), p(d_goff), p(d_q), n_q, p(b["bounds"]), st()))
         if peer is not None:
@@ -686,28 +731,29 @@ class Engine:
         else:
             dist.all_gather_into_tensor(b["bounds_all"], b["bounds"], group=group)
             bounds_all = b["bounds_all"]
-        _abi.check(lib.pmx_bsel_sweep(self.ctx, p(x), S, T, p(d_seg), n_seg, p(d_perm), p(d_goff), n_q, p(bounds_all), world,
-                                      p(b["packed"]), st()))
+        stage("sweep", lambda: _abi.check(lib.pmx_bsel_sweep(self.ctx, p(x), S, T, p(d_seg), n_seg, p(d_perm), p(d_goff), n_q,
+                                                             p(bounds_all), world, p(b["packed"]), st())))
         if peer is not None:
             packed_all = peer.all_gather("packed", b["packed"])
         else:
             dist.all_gather_into_tensor(b["packed_all"], b["packed"], group=group)
             packed_all = b["packed_all"]
-        _abi.check(lib.pmx_bsel_hist(self.ctx, S, T, n_seg, p(d_q), n_q, p(packed_all), world, p(sm), p(cnt), p(mn), p(mx),
-                                     p(mean), p(b["hist2"]), st()))
+        stage("hist", lambda: _abi.check(lib.pmx_bsel_hist(self.ctx, S, T, n_seg, p(d_q), n_q, p(packed_all), world, p(sm), p(cnt),
+                                                           p(mn), p(mx), p(mean), p(b["hist2"]), st())))
         if peer is not None:
             hist2, n_hist = peer.all_gather("hist2", b["hist2"]), world
         else:
             dist.all_reduce(b["hist2"], op=dist.ReduceOp.SUM, group=group)
             hist2, n_hist = b["hist2"], 1
-        _abi.check(lib.pmx_bsel_rows(self.ctx, S, T, n_seg, n_q, p(hist2), n_hist, p(b["rows"]), st()))
+        stage("rows", lambda: _abi.check(lib.pmx_bsel_rows(self.ctx, S, T, n_seg, n_q, p(hist2), n_hist, p(b["rows"]), st())))
         if peer is not None:
             rows_all = peer.all_gather("rows", b["rows"])
         else:
             dist.all_gather_into_tensor(b["rows_all"], b["rows"], group=group)
             rows_all = b["rows_all"]
-        _abi.check(lib.pmx_bsel_finish(self.ctx, S, T, n_seg, n_q, p(rows_all), world, p(cnt), p(outs["n"]), p(outs["lo"]),
-                                       p(outs["hi"]), p(outs["x_lo"]), p(outs["x_hi"]), p(outs["value"]), p(failed), st()))
+        stage("finish", lambda: _abi.check(lib.pmx_bsel_finish(self.ctx, S, T, n_seg, n_q, p(rows_all), world, p(cnt), p(outs["n"]),
+                                                               p(outs["lo"]), p(outs["hi"]), p(outs["x_lo"]), p(outs["x_hi"]),
+                                                               p(outs["value"]), p(failed), st())))
         # sample, bounds | merge, sweep, histogram (+ fold and pack) | pick, histogram | pick | final
         self.launches += (9 if S > 0 and T > 0 else 6) - (0 if not begun else (2 if S > 0 and T > 0 else 1))
         return (sm, cnt, mn, mx, mean), outs, failed

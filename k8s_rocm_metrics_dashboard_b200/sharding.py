@@ -199,7 +199,7 @@ class ShardedEngine:
         return summary[1], summary[2], summary[3]
 
     def summarize(self, x, seg, n_seg, perm_goff, qs=(0.5, 0.95, 0.99), defer_check=False, _unchecked=False,
-                  brackets_ready=False):
+                  brackets_ready=False, stage_graphs=False):
         """Per-segment sum / count / min / max / mean and exact quantiles of the [S, T] device matrix ``x`` over
         ALL ranks (every rank calls this with its own rows; S may be 0).  Returns (summary, quantiles).
         One rank and at most four levels: one sweep of ``x`` (``Engine.summary_quantiles``); its brackets
@@ -213,7 +213,8 @@ class ShardedEngine:
                 summary, q, failed = eng.summary_quantiles(x, seg, n_seg, qs, perm_goff, brackets_ready=brackets_ready)
             else:                                       # ``failed`` is the same on every rank: they fall back together
                 summary, q, failed = eng.summary_quantiles_ranks(x, seg, n_seg, qs, perm_goff, self.group or _world_group(),
-                                                                 begun=brackets_ready, peer=self._peer(n_seg, len(qs)))
+                                                                 begun=brackets_ready, peer=self._peer(n_seg, len(qs)),
+                                                                 stage_graphs=stage_graphs)
             if _unchecked:
                 return summary, q, failed
             if defer_check:
@@ -315,7 +316,9 @@ class ShardedEngine:
         if graph and self.world == 1 and host is None:
             summary, q = self.summarize_graph(out["aligned"], seg, n_seg, perm_goff, qs, defer_check=defer_check, brackets_ready=pre)
         else:
-            summary, q = self.summarize(out["aligned"], seg, n_seg, perm_goff, qs, defer_check, brackets_ready=pre)
+            # several ranks with ``graph``: the launches between two exchanges are replayed from graphs
+            summary, q = self.summarize(out["aligned"], seg, n_seg, perm_goff, qs, defer_check, brackets_ready=pre,
+                                        stage_graphs=graph and self.world > 1 and host is None)
         return out, summary, q
 
 

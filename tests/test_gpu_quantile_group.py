@@ -115,3 +115,26 @@ def test_peer_memory_exchange_on_a_one_rank_group(eng, world1):
     s0, q0, f0 = eng.summary_quantiles_ranks(dx, seg, M, QS, pg, world1)
     assert int(f1.item()) == 0 and int(f0.item()) == 0
     _same(s1, q1, s0, q0, "peer exchange vs NCCL")
+
+
+def test_stage_graphs_of_the_several_rank_selection(eng, world1):
+    """stage_graphs=True: the launches between two exchanges replayed from CUDA graphs (captured on the third
+    call) give the eager results, also after the matrix was refilled in place."""
+    from tests.test_gpu_summary_quantiles import QS, _data, _same
+    t = eng.torch
+    S, T, M = 48, 3000, 4
+    gid = (np.arange(S) % M).astype(np.int32)
+    perm, goff = group_index(gid, M)
+    pg = (t.as_tensor(perm, device=eng.device), t.as_tensor(goff, device=eng.device))
+    seg = t.as_tensor(gid, device=eng.device)
+    dx = t.empty((S, T), dtype=t.float64, device=eng.device)
+    for it, kind in enumerate(["uniform", "integers", "counters", "zeros", "uniform"]):
+        x = _data(kind, S, T, np.random.default_rng(950 + it))
+        dx.copy_(t.as_tensor(x, device=eng.device))
+        s1, q1, f1 = eng.summary_quantiles_ranks(dx, seg, M, QS, pg, world1, stage_graphs=True)
+        got_s = [v.clone() for v in s1]; got_q = {k: v.clone() for k, v in q1.items()}
+        s0, q0, f0 = eng.summary_quantiles_ranks(dx, seg, M, QS, pg, world1)
+        assert int(f1.item()) == 0 and int(f0.item()) == 0
+        _same(got_s, got_q, s0, q0, f"stage graphs, call {it} ({kind})")
+    graphs = [v for k, v in eng._bsel[(M, len(QS), 1)]["graphs"].items() if k[0] != "res"]
+    assert graphs and all(g[1] is not None for g in graphs), "a stage was not captured"
