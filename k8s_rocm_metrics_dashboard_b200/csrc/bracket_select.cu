@@ -650,10 +650,11 @@ bs_resolve_kernel(const BsSeg* __restrict__ segs, const unsigned long long* __re
 // ------------------------------------------------------------------------------------------------
 // Several ranks (one process per GPU, rows sharded): every rank samples its own rows and proposes
 // brackets; the hull of the proposals (the global quantile lies between the smallest and the largest
-// local one) is what all ranks sweep with; counters and summary partials are combined in rank order;
-// the first digit of the keys inside a bracket is histogrammed and all-reduced; every rank then
-// contributes the few keys of the buckets that hold the wanted ranks, and all ranks settle every
-// quantile alike from the gathered rows.  Four small collectives, one sweep of the data.
+// local one) is what all ranks sweep with; counters, summary partials and the first digit's histogram
+// of the keys inside every bracket are gathered and combined in rank order; the second digit's
+// histograms are summed; every rank then contributes the few keys of the 22-bit buckets that hold
+// the wanted ranks, and all ranks settle every quantile alike from the gathered rows.  Four small
+// exchanges (NCCL calls, or stores into peer memory: peer.cu), one sweep of the data.
 constexpr int BS_PACK_W = 4 + 3 * BS_MAX_Q + 2;  // sum, count, min, max | below, eq_lo, eq_hi | -0.0 count, overflow
 constexpr unsigned BS_ROWK = 1024;               // keys a rank can contribute per (segment, quantile)
 constexpr unsigned BS_ROW_W = 5 + BS_ROWK + 1;   // count, (min, max) of either rank's bucket, keys, pad (rows stay multiples of 16 bytes)

@@ -115,16 +115,6 @@ __global__ void group_combine_kernel(const double* __restrict__ all, int world, 
 
 }  // namespace
 
-int pmx_internal_group_fold(const Part* part, const int32_t* d_perm, const int64_t* d_goff, int64_t n_groups,
-                            double* d_sum, int64_t* d_count, double* d_min, double* d_max, double* d_mean,
-                            cudaStream_t st) {
-  if (n_groups <= 0) return PMX_OK;
-  group_fold_kernel<<<(unsigned)((n_groups + 3) / 4), 128, 0, st>>>(part, d_perm, d_goff, n_groups, d_sum, d_count,
-                                                                      d_min, d_max, d_mean);
-  PMX_LAUNCH_CHECK();
-  return PMX_OK;
-}
-
 extern "C" {
 
 int pmx_group_index(const int32_t* h_group_id, int64_t n_series, int64_t n_groups, int32_t* h_perm,

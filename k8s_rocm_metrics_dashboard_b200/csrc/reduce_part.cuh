@@ -125,8 +125,3 @@ __device__ __forceinline__ void group_fold_warp(const Part* __restrict__ part, c
 
 // threads of a CTA that walks one row (series_partial_kernel and bs_sweep_kernel: the same walk)
 constexpr int PMX_ROW_THREADS = 128;
-
-// launches group_fold_kernel (reduce.cu): per group, fold part[perm[k]] in CSR order
-int pmx_internal_group_fold(const Part* part, const int32_t* d_perm, const int64_t* d_goff, int64_t n_groups,
-                            double* d_sum, int64_t* d_count, double* d_min, double* d_max, double* d_mean,
-                            cudaStream_t st);
