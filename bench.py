@@ -253,7 +253,7 @@ def config3_block(eng, sh, world, rank, barrier, steps=5):
         def one():
             engine_like.aggregate_step(ts, val, off, START_MS, STEP_MS, T3, WINDOW_STEPS, seg, M3, pg, QS, out=out,
                                        lookback_ms=LOOKBACK_MS, defer_check=True, graph=True)
-        for _ in range(2):
+        for _ in range(4):                                       # the graphs of the step are captured on the third call
             one()
         barrier()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
