@@ -257,6 +257,11 @@ int pmx_where_gt(pmx_ctx* ctx, const double* d_x, int64_t n, double threshold, d
  * to d_out_*[d_off[s] ..): a CSR that pmx_fused_align_rolling_rate takes as it is. */
 int pmx_slab_tail_lengths(pmx_ctx* ctx, const int64_t* d_ts, const int64_t* d_count, int64_t n_series, int64_t cap,
                           int64_t threshold_ms, int64_t* d_first, int64_t* d_len, pmx_stream stream);
+/* pmx_slab_tail_lengths and the cumulative sum in one launch: d_first[s] as above, d_off[0 .. n_series] =
+ * exclusive sums of the tail lengths (the CSR offsets pmx_slab_tail_gather and the fused kernel take).
+ * d_work: one uint32 that is zero before the first call; the call leaves it zero. */
+int pmx_slab_tail_offsets(pmx_ctx* ctx, const int64_t* d_ts, const int64_t* d_count, int64_t n_series, int64_t cap,
+                          int64_t threshold_ms, int64_t* d_first, int64_t* d_off, uint32_t* d_work, pmx_stream stream);
 int pmx_slab_tail_gather(pmx_ctx* ctx, const int64_t* d_ts, const double* d_val, const int64_t* d_first,
                          const int64_t* d_off, int64_t n_series, int64_t cap, int64_t* d_out_ts, double* d_out_val,
                          pmx_stream stream);

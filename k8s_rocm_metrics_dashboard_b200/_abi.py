@@ -75,6 +75,7 @@ SIGNATURES = {
     "pmx_ratio_pct": (_int, [_p, _p, _i64, _p, _i64, _i64, _p, _i64, _p, _p]),
     "pmx_where_gt": (_int, [_p, _p, _i64, C.c_double, _p, _p]),
     "pmx_slab_tail_lengths": (_int, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p]),
+    "pmx_slab_tail_offsets": (_int, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p, _p]),
     "pmx_slab_tail_gather": (_int, [_p, _p, _p, _p, _p, _i64, _i64, _p, _p, _p]),
     "pmx_slab_append": (_int, [_p, _p, _p, _p, _i64, _p, _p, _p, _p, _i64, _i64, _p, _p, _p]),
     "pmx_csr_copy": (_int, [_p, _p, _p, _p, _p, _i64, _p, _p, _p]),

@@ -134,15 +134,15 @@ class SeriesCache:
         g0 = self.start_ms + a * self.step_ms
         S = self._rows
         # a sample can serve a grid point >= g0 only if it is newer than g0 - lookback: the tails of
-        # the slab rows from there on, gathered into one CSR (two kernels and a cumulative sum; the
+        # the slab rows from there on, gathered into one CSR (two kernels; the
         # compact buffers are sized for full rows, so no count has to come back to the host)
         from . import _abi
         p = eng._ptr
-        first, lens = eng._empty((S,), t.int64), eng._empty((S,), t.int64)
-        _abi.check(eng.lib.pmx_slab_tail_lengths(eng.ctx, p(self.ts), p(self.cnt), S, self.cap, g0 - self.lookback_ms,
-                                                 p(first), p(lens), eng._stream()))
-        off = t.zeros((S + 1,), dtype=t.int64, device=dev)
-        t.cumsum(lens, 0, out=off[1:])
+        first, off = eng._empty((S,), t.int64), eng._empty((S + 1,), t.int64)
+        if getattr(self, "_tail_work", None) is None:
+            self._tail_work = t.zeros((1,), dtype=t.int32, device=dev)
+        _abi.check(eng.lib.pmx_slab_tail_offsets(eng.ctx, p(self.ts), p(self.cnt), S, self.cap, g0 - self.lookback_ms,
+                                                 p(first), p(off), p(self._tail_work), eng._stream()))
         if getattr(self, "_compact_rows", 0) < S:
             self._ts_c, self._val_c = eng._empty((S * self.cap,), t.int64), eng._empty((S * self.cap,), t.float64)
             self._compact_rows = S

@@ -4,6 +4,7 @@
 //   pmx_slab_tail_lengths : first[s] = number of held samples with ts <= threshold (binary search,
 //                           one thread per series), len[s] = count[s] - first[s];
 //   (the caller turns len into offsets with one cumulative sum)
+//   pmx_slab_tail_offsets : the same search and off[0 .. S] (exclusive sums of len) in ONE launch;
 //   pmx_slab_tail_gather  : one warp per series copies ts/val[s][first[s] .. count[s]) to
 //                           out[off[s] ..);
 //   pmx_slab_append       : the samples of a new answer go to the ends of their rows (skipping what
@@ -27,6 +28,52 @@ __global__ void tail_lengths_kernel(const int64_t* __restrict__ ts, const int64_
   }
   first[s] = lo;
   len[s] = n - lo;
+}
+
+// The same search and the offsets in one launch: every CTA searches 1024 series and parks their tail
+// lengths in off[s + 1]; the CTA that finishes last (a counter that it leaves at zero again) turns them
+// into running sums, 1024 at a time.  A refresh is latency-bound: the launches saved are what counts.
+__global__ void __launch_bounds__(1024)
+tail_offsets_kernel(const int64_t* __restrict__ ts, const int64_t* __restrict__ count, int64_t n_series, int64_t cap,
+                    int64_t threshold, int64_t* __restrict__ first, int64_t* __restrict__ off, unsigned int* __restrict__ done) {
+  __shared__ long long s_warp[32];
+  __shared__ long long s_total;
+  __shared__ bool s_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  {
+    const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < n_series) {
+      const int64_t* row = ts + s * cap;
+      int64_t lo = 0, hi = count[s];
+      const int64_t n = hi;
+      while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if (row[mid] <= threshold) lo = mid + 1; else hi = mid; }
+      first[s] = lo;
+      off[s + 1] = n - lo;
+    }
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = atomicAdd(done, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  if (threadIdx.x == 0) { s_total = 0; off[0] = 0; *done = 0; }
+  __syncthreads();
+  for (int64_t s0 = 0; s0 < n_series; s0 += blockDim.x) {
+    const int64_t s = s0 + threadIdx.x;
+    const long long len = s < n_series ? (long long)__ldcg(off + s + 1) : 0;
+    long long inc = len;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const long long v = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += v; }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    long long base = s_total;
+    for (int w = 0; w < warp; ++w) base += s_warp[w];
+    if (s < n_series) off[s + 1] = base + inc;
+    __syncthreads();
+    if (threadIdx.x == blockDim.x - 1) s_total = base + inc;
+    __syncthreads();
+  }
 }
 
 __global__ void __launch_bounds__(256)
@@ -128,6 +175,19 @@ int pmx_slab_tail_lengths(pmx_ctx* ctx, const int64_t* d_ts, const int64_t* d_co
   PMX_REQUIRE(d_ts && d_count && d_first && d_len, "NULL buffer");
   tail_lengths_kernel<<<(unsigned)((n_series + 255) / 256), 256, 0, pmx_st(stream)>>>(d_ts, d_count, n_series, cap,
                                                                                     threshold_ms, d_first, d_len);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
+int pmx_slab_tail_offsets(pmx_ctx* ctx, const int64_t* d_ts, const int64_t* d_count, int64_t n_series, int64_t cap,
+                          int64_t threshold_ms, int64_t* d_first, int64_t* d_off, uint32_t* d_work, pmx_stream stream) {
+  PMX_REQUIRE(ctx, "ctx is NULL");
+  PMX_REQUIRE(n_series >= 0 && cap >= 1, "bad sizes");
+  PMX_REQUIRE(d_off && d_work, "NULL buffer");
+  if (n_series == 0) { PMX_CUDA(cudaMemsetAsync(d_off, 0, sizeof(int64_t), pmx_st(stream))); return PMX_OK; }
+  PMX_REQUIRE(d_ts && d_count && d_first, "NULL buffer");
+  tail_offsets_kernel<<<(unsigned)((n_series + 1023) / 1024), 1024, 0, pmx_st(stream)>>>(d_ts, d_count, n_series, cap, threshold_ms,
+                                                                                       d_first, d_off, d_work);
   PMX_LAUNCH_CHECK();
   return PMX_OK;
 }
