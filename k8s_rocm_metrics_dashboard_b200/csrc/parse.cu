@@ -67,8 +67,7 @@ parse_samples_kernel(const uint8_t* __restrict__ text, uint64_t text_len, const 
       if (vec && o < safe) {
         uint64_t W[4];
         load_window(text, o, W);
-        const int L = pmx::find_byte24(W, (uint8_t)'"');
-        if (L < 24) fast = pmx::fast_f64(W, L, pmx_pow5_128, &bits);
+        fast = pmx::fast_f64_scan(W, (uint8_t)'"', pmx_pow5_128, &bits);
       }
       st = fast == pmx::FAST_OK ? pmx::PARSE_OK : slow_f64(text, text_len, o, &bits);
     }
@@ -84,8 +83,7 @@ parse_samples_kernel(const uint8_t* __restrict__ text, uint64_t text_len, const 
       if (vec && o < safe) {
         uint64_t W[4];
         load_window(text, o, W);
-        const int L = pmx::find_byte24(W, (uint8_t)',');
-        if (L < 24) fast = pmx::fast_ts_ms(W, L, &v);
+        fast = pmx::fast_ts_ms_scan(W, (uint8_t)',', &v);
       }
       st = fast == pmx::FAST_OK ? pmx::PARSE_OK : slow_ts(text, text_len, o, &v);
     }

@@ -1,4 +1,6 @@
 // strtod_fast.h -- the common case of K1 without a byte loop (SURVEY X2, app.py:188).
+// (The kernel runs the SECOND form at the end of this file -- scan_token / decimal_scanned; the first
+// form below it grew out of stays for the host fuzz test, which checks both.)
 //
 // Prometheus writes sample values as shortest round-trip decimals and timestamps as seconds with
 // up to three decimals: plain [-]digits[.digits] in all but a few tokens (NaN, +Inf, exponents).
@@ -157,6 +159,136 @@ PMX_HD inline int fast_ts_ms(const uint64_t* W, int L, int64_t* out) {
   if (nf > 3 || ni > 15) return FAST_FALLBACK;         // sub-millisecond digits / overflow: the byte-wise path decides
   const int64_t ms = (int64_t)(m * pow10_u64(3 - nf));
   *out = neg ? -ms : ms;
+  return FAST_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Second form: the window is scanned ONCE for the bytes that are not digits.  The first of them is
+// the decimal point or the terminator, the second (after a point) the terminator; everything between
+// is digits by construction, so neither a search per character nor a digit check is needed, and a
+// token of at most eight bytes -- most gauge readings -- is decoded from the first word alone.
+
+// 0x80 in every byte of v that is not '0'..'9' (exact per byte: no carry crosses a byte)
+PMX_HD inline uint64_t nondigit_bytes(uint64_t v) {
+  const uint64_t t = v & 0x7f7f7f7f7f7f7f7fULL;
+  const uint64_t ge3a = t + 0x4646464646464646ULL;             // bit 7 set iff t >= 0x3A
+  const uint64_t ge30 = t + 0x5050505050505050ULL;             // bit 7 set iff t >= 0x30
+  return (v | ge3a | ~ge30) & 0x8080808080808080ULL;
+}
+PMX_HD inline uint32_t byte_at24(const uint64_t* W, int p) {   // byte p (0..23) of the window
+  const uint64_t w = p < 8 ? W[0] : (p < 16 ? W[1] : W[2]);
+  return (uint32_t)(w >> ((p & 7) * 8)) & 0xffu;
+}
+struct TokenScan { int L; int dot; bool neg; };                 // dot == L: no decimal point
+
+// [-]digits[.digits] at byte 0 of the window, ended by `term` within the first 24 bytes
+PMX_HD inline bool scan_token(const uint64_t* W, uint8_t term, TokenScan* s) {
+  uint64_t f0 = nondigit_bytes(W[0]), f1 = nondigit_bytes(W[1]), f2 = nondigit_bytes(W[2]);
+  const bool neg = (W[0] & 0xff) == '-';
+  if (neg) f0 &= ~0x80ULL;
+  int p1;
+  if (f0) { p1 = first_set_byte(f0); f0 &= f0 - 1; }
+  else if (f1) { p1 = 8 + first_set_byte(f1); f1 &= f1 - 1; }
+  else if (f2) { p1 = 16 + first_set_byte(f2); f2 &= f2 - 1; }
+  else return false;
+  const uint32_t c1 = byte_at24(W, p1);
+  s->neg = neg;
+  if (c1 == term) { s->L = p1; s->dot = p1; return true; }
+  if (c1 != '.') return false;
+  int p2;
+  if (f0) p2 = first_set_byte(f0);
+  else if (f1) p2 = 8 + first_set_byte(f1);
+  else if (f2) p2 = 16 + first_set_byte(f2);
+  else return false;
+  if (byte_at24(W, p2) != term) return false;
+  s->L = p2; s->dot = p1;
+  return true;
+}
+
+// significand (<= 19 digits) and digit counts of a scanned token; FALLBACK for "5.", ".5", long mantissas
+PMX_HD inline int decimal_scanned(const uint64_t* W, const TokenScan& sc, uint64_t* m, int* n_frac, int* n_int) {
+  const int L = sc.L, s0 = sc.neg ? 1 : 0;
+  const bool has_dot = sc.dot < L;
+  const int nf = has_dot ? L - sc.dot - 1 : 0;
+  const int ni = sc.dot - s0;
+  const int nd = ni + nf;
+  if (ni < 1 || (has_dot && nf < 1) || nd > 19) return FAST_FALLBACK;
+  *n_frac = nf; *n_int = ni;
+  if (L <= 8) {
+    // the whole token sits in the first word: its last byte to byte 7, the integer part one byte
+    // further to close the point up, '0' in front, one 8-digit conversion
+    const uint64_t A = W[0] << (8 * (8 - L));
+    const uint64_t B = A << 8;
+    const int rf = 8 - nf, ri = 8 - nd;
+    const uint64_t below_frac = rf >= 8 ? ~0ULL : ((1ULL << (8 * rf)) - 1ULL);
+    const uint64_t below_int = ri >= 8 ? ~0ULL : ((1ULL << (8 * ri)) - 1ULL);
+    const uint64_t D = (A & ~below_frac) | ((has_dot ? B : A) & below_frac & ~below_int) | (0x3030303030303030ULL & below_int);
+    *m = eight_digits(D);
+    return FAST_OK;
+  }
+  if (L <= 16) {
+    // two words (timestamps, counters): the same with the token's last byte at position 15
+    const int sh = 8 * (16 - L);                       // 0 .. 56 bits
+    const uint64_t A1 = sh ? (W[1] << sh) | (W[0] >> (64 - sh)) : W[1], A0 = W[0] << sh;
+    const uint64_t B1 = (A1 << 8) | (A0 >> 56), B0 = A0 << 8;
+    const uint64_t bf0 = low_bytes_mask(16 - nf, 0), bf1 = low_bytes_mask(16 - nf, 1);
+    const uint64_t bi0 = low_bytes_mask(16 - nd, 0), bi1 = low_bytes_mask(16 - nd, 1);
+    const uint64_t D0 = (A0 & ~bf0) | ((has_dot ? B0 : A0) & bf0 & ~bi0) | (0x3030303030303030ULL & bi0);
+    const uint64_t D1 = (A1 & ~bf1) | ((has_dot ? B1 : A1) & bf1 & ~bi1) | (0x3030303030303030ULL & bi1);
+    *m = (uint64_t)eight_digits(D0) * 100000000ULL + eight_digits(D1);
+    return FAST_OK;
+  }
+  uint64_t A[4], B[4];
+  shl_bytes(W, 24 - L, A);                             // the token's last byte at position 23: fraction (or all digits) in place
+  shl_bytes(W, 25 - L, B);                             // one further: the integer part next to the fraction
+  uint64_t D[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const uint64_t below_frac = low_bytes_mask(24 - nf, k), below_int = low_bytes_mask(24 - nd, k);
+    const uint64_t ipart = has_dot ? B[k] : A[k];
+    D[k] = (A[k] & ~below_frac) | (ipart & below_frac & ~below_int) | (0x3030303030303030ULL & below_int);
+  }
+  const uint64_t c1 = eight_digits(D[1]), c2 = eight_digits(D[2]);
+  uint64_t hi = 0;
+  if (nd > 16) hi = eight_digits(D[0]);                // < 1000 (nd <= 19)
+  *m = (hi * 100000000ULL + c1) * 100000000ULL + c2;
+  return FAST_OK;
+}
+
+// value token ended by `term` -> bits of float(token)
+PMX_HD inline int fast_f64_scan(const uint64_t* W, uint8_t term, const uint64_t* __restrict__ tab, uint64_t* out_bits) {
+  TokenScan sc;
+  if (!scan_token(W, term, &sc)) return FAST_FALLBACK;
+  uint64_t m; int nf, ni;
+  if (decimal_scanned(W, sc, &m, &nf, &ni) != FAST_OK) return FAST_FALLBACK;
+  const uint64_t sign = sc.neg ? 0x8000000000000000ULL : 0;
+  if (m == 0) { *out_bits = sign; return FAST_OK; }
+  if (m <= (1ULL << 53) && nf <= 22) {
+    const double v = (double)m / pow10_f64(nf);        // both operands exact: one IEEE rounding
+    uint64_t b;
+#if defined(__CUDA_ARCH__)
+    b = (uint64_t)__double_as_longlong(v);
+#else
+    __builtin_memcpy(&b, &v, 8);
+#endif
+    *out_bits = b | sign;
+    return FAST_OK;
+  }
+  const AdjMant a = eisel_lemire(-(int64_t)nf, m, tab);
+  if (!a.certain) return FAST_FALLBACK;
+  *out_bits = (a.mant | ((uint64_t)a.pow2 << 52)) | sign;
+  return FAST_OK;
+}
+
+// timestamp token [-]digits[.d{1,3}] seconds ended by `term` -> int64 ms
+PMX_HD inline int fast_ts_ms_scan(const uint64_t* W, uint8_t term, int64_t* out) {
+  TokenScan sc;
+  if (!scan_token(W, term, &sc)) return FAST_FALLBACK;
+  uint64_t m; int nf, ni;
+  if (decimal_scanned(W, sc, &m, &nf, &ni) != FAST_OK) return FAST_FALLBACK;
+  if (nf > 3 || ni > 15) return FAST_FALLBACK;         // sub-millisecond digits / overflow: the byte-wise path decides
+  const int64_t ms = (int64_t)(m * pow10_u64(3 - nf));
+  *out = sc.neg ? -ms : ms;
   return FAST_OK;
 }
 

@@ -32,3 +32,21 @@ extern "C" int host_fast_ts_ms(const uint8_t* p, int64_t len, int64_t* out) {
   memcpy(W, p, (size_t)len);
   return pmx::fast_ts_ms(W, (int)len, out);
 }
+
+// the scanning form: the window holds the token AND its terminator (what the kernel sees)
+extern "C" int host_scan_f64(const uint8_t* p, int64_t len, uint8_t term, uint64_t* bits) {
+  uint8_t buf[32];
+  memset(buf, 'x', sizeof buf);                         // whatever follows in the body
+  if (len >= 31) return pmx::FAST_FALLBACK;
+  memcpy(buf, p, (size_t)len); buf[len] = term;
+  uint64_t W[4]; memcpy(W, buf, 32);
+  return pmx::fast_f64_scan(W, term, pmx_pow5_128, bits);
+}
+extern "C" int host_scan_ts_ms(const uint8_t* p, int64_t len, uint8_t term, int64_t* out) {
+  uint8_t buf[32];
+  memset(buf, '7', sizeof buf);                         // digits behind the terminator must not matter
+  if (len >= 31) return pmx::FAST_FALLBACK;
+  memcpy(buf, p, (size_t)len); buf[len] = term;
+  uint64_t W[4]; memcpy(W, buf, 32);
+  return pmx::fast_ts_ms_scan(W, term, out);
+}

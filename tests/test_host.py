@@ -255,6 +255,37 @@ def test_fast_window_decode_on_host_matches_python_float(host_lib, golden_dir):
             assert o.value == int(Decimal(tk) * 1000), tk
     for tk in ("1.2345", "12345678901234567", "1e3", "", "-", "1.", ".5", " 1"):     # not this path's business
         assert lib.host_fast_ts_ms(tk.encode(), len(tk), C.byref(C.c_int64())) == 1 or tk == "12345678901234567"
+    # the scanning form (what the kernel runs now): window = token + terminator + whatever follows
+    lib.host_scan_f64.argtypes = [C.c_char_p, C.c_int64, C.c_uint8, C.POINTER(C.c_uint64)]
+    lib.host_scan_ts_ms.argtypes = [C.c_char_p, C.c_int64, C.c_uint8, C.POINTER(C.c_int64)]
+    decoded = short = 0
+    for tk in toks:
+        raw = tk.encode()
+        b = C.c_uint64()
+        if lib.host_scan_f64(raw, len(raw), ord('"'), C.byref(b)) == 0:
+            decoded += 1
+            short += len(raw) <= 8
+            assert b.value == struct.unpack("<Q", struct.pack("<d", float(tk)))[0], repr(tk)
+        elif len(raw) < 24 and raw.lstrip(b"-").replace(b".", b"", 1).isdigit() and raw[-1:] != b"." and raw.lstrip(b"-")[:1] != b"." \
+                and len(raw.lstrip(b"-").replace(b".", b"")) <= 19 and raw.count(b"-") <= 1:
+            # a plain decimal it may only hand on for the Eisel-Lemire "uncertain" cases
+            assert len(raw.lstrip(b"-").replace(b".", b"")) > 15, repr(tk)
+    assert decoded > 40000 and short > 5000
+    for tk in ("1.2345", "0.001", "7", "-3.5", "99999999", "1234567.8", "-0", "0.0", "12.34567", "100000000"):
+        b = C.c_uint64()
+        assert lib.host_scan_f64(tk.encode(), len(tk), ord('"'), C.byref(b)) == 0, tk
+        assert b.value == struct.unpack("<Q", struct.pack("<d", float(tk)))[0], tk
+    for tk in ("1e3", "", "-", "1.", ".5", " 1", "NaN", "+Inf", "1.2.3", "1_0", "--1", "1-"):
+        assert lib.host_scan_f64(tk.encode(), len(tk), ord('"'), C.byref(C.c_uint64())) == 1, tk
+    for _ in range(20000):
+        s_ = rnd.randrange(0, 4 * 10 ** 9); f = rnd.randrange(0, 1000); nf = rnd.randrange(0, 4)
+        tk = f"{s_}" if nf == 0 else f"{s_}.{f:03d}"[:len(str(s_)) + 1 + nf]
+        tk = ("-" if rnd.random() < 0.1 else "") + tk
+        o = C.c_int64()
+        assert lib.host_scan_ts_ms(tk.encode(), len(tk), ord(","), C.byref(o)) == 0, tk
+        assert o.value == int(Decimal(tk) * 1000), tk
+    for tk in ("1.2345", "1e3", "", "-", "1.", ".5", " 1"):
+        assert lib.host_scan_ts_ms(tk.encode(), len(tk), ord(","), C.byref(C.c_int64())) == 1, tk
 
 
 def test_interned_label_table_equals_json_loads():
