@@ -168,6 +168,17 @@ PMX_HD inline int fast_ts_ms(const uint64_t* W, int L, int64_t* out) {
 // is digits by construction, so neither a search per character nor a digit check is needed, and a
 // token of at most eight bytes -- most gauge readings -- is decoded from the first word alone.
 
+// a window of THREE words shifted up by s bytes (0 <= s < 24): what lies above byte 23 is dropped
+PMX_HD inline void shl_bytes3(const uint64_t* W, int s, uint64_t* out) {
+  const bool w1 = (s & 8) != 0, w2 = (s & 16) != 0;
+  const int b = (s & 7) * 8;
+  const uint64_t y2 = w1 ? W[1] : W[2], y1 = w1 ? W[0] : W[1], y0 = w1 ? 0 : W[0];
+  const uint64_t z2 = w2 ? y0 : y2, z1 = w2 ? 0 : y1, z0 = w2 ? 0 : y0;
+  out[2] = b ? (z2 << b) | (z1 >> (64 - b)) : z2;
+  out[1] = b ? (z1 << b) | (z0 >> (64 - b)) : z1;
+  out[0] = b ? (z0 << b) : z0;
+}
+
 // 0x80 in every byte of v that is not '0'..'9' (exact per byte: no carry crosses a byte)
 PMX_HD inline uint64_t nondigit_bytes(uint64_t v) {
   const uint64_t t = v & 0x7f7f7f7f7f7f7f7fULL;
@@ -183,9 +194,14 @@ struct TokenScan { int L; int dot; bool neg; };                 // dot == L: no 
 
 // [-]digits[.digits] at byte 0 of the window, ended by `term` within the first 24 bytes
 PMX_HD inline bool scan_token(const uint64_t* W, uint8_t term, TokenScan* s) {
-  uint64_t f0 = nondigit_bytes(W[0]), f1 = nondigit_bytes(W[1]), f2 = nondigit_bytes(W[2]);
+  uint64_t f0 = nondigit_bytes(W[0]), f1 = nondigit_bytes(W[1]), f2 = 0;
   const bool neg = (W[0] & 0xff) == '-';
   if (neg) f0 &= ~0x80ULL;
+  // the third word only when the first two do not hold both marks (tokens beyond ~15 bytes: rare)
+  {
+    const uint64_t g0 = f0 & (f0 - 1);                 // f0 without its lowest mark
+    if (!(g0 | (f0 && f1) | (f1 & (f1 - 1)))) f2 = nondigit_bytes(W[2]);
+  }
   int p1;
   if (f0) { p1 = first_set_byte(f0); f0 &= f0 - 1; }
   else if (f1) { p1 = 8 + first_set_byte(f1); f1 &= f1 - 1; }
@@ -238,9 +254,9 @@ PMX_HD inline int decimal_scanned(const uint64_t* W, const TokenScan& sc, uint64
     *m = (uint64_t)eight_digits(D0) * 100000000ULL + eight_digits(D1);
     return FAST_OK;
   }
-  uint64_t A[4], B[4];
-  shl_bytes(W, 24 - L, A);                             // the token's last byte at position 23: fraction (or all digits) in place
-  shl_bytes(W, 25 - L, B);                             // one further: the integer part next to the fraction
+  uint64_t A[3], B[3];
+  shl_bytes3(W, 24 - L, A);                            // the token's last byte at position 23: fraction (or all digits) in place
+  shl_bytes3(W, 25 - L, B);                            // one further: the integer part next to the fraction
   uint64_t D[3];
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
