@@ -6,15 +6,19 @@
 //
 // The body is a flat array of bytes; what a byte means depends on whether it lies inside a JSON
 // string, i.e. on the parity of the unescaped quotes before it.  Three kernels:
-//   count : CTA c walks chunk c (64 KiB) in rounds of 4 KiB, 16 bytes per thread per round, and
+//   count : warp w walks chunk w (8 KiB) in rounds of 512 bytes, 16 bytes per lane per round, and
 //           reports the chunk's quote parity and its number of sample starts ('[' followed by a
 //           digit or '-'), series starts ('{"metric":{') and '[' -- each counted twice, once for
 //           "the chunk begins outside a string" and once for "inside";
 //   scan  : one CTA turns the parities into every chunk's true starting state and the counts that
 //           belong to it into output offsets, and checks the envelope and the bracket balance;
 //   emit  : the same walk with the state known; every sample start writes its two token offsets
-//           (the thread scans forward to the ',' and checks the '"' behind it), every series start
-//           its CSR offset and the span of its label object.
+//           (the ',' behind the timestamp is found in the lane's and its neighbour's comma masks),
+//           every series start its CSR offset and the span of its label object.
+// A lane never looks at its 16 bytes one by one: each byte class ('"', '[' or '{', ',') becomes a
+// 16-bit mask by an exact SWAR comparison of the four words, the state inside the segment is the
+// prefix parity of the quote mask, and only set bits are visited.  A chunk belongs to one warp, so
+// the running state passes from round to round by ballot and shuffle: no shared memory, no barrier.
 // Token offsets have the meaning pmx_tokenize gives them, so pmx_parse_f64 / pmx_parse_ts_ms take
 // the body and these arrays as they are.
 #include <stdint.h>
@@ -23,10 +27,12 @@
 namespace {
 
 constexpr int TT = 256;                 // threads per CTA
-constexpr int SEG = 16;                 // bytes per thread per round
-constexpr int ROUND = TT * SEG;         // 4 KiB
+constexpr int WARPS = TT / 32;
+constexpr int SEG = 16;                 // bytes per lane per round
+constexpr int ROUND = 32 * SEG;         // 512 bytes per warp and round
 constexpr int ROUNDS = 16;              // rounds per chunk
-constexpr int64_t CHUNK = (int64_t)ROUND * ROUNDS;
+constexpr int64_t CHUNK = (int64_t)ROUND * ROUNDS;            // 8 KiB, one warp
+constexpr unsigned FULL = 0xffffffffu;
 
 struct ChunkSum { uint32_t parity, samples[2], series[2], brackets[2]; };
 struct ChunkBase { uint32_t in_string; uint32_t pad; int64_t samples, series; };
@@ -39,12 +45,39 @@ __device__ __forceinline__ unsigned char byte_at(const uint8_t* __restrict__ b, 
   return i < len ? b[i] : (unsigned char)0;
 }
 
-// The 16 bytes of this thread's segment (zeros past the end) and the mask of its unescaped quotes.
-// A quote is escaped iff an odd run of backslashes ends right before it; runs are rare and short,
-// so the look-back reads global memory.
-__device__ __forceinline__ unsigned load_segment(const uint8_t* __restrict__ body, uint64_t len, uint64_t pos,
-                                                 unsigned char* c) {
-  uint32_t w[4] = {0, 0, 0, 0};
+// bit k (k = 0..3) set iff byte k of w equals the byte repeated in pat4.  Exact: the zero-byte test
+// carries nothing from one byte into the next, and the multiply gathers bits 0, 8, 16, 24 into
+// bits 24..27 with no two partial products on the same bit.
+__device__ __forceinline__ unsigned eq4(uint32_t w, uint32_t pat4) {
+  const uint32_t x = w ^ pat4;
+  const uint32_t t = (x & 0x7f7f7f7fu) + 0x7f7f7f7fu;
+  const uint32_t z = ~(t | x) & 0x80808080u;
+  return ((z >> 7) * 0x01020408u) >> 24;
+}
+__device__ __forceinline__ unsigned eq16(const uint32_t* w, uint32_t pat4) {
+  return eq4(w[0], pat4) | (eq4(w[1], pat4) << 4) | (eq4(w[2], pat4) << 8) | (eq4(w[3], pat4) << 12);
+}
+// bit k set iff bit 5 of byte k is set ('{' against '[')
+__device__ __forceinline__ unsigned bit5_16(const uint32_t* w) {
+  unsigned m = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) m |= ((((w[j] >> 5) & 0x01010101u) * 0x01020408u) >> 24) << (4 * j);
+  return m;
+}
+// '[' or '{': the two differ in bit 5 alone
+__device__ __forceinline__ unsigned open_mask(const uint32_t* w) {
+  const uint32_t v[4] = {w[0] | 0x20202020u, w[1] | 0x20202020u, w[2] | 0x20202020u, w[3] | 0x20202020u};
+  return eq16(v, 0x7b7b7b7bu);
+}
+// may this word hold the byte?  (false positives allowed, no false negatives)
+__device__ __forceinline__ uint32_t maybe4(uint32_t w, uint32_t pat4) {
+  const uint32_t x = w ^ pat4;
+  return (x - 0x01010101u) & ~x & 0x80808080u;
+}
+
+// The 16 bytes of this lane's segment (zeros past the end), as four words.
+__device__ __forceinline__ void load_words(const uint8_t* __restrict__ body, uint64_t len, uint64_t pos, uint32_t* w) {
+  w[0] = w[1] = w[2] = w[3] = 0;
   if (pos + SEG <= len) {
     const uint4 v = *reinterpret_cast<const uint4*>(body + pos);
     w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w;
@@ -52,56 +85,48 @@ __device__ __forceinline__ unsigned load_segment(const uint8_t* __restrict__ bod
     for (int k = 0; k < SEG; ++k)
       if (pos + k < len) w[k >> 2] |= (uint32_t)body[pos + k] << (8 * (k & 3));
   }
-  unsigned qmask = 0;
-#pragma unroll
-  for (int k = 0; k < SEG; ++k) {
-    c[k] = (unsigned char)(w[k >> 2] >> (8 * (k & 3)));
-    if (c[k] == '"') qmask |= 1u << k;
+}
+
+// byte k (0..15) of the segment
+__device__ __forceinline__ unsigned seg_byte(const uint32_t* w, int k) {
+  const uint32_t lo = (k & 8) ? w[2] : w[0], hi = (k & 8) ? w[3] : w[1];
+  return ((k & 4 ? hi : lo) >> (8 * (k & 3))) & 0xffu;
+}
+
+// Mask of the segment's unescaped quotes.  A quote is escaped iff an odd run of backslashes ends
+// right before it; backslashes are rare, so only a segment that may hold one, or that begins with a
+// quote behind a backslash, looks back through global memory.  All lanes of the warp call this.
+__device__ __forceinline__ unsigned quote_mask(const uint8_t* __restrict__ body, uint64_t len, uint64_t pos,
+                                               const uint32_t* w) {
+  unsigned q = eq16(w, 0x22222222u);
+  const int lane = threadIdx.x & 31;
+  unsigned prev = __shfl_up_sync(FULL, w[3] >> 24, 1);
+  if (lane == 0) prev = (pos > 0 && pos <= len) ? body[pos - 1] : 0u;
+  const uint32_t bs = maybe4(w[0], 0x5c5c5c5cu) | maybe4(w[1], 0x5c5c5c5cu) | maybe4(w[2], 0x5c5c5c5cu) |
+                      maybe4(w[3], 0x5c5c5c5cu);
+  if (q && (bs || (prev == '\\' && (q & 1u)))) {
+    unsigned m = q;
+    while (m) {
+      const int k = __ffs(m) - 1;
+      m &= m - 1;
+      uint64_t i = pos + k;
+      int run = 0;
+      while (i > 0 && body[i - 1] == '\\') { ++run; --i; }
+      if (run & 1) q &= ~(1u << k);
+    }
   }
-  unsigned m = qmask;
-  while (m) {                                               // drop escaped quotes
-    const int k = __ffs(m) - 1;
-    m &= m - 1;
-    uint64_t i = pos + k;
-    int run = 0;
-    while (i > 0 && body[i - 1] == '\\') { ++run; --i; }
-    if (run & 1) qmask &= ~(1u << k);
-  }
-  return qmask;
+  return q;
 }
 
-// exclusive XOR over the CTA of one bit per thread; *total receives the CTA's XOR
-__device__ __forceinline__ unsigned cta_xor_scan(unsigned bit, unsigned* s_warp, unsigned* total) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const unsigned ballot = __ballot_sync(0xffffffffu, bit);
-  const unsigned before = __popc(ballot & ((1u << lane) - 1u)) & 1u;
-  __syncthreads();                                          // s_warp may still be read from the last call
-  if (lane == 0) s_warp[warp] = __popc(ballot) & 1u;
-  __syncthreads();
-  unsigned acc = 0, all = 0;
-#pragma unroll
-  for (int w = 0; w < TT / 32; ++w) { const unsigned v = s_warp[w]; if (w < warp) acc ^= v; all ^= v; }
-  *total = all;
-  return acc ^ before;
+// positions of the segment that lie inside a string when the segment begins outside one; bit 16 of
+// the result: the segment's own parity
+__device__ __forceinline__ unsigned inside_mask(unsigned q) {
+  unsigned x = q;
+  x ^= x << 1; x ^= x << 2; x ^= x << 4; x ^= x << 8;           // inclusive prefix parity
+  return (x << 1) & 0x1ffffu;
 }
 
-// exclusive sum over the CTA; *total receives the CTA's sum
-__device__ __forceinline__ unsigned cta_sum_scan(unsigned v, unsigned* s_warp, unsigned* total) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  unsigned inc = v;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) { const unsigned u = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += u; }
-  __syncthreads();
-  if (lane == 31) s_warp[warp] = inc;
-  __syncthreads();
-  unsigned acc = 0, all = 0;
-#pragma unroll
-  for (int w = 0; w < TT / 32; ++w) { const unsigned u = s_warp[w]; if (w < warp) acc += u; all += u; }
-  *total = all;
-  return acc + inc - v;
-}
-
-__device__ __forceinline__ bool starts_number(unsigned char c) { return (c >= '0' && c <= '9') || c == '-'; }
+__device__ __forceinline__ bool starts_number(unsigned c) { return (c >= '0' && c <= '9') || c == '-'; }
 
 // '{' at p opens a series object iff it is followed by "metric":{
 __device__ __forceinline__ bool series_at(const uint8_t* __restrict__ body, uint64_t len, uint64_t p) {
@@ -112,45 +137,86 @@ __device__ __forceinline__ bool series_at(const uint8_t* __restrict__ body, uint
   return true;
 }
 
+__device__ __forceinline__ unsigned warp_sum(unsigned v) {
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(FULL, v, d);
+  return v;
+}
+
 __global__ void __launch_bounds__(TT)
-tokd_count_kernel(const uint8_t* __restrict__ body, uint64_t len, ChunkSum* __restrict__ sums) {
-  __shared__ unsigned s_warp[TT / 32];
-  const uint64_t c0 = (uint64_t)blockIdx.x * CHUNK;
+tokd_count_kernel(const uint8_t* __restrict__ body, uint64_t len, ChunkSum* __restrict__ sums, int64_t n_chunks) {
+  const int lane = threadIdx.x & 31;
+  const int64_t chunk = (int64_t)blockIdx.x * WARPS + (threadIdx.x >> 5);
+  if (chunk >= n_chunks) return;                            // whole warps leave
+  const uint64_t c0 = (uint64_t)chunk * CHUNK;
   unsigned run = 0;                                         // quote parity of the chunk so far
   unsigned n_smp[2] = {0, 0}, n_ser[2] = {0, 0}, n_br[2] = {0, 0};
   for (int r = 0; r < ROUNDS; ++r) {
-    const uint64_t pos = c0 + (uint64_t)r * ROUND + (uint64_t)threadIdx.x * SEG;
-    if (c0 + (uint64_t)r * ROUND >= len) break;             // uniform
-    unsigned char c[SEG];
-    const unsigned qmask = pos < len ? load_segment(body, len, pos, c) : 0u;
-    unsigned total;
-    const unsigned before = run ^ cta_xor_scan(__popc(qmask) & 1u, s_warp, &total);
-    if (pos < len) {
-#pragma unroll
-      for (int k = 0; k < SEG; ++k) {
-        if (c[k] != '[' && c[k] != '{') continue;
-        const unsigned par = before ^ (__popc(qmask & ((1u << k) - 1u)) & 1u);
-        if (c[k] == '[') {
-          ++n_br[par];
-          const unsigned char nx = k + 1 < SEG ? c[k + 1] : byte_at(body, len, pos + SEG);
-          if (starts_number(nx)) ++n_smp[par];
-        } else if (series_at(body, len, pos + k)) {
-          ++n_ser[par];
-        }
+    const uint64_t base = c0 + (uint64_t)r * ROUND;
+    if (base >= len) break;                                 // uniform
+    const uint64_t pos = base + (uint64_t)lane * SEG;
+    uint32_t w[4];
+    load_words(body, len, pos, w);
+    const unsigned q = quote_mask(body, len, pos, w);
+    const unsigned in0 = inside_mask(q);
+    const unsigned ballot = __ballot_sync(FULL, (in0 >> 16) & 1u);
+    const unsigned before = run ^ (__popc(ballot & ((1u << lane) - 1u)) & 1u);
+    run ^= __popc(ballot) & 1u;
+    const unsigned ins = (in0 ^ (before ? 0xffffu : 0u)) & 0xffffu;     // inside a string if the chunk began outside
+    const unsigned open = open_mask(w);
+    unsigned next0 = __shfl_down_sync(FULL, w[0] & 0xffu, 1);
+    if (lane == 31) next0 = byte_at(body, len, pos + SEG);
+    if (open) {
+      const unsigned brace = open & bit5_16(w), square = open & ~brace;
+      n_br[0] += __popc(square & ~ins);
+      n_br[1] += __popc(square & ins);
+      unsigned m = square;
+      while (m) {
+        const int k = __ffs(m) - 1;
+        m &= m - 1;
+        if (starts_number(k + 1 < SEG ? seg_byte(w, k + 1) : next0)) ++n_smp[(ins >> k) & 1u];
+      }
+      m = brace;
+      while (m) {
+        const int k = __ffs(m) - 1;
+        m &= m - 1;
+        if (series_at(body, len, pos + k)) ++n_ser[(ins >> k) & 1u];
       }
     }
-    run ^= total;
   }
-  // CTA totals of the six counters
-  unsigned tot[6];
-  unsigned vals[6] = {n_smp[0], n_smp[1], n_ser[0], n_ser[1], n_br[0], n_br[1]};
-  for (int i = 0; i < 6; ++i) cta_sum_scan(vals[i], s_warp, &tot[i]);
-  if (threadIdx.x == 0) {
-    ChunkSum s;
-    s.parity = run; s.samples[0] = tot[0]; s.samples[1] = tot[1]; s.series[0] = tot[2]; s.series[1] = tot[3];
-    s.brackets[0] = tot[4]; s.brackets[1] = tot[5];
-    sums[blockIdx.x] = s;
-  }
+  ChunkSum s;
+  s.parity = run;
+  s.samples[0] = warp_sum(n_smp[0]); s.samples[1] = warp_sum(n_smp[1]);
+  s.series[0] = warp_sum(n_ser[0]); s.series[1] = warp_sum(n_ser[1]);
+  s.brackets[0] = warp_sum(n_br[0]); s.brackets[1] = warp_sum(n_br[1]);
+  if (lane == 0) sums[chunk] = s;
+}
+
+// exclusive scans over a CTA of 1024 threads: XOR of one bit, sums of three counters.  *tot: CTA totals.
+__device__ __forceinline__ unsigned cta_xor_excl(unsigned bit, unsigned* s_w) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned ballot = __ballot_sync(FULL, bit);
+  if (lane == 0) s_w[warp] = __popc(ballot) & 1u;
+  __syncthreads();
+  const unsigned wb = __ballot_sync(FULL, s_w[lane]);       // 32 warps: one bit each
+  __syncthreads();
+  return (__popc(ballot & ((1u << lane) - 1u)) ^ __popc(wb & ((1u << warp) - 1u))) & 1u;
+}
+__device__ __forceinline__ unsigned long long cta_sum_excl(unsigned long long v, unsigned long long* s_w,
+                                                           unsigned long long* tot) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  unsigned long long inc = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) { const unsigned long long u = __shfl_up_sync(FULL, inc, d); if (lane >= d) inc += u; }
+  if (lane == 31) s_w[warp] = inc;
+  __syncthreads();
+  unsigned long long wi = s_w[lane], wt = wi;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) { const unsigned long long u = __shfl_up_sync(FULL, wi, d); if (lane >= d) wi += u; }
+  const unsigned long long below = __shfl_sync(FULL, wi - wt, warp);
+  *tot = __shfl_sync(FULL, wi, 31);
+  __syncthreads();
+  return below + inc - v;
 }
 
 // One CTA: chunk states and output bases; envelope and balance checks; totals.
@@ -158,28 +224,22 @@ __global__ void __launch_bounds__(1024)
 tokd_scan_kernel(const uint8_t* __restrict__ body, uint64_t len, const ChunkSum* __restrict__ sums,
                  ChunkBase* __restrict__ bases, int64_t n_chunks, int64_t cap_samples, int64_t cap_series,
                  int64_t* __restrict__ series_off, int64_t* __restrict__ status) {
-  __shared__ unsigned s_par[1024];
-  __shared__ unsigned long long s_smp[1024], s_ser[1024], s_br[1024];
+  __shared__ unsigned s_par[32];
+  __shared__ unsigned long long s_sum[32];
   const int t = threadIdx.x;
   const int64_t per = (n_chunks + 1023) / 1024;
   const int64_t a = (int64_t)t * per, b = a + per < n_chunks ? a + per : n_chunks;
   unsigned par = 0;
   for (int64_t c = a; c < b; ++c) par ^= sums[c].parity;
-  s_par[t] = par;
-  __syncthreads();
-  if (t == 0) { unsigned acc = 0; for (int i = 0; i < 1024; ++i) { const unsigned v = s_par[i]; s_par[i] = acc; acc ^= v; } }
-  __syncthreads();
-  unsigned h = s_par[t];                                    // state at the start of this thread's first chunk
+  const unsigned h0 = cta_xor_excl(par, s_par);             // state at the start of this thread's first chunk
+  unsigned h = h0;
   unsigned long long smp = 0, ser = 0, br = 0;
   for (int64_t c = a; c < b; ++c) { smp += sums[c].samples[h]; ser += sums[c].series[h]; br += sums[c].brackets[h]; h ^= sums[c].parity; }
-  s_smp[t] = smp; s_ser[t] = ser; s_br[t] = br;
-  __syncthreads();
+  unsigned long long x, y, z;
+  smp = cta_sum_excl(smp, s_sum, &x);
+  ser = cta_sum_excl(ser, s_sum, &y);
+  cta_sum_excl(br, s_sum, &z);
   if (t == 0) {
-    unsigned long long x = 0, y = 0, z = 0;
-    for (int i = 0; i < 1024; ++i) {
-      const unsigned long long u = s_smp[i], v = s_ser[i], w = s_br[i];
-      s_smp[i] = x; s_ser[i] = y; s_br[i] = z; x += u; y += v; z += w;
-    }
     // envelope: Prometheus' own encoding of a successful matrix / vector answer
     const char pre[] = "{\"status\":\"success\",\"data\":{\"resultType\":\"";
     const int np = (int)sizeof(pre) - 1;
@@ -203,9 +263,7 @@ tokd_scan_kernel(const uint8_t* __restrict__ body, uint64_t len, const ChunkSum*
     status[ST_SAMPLES] = (long long)x; status[ST_SERIES] = (long long)y; status[ST_ERROR] = err; status[ST_WHERE] = where;
     if (!err) series_off[y] = (long long)x;
   }
-  __syncthreads();
-  h = s_par[t];
-  smp = s_smp[t]; ser = s_ser[t];
+  h = h0;
   for (int64_t c = a; c < b; ++c) {
     ChunkBase o; o.in_string = h; o.pad = 0; o.samples = (long long)smp; o.series = (long long)ser;
     bases[c] = o;
@@ -219,45 +277,72 @@ __device__ __forceinline__ void report(int64_t* status, int err, uint64_t where)
 }
 
 __global__ void __launch_bounds__(TT)
-tokd_emit_kernel(const uint8_t* __restrict__ body, uint64_t len, const ChunkBase* __restrict__ bases,
+tokd_emit_kernel(const uint8_t* __restrict__ body, uint64_t len, const ChunkBase* __restrict__ bases, int64_t n_chunks,
                  uint32_t* __restrict__ ts_off, uint32_t* __restrict__ val_off,
                  int64_t* __restrict__ series_off, uint32_t* __restrict__ metric_off,
                  uint32_t* __restrict__ metric_len, int64_t cap_samples, int64_t cap_series,
                  int64_t* __restrict__ status) {
-  __shared__ unsigned s_warp[TT / 32];
-  __shared__ int s_refused;
-  // The scan may have refused the body, and other CTAs of this kernel may report an error while
-  // this one starts: one thread looks, everybody leaves together (the scans below need all warps).
-  if (threadIdx.x == 0) s_refused = status[ST_ERROR] != 0;
-  __syncthreads();
-  if (s_refused) return;
-  const uint64_t c0 = (uint64_t)blockIdx.x * CHUNK;
-  const ChunkBase cb = bases[blockIdx.x];
+  const int lane = threadIdx.x & 31;
+  const int64_t chunk = (int64_t)blockIdx.x * WARPS + (threadIdx.x >> 5);
+  if (chunk >= n_chunks) return;                            // whole warps leave
+  // The scan may have refused the body, and other warps may report an error while this one starts:
+  // one lane looks, the warp leaves together (the ballots below need all lanes).
+  int refused = lane == 0 ? (int)(status[ST_ERROR] != 0) : 0;
+  refused = __shfl_sync(FULL, refused, 0);
+  if (refused) return;
+  const uint64_t c0 = (uint64_t)chunk * CHUNK;
+  const ChunkBase cb = bases[chunk];
   unsigned run = cb.in_string;
   long long smp_base = cb.samples, ser_base = cb.series;
   for (int r = 0; r < ROUNDS; ++r) {
-    const uint64_t pos = c0 + (uint64_t)r * ROUND + (uint64_t)threadIdx.x * SEG;
-    if (c0 + (uint64_t)r * ROUND >= len) break;             // uniform
-    unsigned char c[SEG];
-    const unsigned qmask = pos < len ? load_segment(body, len, pos, c) : 0u;
-    unsigned total;
-    const unsigned before = run ^ cta_xor_scan(__popc(qmask) & 1u, s_warp, &total);
+    const uint64_t base = c0 + (uint64_t)r * ROUND;
+    if (base >= len) break;                                 // uniform
+    const uint64_t pos = base + (uint64_t)lane * SEG;
+    uint32_t w[4];
+    load_words(body, len, pos, w);
+    const unsigned q = quote_mask(body, len, pos, w);
+    const unsigned in0 = inside_mask(q);
+    const unsigned ballot = __ballot_sync(FULL, (in0 >> 16) & 1u);
+    const unsigned before = run ^ (__popc(ballot & ((1u << lane) - 1u)) & 1u);
+    run ^= __popc(ballot) & 1u;
+    const unsigned ins = (in0 ^ (before ? 0xffffu : 0u)) & 0xffffu;     // inside a string
+    const unsigned open = open_mask(w) & ~ins;
+    unsigned next0 = __shfl_down_sync(FULL, w[0] & 0xffu, 1);
+    if (lane == 31) next0 = byte_at(body, len, pos + SEG);
+    // commas of this segment and the next one: the ',' behind a timestamp lies there (a timestamp
+    // longer than that is looked for byte by byte)
+    unsigned commas = eq16(w, 0x2c2c2c2cu);
+    {
+      unsigned nxt = __shfl_down_sync(FULL, commas, 1);
+      if (lane == 31) {
+        uint32_t v[4];
+        load_words(body, len, pos + SEG, v);
+        nxt = eq16(v, 0x2c2c2c2cu);
+      }
+      commas |= nxt << 16;
+    }
     unsigned smask = 0, rmask = 0;                          // sample starts / series starts in this segment
-    if (pos < len) {
-#pragma unroll
-      for (int k = 0; k < SEG; ++k) {
-        if (c[k] != '[' && c[k] != '{') continue;
-        if (before ^ (__popc(qmask & ((1u << k) - 1u)) & 1u)) continue;      // inside a string
-        if (c[k] == '[') {
-          const unsigned char nx = k + 1 < SEG ? c[k + 1] : byte_at(body, len, pos + SEG);
-          if (starts_number(nx)) smask |= 1u << k;
-        } else if (series_at(body, len, pos + k)) {
-          rmask |= 1u << k;
-        }
+    if (open) {
+      const unsigned brace = open & bit5_16(w);
+      unsigned m = open & ~brace;
+      while (m) {
+        const int k = __ffs(m) - 1;
+        m &= m - 1;
+        if (starts_number(k + 1 < SEG ? seg_byte(w, k + 1) : next0)) smask |= 1u << k;
+      }
+      m = brace;
+      while (m) {
+        const int k = __ffs(m) - 1;
+        m &= m - 1;
+        if (series_at(body, len, pos + k)) rmask |= 1u << k;
       }
     }
-    unsigned tot;
-    const unsigned packed = cta_sum_scan((unsigned)__popc(smask) | ((unsigned)__popc(rmask) << 16), s_warp, &tot);
+    // exclusive sums over the warp of both counts, packed 16 + 16
+    const unsigned mine = (unsigned)__popc(smask) | ((unsigned)__popc(rmask) << 16);
+    unsigned inc = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const unsigned u = __shfl_up_sync(FULL, inc, d); if (lane >= d) inc += u; }
+    const unsigned tot = __shfl_sync(FULL, inc, 31), packed = inc - mine;
     long long si = smp_base + (packed & 0xffffu), ri = ser_base + (packed >> 16);
     unsigned m = smask | rmask;
     while (m) {
@@ -267,8 +352,14 @@ tokd_emit_kernel(const uint8_t* __restrict__ body, uint64_t len, const ChunkBase
       if ((smask >> k) & 1u) {
         // [<number>,"<value>"] : the timestamp token ends at the ',', the value token begins
         // behind the quote that follows it
-        uint64_t e = p + 2;
-        while (e < len && e < p + 48 && body[e] != ',') ++e;
+        const unsigned ahead = commas >> (k + 2);           // k + 2 <= 17
+        uint64_t e;
+        if (ahead) e = p + 2 + (uint64_t)(__ffs(ahead) - 1);
+        else {
+          e = pos + 2 * SEG;
+          if (e < p + 2) e = p + 2;
+          while (e < len && e < p + 48 && body[e] != ',') ++e;
+        }
         if (e + 1 >= len || body[e] != ',' || body[e + 1] != '"') { report(status, ERR_SAMPLE, p); }
         else if (si >= 0 && si < cap_samples) { ts_off[si] = (uint32_t)(p + 1); val_off[si] = (uint32_t)(e + 2); }
         ++si;
@@ -294,7 +385,6 @@ tokd_emit_kernel(const uint8_t* __restrict__ body, uint64_t len, const ChunkBase
         ++ri;
       }
     }
-    run ^= total;
     smp_base += tot & 0xffffu;
     ser_base += tot >> 16;
   }
@@ -320,11 +410,12 @@ int pmx_tokenize_device(pmx_ctx* ctx, const uint8_t* d_body, uint64_t len,
   if (!scr) return PMX_E_CUDA;
   ChunkSum* sums = (ChunkSum*)scr;
   ChunkBase* bases = (ChunkBase*)(scr + sums_bytes);
-  tokd_count_kernel<<<(unsigned)n_chunks, TT, 0, st>>>(d_body, len, sums);
+  const unsigned grid = (unsigned)((n_chunks + WARPS - 1) / WARPS);
+  tokd_count_kernel<<<grid, TT, 0, st>>>(d_body, len, sums, n_chunks);
   PMX_LAUNCH_CHECK();
   tokd_scan_kernel<<<1, 1024, 0, st>>>(d_body, len, sums, bases, n_chunks, cap_samples, cap_series, d_series_off, d_status);
   PMX_LAUNCH_CHECK();
-  tokd_emit_kernel<<<(unsigned)n_chunks, TT, 0, st>>>(d_body, len, bases, d_ts_off, d_val_off, d_series_off, d_metric_off,
+  tokd_emit_kernel<<<grid, TT, 0, st>>>(d_body, len, bases, n_chunks, d_ts_off, d_val_off, d_series_off, d_metric_off,
                                                     d_metric_len, cap_samples, cap_series, d_status);
   PMX_LAUNCH_CHECK();
   return PMX_OK;

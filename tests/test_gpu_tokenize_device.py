@@ -73,3 +73,36 @@ def test_bodies_outside_the_compact_encoding_are_refused_not_guessed(eng):
         with pytest.raises(ValueError):
             eng.tokenize_device(bad)
     assert tokenize(good.replace(b'[1700000000', b'[ 1700000000')).n_samples == 2   # the host tokenizer takes general JSON
+
+
+def test_byte_classes_next_to_each_other_and_tokens_across_segments_and_chunks(eng):
+    """The masks of the device tokenizer are built four bytes at a time: bytes one code point away
+    from '"', '[', '{', ',' and the backslash must not be taken for them, wherever they fall in a word;
+    a timestamp of 44 bytes (sub-millisecond zeros) takes the byte-wise search for its ','; and with a label of
+    every length from 0 to 63 each structural byte meets each position of a segment, a warp's round
+    (512 bytes) and a chunk (8 KiB)."""
+    rng = np.random.default_rng(5)
+    near = '"#![Z\\\\]{z|},+-\\\\"0:'
+    series = []
+    for n in range(64):
+        junk = "".join(near[i] for i in rng.integers(0, len(near), size=n))
+        lab = {"__name__": "m", "k": junk, "n": "x" * n}
+        t0 = 1_700_000_000 + 15 * n
+        samples = [(f"{t0}", "1"), (f"{t0 + 15}.5", "-2.5"), (f"{t0 + 30}.125{'0' * 30}", "NaN"),
+                   (f"{t0 + 45}.250", f"{n}.125")] * (1 + n % 5)
+        series.append((lab, samples))
+    import json
+    parts = []
+    for lab, samples in series:
+        vals = ",".join(f'[{t},"{v}"]' for t, v in samples)
+        parts.append('{"metric":' + json.dumps(lab, separators=(",", ":")) + ',"values":[' + vals + "]}")
+    body = ('{"status":"success","data":{"resultType":"matrix","result":[' + ",".join(parts) + "]}}").encode()
+    assert len(body) > 3 * 8192
+    h, d = _same_as_host(eng, body)
+    assert d.n_series == 64 and d.n_samples == sum(len(s) for _, s in series)
+    assert d.labels() == [lab for lab, _ in series]
+    t_dev, v_dev = eng.parse(d)
+    want_v = np.array([float(v) for _, s in series for _, v in s])
+    assert_bits_equal(v_dev.cpu().numpy(), want_v, "values")
+    want_t = np.array([int(round(float(t) * 1000)) for _, s in series for t, _ in s], dtype=np.int64)
+    np.testing.assert_array_equal(t_dev.cpu().numpy(), want_t)
