@@ -37,10 +37,17 @@ __device__ __forceinline__ void st4(double* p, double a, double b, double c, dou
   asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
 }
 
+// The arrays of the statistics that a launch does not produce shrink to one element: 52.7 KB for
+// both, 40.8 KB for the rolling statistics alone, 25.7 KB for increase / rate alone.  Measured on
+// 400 000 series: rolling alone keeps four CTAs per SM (126 registers; five at 96 registers spill and
+// are slower, 28.7 against 34.5 G samples/s) and gains from the code it no longer carries;
+// increase / rate alone runs six CTAs per SM at 80 registers (36.2; 33.3 at five, 34.3 at seven).
+template <bool ROLL, bool RATE>
 struct Smem {
   int64_t ts[NSP];
-  double S_sum[NE], S_mn[NE], S_mx[NE], S_d[NE];
-  double T_sum[NT], T_mn[NT], T_mx[NT], T_fv[NT], T_lv[NT], T_di[NT], T_tj[NT];
+  double S_sum[ROLL ? NE : 1], S_mn[ROLL ? NE : 1], S_mx[ROLL ? NE : 1], S_d[RATE ? NE : 1];
+  double T_sum[ROLL ? NT : 1], T_mn[ROLL ? NT : 1], T_mx[ROLL ? NT : 1];
+  double T_fv[RATE ? NT : 1], T_lv[RATE ? NT : 1], T_di[RATE ? NT : 1], T_tj[RATE ? NT : 1];
   uint32_t T_meta[NT];
   uint16_t B[BMAX];                  // tile-relative (0 .. NE): 16 bits do; with the direct folds returning in
                                      // registers the CTA needs 52.7 KB instead of 59 and four fit an SM
@@ -89,10 +96,11 @@ __device__ __noinline__ Folded fold_direct(const int64_t* __restrict__ ts, const
   return res;
 }
 
-__global__ void __launch_bounds__(NT, 4)
+template <bool ROLL, bool RATE>
+__global__ void __launch_bounds__(NT, ROLL ? 4 : 6)
 ragged_fast_kernel(const RParams p, int64_t n_tiles, int tiles_per_cta) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
+  Smem<ROLL, RATE>& sm = *reinterpret_cast<Smem<ROLL, RATE>*>(smem_raw);
   const int t = threadIdx.x;
   const int e0 = t * E;
   const int64_t N = p.n_samples;
@@ -101,8 +109,7 @@ ragged_fast_kernel(const RParams p, int64_t n_tiles, int tiles_per_cta) {
   if (tile_a >= tile_b) return;
   const double INF = __longlong_as_double(0x7FF0000000000000LL);
   const int need = p.min_periods > 1 ? p.min_periods : 1;
-  const bool do_roll = p.o_min || p.o_max || p.o_mean || p.o_cnt;
-  const bool do_rate = p.o_inc || p.o_rate;
+  constexpr bool do_roll = ROLL, do_rate = RATE;
 
   // series that contains the first flat index of the CTA's first tile
   int64_t sc, off_sc;
@@ -217,10 +224,12 @@ ragged_fast_kernel(const RParams p, int64_t n_tiles, int tiles_per_cta) {
           sfv = v; foff = r; ++scn;
         }
         const int si = r * NT + t;
-        sm.S_sum[si] = ss; sm.S_mn[si] = smn; sm.S_mx[si] = smx; sm.S_d[si] = sd;
+        if (ROLL) { sm.S_sum[si] = ss; sm.S_mn[si] = smn; sm.S_mx[si] = smx; }
+        if (RATE) sm.S_d[si] = sd;
         sm.S_meta[si] = (uint16_t)(scf | (scn << 4) | (((foff - r) & 7) << 8));
       }
-      sm.T_sum[t] = ss; sm.T_mn[t] = smn; sm.T_mx[t] = smx; sm.T_fv[t] = sfv; sm.T_lv[t] = lv; sm.T_di[t] = sd;
+      if (ROLL) { sm.T_sum[t] = ss; sm.T_mn[t] = smn; sm.T_mx[t] = smx; }
+      if (RATE) { sm.T_fv[t] = sfv; sm.T_lv[t] = lv; sm.T_di[t] = sd; }
       sm.T_meta[t] = (uint32_t)(scf | (scn << 4) | (foff << 8) | (lpos << 12));
       c_fv = sfv; c_cn = scn;
     }
@@ -228,13 +237,16 @@ ragged_fast_kernel(const RParams p, int64_t n_tiles, int tiles_per_cta) {
     // ---- junction delta of the own chunk with the last valid sample before it (any chunk back to
     // the halo); published so that chunk ranges can be summed without order bookkeeping
     double clv = 0.0; int clpos = -1;
-    for (int k = t - 1; k >= 0; --k) {
-      const uint32_t m = sm.T_meta[k];
-      if ((m >> 4) & 0xf) { clv = sm.T_lv[k]; clpos = k * E + (int)((m >> 12) & 7); break; }
+    double Jc = 0.0;
+    if (RATE) {
+      for (int k = t - 1; k >= 0; --k) {
+        const uint32_t m = sm.T_meta[k];
+        if ((m >> 4) & 0xf) { clv = sm.T_lv[k]; clpos = k * E + (int)((m >> 12) & 7); break; }
+      }
+      Jc = (c_cn > 0 && clpos >= 0) ? delta_of(c_fv, clv) : 0.0;
+      sm.T_tj[t] = sm.T_di[t] + Jc;
+      __syncthreads();
     }
-    const double Jc = (c_cn > 0 && clpos >= 0) ? delta_of(c_fv, clv) : 0.0;
-    sm.T_tj[t] = sm.T_di[t] + Jc;
-    __syncthreads();
 
     const int clb = wl[E - 1] >= 0 ? (wl[E - 1] >> 3) : t;   // chunk of the last output's window start
     const int64_t obase = tile_lo + e0;                    // flat index of the thread's first output
@@ -389,6 +401,15 @@ ragged_fast_kernel(const RParams p, int64_t n_tiles, int tiles_per_cta) {
   }
 }
 
+template <bool ROLL, bool RATE>
+int launch_as(const RParams& p, int64_t n_tiles, int64_t grid, int64_t tpc, cudaStream_t st) {
+  PMX_CUDA(cudaFuncSetAttribute(ragged_fast_kernel<ROLL, RATE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)sizeof(Smem<ROLL, RATE>)));
+  ragged_fast_kernel<ROLL, RATE><<<(unsigned)grid, NT, sizeof(Smem<ROLL, RATE>), st>>>(p, n_tiles, (int)tpc);
+  PMX_LAUNCH_CHECK();
+  return PMX_OK;
+}
+
 bool aligned32(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 31) == 0; }
 
 }  // namespace
@@ -404,9 +425,10 @@ int launch_ragged_fast(const pmx_ctx* ctx, const RParams& p, cudaStream_t st) {
   if (ctas > n_tiles) ctas = n_tiles;
   const int64_t tpc = (n_tiles + ctas - 1) / ctas;
   const int64_t grid = (n_tiles + tpc - 1) / tpc;
-  PMX_CUDA(cudaFuncSetAttribute(ragged_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem)));
-  ragged_fast_kernel<<<(unsigned)grid, NT, sizeof(Smem), st>>>(p, n_tiles, (int)tpc);
-  PMX_LAUNCH_CHECK();
+  const bool roll = p.o_min || p.o_max || p.o_mean || p.o_cnt, rate = p.o_inc || p.o_rate;
+  if (roll && rate) return launch_as<true, true>(p, n_tiles, grid, tpc, st);
+  if (roll) return launch_as<true, false>(p, n_tiles, grid, tpc, st);
+  if (rate) return launch_as<false, true>(p, n_tiles, grid, tpc, st);
   return PMX_OK;
 }
 
