@@ -192,14 +192,15 @@ tokd_count_kernel(const uint8_t* __restrict__ body, uint64_t len, ChunkSum* __re
   if (lane == 0) sums[chunk] = s;
 }
 
-// exclusive scans over a CTA of 1024 threads: XOR of one bit, sums of three counters.  *tot: CTA totals.
-__device__ __forceinline__ unsigned cta_xor_excl(unsigned bit, unsigned* s_w) {
+// exclusive scans over a CTA of 1024 threads: XOR of one bit, sum of a 64-bit word.  *tot: CTA totals.
+__device__ __forceinline__ unsigned cta_xor_excl(unsigned bit, unsigned* s_w, unsigned* tot) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const unsigned ballot = __ballot_sync(FULL, bit);
   if (lane == 0) s_w[warp] = __popc(ballot) & 1u;
   __syncthreads();
   const unsigned wb = __ballot_sync(FULL, s_w[lane]);       // 32 warps: one bit each
   __syncthreads();
+  *tot = __popc(wb) & 1u;
   return (__popc(ballot & ((1u << lane) - 1u)) ^ __popc(wb & ((1u << warp) - 1u))) & 1u;
 }
 __device__ __forceinline__ unsigned long long cta_sum_excl(unsigned long long v, unsigned long long* s_w,
@@ -219,7 +220,10 @@ __device__ __forceinline__ unsigned long long cta_sum_excl(unsigned long long v,
   return below + inc - v;
 }
 
-// One CTA: chunk states and output bases; envelope and balance checks; totals.
+// One CTA: chunk states and output bases; envelope and balance checks; totals.  The chunk summaries
+// are taken 1024 at a time, one per thread (coalesced); the state and the counts before each tile
+// are carried in registers.  Inside a tile the sample and series counts share one 64-bit scan
+// (at most 2^23 each).
 __global__ void __launch_bounds__(1024)
 tokd_scan_kernel(const uint8_t* __restrict__ body, uint64_t len, const ChunkSum* __restrict__ sums,
                  ChunkBase* __restrict__ bases, int64_t n_chunks, int64_t cap_samples, int64_t cap_series,
@@ -227,18 +231,34 @@ tokd_scan_kernel(const uint8_t* __restrict__ body, uint64_t len, const ChunkSum*
   __shared__ unsigned s_par[32];
   __shared__ unsigned long long s_sum[32];
   const int t = threadIdx.x;
-  const int64_t per = (n_chunks + 1023) / 1024;
-  const int64_t a = (int64_t)t * per, b = a + per < n_chunks ? a + per : n_chunks;
-  unsigned par = 0;
-  for (int64_t c = a; c < b; ++c) par ^= sums[c].parity;
-  const unsigned h0 = cta_xor_excl(par, s_par);             // state at the start of this thread's first chunk
-  unsigned h = h0;
-  unsigned long long smp = 0, ser = 0, br = 0;
-  for (int64_t c = a; c < b; ++c) { smp += sums[c].samples[h]; ser += sums[c].series[h]; br += sums[c].brackets[h]; h ^= sums[c].parity; }
-  unsigned long long x, y, z;
-  smp = cta_sum_excl(smp, s_sum, &x);
-  ser = cta_sum_excl(ser, s_sum, &y);
-  cta_sum_excl(br, s_sum, &z);
+  unsigned state = 0;                                       // inside a string at the start of the tile?
+  unsigned long long x = 0, y = 0;                          // samples, series before the tile
+  unsigned long long my_br = 0;                             // this thread's share of the '[' count
+  ChunkSum zero;
+  zero.parity = 0; zero.samples[0] = zero.samples[1] = zero.series[0] = zero.series[1] = zero.brackets[0] = zero.brackets[1] = 0;
+  ChunkSum nxt = t < n_chunks ? sums[t] : zero;
+  for (int64_t base = 0; base < n_chunks; base += 1024) {
+    const int64_t c = base + t;
+    const ChunkSum cs = nxt;
+    nxt = c + 1024 < n_chunks ? sums[c + 1024] : zero;      // the next tile's load flies during this tile's scans
+    unsigned tile_par;
+    const unsigned h = state ^ cta_xor_excl(cs.parity, s_par, &tile_par);      // state at the start of chunk c
+    unsigned long long tot;
+    const unsigned long long before =
+        cta_sum_excl((unsigned long long)(h ? cs.samples[1] : cs.samples[0]) |
+                     ((unsigned long long)(h ? cs.series[1] : cs.series[0]) << 32), s_sum, &tot);
+    my_br += h ? cs.brackets[1] : cs.brackets[0];
+    if (c < n_chunks) {
+      ChunkBase o;
+      o.in_string = h; o.pad = 0;
+      o.samples = (long long)(x + (before & 0xffffffffULL)); o.series = (long long)(y + (before >> 32));
+      bases[c] = o;
+    }
+    state ^= tile_par;
+    x += tot & 0xffffffffULL; y += tot >> 32;
+  }
+  unsigned long long z;
+  cta_sum_excl(my_br, s_sum, &z);
   if (t == 0) {
     // envelope: Prometheus' own encoding of a successful matrix / vector answer
     const char pre[] = "{\"status\":\"success\",\"data\":{\"resultType\":\"";
@@ -262,12 +282,6 @@ tokd_scan_kernel(const uint8_t* __restrict__ body, uint64_t len, const ChunkSum*
     if (!err && ((long long)x > cap_samples || (long long)y > cap_series)) err = ERR_CAPACITY;
     status[ST_SAMPLES] = (long long)x; status[ST_SERIES] = (long long)y; status[ST_ERROR] = err; status[ST_WHERE] = where;
     if (!err) series_off[y] = (long long)x;
-  }
-  h = h0;
-  for (int64_t c = a; c < b; ++c) {
-    ChunkBase o; o.in_string = h; o.pad = 0; o.samples = (long long)smp; o.series = (long long)ser;
-    bases[c] = o;
-    smp += sums[c].samples[h]; ser += sums[c].series[h]; h ^= sums[c].parity;
   }
 }
 
