@@ -23,8 +23,11 @@
 // the body and these arrays as they are.
 #include <stdint.h>
 #include "pmx_common.cuh"
+#include "byte_masks.h"
 
 namespace {
+
+using namespace pmx;
 
 constexpr int TT = 256;                 // threads per CTA
 constexpr int WARPS = TT / 32;
@@ -45,36 +48,6 @@ __device__ __forceinline__ unsigned char byte_at(const uint8_t* __restrict__ b, 
   return i < len ? b[i] : (unsigned char)0;
 }
 
-// bit k (k = 0..3) set iff byte k of w equals the byte repeated in pat4.  Exact: the zero-byte test
-// carries nothing from one byte into the next, and the multiply gathers bits 0, 8, 16, 24 into
-// bits 24..27 with no two partial products on the same bit.
-__device__ __forceinline__ unsigned eq4(uint32_t w, uint32_t pat4) {
-  const uint32_t x = w ^ pat4;
-  const uint32_t t = (x & 0x7f7f7f7fu) + 0x7f7f7f7fu;
-  const uint32_t z = ~(t | x) & 0x80808080u;
-  return ((z >> 7) * 0x01020408u) >> 24;
-}
-__device__ __forceinline__ unsigned eq16(const uint32_t* w, uint32_t pat4) {
-  return eq4(w[0], pat4) | (eq4(w[1], pat4) << 4) | (eq4(w[2], pat4) << 8) | (eq4(w[3], pat4) << 12);
-}
-// bit k set iff bit 5 of byte k is set ('{' against '[')
-__device__ __forceinline__ unsigned bit5_16(const uint32_t* w) {
-  unsigned m = 0;
-#pragma unroll
-  for (int j = 0; j < 4; ++j) m |= ((((w[j] >> 5) & 0x01010101u) * 0x01020408u) >> 24) << (4 * j);
-  return m;
-}
-// '[' or '{': the two differ in bit 5 alone
-__device__ __forceinline__ unsigned open_mask(const uint32_t* w) {
-  const uint32_t v[4] = {w[0] | 0x20202020u, w[1] | 0x20202020u, w[2] | 0x20202020u, w[3] | 0x20202020u};
-  return eq16(v, 0x7b7b7b7bu);
-}
-// may this word hold the byte?  (false positives allowed, no false negatives)
-__device__ __forceinline__ uint32_t maybe4(uint32_t w, uint32_t pat4) {
-  const uint32_t x = w ^ pat4;
-  return (x - 0x01010101u) & ~x & 0x80808080u;
-}
-
 // The 16 bytes of this lane's segment (zeros past the end), as four words.
 __device__ __forceinline__ void load_words(const uint8_t* __restrict__ body, uint64_t len, uint64_t pos, uint32_t* w) {
   w[0] = w[1] = w[2] = w[3] = 0;
@@ -85,12 +58,6 @@ __device__ __forceinline__ void load_words(const uint8_t* __restrict__ body, uin
     for (int k = 0; k < SEG; ++k)
       if (pos + k < len) w[k >> 2] |= (uint32_t)body[pos + k] << (8 * (k & 3));
   }
-}
-
-// byte k (0..15) of the segment
-__device__ __forceinline__ unsigned seg_byte(const uint32_t* w, int k) {
-  const uint32_t lo = (k & 8) ? w[2] : w[0], hi = (k & 8) ? w[3] : w[1];
-  return ((k & 4 ? hi : lo) >> (8 * (k & 3))) & 0xffu;
 }
 
 // Mask of the segment's unescaped quotes.  A quote is escaped iff an odd run of backslashes ends
@@ -116,14 +83,6 @@ __device__ __forceinline__ unsigned quote_mask(const uint8_t* __restrict__ body,
     }
   }
   return q;
-}
-
-// positions of the segment that lie inside a string when the segment begins outside one; bit 16 of
-// the result: the segment's own parity
-__device__ __forceinline__ unsigned inside_mask(unsigned q) {
-  unsigned x = q;
-  x ^= x << 1; x ^= x << 2; x ^= x << 4; x ^= x << 8;           // inclusive prefix parity
-  return (x << 1) & 0x1ffffu;
 }
 
 __device__ __forceinline__ bool starts_number(unsigned c) { return (c >= '0' && c <= '9') || c == '-'; }

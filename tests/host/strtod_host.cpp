@@ -50,3 +50,23 @@ extern "C" int host_scan_ts_ms(const uint8_t* p, int64_t len, uint8_t term, int6
   uint64_t W[4]; memcpy(W, buf, 32);
   return pmx::fast_ts_ms_scan(W, term, out);
 }
+
+// the byte-class masks of the device tokenizer (csrc/byte_masks.h) over one 16-byte segment:
+// out[0] quotes, out[1] '[' or '{', out[2] bit 5 of every byte, out[3] commas, out[4] inside_mask(out[0]),
+// out[5] = bit k set iff word k>>2 "may hold" a backslash (maybe4), out[6..21] = seg_byte(k)
+#include "../../k8s_rocm_metrics_dashboard_b200/csrc/byte_masks.h"
+extern "C" void host_segment_masks(const uint8_t* seg, uint32_t* out) {
+  uint32_t w[4];
+  memcpy(w, seg, 16);
+  out[0] = pmx::eq16(w, 0x22222222u);
+  out[1] = pmx::open_mask(w);
+  out[2] = pmx::bit5_16(w);
+  out[3] = pmx::eq16(w, 0x2c2c2c2cu);
+  out[4] = pmx::inside_mask(out[0]);
+  out[5] = 0;
+  for (int j = 0; j < 4; ++j) if (pmx::maybe4(w[j], 0x5c5c5c5cu)) out[5] |= 0xfu << (4 * j);
+  for (int k = 0; k < 16; ++k) out[6 + k] = pmx::seg_byte(w, k);
+}
+extern "C" void host_segment_masks_many(const uint8_t* segs, int64_t n, uint32_t* out) {
+  for (int64_t i = 0; i < n; ++i) host_segment_masks(segs + 16 * i, out + 22 * i);
+}

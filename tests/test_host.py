@@ -308,3 +308,47 @@ def test_interned_label_table_equals_json_loads():
         n1, g1 = _group_ids(table, keys)
         n2, g2 = _group_ids(ref, keys)
         assert n1 == n2 and np.array_equal(g1, g2), keys
+
+
+def test_byte_class_masks_of_the_device_tokenizer_are_exact(host_lib):
+    """csrc/byte_masks.h builds the masks of a 16-byte segment four bytes at a time.  Against a
+    byte-by-byte restatement: random bytes, bytes drawn from the neighbours of every class byte
+    (one code point away, bit 5 / bit 7 flipped, 0x00, 0x01, 0x7f, 0x80, 0xff), and every byte value
+    at every position of a word beside a matching byte (where a carry or borrow would leak)."""
+    lib = host_lib
+    lib.host_segment_masks_many.argtypes = [C.c_void_p, C.c_int64, C.c_void_p]
+    rng = np.random.default_rng(3)
+    cls = [0x22, 0x5b, 0x7b, 0x2c, 0x5c]
+    near = sorted({(c + d) & 0xff for c in cls for d in (-1, 0, 1)} | {c ^ 0x20 for c in cls} | {c ^ 0x80 for c in cls}
+                  | {0x00, 0x01, 0x7f, 0x80, 0xff, 0x30, 0x2d})
+    segs = [rng.integers(0, 256, size=(20000, 16), dtype=np.uint8),
+            np.array(near, dtype=np.uint8)[rng.integers(0, len(near), size=(60000, 16))]]
+    pairs = np.zeros((len(cls) * 256 * 4 * 2, 16), dtype=np.uint8)
+    i = 0
+    for c in cls:
+        for v in range(256):
+            for pos in range(4):
+                for side in (0, 1):                                 # the matching byte below / above the probe
+                    row = np.full(16, 0x41, dtype=np.uint8)
+                    row[4 + pos] = v
+                    other = 4 + (pos + (1 if side else -1)) % 4
+                    row[other] = c
+                    pairs[i] = row; i += 1
+    segs = np.ascontiguousarray(np.concatenate(segs + [pairs]))
+    out = np.zeros((len(segs), 22), dtype=np.uint32)
+    lib.host_segment_masks_many(segs.ctypes.data, len(segs), out.ctypes.data)
+    bit = (1 << np.arange(16, dtype=np.uint32))
+    mask = lambda cond: (cond.astype(np.uint32) * bit).sum(axis=1).astype(np.uint32)
+    np.testing.assert_array_equal(out[:, 0], mask(segs == 0x22))
+    np.testing.assert_array_equal(out[:, 1], mask((segs == 0x5b) | (segs == 0x7b)))
+    np.testing.assert_array_equal(out[:, 2], mask((segs & 0x20) != 0))
+    np.testing.assert_array_equal(out[:, 3], mask(segs == 0x2c))
+    # inside a string at position k (segment begins outside): odd number of quotes before k; bit 16: parity of all
+    q = (segs == 0x22).astype(np.uint32)
+    before = np.concatenate([np.zeros((len(segs), 1), dtype=np.uint32), np.cumsum(q, axis=1)], axis=1) & 1
+    want_inside = (before * (1 << np.arange(17, dtype=np.uint32))).sum(axis=1).astype(np.uint32)
+    np.testing.assert_array_equal(out[:, 4], want_inside)
+    # maybe4: never misses a backslash (false positives are allowed)
+    has_bs = mask(np.repeat((segs.reshape(-1, 4, 4) == 0x5c).any(axis=2), 4, axis=1))
+    assert np.all((out[:, 5] & has_bs) == has_bs)
+    np.testing.assert_array_equal(out[:, 6:], segs.astype(np.uint32))
