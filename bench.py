@@ -297,9 +297,10 @@ def e2e_text_block(eng, steps=5):
     def one():
         nonlocal out
         tok = eng.tokenize_device(pinned)                                 # H2D of the body + the cut
-        labels = tok.labels()
-        names, gid = adapter._group_ids(labels, ("__name__",))             # integer work on the interned table, as aggregate_range does
-        ts, val = eng.parse(tok)
+        ts, val, decoded = eng.parse_async(tok)                            # the decode kernel runs while the host interns the labels,
+        labels = tok.labels()                                             # as aggregate_range does
+        names, gid = adapter._group_ids(labels, ("__name__",))             # integer work on the interned table
+        decoded()                                                         # the kernel's verdict on malformed tokens
         out = eng.fused(ts, val, tok.series_off, START_MS, STEP_MS, N_STEPS, WINDOW_STEPS, LOOKBACK_MS, out=out)
         pg = group_index(gid, len(names))
         sm, cnt, mn, mx, mean = eng.group_reduce(out["aligned"], None, len(names), perm_goff=pg)

@@ -219,8 +219,13 @@ def aggregate_range(body, start_ms, step_ms, n_steps, window_ms, lookback_ms=DEF
     """
     eng = eng or engine()
     tok = _range_tokens(eng, body, tokenizer)
-    labels = tok.labels()
-    ts, val = eng.parse(tok)
+    if hasattr(tok, "d_text"):                                        # tokens on the device: the decode kernel runs
+        ts, val, decoded = eng.parse_async(tok)                       # while the host interns the label sets
+        labels = tok.labels()
+        decoded()                                                     # raises for a malformed token, like parse
+    else:
+        labels = tok.labels()
+        ts, val = eng.parse(tok)
     return _aggregate_series(eng, labels, ts, val, tok.series_off, start_ms, step_ms, n_steps, window_ms,
                              lookback_ms, quantiles, as_frame, group_keys)
 

@@ -323,9 +323,41 @@ class Engine:
         self.launches += 1
         return ts, val, bad.cpu().tolist()
 
+    def parse_async(self, tok, want_ts=True):
+        """``parse`` of DeviceTokens in two halves: the kernel is launched and (ts | None, val, finish)
+        returned at once; ``finish()`` waits for the kernel's verdict and raises what ``parse`` would
+        raise.  Host work that does not need the numbers (the label table) runs between the two;
+        nothing may USE ts / val before ``finish()`` has returned."""
+        t = self.torch
+        if not isinstance(tok, DeviceTokens):
+            raise TypeError("parse_async takes DeviceTokens (Engine.tokenize_device)")
+        n = tok.n_samples
+        val = self._empty((n,), t.float64)
+        ts = self._empty((n,), t.int64) if want_ts else None
+        bad = self._empty((2,), t.int64)
+        _abi.check(self.lib.pmx_parse_samples(self.ctx, self._ptr(tok.d_text), tok.d_text.numel(),
+                                              self._ptr(tok.d_ts_off if want_ts else None), self._ptr(tok.d_val_off), n,
+                                              self._ptr(ts), self._ptr(val), self._ptr(bad), self._stream()))
+        self.launches += 1
+        pool = self.__dict__.setdefault("_bad_pool", [])
+        host = pool.pop() if pool else t.empty((2,), dtype=t.int64).pin_memory()
+        host.copy_(bad, non_blocking=True)
+        ev = t.cuda.Event(); ev.record()
+
+        def finish():
+            ev.synchronize()
+            b = host.tolist()
+            pool.append(host)
+            self._raise_bad_token(tok, b, n, want_ts)
+        return ts, val, finish
+
     def _parse_device(self, tok, want_ts):
         n = tok.n_samples
         ts, val, b = self._parse_launch(tok.d_text, tok.d_ts_off if want_ts else None, tok.d_val_off, n, want_ts)
+        self._raise_bad_token(tok, b, n, want_ts)
+        return ts, val
+
+    def _raise_bad_token(self, tok, b, n, want_ts):
         if b[0] < n:
             o = int(tok.d_val_off[b[0]].item()) & 0xffffffff
             tail = bytes(tok.body[o:o + 4096])               # (bytes, or the uint8 view of a pinned body)
@@ -335,7 +367,6 @@ class Engine:
             raise err
         if want_ts and b[1] < n:
             raise ValueError(f"malformed timestamp in sample {b[1]}")
-        return ts, val
 
     # ------------------------------------------------------------------ K2
     def align(self, ts, val, off, start_ms, step_ms, n_steps, lookback_ms=DEFAULT_LOOKBACK_MS, want_idx=True):

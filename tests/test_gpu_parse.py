@@ -115,3 +115,40 @@ def test_pinned_tensor_body_equals_bytes_body(eng):
     bad[k] = ord("x")
     with pytest.raises(ValueError, match="could not convert string to float"):
         eng.parse(eng.tokenize_device(torch.frombuffer(bad, dtype=torch.uint8).pin_memory()))
+
+
+def test_parse_async_gives_parse_s_numbers_and_errors(eng):
+    """parse_async (decode kernel in flight while the host interns the labels): the same numbers as
+    parse, the same ValueError at finish(), and aggregate_range over device tokens still refuses a
+    malformed body."""
+    import torch
+    from k8s_rocm_metrics_dashboard_b200 import adapter, synth
+    d = synth.dense(1, 2, 3, 50, seed=4)
+    body = synth.to_matrix_json(d["labels"], d["ts"], d["val"], d["off"])
+    tok = eng.tokenize_device(body)
+    t0, v0 = eng.parse(tok)
+    t1, v1, done = eng.parse_async(tok)
+    labels = tok.labels()
+    done()
+    assert torch.equal(t0, t1) and torch.equal(v0.view(torch.int64), v1.view(torch.int64)) and len(labels) == 6
+    _, v2, done = eng.parse_async(tok, want_ts=False)
+    done()
+    assert torch.equal(v0.view(torch.int64), v2.view(torch.int64))
+    with pytest.raises(TypeError):
+        from k8s_rocm_metrics_dashboard_b200 import tokenize
+        eng.parse_async(tokenize(body))
+    bad = bytearray(body)
+    k = bad.find(b'"', bad.find(b'"values":[[') + 11) + 1
+    bad[k] = ord("x")
+    _, _, done = eng.parse_async(eng.tokenize_device(bytes(bad)))
+    with pytest.raises(ValueError, match="could not convert string to float"):
+        done()
+    step = int(d["step_ms"])
+    kw = dict(start_ms=int(d["start_ms"]), step_ms=step, n_steps=int(d["n_steps"]), window_ms=5 * step, as_frame=False, eng=eng)
+    tidy_d, summ_d = adapter.aggregate_range(body, tokenizer="device", **kw)
+    tidy_h, summ_h = adapter.aggregate_range(body, tokenizer="host", **kw)
+    for k2 in ("value", "roll_mean", "rate"):
+        np.testing.assert_array_equal(np.asarray(tidy_d[k2]).view(np.int64), np.asarray(tidy_h[k2]).view(np.int64))
+    np.testing.assert_array_equal(summ_d["count"], summ_h["count"])
+    with pytest.raises(ValueError, match="could not convert string to float"):
+        adapter.aggregate_range(bytes(bad), tokenizer="device", **kw)
