@@ -116,7 +116,6 @@ hist_kernel(const double* __restrict__ x, int64_t n_steps, const int32_t* __rest
   __shared__ unsigned int s_bitmap[BINS / 32];             // previous digits carried by some target prefix
   __shared__ Geom s_geom;                                  // where this pass looks in the current segment's keys
   const int64_t s0 = (int64_t)blockIdx.x * rows_per_cta;
-  const int lane = threadIdx.x & 31;
   const int n_h = pass == 0 ? 1 : n_t;                     // histograms per segment in global memory
   int cur_seg = -1;
   if (mode == 2 && *cand_overflow == 0) return;            // every candidate list is complete (the usual case)
@@ -398,7 +397,6 @@ cand_hist_kernel(const unsigned long long* __restrict__ cand, const unsigned int
   if (gm.bits == 0) return;
   const int shift = gm.shift, pshift = gm.pshift;
   const unsigned mask = (1u << gm.bits) - 1u;
-  const int lane = threadIdx.x & 31;
   if (threadIdx.x == 0) load_prefixes(state, sw, sg, n_t, pass, s_uprefix, s_umap, s_urep, &s_nu);
   __syncthreads();
   const int nu = s_nu;
