@@ -253,10 +253,24 @@ def _group_ids(labels, group_keys):
             ids = labels.column(k).astype(np.int64)
             ids[ids < 0] = empty
             cols.append(rank[ids])
-        mat = np.stack(cols, axis=1) if cols else np.zeros((len(labels), 0), dtype=np.int64)
-        uniq, inv = np.unique(mat, axis=0, return_inverse=True)
         strings = labels.strings + [""]
-        names = [tuple(strings[order[r]] for r in row) for row in uniq.tolist()]
+        base = len(strings)
+        if cols and base ** len(cols) < (1 << 62):                    # rows as one integer each: a 1-D unique
+            key = cols[0]
+            for c in cols[1:]:
+                key = key * base + c                                  # the first key is the most significant
+            uk, inv = np.unique(key, return_inverse=True)
+            digits = []
+            for _ in cols:
+                digits.append(uk % base)
+                uk = uk // base
+            uniq = np.stack(digits[::-1], axis=1)
+        else:
+            mat = np.stack(cols, axis=1) if cols else np.zeros((len(labels), 0), dtype=np.int64)
+            uniq, inv = np.unique(mat, axis=0, return_inverse=True)
+        ranked = [strings[i] for i in order.tolist()]                 # the strings in rank order
+        per_key = [[ranked[r] for r in uniq[:, j].tolist()] for j in range(uniq.shape[1])]
+        names = list(zip(*per_key)) if per_key else [()] * len(uniq)
         return names, inv.reshape(-1).astype(np.int32)
     tuples = [tuple(l.get(k, "") for k in group_keys) for l in labels]
     names = sorted(set(tuples))

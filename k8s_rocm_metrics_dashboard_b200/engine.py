@@ -67,16 +67,22 @@ class LabelTable:
 
 
 def _label_table(body, spans):
-    """pmx_labels_intern on the metric spans of a body (bytes or uint8 array)."""
+    """pmx_labels_intern on the metric spans of a body (bytes or uint8 array).  ``spans``: a list of
+    (offset, length) or the two uint32 arrays themselves (what the tokenizers produce: no per-series
+    Python object on the way)."""
     lib = _abi.lib()
-    n = len(spans)
+    arrays = isinstance(spans, tuple) and len(spans) == 2 and isinstance(spans[0], np.ndarray)
+    n = len(spans[0]) if arrays else len(spans)
     if isinstance(body, (bytes, bytearray)):
         raw, raw_len = body, len(body)
     else:                                                    # uint8 array (e.g. the view of a pinned tensor): no copy
         arr = np.ascontiguousarray(body, dtype=np.uint8)
         raw, raw_len = C.c_void_p(arr.ctypes.data), arr.size
-    m_off = np.fromiter((o for o, _ in spans), dtype=np.uint32, count=n)
-    m_len = np.fromiter((l for _, l in spans), dtype=np.uint32, count=n)
+    if arrays:
+        m_off, m_len = (np.ascontiguousarray(a, dtype=np.uint32) for a in spans)
+    else:
+        m_off = np.fromiter((o for o, _ in spans), dtype=np.uint32, count=n)
+        m_len = np.fromiter((l for _, l in spans), dtype=np.uint32, count=n)
     total = int(m_len.sum())
     cap_pairs = total // 6 + 1                               # "k":"v", is at least 8 bytes; be generous
     pair_off = np.empty(n + 1, dtype=np.int64)
@@ -105,6 +111,7 @@ class Tokens:
     series_off: np.ndarray      # int64[S+1]
     metric_spans: list          # [(off, len)] of each series' "metric" object in the body
     result_type: str            # "matrix" | "vector"
+    span_arrays: tuple = None   # the same spans as (uint32[S] offsets, uint32[S] lengths)
 
     @property
     def n_samples(self):
@@ -116,7 +123,7 @@ class Tokens:
 
     def labels(self):
         """The label sets, interned (``LabelTable``: indexes and iterates like a list of dicts)."""
-        return _label_table(self.flat, self.metric_spans)
+        return _label_table(self.flat, self.span_arrays if self.span_arrays is not None else self.metric_spans)
 
 
 @dataclass
@@ -130,6 +137,7 @@ class DeviceTokens:
     series_off: np.ndarray      # int64[S+1] (host)
     metric_spans: list
     result_type: str
+    span_arrays: tuple = None   # the same spans as (uint32[S] offsets, uint32[S] lengths)
 
     @property
     def n_samples(self):
@@ -141,7 +149,7 @@ class DeviceTokens:
 
     def labels(self):
         """The label sets, interned (``LabelTable``: indexes and iterates like a list of dicts)."""
-        return _label_table(self.body, self.metric_spans)
+        return _label_table(self.body, self.span_arrays if self.span_arrays is not None else self.metric_spans)
 
 
 _TOKD_ERRORS = {1: "not a successful Prometheus matrix/vector answer in compact encoding",
@@ -185,9 +193,9 @@ def tokenize(body: bytes, threads=None) -> Tokens:
     flat = np.frombuffer(body, dtype=np.uint8)
     if ne:
         flat = np.concatenate([flat, extra[:ne]])
+    mo, ml = m_off[:nr].astype(np.uint32), m_len[:nr].astype(np.uint32)
     return Tokens(flat, ts_off[:ns].copy(), val_off[:ns].copy(), series_off[:nr + 1].copy(),
-                  list(zip(m_off[:nr].tolist(), m_len[:nr].tolist())),
-                  "matrix" if res.result_type == 0 else "vector")
+                  list(zip(mo.tolist(), ml.tolist())), "matrix" if res.result_type == 0 else "vector", (mo, ml))
 
 
 def group_index(group_id, n_groups):
@@ -280,9 +288,10 @@ class Engine:
         if err:
             raise ValueError("pmx_tokenize_device: " + _TOKD_ERRORS.get(err, f"error {err}").format(where=where))
         soff = series_off[:nr + 1].cpu().numpy()
-        spans = list(zip(m_off[:nr].cpu().numpy().view(np.uint32).tolist(), m_len[:nr].cpu().numpy().view(np.uint32).tolist()))
+        mo, ml = m_off[:nr].cpu().numpy().view(np.uint32), m_len[:nr].cpu().numpy().view(np.uint32)
+        spans = list(zip(mo.tolist(), ml.tolist()))
         kind = "matrix" if bytes(body[42:48]) == b"matrix" else "vector"
-        return DeviceTokens(body, text, ts_off[:ns], val_off[:ns], soff, spans, kind)
+        return DeviceTokens(body, text, ts_off[:ns], val_off[:ns], soff, spans, kind, (mo, ml))
 
     def parse(self, tok, want_ts=True):
         """Device decode of all value (and timestamp) tokens.  Returns (ts int64[N] | None, val float64[N]).

@@ -352,3 +352,39 @@ def test_byte_class_masks_of_the_device_tokenizer_are_exact(host_lib):
     has_bs = mask(np.repeat((segs.reshape(-1, 4, 4) == 0x5c).any(axis=2), 4, axis=1))
     assert np.all((out[:, 5] & has_bs) == has_bs)
     np.testing.assert_array_equal(out[:, 6:], segs.astype(np.uint32))
+
+
+def test_group_ids_on_the_interned_table_equal_the_dict_walk():
+    """adapter._group_ids: the integer path (one 1-D unique over rows folded into one key) must give
+    the names and ids of the plain walk over label dicts, for one and several keys, missing labels
+    and an empty-string value."""
+    import random
+    from k8s_rocm_metrics_dashboard_b200 import adapter
+    rnd = random.Random(4)
+    labels = []
+    for i in range(300):
+        l = {"__name__": rnd.choice(["amd_gpu_power", "amd_gpu_edge_temperature", "amd_gpu_gfx_activity", ""]),
+             "instance": f"node{rnd.randrange(7)}:9400", "gpu_id": str(rnd.randrange(8))}
+        if rnd.random() < 0.2:
+            del l["gpu_id"]
+        if rnd.random() < 0.1:
+            del l["__name__"]
+        labels.append(l)
+    ts = np.arange(len(labels), dtype=np.int64) * 1000 + 1_700_000_000_000
+    body = synth.to_matrix_json(labels, ts, np.ones(len(labels)), np.arange(len(labels) + 1, dtype=np.int64))
+    tok = tokenize(body)
+    table = tok.labels()
+    assert table == labels and tok.span_arrays is not None
+    assert tok.metric_spans == list(zip(tok.span_arrays[0].tolist(), tok.span_arrays[1].tolist()))
+    # the device tokenizer's result reads its labels the same way (body + the two span arrays)
+    from k8s_rocm_metrics_dashboard_b200.engine import DeviceTokens
+    dt = DeviceTokens(body, None, None, None, tok.series_off, tok.metric_spans, "matrix",
+                      (tok.span_arrays[0].view(np.int32).view(np.uint32), tok.span_arrays[1].copy()))
+    assert dt.labels() == labels and dt.n_series == len(labels)
+    assert DeviceTokens(np.frombuffer(body, dtype=np.uint8), None, None, None, tok.series_off, tok.metric_spans,
+                        "matrix").labels() == labels                  # a uint8 view of the body, spans as a list
+    for keys in (("__name__",), ("instance", "gpu_id"), ("__name__", "instance", "gpu_id"), ("absent",), ()):
+        n1, g1 = adapter._group_ids(table, keys)
+        n2, g2 = adapter._group_ids(labels, keys)
+        assert n1 == n2, keys
+        np.testing.assert_array_equal(g1, g2)
